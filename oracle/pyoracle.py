@@ -1,0 +1,227 @@
+"""oracle/pyoracle.py -- TEST INFRASTRUCTURE. ctypes bindings to the two CPU checkers:
+
+  * `Oracle`  : oracle/_build/libfec_oracle.so, the plain-C restatement (fec_oracle.c / fec_tx.c); always buildable.
+  * `Ref`     : oracle/_ref/libref_fec.so, the UNMODIFIED reference sources + ref_shim.cpp; built only where
+                /root/reference exists (the build container) and shipped to the GPU box as a prebuilt file.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "_build", "libfec_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libref_fec.so")
+
+ALL_Z = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48, 52, 56, 60,
+         64, 72, 80, 88, 96, 104, 112, 120, 128, 144, 160, 176, 192, 208, 224, 240, 256, 288, 320, 352, 384]
+CRC24A, CRC24B, CRC16 = 0, 1, 2
+CRC_LEN = {CRC24A: 24, CRC24B: 24, CRC16: 16}
+
+
+def build_oracle():
+    subprocess.check_call(["make", "-s", "-C", HERE, "oracle"])
+
+
+def build_ref():
+    """Builds oracle/_ref when the reference tree is present; returns True if the .so exists afterwards."""
+    if os.path.isdir("/root/reference/lib"):
+        subprocess.check_call(["make", "-s", "-j8", "-C", HERE, "ref"])
+    return os.path.exists(REF_SO)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def dims(bg, Z):
+    kb, nb = (22, 66) if bg == 1 else (10, 50)
+    return kb * Z, nb * Z
+
+
+class Oracle:
+    """The C restatement (kind "port")."""
+
+    def __init__(self):
+        if not os.path.exists(ORACLE_SO):
+            build_oracle()
+        self.lib = C.CDLL(ORACLE_SO)
+        L = self.lib
+        L.orc_crc.restype = C.c_uint32
+        L.orc_quantize.restype = C.c_int8
+        L.orc_quantize.argtypes = [C.c_float, C.c_float]
+
+    def crc(self, poly, packed, nbits):
+        packed = np.ascontiguousarray(packed, np.uint8)
+        return int(self.lib.orc_crc(poly, _p(packed), C.c_uint32(nbits)))
+
+    def rate_dematch(self, bg, Z, soft, llr, new_data, rv, qm, Nref, fillers):
+        assert soft.dtype == np.int8 and soft.flags.c_contiguous and soft.size == dims(bg, Z)[1]
+        llr = np.ascontiguousarray(llr, np.int8)
+        r = self.lib.orc_rate_dematch(bg, Z, _p(soft), _p(llr), C.c_uint32(llr.size), int(new_data), C.c_uint32(rv),
+                                      C.c_uint32(qm), C.c_uint32(Nref), C.c_uint32(fillers))
+        assert r == 0
+        return soft
+
+    def decode(self, bg, Z, llr, fillers=0, crc_poly=-1, max_iter=6, scaling=0.8, out=None):
+        K, _ = dims(bg, Z)
+        llr = np.ascontiguousarray(llr, np.int8)
+        if out is None:
+            out = np.zeros((K + 7) // 8, np.uint8)
+        it = self.lib.orc_decode(bg, Z, _p(out), _p(llr), C.c_uint32(llr.size), C.c_uint32(fillers), crc_poly,
+                                 C.c_uint32(max_iter), C.c_float(scaling))
+        return it, out
+
+    def cb_chain(self, bg, Z, soft, llr, new_data, rv, qm, Nref, fillers, crc_poly, max_iter, early_stop):
+        K, _ = dims(bg, Z)
+        llr = np.ascontiguousarray(llr, np.int8)
+        out = np.zeros((K + 7) // 8, np.uint8)
+        it = self.lib.orc_cb_chain(bg, Z, _p(soft), _p(llr), C.c_uint32(llr.size), int(new_data), C.c_uint32(rv),
+                                   C.c_uint32(qm), C.c_uint32(Nref), C.c_uint32(fillers), crc_poly,
+                                   C.c_uint32(max_iter), int(early_stop), _p(out))
+        return it, out
+
+    # ---- transmit side (input generation) ----
+    def random_bits(self, n, seed):
+        b = np.zeros(n, np.uint8)
+        self.lib.orc_random_bits(_p(b), C.c_uint32(n), C.c_uint64(seed))
+        return b
+
+    def make_message(self, bg, Z, fillers, crc_poly, seed):
+        """Random payload + CB CRC + zero fillers -> K unpacked bits."""
+        K, _ = dims(bg, Z)
+        n_pay = K - fillers - CRC_LEN[crc_poly]
+        msg = np.zeros(K + 32, np.uint8)
+        msg[:n_pay] = self.random_bits(n_pay, seed)
+        self.lib.orc_crc_attach_bits(crc_poly, _p(msg), C.c_uint32(n_pay))
+        return msg[:K].copy()
+
+    def encode(self, bg, Z, msg):
+        _, N = dims(bg, Z)
+        msg = np.ascontiguousarray(msg, np.uint8)
+        cb = np.zeros(N, np.uint8)
+        r = self.lib.orc_encode(bg, Z, _p(msg), _p(cb))
+        assert r == 0, r
+        return cb
+
+    def rate_match(self, bg, Z, cb, E, rv, qm, Nref, fillers):
+        cb = np.ascontiguousarray(cb, np.uint8)
+        out = np.zeros(E, np.uint8)
+        r = self.lib.orc_rate_match(bg, Z, _p(cb), _p(out), C.c_uint32(E), C.c_uint32(rv), C.c_uint32(qm),
+                                    C.c_uint32(Nref), C.c_uint32(fillers))
+        assert r == 0
+        return out
+
+    def awgn_llr(self, bits, esn0_db, seed):
+        bits = np.ascontiguousarray(bits, np.uint8)
+        llr = np.zeros(bits.size, np.int8)
+        self.lib.orc_awgn_llr(_p(bits), _p(llr), C.c_uint32(bits.size), C.c_float(esn0_db), C.c_uint64(seed))
+        return llr
+
+    def make_case(self, bg, Z, E, rv=0, qm=1, Nref=0, fillers=0, crc_poly=CRC24B, esn0_db=2.0, seed=0):
+        """message -> encode -> rate match -> AWGN LLRs. Returns (llr[E], msg_bits[K])."""
+        msg = self.make_message(bg, Z, fillers, crc_poly, seed)
+        cb = self.encode(bg, Z, msg)
+        tx = self.rate_match(bg, Z, cb, E, rv, qm, Nref, fillers)
+        return self.awgn_llr(tx, esn0_db, seed + 7919), msg
+
+
+class Ref:
+    """The reference itself (kind "reference"). impl: 0 generic, 1 avx2, 2 avx512, 3 auto."""
+    GENERIC, AVX2, AVX512, AUTO = 0, 1, 2, 3
+
+    def __init__(self):
+        if not os.path.exists(REF_SO):
+            raise FileNotFoundError(REF_SO)
+        self.lib = C.CDLL(REF_SO)
+        self.lib.ref_crc.restype = C.c_uint
+        self.lib.ref_batch_chain.restype = C.c_double
+        self.lib.ref_tbs.restype = C.c_uint
+        self.lib.ref_tbs.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_float, C.c_uint, C.c_uint]
+
+    @staticmethod
+    def available():
+        return os.path.exists(REF_SO)
+
+    def impl_available(self, impl):
+        return bool(self.lib.ref_impl_available(impl))
+
+    def graph(self, bg, Z):
+        cols = np.zeros((46, 20), np.uint16)
+        sh = np.zeros((46, 20), np.uint16)
+        deg = np.zeros(46, np.uint16)
+        M = self.lib.ref_graph(bg, Z, _p(cols), _p(sh), _p(deg))
+        return M, cols, sh, deg
+
+    def crc(self, poly, packed, nbits):
+        packed = np.ascontiguousarray(packed, np.uint8)
+        return int(self.lib.ref_crc(poly, _p(packed), C.c_uint(nbits)))
+
+    def encode(self, bg, Z, msg):
+        _, N = dims(bg, Z)
+        msg = np.ascontiguousarray(msg, np.uint8)
+        cb = np.zeros(N, np.uint8)
+        self.lib.ref_encode(bg, Z, _p(msg), _p(cb))
+        return cb
+
+    def rate_match(self, bg, Z, cb, E, rv, qm, Nref, fillers):
+        cb = np.ascontiguousarray(cb, np.uint8)
+        out = np.zeros(E, np.uint8)
+        self.lib.ref_rate_match(bg, Z, _p(cb), _p(out), C.c_uint(E), C.c_uint(rv), C.c_uint(qm), C.c_uint(Nref),
+                                C.c_uint(fillers))
+        return out
+
+    def rate_dematch(self, bg, Z, soft, llr, new_data, rv, qm, Nref, fillers, impl=0):
+        llr = np.ascontiguousarray(llr, np.int8)
+        assert soft.dtype == np.int8 and soft.flags.c_contiguous
+        r = self.lib.ref_rate_dematch(impl, bg, Z, _p(soft), _p(llr), C.c_uint(llr.size), int(new_data), C.c_uint(rv),
+                                      C.c_uint(qm), C.c_uint(Nref), C.c_uint(fillers))
+        assert r == 0
+        return soft
+
+    def decode(self, bg, Z, llr, fillers=0, crc_poly=-1, max_iter=6, scaling=0.8, out=None, impl=0):
+        K, _ = dims(bg, Z)
+        llr = np.ascontiguousarray(llr, np.int8)
+        if out is None:
+            out = np.zeros((K + 7) // 8, np.uint8)
+        it = self.lib.ref_decode(impl, bg, Z, _p(out), _p(llr), C.c_uint(llr.size), C.c_uint(fillers), crc_poly,
+                                 C.c_uint(max_iter), C.c_float(scaling))
+        return it, out
+
+    def cb_chain(self, bg, Z, soft, llr, new_data, rv, qm, Nref, fillers, crc_poly, max_iter, early_stop, impl=0):
+        K, _ = dims(bg, Z)
+        llr = np.ascontiguousarray(llr, np.int8)
+        out = np.zeros((K + 7) // 8, np.uint8)
+        it = self.lib.ref_cb_chain(impl, bg, Z, _p(soft), _p(llr), C.c_uint(llr.size), int(new_data), C.c_uint(rv),
+                                   C.c_uint(qm), C.c_uint(Nref), C.c_uint(fillers), crc_poly, C.c_uint(max_iter),
+                                   int(early_stop), _p(out))
+        return it, out
+
+    def batch_chain(self, impl, n_threads, bg, Z, llr, new_data, rv, qm, Nref, fillers, crc_poly, max_iter,
+                    early_stop):
+        """llr: [n, E] int8. Returns (seconds, iters[n], out[n, K/8])."""
+        K, N = dims(bg, Z)
+        llr = np.ascontiguousarray(llr, np.int8)
+        n, E = llr.shape
+        soft = np.zeros((n, N), np.int8)
+        out = np.zeros((n, (K + 7) // 8), np.uint8)
+        iters = np.zeros(n, np.int32)
+        sec = self.lib.ref_batch_chain(impl, n_threads, C.c_uint(n), bg, Z, _p(soft), _p(llr), C.c_uint(E),
+                                       int(new_data), C.c_uint(rv), C.c_uint(qm), C.c_uint(Nref), C.c_uint(fillers),
+                                       crc_poly, C.c_uint(max_iter), int(early_stop), _p(out), _p(iters))
+        return sec, iters, out
+
+    def tbs(self, nof_symb, nof_dmrs_prb, nof_oh_prb, qm, rate_x1024, nof_layers, n_prb):
+        return int(self.lib.ref_tbs(nof_symb, nof_dmrs_prb, nof_oh_prb, qm, float(rate_x1024), nof_layers, n_prb))
+
+    def segment(self, tbs, bg, rv, qm, Nref, nof_layers, nof_ch_symbols):
+        rm = np.zeros(162, np.uint32)
+        off = np.zeros(162, np.uint32)
+        sc = np.zeros(8, np.uint32)
+        n = self.lib.ref_segment(C.c_uint(tbs), bg, C.c_uint(rv), C.c_uint(qm), C.c_uint(Nref), C.c_uint(nof_layers),
+                                 C.c_uint(nof_ch_symbols), _p(rm), _p(off), _p(sc))
+        return dict(n=n, rm_len=rm[:n].copy(), cw_off=off[:n].copy(), bg=int(sc[0]), Z=int(sc[1]), fillers=int(sc[2]),
+                    N=int(sc[3]), crc_bits=int(sc[4]))
