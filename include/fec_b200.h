@@ -1,0 +1,169 @@
+/* include/fec_b200.h -- C ABI of the B200 PUSCH FEC decode engine (rate dematch + HARQ combine -> layered scaled
+ * min-sum LDPC -> CB CRC), the drop-in boundary for the reference's hardware-accelerator plug-in point.
+ *
+ * Plain C types only: no STL, no exceptions, no torch types. Every entry point returns 0 (FEC_OK) or a negative
+ * fec_status; fec_last_error() gives a thread-local message. There is NO CPU fallback behind this interface: without
+ * a CUDA device fec_engine_create() fails with FEC_ERR_NO_DEVICE.
+ *
+ * Reference interfaces replaced / served (paths relative to the reference tree):
+ *   hal::hw_accelerator_pusch_dec         include/srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec.h:83-115
+ *     enqueue_operation / dequeue_operation  include/srsran/hal/hw_accelerator.h:48,56        -> fec_queue_enqueue / fec_queue_poll
+ *     configure_operation                    hw_accelerator_pusch_dec.h:98                     -> fec_cb_desc (one per CB)
+ *     read_operation_outputs                 hw_accelerator_pusch_dec.h:105-106                -> fec_cb_result
+ *     free_harq_context_entry                hw_accelerator_pusch_dec.h:110                    -> fec_harq_free
+ *     reserve_queue / free_queue             hw_accelerator_pusch_dec.h:90,93                  -> fec_queue_reserve / fec_queue_free
+ *   hal::hw_pusch_decoder_configuration   hw_accelerator_pusch_dec.h:39-72                     -> fec_cb_desc
+ *   hal::hw_pusch_decoder_outputs         hw_accelerator_pusch_dec.h:75-80                     -> fec_cb_result
+ *   ldpc_decoder::decode                  include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:73-74      -> FEC_MODE_DECODE
+ *   ldpc_rate_dematcher::rate_dematch     include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:52-57 -> FEC_MODE_DEMATCH
+ *   pusch_codeblock_decoder::decode       lib/phy/upper/channel_processors/pusch/pusch_codeblock_decoder.cpp:34-71  -> FEC_MODE_CHAIN
+ * The reference-side bindings (C++ adapter classes over this ABI) are shown in INTEGRATION.md and live in
+ * srsran-5g_b200/host/.
+ */
+#ifndef FEC_B200_H
+#define FEC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEC_B200_ABI_VERSION 1
+
+typedef enum {
+  FEC_OK             = 0,
+  FEC_ERR_NO_DEVICE  = -1, /* no CUDA device / driver: the engine never falls back to the CPU */
+  FEC_ERR_BAD_ARG    = -2,
+  FEC_ERR_CUDA       = -3,
+  FEC_ERR_NO_MEMORY  = -4,
+  FEC_ERR_QUEUE_FULL = -5,
+  FEC_ERR_BAD_QUEUE  = -6
+} fec_status;
+
+/* CB CRC selector: same numbering as hal::hw_dec_cb_crc_type (hw_accelerator_pusch_dec.h:36). */
+enum { FEC_CRC16 = 0, FEC_CRC24B = 1, FEC_CRC24A = 2 };
+
+/* What one descriptor asks the engine to do. */
+enum {
+  FEC_MODE_CHAIN   = 0, /* rate dematch (+HARQ combine) into the soft-buffer slot, then LDPC decode + CRC from it */
+  FEC_MODE_DECODE  = 1, /* ldpc_decoder::decode on n_in LLRs given directly (no soft buffer involved)            */
+  FEC_MODE_DEMATCH = 2  /* ldpc_rate_dematcher::rate_dematch only (soft-buffer slot updated, nothing decoded)    */
+};
+
+/* fec_cb_desc.flags */
+#define FEC_FLAG_NEW_DATA   0x01u /* first HARQ transmission: copy instead of combine (hw cfg .new_data)             */
+#define FEC_FLAG_EARLY_STOP 0x02u /* check CRC after every iteration (hw cfg .use_early_stop; crc != nullptr)        */
+#define FEC_FLAG_NO_CRC     0x04u /* FEC_MODE_DECODE with crc == nullptr: never report crc_pass                      */
+
+/* One codeblock operation: POD mirror of hal::hw_pusch_decoder_configuration + buffer placement. 48 bytes.
+ * The same struct is read by the host engine and by the kernels. */
+typedef struct fec_cb_desc {
+  uint64_t llr_offset;      /* byte offset of this CB's input LLRs inside the batch LLR buffer                        */
+  uint32_t out_offset;      /* byte offset of this CB's ceil(K/8) decoded bytes inside the batch output buffer        */
+  uint32_t harq_slot;       /* soft-buffer slot in HBM (hw cfg .absolute_cb_id); ignored by FEC_MODE_DECODE            */
+  uint32_t E;               /* rate-matched length (hw cfg .cw_length); FEC_MODE_DECODE: number of input LLRs n_in    */
+  uint32_t Nref;            /* limited-buffer rate matching length, 0 = unlimited (hw cfg .Nref)                       */
+  uint32_t nof_filler_bits; /* hw cfg .nof_filler_bits                                                                */
+  uint32_t k0;              /* filled in by the engine (starting position in the circular buffer); callers pass 0     */
+  uint16_t lifting_size;    /* Z (hw cfg .lifting_size)                                                               */
+  uint16_t graph_index;     /* filled in by the engine: (bg-1)*51 + index of Z among the 51 lifting sizes             */
+  uint8_t  base_graph;      /* 1 or 2 (hw cfg .base_graph_index)                                                      */
+  uint8_t  rv;              /* redundancy version 0..3                                                                */
+  uint8_t  qm;              /* bits per modulation symbol 1,2,4,6,8 (hw cfg .modulation)                              */
+  uint8_t  crc_type;        /* FEC_CRC16 / FEC_CRC24B / FEC_CRC24A (hw cfg .cb_crc_type)                              */
+  uint8_t  max_iter;        /* hw cfg .max_nof_ldpc_iterations (1..255)                                               */
+  uint8_t  mode;            /* FEC_MODE_*                                                                             */
+  uint8_t  flags;           /* FEC_FLAG_*                                                                             */
+  uint8_t  reserved0;
+  uint32_t reserved1;
+} fec_cb_desc;
+
+/* fec_cb_result.status bits */
+#define FEC_RES_CRC_PASS  0x01u /* hw outputs .CRC_pass                                                              */
+#define FEC_RES_TOO_SHORT 0x02u /* fewer than K significant LLRs: decoder returned nullopt without iterating; with     */
+                                /* FEC_FLAG_EARLY_STOP the output bytes were left untouched, otherwise set to all ones */
+#define FEC_RES_DONE      0x80u /* written last by the kernel                                                         */
+
+/* Per-CB outcome: mirror of hal::hw_pusch_decoder_outputs. 8 bytes. */
+typedef struct fec_cb_result {
+  uint16_t nof_ldpc_iterations; /* iterations run: it+1 on early stop, else max_iter                                   */
+  uint8_t  status;              /* FEC_RES_*                                                                          */
+  uint8_t  nof_layers;          /* base-graph rows actually processed per iteration (trimmed codeblock length)          */
+  uint32_t reserved;
+} fec_cb_result;
+
+typedef struct fec_engine_cfg {
+  int32_t  device;          /* CUDA device ordinal                                                                    */
+  uint32_t harq_slots;      /* number of soft-buffer slots to reserve in HBM (each FEC_HARQ_SLOT_BYTES)               */
+  uint32_t max_batch_cbs;   /* capacity of one launch (descriptor / result arrays, queue staging)                     */
+  uint32_t max_batch_llrs;  /* staging capacity in LLRs (bytes) for the host-buffer entry points                      */
+  uint32_t nof_queues;      /* number of independent submission queues (one per hw_accelerator_pusch_dec instance)    */
+  float    scaling_factor;  /* normalised min-sum factor, 0 < sf < 1 (reference default 0.8)                          */
+  uint32_t kernel_variant;  /* 0 = auto; 1 = force the generic one-thread-per-check kernel (debug / A-B comparison)   */
+  uint32_t reserved;
+} fec_engine_cfg;
+
+#define FEC_HARQ_SLOT_BYTES 25344u /* 66 * 384, the largest codeblock; slots are contiguous in HBM                    */
+#define FEC_MAX_CB_OUT_BYTES 1056u /* 22 * 384 / 8                                                                    */
+
+typedef struct fec_engine fec_engine;
+
+/* ---- lifecycle ---------------------------------------------------------------------------------------------------- */
+uint32_t    fec_abi_version(void);
+const char* fec_last_error(void);
+void        fec_engine_default_cfg(fec_engine_cfg* cfg);
+int         fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out);
+void        fec_engine_destroy(fec_engine* e);
+/* The CUDA stream (cudaStream_t) every launch of this engine is issued on, for event timing by the caller. */
+void*       fec_engine_stream(fec_engine* e);
+/* Device pointer to soft-buffer slot `slot` (FEC_HARQ_SLOT_BYTES bytes), NULL if out of range. */
+void*       fec_harq_slot_ptr(fec_engine* e, uint32_t slot);
+/* Number of kernels this engine has launched so far (bench.py's gpu_launches). */
+uint64_t    fec_engine_launch_count(fec_engine* e);
+
+/* ---- validation helper (host only, no GPU work) -------------------------------------------------------------------- */
+/* Checks a descriptor and fills in k0 / graph_index exactly as the engine will. Returns FEC_OK or FEC_ERR_BAD_ARG. */
+int fec_desc_prepare(fec_cb_desc* d);
+
+/* ---- device-resident batch: everything already in HBM (bench.py "value") ------------------------------------------ */
+/* d_descs: n prepared descriptors in device memory; d_llr / d_out / d_results: device buffers the descriptors index
+ * into. Asynchronous on fec_engine_stream(); max_Z / max_bg1 size the launch (largest lifting size in the batch and
+ * whether any CB uses BG1). */
+int fec_launch_device(fec_engine* e, const fec_cb_desc* d_descs, uint32_t n, const int8_t* d_llr, uint8_t* d_out,
+                      fec_cb_result* d_results, uint32_t max_Z, int any_bg1);
+
+/* ---- host-buffer batch: H2D + kernels + D2H, synchronous (bench.py "e2e", unit-test surface) ----------------------- */
+/* h_descs need not be prepared. llr_bytes / out_bytes are the sizes of the two host buffers. h_soft_out, if not NULL,
+ * receives the n soft buffers (n * FEC_HARQ_SLOT_BYTES) after the operation. Pinned buffers (fec_host_alloc) make the
+ * copies asynchronous DMA. */
+int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* h_llr, size_t llr_bytes, uint8_t* h_out,
+                 size_t out_bytes, fec_cb_result* h_results, int8_t* h_soft_out);
+
+void* fec_host_alloc(size_t bytes); /* pinned host memory */
+void  fec_host_free(void* p);
+
+/* ---- HARQ soft buffers --------------------------------------------------------------------------------------------- */
+int fec_harq_free(fec_engine* e, uint32_t slot);                       /* free_harq_context_entry: zeroes the slot   */
+int fec_harq_read(fec_engine* e, uint32_t slot, int8_t* h_dst, uint32_t n);  /* D2H copy of the first n soft bits     */
+int fec_harq_write(fec_engine* e, uint32_t slot, const int8_t* h_src, uint32_t n); /* H2D (tests, HARQ migration)    */
+
+/* ---- queue interface: the shape hal::hw_accelerator_pusch_dec needs ----------------------------------------------- */
+/* One queue per accelerator instance / submitting thread. enqueue copies the LLRs into pinned staging and returns
+ * immediately (FEC_ERR_QUEUE_FULL when the staging ring is full: the caller retries, it never blocks). A batch is
+ * launched when it reaches max_batch_cbs or on fec_queue_flush(). poll is non-blocking and returns the number of
+ * completed operations written to tags/results (at most `max`); decoded bytes are copied out with fec_queue_fetch(). */
+int fec_queue_reserve(fec_engine* e, uint32_t* queue_id);
+int fec_queue_free(fec_engine* e, uint32_t queue_id);
+int fec_queue_enqueue(fec_engine* e, uint32_t queue_id, const fec_cb_desc* desc, const int8_t* llr, uint64_t tag);
+int fec_queue_flush(fec_engine* e, uint32_t queue_id);
+int fec_queue_poll(fec_engine* e, uint32_t queue_id, uint64_t* tags, fec_cb_result* results, uint32_t max);
+/* Copies the decoded bytes of a completed (polled) operation; valid until the next fec_queue_enqueue after a poll
+ * that returned it. nbytes <= ceil(K/8). */
+int fec_queue_fetch(fec_engine* e, uint32_t queue_id, uint64_t tag, uint8_t* dst, uint32_t nbytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEC_B200_H */

@@ -1,0 +1,743 @@
+// srsran-5g_b200/csrc/fec_engine.cu -- host side of the C ABI declared in include/fec_b200.h.
+//
+// One engine per GPU: graph/CRC tables and the HARQ soft-buffer pool live in HBM for the engine's lifetime; batches of
+// codeblock descriptors are launched on the engine's stream (device-resident entry point) or on per-queue streams fed
+// from pinned staging (host entry points). There is no CPU decode path in this file: every entry point that produces
+// decoded bits does so by launching the kernels in fec_kernel_*.cuh.
+#include "fec_device.cuh"
+#include "fec_kernel_generic.cuh"
+#include "fec_kernel_packed.cuh"
+#include "ldpc_tables.h"
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CU_TRY(expr)                                                                                                   \
+  do {                                                                                                                 \
+    cudaError_t err__ = (expr);                                                                                        \
+    if (err__ != cudaSuccess) {                                                                                        \
+      return fail(FEC_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(err__));                                    \
+    }                                                                                                                  \
+  } while (0)
+
+int z_index(unsigned Z)
+{
+  for (int i = 0; i < 51; ++i) {
+    if (FEC_ALL_Z[i] == Z) {
+      return i;
+    }
+  }
+  return -1;
+}
+
+const uint32_t CRC_POLY[3] = {0x11021u, 0x1800063u, 0x1864CFBu}; // FEC_CRC16, FEC_CRC24B, FEC_CRC24A
+const uint32_t CRC_LEN[3]  = {16, 24, 24};
+
+void build_tables(fec_dev_tables& t, float sf)
+{
+  memset(&t, 0, sizeof(t));
+  for (int bg = 0; bg < 2; ++bg) {
+    const uint8_t* deg = bg ? FEC_BG2_DEG : FEC_BG1_DEG;
+    const uint8_t* col = bg ? FEC_BG2_COL : FEC_BG1_COL;
+    const int      M   = bg ? FEC_BG2_M : FEC_BG1_M;
+    const int      ne  = bg ? FEC_BG2_EDGES : FEC_BG1_EDGES;
+    int            e   = 0;
+    for (int m = 0; m < M; ++m) {
+      t.deg[bg][m]       = deg[m];
+      t.row_start[bg][m] = (uint16_t)e;
+      e += deg[m];
+    }
+    t.row_start[bg][M] = (uint16_t)e;
+    memcpy(t.col[bg], col, ne);
+    for (int zi = 0; zi < 51; ++zi) {
+      const unsigned  Z   = FEC_ALL_Z[zi];
+      const uint16_t* raw = bg ? FEC_BG2_SHIFT[FEC_Z_SET[zi]] : FEC_BG1_SHIFT[FEC_Z_SET[zi]];
+      for (int i = 0; i < ne; ++i) {
+        t.shift[bg * 51 + zi][i] = (uint16_t)(raw[i] % Z);
+      }
+    }
+  }
+  // Same expression as the reference's generic scaling: round(float(x) * sf), +-127 pass through.
+  for (int x = 0; x < 128; ++x) {
+    t.scale_lut[x] = (x > 120) ? (uint8_t)x : (uint8_t)(int)std::round((float)x * sf);
+  }
+  for (int p = 0; p < 3; ++p) {
+    t.crc_poly[p]   = CRC_POLY[p];
+    t.crc_len[p]    = CRC_LEN[p];
+    const uint32_t top = 1u << CRC_LEN[p];
+    uint32_t       r   = 1; // x^0
+    for (int j = 0; j < FEC_CRC_X32_ENTRIES; ++j) {
+      t.crc_x32[p][j] = r;
+      for (int i = 0; i < 32; ++i) {
+        r <<= 1;
+        if (r & top) {
+          r ^= CRC_POLY[p];
+        }
+      }
+    }
+  }
+}
+
+struct batch_slot {
+  enum state_t { FREE, FILLING, INFLIGHT, DONE } state = FREE;
+  uint32_t      n        = 0;
+  uint32_t      llr_used = 0;
+  uint32_t      out_used = 0;
+  uint32_t      polled   = 0;
+  uint32_t      max_Z    = 0;
+  int           any_bg1  = 0;
+  uint64_t      seq      = 0;
+  fec_cb_desc*  h_descs  = nullptr; // pinned
+  uint64_t*     tags     = nullptr;
+  int8_t*       h_llr    = nullptr; // pinned
+  uint8_t*      h_out    = nullptr; // pinned
+  fec_cb_result* h_res   = nullptr; // pinned
+  fec_cb_desc*  d_descs  = nullptr;
+  int8_t*       d_llr    = nullptr;
+  uint8_t*      d_out    = nullptr;
+  fec_cb_result* d_res   = nullptr;
+  cudaEvent_t   done     = nullptr;
+};
+
+constexpr int SLOTS_PER_QUEUE = 4;
+
+struct queue_t {
+  std::mutex   mtx;
+  bool         reserved = false;
+  bool         inited   = false;
+  cudaStream_t stream   = nullptr;
+  batch_slot   slots[SLOTS_PER_QUEUE];
+  int          filling  = -1;
+  uint64_t     next_seq = 1;
+};
+
+} // namespace
+
+struct fec_engine {
+  fec_engine_cfg        cfg;
+  int                   sm_count     = 0;
+  cudaStream_t          stream       = nullptr;
+  fec_dev_tables*       d_tab        = nullptr;
+  int8_t*               d_harq       = nullptr;
+  std::atomic<uint64_t> launches{0};
+  std::mutex            run_mtx; // serialises fec_run_host users of the shared staging below
+  // staging for fec_run_host
+  fec_cb_desc*   d_descs = nullptr;
+  int8_t*        d_llr   = nullptr;
+  uint8_t*       d_out   = nullptr;
+  fec_cb_result* d_res   = nullptr;
+  std::vector<queue_t>* queues = nullptr;
+  std::mutex            queues_mtx;
+};
+
+namespace {
+
+int launch(fec_engine*          e,
+           cudaStream_t         st,
+           const fec_cb_desc*   d_descs,
+           uint32_t             n,
+           const int8_t*        d_llr,
+           uint8_t*             d_out,
+           fec_cb_result*       d_res,
+           uint32_t             max_Z,
+           int                  any_bg1)
+{
+  if (n == 0) {
+    return FEC_OK;
+  }
+  if (z_index(max_Z) < 0) {
+    return fail(FEC_ERR_BAD_ARG, "max_Z=%u is not a lifting size", max_Z);
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  const bool packed_ok = (e->cfg.kernel_variant != 1) && fec_packed_supported(max_Z);
+  if (packed_ok) {
+    int r = fec_packed_launch(st, d_descs, n, d_llr, d_out, d_res, e->d_harq, e->d_tab, max_Z, any_bg1);
+    if (r != FEC_OK) {
+      return fail(r, "packed kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+  } else {
+    const fec_generic_smem_layout L = fec_generic_layout(max_Z, any_bg1);
+    unsigned                      threads = ((max_Z + 31) / 32) * 32;
+    threads                               = threads > 384 ? 384 : threads;
+    CU_TRY(cudaFuncSetAttribute(fec_cb_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+    fec_cb_generic_kernel<<<n, threads, L.total, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab);
+    CU_TRY(cudaGetLastError());
+  }
+  e->launches.fetch_add(1);
+  return FEC_OK;
+}
+
+int slot_alloc(fec_engine* e, batch_slot& s)
+{
+  const uint32_t nc = e->cfg.max_batch_cbs;
+  const size_t   nl = e->cfg.max_batch_llrs;
+  CU_TRY(cudaHostAlloc((void**)&s.h_descs, nc * sizeof(fec_cb_desc), cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&s.h_llr, nl, cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&s.h_out, (size_t)nc * FEC_MAX_CB_OUT_BYTES, cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&s.h_res, nc * sizeof(fec_cb_result), cudaHostAllocDefault));
+  s.tags = new (std::nothrow) uint64_t[nc];
+  CU_TRY(cudaMalloc((void**)&s.d_descs, nc * sizeof(fec_cb_desc)));
+  CU_TRY(cudaMalloc((void**)&s.d_llr, nl));
+  CU_TRY(cudaMalloc((void**)&s.d_out, (size_t)nc * FEC_MAX_CB_OUT_BYTES));
+  CU_TRY(cudaMalloc((void**)&s.d_res, nc * sizeof(fec_cb_result)));
+  CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  return FEC_OK;
+}
+
+void slot_free(batch_slot& s)
+{
+  cudaFreeHost(s.h_descs);
+  cudaFreeHost(s.h_llr);
+  cudaFreeHost(s.h_out);
+  cudaFreeHost(s.h_res);
+  delete[] s.tags;
+  cudaFree(s.d_descs);
+  cudaFree(s.d_llr);
+  cudaFree(s.d_out);
+  cudaFree(s.d_res);
+  if (s.done) {
+    cudaEventDestroy(s.done);
+  }
+  s = batch_slot();
+}
+
+int queue_launch_slot(fec_engine* e, queue_t& q, batch_slot& s)
+{
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  CU_TRY(cudaMemcpyAsync(s.d_descs, s.h_descs, s.n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, q.stream));
+  CU_TRY(cudaMemcpyAsync(s.d_llr, s.h_llr, s.llr_used, cudaMemcpyHostToDevice, q.stream));
+  int r = launch(e, q.stream, s.d_descs, s.n, s.d_llr, s.d_out, s.d_res, s.max_Z, s.any_bg1);
+  if (r != FEC_OK) {
+    return r;
+  }
+  CU_TRY(cudaMemcpyAsync(s.h_out, s.d_out, s.out_used, cudaMemcpyDeviceToHost, q.stream));
+  CU_TRY(cudaMemcpyAsync(s.h_res, s.d_res, s.n * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, q.stream));
+  CU_TRY(cudaEventRecord(s.done, q.stream));
+  s.state = batch_slot::INFLIGHT;
+  return FEC_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+uint32_t fec_abi_version(void)
+{
+  return FEC_B200_ABI_VERSION;
+}
+
+const char* fec_last_error(void)
+{
+  return g_err;
+}
+
+void fec_engine_default_cfg(fec_engine_cfg* cfg)
+{
+  memset(cfg, 0, sizeof(*cfg));
+  cfg->device         = 0;
+  cfg->harq_slots     = 4096;
+  cfg->max_batch_cbs  = 2048;
+  cfg->max_batch_llrs = 2048u * 25344u;
+  cfg->nof_queues     = 8;
+  cfg->scaling_factor = 0.8f;
+  cfg->kernel_variant = 0;
+}
+
+int fec_desc_prepare(fec_cb_desc* d)
+{
+  if (d == nullptr) {
+    return fail(FEC_ERR_BAD_ARG, "null descriptor");
+  }
+  if (d->base_graph != 1 && d->base_graph != 2) {
+    return fail(FEC_ERR_BAD_ARG, "base_graph=%u", d->base_graph);
+  }
+  const int zi = z_index(d->lifting_size);
+  if (zi < 0) {
+    return fail(FEC_ERR_BAD_ARG, "lifting_size=%u is not one of the 51 NR lifting sizes", d->lifting_size);
+  }
+  const uint32_t Z = d->lifting_size, Kb = (d->base_graph == 1) ? 22 : 10, nb = (d->base_graph == 1) ? 66 : 50;
+  const uint32_t N = nb * Z, K = Kb * Z;
+  d->graph_index   = (uint16_t)((d->base_graph - 1) * 51 + zi);
+  if (d->max_iter == 0 || d->crc_type > 2 || d->mode > 2) {
+    return fail(FEC_ERR_BAD_ARG, "max_iter=%u crc_type=%u mode=%u", d->max_iter, d->crc_type, d->mode);
+  }
+  if (d->nof_filler_bits >= (Kb - 2) * Z || K - d->nof_filler_bits <= CRC_LEN[d->crc_type]) {
+    return fail(FEC_ERR_BAD_ARG, "nof_filler_bits=%u out of range", d->nof_filler_bits);
+  }
+  if (d->mode == FEC_MODE_DECODE) {
+    if (d->E < K + 2 * Z || d->E > N) {
+      return fail(FEC_ERR_BAD_ARG, "decode input length %u outside [%u, %u]", d->E, K + 2 * Z, N);
+    }
+    d->k0 = 0;
+    return FEC_OK;
+  }
+  if (d->rv > 3 || (d->qm != 1 && d->qm != 2 && d->qm != 4 && d->qm != 6 && d->qm != 8) || d->E == 0 ||
+      (d->E % d->qm) != 0) {
+    return fail(FEC_ERR_BAD_ARG, "rv=%u qm=%u E=%u", d->rv, d->qm, d->E);
+  }
+  const uint32_t Ncb = (d->Nref > 0) ? (d->Nref < N ? d->Nref : N) : N;
+  if (Ncb <= (Kb - 2) * Z) {
+    return fail(FEC_ERR_BAD_ARG, "Nref=%u leaves no parity in the circular buffer", d->Nref);
+  }
+  // k0 as the reference computes it: floor(f * Ncb / N) * Z in double precision, truncated to 16 bits.
+  static const double F1[4] = {0, 17, 33, 56};
+  static const double F2[4] = {0, 13, 25, 43};
+  const double        f     = (d->base_graph == 1) ? F1[d->rv] : F2[d->rv];
+  d->k0                     = (uint32_t)(uint16_t)std::floor(f * (double)Ncb / (double)N) * Z;
+  return FEC_OK;
+}
+
+int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
+{
+  if (cfg == nullptr || out == nullptr) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  *out = nullptr;
+  if (!(cfg->scaling_factor > 0.f && cfg->scaling_factor < 1.f) || cfg->max_batch_cbs == 0 || cfg->harq_slots == 0) {
+    return fail(FEC_ERR_BAD_ARG, "scaling_factor must be in (0,1); max_batch_cbs and harq_slots must be > 0");
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= cfg->device || cfg->device < 0) {
+    cudaGetLastError();
+    return fail(FEC_ERR_NO_DEVICE, "CUDA device %d not available (%d devices): this engine has no CPU fallback",
+                cfg->device, ndev);
+  }
+  CU_TRY(cudaSetDevice(cfg->device));
+  fec_engine* e = new (std::nothrow) fec_engine();
+  if (!e) {
+    return fail(FEC_ERR_NO_MEMORY, "host allocation failed");
+  }
+  e->cfg = *cfg;
+  if (e->cfg.max_batch_llrs == 0) {
+    e->cfg.max_batch_llrs = e->cfg.max_batch_cbs * 25344u;
+  }
+  cudaDeviceProp prop;
+  CU_TRY(cudaGetDeviceProperties(&prop, cfg->device));
+  e->sm_count = prop.multiProcessorCount;
+  CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  fec_dev_tables* h = new (std::nothrow) fec_dev_tables();
+  build_tables(*h, cfg->scaling_factor);
+  CU_TRY(cudaMalloc((void**)&e->d_tab, sizeof(fec_dev_tables)));
+  CU_TRY(cudaMemcpy(e->d_tab, h, sizeof(fec_dev_tables), cudaMemcpyHostToDevice));
+  delete h;
+  const size_t harq_bytes = (size_t)cfg->harq_slots * FEC_HARQ_SLOT_BYTES;
+  if (cudaMalloc((void**)&e->d_harq, harq_bytes) != cudaSuccess) {
+    cudaGetLastError();
+    fec_engine_destroy(e);
+    return fail(FEC_ERR_NO_MEMORY, "cannot reserve %zu bytes of HBM for %u HARQ slots", harq_bytes, cfg->harq_slots);
+  }
+  CU_TRY(cudaMemset(e->d_harq, 0, harq_bytes));
+  CU_TRY(cudaMalloc((void**)&e->d_descs, e->cfg.max_batch_cbs * sizeof(fec_cb_desc)));
+  CU_TRY(cudaMalloc((void**)&e->d_llr, e->cfg.max_batch_llrs));
+  CU_TRY(cudaMalloc((void**)&e->d_out, (size_t)e->cfg.max_batch_cbs * FEC_MAX_CB_OUT_BYTES));
+  CU_TRY(cudaMalloc((void**)&e->d_res, e->cfg.max_batch_cbs * sizeof(fec_cb_result)));
+  e->queues = new std::vector<queue_t>(cfg->nof_queues);
+  *out      = e;
+  return FEC_OK;
+}
+
+void fec_engine_destroy(fec_engine* e)
+{
+  if (!e) {
+    return;
+  }
+  cudaSetDevice(e->cfg.device);
+  cudaDeviceSynchronize();
+  if (e->queues) {
+    for (auto& q : *e->queues) {
+      if (q.inited) {
+        for (auto& s : q.slots) {
+          slot_free(s);
+        }
+        cudaStreamDestroy(q.stream);
+      }
+    }
+    delete e->queues;
+  }
+  cudaFree(e->d_descs);
+  cudaFree(e->d_llr);
+  cudaFree(e->d_out);
+  cudaFree(e->d_res);
+  cudaFree(e->d_harq);
+  cudaFree(e->d_tab);
+  if (e->stream) {
+    cudaStreamDestroy(e->stream);
+  }
+  delete e;
+}
+
+void* fec_engine_stream(fec_engine* e)
+{
+  return e ? (void*)e->stream : nullptr;
+}
+
+void* fec_harq_slot_ptr(fec_engine* e, uint32_t slot)
+{
+  if (!e || slot >= e->cfg.harq_slots) {
+    return nullptr;
+  }
+  return e->d_harq + (size_t)slot * FEC_HARQ_SLOT_BYTES;
+}
+
+uint64_t fec_engine_launch_count(fec_engine* e)
+{
+  return e ? e->launches.load() : 0;
+}
+
+int fec_launch_device(fec_engine* e, const fec_cb_desc* d_descs, uint32_t n, const int8_t* d_llr, uint8_t* d_out,
+                      fec_cb_result* d_results, uint32_t max_Z, int any_bg1)
+{
+  if (!e || !d_descs || !d_results) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  return launch(e, e->stream, d_descs, n, d_llr, d_out, d_results, max_Z, any_bg1);
+}
+
+int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* h_llr, size_t llr_bytes, uint8_t* h_out,
+                 size_t out_bytes, fec_cb_result* h_results, int8_t* h_soft_out)
+{
+  if (!e || !h_descs || !h_results || (llr_bytes && !h_llr) || (out_bytes && !h_out)) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (n == 0) {
+    return FEC_OK;
+  }
+  if (n > e->cfg.max_batch_cbs || llr_bytes > e->cfg.max_batch_llrs ||
+      out_bytes > (size_t)e->cfg.max_batch_cbs * FEC_MAX_CB_OUT_BYTES) {
+    return fail(FEC_ERR_BAD_ARG, "batch of %u CBs / %zu LLR bytes / %zu output bytes exceeds the engine capacity", n,
+                llr_bytes, out_bytes);
+  }
+  uint32_t max_Z = 0;
+  int      any1  = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    int r = fec_desc_prepare(&h_descs[i]);
+    if (r != FEC_OK) {
+      return r;
+    }
+    const fec_cb_desc& d  = h_descs[i];
+    const uint32_t     kb = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
+    if (d.llr_offset + d.E > llr_bytes || (d.mode != FEC_MODE_DEMATCH && (size_t)d.out_offset + kb > out_bytes)) {
+      return fail(FEC_ERR_BAD_ARG, "descriptor %u indexes outside the batch buffers", i);
+    }
+    if (d.mode != FEC_MODE_DECODE && d.harq_slot >= e->cfg.harq_slots) {
+      return fail(FEC_ERR_BAD_ARG, "descriptor %u: harq_slot %u >= %u", i, d.harq_slot, e->cfg.harq_slots);
+    }
+    max_Z = d.lifting_size > max_Z ? d.lifting_size : max_Z;
+    any1 |= (d.base_graph == 1);
+  }
+  std::lock_guard<std::mutex> lk(e->run_mtx);
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  CU_TRY(cudaMemcpyAsync(e->d_descs, h_descs, n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr, llr_bytes, cudaMemcpyHostToDevice, e->stream));
+  if (out_bytes) {
+    // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
+    CU_TRY(cudaMemcpyAsync(e->d_out, h_out, out_bytes, cudaMemcpyHostToDevice, e->stream));
+  }
+  int r = launch(e, e->stream, e->d_descs, n, e->d_llr, e->d_out, e->d_res, max_Z, any1);
+  if (r != FEC_OK) {
+    return r;
+  }
+  if (out_bytes) {
+    CU_TRY(cudaMemcpyAsync(h_out, e->d_out, out_bytes, cudaMemcpyDeviceToHost, e->stream));
+  }
+  CU_TRY(cudaMemcpyAsync(h_results, e->d_res, n * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, e->stream));
+  if (h_soft_out) {
+    for (uint32_t i = 0; i < n; ++i) {
+      if (h_descs[i].mode != FEC_MODE_DECODE) {
+        CU_TRY(cudaMemcpyAsync(h_soft_out + (size_t)i * FEC_HARQ_SLOT_BYTES,
+                               e->d_harq + (size_t)h_descs[i].harq_slot * FEC_HARQ_SLOT_BYTES, FEC_HARQ_SLOT_BYTES,
+                               cudaMemcpyDeviceToHost, e->stream));
+      }
+    }
+  }
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  return FEC_OK;
+}
+
+void* fec_host_alloc(size_t bytes)
+{
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+
+void fec_host_free(void* p)
+{
+  if (p) {
+    cudaFreeHost(p);
+  }
+}
+
+int fec_harq_free(fec_engine* e, uint32_t slot)
+{
+  if (!e || slot >= e->cfg.harq_slots) {
+    return fail(FEC_ERR_BAD_ARG, "bad HARQ slot %u", slot);
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  CU_TRY(cudaMemsetAsync(e->d_harq + (size_t)slot * FEC_HARQ_SLOT_BYTES, 0, FEC_HARQ_SLOT_BYTES, e->stream));
+  return FEC_OK;
+}
+
+int fec_harq_read(fec_engine* e, uint32_t slot, int8_t* h_dst, uint32_t n)
+{
+  if (!e || slot >= e->cfg.harq_slots || n > FEC_HARQ_SLOT_BYTES || !h_dst) {
+    return fail(FEC_ERR_BAD_ARG, "bad HARQ read");
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  CU_TRY(cudaDeviceSynchronize());
+  CU_TRY(cudaMemcpy(h_dst, e->d_harq + (size_t)slot * FEC_HARQ_SLOT_BYTES, n, cudaMemcpyDeviceToHost));
+  return FEC_OK;
+}
+
+int fec_harq_write(fec_engine* e, uint32_t slot, const int8_t* h_src, uint32_t n)
+{
+  if (!e || slot >= e->cfg.harq_slots || n > FEC_HARQ_SLOT_BYTES || !h_src) {
+    return fail(FEC_ERR_BAD_ARG, "bad HARQ write");
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  CU_TRY(cudaDeviceSynchronize());
+  CU_TRY(cudaMemcpy(e->d_harq + (size_t)slot * FEC_HARQ_SLOT_BYTES, h_src, n, cudaMemcpyHostToDevice));
+  return FEC_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------------- queues */
+
+int fec_queue_reserve(fec_engine* e, uint32_t* queue_id)
+{
+  if (!e || !queue_id) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  std::lock_guard<std::mutex> lk(e->queues_mtx);
+  for (uint32_t i = 0; i < e->queues->size(); ++i) {
+    queue_t& q = (*e->queues)[i];
+    if (!q.reserved) {
+      if (!q.inited) {
+        CU_TRY(cudaSetDevice(e->cfg.device));
+        CU_TRY(cudaStreamCreateWithFlags(&q.stream, cudaStreamNonBlocking));
+        for (auto& s : q.slots) {
+          int r = slot_alloc(e, s);
+          if (r != FEC_OK) {
+            return r;
+          }
+        }
+        q.inited = true;
+      }
+      q.reserved = true;
+      *queue_id  = i;
+      return FEC_OK;
+    }
+  }
+  return fail(FEC_ERR_QUEUE_FULL, "all %zu queues are reserved", e->queues->size());
+}
+
+int fec_queue_free(fec_engine* e, uint32_t queue_id)
+{
+  if (!e || queue_id >= e->queues->size()) {
+    return fail(FEC_ERR_BAD_QUEUE, "bad queue %u", queue_id);
+  }
+  queue_t&                    q = (*e->queues)[queue_id];
+  std::lock_guard<std::mutex> lk(q.mtx);
+  if (q.inited) {
+    cudaStreamSynchronize(q.stream);
+    for (auto& s : q.slots) {
+      s.state = batch_slot::FREE;
+      s.n = s.llr_used = s.out_used = s.polled = 0;
+    }
+  }
+  q.filling  = -1;
+  q.reserved = false;
+  return FEC_OK;
+}
+
+int fec_queue_enqueue(fec_engine* e, uint32_t queue_id, const fec_cb_desc* desc, const int8_t* llr, uint64_t tag)
+{
+  if (!e || queue_id >= e->queues->size() || !desc || !llr) {
+    return fail(FEC_ERR_BAD_QUEUE, "bad queue %u or null argument", queue_id);
+  }
+  fec_cb_desc d = *desc;
+  int         r = fec_desc_prepare(&d);
+  if (r != FEC_OK) {
+    return r;
+  }
+  if (d.mode != FEC_MODE_DECODE && d.harq_slot >= e->cfg.harq_slots) {
+    return fail(FEC_ERR_BAD_ARG, "harq_slot %u >= %u", d.harq_slot, e->cfg.harq_slots);
+  }
+  const uint32_t kb      = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
+  const uint32_t llr_pad = (d.E + 15u) & ~15u;
+  if (llr_pad > e->cfg.max_batch_llrs) {
+    return fail(FEC_ERR_BAD_ARG, "E=%u exceeds the staging capacity", d.E);
+  }
+  queue_t&                    q = (*e->queues)[queue_id];
+  std::lock_guard<std::mutex> lk(q.mtx);
+  if (!q.reserved) {
+    return fail(FEC_ERR_BAD_QUEUE, "queue %u is not reserved", queue_id);
+  }
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    if (q.filling < 0) {
+      // Recycle the oldest fully polled slot, or take a free one.
+      int      pick = -1;
+      uint64_t best = ~0ull;
+      for (int i = 0; i < SLOTS_PER_QUEUE; ++i) {
+        batch_slot& s = q.slots[i];
+        if (s.state == batch_slot::FREE) {
+          pick = i;
+          break;
+        }
+        if (s.state == batch_slot::DONE && s.polled == s.n && s.seq < best) {
+          best = s.seq;
+          pick = i;
+        }
+      }
+      if (pick < 0) {
+        return fail(FEC_ERR_QUEUE_FULL, "queue %u: all batch slots are in flight", queue_id);
+      }
+      batch_slot& s = q.slots[pick];
+      s.state       = batch_slot::FILLING;
+      s.n = s.llr_used = s.out_used = s.polled = 0;
+      s.max_Z                                  = 0;
+      s.any_bg1                                = 0;
+      s.seq                                    = q.next_seq++;
+      q.filling                                = pick;
+    }
+    batch_slot& s = q.slots[q.filling];
+    if (s.n < e->cfg.max_batch_cbs && s.llr_used + llr_pad <= e->cfg.max_batch_llrs) {
+      d.llr_offset = s.llr_used;
+      d.out_offset = s.out_used;
+      memcpy(s.h_llr + s.llr_used, llr, d.E);
+      s.h_descs[s.n] = d;
+      s.tags[s.n]    = tag;
+      s.h_res[s.n].status = 0;
+      s.n++;
+      s.llr_used += llr_pad;
+      s.out_used += (kb + 15u) & ~15u;
+      s.max_Z = d.lifting_size > s.max_Z ? d.lifting_size : s.max_Z;
+      s.any_bg1 |= (d.base_graph == 1);
+      if (s.n == e->cfg.max_batch_cbs) {
+        q.filling = -1;
+        return queue_launch_slot(e, q, s);
+      }
+      return FEC_OK;
+    }
+    // Current batch cannot take it: launch it and try a fresh slot.
+    q.filling = -1;
+    r         = queue_launch_slot(e, q, s);
+    if (r != FEC_OK) {
+      return r;
+    }
+  }
+  return fail(FEC_ERR_QUEUE_FULL, "queue %u: no room", queue_id);
+}
+
+int fec_queue_flush(fec_engine* e, uint32_t queue_id)
+{
+  if (!e || queue_id >= e->queues->size()) {
+    return fail(FEC_ERR_BAD_QUEUE, "bad queue %u", queue_id);
+  }
+  queue_t&                    q = (*e->queues)[queue_id];
+  std::lock_guard<std::mutex> lk(q.mtx);
+  if (q.filling >= 0) {
+    batch_slot& s = q.slots[q.filling];
+    q.filling     = -1;
+    if (s.n > 0) {
+      return queue_launch_slot(e, q, s);
+    }
+    s.state = batch_slot::FREE;
+  }
+  return FEC_OK;
+}
+
+int fec_queue_poll(fec_engine* e, uint32_t queue_id, uint64_t* tags, fec_cb_result* results, uint32_t max)
+{
+  if (!e || queue_id >= e->queues->size() || !tags || !results) {
+    return fail(FEC_ERR_BAD_QUEUE, "bad queue %u or null argument", queue_id);
+  }
+  queue_t&                    q = (*e->queues)[queue_id];
+  std::lock_guard<std::mutex> lk(q.mtx);
+  uint32_t                    got = 0;
+  // Report in submission order.
+  for (int pass = 0; pass < SLOTS_PER_QUEUE && got < max; ++pass) {
+    int      pick = -1;
+    uint64_t best = ~0ull;
+    for (int i = 0; i < SLOTS_PER_QUEUE; ++i) {
+      batch_slot& s = q.slots[i];
+      if ((s.state == batch_slot::INFLIGHT || (s.state == batch_slot::DONE && s.polled < s.n)) && s.seq < best) {
+        best = s.seq;
+        pick = i;
+      }
+    }
+    if (pick < 0) {
+      break;
+    }
+    batch_slot& s = q.slots[pick];
+    if (s.state == batch_slot::INFLIGHT) {
+      cudaError_t st = cudaEventQuery(s.done);
+      if (st == cudaErrorNotReady) {
+        break;
+      }
+      if (st != cudaSuccess) {
+        // A device fault must surface as failed codeblocks, never as a hang (the consumer's poll loop has no timeout).
+        cudaGetLastError();
+        for (uint32_t i = 0; i < s.n; ++i) {
+          s.h_res[i].status              = FEC_RES_DONE;
+          s.h_res[i].nof_ldpc_iterations = s.h_descs[i].max_iter;
+        }
+      }
+      s.state = batch_slot::DONE;
+    }
+    while (s.polled < s.n && got < max) {
+      tags[got]    = s.tags[s.polled];
+      results[got] = s.h_res[s.polled];
+      ++got;
+      ++s.polled;
+    }
+  }
+  return (int)got;
+}
+
+int fec_queue_fetch(fec_engine* e, uint32_t queue_id, uint64_t tag, uint8_t* dst, uint32_t nbytes)
+{
+  if (!e || queue_id >= e->queues->size() || !dst) {
+    return fail(FEC_ERR_BAD_QUEUE, "bad queue %u or null argument", queue_id);
+  }
+  queue_t&                    q = (*e->queues)[queue_id];
+  std::lock_guard<std::mutex> lk(q.mtx);
+  for (auto& s : q.slots) {
+    if (s.state != batch_slot::DONE) {
+      continue;
+    }
+    for (uint32_t i = 0; i < s.polled; ++i) {
+      if (s.tags[i] == tag) {
+        const fec_cb_desc& d = s.h_descs[i];
+        if ((s.h_res[i].status & FEC_RES_TOO_SHORT) && (d.flags & FEC_FLAG_EARLY_STOP)) {
+          return FEC_OK; // reference leaves the output untouched in this case
+        }
+        memcpy(dst, s.h_out + d.out_offset, nbytes);
+        return FEC_OK;
+      }
+    }
+  }
+  return fail(FEC_ERR_BAD_ARG, "tag not found among completed operations of queue %u", queue_id);
+}
+
+} // extern "C"

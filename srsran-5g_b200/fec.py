@@ -1,0 +1,393 @@
+"""ctypes binding of the C ABI in include/fec_b200.h plus Python mirrors of the reference interfaces it serves.
+
+The classes below keep the reference's names, argument meaning and error behaviour for this path so that the parity
+tests read like the reference's own tests (paths relative to the reference tree):
+
+  LdpcDecoder.decode            <- ldpc_decoder::decode            include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:73
+  LdpcRateDematcher.rate_dematch<- ldpc_rate_dematcher::rate_dematch include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:52
+  HwAcceleratorPuschDec         <- hal::hw_accelerator_pusch_dec   include/srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec.h:83
+
+There is no CPU fallback: constructing FecEngine without the compiled extension or without a CUDA device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+CRC16, CRC24B, CRC24A = 0, 1, 2  # hal::hw_dec_cb_crc_type numbering
+MODE_CHAIN, MODE_DECODE, MODE_DEMATCH = 0, 1, 2
+FLAG_NEW_DATA, FLAG_EARLY_STOP, FLAG_NO_CRC = 1, 2, 4
+RES_CRC_PASS, RES_TOO_SHORT, RES_DONE = 1, 2, 0x80
+HARQ_SLOT_BYTES = 25344
+MAX_CB_OUT_BYTES = 1056
+
+ALL_Z = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48, 52, 56, 60,
+         64, 72, 80, 88, 96, 104, 112, 120, 128, 144, 160, 176, 192, 208, 224, 240, 256, 288, 320, 352, 384]
+
+# numpy mirror of struct fec_cb_desc (48 bytes) and fec_cb_result (8 bytes)
+DESC_DTYPE = np.dtype({
+    "names": ["llr_offset", "out_offset", "harq_slot", "E", "Nref", "nof_filler_bits", "k0", "lifting_size",
+              "graph_index", "base_graph", "rv", "qm", "crc_type", "max_iter", "mode", "flags", "reserved0",
+              "reserved1"],
+    "formats": ["<u8", "<u4", "<u4", "<u4", "<u4", "<u4", "<u4", "<u2", "<u2", "u1", "u1", "u1", "u1", "u1", "u1",
+                "u1", "u1", "<u4"],
+    "offsets": [0, 8, 12, 16, 20, 24, 28, 32, 34, 36, 37, 38, 39, 40, 41, 42, 43, 44],
+    "itemsize": 48})
+RESULT_DTYPE = np.dtype({"names": ["nof_ldpc_iterations", "status", "nof_layers", "reserved"],
+                         "formats": ["<u2", "u1", "u1", "<u4"], "offsets": [0, 2, 3, 4], "itemsize": 8})
+
+
+class EngineCfg(C.Structure):
+    _fields_ = [("device", C.c_int32), ("harq_slots", C.c_uint32), ("max_batch_cbs", C.c_uint32),
+                ("max_batch_llrs", C.c_uint32), ("nof_queues", C.c_uint32), ("scaling_factor", C.c_float),
+                ("kernel_variant", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_engine_create", "fec_engine_destroy",
+           "fec_engine_stream", "fec_harq_slot_ptr", "fec_engine_launch_count", "fec_desc_prepare",
+           "fec_launch_device", "fec_run_host", "fec_host_alloc", "fec_host_free", "fec_harq_free", "fec_harq_read",
+           "fec_harq_write", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
+           "fec_queue_poll", "fec_queue_fetch"]
+
+_lib = None
+
+
+class FecError(RuntimeError):
+    pass
+
+
+def load_library():
+    """Loads libfec_b200.so (building it first if sources are newer). Raises if it cannot be had: no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.build()
+    if not os.path.exists(path):
+        raise FecError("libfec_b200.so is missing: build the CUDA extension (__graft_entry__.build())")
+    lib = C.CDLL(path)
+    lib.fec_last_error.restype = C.c_char_p
+    lib.fec_abi_version.restype = C.c_uint32
+    lib.fec_engine_stream.restype = C.c_void_p
+    lib.fec_engine_stream.argtypes = [C.c_void_p]
+    lib.fec_harq_slot_ptr.restype = C.c_void_p
+    lib.fec_harq_slot_ptr.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_engine_launch_count.restype = C.c_uint64
+    lib.fec_engine_launch_count.argtypes = [C.c_void_p]
+    lib.fec_host_alloc.restype = C.c_void_p
+    lib.fec_host_alloc.argtypes = [C.c_size_t]
+    lib.fec_host_free.argtypes = [C.c_void_p]
+    lib.fec_engine_create.argtypes = [C.POINTER(EngineCfg), C.POINTER(C.c_void_p)]
+    lib.fec_engine_destroy.argtypes = [C.c_void_p]
+    lib.fec_desc_prepare.argtypes = [C.c_void_p]
+    lib.fec_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_uint32, C.c_int]
+    lib.fec_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                 C.c_void_p, C.c_void_p]
+    lib.fec_harq_free.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_harq_read.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+    lib.fec_harq_write.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+    lib.fec_queue_reserve.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
+    lib.fec_queue_free.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_queue_enqueue.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.fec_queue_flush.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_queue_poll.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
+    lib.fec_queue_fetch.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_uint32]
+    _lib = lib
+    return lib
+
+
+def _check(lib, rc):
+    if rc < 0:
+        raise FecError("fec error %d: %s" % (rc, lib.fec_last_error().decode()))
+    return rc
+
+
+def dims(bg, Z):
+    kb, nb = (22, 66) if bg == 1 else (10, 50)
+    return kb * Z, nb * Z
+
+
+def make_descs(n):
+    return np.zeros(n, DESC_DTYPE)
+
+
+def desc_prepare(desc):
+    """Validates descriptors in place (fills k0 / graph_index); raises FecError on invalid fields. Host only."""
+    lib = load_library()
+    arr = np.atleast_1d(desc)
+    for i in range(arr.size):
+        _check(lib, lib.fec_desc_prepare(arr[i:i + 1].ctypes.data))
+    return desc
+
+
+class FecEngine:
+    """One engine per GPU (fec_engine_create). All decode work happens in the CUDA kernels behind the C ABI."""
+
+    def __init__(self, device=0, harq_slots=4096, max_batch_cbs=2048, max_batch_llrs=0, nof_queues=8,
+                 scaling_factor=0.8, kernel_variant=0):
+        self.lib = load_library()
+        cfg = EngineCfg()
+        self.lib.fec_engine_default_cfg(C.byref(cfg))
+        cfg.device = device
+        cfg.harq_slots = harq_slots
+        cfg.max_batch_cbs = max_batch_cbs
+        cfg.max_batch_llrs = max_batch_llrs or min(max_batch_cbs * 25344, 0xFFFFFF00)
+        cfg.nof_queues = nof_queues
+        cfg.scaling_factor = scaling_factor
+        cfg.kernel_variant = kernel_variant
+        self.cfg = cfg
+        self.h = C.c_void_p()
+        _check(self.lib, self.lib.fec_engine_create(C.byref(cfg), C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.fec_engine_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return self.lib.fec_engine_stream(self.h)
+
+    @property
+    def launch_count(self):
+        return int(self.lib.fec_engine_launch_count(self.h))
+
+    def harq_slot_ptr(self, slot):
+        return self.lib.fec_harq_slot_ptr(self.h, slot)
+
+    def launch_device(self, d_descs_ptr, n, d_llr_ptr, d_out_ptr, d_res_ptr, max_Z, any_bg1):
+        """Asynchronous launch on self.stream; all pointers are device addresses (ints)."""
+        _check(self.lib, self.lib.fec_launch_device(self.h, d_descs_ptr, n, d_llr_ptr, d_out_ptr, d_res_ptr, max_Z,
+                                                    int(any_bg1)))
+
+    def run_host(self, descs, llr, out, results=None, soft_out=None):
+        """Synchronous H2D -> kernels -> D2H over host numpy buffers (or raw pinned pointers given as ints)."""
+        n = descs.size
+        assert descs.dtype == DESC_DTYPE and descs.flags.c_contiguous
+        if results is None:
+            results = np.zeros(n, RESULT_DTYPE)
+
+        def ptr(a):
+            return a if isinstance(a, int) else (a.ctypes.data if a is not None else None)
+
+        def size(a, given=None):
+            return a.nbytes if hasattr(a, "nbytes") else given
+
+        _check(self.lib, self.lib.fec_run_host(self.h, descs.ctypes.data, n, ptr(llr), size(llr), ptr(out), size(out),
+                                               results.ctypes.data, ptr(soft_out)))
+        return results
+
+    def harq_free(self, slot):
+        _check(self.lib, self.lib.fec_harq_free(self.h, slot))
+
+    def harq_read(self, slot, n=HARQ_SLOT_BYTES):
+        buf = np.zeros(n, np.int8)
+        _check(self.lib, self.lib.fec_harq_read(self.h, slot, buf.ctypes.data, n))
+        return buf
+
+    def harq_write(self, slot, data):
+        data = np.ascontiguousarray(data, np.int8)
+        _check(self.lib, self.lib.fec_harq_write(self.h, slot, data.ctypes.data, data.size))
+
+    # ---- queue interface ----
+    def queue_reserve(self):
+        q = C.c_uint32()
+        _check(self.lib, self.lib.fec_queue_reserve(self.h, C.byref(q)))
+        return q.value
+
+    def queue_free(self, q):
+        _check(self.lib, self.lib.fec_queue_free(self.h, q))
+
+    def queue_enqueue(self, q, desc, llr, tag):
+        """Returns False when the staging ring is full (caller retries), True when accepted."""
+        llr = np.ascontiguousarray(llr, np.int8)
+        rc = self.lib.fec_queue_enqueue(self.h, q, desc.ctypes.data, llr.ctypes.data, tag)
+        if rc == -5:
+            return False
+        _check(self.lib, rc)
+        return True
+
+    def queue_flush(self, q):
+        _check(self.lib, self.lib.fec_queue_flush(self.h, q))
+
+    def queue_poll(self, q, max_ops=256):
+        tags = np.zeros(max_ops, np.uint64)
+        res = np.zeros(max_ops, RESULT_DTYPE)
+        n = _check(self.lib, self.lib.fec_queue_poll(self.h, q, tags.ctypes.data, res.ctypes.data, max_ops))
+        return tags[:n], res[:n]
+
+    def queue_fetch(self, q, tag, dst):
+        _check(self.lib, self.lib.fec_queue_fetch(self.h, q, int(tag), dst.ctypes.data, dst.size))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Mirrors of the reference's operator interfaces for this path (same names, argument meaning, error behaviour).
+# ------------------------------------------------------------------------------------------------------------------
+class CodeblockMetadata:
+    """codeblock_metadata (include/srsran/phy/upper/codeblock_metadata.h:42-80), flattened."""
+
+    def __init__(self, base_graph=1, lifting_size=2, rv=0, mod_order=1, Nref=0, nof_filler_bits=0, nof_crc_bits=24,
+                 rm_length=0):
+        self.base_graph = base_graph
+        self.lifting_size = lifting_size
+        self.rv = rv
+        self.mod_order = mod_order  # bits per symbol of tb_common.mod
+        self.Nref = Nref
+        self.nof_filler_bits = nof_filler_bits
+        self.nof_crc_bits = nof_crc_bits
+        self.rm_length = rm_length
+
+
+class LdpcRateDematcher:
+    """ldpc_rate_dematcher (ldpc_rate_dematcher.h:35-58): rate_dematch(output, input, new_data, cfg), in place."""
+
+    SCRATCH_SLOT = 0
+
+    def __init__(self, engine):
+        self.engine = engine
+
+    def rate_dematch(self, output, input, new_data, cfg):
+        K, N = dims(cfg.base_graph, cfg.lifting_size)
+        if output.size != N or output.dtype != np.int8:
+            raise FecError("rate_dematch: output must be the full %d-LLR int8 codeblock" % N)
+        d = make_descs(1)
+        d["base_graph"], d["lifting_size"], d["rv"], d["qm"] = cfg.base_graph, cfg.lifting_size, cfg.rv, cfg.mod_order
+        d["Nref"], d["nof_filler_bits"], d["E"] = cfg.Nref, cfg.nof_filler_bits, input.size
+        d["crc_type"], d["max_iter"], d["mode"] = CRC24B, 1, MODE_DEMATCH
+        d["flags"] = FLAG_NEW_DATA if new_data else 0
+        d["harq_slot"] = self.SCRATCH_SLOT
+        self.engine.harq_write(self.SCRATCH_SLOT, output)
+        llr = np.ascontiguousarray(input, np.int8)
+        self.engine.run_host(d, llr, None)
+        output[:] = self.engine.harq_read(self.SCRATCH_SLOT, N)
+        return output
+
+
+class LdpcDecoder:
+    """ldpc_decoder (ldpc_decoder.h:37-75): decode(output, input, crc, cfg) -> iterations or None.
+
+    `crc` conveys only the polynomial (CRC16 / CRC24A / CRC24B or None); the check itself runs on the device.
+    `output` is a uint8 array of ceil(K/8) bytes, MSB-first packed like bit_buffer."""
+
+    def __init__(self, engine):
+        self.engine = engine
+
+    def decode(self, output, input, crc, cfg, max_iterations=6):
+        K, N = dims(cfg.base_graph, cfg.lifting_size)
+        if output.size != (K + 7) // 8:
+            raise FecError("decode: output size %d does not match the message length %d bits" % (output.size, K))
+        d = make_descs(1)
+        d["base_graph"], d["lifting_size"] = cfg.base_graph, cfg.lifting_size
+        d["nof_filler_bits"], d["E"] = cfg.nof_filler_bits, input.size
+        d["max_iter"], d["mode"] = max_iterations, MODE_DECODE
+        if crc is None:
+            d["crc_type"], d["flags"] = CRC24B, FLAG_NO_CRC
+        else:
+            d["crc_type"], d["flags"] = crc, FLAG_EARLY_STOP
+        llr = np.ascontiguousarray(input, np.int8)
+        res = self.engine.run_host(d, llr, output)
+        if crc is not None and (res["status"][0] & RES_CRC_PASS):
+            return int(res["nof_ldpc_iterations"][0])
+        return None
+
+
+class HwPuschDecoderConfiguration:
+    """hal::hw_pusch_decoder_configuration (hw_accelerator_pusch_dec.h:39-72)."""
+
+    def __init__(self, **kw):
+        self.base_graph_index = 1
+        self.modulation = 2
+        self.nof_segments = 1
+        self.rv = 0
+        self.cw_length = 0
+        self.lifting_size = 2
+        self.Ncb = 0
+        self.Nref = 0
+        self.nof_segment_bits = 0
+        self.nof_filler_bits = 0
+        self.max_nof_ldpc_iterations = 6
+        self.use_early_stop = True
+        self.new_data = True
+        self.cb_crc_len = 24
+        self.cb_crc_type = CRC24B
+        self.absolute_cb_id = 0
+        self.__dict__.update(kw)
+
+
+class HwPuschDecoderOutputs:
+    def __init__(self):
+        self.CRC_pass = False
+        self.nof_ldpc_iterations = 0
+
+
+class HwAcceleratorPuschDec:
+    """hal::hw_accelerator_pusch_dec (hw_accelerator_pusch_dec.h:83-115) over the queue entry points of the C ABI.
+
+    Same call sequence as pusch_decoder_hw_impl drives (lib/phy/upper/channel_processors/pusch/pusch_decoder_hw_impl.cpp:149-358):
+    reserve_queue, {configure_operation, enqueue_operation}*, {dequeue_operation (polled), read_operation_outputs}*,
+    free_harq_context_entry*, free_queue. HARQ is external: soft buffers stay in HBM keyed by absolute_cb_id."""
+
+    MAX_NOF_SEGMENTS = 162
+
+    def __init__(self, engine):
+        self.engine = engine
+        self.queue = None
+        self.cfgs = {}
+        self.done = {}
+
+    def reserve_queue(self):
+        if self.queue is None:
+            self.queue = self.engine.queue_reserve()
+
+    def free_queue(self):
+        if self.queue is not None:
+            self.engine.queue_free(self.queue)
+            self.queue = None
+        self.cfgs.clear()
+        self.done.clear()
+
+    def configure_operation(self, config, cb_index=0):
+        self.cfgs[cb_index] = config
+
+    def enqueue_operation(self, data, aux_data=None, cb_index=0):
+        c = self.cfgs[cb_index]
+        d = make_descs(1)
+        d["base_graph"], d["lifting_size"], d["rv"], d["qm"] = c.base_graph_index, c.lifting_size, c.rv, c.modulation
+        d["Nref"], d["nof_filler_bits"], d["E"] = c.Nref, c.nof_filler_bits, c.cw_length
+        d["crc_type"], d["max_iter"], d["mode"] = c.cb_crc_type, c.max_nof_ldpc_iterations, MODE_CHAIN
+        d["flags"] = (FLAG_NEW_DATA if c.new_data else 0) | (FLAG_EARLY_STOP if c.use_early_stop else 0)
+        d["harq_slot"] = c.absolute_cb_id
+        if len(data) != c.cw_length:
+            raise FecError("enqueue_operation: %d LLRs given, cw_length is %d" % (len(data), c.cw_length))
+        return self.engine.queue_enqueue(self.queue, d, data, cb_index)
+
+    def dequeue_operation(self, data, aux_data=None, segment_index=0):
+        """Non-blocking: False until the operation has completed; then fills `data` with the decoded bytes."""
+        if segment_index not in self.done:
+            self.engine.queue_flush(self.queue)
+            tags, res = self.engine.queue_poll(self.queue)
+            for t, r in zip(tags, res):
+                self.done[int(t)] = r.copy()
+        if segment_index not in self.done:
+            return False
+        self.engine.queue_fetch(self.queue, segment_index, data)
+        return True
+
+    def read_operation_outputs(self, out, cb_index=0, absolute_cb_id=0):
+        r = self.done.pop(cb_index)
+        out.CRC_pass = bool(r["status"] & RES_CRC_PASS)
+        out.nof_ldpc_iterations = int(r["nof_ldpc_iterations"])
+
+    def free_harq_context_entry(self, absolute_cb_id):
+        self.engine.harq_free(absolute_cb_id)
+
+    def is_harq_external(self):
+        return True

@@ -1,0 +1,45 @@
+"""Seeded case generators shared by the golden-vector script and the parity tests."""
+import numpy as np
+
+ALL_Z = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48, 52, 56, 60,
+         64, 72, 80, 88, 96, 104, 112, 120, 128, 144, 160, 176, 192, 208, 224, 240, 256, 288, 320, 352, 384]
+ORC_CRC_LEN = {0: 24, 1: 24, 2: 16}  # oracle numbering: 0=CRC24A 1=CRC24B 2=CRC16
+ORC_TO_HAL_CRC = {0: 2, 1: 1, 2: 0}
+
+
+def dims(bg, Z):
+    kb, nb = (22, 66) if bg == 1 else (10, 50)
+    return kb * Z, nb * Z
+
+
+def random_chain_params(rng, bg=None, Z=None, z_pool=None):
+    """Random (but valid) per-CB parameters in the spirit of BASELINE config 2."""
+    bg = int(rng.choice([1, 2])) if bg is None else bg
+    Z = int(rng.choice(z_pool or ALL_Z)) if Z is None else Z
+    K, N = dims(bg, Z)
+    Kb = 22 if bg == 1 else 10
+    qm = int(rng.choice([1, 2, 4, 6, 8]))
+    poly = int(rng.choice([0, 1, 2]))
+    if K - ORC_CRC_LEN[poly] < 4:
+        poly = 2  # tiny codeblocks (BG2, Z = 2) only have room for CRC16
+    max_fill = min((Kb - 2) * Z - 1, 2 * Z, K - ORC_CRC_LEN[poly] - 1)
+    fill = int(rng.integers(0, max_fill + 1)) if (rng.random() < 0.5 and max_fill > 0) else 0
+    lo = K - fill + 2 * Z
+    E = int(rng.integers(lo, 3 * N + 1))
+    E = max(qm, (E // qm) * qm)
+    rv = int(rng.choice([0, 0, 0, 1, 2, 3]))
+    Nref = 0 if rng.random() < 0.6 else int(rng.integers(K + 2 * Z + 1, N + 10))
+    rate = (K - fill) / E
+    # Es/N0 around the waterfall of that rate (BPSK-per-bit channel model of oracle/fec_tx.c)
+    snr = 10 * np.log10(max(2 ** (2 * rate) - 1, 1e-3)) - 0.5 + float(rng.uniform(-2.5, 5.0))
+    return dict(bg=bg, Z=Z, E=E, rv=rv, qm=qm, Nref=Nref, fill=fill, poly=poly, snr=snr,
+                max_iter=int(rng.choice([1, 2, 6, 6, 10, 10])), early=bool(rng.random() < 0.7))
+
+
+def fill_chain_desc(fec, d, i, p, new_data, harq_slot, llr_offset, out_offset, mode=None):
+    d["base_graph"][i], d["lifting_size"][i], d["rv"][i], d["qm"][i] = p["bg"], p["Z"], p["rv"], p["qm"]
+    d["Nref"][i], d["nof_filler_bits"][i], d["E"][i] = p["Nref"], p["fill"], p["E"]
+    d["crc_type"][i], d["max_iter"][i] = ORC_TO_HAL_CRC[p["poly"]], p["max_iter"]
+    d["mode"][i] = fec.MODE_CHAIN if mode is None else mode
+    d["flags"][i] = (fec.FLAG_NEW_DATA if new_data else 0) | (fec.FLAG_EARLY_STOP if p["early"] else 0)
+    d["harq_slot"][i], d["llr_offset"][i], d["out_offset"][i] = harq_slot, llr_offset, out_offset
