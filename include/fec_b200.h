@@ -56,6 +56,8 @@ enum {
 #define FEC_FLAG_NEW_DATA   0x01u /* first HARQ transmission: copy instead of combine (hw cfg .new_data)             */
 #define FEC_FLAG_EARLY_STOP 0x02u /* check CRC after every iteration (hw cfg .use_early_stop; crc != nullptr)        */
 #define FEC_FLAG_NO_CRC     0x04u /* FEC_MODE_DECODE with crc == nullptr: never report crc_pass                      */
+#define FEC_FLAG_HARQ_ZERO  0x08u /* read the soft-buffer slot as all zeros (slot was freed; set by the engine for   */
+                                  /* host-driven batches, by the caller for fec_launch_device)                        */
 
 /* One codeblock operation: POD mirror of hal::hw_pusch_decoder_configuration + buffer placement. 48 bytes.
  * The same struct is read by the host engine and by the kernels. */
@@ -145,7 +147,12 @@ void* fec_host_alloc(size_t bytes); /* pinned host memory */
 void  fec_host_free(void* p);
 
 /* ---- HARQ soft buffers --------------------------------------------------------------------------------------------- */
-int fec_harq_free(fec_engine* e, uint32_t slot);                       /* free_harq_context_entry: zeroes the slot   */
+/* free_harq_context_entry: the slot reads as zeros from now on. Lazy and non-blocking: the engine marks the slot and the
+ * next host-driven operation on it (fec_run_host / fec_queue_enqueue) carries FEC_FLAG_HARQ_ZERO; no GPU work here. */
+int fec_harq_free(fec_engine* e, uint32_t slot);
+/* Materialises the zeros of every freed slot in HBM and synchronises (needed only before fec_launch_device batches
+ * whose descriptors do not carry FEC_FLAG_HARQ_ZERO, or before reading fec_harq_slot_ptr memory directly). */
+int fec_harq_flush(fec_engine* e);
 int fec_harq_read(fec_engine* e, uint32_t slot, int8_t* h_dst, uint32_t n);  /* D2H copy of the first n soft bits     */
 int fec_harq_write(fec_engine* e, uint32_t slot, const int8_t* h_src, uint32_t n); /* H2D (tests, HARQ migration)    */
 

@@ -138,6 +138,7 @@ struct fec_engine {
   fec_dev_tables*       d_tab        = nullptr;
   int8_t*               d_harq       = nullptr;
   std::atomic<uint64_t> launches{0};
+  std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
   std::mutex            run_mtx; // serialises fec_run_host users of the shared staging below
   // staging for fec_run_host
   fec_cb_desc*   d_descs = nullptr;
@@ -183,6 +184,14 @@ int launch(fec_engine*          e,
   }
   e->launches.fetch_add(1);
   return FEC_OK;
+}
+
+// Freed slots are zeroed lazily: the first host-driven operation on one carries FEC_FLAG_HARQ_ZERO.
+void apply_fresh(fec_engine* e, fec_cb_desc& d)
+{
+  if (d.mode != FEC_MODE_DECODE && d.harq_slot < e->cfg.harq_slots && e->fresh[d.harq_slot].exchange(0)) {
+    d.flags |= FEC_FLAG_HARQ_ZERO;
+  }
 }
 
 int slot_alloc(fec_engine* e, batch_slot& s)
@@ -279,7 +288,8 @@ int fec_desc_prepare(fec_cb_desc* d)
   if (d->max_iter == 0 || d->crc_type > 2 || d->mode > 2) {
     return fail(FEC_ERR_BAD_ARG, "max_iter=%u crc_type=%u mode=%u", d->max_iter, d->crc_type, d->mode);
   }
-  if (d->nof_filler_bits >= (Kb - 2) * Z || K - d->nof_filler_bits <= CRC_LEN[d->crc_type]) {
+  if (d->nof_filler_bits >= (Kb - 2) * Z ||
+      (!(d->flags & FEC_FLAG_NO_CRC) && d->mode != FEC_MODE_DEMATCH && K - d->nof_filler_bits <= CRC_LEN[d->crc_type])) {
     return fail(FEC_ERR_BAD_ARG, "nof_filler_bits=%u out of range", d->nof_filler_bits);
   }
   if (d->mode == FEC_MODE_DECODE) {
@@ -345,6 +355,10 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
     return fail(FEC_ERR_NO_MEMORY, "cannot reserve %zu bytes of HBM for %u HARQ slots", harq_bytes, cfg->harq_slots);
   }
   CU_TRY(cudaMemset(e->d_harq, 0, harq_bytes));
+  e->fresh = new (std::nothrow) std::atomic<uint8_t>[cfg->harq_slots];
+  for (uint32_t i = 0; i < cfg->harq_slots; ++i) {
+    e->fresh[i].store(0);
+  }
   CU_TRY(cudaMalloc((void**)&e->d_descs, e->cfg.max_batch_cbs * sizeof(fec_cb_desc)));
   CU_TRY(cudaMalloc((void**)&e->d_llr, e->cfg.max_batch_llrs));
   CU_TRY(cudaMalloc((void**)&e->d_out, (size_t)e->cfg.max_batch_cbs * FEC_MAX_CB_OUT_BYTES));
@@ -377,6 +391,7 @@ void fec_engine_destroy(fec_engine* e)
   cudaFree(e->d_out);
   cudaFree(e->d_res);
   cudaFree(e->d_harq);
+  delete[] e->fresh;
   cudaFree(e->d_tab);
   if (e->stream) {
     cudaStreamDestroy(e->stream);
@@ -443,6 +458,9 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     max_Z = d.lifting_size > max_Z ? d.lifting_size : max_Z;
     any1 |= (d.base_graph == 1);
   }
+  for (uint32_t i = 0; i < n; ++i) {
+    apply_fresh(e, h_descs[i]);
+  }
   std::lock_guard<std::mutex> lk(e->run_mtx);
   CU_TRY(cudaSetDevice(e->cfg.device));
   CU_TRY(cudaMemcpyAsync(e->d_descs, h_descs, n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, e->stream));
@@ -494,8 +512,23 @@ int fec_harq_free(fec_engine* e, uint32_t slot)
   if (!e || slot >= e->cfg.harq_slots) {
     return fail(FEC_ERR_BAD_ARG, "bad HARQ slot %u", slot);
   }
+  e->fresh[slot].store(1);
+  return FEC_OK;
+}
+
+int fec_harq_flush(fec_engine* e)
+{
+  if (!e) {
+    return fail(FEC_ERR_BAD_ARG, "null engine");
+  }
   CU_TRY(cudaSetDevice(e->cfg.device));
-  CU_TRY(cudaMemsetAsync(e->d_harq + (size_t)slot * FEC_HARQ_SLOT_BYTES, 0, FEC_HARQ_SLOT_BYTES, e->stream));
+  CU_TRY(cudaDeviceSynchronize());
+  for (uint32_t s = 0; s < e->cfg.harq_slots; ++s) {
+    if (e->fresh[s].exchange(0)) {
+      CU_TRY(cudaMemsetAsync(e->d_harq + (size_t)s * FEC_HARQ_SLOT_BYTES, 0, FEC_HARQ_SLOT_BYTES, e->stream));
+    }
+  }
+  CU_TRY(cudaStreamSynchronize(e->stream));
   return FEC_OK;
 }
 
@@ -503,6 +536,10 @@ int fec_harq_read(fec_engine* e, uint32_t slot, int8_t* h_dst, uint32_t n)
 {
   if (!e || slot >= e->cfg.harq_slots || n > FEC_HARQ_SLOT_BYTES || !h_dst) {
     return fail(FEC_ERR_BAD_ARG, "bad HARQ read");
+  }
+  if (e->fresh[slot].load()) {
+    memset(h_dst, 0, n);
+    return FEC_OK;
   }
   CU_TRY(cudaSetDevice(e->cfg.device));
   CU_TRY(cudaDeviceSynchronize());
@@ -517,6 +554,9 @@ int fec_harq_write(fec_engine* e, uint32_t slot, const int8_t* h_src, uint32_t n
   }
   CU_TRY(cudaSetDevice(e->cfg.device));
   CU_TRY(cudaDeviceSynchronize());
+  if (e->fresh[slot].exchange(0)) {
+    CU_TRY(cudaMemset(e->d_harq + (size_t)slot * FEC_HARQ_SLOT_BYTES, 0, FEC_HARQ_SLOT_BYTES));
+  }
   CU_TRY(cudaMemcpy(e->d_harq + (size_t)slot * FEC_HARQ_SLOT_BYTES, h_src, n, cudaMemcpyHostToDevice));
   return FEC_OK;
 }
@@ -625,6 +665,7 @@ int fec_queue_enqueue(fec_engine* e, uint32_t queue_id, const fec_cb_desc* desc,
       d.llr_offset = s.llr_used;
       d.out_offset = s.out_used;
       memcpy(s.h_llr + s.llr_used, llr, d.E);
+      apply_fresh(e, d); // only once the operation is certain to be accepted
       s.h_descs[s.n] = d;
       s.tags[s.n]    = tag;
       s.h_res[s.n].status = 0;

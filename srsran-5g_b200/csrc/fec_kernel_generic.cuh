@@ -139,6 +139,7 @@ __device__ __forceinline__ void fec_dematch_cta(const fec_cb_desc& D,
   const uint32_t qm      = D.qm;
   const uint32_t Kp      = E / qm;
   const bool     newd    = (D.flags & FEC_FLAG_NEW_DATA) != 0;
+  const bool     hzero   = (D.flags & FEC_FLAG_HARQ_ZERO) != 0;
   const uint32_t Lc      = Ncb - fillers;                                    // non-filler positions of the circular buffer
   const uint32_t k0c     = (k0 < info) ? k0 : (max(k0, sys) - fillers);      // start, in filler-free coordinates
   const uint32_t zero_lo = min(k0, info);                                    // [0, zero_lo) is zeroed in copy mode
@@ -162,7 +163,7 @@ __device__ __forceinline__ void fec_dematch_cta(const fec_cb_desc& D,
     } else if (newd && is_filler) {
       acc = 127;
     } else {
-      acc = harq[o];
+      acc = hzero ? 0 : harq[o];
     }
     if (!is_filler && o < Ncb) {
       const uint32_t q     = (o < info) ? o : (o - fillers);

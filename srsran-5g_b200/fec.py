@@ -18,7 +18,7 @@ from . import build as _build
 
 CRC16, CRC24B, CRC24A = 0, 1, 2  # hal::hw_dec_cb_crc_type numbering
 MODE_CHAIN, MODE_DECODE, MODE_DEMATCH = 0, 1, 2
-FLAG_NEW_DATA, FLAG_EARLY_STOP, FLAG_NO_CRC = 1, 2, 4
+FLAG_NEW_DATA, FLAG_EARLY_STOP, FLAG_NO_CRC, FLAG_HARQ_ZERO = 1, 2, 4, 8
 RES_CRC_PASS, RES_TOO_SHORT, RES_DONE = 1, 2, 0x80
 HARQ_SLOT_BYTES = 25344
 MAX_CB_OUT_BYTES = 1056
@@ -48,7 +48,7 @@ class EngineCfg(C.Structure):
 EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_engine_create", "fec_engine_destroy",
            "fec_engine_stream", "fec_harq_slot_ptr", "fec_engine_launch_count", "fec_desc_prepare",
            "fec_launch_device", "fec_run_host", "fec_host_alloc", "fec_host_free", "fec_harq_free", "fec_harq_read",
-           "fec_harq_write", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
+           "fec_harq_write", "fec_harq_flush", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
            "fec_queue_poll", "fec_queue_fetch"]
 
 _lib = None
@@ -86,6 +86,7 @@ def load_library():
     lib.fec_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
                                  C.c_void_p, C.c_void_p]
     lib.fec_harq_free.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_harq_flush.argtypes = [C.c_void_p]
     lib.fec_harq_read.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
     lib.fec_harq_write.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
     lib.fec_queue_reserve.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
@@ -179,7 +180,7 @@ class FecEngine:
             return a if isinstance(a, int) else (a.ctypes.data if a is not None else None)
 
         def size(a, given=None):
-            return a.nbytes if hasattr(a, "nbytes") else given
+            return a.nbytes if hasattr(a, "nbytes") else (given or 0)
 
         _check(self.lib, self.lib.fec_run_host(self.h, descs.ctypes.data, n, ptr(llr), size(llr), ptr(out), size(out),
                                                results.ctypes.data, ptr(soft_out)))
@@ -187,6 +188,9 @@ class FecEngine:
 
     def harq_free(self, slot):
         _check(self.lib, self.lib.fec_harq_free(self.h, slot))
+
+    def harq_flush(self):
+        _check(self.lib, self.lib.fec_harq_flush(self.h))
 
     def harq_read(self, slot, n=HARQ_SLOT_BYTES):
         buf = np.zeros(n, np.int8)
@@ -289,7 +293,7 @@ class LdpcDecoder:
         d["nof_filler_bits"], d["E"] = cfg.nof_filler_bits, input.size
         d["max_iter"], d["mode"] = max_iterations, MODE_DECODE
         if crc is None:
-            d["crc_type"], d["flags"] = CRC24B, FLAG_NO_CRC
+            d["crc_type"], d["flags"] = CRC16, FLAG_NO_CRC
         else:
             d["crc_type"], d["flags"] = crc, FLAG_EARLY_STOP
         llr = np.ascontiguousarray(input, np.int8)

@@ -52,7 +52,7 @@ def test_hal_tb_harq_sequence(fec, engine, oracle, orc):
         cfgs, llrs, want = [], [], []
         for i in range(n_cb):
             tx = oracle.rate_match(bg, Z, cbs[i], Es[i], rv, qm, 0, fill)
-            llr = oracle.awgn_llr(tx, 7.0 + 0.25 * i, seed=i * 8 + t)
+            llr = oracle.awgn_llr(tx, 4.6 + 0.25 * i, seed=i * 8 + t)
             cfgs.append(fec.HwPuschDecoderConfiguration(
                 base_graph_index=bg, modulation=qm, nof_segments=n_cb, rv=rv, cw_length=Es[i], lifting_size=Z,
                 Ncb=N, Nref=0, nof_segment_bits=K - fill - 24, nof_filler_bits=fill, max_nof_ldpc_iterations=6,
@@ -114,7 +114,7 @@ def test_full_size_batch_properties(fec, oracle, orc):
         K, N = cases.dims(bg, Z)
         base, msgs = [], []
         for i in range(n_distinct):
-            llr, msg = oracle.make_case(bg, Z, N, 0, 2, 0, 0, orc.CRC24B, -1.6 + 0.1 * i, seed=9000 + i)
+            llr, msg = oracle.make_case(bg, Z, N, 0, 2, 0, 0, orc.CRC24B, -4.2 + 0.1 * i, seed=9000 + i)
             base.append(llr)
             msgs.append(np.packbits(msg))
         llr = np.stack([base[i % n_distinct] for i in range(n)])

@@ -20,6 +20,8 @@ def run_chain_batch(fec, eng, items, mode=None):
     offs = np.cumsum([0] + [((it["llr"].size + 15) // 16) * 16 for it in items])
     llr = np.zeros(int(offs[-1]) + 16, np.int8)
     for i, it in enumerate(items):
+        if it["new_data"]:
+            eng.harq_free(it["slot"])  # the reference starts a new HARQ process from a zeroed buffer (trap T8)
         cases.fill_chain_desc(fec, d, i, it["p"], it["new_data"], it["slot"], int(offs[i]), i * fec.MAX_CB_OUT_BYTES,
                               mode=mode)
         llr[offs[i]:offs[i] + it["llr"].size] = it["llr"]
