@@ -1,0 +1,360 @@
+#!/usr/bin/env python3
+"""bench.py -- decoded info Gbit/s of the PUSCH FEC decode hot path (rate dematch + HARQ write -> LDPC -> CRC).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--cbs B] [--esn0 dB]
+
+A "step" is one pass of the hot path over one batch of B synthetic codeblocks (BASELINE.json metric shape: BG1, Z=384,
+rate ~1/3 i.e. E = N = 25344 LLRs per codeblock, QPSK interleaving, new data, 6 LDPC iterations FORCED (no early stop: the
+work is data independent and nothing is skipped), CRC24B check). One JSON line on stdout; see DESIGN.md "Measurement".
+
+  value        device-resident: LLRs already in HBM, one fec_launch_device per step, CUDA events on the engine's stream
+  e2e          the same batch through fec_run_host from pinned HOST buffers (H2D + kernels + D2H inside the timed region)
+  roofline     the decode kernel against the measured HBM peak (algorithmic bytes per codeblock: DESIGN.md), plus the
+               integer-ALU view in "alu"
+  cpu_baseline the reference's own best CPU decoder (oracle/_ref: AVX-512 / AVX2 chosen by its own factory) on all host
+               cores, bounded sample, rank 0 at N=1 only
+  --impl reference   the reference CPU implementation alone, same config / metric / unit
+
+The product path never touches oracle/: only cpu_baseline and --impl reference load oracle/pyoracle.py (the checker).
+Inputs are an all-zero codeword (a valid codeword of every linear code, CRC included) through a BPSK-AWGN channel,
+quantised like log_likelihood_ratio::quantize(2y/sigma^2, 20) (lib/phy/upper/log_likelihood_ratio.cpp:90-99).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as ge  # noqa: E402
+
+BG, Z, QM, MAX_ITER = 1, 384, 2, 6
+K, N = 22 * Z, 66 * Z
+E = N
+INFO_BITS = K  # no fillers
+# Algorithmic HBM bytes per codeblock of this workload: E LLRs in + N soft-buffer bytes out + K/8 decoded
+# bytes + 8 result bytes + 48 descriptor bytes.
+ALGO_BYTES_PER_CB = E + N + K // 8 + 8 + 48
+# Edge-message updates per codeblock: iterations x Z x sum of row degrees (316 for the 46 rows of BG1).
+EDGE_UPDATES_PER_CB = MAX_ITER * Z * 316
+LANE_OPS_PER_UPDATE = 26  # canonical scalar cost of the reference's generic code per update
+
+
+def make_llrs(n, esn0_db, seed):
+    """n x E int8 LLRs: all-zero codeword, y = 1 + sigma*n, llr = quantize(2y/sigma^2, range 20) -> [-120, 120]."""
+    rng = np.random.default_rng(seed)
+    sigma2 = 0.5 * 10.0 ** (-esn0_db / 10.0)
+    out = np.empty((n, E), np.int8)
+    chunk = 256
+    for i in range(0, n, chunk):
+        m = min(chunk, n - i)
+        y = 1.0 + np.sqrt(sigma2) * rng.standard_normal((m, E), dtype=np.float32)
+        v = np.clip(2.0 * y / sigma2, -20.0, 20.0) / 20.0 * 120.0
+        out[i:i + m] = np.round(v).astype(np.int8)
+    return out
+
+
+def fill_descs(fec, d, n, early_stop, slot0=0):
+    d["base_graph"], d["lifting_size"], d["qm"], d["E"], d["rv"] = BG, Z, QM, E, 0
+    d["crc_type"], d["max_iter"], d["mode"] = fec.CRC24B, MAX_ITER, fec.MODE_CHAIN
+    d["flags"] = fec.FLAG_NEW_DATA | (fec.FLAG_EARLY_STOP if early_stop else 0)
+    d["harq_slot"] = slot0 + np.arange(n)
+    d["llr_offset"] = np.arange(n, dtype=np.uint64) * E
+    d["out_offset"] = np.arange(n) * (K // 8)
+    fec.desc_prepare(d)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    FIELDS = ["clocks.sm", "clocks.max.sm", "power.draw", "clocks_event_reasons.hw_slowdown",
+              "clocks_event_reasons.hw_thermal_slowdown", "clocks_event_reasons.sw_thermal_slowdown",
+              "clocks_event_reasons.sw_power_cap"]
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + ",".join(self.FIELDS),
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.1] or [r for _, r in self.rows[-3:]]
+        sm, smax, reasons, power = [], [], set(), []
+        for r in rows:
+            try:
+                sm.append(float(r[0]))
+                smax.append(float(r[1]))
+                power.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def reference_cpu(llr, n_threads, seconds, early_stop, impl=None):
+    """Times the reference's CPU chain (dematch + LDPC + CRC; oracle/_ref = unmodified reference sources) on a bounded
+    sample: calibrates on a few codeblocks, then runs about `seconds` of work. Returns (Gbit/s, description dict)."""
+    orc = ge.load_oracle()
+    if not orc.Ref.available():
+        return None, {"unavailable": "oracle/_ref/libref_fec.so was not shipped"}
+    ref = orc.Ref()
+    if impl is None:
+        impl = orc.Ref.AVX512 if ref.impl_available(orc.Ref.AVX512) else (
+            orc.Ref.AVX2 if ref.impl_available(orc.Ref.AVX2) else orc.Ref.GENERIC)
+    name = {orc.Ref.GENERIC: "generic", orc.Ref.AVX2: "avx2", orc.Ref.AVX512: "avx512"}[impl]
+    args_ = (True, 0, QM, 0, 0, orc.CRC24B, MAX_ITER, early_stop)
+    ref.batch_chain(impl, n_threads, BG, Z, llr[:n_threads], *args_)  # warm-up: decoder objects, page faults
+    total_s, total_n, n_pass, t_start = 0.0, 0, 0, time.time()
+    while total_s < seconds and time.time() - t_start < 3 * seconds + 5:
+        sec, iters, _ = ref.batch_chain(impl, n_threads, BG, Z, llr, *args_)
+        total_s += sec
+        total_n += len(llr)
+        n_pass += int((iters > 0).sum())
+    gbps = total_n * INFO_BITS / total_s / 1e9
+    return gbps, {"kind": "reference", "cores": n_threads, "impl": "ldpc_decoder_" + name + " + ldpc_rate_dematcher_" + name,
+                  "sample": "%d codeblocks (%d distinct) of the same workload (BG1 Z=384 E=%d, %d iterations, "
+                            "early_stop=%s) in %.2f s of parallel decode time" % (total_n, len(llr), E, MAX_ITER,
+                                                                                  early_stop, total_s),
+                  "crc_pass_fraction": n_pass / max(total_n, 1)}
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation, all host threads, same config / metric / unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = host_threads()
+    per_step = min(20.0, 150.0 / max(1, args.steps + args.warmup))
+    llr = make_llrs(max(32 * threads, 256), args.esn0, seed=1)
+    vals, desc = [], None
+    for s in range(args.warmup + args.steps):
+        t0 = time.time()
+        gbps, desc = reference_cpu(llr, threads, per_step, early_stop=False)
+        if gbps is None:
+            print(json.dumps({"impl": "reference", "unavailable": desc["unavailable"]}))
+            return 0
+        if s >= args.warmup:
+            vals.append((gbps, time.time() - t0))
+    value = float(np.mean([v for v, _ in vals]))
+    desc["value"] = value
+    desc["unit"] = "Gbit/s"
+    line = {"impl": "reference", "metric": "decoded_info_gbps", "value": value, "unit": "Gbit/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean([t for _, t in vals]) * 1e3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": workload_config(args.cbs), "cpu_baseline": desc,
+            "e2e": {"value": value, "unit": "Gbit/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(n_cbs):
+    return {"workload": "PUSCH FEC decode chain, BG1 Z=384 K=8448, E=N=25344 (rate ~1/3), Qm=2, rv0 new data, "
+                        "6 LDPC iterations forced (no early stop), CRC24B, scaled min-sum 0.8",
+            "codeblocks_per_step_per_gpu": n_cbs, "max_iterations": MAX_ITER, "early_stop": False,
+            "l2_policy": "inputs larger than L2 (%d MB of LLRs + as much soft buffer per step)"
+                         % ((n_cbs or 0) * E // 1000000)}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the FEC engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    fec = ge.load_package().fec
+    n = args.cbs
+    eng = fec.FecEngine(device=local, harq_slots=n, max_batch_cbs=n, nof_queues=2)
+    dev = torch.device("cuda", local)
+
+    # ---- synthetic inputs: pinned host copies (e2e) and device-resident copies (value) --------------------------------
+    llr_h = make_llrs(n, args.esn0, seed=1234 + rank)
+    descs = fec.make_descs(n)
+    fill_descs(fec, descs, n, early_stop=False)
+    t_llr_pin = torch.from_numpy(llr_h).pin_memory()
+    t_out_pin = torch.zeros(n * (K // 8), dtype=torch.uint8).pin_memory()
+    d_llr = t_llr_pin.to(dev)
+    d_descs = torch.from_numpy(descs.view(np.uint8).copy()).to(dev)
+    d_out = torch.zeros(n * (K // 8), dtype=torch.uint8, device=dev)
+    d_res = torch.zeros(n * 8, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.ExternalStream(eng.stream, device=dev)  # events must sit on the stream the kernels run on
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(dd=d_descs):
+        eng.launch_device(dd.data_ptr(), n, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True)
+
+    def timed(fn, steps, per_step_events=False):
+        """Barrier + sync both sides, CUDA events on the engine stream; returns (seconds, per-step ms list)."""
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+        barrier()
+        t0 = time.time()
+        with torch.cuda.stream(stream):
+            evs[0].record(stream)
+            for i in range(steps):
+                fn()
+                evs[i + 1].record(stream)
+        stream.synchronize()
+        barrier()
+        t1 = time.time()
+        per = [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
+        return evs[0].elapsed_time(evs[-1]) / 1e3, per, t0, t1
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- value: device-resident ------------------------------------------------------------------------------------------
+    for _ in range(args.warmup):
+        step_device()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    l0 = eng.launch_count
+    sec, per_step, t0, t1 = timed(step_device, args.steps)
+    launches = eng.launch_count - l0
+    clocks = sampler.stop(t0, t1)
+    sec = max_over_ranks(sec)
+    total_cbs = n * args.steps * world
+    value = total_cbs * INFO_BITS / sec / 1e9
+    kernel_s = float(np.mean(per_step)) / 1e3  # one launch per step: the step time IS the kernel's launch duration
+    res = np.frombuffer(d_res.cpu().numpy().tobytes(), fec.RESULT_DTYPE)
+    out_h = d_out.cpu().numpy().reshape(n, K // 8)
+    passed = (res["status"] & fec.RES_CRC_PASS) != 0
+    assert (res["status"] & fec.RES_DONE).all(), "kernel did not complete every codeblock"
+    assert (out_h[passed] == 0).all(), "a CRC-passing codeblock does not carry the transmitted (all-zero) message"
+
+    # ---- early-stop variant of the same batch (reported beside the headline, not instead of it) ------------------------
+    descs_es = descs.copy()
+    descs_es["flags"] = fec.FLAG_NEW_DATA | fec.FLAG_EARLY_STOP
+    d_descs_es = torch.from_numpy(descs_es.view(np.uint8).copy()).to(dev)
+    step_device(d_descs_es)
+    sec_es, _, _, _ = timed(lambda: step_device(d_descs_es), max(2, args.steps // 2))
+    sec_es = max_over_ranks(sec_es)
+    res_es = np.frombuffer(d_res.cpu().numpy().tobytes(), fec.RESULT_DTYPE)
+    early = {"value": n * max(2, args.steps // 2) * world * INFO_BITS / sec_es / 1e9, "unit": "Gbit/s",
+             "esn0_db": args.esn0, "mean_iterations": float(res_es["nof_ldpc_iterations"].mean()),
+             "crc_pass_fraction": float(((res_es["status"] & fec.RES_CRC_PASS) != 0).mean())}
+
+    # ---- e2e: host buffers through fec_run_host (H2D + kernels + D2H inside the timed region) --------------------------
+    res_h = np.zeros(n, fec.RESULT_DTYPE)
+    llr_ptr, out_ptr = t_llr_pin.data_ptr(), t_out_pin.data_ptr()
+
+    def step_host():
+        eng.lib.fec_run_host(eng.h, descs.ctypes.data, n, llr_ptr, n * E, out_ptr, n * (K // 8), res_h.ctypes.data, None)
+
+    for _ in range(2):
+        step_host()
+    barrier()
+    e2e_steps = max(2, min(args.steps, 10))
+    tw0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_host()  # synchronous: returns after the D2H copies have landed
+    barrier()
+    e2e_sec = max_over_ranks(time.perf_counter() - tw0)
+    e2e_val = n * e2e_steps * world * INFO_BITS / e2e_sec / 1e9
+    assert (res_h["status"] & fec.RES_DONE).all()
+
+    line = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = n * ALGO_BYTES_PER_CB / kernel_s / 1e9
+        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+        sm_mhz = clocks.get("sm_mhz") or 1965.0
+        upd_per_s = n * EDGE_UPDATES_PER_CB / kernel_s
+        alu_peak = sm_count * 128 * sm_mhz * 1e6 * 4  # packed int8 lane-ops/s if every INT32 lane did 4 bytes per clock
+        line = {"metric": "decoded_info_gbps", "value": value, "unit": "Gbit/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+                "config": workload_config(n), "per_gpu_gbps": value / world,
+                "crc_pass_fraction": float(passed.mean()),
+                "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + K // 8 + 48),
+                        "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
+                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
+                             "frac": achieved / peak_gbs, "traffic": None, "kernel": "fec decode kernel (1 launch/step)",
+                             "kernel_ms": kernel_s * 1e3, "algorithmic_bytes_per_cb": ALGO_BYTES_PER_CB,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                             "alu": {"edge_updates_per_s": upd_per_s,
+                                     "lane_ops_per_s": upd_per_s * LANE_OPS_PER_UPDATE, "peak_lane_ops_per_s": alu_peak,
+                                     "frac": upd_per_s * LANE_OPS_PER_UPDATE / alu_peak, "sm_count": sm_count,
+                                     "note": "canonical 26 int8 lane-ops per edge update vs SMs x 128 lanes x 4 bytes "
+                                             "x sampled SM clock"}}}
+        if world == 1 and not args.no_cpu_baseline:
+            gbps, desc = reference_cpu(llr_h[:max(32 * host_threads(), 256)], host_threads(), args.cpu_seconds, False)
+            if gbps is not None:
+                desc["value"], desc["unit"] = gbps, "Gbit/s"
+            line["cpu_baseline"] = desc
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cbs", type=int, default=148 * 48, help="codeblocks per step per GPU")
+    ap.add_argument("--esn0", type=float, default=-2.0, help="BPSK Es/N0 in dB of the synthetic channel")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    return run_reference(args) if args.impl == "reference" else run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
