@@ -136,6 +136,8 @@ struct fec_engine {
   int                   sm_count     = 0;
   cudaStream_t          stream       = nullptr;
   fec_dev_tables*       d_tab        = nullptr;
+  fec_packed_tables*    d_ptab       = nullptr;
+  bool                  packed_ok    = false;
   int8_t*               d_harq       = nullptr;
   std::atomic<uint64_t> launches{0};
   std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
@@ -168,9 +170,9 @@ int launch(fec_engine*          e,
     return fail(FEC_ERR_BAD_ARG, "max_Z=%u is not a lifting size", max_Z);
   }
   CU_TRY(cudaSetDevice(e->cfg.device));
-  const bool packed_ok = (e->cfg.kernel_variant != 1) && fec_packed_supported(max_Z);
+  const bool packed_ok = (e->cfg.kernel_variant != 1) && e->packed_ok;
   if (packed_ok) {
-    int r = fec_packed_launch(st, d_descs, n, d_llr, d_out, d_res, e->d_harq, e->d_tab, max_Z, any_bg1);
+    int r = fec_packed_launch(st, d_descs, n, d_llr, d_out, d_res, e->d_harq, e->d_tab, e->d_ptab, max_Z, any_bg1);
     if (r != FEC_OK) {
       return fail(r, "packed kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
     }
@@ -347,6 +349,13 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   build_tables(*h, cfg->scaling_factor);
   CU_TRY(cudaMalloc((void**)&e->d_tab, sizeof(fec_dev_tables)));
   CU_TRY(cudaMemcpy(e->d_tab, h, sizeof(fec_dev_tables), cudaMemcpyHostToDevice));
+  {
+    fec_packed_tables* hp = new (std::nothrow) fec_packed_tables();
+    e->packed_ok          = fec_packed_build_tables(*hp, *h, FEC_ALL_Z);
+    CU_TRY(cudaMalloc((void**)&e->d_ptab, sizeof(fec_packed_tables)));
+    CU_TRY(cudaMemcpy(e->d_ptab, hp, sizeof(fec_packed_tables), cudaMemcpyHostToDevice));
+    delete hp;
+  }
   delete h;
   const size_t harq_bytes = (size_t)cfg->harq_slots * FEC_HARQ_SLOT_BYTES;
   if (cudaMalloc((void**)&e->d_harq, harq_bytes) != cudaSuccess) {
@@ -393,6 +402,7 @@ void fec_engine_destroy(fec_engine* e)
   cudaFree(e->d_harq);
   delete[] e->fresh;
   cudaFree(e->d_tab);
+  cudaFree(e->d_ptab);
   if (e->stream) {
     cudaStreamDestroy(e->stream);
   }

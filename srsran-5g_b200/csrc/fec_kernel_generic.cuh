@@ -121,10 +121,23 @@ __device__ __forceinline__ void fec_generic_row(int8_t*         soft,
 // Rate dematcher for one codeblock, executed by the whole CTA. Writes the updated soft buffer to `harq` (N bytes) and,
 // when `soft` is not null, the clamped copy the decoder starts from. Returns through *n_sig_smem (atomicMax) the
 // number of LLRs left after trimming trailing zeros.
+// Where the decoder's working copy of the dematched soft bits goes: natural int8 layout (generic kernel) or nothing.
+struct fec_soft_store_natural {
+  int8_t*  soft; // nullptr: dematch only
+  uint32_t Z;
+  __device__ __forceinline__ void operator()(uint32_t o, int acc) const
+  {
+    if (soft != nullptr) {
+      soft[2 * Z + o] = (int8_t)fec_clampi(acc, -64, 64);
+    }
+  }
+};
+
+template <class SoftStore>
 __device__ __forceinline__ void fec_dematch_cta(const fec_cb_desc& D,
                                                 const int8_t* __restrict__ in,
                                                 int8_t* __restrict__ harq,
-                                                int8_t*   soft,
+                                                const SoftStore& soft_store,
                                                 uint32_t* n_sig_smem)
 {
   const uint32_t Z       = D.lifting_size;
@@ -186,9 +199,7 @@ __device__ __forceinline__ void fec_dematch_cta(const fec_cb_desc& D,
       acc = 0;
     }
     harq[o] = (int8_t)acc;
-    if (soft != nullptr) {
-      soft[2 * Z + o] = (int8_t)fec_clampi(acc, -64, 64);
-    }
+    soft_store(o, acc);
     if (acc != 0) {
       my_sig = o + 1; // o increases monotonically per thread
     }
@@ -255,18 +266,18 @@ __device__ __forceinline__ bool fec_crc_ok_cta(const uint32_t* bitsw, uint32_t T
   return ok;
 }
 
-__global__ void __launch_bounds__(384, 2)
-fec_cb_generic_kernel(const fec_cb_desc* __restrict__ descs,
-                      const int8_t* __restrict__ llr_base,
-                      uint8_t* __restrict__ out_base,
-                      fec_cb_result* __restrict__ results,
-                      int8_t* __restrict__ harq_base,
-                      const fec_dev_tables* __restrict__ tab)
+// One codeblock by the whole CTA (any blockDim that is a multiple of 32): dematch / load, decode, CRC, outputs.
+__device__ __noinline__ void fec_generic_cb(const fec_cb_desc& D,
+                                            uint32_t           cb,
+                                            uint8_t*           smem_raw,
+                                            const int8_t* __restrict__ llr_base,
+                                            uint8_t* __restrict__ out_base,
+                                            fec_cb_result* __restrict__ results,
+                                            int8_t* __restrict__ harq_base,
+                                            const fec_dev_tables* __restrict__ tab)
 {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  __shared__ uint32_t                     s_nsig;
+  __shared__ uint32_t s_nsig;
 
-  const fec_cb_desc D   = descs[blockIdx.x];
   const uint32_t    Z   = D.lifting_size;
   const int         bg1 = (D.base_graph == 1);
   const uint32_t    Kb = bg1 ? 22u : 10u, nfull = bg1 ? 68u : 52u, M = bg1 ? 46u : 42u;
@@ -338,11 +349,11 @@ fec_cb_generic_kernel(const fec_cb_desc* __restrict__ descs,
     }
   } else {
     int8_t* harq = harq_base + (size_t)D.harq_slot * FEC_HARQ_SLOT_BYTES;
-    fec_dematch_cta(D, in, harq, (D.mode == FEC_MODE_CHAIN) ? soft : nullptr, &s_nsig);
+    fec_dematch_cta(D, in, harq, fec_soft_store_natural{(D.mode == FEC_MODE_CHAIN) ? soft : nullptr, Z}, &s_nsig);
     if (D.mode == FEC_MODE_DEMATCH) {
       if (threadIdx.x == 0) {
         res.status           = FEC_RES_DONE;
-        results[blockIdx.x] = res;
+        results[cb] = res;
       }
       return;
     }
@@ -363,7 +374,7 @@ fec_cb_generic_kernel(const fec_cb_desc* __restrict__ descs,
     }
     if (threadIdx.x == 0) {
       res.status           = FEC_RES_TOO_SHORT | FEC_RES_DONE;
-      results[blockIdx.x] = res;
+      results[cb] = res;
     }
     return;
   }
@@ -407,6 +418,19 @@ fec_cb_generic_kernel(const fec_cb_desc* __restrict__ descs,
     res.nof_ldpc_iterations = (uint16_t)(pass && early_stop ? it : D.max_iter);
     res.status              = (pass ? FEC_RES_CRC_PASS : 0) | FEC_RES_DONE;
     res.nof_layers          = (uint8_t)nlayers;
-    results[blockIdx.x]    = res;
+    results[cb]    = res;
   }
+}
+
+__global__ void __launch_bounds__(384, 2)
+fec_cb_generic_kernel(const fec_cb_desc* __restrict__ descs,
+                      const int8_t* __restrict__ llr_base,
+                      uint8_t* __restrict__ out_base,
+                      fec_cb_result* __restrict__ results,
+                      int8_t* __restrict__ harq_base,
+                      const fec_dev_tables* __restrict__ tab)
+{
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const fec_cb_desc D = descs[blockIdx.x];
+  fec_generic_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab);
 }
