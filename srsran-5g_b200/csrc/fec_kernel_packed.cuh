@@ -1,5 +1,5 @@
-// srsran-5g_b200/csrc/fec_kernel_packed.cuh -- the hot kernel: one CTA per codeblock, one thread per FOUR lifted check
-// nodes, 16-bit SIMD-in-register arithmetic on the native sm_100a half2 pipes.
+// srsran-5g_b200/csrc/fec_kernel_packed.cuh -- the hot kernel: one CTA per codeblock, one thread per TWO lifted check
+// nodes, 16-bit SIMD-in-register arithmetic on the native sm_100a half2 instructions.
 //
 // Number format. Every LLR-domain quantity x (|x| < 2048) lives in a 16-bit lane as sign-magnitude: bit 15 = sign, bits
 // 14..0 = |x|. That bit pattern IS the IEEE fp16 number x * 2^-24 (subnormal for |x| < 1024, normal above, no gap), so
@@ -7,14 +7,14 @@
 // (min(|a|,|b|) with sign(a)^sign(b)), HSET2.BF gives 1.0/0.0 select masks that feed HFMA2, negation is an XOR and |x| an
 // AND. No tensor cores, no floating-point rounding anywhere (every intermediate is an integer below 2048).
 //
-// Shared-memory layout per codeblock (Z = 4W):
-//   soft   nfull*Z bytes. Column b occupies W words; word w holds variables {w, w+W, w+2W, w+3W} of the column in bytes
-//          0..3, stored offset-binary (value + 128). Magnitudes 121..127 all mean the reference's +-127 "infinity".
-//          With this interleave the cyclic shift s = q*W + r of an edge becomes ONE aligned word load at (t + r) mod W
-//          plus a byte rotation by q (+1 on wrap), and the write-back is one aligned word store.
-//   state  per base row and thread word: m1 (4 bytes: scaled min1 of 4 checks), m2, idx, and 1-3 words of c2v sign bits
-//          (byte k = bits of check lane k for 8 edges). All-zero = "row not initialised" (c2v = 0).
-//   edges  per edge {byte address of (col*W + r), W - r, q}: uniform per CTA, read by broadcast.
+// Shared-memory layout per codeblock (Z = 2H, H "halfwords" per column):
+//   soft   nfull*Z bytes. Column b occupies H halfwords; halfword w holds variables {w, w+H} of the column in bytes 0/1,
+//          stored offset-binary (value + 128). Magnitudes 121..127 all mean the reference's +-127 "infinity".
+//          With this interleave the cyclic shift s = q*H + r of an edge becomes ONE aligned 16-bit load at (t + r) mod H
+//          plus a byte swap when q + wrap is odd, and the write-back is one aligned 16-bit store.
+//   state  per base row and thread: word0 = scaled min1 / min2 of both checks; then index of the min1 edge and the c2v
+//          sign bits (1 more word for rows of degree <= 8, 2 otherwise). All-zero = "row not initialised" (c2v = 0).
+//   edges  per edge {byte address of (col*H + r), H - r, unpack/pack selectors}: uniform per CTA, read by broadcast.
 //
 // Bit-exactness with the reference's generic decoder is argued step by step in DESIGN.md ("packed kernel algebra").
 #pragma once
@@ -23,17 +23,20 @@
 #include <cuda_fp16.h>
 #include <string.h>
 
+#define FEC_PACKED_MAX_THREADS 192
+
 struct fec_packed_edge {
-  uint32_t a;   // (col * W + r) * 4 : byte offset of the word thread 0 reads (before wrap)
-  uint32_t thr; // W - r : threads t >= thr wrap around the column
-  uint32_t q;   // byte rotation without wrap
-  uint32_t pad;
+  uint32_t a;    // (col * H + r) * 2 : byte offset of the halfword thread 0 reads (before wrap)
+  uint32_t thr;  // H - r : threads t >= thr wrap around the column
+  uint32_t selN; // low 16 bits: PRMT selector unpacking the halfword into two 16-bit lanes (swapped if q odd),
+                 // high 16 bits: PRMT selector packing two lanes back; used when the thread does not wrap
+  uint32_t selW; // same for threads that wrap (one more swap)
 };
 
 // Device-global tables for the packed kernel (built once per engine).
 struct fec_packed_tables {
-  fec_packed_edge edges[FEC_NOF_GRAPHS][FEC_MAX_EDGES]; // valid for graphs with Z % 4 == 0
-  uint16_t        state_off[2][FEC_MAX_ROWS + 2];        // first state word of row r, in units of W words
+  fec_packed_edge edges[FEC_NOF_GRAPHS][FEC_MAX_EDGES]; // valid for graphs with even Z >= 4
+  uint16_t        state_off[2][FEC_MAX_ROWS + 2];        // first state word of row r, in units of H words
   uint32_t        scale_mul;                             // scaled = (x * scale_mul + scale_add) >> 8 for x in 0..120
   uint32_t        scale_add;
 };
@@ -42,20 +45,24 @@ struct fec_packed_smem_layout {
   uint32_t state, edges, soff, rs, deg, bitsw, red, soft, total;
 };
 
+__host__ __device__ inline uint32_t fec_packed_row_words(uint32_t d)
+{
+  return d <= 8 ? 2u : 3u;
+}
+
 __host__ __device__ inline uint32_t fec_packed_state_words(int bg1)
 {
-  // BG1: 4 rows of degree 19 (6 words), 3 rows of degree 9-10 (5 words), 39 rows of degree <= 8 (4 words).
-  // BG2: 2 rows of degree 10 (5 words), 40 rows of degree <= 8 (4 words).
-  return bg1 ? (4u * 6u + 3u * 5u + 39u * 4u) : (2u * 5u + 40u * 4u);
+  // BG1: 7 rows of degree > 8 (3 words), 39 rows of degree <= 8 (2 words). BG2: 2 rows of degree 10, 40 rows <= 8.
+  return bg1 ? (7u * 3u + 39u * 2u) : (2u * 3u + 40u * 2u);
 }
 
 __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, int bg1)
 {
   fec_packed_smem_layout L;
-  const uint32_t         W = Z / 4, nfull = bg1 ? 68u : 52u, Kb = bg1 ? 22u : 10u, ne = bg1 ? 316u : 197u;
+  const uint32_t         H = Z / 2, nfull = bg1 ? 68u : 52u, Kb = bg1 ? 22u : 10u, ne = bg1 ? 316u : 197u;
   uint32_t               o = 0;
   L.state                  = o;
-  o += fec_packed_state_words(bg1) * W * 4;
+  o += fec_packed_state_words(bg1) * H * 4;
   o       = (o + 15) & ~15u;
   L.edges = o;
   o += ne * 16;
@@ -138,158 +145,166 @@ __device__ __forceinline__ uint32_t prmt_f4e(uint32_t a, uint32_t b, uint32_t c)
 #define H2_FM96 0xd600d600u     // -96.0
 #define H2_F2M11 0x10001000u    // 2^-11  : (+-1/16) * 2^-11 = +-512 LLR units
 
-// ---- one base row for the 4 checks {t, t+W, t+2W, t+3W} of this thread -------------------------------------------------
-// D = row degree (compile time so that the per-edge values stay in registers). Lanes: half A = checks (t, t+W), half B =
-// checks (t+2W, t+3W).
+
+// A constant the compiler must keep in a register (LOP3 takes a single immediate).
+__device__ __forceinline__ uint32_t fec_reg_const(uint32_t x)
+{
+  uint32_t r;
+  asm("mov.b32 %0, %1;" : "=r"(r) : "r"(x));
+  return r;
+}
+
+// ---- one base row for the 2 checks {t, t+H} of this thread -------------------------------------------------------------
+// D = row degree (compile time so that the per-edge values stay in registers). Lane 0 = check t, lane 1 = check t+H.
 template <int D>
 __device__ __forceinline__ void fec_packed_row(uint8_t*               soft,
-                                               uint32_t*              st,   // state words of this row for thread t
-                                               const fec_packed_edge* ed,   // D edge records (shared memory)
-                                               uint32_t               W,
+                                               uint32_t*              st, // state words of this row for thread t
+                                               const fec_packed_edge* ed, // D edge records (shared memory)
+                                               uint32_t               H,
                                                uint32_t               t,
                                                uint32_t               scale_mul,
-                                               uint32_t               scale_add)
+                                               uint32_t               scale_add,
+                                               uint32_t               kneg)
 {
-  constexpr int NS = (D + 7) / 8; // sign words
-  const uint32_t t4 = t * 4, W4 = W * 4;
+  constexpr int  NW = (D <= 8) ? 2 : 3;
+  const uint32_t t2 = t * 2, Hb = H * 2;
 
-  // Issue the soft-word loads of every edge first (independent, one aligned LDS.32 each).
-  uint32_t addr[D], rho[D], raw[D];
+  // Issue the soft loads of every edge first (independent, one aligned 16-bit load each).
+  uint32_t addr[D], sel[D], raw[D];
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint4    E    = *reinterpret_cast<const uint4*>(&ed[e]);
-    const bool     wrap = t >= E.y;
-    addr[e]             = E.x + t4 - (wrap ? W4 : 0u);
-    rho[e]              = E.z + (wrap ? 1u : 0u);
-    raw[e]              = *reinterpret_cast<const uint32_t*>(soft + addr[e]);
+    const uint4 E    = *reinterpret_cast<const uint4*>(&ed[e]);
+    const bool  wrap = t >= E.y;
+    addr[e]          = E.x + t2 - (wrap ? Hb : 0u);
+    sel[e]           = wrap ? E.w : E.z;
+    raw[e]           = *reinterpret_cast<const uint16_t*>(soft + addr[e]);
   }
 
   // Previous check-to-variable state of this row.
-  const uint32_t m1w = st[0], m2w = st[W], idw = st[2 * W];
-  uint32_t       sgw[NS];
-#pragma unroll
-  for (int k = 0; k < NS; ++k) {
-    sgw[k] = st[(3 + k) * W];
+  const uint32_t w0 = st[0], w1 = st[H];
+  uint32_t       w2 = 0;
+  if (NW == 3) {
+    w2 = st[2 * H];
   }
-  const uint32_t om1[2] = {__byte_perm(m1w, 0, 0x4140), __byte_perm(m1w, 0, 0x4342)};
-  const uint32_t om2[2] = {__byte_perm(m2w, 0, 0x4140), __byte_perm(m2w, 0, 0x4342)};
-  const uint32_t oid[2] = {__byte_perm(idw, 0, 0x4140), __byte_perm(idw, 0, 0x4342)};
-  uint32_t       odl[2];
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    odl[h] = h2_add(om2[h], om1[h] ^ H2_SIGN); // m2 - m1 >= 0
-  }
+  const uint32_t om1 = __byte_perm(w0, 0, 0x4140), om2 = __byte_perm(w0, 0, 0x4342);
+  const uint32_t odl = h2_add(om2, om1 ^ H2_SIGN); // m2 - m1 >= 0
+  const uint32_t oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 16) ? w2 : __byte_perm(w2, 0, 0x4341));
 
   // ---- phase A: variable-to-check messages and the min1 / min2 / sign-product analysis -----------------------------------
-  uint32_t v[D][2];
-  uint32_t m1[2] = {H2_P120, H2_P120}, m2[2] = {H2_P120, H2_P120};
+  uint32_t v[D];
+  uint32_t m1 = H2_P120, m2 = H2_P120;
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint32_t wr = prmt_f4e(raw[e], raw[e], rho[e]); // lane k <- byte (k + rho) mod 4
-    // sign bits of this edge for lanes (0,1) / (2,3): byte k of sgw holds lane k, bit (e & 7)
-    const uint32_t sw    = sgw[e >> 3];
-    const uint32_t sg[2] = {__byte_perm(sw, 0, 0x1404) << (7 - (e & 7)), __byte_perm(sw, 0, 0x3424) << (7 - (e & 7))};
-    const uint32_t up[2] = {__byte_perm(wr, 0, 0x4140), __byte_perm(wr, 0, 0x4342)};
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const uint32_t S    = h2_add(up[h], H2_M128);                                  // soft value
-      const uint32_t ism  = h2_eq_bf(oid[h], FEC_H2(e));                             // edge e was the min1 edge
-      const uint32_t mag  = h2_fma(ism, odl[h], om1[h]);                             // |old c2v|
-      const uint32_t nsgn = (sg[h] & H2_SIGN) ^ H2_NEG_ONE;                          // -sign(old c2v) as +-1.0
-      const uint32_t vraw = h2_fma(mag, nsgn, S);                                    // soft - c2v, |.| <= 223
-      const uint32_t y    = h2_add(h2_fma(S, H2_F4352, H2_F96), H2_FM96);            // +-1/16 iff |S| > 120
-      const uint32_t vcl  = h2_min_xs(vraw, H2_P120);                                // saturate at +-120
-      const uint32_t vv   = h2_fma(y, H2_F2M11, vcl);                                // "infinite" soft bits stay huge
-      v[e][h]             = vv;
-      const uint32_t mx   = h2_max_xs(m1[h], vv);
-      m2[h]               = h2_min_xs(m2[h], mx);
-      m1[h]               = h2_min_xs(m1[h], vv);
-    }
+    const uint32_t up   = prmt(raw[e], 0u, sel[e]);                                  // lane k <- byte (k + rho) mod 2
+    const uint32_t sw   = (e < 16) ? w1 : w2;
+    const uint32_t S    = h2_add(up, H2_M128);                                       // soft value
+    const uint32_t ism  = h2_eq_bf(oid, FEC_H2(e));                                  // edge e was the min1 edge
+    const uint32_t mag  = h2_fma(ism, odl, om1);                                     // |old c2v|
+    const uint32_t nsgn = ((sw << (15 - (e & 15))) & H2_SIGN) ^ kneg;                // -sign(old c2v) as +-1.0
+    const uint32_t vraw = h2_fma(mag, nsgn, S);                                      // soft - c2v, |.| <= 223
+    const uint32_t y    = h2_add(h2_fma(S, H2_F4352, H2_F96), H2_FM96);              // +-1/16 iff |S| > 120
+    const uint32_t vcl  = h2_min_xs(vraw, H2_P120);                                  // saturate at +-120
+    const uint32_t vv   = h2_fma(y, H2_F2M11, vcl);                                  // "infinite" soft bits stay huge
+    v[e]                = vv;
+    const uint32_t mx   = h2_max_xs(m1, vv);
+    m2                  = h2_min_xs(m2, mx);
+    m1                  = h2_min_xs(m1, vv);
   }
 
-  // ---- scale the two minima: scaled = (x * mul + add) >> 8, two lanes per 32-bit multiply ---------------------------------
-  uint32_t M1s[2], dls[2], a1[2], s1[2], s2[2];
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const uint32_t sp = m1[h] & H2_SIGN; // product of all v2c signs
-    a1[h]             = m1[h] & H2_ABS;
-    s1[h]             = (((a1[h]) * scale_mul + scale_add) >> 8) & 0x00ff00ffu;
-    s2[h]             = (((m2[h] & H2_ABS) * scale_mul + scale_add) >> 8) & 0x00ff00ffu;
-    M1s[h]            = s1[h] | sp;
-    dls[h]            = h2_add(s2[h], s1[h] ^ H2_SIGN) | sp;
-  }
+  // ---- scale the two minima: scaled = (x * mul + add) >> 8, both lanes in one 32-bit multiply -----------------------------
+  const uint32_t sp  = m1 & H2_SIGN; // product of all v2c signs
+  const uint32_t a1  = m1 & H2_ABS;
+  const uint32_t s1  = ((a1 * scale_mul + scale_add) >> 8) & 0x00ff00ffu;
+  const uint32_t s2  = (((m2 & H2_ABS) * scale_mul + scale_add) >> 8) & 0x00ff00ffu;
+  const uint32_t M1s = s1 | sp;
+  const uint32_t dls = h2_add(s2, s1 ^ H2_SIGN) | sp;
 
   // ---- phase B: new check-to-variable messages, soft-bit update, write-back ------------------------------------------------
-  uint32_t nid[2] = {0, 0};
-  uint32_t nsg[NS];
-#pragma unroll
-  for (int k = 0; k < NS; ++k) {
-    nsg[k] = 0;
-  }
+  uint32_t nid = 0, sg1 = 0, sg2 = 0;
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    uint32_t o[2];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const uint32_t vv  = v[e][h];
-      const uint32_t eq  = h2_eq_bf(vv & H2_ABS, a1[h]);       // this edge holds min1 -> it gets min2
-      const uint32_t mg  = h2_fma(eq, dls[h], M1s[h]);         // sign product * scaled magnitude
-      const uint32_t c   = mg ^ (vv & H2_SIGN);                // new c2v
-      nid[h]             = h2_fma(eq, FEC_H2(e), nid[h]);      // index of the min1 edge (any value if min1 == min2)
-      const uint32_t tt  = h2_add(c, vv);                      // c2v + v2c
-      const uint32_t nw  = h2_min_xs(tt, H2_P127);             // |.| > 120 is "infinity" from here on
-      o[h]               = h2_add(nw, H2_P128);                // offset binary in the low byte of each lane
+    const uint32_t vv = v[e];
+    const uint32_t eq = h2_eq_bf(vv & H2_ABS, a1);       // this edge holds min1 -> it gets min2
+    const uint32_t mg = h2_fma(eq, dls, M1s);            // sign product * scaled magnitude
+    const uint32_t c  = mg ^ (vv & H2_SIGN);             // new c2v
+    nid               = h2_fma(eq, FEC_H2(e), nid);      // index of the min1 edge (any value if min1 == min2)
+    const uint32_t tt = h2_add(c, vv);                   // c2v + v2c
+    const uint32_t nw = h2_min_xs(tt, H2_P127);          // |.| > 120 is "infinity" from here on
+    const uint32_t o  = h2_add(nw, H2_P128);             // offset binary in the low byte of each lane
+    // sign(v2c) of the two lanes -> bit (e & 15) of the sign word
+    const uint32_t sb = (vv >> (15 - (e & 15))) & (0x00010001u << (e & 15));
+    if (e < 16) {
+      sg1 |= sb;
+    } else {
+      sg2 |= sb;
     }
-    // sign(v2c) of the 4 lanes as byte masks -> bit (e & 7) of the sign word
-    const uint32_t sm = prmt(v[e][0], v[e][1], 0xfdb9);
-    nsg[e >> 3] |= sm & (0x01010101u << (e & 7));
-    const uint32_t pk = __byte_perm(o[0], o[1], 0x6420);
-    *reinterpret_cast<uint32_t*>(soft + addr[e]) = prmt_f4e(pk, pk, 0u - rho[e]); // byte j <- lane (j - rho) mod 4
+    *reinterpret_cast<uint16_t*>(soft + addr[e]) = (uint16_t)prmt(o, o, sel[e] >> 16); // byte j <- lane (j - rho) mod 2
   }
 
   // ---- new state: c2v sign = sign product ^ sign(v2c) ----------------------------------------------------------------------
-  const uint32_t pm = prmt(m1[0], m1[1], 0xfdb9); // 0xff in the lanes whose sign product is negative
-  st[0]             = __byte_perm(s1[0], s1[1], 0x6420);
-  st[W]             = __byte_perm(s2[0], s2[1], 0x6420);
-  st[2 * W]         = __byte_perm(nid[0], nid[1], 0x6420);
-#pragma unroll
-  for (int k = 0; k < NS; ++k) {
-    st[(3 + k) * W] = nsg[k] ^ pm;
+  const uint32_t pm = prmt(m1, 0u, 0xbb99); // 0xffff in the lanes whose sign product is negative
+  st[0]             = __byte_perm(s1, s2, 0x6420);
+  if (D <= 8) {
+    st[H] = ((sg1 ^ pm) & 0x00ff00ffu) | (nid << 8);
+  } else if (D <= 16) {
+    st[H]     = sg1 ^ pm;
+    st[2 * H] = nid;
+  } else {
+    st[H]     = sg1 ^ pm;
+    st[2 * H] = ((sg2 ^ pm) & 0x00070007u) | (nid << 8);
   }
 }
 
 // Byte address of variable j (0 <= j < Z) of column col in the interleaved soft layout.
-__device__ __forceinline__ uint32_t fec_packed_soft_addr(uint32_t col, uint32_t j, uint32_t Z, uint32_t W, uint32_t invW)
+__device__ __forceinline__ uint32_t fec_packed_soft_addr(uint32_t col, uint32_t j, uint32_t Z, uint32_t H)
 {
-  const uint32_t lane = __umulhi(j, invW); // j / W, exact for j < 2^32 / W
-  return col * Z + (j - lane * W) * 4 + lane;
+  const uint32_t lane = (j >= H) ? 1u : 0u;
+  return col * Z + (j - lane * H) * 2 + lane;
 }
 
 // Dematcher / loader target: clamp to +-64 (ldpc_decoder_impl.cpp:168-169) and store offset-binary in the packed layout.
 struct fec_soft_store_packed {
   uint8_t* soft;
-  uint32_t Z, W, invZ, invW;
+  uint32_t Z, H, invZ;
   __device__ __forceinline__ void operator()(uint32_t o, int acc) const
   {
     const uint32_t op  = o + 2 * Z;
     const uint32_t col = __umulhi(op, invZ);
-    soft[fec_packed_soft_addr(col, op - col * Z, Z, W, invW)] = (uint8_t)(fec_clampi(acc, -64, 64) + 128);
+    soft[fec_packed_soft_addr(col, op - col * Z, Z, H)] = (uint8_t)(fec_clampi(acc, -64, 64) + 128);
   }
 };
 
 // Hard decision of the first K soft bits (bit = soft <= 0) into bitsw, big-endian bit order; true if no soft bit is zero.
-__device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32_t* bitsw, uint32_t K, uint32_t Z, uint32_t W,
-                                                     uint32_t invZ, uint32_t invW)
+__device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32_t* bitsw, uint32_t K, uint32_t Z, uint32_t H,
+                                                     uint32_t invZ)
 {
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const uint32_t nw   = (K + 31) / 32;
   int            zero = 0;
+  if ((H & 31u) == 0) {
+    // One column per step: thread t holds variables t and t+H of the column; a ballot yields 32 consecutive bits.
+    const uint32_t Kb = K / Z;
+    if (threadIdx.x < H) {
+      for (uint32_t col = 0; col < Kb; ++col) {
+        const uint32_t hw = *reinterpret_cast<const uint16_t*>(soft + col * Z + threadIdx.x * 2);
+        const uint32_t b0 = hw & 0xffu, b1 = hw >> 8;
+        zero |= (b0 == 128) | (b1 == 128);
+        const uint32_t bal0 = __ballot_sync(0xffffffffu, b0 <= 128);
+        const uint32_t bal1 = __ballot_sync(0xffffffffu, b1 <= 128);
+        if (lane == 0) {
+          bitsw[(col * Z + warp * 32) >> 5]     = __brev(bal0);
+          bitsw[(col * Z + H + warp * 32) >> 5] = __brev(bal1);
+        }
+      }
+    }
+    return __syncthreads_or(zero) == 0;
+  }
+  const uint32_t nw = (K + 31) / 32;
   for (uint32_t w = warp; w < nw; w += nwarps) {
     const uint32_t i = w * 32 + lane;
     uint32_t       b = 129; // positive
     if (i < K) {
       const uint32_t col = __umulhi(i, invZ);
-      b                  = soft[fec_packed_soft_addr(col, i - col * Z, Z, W, invW)];
+      b                  = soft[fec_packed_soft_addr(col, i - col * Z, Z, H)];
     }
     zero |= (b == 128);
     const uint32_t bal = __ballot_sync(0xffffffffu, b <= 128);
@@ -300,11 +315,217 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32
   return __syncthreads_or(zero) == 0;
 }
 
+// ---- rate dematcher of the packed path ------------------------------------------------------------------------------------
+// Same arithmetic as fec_dematch_cta (the per-byte statement of ldpc_rate_dematcher_impl.cpp:46-257), organised for
+// throughput: the E input LLRs are staged in shared memory with coalesced 16-byte loads (`stage`: the not-yet-used
+// check-state area; global reads when E does not fit), then every thread produces FOUR consecutive soft-buffer bytes per
+// step -- one 32-bit HBM store of the HARQ buffer, a 32-bit load of its previous contents only where the reference keeps
+// or combines them, four byte stores into the decoder's interleaved layout. Groups that straddle a region boundary
+// (k0, fillers, Ncb, end of data, ...) or belong to a wrapping transmission take the per-byte path.
+struct fec_dematch_geom {
+  uint32_t Z, N, Ncb, fillers, sys, info, E, qm, Kp, invKp, Lc, k0c, zero_lo, zero_from, kstart;
+  bool     newd, hzero, wrapped;
+};
+
+__device__ __forceinline__ fec_dematch_geom fec_dematch_geometry(const fec_cb_desc& D)
+{
+  fec_dematch_geom G;
+  G.Z                = D.lifting_size;
+  const uint32_t Kb  = (D.base_graph == 1) ? 22u : 10u;
+  G.N                = ((D.base_graph == 1) ? 66u : 50u) * G.Z;
+  G.Ncb              = (D.Nref > 0) ? min(D.Nref, G.N) : G.N;
+  G.fillers          = D.nof_filler_bits;
+  G.sys              = (Kb - 2) * G.Z;
+  G.info             = G.sys - G.fillers;
+  G.E                = D.E;
+  G.qm               = D.qm;
+  G.Kp               = G.E / G.qm;
+  G.invKp            = 0xffffffffu / G.Kp + 1; // unused when Kp == 1
+  G.newd             = (D.flags & FEC_FLAG_NEW_DATA) != 0;
+  G.hzero            = (D.flags & FEC_FLAG_HARQ_ZERO) != 0;
+  G.Lc               = G.Ncb - G.fillers;                                      // non-filler positions of the circular buffer
+  G.k0c              = (D.k0 < G.info) ? D.k0 : (max(D.k0, G.sys) - G.fillers); // start, in filler-free coordinates
+  G.kstart           = (D.k0 < G.info) ? D.k0 : max(D.k0, G.sys);              // same, as a buffer position
+  G.zero_lo          = min(D.k0, G.info);                                      // [0, zero_lo) is zeroed in copy mode
+  const uint32_t e1  = G.Lc - G.k0c;                                           // LLRs consumed before the first wrap
+  G.wrapped          = G.E > e1;
+  G.zero_from        = G.N;                                                    // [zero_from, N) zeroed at the end
+  if (G.newd && !G.wrapped) {
+    const uint32_t q_end = G.k0c + G.E;
+    uint32_t       idxf  = (G.k0c < G.info && q_end <= G.info) ? G.sys : (q_end + G.fillers);
+    idxf                 = (idxf >= G.Ncb) ? idxf - G.Ncb : idxf;
+    if (idxf != 0) {
+      G.zero_from = G.N - (G.Ncb - idxf);
+    }
+  }
+  return G;
+}
+
+__device__ __forceinline__ uint32_t fec_dematch_src_index(const fec_dematch_geom& G, uint32_t p)
+{
+  if (G.qm == 1) {
+    return p;
+  }
+  const uint32_t j = (G.Kp == 1) ? p : __umulhi(p, G.invKp);
+  return (p - j * G.Kp) * G.qm + j;
+}
+
+// One soft-buffer byte, any case. `old` is the previous buffer value (0 when the slot reads as zeros).
+__device__ __forceinline__ int fec_dematch_byte(const fec_dematch_geom& G, const int8_t* src, uint32_t o, int old)
+{
+  const bool is_filler = (o >= G.info) && (o < G.sys);
+  int        acc;
+  if (G.newd && o < G.zero_lo) {
+    acc = 0;
+  } else if (G.newd && is_filler) {
+    acc = 127;
+  } else {
+    acc = old;
+  }
+  if (!is_filler && o < G.Ncb) {
+    const uint32_t q     = (o < G.info) ? o : (o - G.fillers);
+    const bool     first = (q >= G.k0c);
+    uint32_t       p     = first ? (q - G.k0c) : (q + G.Lc - G.k0c);
+    bool           copy  = G.newd && first;
+    for (; p < G.E; p += G.Lc) {
+      const int dv = src[fec_dematch_src_index(G, p)];
+      acc          = copy ? dv : fec_sat_add(acc, dv);
+      copy         = false;
+    }
+  }
+  return (o >= G.zero_from) ? 0 : acc;
+}
+
+__device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
+                                                   const int8_t* __restrict__ in,
+                                                   int8_t* __restrict__ harq,
+                                                   uint8_t*  soft, // interleaved decoder layout, nullptr = do not fill
+                                                   uint32_t  H,
+                                                   int8_t*   stage,
+                                                   uint32_t  stage_cap,
+                                                   uint32_t* n_sig_smem)
+{
+  const fec_dematch_geom G = fec_dematch_geometry(D);
+  const uint32_t         Z = G.Z, invZ = 0xffffffffu / Z + 1;
+
+  // Stage the input.
+  const int8_t* src = in;
+  if (G.E <= stage_cap) {
+    if ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) {
+      const uint4*   g4 = reinterpret_cast<const uint4*>(in);
+      uint4*         s4 = reinterpret_cast<uint4*>(stage);
+      const uint32_t n4 = G.E / 16;
+      for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x) {
+        s4[i] = __ldg(g4 + i);
+      }
+      for (uint32_t i = n4 * 16 + threadIdx.x; i < G.E; i += blockDim.x) {
+        stage[i] = in[i];
+      }
+    } else {
+      for (uint32_t i = threadIdx.x; i < G.E; i += blockDim.x) {
+        stage[i] = in[i];
+      }
+    }
+    __syncthreads();
+    src = stage;
+  }
+
+  uint32_t       my_sig  = 0;
+  const uint32_t ngroups = G.N / 4; // Z is even and N = 66Z or 50Z, so N % 4 == 0
+  uint32_t*      harq4   = reinterpret_cast<uint32_t*>(harq);
+  const fec_soft_store_packed store{soft, Z, H, invZ};
+  for (uint32_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
+    const uint32_t o0 = g * 4;
+    int            val[4];
+    // A group is simple when no region boundary falls strictly inside it.
+    auto inside = [o0](uint32_t b) { return (b > o0) && (b < o0 + 4); };
+    bool simple = !G.wrapped && !inside(G.zero_lo) && !inside(G.info) && !inside(G.sys) && !inside(G.Ncb) &&
+                  !inside(G.zero_from) && !inside(G.kstart);
+    const bool is_filler = (o0 >= G.info) && (o0 < G.sys);
+    const bool live      = !is_filler && (o0 < G.Ncb);
+    uint32_t   p0 = 0, sidx0 = 0, stride = 1;
+    bool       has_data = false, first = false;
+    if (simple && live) {
+      const uint32_t q0 = (o0 < G.info) ? o0 : (o0 - G.fillers);
+      first             = (q0 >= G.k0c);
+      p0                = first ? (q0 - G.k0c) : (q0 + G.Lc - G.k0c);
+      has_data          = (p0 + 3 < G.E);
+      simple            = has_data || (p0 >= G.E); // the end of the data must not fall inside the group
+      if (has_data && G.qm > 1) {
+        const uint32_t j = (G.Kp == 1) ? p0 : __umulhi(p0, G.invKp);
+        const uint32_t i = p0 - j * G.Kp;
+        simple           = (i + 3 < G.Kp); // all four in the same interleaver row
+        sidx0            = i * G.qm + j;
+        stride           = G.qm;
+      } else {
+        sidx0 = p0;
+      }
+    }
+    if (simple) {
+      const bool preset   = G.newd && (o0 < G.zero_lo);
+      const bool copy     = G.newd && first && has_data;
+      const bool zero_all = (o0 >= G.zero_from);
+      const bool uses_old = !zero_all && (is_filler ? !G.newd : (live ? (!copy && !preset) : true));
+      uint32_t   old      = 0;
+      if (uses_old && !G.hzero) {
+        old = harq4[g];
+      }
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        int a = (is_filler && G.newd) ? 127 : (int)(int8_t)(old >> (8 * b));
+        if (live && has_data) {
+          const int dv = src[sidx0 + b * stride];
+          a            = copy ? dv : fec_sat_add(a, dv);
+        }
+        val[b] = zero_all ? 0 : a;
+      }
+    } else {
+      uint32_t old = 0;
+      if (!G.hzero) {
+        old = harq4[g];
+      }
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        val[b] = fec_dematch_byte(G, src, o0 + b, (int)(int8_t)(old >> (8 * b)));
+      }
+    }
+    harq4[g] = (uint32_t)(uint8_t)val[0] | ((uint32_t)(uint8_t)val[1] << 8) | ((uint32_t)(uint8_t)val[2] << 16) |
+               ((uint32_t)(uint8_t)val[3] << 24);
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      if (val[b] != 0) {
+        my_sig = o0 + b + 1;
+      }
+    }
+    if (soft != nullptr) {
+      const uint32_t op0 = o0 + 2 * Z;
+      const uint32_t col = __umulhi(op0, invZ);
+      const uint32_t j0  = op0 - col * Z;
+      if (j0 + 3 < H || (j0 >= H && j0 + 3 < Z)) {
+        const uint32_t lane = (j0 >= H) ? 1u : 0u;
+        uint8_t*       dst  = soft + col * Z + (j0 - lane * H) * 2 + lane;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          dst[2 * b] = (uint8_t)(fec_clampi(val[b], -64, 64) + 128);
+        }
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          store(o0 + b, val[b]);
+        }
+      }
+    }
+  }
+  if (my_sig != 0) {
+    atomicMax(n_sig_smem, my_sig);
+  }
+}
+
 __device__ __forceinline__ bool fec_packed_cb_supported(const fec_cb_desc& D)
 {
-  // Z must split into 4 interleaved lanes; the unclamped-tail corner (input not a multiple of Z, never produced by
+  // Z must split into 2 interleaved lanes; the unclamped-tail corner (input not a multiple of Z, never produced by
   // PUSCH) stays on the generic path.
-  return (D.lifting_size % 4 == 0) && (D.lifting_size >= 8) && (D.lifting_size / 4 <= blockDim.x) &&
+  return (D.lifting_size % 2 == 0) && (D.lifting_size >= 4) && (D.lifting_size / 2 <= blockDim.x) &&
          !(D.mode == FEC_MODE_DECODE && (D.E % D.lifting_size) != 0) && D.mode != FEC_MODE_DEMATCH;
 }
 
@@ -320,14 +541,17 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
 {
   __shared__ uint32_t s_nsig;
 
-  const uint32_t Z = D.lifting_size, W = Z / 4;
+  const uint32_t Z = D.lifting_size, H = Z / 2;
   const int      bg1 = (D.base_graph == 1);
   const uint32_t Kb = bg1 ? 22u : 10u, nfull = bg1 ? 68u : 52u, M = bg1 ? 46u : 42u;
   const uint32_t K = Kb * Z, N = (nfull - 2) * Z;
   const uint32_t ne = bg1 ? 316u : 197u;
-  const uint32_t invZ = 0xffffffffu / Z + 1, invW = 0xffffffffu / W + 1;
+  const uint32_t invZ = 0xffffffffu / Z + 1;
   const uint32_t tid = threadIdx.x;
 
+#ifdef FEC_PROFILE
+  long long tp0 = clock64(), tp1 = 0, tp2 = 0, tp3 = 0;
+#endif
   const fec_packed_smem_layout L = fec_packed_layout(Z, bg1);
   uint32_t*        state = reinterpret_cast<uint32_t*>(smem_raw + L.state);
   fec_packed_edge* edges = reinterpret_cast<fec_packed_edge*>(smem_raw + L.edges);
@@ -350,14 +574,9 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
       deg[i]  = tab->deg[bg1 ? 0 : 1][i];
       soff[i] = ptab->state_off[bg1 ? 0 : 1][i];
     }
-    uint4*         s4 = reinterpret_cast<uint4*>(state);
-    const uint32_t n4 = (L.edges - L.state) / 16;
-    for (uint32_t i = tid; i < n4; i += blockDim.x) {
-      s4[i] = make_uint4(0, 0, 0, 0);
-    }
     uint32_t* p2 = reinterpret_cast<uint32_t*>(soft);
-    for (uint32_t i = tid; i < 2 * W; i += blockDim.x) {
-      p2[i] = 0x80808080u; // the two punctured columns: soft = 0
+    for (uint32_t i = tid; i < H; i += blockDim.x) {
+      p2[i] = 0x80808080u; // the two punctured columns (2Z bytes): soft = 0
     }
     if (tid == 0) {
       s_nsig = 0;
@@ -372,8 +591,11 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
   res.nof_layers          = 0;
   res.reserved            = 0;
 
+#ifdef FEC_PROFILE
+  tp1 = clock64();
+#endif
   // ---- stage 1: soft bits into shared memory -----------------------------------------------------------------------------
-  const fec_soft_store_packed store{soft, Z, W, invZ, invW};
+  const fec_soft_store_packed store{soft, Z, H, invZ};
   if (D.mode == FEC_MODE_DECODE) {
     const uint32_t n_in   = D.E; // a multiple of Z on this path
     uint32_t       my_sig = 0;
@@ -392,7 +614,16 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
     }
   } else {
     int8_t* harq = harq_base + (size_t)D.harq_slot * FEC_HARQ_SLOT_BYTES;
-    fec_dematch_cta(D, in, harq, store, &s_nsig);
+    fec_dematch_packed(D, in, harq, soft, H, reinterpret_cast<int8_t*>(state), L.edges - L.state, &s_nsig);
+  }
+  __syncthreads();
+  {
+    // The check state doubles as the dematcher's staging area: clear it now ("no c2v messages yet").
+    uint4*         s4 = reinterpret_cast<uint4*>(state);
+    const uint32_t n4 = (L.edges - L.state) / 16;
+    for (uint32_t i = tid; i < n4; i += blockDim.x) {
+      s4[i] = make_uint4(0, 0, 0, 0);
+    }
   }
   __syncthreads();
 
@@ -419,30 +650,34 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
   const uint32_t nlayers = cbl / Z - Kb;
   const uint32_t T       = K - D.nof_filler_bits;
   const uint32_t smul = ptab->scale_mul, sadd = ptab->scale_add;
+  const uint32_t kneg = fec_reg_const(H2_NEG_ONE);
 
+#ifdef FEC_PROFILE
+  tp2 = clock64();
+#endif
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
     for (uint32_t l = 0; l < nlayers; ++l) {
-      if (tid < W) {
-        uint32_t*              st = state + (uint32_t)soff[l] * W + tid;
+      if (tid < H) {
+        uint32_t*              st = state + (uint32_t)soff[l] * H + tid;
         const fec_packed_edge* ed = edges + rs[l];
         switch (deg[l]) {
-          case 3: fec_packed_row<3>(soft, st, ed, W, tid, smul, sadd); break;
-          case 4: fec_packed_row<4>(soft, st, ed, W, tid, smul, sadd); break;
-          case 5: fec_packed_row<5>(soft, st, ed, W, tid, smul, sadd); break;
-          case 6: fec_packed_row<6>(soft, st, ed, W, tid, smul, sadd); break;
-          case 7: fec_packed_row<7>(soft, st, ed, W, tid, smul, sadd); break;
-          case 8: fec_packed_row<8>(soft, st, ed, W, tid, smul, sadd); break;
-          case 9: fec_packed_row<9>(soft, st, ed, W, tid, smul, sadd); break;
-          case 10: fec_packed_row<10>(soft, st, ed, W, tid, smul, sadd); break;
-          default: fec_packed_row<19>(soft, st, ed, W, tid, smul, sadd); break;
+          case 3: fec_packed_row<3>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 4: fec_packed_row<4>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 5: fec_packed_row<5>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 6: fec_packed_row<6>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 7: fec_packed_row<7>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 8: fec_packed_row<8>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 9: fec_packed_row<9>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 10: fec_packed_row<10>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          default: fec_packed_row<19>(soft, st, ed, H, tid, smul, sadd, kneg); break;
         }
       }
       __syncthreads();
     }
     if (early_stop) {
-      const bool clean = fec_hard_bits_packed(soft, bitsw, K, Z, W, invZ, invW);
+      const bool clean = fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
       const bool crc   = fec_crc_ok_cta(bitsw, T, tab, D.crc_type, red);
       if (clean && crc) {
         pass = true;
@@ -451,8 +686,11 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
       }
     }
   }
+#ifdef FEC_PROFILE
+  tp3 = clock64();
+#endif
   if (!early_stop) {
-    fec_hard_bits_packed(soft, bitsw, K, Z, W, invZ, invW);
+    fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
     pass = fec_crc_ok_cta(bitsw, T, tab, D.crc_type, red) && !(D.flags & FEC_FLAG_NO_CRC);
   }
   for (uint32_t i = tid; i < kbytes; i += blockDim.x) {
@@ -462,13 +700,19 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
     res.nof_ldpc_iterations = (uint16_t)(pass && early_stop ? it : D.max_iter);
     res.status              = (pass ? FEC_RES_CRC_PASS : 0) | FEC_RES_DONE;
     res.nof_layers          = (uint8_t)nlayers;
+#ifdef FEC_PROFILE
+    // phase clocks / 256: [7:0] setup, [15:8] dematch / 4, [23:16] decode / 16, [31:24] tail
+    const long long tp4 = clock64();
+    res.reserved = (uint32_t)min(255ll, (tp1 - tp0) >> 8) | ((uint32_t)min(255ll, (tp2 - tp1) >> 10) << 8) |
+                   ((uint32_t)min(255ll, (tp3 - tp2) >> 12) << 16) | ((uint32_t)min(255ll, (tp4 - tp3) >> 8) << 24);
+#endif
     results[cb]            = res;
   }
 }
 
-// Dispatcher: every codeblock the packed path covers goes there, the rest (Z not a multiple of 4, dematch-only
+// Dispatcher: every codeblock the packed path covers goes there, the rest (odd Z, dematch-only
 // operations, unaligned decoder inputs) runs the generic per-check code in the same launch.
-__global__ void __launch_bounds__(96, 2)
+__global__ void __launch_bounds__(FEC_PACKED_MAX_THREADS, 2)
 fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
                      const int8_t* __restrict__ llr_base,
                      uint8_t* __restrict__ out_base,
@@ -511,7 +755,7 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
     uint32_t  off = 0;
     for (int m = 0; m < M; ++m) {
       pt.state_off[bg][m] = (uint16_t)off;
-      off += 3 + (t.deg[bg][m] + 7) / 8;
+      off += fec_packed_row_words(t.deg[bg][m]);
     }
     pt.state_off[bg][M] = (uint16_t)off;
     if (off != fec_packed_state_words(bg == 0)) {
@@ -520,16 +764,20 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
     const int ne = t.row_start[bg][M];
     for (int zi = 0; zi < 51; ++zi) {
       const uint32_t Z = all_z[zi];
-      if (Z % 4 != 0 || Z < 8) {
+      if (Z % 2 != 0 || Z < 4) {
         continue;
       }
-      const uint32_t W = Z / 4;
+      const uint32_t H = Z / 2;
       for (int i = 0; i < ne; ++i) {
         const uint32_t   s = t.shift[bg * 51 + zi][i], col = t.col[bg][i];
+        const uint32_t   q = s / H, r = s % H;
         fec_packed_edge& e = pt.edges[bg * 51 + zi][i];
-        e.a                = (col * W + s % W) * 4;
-        e.thr              = W - s % W;
-        e.q                = s / W;
+        // selector words: low half unpacks (lane k <- byte (k + rho) mod 2, zero-extended), high half packs back
+        const uint32_t sel_even = 0x00204140u, sel_odd = 0x00024041u;
+        e.a                     = (col * H + r) * 2;
+        e.thr                   = H - r;
+        e.selN                  = (q & 1) ? sel_odd : sel_even;
+        e.selW                  = (q & 1) ? sel_even : sel_odd;
       }
     }
   }
@@ -548,10 +796,10 @@ static inline int fec_packed_launch(cudaStream_t             st,
                                     uint32_t                 max_Z,
                                     int                      any_bg1)
 {
-  uint32_t threads = ((max_Z / 4 + 31) / 32) * 32;
-  threads          = threads < 32 ? 32 : (threads > 96 ? 96 : threads);
+  uint32_t threads = ((max_Z / 2 + 31) / 32) * 32;
+  threads          = threads < 32 ? 32 : (threads > FEC_PACKED_MAX_THREADS ? FEC_PACKED_MAX_THREADS : threads);
   const uint32_t a = fec_generic_layout(max_Z, any_bg1).total;
-  const uint32_t b = (max_Z % 4 == 0 && max_Z >= 8) ? fec_packed_layout(max_Z, any_bg1).total : 0;
+  const uint32_t b = (max_Z % 2 == 0 && max_Z >= 4) ? fec_packed_layout(max_Z, any_bg1).total : 0;
   const uint32_t smem = a > b ? a : b;
   if (cudaFuncSetAttribute(fec_cb_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
     return FEC_ERR_CUDA;
