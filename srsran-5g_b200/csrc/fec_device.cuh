@@ -34,19 +34,14 @@ __device__ __forceinline__ int fec_clampi(int v, int lo, int hi)
   return max(lo, min(v, hi));
 }
 
-// x + y with the reference's special cases (x is the accumulator, y the new LLR).
+// x + y with the reference's special cases (x is the accumulator, y the new LLR). Branch-free: later rules override
+// earlier ones in the order of log_likelihood_ratio.cpp:40-73 (equal-and-opposite first, then y infinite, then x infinite).
 __device__ __forceinline__ int fec_sat_add(int x, int y)
 {
-  if (y == -x) {
-    return 0;
-  }
-  if (y == 127 || y == -127) {
-    return y;
-  }
-  if (x == 127 || x == -127) {
-    return x;
-  }
-  return fec_clampi(x + y, -120, 120);
+  int r = fec_clampi(x + y, -120, 120);
+  r     = (x == 127 || x == -127) ? x : r;
+  r     = (y == 127 || y == -127) ? y : r;
+  return (y == -x) ? 0 : r;
 }
 
 // One step of polynomial long division: r <- (r * x) mod g, r of degree < len.

@@ -26,11 +26,10 @@
 #define FEC_PACKED_MAX_THREADS 192
 
 struct fec_packed_edge {
-  uint32_t a;    // (col * H + r) * 2 : byte offset of the halfword thread 0 reads (before wrap)
-  uint32_t thr;  // H - r : threads t >= thr wrap around the column
-  uint32_t selN; // low 16 bits: PRMT selector unpacking the halfword into two 16-bit lanes (swapped if q odd),
-                 // high 16 bits: PRMT selector packing two lanes back; used when the thread does not wrap
-  uint32_t selW; // same for threads that wrap (one more swap)
+  uint32_t aN;  // byte offset of lane 0 for thread 0 when it does not wrap: (col * H + r) * 2 + (q & 1)
+  uint32_t aW;  // same for threads that wrap around the column: (col * H + r - H) * 2 + ((q + 1) & 1)
+  uint32_t thr; // H - r : threads t >= thr wrap
+  uint32_t pad; // lane 1 always sits at the lane-0 address ^ 1
 };
 
 // Device-global tables for the packed kernel (built once per engine).
@@ -118,6 +117,12 @@ __device__ __forceinline__ uint32_t h2_eq_bf(uint32_t a, uint32_t b)
   asm("set.eq.f16x2.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
   return r;
 }
+__device__ __forceinline__ uint32_t h2_abs(uint32_t a)
+{
+  uint32_t r;
+  asm("abs.f16x2 %0, %1;" : "=r"(r) : "r"(a));
+  return r;
+}
 // Generic-mode PRMT with the full selector (the __byte_perm intrinsic strips the sign-replicate bit of each nibble).
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t c)
 {
@@ -154,30 +159,54 @@ __device__ __forceinline__ uint32_t fec_reg_const(uint32_t x)
   return r;
 }
 
+// Shared-memory byte accesses by 32-bit shared-window address (lets the two lanes of a halfword be addressed A and A^1).
+__device__ __forceinline__ uint32_t lds_u8(uint32_t a)
+{
+  uint32_t r;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ void sts_u8(uint32_t a, uint32_t v)
+{
+  asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+// Integer helpers pinned to the FMA pipe (IMAD / IMAD.HI), which this kernel under-uses, instead of SHF / PRMT on the ALU.
+__device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
+{
+  uint32_t r;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t imul_hi(uint32_t a, uint32_t b)
+{
+  uint32_t r;
+  asm("mul.hi.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+
 // ---- one base row for the 2 checks {t, t+H} of this thread -------------------------------------------------------------
 // D = row degree (compile time so that the per-edge values stay in registers). Lane 0 = check t, lane 1 = check t+H.
+// Instruction budget per edge and thread: ALU pipe 14 (ISETP, SEL, IADD3, LOP3 for the addresses; 2 HSET2,
+// 5 HMNMX2, 3 LOP3), FMA pipe 15 (HFMA2 / HADD2 / IMAD), LSU 5.
 template <int D>
-__device__ __forceinline__ void fec_packed_row(uint8_t*               soft,
-                                               uint32_t*              st, // state words of this row for thread t
-                                               const fec_packed_edge* ed, // D edge records (shared memory)
+__device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, // shared-window address of the soft array
+                                               uint32_t*              st,     // state words of this row for thread t
+                                               const fec_packed_edge* ed,     // D edge records (shared memory)
                                                uint32_t               H,
                                                uint32_t               t,
                                                uint32_t               scale_mul,
-                                               uint32_t               scale_add,
-                                               uint32_t               kneg)
+                                               uint32_t               scale_add)
 {
   constexpr int  NW = (D <= 8) ? 2 : 3;
-  const uint32_t t2 = t * 2, Hb = H * 2;
+  const uint32_t tb = soft_s + t * 2;
 
-  // Issue the soft loads of every edge first (independent, one aligned 16-bit load each).
-  uint32_t addr[D], sel[D], raw[D];
+  // Issue the soft loads of every edge first (independent byte loads: lane 0 at A, lane 1 at A ^ 1).
+  uint32_t a0[D], up[D];
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint4 E    = *reinterpret_cast<const uint4*>(&ed[e]);
-    const bool  wrap = t >= E.y;
-    addr[e]          = E.x + t2 - (wrap ? Hb : 0u);
-    sel[e]           = wrap ? E.w : E.z;
-    raw[e]           = *reinterpret_cast<const uint16_t*>(soft + addr[e]);
+    const uint4 E = *reinterpret_cast<const uint4*>(&ed[e]);
+    a0[e]         = ((t >= E.z) ? E.y : E.x) + tb;
+    up[e]         = imad(lds_u8(a0[e] ^ 1u), 65536u, lds_u8(a0[e]));
   }
 
   // Previous check-to-variable state of this row.
@@ -195,13 +224,13 @@ __device__ __forceinline__ void fec_packed_row(uint8_t*               soft,
   uint32_t m1 = H2_P120, m2 = H2_P120;
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint32_t up   = prmt(raw[e], 0u, sel[e]);                                  // lane k <- byte (k + rho) mod 2
     const uint32_t sw   = (e < 16) ? w1 : w2;
-    const uint32_t S    = h2_add(up, H2_M128);                                       // soft value
+    const uint32_t S    = h2_add(up[e], H2_M128);                                    // soft value
     const uint32_t ism  = h2_eq_bf(oid, FEC_H2(e));                                  // edge e was the min1 edge
     const uint32_t mag  = h2_fma(ism, odl, om1);                                     // |old c2v|
-    const uint32_t nsgn = ((sw << (15 - (e & 15))) & H2_SIGN) ^ kneg;                // -sign(old c2v) as +-1.0
-    const uint32_t vraw = h2_fma(mag, nsgn, S);                                      // soft - c2v, |.| <= 223
+    const uint32_t sgs  = imad(sw, 1u << (15 - (e & 15)), 0u);                       // its sign bits at 15 / 31
+    const uint32_t cneg = mag ^ (~sgs & H2_SIGN);                                    // -(old c2v)
+    const uint32_t vraw = h2_add(S, cneg);                                           // soft - c2v, |.| <= 223
     const uint32_t y    = h2_add(h2_fma(S, H2_F4352, H2_F96), H2_FM96);              // +-1/16 iff |S| > 120
     const uint32_t vcl  = h2_min_xs(vraw, H2_P120);                                  // saturate at +-120
     const uint32_t vv   = h2_fma(y, H2_F2M11, vcl);                                  // "infinite" soft bits stay huge
@@ -214,8 +243,8 @@ __device__ __forceinline__ void fec_packed_row(uint8_t*               soft,
   // ---- scale the two minima: scaled = (x * mul + add) >> 8, both lanes in one 32-bit multiply -----------------------------
   const uint32_t sp  = m1 & H2_SIGN; // product of all v2c signs
   const uint32_t a1  = m1 & H2_ABS;
-  const uint32_t s1  = ((a1 * scale_mul + scale_add) >> 8) & 0x00ff00ffu;
-  const uint32_t s2  = (((m2 & H2_ABS) * scale_mul + scale_add) >> 8) & 0x00ff00ffu;
+  const uint32_t s1  = imul_hi(imad(a1, scale_mul, scale_add), 1u << 24) & 0x00ff00ffu;
+  const uint32_t s2  = imul_hi(imad(m2 & H2_ABS, scale_mul, scale_add), 1u << 24) & 0x00ff00ffu;
   const uint32_t M1s = s1 | sp;
   const uint32_t dls = h2_add(s2, s1 ^ H2_SIGN) | sp;
 
@@ -224,7 +253,7 @@ __device__ __forceinline__ void fec_packed_row(uint8_t*               soft,
 #pragma unroll
   for (int e = 0; e < D; ++e) {
     const uint32_t vv = v[e];
-    const uint32_t eq = h2_eq_bf(vv & H2_ABS, a1);       // this edge holds min1 -> it gets min2
+    const uint32_t eq = h2_eq_bf(h2_abs(vv), a1);        // this edge holds min1 -> it gets min2
     const uint32_t mg = h2_fma(eq, dls, M1s);            // sign product * scaled magnitude
     const uint32_t c  = mg ^ (vv & H2_SIGN);             // new c2v
     nid               = h2_fma(eq, FEC_H2(e), nid);      // index of the min1 edge (any value if min1 == min2)
@@ -232,13 +261,14 @@ __device__ __forceinline__ void fec_packed_row(uint8_t*               soft,
     const uint32_t nw = h2_min_xs(tt, H2_P127);          // |.| > 120 is "infinity" from here on
     const uint32_t o  = h2_add(nw, H2_P128);             // offset binary in the low byte of each lane
     // sign(v2c) of the two lanes -> bit (e & 15) of the sign word
-    const uint32_t sb = (vv >> (15 - (e & 15))) & (0x00010001u << (e & 15));
+    const uint32_t sh = ((e & 15) == 15) ? vv : imul_hi(vv, 1u << (17 + (e & 15)));
     if (e < 16) {
-      sg1 |= sb;
+      sg1 |= sh & (0x00010001u << (e & 15));
     } else {
-      sg2 |= sb;
+      sg2 |= sh & (0x00010001u << (e & 15));
     }
-    *reinterpret_cast<uint16_t*>(soft + addr[e]) = (uint16_t)prmt(o, o, sel[e] >> 16); // byte j <- lane (j - rho) mod 2
+    sts_u8(a0[e], o);
+    sts_u8(a0[e] ^ 1u, imul_hi(o, 65536u));
   }
 
   // ---- new state: c2v sign = sign product ^ sign(v2c) ----------------------------------------------------------------------
@@ -396,41 +426,18 @@ __device__ __forceinline__ int fec_dematch_byte(const fec_dematch_geom& G, const
   return (o >= G.zero_from) ? 0 : acc;
 }
 
-__device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
-                                                   const int8_t* __restrict__ in,
-                                                   int8_t* __restrict__ harq,
-                                                   uint8_t*  soft, // interleaved decoder layout, nullptr = do not fill
-                                                   uint32_t  H,
-                                                   int8_t*   stage,
-                                                   uint32_t  stage_cap,
-                                                   uint32_t* n_sig_smem)
+// The per-group loop of fec_dematch_packed. `src` is either the shared-memory staging copy or the global input; keeping
+// the two as separate instantiations lets the compiler use LDS for the former.
+template <class SrcPtr>
+__device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G,
+                                                       SrcPtr                  src,
+                                                       int8_t* __restrict__    harq,
+                                                       uint8_t*                soft,
+                                                       uint32_t                H,
+                                                       uint32_t                invZ)
 {
-  const fec_dematch_geom G = fec_dematch_geometry(D);
-  const uint32_t         Z = G.Z, invZ = 0xffffffffu / Z + 1;
-
-  // Stage the input.
-  const int8_t* src = in;
-  if (G.E <= stage_cap) {
-    if ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) {
-      const uint4*   g4 = reinterpret_cast<const uint4*>(in);
-      uint4*         s4 = reinterpret_cast<uint4*>(stage);
-      const uint32_t n4 = G.E / 16;
-      for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x) {
-        s4[i] = __ldg(g4 + i);
-      }
-      for (uint32_t i = n4 * 16 + threadIdx.x; i < G.E; i += blockDim.x) {
-        stage[i] = in[i];
-      }
-    } else {
-      for (uint32_t i = threadIdx.x; i < G.E; i += blockDim.x) {
-        stage[i] = in[i];
-      }
-    }
-    __syncthreads();
-    src = stage;
-  }
-
   uint32_t       my_sig  = 0;
+  const uint32_t Z = G.Z;
   const uint32_t ngroups = G.N / 4; // Z is even and N = 66Z or 50Z, so N % 4 == 0
   uint32_t*      harq4   = reinterpret_cast<uint32_t*>(harq);
   const fec_soft_store_packed store{soft, Z, H, invZ};
@@ -470,14 +477,18 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
       if (uses_old && !G.hzero) {
         old = harq4[g];
       }
+      int        dv[4];
+      const bool ld = live && has_data;
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
-        int a = (is_filler && G.newd) ? 127 : (int)(int8_t)(old >> (8 * b));
-        if (live && has_data) {
-          const int dv = src[sidx0 + b * stride];
-          a            = copy ? dv : fec_sat_add(a, dv);
-        }
-        val[b] = zero_all ? 0 : a;
+        dv[b] = ld ? (int)src[sidx0 + b * stride] : 0;
+      }
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int base = (is_filler && G.newd) ? 127 : (int)(int8_t)(old >> (8 * b));
+        const int comb = fec_sat_add(base, dv[b]);
+        const int a    = ld ? (copy ? dv[b] : comb) : base;
+        val[b]         = zero_all ? 0 : a;
       }
     } else {
       uint32_t old = 0;
@@ -516,9 +527,63 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
       }
     }
   }
+  return my_sig;
+}
+
+__device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
+                                                   const int8_t* __restrict__ in,
+                                                   int8_t* __restrict__ harq,
+                                                   uint8_t*  soft, // interleaved decoder layout, nullptr = do not fill
+                                                   uint32_t  H,
+                                                   int8_t*   stage,
+                                                   uint32_t  stage_cap,
+                                                   uint32_t* n_sig_smem)
+{
+#ifdef FEC_PROFILE
+  const long long td0 = clock64();
+#endif
+  const fec_dematch_geom G = fec_dematch_geometry(D);
+  const uint32_t         Z = G.Z, invZ = 0xffffffffu / Z + 1;
+
+  // Stage the input.
+  const int8_t* src = in;
+  if (G.E <= stage_cap) {
+    if ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) {
+      const uint4*   g4 = reinterpret_cast<const uint4*>(in);
+      uint4*         s4 = reinterpret_cast<uint4*>(stage);
+      const uint32_t n4 = G.E / 16;
+      for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x) {
+        s4[i] = __ldg(g4 + i);
+      }
+      for (uint32_t i = n4 * 16 + threadIdx.x; i < G.E; i += blockDim.x) {
+        stage[i] = in[i];
+      }
+    } else {
+      for (uint32_t i = threadIdx.x; i < G.E; i += blockDim.x) {
+        stage[i] = in[i];
+      }
+    }
+    __syncthreads();
+    src = stage;
+  }
+
+#ifdef FEC_PROFILE
+  const long long td1 = clock64();
+#endif
+  uint32_t my_sig;
+  if (src == stage) {
+    my_sig = fec_dematch_groups<const int8_t*>(G, stage, harq, soft, H, invZ);
+  } else {
+    my_sig = fec_dematch_groups<const int8_t* __restrict__>(G, in, harq, soft, H, invZ);
+  }
   if (my_sig != 0) {
     atomicMax(n_sig_smem, my_sig);
   }
+#ifdef FEC_PROFILE
+  if (threadIdx.x == 0) {
+    n_sig_smem[1] = (uint32_t)((td1 - td0) >> 6) | ((uint32_t)((clock64() - td1) >> 6) << 16);
+  }
+#endif
 }
 
 __device__ __forceinline__ bool fec_packed_cb_supported(const fec_cb_desc& D)
@@ -529,7 +594,7 @@ __device__ __forceinline__ bool fec_packed_cb_supported(const fec_cb_desc& D)
          !(D.mode == FEC_MODE_DECODE && (D.E % D.lifting_size) != 0) && D.mode != FEC_MODE_DEMATCH;
 }
 
-__device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
+__device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
                                            uint32_t           cb,
                                            uint8_t*           smem_raw,
                                            const int8_t* __restrict__ llr_base,
@@ -539,7 +604,8 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
                                            const fec_dev_tables* __restrict__ tab,
                                            const fec_packed_tables* __restrict__ ptab)
 {
-  __shared__ uint32_t s_nsig;
+  __shared__ uint32_t s_nsig_arr[2];
+#define s_nsig s_nsig_arr[0]
 
   const uint32_t Z = D.lifting_size, H = Z / 2;
   const int      bg1 = (D.base_graph == 1);
@@ -650,7 +716,7 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
   const uint32_t nlayers = cbl / Z - Kb;
   const uint32_t T       = K - D.nof_filler_bits;
   const uint32_t smul = ptab->scale_mul, sadd = ptab->scale_add;
-  const uint32_t kneg = fec_reg_const(H2_NEG_ONE);
+  const uint32_t soft_s = (uint32_t)__cvta_generic_to_shared(soft);
 
 #ifdef FEC_PROFILE
   tp2 = clock64();
@@ -663,15 +729,15 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
         uint32_t*              st = state + (uint32_t)soff[l] * H + tid;
         const fec_packed_edge* ed = edges + rs[l];
         switch (deg[l]) {
-          case 3: fec_packed_row<3>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          case 4: fec_packed_row<4>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          case 5: fec_packed_row<5>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          case 6: fec_packed_row<6>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          case 7: fec_packed_row<7>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          case 8: fec_packed_row<8>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          case 9: fec_packed_row<9>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          case 10: fec_packed_row<10>(soft, st, ed, H, tid, smul, sadd, kneg); break;
-          default: fec_packed_row<19>(soft, st, ed, H, tid, smul, sadd, kneg); break;
+          case 3: fec_packed_row<3>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 4: fec_packed_row<4>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 5: fec_packed_row<5>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 6: fec_packed_row<6>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 7: fec_packed_row<7>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 8: fec_packed_row<8>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 9: fec_packed_row<9>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 10: fec_packed_row<10>(soft_s, st, ed, H, tid, smul, sadd); break;
+          default: fec_packed_row<19>(soft_s, st, ed, H, tid, smul, sadd); break;
         }
       }
       __syncthreads();
@@ -703,13 +769,15 @@ __device__ __noinline__ void fec_packed_cb(const fec_cb_desc& D,
 #ifdef FEC_PROFILE
     // phase clocks / 256: [7:0] setup, [15:8] dematch / 4, [23:16] decode / 16, [31:24] tail
     const long long tp4 = clock64();
-    res.reserved = (uint32_t)min(255ll, (tp1 - tp0) >> 8) | ((uint32_t)min(255ll, (tp2 - tp1) >> 10) << 8) |
+    res.reserved = s_nsig_arr[1];
+    if (false) res.reserved = (uint32_t)min(255ll, (tp1 - tp0) >> 8) | ((uint32_t)min(255ll, (tp2 - tp1) >> 10) << 8) |
                    ((uint32_t)min(255ll, (tp3 - tp2) >> 12) << 16) | ((uint32_t)min(255ll, (tp4 - tp3) >> 8) << 24);
 #endif
     results[cb]            = res;
   }
 }
 
+#undef s_nsig
 // Dispatcher: every codeblock the packed path covers goes there, the rest (odd Z, dematch-only
 // operations, unaligned decoder inputs) runs the generic per-check code in the same launch.
 __global__ void __launch_bounds__(FEC_PACKED_MAX_THREADS, 2)
@@ -772,12 +840,10 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
         const uint32_t   s = t.shift[bg * 51 + zi][i], col = t.col[bg][i];
         const uint32_t   q = s / H, r = s % H;
         fec_packed_edge& e = pt.edges[bg * 51 + zi][i];
-        // selector words: low half unpacks (lane k <- byte (k + rho) mod 2, zero-extended), high half packs back
-        const uint32_t sel_even = 0x00204140u, sel_odd = 0x00024041u;
-        e.a                     = (col * H + r) * 2;
-        e.thr                   = H - r;
-        e.selN                  = (q & 1) ? sel_odd : sel_even;
-        e.selW                  = (q & 1) ? sel_even : sel_odd;
+        e.aN  = (col * H + r) * 2 + (q & 1);
+        e.aW  = (col * H + r - H) * 2 + ((q + 1) & 1); // only used by threads t >= H - r, so t + r - H >= 0
+        e.thr = H - r;
+        e.pad = 0;
       }
     }
   }
