@@ -141,12 +141,16 @@ struct fec_engine {
   int8_t*               d_harq       = nullptr;
   std::atomic<uint64_t> launches{0};
   std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
+  cudaStream_t          pipe[3]      = {nullptr, nullptr, nullptr}; // fec_run_host chunk pipeline (copy/compute overlap)
+  cudaEvent_t           pipe_done[3] = {nullptr, nullptr, nullptr};
   std::mutex            run_mtx; // serialises fec_run_host users of the shared staging below
   // staging for fec_run_host
   fec_cb_desc*   d_descs = nullptr;
   int8_t*        d_llr   = nullptr;
   uint8_t*       d_out   = nullptr;
   fec_cb_result* d_res   = nullptr;
+  fec_cb_result* h_res_pin   = nullptr; // pinned bounce buffers: async copies from/to pageable memory would block
+  fec_cb_desc*   h_descs_pin = nullptr; // the host and serialise the chunk pipeline
   std::vector<queue_t>* queues = nullptr;
   std::mutex            queues_mtx;
 };
@@ -345,6 +349,10 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   CU_TRY(cudaGetDeviceProperties(&prop, cfg->device));
   e->sm_count = prop.multiProcessorCount;
   CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 3; ++i) {
+    CU_TRY(cudaStreamCreateWithFlags(&e->pipe[i], cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreateWithFlags(&e->pipe_done[i], cudaEventDisableTiming));
+  }
   fec_dev_tables* h = new (std::nothrow) fec_dev_tables();
   build_tables(*h, cfg->scaling_factor);
   CU_TRY(cudaMalloc((void**)&e->d_tab, sizeof(fec_dev_tables)));
@@ -372,6 +380,8 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   CU_TRY(cudaMalloc((void**)&e->d_llr, e->cfg.max_batch_llrs));
   CU_TRY(cudaMalloc((void**)&e->d_out, (size_t)e->cfg.max_batch_cbs * FEC_MAX_CB_OUT_BYTES));
   CU_TRY(cudaMalloc((void**)&e->d_res, e->cfg.max_batch_cbs * sizeof(fec_cb_result)));
+  CU_TRY(cudaHostAlloc((void**)&e->h_res_pin, e->cfg.max_batch_cbs * sizeof(fec_cb_result), cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&e->h_descs_pin, e->cfg.max_batch_cbs * sizeof(fec_cb_desc), cudaHostAllocDefault));
   e->queues = new std::vector<queue_t>(cfg->nof_queues);
   *out      = e;
   return FEC_OK;
@@ -400,11 +410,21 @@ void fec_engine_destroy(fec_engine* e)
   cudaFree(e->d_out);
   cudaFree(e->d_res);
   cudaFree(e->d_harq);
+  cudaFreeHost(e->h_res_pin);
+  cudaFreeHost(e->h_descs_pin);
   delete[] e->fresh;
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
   if (e->stream) {
     cudaStreamDestroy(e->stream);
+  }
+  for (int i = 0; i < 3; ++i) {
+    if (e->pipe[i]) {
+      cudaStreamDestroy(e->pipe[i]);
+    }
+    if (e->pipe_done[i]) {
+      cudaEventDestroy(e->pipe_done[i]);
+    }
   }
   delete e;
 }
@@ -473,20 +493,77 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   }
   std::lock_guard<std::mutex> lk(e->run_mtx);
   CU_TRY(cudaSetDevice(e->cfg.device));
-  CU_TRY(cudaMemcpyAsync(e->d_descs, h_descs, n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr, llr_bytes, cudaMemcpyHostToDevice, e->stream));
-  if (out_bytes) {
-    // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
-    CU_TRY(cudaMemcpyAsync(e->d_out, h_out, out_bytes, cudaMemcpyHostToDevice, e->stream));
+  // Large batches are cut into chunks of whole kernel waves that travel on three streams, so that the H2D copy of one
+  // chunk overlaps the kernels of the previous one and the D2H copy of the one before (PCIe is full duplex).
+  const uint32_t wave  = 2u * (uint32_t)e->sm_count;
+  uint32_t       chunk = (n >= 6 * wave) ? 3 * wave : n;
+  if (chunk != n) {
+    // Chunks may only run concurrently if their slices of the batch buffers do not interleave.
+    size_t prev_l1 = 0, prev_o1 = 0;
+    for (uint32_t c0 = 0; c0 < n && chunk != n; c0 += chunk) {
+      const uint32_t cn = (n - c0 < chunk) ? (n - c0) : chunk;
+      size_t         l0 = ~(size_t)0, l1 = 0, o0 = ~(size_t)0, o1 = 0;
+      for (uint32_t i = c0; i < c0 + cn; ++i) {
+        const fec_cb_desc& d = h_descs[i];
+        l0                   = d.llr_offset < l0 ? (size_t)d.llr_offset : l0;
+        l1                   = d.llr_offset + d.E > l1 ? (size_t)(d.llr_offset + d.E) : l1;
+        const uint32_t     kb = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
+        o0                   = d.out_offset < o0 ? (size_t)d.out_offset : o0;
+        o1                   = (size_t)d.out_offset + kb > o1 ? (size_t)d.out_offset + kb : o1;
+      }
+      if (l0 < prev_l1 || o0 < prev_o1) {
+        chunk = n;
+      }
+      prev_l1 = l1;
+      prev_o1 = o1;
+    }
   }
-  int r = launch(e, e->stream, e->d_descs, n, e->d_llr, e->d_out, e->d_res, max_Z, any1);
-  if (r != FEC_OK) {
-    return r;
+  memcpy(e->h_descs_pin, h_descs, n * sizeof(fec_cb_desc));
+  CU_TRY(cudaMemcpyAsync(e->d_descs, e->h_descs_pin, n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaEventRecord(e->pipe_done[0], e->stream));
+  for (int k = 0; k < 3; ++k) {
+    CU_TRY(cudaStreamWaitEvent(e->pipe[k], e->pipe_done[0], 0));
   }
-  if (out_bytes) {
-    CU_TRY(cudaMemcpyAsync(h_out, e->d_out, out_bytes, cudaMemcpyDeviceToHost, e->stream));
+  uint32_t nchunks = 0;
+  for (uint32_t c0 = 0; c0 < n; c0 += chunk, ++nchunks) {
+    const uint32_t cn = (n - c0 < chunk) ? (n - c0) : chunk;
+    cudaStream_t   st = (chunk == n) ? e->stream : e->pipe[nchunks % 3];
+    // byte ranges of the batch buffers this chunk touches
+    size_t   l0 = ~(size_t)0, l1 = 0, o0 = ~(size_t)0, o1 = 0;
+    uint32_t cz = 0;
+    int      c1 = 0;
+    for (uint32_t i = c0; i < c0 + cn; ++i) {
+      const fec_cb_desc& d  = h_descs[i];
+      const uint32_t     kb = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
+      l0                    = d.llr_offset < l0 ? (size_t)d.llr_offset : l0;
+      l1                    = d.llr_offset + d.E > l1 ? (size_t)(d.llr_offset + d.E) : l1;
+      if (d.mode != FEC_MODE_DEMATCH) {
+        o0 = d.out_offset < o0 ? (size_t)d.out_offset : o0;
+        o1 = (size_t)d.out_offset + kb > o1 ? (size_t)d.out_offset + kb : o1;
+      }
+      cz = d.lifting_size > cz ? d.lifting_size : cz;
+      c1 |= (d.base_graph == 1);
+    }
+    CU_TRY(cudaMemcpyAsync(e->d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+    if (out_bytes && o1 > o0) {
+      // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
+      CU_TRY(cudaMemcpyAsync(e->d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, st));
+    }
+    int r = launch(e, st, e->d_descs + c0, cn, e->d_llr, e->d_out, e->d_res + c0, cz, c1);
+    if (r != FEC_OK) {
+      return r;
+    }
+    if (out_bytes && o1 > o0) {
+      CU_TRY(cudaMemcpyAsync(h_out + o0, e->d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, st));
+    }
+    CU_TRY(cudaMemcpyAsync(e->h_res_pin + c0, e->d_res + c0, cn * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st));
   }
-  CU_TRY(cudaMemcpyAsync(h_results, e->d_res, n * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, e->stream));
+  if (chunk != n) {
+    for (int k = 0; k < 3; ++k) {
+      CU_TRY(cudaEventRecord(e->pipe_done[k], e->pipe[k]));
+      CU_TRY(cudaStreamWaitEvent(e->stream, e->pipe_done[k], 0));
+    }
+  }
   if (h_soft_out) {
     for (uint32_t i = 0; i < n; ++i) {
       if (h_descs[i].mode != FEC_MODE_DECODE) {
@@ -497,6 +574,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     }
   }
   CU_TRY(cudaStreamSynchronize(e->stream));
+  memcpy(h_results, e->h_res_pin, n * sizeof(fec_cb_result));
   return FEC_OK;
 }
 
@@ -773,11 +851,24 @@ int fec_queue_fetch(fec_engine* e, uint32_t queue_id, uint64_t tag, uint8_t* dst
   }
   queue_t&                    q = (*e->queues)[queue_id];
   std::lock_guard<std::mutex> lk(q.mtx);
-  for (auto& s : q.slots) {
-    if (s.state != batch_slot::DONE) {
-      continue;
+  // Newest batch first: tags are caller-chosen (the HAL uses the codeblock index) and repeat from one transport block to
+  // the next, while an older, fully polled batch may still sit in its slot.
+  bool seen[SLOTS_PER_QUEUE] = {};
+  for (int pass = 0; pass < SLOTS_PER_QUEUE; ++pass) {
+    int      pick = -1;
+    uint64_t best = 0;
+    for (int i = 0; i < SLOTS_PER_QUEUE; ++i) {
+      if (!seen[i] && q.slots[i].state == batch_slot::DONE && q.slots[i].seq >= best) {
+        best = q.slots[i].seq;
+        pick = i;
+      }
     }
-    for (uint32_t i = 0; i < s.polled; ++i) {
+    if (pick < 0) {
+      break;
+    }
+    seen[pick]    = true;
+    batch_slot& s = q.slots[pick];
+    for (uint32_t i = s.polled; i-- > 0;) {
       if (s.tags[i] == tag) {
         const fec_cb_desc& d = s.h_descs[i];
         if ((s.h_res[i].status & FEC_RES_TOO_SHORT) && (d.flags & FEC_FLAG_EARLY_STOP)) {

@@ -395,3 +395,34 @@ class HwAcceleratorPuschDec:
 
     def is_harq_external(self):
         return True
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Multi-GPU sharding (one process and one engine per GPU). Codeblocks are independent: there is no data-path collective.
+# The only constraint is HARQ affinity -- every (re)transmission of a codeblock must reach the GPU that holds its soft
+# buffer -- so work is routed by cell (BASELINE config 5) or by absolute codeblock id range, never round-robin.
+# ------------------------------------------------------------------------------------------------------------------
+def cells_of_rank(n_cells, world_size, rank):
+    """Cells served by `rank`: cell_id mod world_size == rank."""
+    return [c for c in range(n_cells) if c % world_size == rank]
+
+
+def harq_owner(absolute_cb_id, slots_per_gpu, world_size):
+    """(rank, local slot) owning a soft buffer: each GPU owns a contiguous slice of the rx-buffer codeblock pool
+    (lib/phy/upper/rx_buffer_impl.h:170-177 hands out absolute ids from one global pool)."""
+    rank = absolute_cb_id // slots_per_gpu
+    if rank >= world_size:
+        raise FecError("absolute_cb_id %d outside the %d x %d soft-buffer slots" % (absolute_cb_id, world_size,
+                                                                                    slots_per_gpu))
+    return rank, absolute_cb_id - rank * slots_per_gpu
+
+
+def shard_transport_blocks(tbs, world_size, rank):
+    """tbs: iterable of dicts with 'cell' and 'cb_ids' (absolute ids). Returns the TBs this rank decodes, with cb ids
+    rewritten to local HARQ slots; asserts that a TB never straddles two GPUs."""
+    mine = []
+    for tb in tbs:
+        if tb["cell"] % world_size != rank:
+            continue
+        mine.append(dict(tb))
+    return mine

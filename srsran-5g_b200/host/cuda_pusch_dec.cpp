@@ -1,0 +1,225 @@
+// srsran-5g_b200/host/cuda_pusch_dec.cpp -- see cuda_pusch_dec.h. Host-only C++17; all device work is behind the C ABI.
+#include "cuda_pusch_dec.h"
+#include "srsran/support/error_handling.h"
+#include <cstring>
+#include <vector>
+
+using namespace srsran;
+using namespace srsran::b200;
+
+namespace {
+
+uint8_t to_fec_crc(hal::hw_dec_cb_crc_type t)
+{
+  // Same numbering on both sides (hw_accelerator_pusch_dec.h:36 / fec_b200.h).
+  return static_cast<uint8_t>(t);
+}
+
+uint8_t to_fec_crc(crc_generator_poly poly)
+{
+  switch (poly) {
+    case crc_generator_poly::CRC24A:
+      return FEC_CRC24A;
+    case crc_generator_poly::CRC24B:
+      return FEC_CRC24B;
+    case crc_generator_poly::CRC16:
+      return FEC_CRC16;
+    default:
+      report_fatal_error("The CUDA LDPC decoder checks CRC16, CRC24A or CRC24B only.");
+  }
+}
+
+} // namespace
+
+fec_engine_handle::fec_engine_handle(const fec_engine_cfg& cfg)
+{
+  // No CPU fallback: a missing device is fatal at start-up, exactly where the bbdev factory would fail.
+  report_fatal_error_if_not(fec_engine_create(&cfg, &engine) == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+}
+
+fec_engine_handle::~fec_engine_handle()
+{
+  fec_engine_destroy(engine);
+}
+
+cuda_pusch_dec_accelerator::cuda_pusch_dec_accelerator(std::shared_ptr<fec_engine_handle> engine_) :
+  engine(std::move(engine_))
+{
+}
+
+cuda_pusch_dec_accelerator::~cuda_pusch_dec_accelerator()
+{
+  if (has_queue) {
+    fec_queue_free(engine->get(), queue);
+  }
+}
+
+void cuda_pusch_dec_accelerator::reserve_queue()
+{
+  if (!has_queue) {
+    report_fatal_error_if_not(fec_queue_reserve(engine->get(), &queue) == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+    has_queue = true;
+  }
+}
+
+void cuda_pusch_dec_accelerator::free_queue()
+{
+  // The reference calls this once per transport block (pusch_decoder_hw_impl.cpp:439); the engine queue itself is kept
+  // for the lifetime of the instance so that its pinned staging is not re-created every slot.
+  for (operation& op : ops) {
+    op.enqueued = false;
+    op.done     = false;
+  }
+  dirty = false;
+}
+
+void cuda_pusch_dec_accelerator::configure_operation(const hal::hw_pusch_decoder_configuration& config, unsigned cb_index)
+{
+  srsran_assert(cb_index < MAX_NOF_SEGMENTS, "Codeblock index {} out of range.", cb_index);
+  ops[cb_index].cfg      = config;
+  ops[cb_index].enqueued = false;
+  ops[cb_index].done     = false;
+}
+
+bool cuda_pusch_dec_accelerator::enqueue_operation(span<const int8_t> data, span<const int8_t> /*aux_data*/, unsigned cb_index)
+{
+  srsran_assert(has_queue, "enqueue_operation() before reserve_queue().");
+  const hal::hw_pusch_decoder_configuration& c = ops[cb_index].cfg;
+  srsran_assert(data.size() == c.cw_length, "Codeblock {}: {} soft bits given, cw_length is {}.", cb_index, data.size(),
+                c.cw_length);
+  fec_cb_desc d     = {};
+  d.harq_slot       = c.absolute_cb_id;
+  d.E               = c.cw_length;
+  d.Nref            = c.Nref;
+  d.nof_filler_bits = c.nof_filler_bits;
+  d.lifting_size    = static_cast<uint16_t>(c.lifting_size);
+  d.base_graph      = static_cast<uint8_t>(c.base_graph_index);
+  d.rv              = static_cast<uint8_t>(c.rv);
+  d.qm              = static_cast<uint8_t>(get_bits_per_symbol(c.modulation));
+  d.crc_type        = to_fec_crc(c.cb_crc_type);
+  d.max_iter        = static_cast<uint8_t>(c.max_nof_ldpc_iterations);
+  d.mode            = FEC_MODE_CHAIN;
+  d.flags           = (c.new_data ? FEC_FLAG_NEW_DATA : 0u) | (c.use_early_stop ? FEC_FLAG_EARLY_STOP : 0u);
+  const int rc      = fec_queue_enqueue(engine->get(), queue, &d, data.data(), cb_index);
+  if (rc == FEC_ERR_QUEUE_FULL) {
+    return false; // the consumer stops enqueuing and drains (pusch_decoder_hw_impl.cpp:253-257)
+  }
+  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+  ops[cb_index].enqueued = true;
+  dirty                  = true;
+  return true;
+}
+
+void cuda_pusch_dec_accelerator::poll()
+{
+  std::array<uint64_t, 64>      tags;
+  std::array<fec_cb_result, 64> results;
+  for (;;) {
+    const int n = fec_queue_poll(engine->get(), queue, tags.data(), results.data(), tags.size());
+    for (int i = 0; i < n; ++i) {
+      operation& op = ops[tags[i]];
+      op.result     = results[i];
+      op.done       = true;
+    }
+    if (n < static_cast<int>(tags.size())) {
+      break;
+    }
+  }
+}
+
+bool cuda_pusch_dec_accelerator::dequeue_operation(span<uint8_t> data, span<int8_t> /*aux_data*/, unsigned segment_index)
+{
+  operation& op = ops[segment_index];
+  if (!op.enqueued) {
+    return false;
+  }
+  if (!op.done) {
+    if (dirty) {
+      // First dequeue after a run of enqueues: launch whatever is still staged (the consumer enqueues every codeblock
+      // of the transport block before it starts polling because HARQ is external).
+      fec_queue_flush(engine->get(), queue);
+      dirty = false;
+    }
+    poll();
+    if (!op.done) {
+      return false;
+    }
+  }
+  fec_queue_fetch(engine->get(), queue, segment_index, data.data(), static_cast<uint32_t>(data.size()));
+  return true;
+}
+
+void cuda_pusch_dec_accelerator::read_operation_outputs(hal::hw_pusch_decoder_outputs& out,
+                                                        unsigned                       cb_index,
+                                                        unsigned /*absolute_cb_id*/)
+{
+  const operation& op     = ops[cb_index];
+  out.CRC_pass            = (op.result.status & FEC_RES_CRC_PASS) != 0;
+  out.nof_ldpc_iterations = op.result.nof_ldpc_iterations;
+}
+
+void cuda_pusch_dec_accelerator::free_harq_context_entry(unsigned absolute_cb_id)
+{
+  fec_harq_free(engine->get(), absolute_cb_id);
+}
+
+std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> srsran::b200::create_cuda_pusch_dec_acc_factory(const fec_engine_cfg& cfg)
+{
+  return std::make_shared<cuda_pusch_dec_factory>(cfg);
+}
+
+std::optional<unsigned> ldpc_decoder_cuda::decode(bit_buffer&                      output,
+                                                  span<const log_likelihood_ratio> input,
+                                                  crc_calculator*                  crc,
+                                                  const configuration&             cfg)
+{
+  const codeblock_metadata& m = cfg.block_conf;
+  fec_cb_desc               d = {};
+  d.E                         = static_cast<uint32_t>(input.size());
+  d.nof_filler_bits           = m.cb_specific.nof_filler_bits;
+  d.lifting_size              = static_cast<uint16_t>(m.tb_common.lifting_size);
+  d.base_graph                = static_cast<uint8_t>(m.tb_common.base_graph);
+  d.max_iter                  = static_cast<uint8_t>(cfg.algorithm_conf.max_iterations);
+  d.mode                      = FEC_MODE_DECODE;
+  d.crc_type                  = (crc != nullptr) ? to_fec_crc(crc->get_generator_poly()) : static_cast<uint8_t>(FEC_CRC16);
+  d.flags                     = (crc != nullptr) ? FEC_FLAG_EARLY_STOP : FEC_FLAG_NO_CRC;
+  fec_cb_result        res    = {};
+  span<uint8_t>        bytes  = output.get_buffer();
+  static_assert(sizeof(log_likelihood_ratio) == 1, "LLRs are int8 on both sides of the boundary.");
+  const int rc = fec_run_host(engine->get(), &d, 1, reinterpret_cast<const int8_t*>(input.data()), input.size(),
+                              bytes.data(), bytes.size(), &res, nullptr);
+  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+  if ((crc != nullptr) && (res.status & FEC_RES_CRC_PASS)) {
+    return res.nof_ldpc_iterations;
+  }
+  return std::nullopt;
+}
+
+void ldpc_rate_dematcher_cuda::rate_dematch(span<log_likelihood_ratio>       output,
+                                            span<const log_likelihood_ratio> input,
+                                            bool                             new_data,
+                                            const codeblock_metadata&        cfg)
+{
+  fec_cb_desc d     = {};
+  d.harq_slot       = scratch_slot;
+  d.E               = static_cast<uint32_t>(input.size());
+  d.Nref            = cfg.tb_common.Nref;
+  d.nof_filler_bits = cfg.cb_specific.nof_filler_bits;
+  d.lifting_size    = static_cast<uint16_t>(cfg.tb_common.lifting_size);
+  d.base_graph      = static_cast<uint8_t>(cfg.tb_common.base_graph);
+  d.rv              = static_cast<uint8_t>(cfg.tb_common.rv);
+  d.qm              = static_cast<uint8_t>(get_bits_per_symbol(cfg.tb_common.mod));
+  d.crc_type        = FEC_CRC24B;
+  d.max_iter        = 1;
+  d.mode            = FEC_MODE_DEMATCH;
+  d.flags           = new_data ? FEC_FLAG_NEW_DATA : 0u;
+  fec_cb_result res = {};
+  int8_t*       out = reinterpret_cast<int8_t*>(output.data());
+  int           rc  = fec_harq_write(engine->get(), scratch_slot, out, static_cast<uint32_t>(output.size()));
+  rc                = (rc == FEC_OK)
+                          ? fec_run_host(engine->get(), &d, 1, reinterpret_cast<const int8_t*>(input.data()), input.size(), nullptr, 0,
+                                         &res, nullptr)
+                          : rc;
+  rc                = (rc == FEC_OK) ? fec_harq_read(engine->get(), scratch_slot, out, static_cast<uint32_t>(output.size())) : rc;
+  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+}

@@ -1,0 +1,135 @@
+// srsran-5g_b200/host/cuda_pusch_dec.h -- reference-side binding of the B200 FEC engine.
+//
+// These classes derive from the reference's own interfaces (headers of the reference tree, found through the include
+// path given at build time; nothing of the reference is copied here) and forward to the C ABI in include/fec_b200.h:
+//
+//   cuda_pusch_dec_accelerator : hal::hw_accelerator_pusch_dec
+//        include/srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec.h:83-115 -- the object
+//        pusch_decoder_hw_impl drives (lib/phy/upper/channel_processors/pusch/pusch_decoder_hw_impl.cpp:149-358)
+//   cuda_pusch_dec_factory     : hal::hw_accelerator_pusch_dec_factory
+//        include/srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec_factory.h:31-36 -- what
+//        pusch_decoder_factory_hw_configuration::hw_decoder_factory expects (.../pusch/factories.h:74-83)
+//   ldpc_decoder_cuda          : ldpc_decoder        include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:37-75
+//   ldpc_rate_dematcher_cuda   : ldpc_rate_dematcher include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:35-58
+//
+// One fec_engine (one GPU) is shared by every accelerator instance the factory creates; each instance owns one engine
+// queue, is driven by one thread (the reference pins instances to threads), and never blocks: enqueue returns false when
+// the staging ring is full, dequeue returns false until the operation has completed.
+#pragma once
+
+#include "fec_b200.h"
+#include "srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec.h"
+#include "srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec_factory.h"
+#include "srsran/phy/upper/channel_coding/crc_calculator.h"
+#include "srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h"
+#include "srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h"
+#include "srsran/ran/sch/sch_constants.h"
+#include <array>
+#include <memory>
+
+namespace srsran {
+namespace b200 {
+
+/// Owns one engine (one GPU); shared by the accelerator instances and adapters created from it.
+class fec_engine_handle
+{
+public:
+  explicit fec_engine_handle(const fec_engine_cfg& cfg);
+  ~fec_engine_handle();
+  fec_engine_handle(const fec_engine_handle&)            = delete;
+  fec_engine_handle& operator=(const fec_engine_handle&) = delete;
+  fec_engine*        get() const { return engine; }
+
+private:
+  fec_engine* engine = nullptr;
+};
+
+/// hal::hw_accelerator_pusch_dec over the queue entry points of the C ABI. HARQ soft buffers are external (in HBM).
+class cuda_pusch_dec_accelerator : public hal::hw_accelerator_pusch_dec
+{
+public:
+  explicit cuda_pusch_dec_accelerator(std::shared_ptr<fec_engine_handle> engine_);
+  ~cuda_pusch_dec_accelerator() override;
+
+  // See hal::hw_accelerator for the documentation.
+  bool enqueue_operation(span<const int8_t> data, span<const int8_t> aux_data = {}, unsigned cb_index = 0) override;
+  bool dequeue_operation(span<uint8_t> data, span<int8_t> aux_data = {}, unsigned segment_index = 0) override;
+  // See hal::hw_accelerator_pusch_dec for the documentation.
+  void reserve_queue() override;
+  void free_queue() override;
+  void configure_operation(const hal::hw_pusch_decoder_configuration& config, unsigned cb_index = 0) override;
+  void read_operation_outputs(hal::hw_pusch_decoder_outputs& out,
+                              unsigned                       cb_index       = 0,
+                              unsigned                       absolute_cb_id = 0) override;
+  void free_harq_context_entry(unsigned absolute_cb_id) override;
+  bool is_harq_external() const override { return true; }
+
+private:
+  struct operation {
+    hal::hw_pusch_decoder_configuration cfg      = {};
+    fec_cb_result                       result   = {};
+    bool                                enqueued = false;
+    bool                                done     = false;
+  };
+
+  void poll();
+
+  std::shared_ptr<fec_engine_handle>       engine;
+  uint32_t                                 queue     = 0;
+  bool                                     has_queue = false;
+  bool                                     dirty     = false; // operations enqueued since the last flush
+  std::array<operation, MAX_NOF_SEGMENTS>  ops;
+};
+
+/// Factory handed to pusch_decoder_factory_hw_configuration::hw_decoder_factory.
+class cuda_pusch_dec_factory : public hal::hw_accelerator_pusch_dec_factory
+{
+public:
+  explicit cuda_pusch_dec_factory(const fec_engine_cfg& cfg) : engine(std::make_shared<fec_engine_handle>(cfg)) {}
+  std::unique_ptr<hal::hw_accelerator_pusch_dec> create() override
+  {
+    return std::make_unique<cuda_pusch_dec_accelerator>(engine);
+  }
+
+private:
+  std::shared_ptr<fec_engine_handle> engine;
+};
+
+/// The call that replaces create_bbdev_pusch_dec_acc_factory (lib/hal/phy/upper/channel_processors/pusch/
+/// hw_accelerator_factories.cpp:28-36, a stub returning nullptr in the open-source tree).
+std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> create_cuda_pusch_dec_acc_factory(const fec_engine_cfg& cfg);
+
+/// ldpc_decoder over FEC_MODE_DECODE (synchronous, one codeblock). The crc pointer only selects the polynomial.
+class ldpc_decoder_cuda : public ldpc_decoder
+{
+public:
+  explicit ldpc_decoder_cuda(std::shared_ptr<fec_engine_handle> engine_) : engine(std::move(engine_)) {}
+  std::optional<unsigned> decode(bit_buffer&                      output,
+                                 span<const log_likelihood_ratio> input,
+                                 crc_calculator*                  crc,
+                                 const configuration&             cfg) override;
+
+private:
+  std::shared_ptr<fec_engine_handle> engine;
+};
+
+/// ldpc_rate_dematcher over FEC_MODE_DEMATCH (synchronous, one codeblock, through a scratch HARQ slot).
+class ldpc_rate_dematcher_cuda : public ldpc_rate_dematcher
+{
+public:
+  ldpc_rate_dematcher_cuda(std::shared_ptr<fec_engine_handle> engine_, uint32_t scratch_slot_) :
+    engine(std::move(engine_)), scratch_slot(scratch_slot_)
+  {
+  }
+  void rate_dematch(span<log_likelihood_ratio>       output,
+                    span<const log_likelihood_ratio> input,
+                    bool                             new_data,
+                    const codeblock_metadata&        cfg) override;
+
+private:
+  std::shared_ptr<fec_engine_handle> engine;
+  uint32_t                           scratch_slot;
+};
+
+} // namespace b200
+} // namespace srsran
