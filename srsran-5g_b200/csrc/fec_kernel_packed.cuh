@@ -441,9 +441,58 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
   const uint32_t ngroups = G.N / 4; // Z is even and N = 66Z or 50Z, so N % 4 == 0
   uint32_t*      harq4   = reinterpret_cast<uint32_t*>(harq);
   const fec_soft_store_packed store{soft, Z, H, invZ};
+  // Data runs of a non-wrapping transmission: rate-matched position p = o - off lands at buffer position o for
+  // o in [lo, hi), once before the filler gap and once after it. Groups entirely inside a run take the lean path below.
+  uint32_t r1_lo = 1, r1_hi = 0, r1_off = 0, r2_lo = 1, r2_hi = 0, r2_off = 0;
+  if (!G.wrapped) {
+    if (G.k0c < G.info) {
+      r1_lo  = G.k0c;
+      r1_hi  = min(G.k0c + G.E, G.info);
+      r1_off = G.k0c;
+    }
+    if (G.k0c + G.E > G.info) {
+      r2_lo  = max(G.k0c, G.info) + G.fillers;
+      r2_hi  = G.k0c + G.E + G.fillers;
+      r2_off = G.k0c + G.fillers;
+    }
+  }
   for (uint32_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
     const uint32_t o0 = g * 4;
     int            val[4];
+    const bool     in1 = (o0 >= r1_lo) && (o0 + 4 <= r1_hi);
+    const bool     in2 = (o0 >= r2_lo) && (o0 + 4 <= r2_hi);
+    bool           hot = in1 || in2;
+    uint32_t       hs0 = 0, hst = 1;
+    if (hot) {
+      const uint32_t p0 = o0 - (in1 ? r1_off : r2_off);
+      hs0               = p0;
+      if (G.qm > 1) {
+        const uint32_t j = (G.Kp == 1) ? p0 : __umulhi(p0, G.invKp);
+        const uint32_t i = p0 - j * G.Kp;
+        hot              = (i + 3 < G.Kp); // all four in the same interleaver row
+        hs0              = i * G.qm + j;
+        hst              = G.qm;
+      }
+    }
+    if (hot) {
+      int dv[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        dv[b] = src[hs0 + b * hst];
+      }
+      if (G.newd) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          val[b] = dv[b];
+        }
+      } else {
+        const uint32_t old = G.hzero ? 0u : harq4[g];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          val[b] = fec_sat_add((int)(int8_t)(old >> (8 * b)), dv[b]);
+        }
+      }
+    } else {
     // A group is simple when no region boundary falls strictly inside it.
     auto inside = [o0](uint32_t b) { return (b > o0) && (b < o0 + 4); };
     bool simple = !G.wrapped && !inside(G.zero_lo) && !inside(G.info) && !inside(G.sys) && !inside(G.Ncb) &&
@@ -500,6 +549,7 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
         val[b] = fec_dematch_byte(G, src, o0 + b, (int)(int8_t)(old >> (8 * b)));
       }
     }
+    } // general path
     harq4[g] = (uint32_t)(uint8_t)val[0] | ((uint32_t)(uint8_t)val[1] << 8) | ((uint32_t)(uint8_t)val[2] << 16) |
                ((uint32_t)(uint8_t)val[3] << 24);
 #pragma unroll
