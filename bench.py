@@ -185,6 +185,76 @@ def workload_config(n_cbs):
                          % ((n_cbs or 0) * E // 1000000)}
 
 
+def bench_transport_block(fec, eng, torch, dev, stream, args, rank):
+    n_cb, fill, qm, n_short = 152, 16, 8, 40
+    Es = np.array([8960] * n_short + [8992] * (n_cb - n_short), np.uint32)
+    info_bits = n_cb * (K - fill - 24) - 24  # TBS = payload of all CBs minus the TB CRC
+    n_tb = max(1, min(args.cbs // n_cb, 46))
+    rng = np.random.default_rng(77 + rank)
+    sigma2 = 0.5 * 10.0 ** (-args.tb_esn0 / 10.0)
+    offs = np.concatenate([[0], np.cumsum((Es + 15) // 16 * 16)]).astype(np.uint64)
+    tb_bytes = int(offs[-1])
+    llr = np.zeros((n_tb, tb_bytes), np.int8)
+    for t in range(n_tb):
+        y = 1.0 + np.sqrt(sigma2) * rng.standard_normal(tb_bytes, dtype=np.float32)
+        llr[t] = np.round(np.clip(2.0 * y / sigma2, -20.0, 20.0) * 6.0).astype(np.int8)
+    d = fec.make_descs(n_tb * n_cb)
+    d["base_graph"], d["lifting_size"], d["qm"], d["rv"] = BG, Z, qm, 0
+    d["E"] = np.tile(Es, n_tb)
+    d["nof_filler_bits"], d["crc_type"], d["max_iter"], d["mode"] = fill, fec.CRC24B, MAX_ITER, fec.MODE_CHAIN
+    d["flags"] = fec.FLAG_NEW_DATA | fec.FLAG_EARLY_STOP
+    d["harq_slot"] = np.arange(n_tb * n_cb)
+    d["llr_offset"] = (np.arange(n_tb, dtype=np.uint64)[:, None] * np.uint64(tb_bytes) + offs[None, :n_cb]).ravel()
+    d["out_offset"] = np.arange(n_tb * n_cb) * (K // 8)
+    fec.desc_prepare(d)
+    t_llr = torch.from_numpy(llr).pin_memory()
+    t_out = torch.zeros(n_tb * n_cb * (K // 8), dtype=torch.uint8).pin_memory()
+    res = np.zeros(n_tb * n_cb, fec.RESULT_DTYPE)
+    # latency of ONE transport block, host buffers, synchronous call
+    one = d[:n_cb].copy()
+    lat = []
+    for i in range(220):
+        t = i % n_tb
+        one["llr_offset"] = d["llr_offset"][t * n_cb:(t + 1) * n_cb]
+        t0 = time.perf_counter()
+        eng.lib.fec_run_host(eng.h, one.ctypes.data, n_cb, t_llr.data_ptr(), n_tb * tb_bytes, t_out.data_ptr(),
+                             n_cb * (K // 8), res.ctypes.data, None)
+        lat.append((time.perf_counter() - t0) * 1e6)
+    lat = np.array(lat[20:])
+    r1 = res[:n_cb].copy()
+    # device-resident throughput of n_tb transport blocks per launch
+    d_llr = t_llr.to(dev)
+    d_descs = torch.from_numpy(d.view(np.uint8).copy()).to(dev)
+    d_out = torch.zeros(n_tb * n_cb * (K // 8), dtype=torch.uint8, device=dev)
+    d_res = torch.zeros(n_tb * n_cb * 8, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+
+    def step():
+        eng.launch_device(d_descs.data_ptr(), n_tb * n_cb, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True)
+
+    for _ in range(3):
+        step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(10):
+            step()
+        e1.record(stream)
+    stream.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    rr = np.frombuffer(d_res.cpu().numpy().tobytes(), fec.RESULT_DTYPE)
+    return {"workload": "273 PRB x 4 layers 256QAM R948: TBS %d bits, 152 CBs BG1 Z=384 E=8960/8992 Qm=8, early stop, max 6 "
+                        "iterations, Es/N0 %.1f dB (BPSK-equivalent per coded bit)" % (info_bits, args.tb_esn0),
+            "tb_latency_us": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
+                              "max": float(lat.max()), "samples": int(lat.size),
+                              "api": "fec_run_host, 152 codeblocks per call, pinned host buffers, H2D+kernel+D2H"},
+            "device_resident": {"value": n_tb * info_bits / (ms * 1e-3) / 1e9, "unit": "Gbit/s", "tbs_per_launch": n_tb,
+                                "ms_per_launch": ms},
+            "cb_crc_pass_fraction": float(((rr["status"] & fec.RES_CRC_PASS) != 0).mean()),
+            "mean_iterations": float(rr["nof_ldpc_iterations"].mean()), "layers": int(rr["nof_layers"].max()),
+            "first_tb_pass_fraction": float(((r1["status"] & fec.RES_CRC_PASS) != 0).mean())}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -278,6 +348,13 @@ def run_ours(args):
              "esn0_db": args.esn0, "mean_iterations": float(res_es["nof_ldpc_iterations"].mean()),
              "crc_pass_fraction": float(((res_es["status"] & fec.RES_CRC_PASS) != 0).mean())}
 
+    # ---- BASELINE config 3: one full-slot transport block (273 PRB, 4 layers, 256QAM R=948/1024: TBS 1 277 992 bits,
+    # 152 codeblocks of BG1 Z=384 with 16 fillers, E = 8960 / 8992, Qm = 8), early stop, through fec_run_host from
+    # pinned host memory: latency of one TB (call to return) and device-resident throughput of many TBs.
+    tb = None
+    if not args.no_tb:
+        tb = bench_transport_block(fec, eng, torch, dev, stream, args, rank)
+
     # ---- e2e: host buffers through fec_run_host (H2D + kernels + D2H inside the timed region) --------------------------
     res_h = np.zeros(n, fec.RESULT_DTYPE)
     llr_ptr, out_ptr = t_llr_pin.data_ptr(), t_out_pin.data_ptr()
@@ -317,7 +394,7 @@ def run_ours(args):
                 "crc_pass_fraction": float(passed.mean()),
                 "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + K // 8 + 48),
                         "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
-                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early,
+                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                              "frac": achieved / peak_gbs, "traffic": None, "kernel": "fec decode kernel (1 launch/step)",
                              "kernel_ms": kernel_s * 1e3, "algorithmic_bytes_per_cb": ALGO_BYTES_PER_CB,
@@ -349,8 +426,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cbs", type=int, default=148 * 48, help="codeblocks per step per GPU")
     ap.add_argument("--esn0", type=float, default=-2.0, help="BPSK Es/N0 in dB of the synthetic channel")
+    ap.add_argument("--tb-esn0", type=float, default=8.0, help="Es/N0 (dB) of the config-3 transport-block measurement")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tb", action="store_true", help="skip the config-3 transport-block latency measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     return run_reference(args) if args.impl == "reference" else run_ours(args)

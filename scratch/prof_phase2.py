@@ -9,4 +9,4 @@ d=fec.make_descs(n); bench.fill_descs(fec,d,n,False)
 out=np.zeros((n,1056),np.uint8)
 res=eng.run_host(d,llr,out); res=eng.run_host(d,llr,out)
 r=res['reserved']
-print('stage clks',(r&0xffff).mean()*64,'groups clks',(r>>16).mean()*64)
+print('hard clks',(r&0xffff).mean()*16,'crc clks',(r>>16).mean()*16)

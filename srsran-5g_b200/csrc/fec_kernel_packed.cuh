@@ -200,37 +200,47 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   constexpr int  NW = (D <= 8) ? 2 : 3;
   const uint32_t tb = soft_s + t * 2;
 
-  // Issue the soft loads of every edge first (independent byte loads: lane 0 at A, lane 1 at A ^ 1).
-  uint32_t a0[D], up[D];
+  // ---- pre-phase: everything that does not depend on the soft bits (addresses, the previous c2v messages of this row).
+  // It runs BEFORE the CTA barrier that orders this row after the previous one, so warps that finished the previous row
+  // early do useful work instead of waiting, and the table / state load latency overlaps the other warps' tail.
+  uint32_t a0[D], cneg[D];
+  {
+    const uint32_t w0 = st[0], w1 = st[H];
+    uint32_t       w2 = 0;
+    if (NW == 3) {
+      w2 = st[2 * H];
+    }
 #pragma unroll
-  for (int e = 0; e < D; ++e) {
-    const uint4 E = *reinterpret_cast<const uint4*>(&ed[e]);
-    a0[e]         = ((t >= E.z) ? E.y : E.x) + tb;
-    up[e]         = imad(lds_u8(a0[e] ^ 1u), 65536u, lds_u8(a0[e]));
+    for (int e = 0; e < D; ++e) {
+      const uint4 E = *reinterpret_cast<const uint4*>(&ed[e]);
+      a0[e]         = ((t >= E.z) ? E.y : E.x) + tb;
+    }
+    const uint32_t om1 = __byte_perm(w0, 0, 0x4140), om2 = __byte_perm(w0, 0, 0x4342);
+    const uint32_t odl = h2_add(om2, om1 ^ H2_SIGN); // m2 - m1 >= 0
+    const uint32_t oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 16) ? w2 : __byte_perm(w2, 0, 0x4341));
+#pragma unroll
+    for (int e = 0; e < D; ++e) {
+      const uint32_t sw  = (e < 16) ? w1 : w2;
+      const uint32_t ism = h2_eq_bf(oid, FEC_H2(e));                   // edge e was the min1 edge
+      const uint32_t mag = h2_fma(ism, odl, om1);                      // |old c2v|
+      const uint32_t sgs = imad(sw, 1u << (15 - (e & 15)), 0u);        // its sign bits at 15 / 31
+      cneg[e]            = mag ^ (~sgs & H2_SIGN);                     // -(old c2v)
+    }
   }
-
-  // Previous check-to-variable state of this row.
-  const uint32_t w0 = st[0], w1 = st[H];
-  uint32_t       w2 = 0;
-  if (NW == 3) {
-    w2 = st[2 * H];
-  }
-  const uint32_t om1 = __byte_perm(w0, 0, 0x4140), om2 = __byte_perm(w0, 0, 0x4342);
-  const uint32_t odl = h2_add(om2, om1 ^ H2_SIGN); // m2 - m1 >= 0
-  const uint32_t oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 16) ? w2 : __byte_perm(w2, 0, 0x4341));
+  asm volatile("bar.sync 0;" ::: "memory");
 
   // ---- phase A: variable-to-check messages and the min1 / min2 / sign-product analysis -----------------------------------
+  uint32_t up[D];
+#pragma unroll
+  for (int e = 0; e < D; ++e) {
+    up[e] = imad(lds_u8(a0[e] ^ 1u), 65536u, lds_u8(a0[e])); // lane 0 at A, lane 1 at A ^ 1
+  }
   uint32_t v[D];
   uint32_t m1 = H2_P120, m2 = H2_P120;
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint32_t sw   = (e < 16) ? w1 : w2;
     const uint32_t S    = h2_add(up[e], H2_M128);                                    // soft value
-    const uint32_t ism  = h2_eq_bf(oid, FEC_H2(e));                                  // edge e was the min1 edge
-    const uint32_t mag  = h2_fma(ism, odl, om1);                                     // |old c2v|
-    const uint32_t sgs  = imad(sw, 1u << (15 - (e & 15)), 0u);                       // its sign bits at 15 / 31
-    const uint32_t cneg = mag ^ (~sgs & H2_SIGN);                                    // -(old c2v)
-    const uint32_t vraw = h2_add(S, cneg);                                           // soft - c2v, |.| <= 223
+    const uint32_t vraw = h2_add(S, cneg[e]);                                        // soft - c2v, |.| <= 223
     const uint32_t y    = h2_add(h2_fma(S, H2_F4352, H2_F96), H2_FM96);              // +-1/16 iff |S| > 120
     const uint32_t vcl  = h2_min_xs(vraw, H2_P120);                                  // saturate at +-120
     const uint32_t vv   = h2_fma(y, H2_F2M11, vcl);                                  // "infinite" soft bits stay huge
@@ -775,23 +785,28 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
     for (uint32_t l = 0; l < nlayers; ++l) {
-      if (tid < H) {
-        uint32_t*              st = state + (uint32_t)soff[l] * H + tid;
+      if ((tid & ~31u) >= H) {
+        asm volatile("bar.sync 0;" ::: "memory"); // warps without work still take part in the row barrier
+      } else {
+        // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores) so that
+        // whole warps reach the barrier inside the row function.
+        const uint32_t         tq = min(tid, H - 1);
+        uint32_t*              st = state + (uint32_t)soff[l] * H + tq;
         const fec_packed_edge* ed = edges + rs[l];
         switch (deg[l]) {
-          case 3: fec_packed_row<3>(soft_s, st, ed, H, tid, smul, sadd); break;
-          case 4: fec_packed_row<4>(soft_s, st, ed, H, tid, smul, sadd); break;
-          case 5: fec_packed_row<5>(soft_s, st, ed, H, tid, smul, sadd); break;
-          case 6: fec_packed_row<6>(soft_s, st, ed, H, tid, smul, sadd); break;
-          case 7: fec_packed_row<7>(soft_s, st, ed, H, tid, smul, sadd); break;
-          case 8: fec_packed_row<8>(soft_s, st, ed, H, tid, smul, sadd); break;
-          case 9: fec_packed_row<9>(soft_s, st, ed, H, tid, smul, sadd); break;
-          case 10: fec_packed_row<10>(soft_s, st, ed, H, tid, smul, sadd); break;
-          default: fec_packed_row<19>(soft_s, st, ed, H, tid, smul, sadd); break;
+          case 3: fec_packed_row<3>(soft_s, st, ed, H, tq, smul, sadd); break;
+          case 4: fec_packed_row<4>(soft_s, st, ed, H, tq, smul, sadd); break;
+          case 5: fec_packed_row<5>(soft_s, st, ed, H, tq, smul, sadd); break;
+          case 6: fec_packed_row<6>(soft_s, st, ed, H, tq, smul, sadd); break;
+          case 7: fec_packed_row<7>(soft_s, st, ed, H, tq, smul, sadd); break;
+          case 8: fec_packed_row<8>(soft_s, st, ed, H, tq, smul, sadd); break;
+          case 9: fec_packed_row<9>(soft_s, st, ed, H, tq, smul, sadd); break;
+          case 10: fec_packed_row<10>(soft_s, st, ed, H, tq, smul, sadd); break;
+          default: fec_packed_row<19>(soft_s, st, ed, H, tq, smul, sadd); break;
         }
       }
-      __syncthreads();
     }
+    __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     if (early_stop) {
       const bool clean = fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
       const bool crc   = fec_crc_ok_cta(bitsw, T, tab, D.crc_type, red);
@@ -807,7 +822,15 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #endif
   if (!early_stop) {
     fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
+#ifdef FEC_PROFILE
+    const long long tq1 = clock64();
+#endif
     pass = fec_crc_ok_cta(bitsw, T, tab, D.crc_type, red) && !(D.flags & FEC_FLAG_NO_CRC);
+#ifdef FEC_PROFILE
+    if (tid == 0) {
+      s_nsig_arr[1] = (uint32_t)((tq1 - tp3) >> 4) | ((uint32_t)((clock64() - tq1) >> 4) << 16);
+    }
+#endif
   }
   for (uint32_t i = tid; i < kbytes; i += blockDim.x) {
     out[i] = (uint8_t)(bitsw[i >> 2] >> (24 - 8 * (i & 3)));
