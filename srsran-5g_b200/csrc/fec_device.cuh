@@ -16,6 +16,7 @@
 #define FEC_MAX_ROWS 46
 #define FEC_NOF_GRAPHS 102
 #define FEC_CRC_X32_ENTRIES 272 // >= 8448/32 + 1
+#define FEC_CRC_X8_ENTRIES 1064 // >= 8448/8 + 1
 
 // All graph data in one HBM-resident blob (uploaded once at engine creation, L2-resident afterwards).
 struct fec_dev_tables {
@@ -25,6 +26,7 @@ struct fec_dev_tables {
   uint16_t row_start[2][FEC_MAX_ROWS + 2];
   uint8_t  scale_lut[128];                        // lut[x] = round(x * sf) for x <= 120, x otherwise
   uint32_t crc_x32[3][FEC_CRC_X32_ENTRIES];       // x^(32 j) mod g, indexed by FEC_CRC16/24B/24A
+  uint32_t crc_x8[3][FEC_CRC_X8_ENTRIES];         // x^(8 j) mod g (byte-granular variant used by the packed kernel)
   uint32_t crc_poly[3];                           // generator with the top bit
   uint32_t crc_len[3];
 };

@@ -93,6 +93,16 @@ void build_tables(fec_dev_tables& t, float sf)
         }
       }
     }
+    r = 1;
+    for (int j = 0; j < FEC_CRC_X8_ENTRIES; ++j) {
+      t.crc_x8[p][j] = r;
+      for (int i = 0; i < 8; ++i) {
+        r <<= 1;
+        if (r & top) {
+          r ^= CRC_POLY[p];
+        }
+      }
+    }
   }
 }
 

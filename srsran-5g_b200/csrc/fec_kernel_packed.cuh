@@ -41,7 +41,7 @@ struct fec_packed_tables {
 };
 
 struct fec_packed_smem_layout {
-  uint32_t state, edges, soff, rs, deg, bitsw, red, soft, total;
+  uint32_t state, edges, soff, rs, deg, bitsw, red, x8, soft, total;
 };
 
 __host__ __device__ inline uint32_t fec_packed_row_words(uint32_t d)
@@ -75,6 +75,8 @@ __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, 
   o += ((Kb * Z + 31) / 32 + 1) * 4;
   L.red = o;
   o += 64 * 4;
+  L.x8 = o;
+  o += (Kb * Z / 8 + 2) * 4;
   o      = (o + 15) & ~15u;
   L.soft = o;
   o += (nfull * Z + 15) & ~15u;
@@ -322,17 +324,27 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32
   int            zero = 0;
   if ((H & 31u) == 0) {
     // One column per step: thread t holds variables t and t+H of the column; a ballot yields 32 consecutive bits.
-    const uint32_t Kb = K / Z;
+    // Kb is 22 or 10: batches of 11 / 10 loads in flight, then the ballots.
+    const uint32_t Kb = K / Z, nb = (Kb == 22) ? 11u : 10u;
     if (threadIdx.x < H) {
-      for (uint32_t col = 0; col < Kb; ++col) {
-        const uint32_t hw = *reinterpret_cast<const uint16_t*>(soft + col * Z + threadIdx.x * 2);
-        const uint32_t b0 = hw & 0xffu, b1 = hw >> 8;
-        zero |= (b0 == 128) | (b1 == 128);
-        const uint32_t bal0 = __ballot_sync(0xffffffffu, b0 <= 128);
-        const uint32_t bal1 = __ballot_sync(0xffffffffu, b1 <= 128);
-        if (lane == 0) {
-          bitsw[(col * Z + warp * 32) >> 5]     = __brev(bal0);
-          bitsw[(col * Z + H + warp * 32) >> 5] = __brev(bal1);
+      for (uint32_t c0 = 0; c0 < Kb; c0 += nb) {
+        uint32_t hw[11];
+#pragma unroll
+        for (uint32_t c = 0; c < 11; ++c) {
+          hw[c] = (c < nb) ? *reinterpret_cast<const uint16_t*>(soft + (c0 + c) * Z + threadIdx.x * 2) : 0x8181u;
+        }
+#pragma unroll
+        for (uint32_t c = 0; c < 11; ++c) {
+          if (c < nb) {
+            const uint32_t b0 = hw[c] & 0xffu, b1 = hw[c] >> 8;
+            zero |= (b0 == 128) | (b1 == 128);
+            const uint32_t bal0 = __ballot_sync(0xffffffffu, b0 <= 128);
+            const uint32_t bal1 = __ballot_sync(0xffffffffu, b1 <= 128);
+            if (lane == 0) {
+              bitsw[((c0 + c) * Z + warp * 32) >> 5]     = __brev(bal0);
+              bitsw[((c0 + c) * Z + H + warp * 32) >> 5] = __brev(bal1);
+            }
+          }
         }
       }
     }
@@ -353,6 +365,56 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32
     }
   }
   return __syncthreads_or(zero) == 0;
+}
+
+// CRC remainder == 0 test of the first T bits of bitsw (crc_calculator_generic_impl.cpp:111-133 computes the same
+// remainder bytewise). Byte i of the message contributes byte_i(x) * x^(8 (nb-1-i)) mod g; x8[j] = x^(8 j) mod g is staged
+// in shared memory once per codeblock. Up to six independent 8-step multiply chains per thread, one barrier.
+// Kept out of line: inlined into the codeblock function it changes ptxas' register allocation of the row code for the worse.
+__device__ __noinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T, const uint32_t* x8, uint32_t poly,
+                                                  uint32_t top, uint32_t* red)
+{
+  const uint32_t nb = T / 8, r = T % 8;
+  uint32_t       acc = 0;
+  for (uint32_t i0 = threadIdx.x; i0 < nb; i0 += 6 * blockDim.x) {
+    uint32_t a[6], w[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const uint32_t i = i0 + k * blockDim.x;
+      const bool     v = (i < nb);
+      a[k]             = v ? x8[nb - 1 - i] : 0u;
+      w[k]             = v ? (bitsw[i >> 2] >> (24 - 8 * (i & 3))) : 0u;
+    }
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        acc ^= ((w[k] >> s) & 1u) ? a[k] : 0u;
+        a[k] = fec_crc_shift1(a[k], poly, top);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    red[threadIdx.x >> 5] = acc;
+  }
+  __syncthreads();
+  uint32_t rem = 0;
+  for (uint32_t i = 0; i < (blockDim.x >> 5); ++i) {
+    rem ^= red[i];
+  }
+  if (r != 0) {
+    // rem = (the nb full bytes) mod g; continue bitwise over the remaining bits.
+    const uint32_t last = bitsw[nb >> 2] >> (24 - 8 * (nb & 3));
+    for (uint32_t i = 0; i < r; ++i) {
+      rem = (rem << 1) | ((last >> (7 - i)) & 1u);
+      rem = (rem & top) ? (rem ^ poly) : rem;
+    }
+  }
+  return rem == 0;
 }
 
 // ---- rate dematcher of the packed path ------------------------------------------------------------------------------------
@@ -468,6 +530,10 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
   }
   for (uint32_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
     const uint32_t o0 = g * 4;
+    if (o0 >= G.zero_from) {
+      harq4[g] = 0; // the soft bits were preset to zero
+      continue;
+    }
     int            val[4];
     const bool     in1 = (o0 >= r1_lo) && (o0 + 4 <= r1_hi);
     const bool     in2 = (o0 >= r2_lo) && (o0 + 4 <= r2_hi);
@@ -686,6 +752,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   uint8_t*         deg   = smem_raw + L.deg;
   uint32_t*        bitsw = reinterpret_cast<uint32_t*>(smem_raw + L.bitsw);
   uint32_t*        red   = reinterpret_cast<uint32_t*>(smem_raw + L.red);
+  uint32_t*        x8    = reinterpret_cast<uint32_t*>(smem_raw + L.x8);
   uint8_t*         soft  = smem_raw + L.soft;
 
   // Stage the graph of this codeblock and clear the check state.
@@ -700,9 +767,15 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
       deg[i]  = tab->deg[bg1 ? 0 : 1][i];
       soff[i] = ptab->state_off[bg1 ? 0 : 1][i];
     }
-    uint32_t* p2 = reinterpret_cast<uint32_t*>(soft);
-    for (uint32_t i = tid; i < H; i += blockDim.x) {
-      p2[i] = 0x80808080u; // the two punctured columns (2Z bytes): soft = 0
+    // All soft bits start at zero (offset-binary 128): the two punctured columns, and whatever the dematcher skips.
+    uint4*         p4  = reinterpret_cast<uint4*>(soft);
+    const uint32_t ns4 = (L.total - L.soft) / 16;
+    for (uint32_t i = tid; i < ns4; i += blockDim.x) {
+      p4[i] = make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
+    }
+    const uint32_t nx8 = (K - D.nof_filler_bits) / 8;
+    for (uint32_t i = tid; i < nx8; i += blockDim.x) {
+      x8[i] = tab->crc_x8[D.crc_type][i];
     }
     if (tid == 0) {
       s_nsig = 0;
@@ -743,15 +816,6 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
     fec_dematch_packed(D, in, harq, soft, H, reinterpret_cast<int8_t*>(state), L.edges - L.state, &s_nsig);
   }
   __syncthreads();
-  {
-    // The check state doubles as the dematcher's staging area: clear it now ("no c2v messages yet").
-    uint4*         s4 = reinterpret_cast<uint4*>(state);
-    const uint32_t n4 = (L.edges - L.state) / 16;
-    for (uint32_t i = tid; i < n4; i += blockDim.x) {
-      s4[i] = make_uint4(0, 0, 0, 0);
-    }
-  }
-  __syncthreads();
 
   // ---- stage 2: layered scaled min-sum -------------------------------------------------------------------------------------
   const uint32_t n_sig      = s_nsig;
@@ -775,6 +839,16 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   cbl          = ((cbl + Z - 1) / Z) * Z;
   const uint32_t nlayers = cbl / Z - Kb;
   const uint32_t T       = K - D.nof_filler_bits;
+  {
+    // The check state doubles as the dematcher's staging area: clear the rows in use ("no c2v messages yet").
+    uint4*         s4 = reinterpret_cast<uint4*>(state);
+    const uint32_t n4 = ((uint32_t)soff[nlayers] * H * 4 + 15) / 16;
+    for (uint32_t i = tid; i < n4; i += blockDim.x) {
+      s4[i] = make_uint4(0, 0, 0, 0);
+    }
+  }
+  const uint32_t crc_poly = tab->crc_poly[D.crc_type], crc_top = 1u << tab->crc_len[D.crc_type];
+  __syncthreads();
   const uint32_t smul = ptab->scale_mul, sadd = ptab->scale_add;
   const uint32_t soft_s = (uint32_t)__cvta_generic_to_shared(soft);
 
@@ -809,7 +883,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     if (early_stop) {
       const bool clean = fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
-      const bool crc   = fec_crc_ok_cta(bitsw, T, tab, D.crc_type, red);
+      const bool crc   = fec_crc_ok_packed(bitsw, T, x8, crc_poly, crc_top, red);
       if (clean && crc) {
         pass = true;
         ++it;
@@ -825,15 +899,25 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #ifdef FEC_PROFILE
     const long long tq1 = clock64();
 #endif
-    pass = fec_crc_ok_cta(bitsw, T, tab, D.crc_type, red) && !(D.flags & FEC_FLAG_NO_CRC);
+    pass = fec_crc_ok_packed(bitsw, T, x8, crc_poly, crc_top, red) && !(D.flags & FEC_FLAG_NO_CRC);
 #ifdef FEC_PROFILE
     if (tid == 0) {
       s_nsig_arr[1] = (uint32_t)((tq1 - tp3) >> 4) | ((uint32_t)((clock64() - tq1) >> 4) << 16);
     }
 #endif
   }
-  for (uint32_t i = tid; i < kbytes; i += blockDim.x) {
-    out[i] = (uint8_t)(bitsw[i >> 2] >> (24 - 8 * (i & 3)));
+  if ((reinterpret_cast<uintptr_t>(out) & 3u) == 0) {
+    uint32_t* out4 = reinterpret_cast<uint32_t*>(out);
+    for (uint32_t i = tid; i < kbytes / 4; i += blockDim.x) {
+      out4[i] = __byte_perm(bitsw[i], 0, 0x0123);
+    }
+    for (uint32_t i = (kbytes & ~3u) + tid; i < kbytes; i += blockDim.x) {
+      out[i] = (uint8_t)(bitsw[i >> 2] >> (24 - 8 * (i & 3)));
+    }
+  } else {
+    for (uint32_t i = tid; i < kbytes; i += blockDim.x) {
+      out[i] = (uint8_t)(bitsw[i >> 2] >> (24 - 8 * (i & 3)));
+    }
   }
   if (tid == 0) {
     res.nof_ldpc_iterations = (uint16_t)(pass && early_stop ? it : D.max_iter);
