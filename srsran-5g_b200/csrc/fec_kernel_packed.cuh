@@ -419,11 +419,18 @@ __device__ __noinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T
 
 // ---- rate dematcher of the packed path ------------------------------------------------------------------------------------
 // Same arithmetic as fec_dematch_cta (the per-byte statement of ldpc_rate_dematcher_impl.cpp:46-257), organised for
-// throughput: the E input LLRs are staged in shared memory with coalesced 16-byte loads (`stage`: the not-yet-used
-// check-state area; global reads when E does not fit), then every thread produces FOUR consecutive soft-buffer bytes per
-// step -- one 32-bit HBM store of the HARQ buffer, a 32-bit load of its previous contents only where the reference keeps
-// or combines them, four byte stores into the decoder's interleaved layout. Groups that straddle a region boundary
-// (k0, fillers, Ncb, end of data, ...) or belong to a wrapping transmission take the per-byte path.
+// throughput:
+//  1. the E input LLRs are read once with coalesced 16-byte loads and scattered into shared memory (`stage`: the not yet
+//     used check-state area) in RATE-MATCHED order, i.e. the bit de-interleaver of TS 38.212 5.4.2.2 is undone while
+//     staging. The staged position of LLR p is p + d, d in {d1, d2} chosen so that a staged 32-bit word lines up with a
+//     32-bit word of the soft buffer inside either data run of a non-wrapping transmission;
+//  2. the zero tail [zero_from, N) of a first transmission is stored without looking at anything (the decoder's soft bits
+//     were preset to zero);
+//  3. groups of four soft-buffer bytes inside a data run take one 32-bit shared load, one 32-bit HBM store (plus a 32-bit
+//     load and four saturating sums when combining) and four byte stores into the decoder's interleaved layout;
+//  4. every other group (region boundaries, fillers, kept parts of the buffer, wrapping transmissions) takes the general
+//     path: still four bytes per thread, per-byte rules.
+// Inputs that do not fit the staging area (E > 76 KB at Z = 384: heavy repetition) are read from global memory per byte.
 struct fec_dematch_geom {
   uint32_t Z, N, Ncb, fillers, sys, info, E, qm, Kp, invKp, Lc, k0c, zero_lo, zero_from, kstart;
   bool     newd, hzero, wrapped;
@@ -472,8 +479,26 @@ __device__ __forceinline__ uint32_t fec_dematch_src_index(const fec_dematch_geom
   return (p - j * G.Kp) * G.qm + j;
 }
 
+// Where rate-matched LLR number p is read from.
+struct fec_dematch_src {
+  const int8_t* base;   // staged copy (shared memory, rate-matched order) or the global input (interleaved)
+  bool          staged;
+  uint32_t      split;  // first p of the second data run (the one after the filler gap)
+  uint32_t      d1, d2; // staged position of p is p + (p < split ? d1 : d2)
+};
+
+__device__ __forceinline__ uint32_t fec_dematch_stage_pos(const fec_dematch_src& S, uint32_t p)
+{
+  return p + ((p < S.split) ? S.d1 : S.d2);
+}
+
+__device__ __forceinline__ int fec_dematch_fetch(const fec_dematch_geom& G, const fec_dematch_src& S, uint32_t p)
+{
+  return S.staged ? S.base[fec_dematch_stage_pos(S, p)] : S.base[fec_dematch_src_index(G, p)];
+}
+
 // One soft-buffer byte, any case. `old` is the previous buffer value (0 when the slot reads as zeros).
-__device__ __forceinline__ int fec_dematch_byte(const fec_dematch_geom& G, const int8_t* src, uint32_t o, int old)
+__device__ __forceinline__ int fec_dematch_byte(const fec_dematch_geom& G, const fec_dematch_src& S, uint32_t o, int old)
 {
   const bool is_filler = (o >= G.info) && (o < G.sys);
   int        acc;
@@ -490,7 +515,7 @@ __device__ __forceinline__ int fec_dematch_byte(const fec_dematch_geom& G, const
     uint32_t       p     = first ? (q - G.k0c) : (q + G.Lc - G.k0c);
     bool           copy  = G.newd && first;
     for (; p < G.E; p += G.Lc) {
-      const int dv = src[fec_dematch_src_index(G, p)];
+      const int dv = fec_dematch_fetch(G, S, p);
       acc          = copy ? dv : fec_sat_add(acc, dv);
       copy         = false;
     }
@@ -498,84 +523,117 @@ __device__ __forceinline__ int fec_dematch_byte(const fec_dematch_geom& G, const
   return (o >= G.zero_from) ? 0 : acc;
 }
 
-// The per-group loop of fec_dematch_packed. `src` is either the shared-memory staging copy or the global input; keeping
-// the two as separate instantiations lets the compiler use LDS for the former.
-template <class SrcPtr>
+// Four consecutive soft-buffer values (packed little-endian in w, as in the HARQ buffer) into the decoder's soft array.
+__device__ __forceinline__ void fec_soft_store4(const fec_soft_store_packed& store, uint32_t o0, uint32_t w)
+{
+  const uint32_t Z = store.Z, H = store.H;
+  const uint32_t op0 = o0 + 2 * Z;
+  const uint32_t col = __umulhi(op0, store.invZ);
+  const uint32_t j0  = op0 - col * Z;
+  int            val[4];
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    val[b] = (int)(int8_t)(w >> (8 * b));
+  }
+  if (j0 + 3 < H || (j0 >= H && j0 + 3 < Z)) {
+    const uint32_t lane = (j0 >= H) ? 1u : 0u;
+    uint8_t*       dst  = store.soft + col * Z + (j0 - lane * H) * 2 + lane;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      dst[2 * b] = (uint8_t)(fec_clampi(val[b], -64, 64) + 128);
+    }
+  } else {
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      store(o0 + b, val[b]);
+    }
+  }
+}
+
+__device__ __forceinline__ uint32_t fec_pack4(const int* val)
+{
+  return (uint32_t)(uint8_t)val[0] | ((uint32_t)(uint8_t)val[1] << 8) | ((uint32_t)(uint8_t)val[2] << 16) |
+         ((uint32_t)(uint8_t)val[3] << 24);
+}
+
+// Position + 1 of the last non-zero byte of group o0 (0 if the group is all zero).
+__device__ __forceinline__ uint32_t fec_last_sig(uint32_t o0, uint32_t w)
+{
+  return (w != 0) ? (o0 + 4 - (__clz(w) >> 3)) : 0u;
+}
+
+// The soft buffer of one codeblock, four bytes per thread and step. Returns position + 1 of this thread's last non-zero value.
 __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G,
-                                                       SrcPtr                  src,
+                                                       const fec_dematch_src&  S,
                                                        int8_t* __restrict__    harq,
                                                        uint8_t*                soft,
                                                        uint32_t                H,
                                                        uint32_t                invZ)
 {
-  uint32_t       my_sig  = 0;
-  const uint32_t Z = G.Z;
-  const uint32_t ngroups = G.N / 4; // Z is even and N = 66Z or 50Z, so N % 4 == 0
-  uint32_t*      harq4   = reinterpret_cast<uint32_t*>(harq);
-  const fec_soft_store_packed store{soft, Z, H, invZ};
-  // Data runs of a non-wrapping transmission: rate-matched position p = o - off lands at buffer position o for
-  // o in [lo, hi), once before the filler gap and once after it. Groups entirely inside a run take the lean path below.
-  uint32_t r1_lo = 1, r1_hi = 0, r1_off = 0, r2_lo = 1, r2_hi = 0, r2_off = 0;
-  if (!G.wrapped) {
+  uint32_t                    my_sig  = 0;
+  const uint32_t              ngroups = G.N / 4; // Z is even and N = 66Z or 50Z, so N % 4 == 0
+  uint32_t*                   harq4   = reinterpret_cast<uint32_t*>(harq);
+  const fec_soft_store_packed store{soft, G.Z, H, invZ};
+
+  // Data runs of a non-wrapping transmission: rate-matched LLR p = o - off lands at buffer position o for o in [lo, hi),
+  // once before the filler gap and once after it. hg0 / hg1: the groups entirely inside a run (staged inputs only).
+  uint32_t hg0[2] = {1, 1}, hg1[2] = {0, 0}, hoff[2] = {0, 0};
+  if (!G.wrapped && S.staged) {
     if (G.k0c < G.info) {
-      r1_lo  = G.k0c;
-      r1_hi  = min(G.k0c + G.E, G.info);
-      r1_off = G.k0c;
+      hg0[0]  = (G.k0c + 3) / 4;
+      hg1[0]  = min(G.k0c + G.E, G.info) / 4;
+      hoff[0] = G.k0c - S.d1;
     }
     if (G.k0c + G.E > G.info) {
-      r2_lo  = max(G.k0c, G.info) + G.fillers;
-      r2_hi  = G.k0c + G.E + G.fillers;
-      r2_off = G.k0c + G.fillers;
+      hg0[1]  = (max(G.k0c, G.info) + G.fillers + 3) / 4;
+      hg1[1]  = (G.k0c + G.E + G.fillers) / 4;
+      hoff[1] = G.k0c + G.fillers - S.d2;
     }
   }
-  for (uint32_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
-    const uint32_t o0 = g * 4;
-    if (o0 >= G.zero_from) {
-      harq4[g] = 0; // the soft bits were preset to zero
+  const uint32_t gz0 = (G.zero_from + 3) / 4; // groups from here on are all zero
+
+  // (2) zero tail
+  for (uint32_t g = gz0 + threadIdx.x; g < ngroups; g += blockDim.x) {
+    harq4[g] = 0; // the decoder's soft bits were preset to zero
+  }
+
+  // (3) groups inside a data run
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    for (uint32_t g = hg0[r] + threadIdx.x; g < hg1[r]; g += blockDim.x) {
+      const uint32_t o0 = g * 4;
+      uint32_t       w  = *reinterpret_cast<const uint32_t*>(S.base + (o0 - hoff[r]));
+      if (!G.newd) {
+        const uint32_t old = G.hzero ? 0u : harq4[g];
+        int            val[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          val[b] = fec_sat_add((int)(int8_t)(old >> (8 * b)), (int)(int8_t)(w >> (8 * b)));
+        }
+        w = fec_pack4(val);
+      }
+      harq4[g] = w;
+      my_sig   = max(my_sig, fec_last_sig(o0, w));
+      if (soft != nullptr) {
+        fec_soft_store4(store, o0, w);
+      }
+    }
+  }
+
+  // (4) everything else
+  for (uint32_t g = threadIdx.x; g < gz0; g += blockDim.x) {
+    if ((g >= hg0[0] && g < hg1[0]) || (g >= hg0[1] && g < hg1[1])) {
       continue;
     }
+    const uint32_t o0 = g * 4;
     int            val[4];
-    const bool     in1 = (o0 >= r1_lo) && (o0 + 4 <= r1_hi);
-    const bool     in2 = (o0 >= r2_lo) && (o0 + 4 <= r2_hi);
-    bool           hot = in1 || in2;
-    uint32_t       hs0 = 0, hst = 1;
-    if (hot) {
-      const uint32_t p0 = o0 - (in1 ? r1_off : r2_off);
-      hs0               = p0;
-      if (G.qm > 1) {
-        const uint32_t j = (G.Kp == 1) ? p0 : __umulhi(p0, G.invKp);
-        const uint32_t i = p0 - j * G.Kp;
-        hot              = (i + 3 < G.Kp); // all four in the same interleaver row
-        hs0              = i * G.qm + j;
-        hst              = G.qm;
-      }
-    }
-    if (hot) {
-      int dv[4];
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        dv[b] = src[hs0 + b * hst];
-      }
-      if (G.newd) {
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          val[b] = dv[b];
-        }
-      } else {
-        const uint32_t old = G.hzero ? 0u : harq4[g];
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          val[b] = fec_sat_add((int)(int8_t)(old >> (8 * b)), dv[b]);
-        }
-      }
-    } else {
     // A group is simple when no region boundary falls strictly inside it.
     auto inside = [o0](uint32_t b) { return (b > o0) && (b < o0 + 4); };
     bool simple = !G.wrapped && !inside(G.zero_lo) && !inside(G.info) && !inside(G.sys) && !inside(G.Ncb) &&
                   !inside(G.zero_from) && !inside(G.kstart);
     const bool is_filler = (o0 >= G.info) && (o0 < G.sys);
     const bool live      = !is_filler && (o0 < G.Ncb);
-    uint32_t   p0 = 0, sidx0 = 0, stride = 1;
+    uint32_t   p0        = 0;
     bool       has_data = false, first = false;
     if (simple && live) {
       const uint32_t q0 = (o0 < G.info) ? o0 : (o0 - G.fillers);
@@ -583,15 +641,6 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
       p0                = first ? (q0 - G.k0c) : (q0 + G.Lc - G.k0c);
       has_data          = (p0 + 3 < G.E);
       simple            = has_data || (p0 >= G.E); // the end of the data must not fall inside the group
-      if (has_data && G.qm > 1) {
-        const uint32_t j = (G.Kp == 1) ? p0 : __umulhi(p0, G.invKp);
-        const uint32_t i = p0 - j * G.Kp;
-        simple           = (i + 3 < G.Kp); // all four in the same interleaver row
-        sidx0            = i * G.qm + j;
-        stride           = G.qm;
-      } else {
-        sidx0 = p0;
-      }
     }
     if (simple) {
       const bool preset   = G.newd && (o0 < G.zero_lo);
@@ -602,17 +651,13 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
       if (uses_old && !G.hzero) {
         old = harq4[g];
       }
-      int        dv[4];
       const bool ld = live && has_data;
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
-        dv[b] = ld ? (int)src[sidx0 + b * stride] : 0;
-      }
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
+        const int dv   = ld ? fec_dematch_fetch(G, S, p0 + b) : 0;
         const int base = (is_filler && G.newd) ? 127 : (int)(int8_t)(old >> (8 * b));
-        const int comb = fec_sat_add(base, dv[b]);
-        const int a    = ld ? (copy ? dv[b] : comb) : base;
+        const int comb = fec_sat_add(base, dv);
+        const int a    = ld ? (copy ? dv : comb) : base;
         val[b]         = zero_all ? 0 : a;
       }
     } else {
@@ -622,35 +667,14 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
       }
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
-        val[b] = fec_dematch_byte(G, src, o0 + b, (int)(int8_t)(old >> (8 * b)));
+        val[b] = fec_dematch_byte(G, S, o0 + b, (int)(int8_t)(old >> (8 * b)));
       }
     }
-    } // general path
-    harq4[g] = (uint32_t)(uint8_t)val[0] | ((uint32_t)(uint8_t)val[1] << 8) | ((uint32_t)(uint8_t)val[2] << 16) |
-               ((uint32_t)(uint8_t)val[3] << 24);
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      if (val[b] != 0) {
-        my_sig = o0 + b + 1;
-      }
-    }
+    const uint32_t w = fec_pack4(val);
+    harq4[g]         = w;
+    my_sig           = max(my_sig, fec_last_sig(o0, w));
     if (soft != nullptr) {
-      const uint32_t op0 = o0 + 2 * Z;
-      const uint32_t col = __umulhi(op0, invZ);
-      const uint32_t j0  = op0 - col * Z;
-      if (j0 + 3 < H || (j0 >= H && j0 + 3 < Z)) {
-        const uint32_t lane = (j0 >= H) ? 1u : 0u;
-        uint8_t*       dst  = soft + col * Z + (j0 - lane * H) * 2 + lane;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          dst[2 * b] = (uint8_t)(fec_clampi(val[b], -64, 64) + 128);
-        }
-      } else {
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          store(o0 + b, val[b]);
-        }
-      }
+      fec_soft_store4(store, o0, w);
     }
   }
   return my_sig;
@@ -665,52 +689,51 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
                                                    uint32_t  stage_cap,
                                                    uint32_t* n_sig_smem)
 {
-#ifdef FEC_PROFILE
-  const long long td0 = clock64();
-#endif
   const fec_dematch_geom G = fec_dematch_geometry(D);
   const uint32_t         Z = G.Z, invZ = 0xffffffffu / Z + 1;
 
-  // Stage the input.
-  const int8_t* src = in;
-  if (G.E <= stage_cap) {
+  fec_dematch_src S;
+  S.base   = in;
+  S.staged = false;
+  S.split  = (G.k0c < G.info) ? min(G.E, G.info - G.k0c) : 0u;
+  S.d1     = G.k0c & 3u;
+  S.d2     = S.d1 + (G.fillers & 3u);
+  if (G.E + 8 <= stage_cap) {
+    // (1) stage and de-interleave: input byte s = i * Qm + j is rate-matched LLR p = j * (E / Qm) + i.
+    const uint32_t inv_qm = 0xffffffffu / G.qm + 1;
+    auto           put    = [&](uint32_t s, uint32_t byte) {
+      const uint32_t i = (G.qm == 1) ? s : __umulhi(s, inv_qm);
+      const uint32_t p = (s - i * G.qm) * G.Kp + i;
+      stage[fec_dematch_stage_pos(S, p)] = (int8_t)byte;
+    };
+    uint32_t done = 0;
     if ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) {
       const uint4*   g4 = reinterpret_cast<const uint4*>(in);
-      uint4*         s4 = reinterpret_cast<uint4*>(stage);
       const uint32_t n4 = G.E / 16;
-      for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x) {
-        s4[i] = __ldg(g4 + i);
+      for (uint32_t k = threadIdx.x; k < n4; k += blockDim.x) {
+        const uint4    v    = __ldg(g4 + k);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (uint32_t m = 0; m < 16; ++m) {
+          put(16 * k + m, w[m / 4] >> (8 * (m % 4)));
+        }
       }
-      for (uint32_t i = n4 * 16 + threadIdx.x; i < G.E; i += blockDim.x) {
-        stage[i] = in[i];
-      }
-    } else {
-      for (uint32_t i = threadIdx.x; i < G.E; i += blockDim.x) {
-        stage[i] = in[i];
-      }
+      done = n4 * 16;
+    }
+    for (uint32_t s = done + threadIdx.x; s < G.E; s += blockDim.x) {
+      put(s, (uint32_t)(uint8_t)in[s]);
     }
     __syncthreads();
-    src = stage;
+    S.base   = stage;
+    S.staged = true;
   }
 
-#ifdef FEC_PROFILE
-  const long long td1 = clock64();
-#endif
-  uint32_t my_sig;
-  if (src == stage) {
-    my_sig = fec_dematch_groups<const int8_t*>(G, stage, harq, soft, H, invZ);
-  } else {
-    my_sig = fec_dematch_groups<const int8_t* __restrict__>(G, in, harq, soft, H, invZ);
-  }
+  const uint32_t my_sig = fec_dematch_groups(G, S, harq, soft, H, invZ);
   if (my_sig != 0) {
     atomicMax(n_sig_smem, my_sig);
   }
-#ifdef FEC_PROFILE
-  if (threadIdx.x == 0) {
-    n_sig_smem[1] = (uint32_t)((td1 - td0) >> 6) | ((uint32_t)((clock64() - td1) >> 6) << 16);
-  }
-#endif
 }
+
 
 __device__ __forceinline__ bool fec_packed_cb_supported(const fec_cb_desc& D)
 {
@@ -896,15 +919,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #endif
   if (!early_stop) {
     fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
-#ifdef FEC_PROFILE
-    const long long tq1 = clock64();
-#endif
     pass = fec_crc_ok_packed(bitsw, T, x8, crc_poly, crc_top, red) && !(D.flags & FEC_FLAG_NO_CRC);
-#ifdef FEC_PROFILE
-    if (tid == 0) {
-      s_nsig_arr[1] = (uint32_t)((tq1 - tp3) >> 4) | ((uint32_t)((clock64() - tq1) >> 4) << 16);
-    }
-#endif
   }
   if ((reinterpret_cast<uintptr_t>(out) & 3u) == 0) {
     uint32_t* out4 = reinterpret_cast<uint32_t*>(out);
@@ -926,8 +941,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #ifdef FEC_PROFILE
     // phase clocks / 256: [7:0] setup, [15:8] dematch / 4, [23:16] decode / 16, [31:24] tail
     const long long tp4 = clock64();
-    res.reserved = s_nsig_arr[1];
-    if (false) res.reserved = (uint32_t)min(255ll, (tp1 - tp0) >> 8) | ((uint32_t)min(255ll, (tp2 - tp1) >> 10) << 8) |
+    res.reserved = (uint32_t)min(255ll, (tp1 - tp0) >> 8) | ((uint32_t)min(255ll, (tp2 - tp1) >> 10) << 8) |
                    ((uint32_t)min(255ll, (tp3 - tp2) >> 12) << 16) | ((uint32_t)min(255ll, (tp4 - tp3) >> 8) << 24);
 #endif
     results[cb]            = res;
