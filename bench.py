@@ -115,7 +115,8 @@ class ClockSampler:
 
 def reference_cpu(llr, n_threads, seconds, early_stop, impl=None):
     """Times the reference's CPU chain (dematch + LDPC + CRC; oracle/_ref = unmodified reference sources) on a bounded
-    sample: calibrates on a few codeblocks, then runs about `seconds` of work. Returns (Gbit/s, description dict)."""
+    sample: about `seconds` of wall clock; the throughput counts the parallel decode time reported by the shim (threads
+    started and decoders constructed before its clock starts). Returns (Gbit/s, description dict)."""
     orc = ge.load_oracle()
     if not orc.Ref.available():
         return None, {"unavailable": "oracle/_ref/libref_fec.so was not shipped"}
@@ -127,7 +128,7 @@ def reference_cpu(llr, n_threads, seconds, early_stop, impl=None):
     args_ = (True, 0, QM, 0, 0, orc.CRC24B, MAX_ITER, early_stop)
     ref.batch_chain(impl, n_threads, BG, Z, llr[:n_threads], *args_)  # warm-up: decoder objects, page faults
     total_s, total_n, n_pass, t_start = 0.0, 0, 0, time.time()
-    while total_s < seconds and time.time() - t_start < 3 * seconds + 5:
+    while time.time() - t_start < seconds:  # wall clock, so that the step stays bounded whatever the call overhead
         sec, iters, _ = ref.batch_chain(impl, n_threads, BG, Z, llr, *args_)
         total_s += sec
         total_n += len(llr)
