@@ -113,6 +113,9 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+NCU_DRAM_BYTES_PER_CB = 46250  # (180.608512 + 147.953152) MB / 7104 codeblocks, r01 capture
+
+
 def reference_cpu(llr, n_threads, seconds, early_stop, impl=None):
     """Times the reference's CPU chain (dematch + LDPC + CRC; oracle/_ref = unmodified reference sources) on a bounded
     sample: about `seconds` of wall clock; the throughput counts the parallel decode time reported by the shim (threads
@@ -397,7 +400,12 @@ def run_ours(args):
                         "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
                 "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
-                             "frac": achieved / peak_gbs, "traffic": None, "kernel": "fec decode kernel (1 launch/step)",
+                             "frac": achieved / peak_gbs,
+                             # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture
+                             # in profiles/ (46 250 B per codeblock at 7104 codeblocks), scaled to this launch
+                             "traffic": n * NCU_DRAM_BYTES_PER_CB, "traffic_unit": "bytes/launch",
+                             "traffic_source": "profiles/r01_ncu_packed_full_metrics.csv",
+                             "kernel": "fec_cb_packed_kernel (1 launch/step)",
                              "kernel_ms": kernel_s * 1e3, "algorithmic_bytes_per_cb": ALGO_BYTES_PER_CB,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                              "alu": {"edge_updates_per_s": upd_per_s,
