@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 1
+#define FEC_B200_ABI_VERSION 2
 
 typedef enum {
   FEC_OK             = 0,
@@ -86,6 +86,7 @@ typedef struct fec_cb_desc {
 #define FEC_RES_CRC_PASS  0x01u /* hw outputs .CRC_pass                                                              */
 #define FEC_RES_TOO_SHORT 0x02u /* fewer than K significant LLRs: decoder returned nullopt without iterating; with     */
                                 /* FEC_FLAG_EARLY_STOP the output bytes were left untouched, otherwise set to all ones */
+#define FEC_RES_SKIPPED   0x04u /* transport-block interface: not decoded in this call, its CRC passed in an earlier one  */
 #define FEC_RES_DONE      0x80u /* written last by the kernel                                                         */
 
 /* Per-CB outcome: mirror of hal::hw_pusch_decoder_outputs. 8 bytes. */
@@ -169,6 +170,68 @@ int fec_queue_poll(fec_engine* e, uint32_t queue_id, uint64_t* tags, fec_cb_resu
 /* Copies the decoded bytes of a completed (polled) operation; valid until the next fec_queue_enqueue after a poll
  * that returned it. nbytes <= ceil(K/8). */
 int fec_queue_fetch(fec_engine* e, uint32_t queue_id, uint64_t tag, uint8_t* dst, uint32_t nbytes);
+
+/* ---- transport-block interface: segmentation, codeblock decoding, TB assembly and TB CRC ----- */
+/* One call carries whole transport blocks: the engine splits the codeword into codeblocks as ldpc_segmenter_rx_impl::segment
+ * does (lib/phy/upper/channel_coding/ldpc/ldpc_segmenter_rx_impl.cpp:53-106, ldpc_segmenter_helpers.h:82-118, ldpc.h:128-208),
+ * decodes every codeblock whose CRC has not passed in an earlier transmission (the others only have the new LLRs combined
+ * into their soft buffers, as pusch_decoder_impl.cpp:333-344 does), concatenates the codeblock payloads and checks the
+ * transport-block CRC on the device -- the work of pusch_decoder_impl::fork_codeblock_task / join_and_notify /
+ * concatenate_codeblocks (lib/phy/upper/channel_processors/pusch/pusch_decoder_impl.cpp:308-493) and of
+ * pusch_decoder_hw_impl::run_asynch_hw_decoder / copy_tb_and_notify (pusch_decoder_hw_impl.cpp:149-445) without the
+ * per-codeblock host loop. Per-codeblock state that the reference keeps in the rx buffer (CRC flags, decoded messages of earlier
+ * transmissions) lives in the engine, keyed by the codeblock's HARQ slot. */
+#define FEC_MAX_TB_CBS 162u /* MAX_NOF_SEGMENTS */
+
+typedef struct fec_tb_desc {
+  uint64_t llr_offset;      /* first of the nof_llrs codeword LLRs in the LLR buffer                                  */
+  uint64_t out_offset;      /* transport block bytes (tbs / 8) in the output buffer                                   */
+  uint32_t tbs;             /* transport block size in bits (a multiple of 8), TB CRC not included                     */
+  uint32_t nof_llrs;        /* codeword length G = nof_ch_symbols * Qm                                                 */
+  uint32_t Nref;            /* limited-buffer rate matching, 0 = off                                                   */
+  uint32_t harq_slot;       /* HARQ slot of codeblock 0; codeblock r uses harq_slot + r unless slot_list is given      */
+  uint32_t slot_list;       /* index into the `slots` array of the call (first of nof_codeblocks entries), or          */
+                            /* FEC_TB_SLOTS_CONTIGUOUS                                                                 */
+  uint8_t  base_graph;      /* 1 or 2                                                                                  */
+  uint8_t  rv;              /* 0..3                                                                                    */
+  uint8_t  qm;              /* 1, 2, 4, 6, 8                                                                           */
+  uint8_t  nof_layers;      /* 1..4                                                                                    */
+  uint8_t  max_iter;        /* nof_ldpc_iterations                                                                     */
+  uint8_t  flags;           /* FEC_FLAG_NEW_DATA | FEC_FLAG_EARLY_STOP                                                 */
+  uint8_t  reserved[6];
+} fec_tb_desc; /* 48 bytes */
+#define FEC_TB_SLOTS_CONTIGUOUS 0xffffffffu
+
+/* Mirror of pusch_decoder_result (include/srsran/phy/upper/channel_processors/pusch/pusch_decoder_result.h). */
+typedef struct fec_tb_result {
+  uint16_t nof_codeblocks;       /* nof_codeblocks_total                                                               */
+  uint16_t nof_cb_decoded;       /* codeblocks decoded in this call (the others had passed their CRC earlier)          */
+  uint16_t nof_cb_crc_ok;        /* codeblocks whose CRC is good after this call                                       */
+  uint8_t  tb_crc_ok;            /* tb_crc_ok: the transport block bytes were delivered and their CRC is good          */
+  uint8_t  tb_delivered;         /* transport block bytes were written (all codeblock CRCs good), CRC good or not      */
+  uint32_t iter_sum;             /* ldpc_decoder_stats over the decoded codeblocks: sum, min, max of the iterations    */
+  uint16_t iter_min;             /* (a codeblock that fails counts max_iter, as in check_hw_results)                   */
+  uint16_t iter_max;
+} fec_tb_result; /* 16 bytes */
+
+/* Segmentation only, on the host (no GPU needed): fills cbs[0 .. *nof_cbs) with prepared CHAIN descriptors whose
+ * llr_offset is relative to tb->llr_offset + codeword offset, out_offset = r * FEC_MAX_CB_OUT_BYTES, harq_slot as the
+ * call would use it (slots may be NULL). payload_bits[r] (may be NULL) = bits of codeblock r that belong to the
+ * transport block + TB CRC stream (nof_new_bits in pusch_decoder_hw_impl.cpp:228). */
+int fec_tb_segment(const fec_tb_desc* tb, const uint32_t* slots, fec_cb_desc* cbs, uint32_t* nof_cbs,
+                   uint32_t* payload_bits);
+
+/* Decodes n transport blocks from host buffers, synchronously. h_out receives the bytes of every transport block that
+ * is delivered (left untouched otherwise, as the reference leaves `transport_block`). h_cb_results (may be NULL) receives
+ * FEC_MAX_TB_CBS entries per transport block; entries of codeblocks skipped in this call have status FEC_RES_SKIPPED.
+ * After a good TB CRC the HARQ slots of the block are freed (fec_harq_free) and its codeblock flags cleared; after a bad TB
+ * CRC with all codeblock CRCs good the flags are reset (rx_buffer reset_codeblocks_crc). */
+int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr,
+                    size_t llr_bytes, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results,
+                    fec_cb_result* h_cb_results);
+
+/* Forgets the codeblock CRC flags of a slot range (rx buffer released / expired). */
+int fec_tb_reset_slots(fec_engine* e, uint32_t first_slot, uint32_t n);
 
 #ifdef __cplusplus
 }

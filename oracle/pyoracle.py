@@ -225,3 +225,160 @@ class Ref:
                                  C.c_uint(nof_ch_symbols), _p(rm), _p(off), _p(sc))
         return dict(n=n, rm_len=rm[:n].copy(), cw_off=off[:n].copy(), bg=int(sc[0]), Z=int(sc[1]), fillers=int(sc[2]),
                     N=int(sc[3]), crc_bits=int(sc[4]))
+
+
+# ---- transport-block layer -----------------------------------------------------------------------------------------
+def tb_geometry(tbs, bg, qm, nof_layers, nof_llrs):
+    """Receive-side segmentation of a transport block: restatement of ldpc::compute_nof_codeblocks / compute_lifting_size
+    (include/srsran/phy/upper/channel_coding/ldpc/ldpc.h:128-208), ldpc_segmenter_rx_impl::segment
+    (lib/phy/upper/channel_coding/ldpc/ldpc_segmenter_rx_impl.cpp:53-106) and compute_rm_length
+    (ldpc_segmenter_helpers.h:82-94). Returns a dict."""
+    tb_crc = 16 if tbs <= 3824 else 24
+    B = tbs + tb_crc
+    max_seg = 8448 if bg == 1 else 3840
+    C_ = 1 if B <= max_seg else -(-B // (max_seg - 24))
+    B_out = B + (24 * C_ if C_ > 1 else 0)
+    if bg == 1:
+        ref = 22
+    else:
+        ref = 10 if B > 640 else 9 if B > 560 else 8 if B > 192 else 6
+    Z = next(z for z in ALL_Z if z * C_ * ref >= B_out)
+    K, N = dims(bg, Z)
+    msg_bits = -(-B_out // C_)
+    sym = nof_llrs // qm // nof_layers
+    n_short = C_ - sym % C_
+    rm = [((sym // C_) if r < n_short else -(-sym // C_)) * nof_layers * qm for r in range(C_)]
+    data_bits = msg_bits - (tb_crc if C_ == 1 else 24)
+    stream_bits = tbs + (24 if C_ > 1 else 0)
+    payload, left = [], stream_bits
+    for r in range(C_):
+        payload.append(min(left, data_bits))
+        left -= payload[-1]
+    return dict(C=C_, Z=Z, K=K, N=N, fillers=K - msg_bits, rm=rm, cw_off=list(np.cumsum([0] + rm[:-1])),
+                crc=(CRC24B if C_ > 1 else (CRC24A if tbs > 3824 else CRC16)), data_bits=data_bits,
+                stream_bits=stream_bits, payload=payload, tb_crc=tb_crc)
+
+
+def _bits_of(packed, nbits):
+    return np.unpackbits(np.ascontiguousarray(packed, np.uint8))[:nbits]
+
+
+def tb_encode(oracle, tb_bytes, bg):
+    """Transmit side of a transport block (input generation for the tests): TB CRC attachment, segmentation with
+    codeblock CRCs (TS 38.212 5.2.2 as ldpc_segmenter_tx does it, zero padding in the last codeblock), LDPC encoding.
+    Returns the list of encoded codeblocks (unpacked bits, N each)."""
+    tbs = tb_bytes.size * 8
+    g = tb_geometry(tbs, bg, 1, 1, 1)
+    tb_crc_poly = CRC24A if tbs > 3824 else CRC16
+    stream = np.zeros(tbs + 32, np.uint8)
+    stream[:tbs] = np.unpackbits(tb_bytes)
+    oracle.lib.orc_crc_attach_bits(tb_crc_poly, _p(stream), C.c_uint32(tbs))
+    stream = stream[:tbs + g["tb_crc"]]
+    cbs, pos = [], 0
+    per = g["data_bits"] + (g["tb_crc"] if g["C"] == 1 else 0)  # bits of the TB+CRC stream per codeblock
+    for r in range(g["C"]):
+        msg = np.zeros(g["K"] + 32, np.uint8)
+        take = min(per, stream.size - pos)
+        msg[:take] = stream[pos:pos + take]
+        pos += take
+        if g["C"] > 1:
+            oracle.lib.orc_crc_attach_bits(CRC24B, _p(msg), C.c_uint32(per))
+        cbs.append(oracle.encode(bg, g["Z"], msg[:g["K"]].copy()))
+    assert pos == stream.size
+    return cbs
+
+
+def tb_transmit(oracle, cbs, tbs, bg, rv, qm, Nref, nof_layers, nof_llrs, esn0_db, seed):
+    """Rate matching of every codeblock + concatenation + AWGN: the codeword LLRs of one (re)transmission."""
+    g = tb_geometry(tbs, bg, qm, nof_layers, nof_llrs)
+    tx = np.concatenate([oracle.rate_match(bg, g["Z"], cbs[r], g["rm"][r], rv, qm, Nref, g["fillers"])
+                         for r in range(g["C"])])
+    return oracle.awgn_llr(tx, esn0_db, seed)
+
+
+class TbOracle:
+    """Whole transport blocks over the C restatement: the flow of pusch_decoder_impl (new_data :88-130,
+    fork_codeblock_task :308-372, join_and_notify :374-437, concatenate_codeblocks :439-493) with the rx buffer (soft bits,
+    codeblock CRC flags, decoded messages) kept per buffer id. Test infrastructure."""
+
+    def __init__(self, oracle):
+        self.o = oracle
+        self.buffers = {}
+
+    def decode(self, buffer_id, tbs, bg, rv, qm, Nref, nof_layers, new_data, max_iter, early_stop, llrs, tb_out):
+        """Returns dict(tb_crc_ok, nof_codeblocks, iters=[per decoded CB], delivered). tb_out is written as the reference
+        writes transport_block."""
+        g = tb_geometry(tbs, bg, qm, nof_layers, len(llrs))
+        C_, Z, K, N = g["C"], g["Z"], g["K"], g["N"]
+        buf = self.buffers.get(buffer_id)
+        if buf is None or new_data:
+            if buf is None:
+                buf = dict(soft=np.zeros((C_, N), np.int8), msg=np.zeros((C_, (K + 7) // 8), np.uint8))
+            buf["crc"] = np.zeros(C_, bool)
+            self.buffers[buffer_id] = buf
+        iters = []
+        for r in range(C_):
+            cb = np.ascontiguousarray(llrs[g["cw_off"][r]:g["cw_off"][r] + g["rm"][r]], np.int8)
+            if buf["crc"][r]:
+                self.o.rate_dematch(bg, Z, buf["soft"][r], cb, new_data, rv, qm, Nref, g["fillers"])
+                continue
+            it, out = self.o.cb_chain(bg, Z, buf["soft"][r], cb, new_data, rv, qm, Nref, g["fillers"], g["crc"],
+                                      max_iter, early_stop)
+            buf["msg"][r] = out
+            if it > 0:
+                buf["crc"][r] = True
+                iters.append(it)
+            else:
+                iters.append(max_iter)
+        res = dict(tb_crc_ok=False, nof_codeblocks=C_, iters=iters, delivered=False)
+        if C_ == 1:
+            res["tb_crc_ok"] = bool(buf["crc"][0])
+            if res["tb_crc_ok"]:
+                tb_out[:] = buf["msg"][0][:tbs // 8]
+                res["delivered"] = True
+        elif buf["crc"].all():
+            stream = np.concatenate([_bits_of(buf["msg"][r], g["payload"][r]) for r in range(C_)])
+            assert stream.size == tbs + 24
+            tb_out[:] = np.packbits(stream[:tbs])
+            res["delivered"] = True
+            res["tb_crc_ok"] = self.o.crc(CRC24A, np.packbits(stream), stream.size) == 0
+            if not res["tb_crc_ok"]:
+                buf["crc"][:] = False
+        if res["tb_crc_ok"]:
+            del self.buffers[buffer_id]  # unique_rm_buffer.release()
+        return res
+
+    def peek(self, buffer_id):
+        return self.buffers.get(buffer_id)
+
+
+class RefTb:
+    """The reference's pusch_decoder_impl + rx buffer pool (oracle/_ref, generic LDPC kernels)."""
+
+    def __init__(self, ref, nof_buffers=16, nof_codeblocks=2048):
+        self.lib = ref.lib
+        self.lib.ref_tb_create.restype = C.c_void_p
+        self.lib.ref_tb_destroy.argtypes = [C.c_void_p]
+        self.h = C.c_void_p(self.lib.ref_tb_create(C.c_uint(nof_buffers), C.c_uint(nof_codeblocks)))
+
+    def close(self):
+        if self.h:
+            self.lib.ref_tb_destroy(self.h)
+            self.h = None
+
+    def decode(self, buffer_id, tbs, bg, rv, qm, Nref, nof_layers, new_data, max_iter, early_stop, llrs, tb_out):
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        info = np.zeros(8, np.uint32)
+        rc = self.lib.ref_tb_decode(self.h, C.c_uint(buffer_id), C.c_uint(tbs), bg, C.c_uint(rv), C.c_uint(qm),
+                                    C.c_uint(Nref), C.c_uint(nof_layers), int(new_data), C.c_uint(max_iter),
+                                    int(early_stop), _p(llrs), C.c_uint(llrs.size), _p(tb_out), _p(info))
+        if rc != 0:
+            raise RuntimeError("ref_tb_decode failed: %d" % rc)
+        return dict(tb_crc_ok=bool(info[0]), nof_codeblocks=int(info[1]), iter_min=int(info[2]), iter_max=int(info[3]),
+                    nof_obs=int(info[4]))
+
+    def peek(self, buffer_id, nof_cbs, cb_len):
+        flags = np.zeros(nof_cbs, np.uint8)
+        soft = np.zeros((nof_cbs, cb_len), np.int8)
+        n = self.lib.ref_tb_peek(self.h, C.c_uint(buffer_id), C.c_uint(nof_cbs), C.c_uint(cb_len), _p(flags), _p(soft))
+        return None if n < 0 else (flags.astype(bool), soft)

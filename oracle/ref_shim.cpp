@@ -14,8 +14,15 @@
 //   ldpc_graph_impl getters               lib/phy/upper/channel_coding/ldpc/ldpc_graph_impl.h
 //   pusch_codeblock_decoder::decode       lib/phy/upper/channel_processors/pusch/pusch_codeblock_decoder.cpp:34-71 (re-stated
 //                                         in ref_cb_chain below through the same three reference objects)
+//   pusch_decoder_impl + rx_buffer_pool   lib/phy/upper/channel_processors/pusch/pusch_decoder_impl.{h,cpp},
+//                                         lib/phy/upper/rx_buffer_pool_impl.cpp (whole transport blocks: ref_tb_* below)
 #include "ldpc_graph_impl.h"
 #include "ldpc_luts_impl.h"
+#include "phy/upper/channel_processors/pusch/pusch_decoder_impl.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_notifier.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_result.h"
+#include "srsran/phy/upper/rx_buffer_pool.h"
+#include "srsran/phy/upper/unique_rx_buffer.h"
 #include "srsran/phy/upper/channel_coding/channel_coding_factories.h"
 #include "srsran/phy/upper/channel_coding/ldpc/ldpc_encoder_buffer.h"
 #include "srsran/ran/sch/sch_segmentation.h"
@@ -426,6 +433,142 @@ int ref_segment(unsigned tbs, int bg, unsigned rv, unsigned qm, unsigned Nref, u
   scalars[4]                  = m.cb_specific.nof_crc_bits;
   scalars[5]                  = 0;
   return cbs.size();
+}
+
+} // extern "C"
+
+
+// ---- whole transport blocks through the reference's software PUSCH decoder and its rx buffer pool ------------------------
+namespace {
+
+struct ref_tb_notifier : public pusch_decoder_notifier {
+  pusch_decoder_result result;
+  bool                 notified = false;
+  void                 on_sch_data(const pusch_decoder_result& r) override
+  {
+    result   = r;
+    notified = true;
+  }
+};
+
+struct ref_tb_ctx {
+  std::unique_ptr<rx_buffer_pool_controller> pool;
+  std::unique_ptr<pusch_decoder>             dec;
+  unsigned                                   slot_count = 0;
+};
+
+} // namespace
+
+extern "C" {
+
+/// Creates a software PUSCH decoder (generic LDPC kernels) with an rx buffer pool of nof_buffers x nof_codeblocks.
+void* ref_tb_create(unsigned nof_buffers, unsigned nof_codeblocks)
+{
+  auto ctx = new ref_tb_ctx();
+  rx_buffer_pool_config pc;
+  pc.max_codeblock_size   = ldpc::MAX_CODEBLOCK_SIZE;
+  pc.nof_buffers          = nof_buffers;
+  pc.nof_codeblocks       = nof_codeblocks;
+  pc.expire_timeout_slots = 1000000;
+  pc.external_soft_bits   = false;
+  ctx->pool               = create_rx_buffer_pool(pc);
+  auto crcf               = create_crc_calculator_factory_sw("auto");
+  auto make_crcs          = [&crcf]() {
+    pusch_decoder_impl::sch_crc c;
+    c.crc16  = crcf->create(crc_generator_poly::CRC16);
+    c.crc24A = crcf->create(crc_generator_poly::CRC24A);
+    c.crc24B = crcf->create(crc_generator_poly::CRC24B);
+    return c;
+  };
+  pusch_codeblock_decoder::sch_crc cb_crcs;
+  cb_crcs.crc16  = crcf->create(crc_generator_poly::CRC16);
+  cb_crcs.crc24A = crcf->create(crc_generator_poly::CRC24A);
+  cb_crcs.crc24B = crcf->create(crc_generator_poly::CRC24B);
+  std::vector<std::unique_ptr<pusch_codeblock_decoder>> cbd;
+  cbd.push_back(std::make_unique<pusch_codeblock_decoder>(create_ldpc_rate_dematcher_factory_sw("generic")->create(),
+                                                          create_ldpc_decoder_factory_sw("generic")->create(), cb_crcs));
+  auto dpool = std::make_shared<pusch_decoder_impl::codeblock_decoder_pool>(std::move(cbd));
+  ctx->dec   = std::make_unique<pusch_decoder_impl>(create_ldpc_segmenter_rx_factory_sw()->create(), dpool, make_crcs(),
+                                                  nullptr, MAX_RB, 4);
+  return ctx;
+}
+
+void ref_tb_destroy(void* h)
+{
+  delete static_cast<ref_tb_ctx*>(h);
+}
+
+/// One transmission of a transport block. buffer_id selects the rx buffer (rnti << 8 | harq). tb_out (tbs / 8 bytes) is
+/// written only when the reference writes its transport_block. info[0..5] = {tb_crc_ok, nof_codeblocks, iterations min,
+/// iterations max, nof iteration observations, reservation ok}. Returns 0, or -1 when the buffer could not be reserved.
+int ref_tb_decode(void*         h,
+                  unsigned      buffer_id,
+                  unsigned      tbs,
+                  int           bg,
+                  unsigned      rv,
+                  unsigned      qm,
+                  unsigned      Nref,
+                  unsigned      nof_layers,
+                  int           new_data,
+                  unsigned      max_iter,
+                  int           early_stop,
+                  const int8_t* llrs,
+                  unsigned      nof_llrs,
+                  uint8_t*      tb_out,
+                  unsigned*     info)
+{
+  ref_tb_ctx*          ctx = static_cast<ref_tb_ctx*>(h);
+  ldpc_base_graph_type g   = (bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+  unsigned             ncb = ldpc::compute_nof_codeblocks(units::bits(tbs), g);
+  slot_point           slot(0, ctx->slot_count++ % 10240);
+  unique_rx_buffer     buf = ctx->pool->get_pool().reserve(
+      slot, trx_buffer_identifier(static_cast<uint16_t>(buffer_id >> 8), static_cast<uint8_t>(buffer_id & 0xff)), ncb, new_data != 0);
+  info[5] = buf.is_valid() ? 1 : 0;
+  if (!buf.is_valid()) {
+    return -1;
+  }
+  pusch_decoder::configuration cfg;
+  cfg.base_graph          = g;
+  cfg.rv                  = rv;
+  cfg.mod                 = mod_from_qm(qm);
+  cfg.Nref                = Nref;
+  cfg.nof_layers          = nof_layers;
+  cfg.nof_ldpc_iterations = max_iter;
+  cfg.use_early_stop      = early_stop != 0;
+  cfg.new_data            = new_data != 0;
+  ref_tb_notifier       notifier;
+  pusch_decoder_buffer& in = ctx->dec->new_data(span<uint8_t>(tb_out, tbs / 8), std::move(buf), notifier, cfg);
+  in.on_new_softbits(span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(llrs), nof_llrs));
+  in.on_end_softbits();
+  info[0] = notifier.result.tb_crc_ok ? 1 : 0;
+  info[1] = notifier.result.nof_codeblocks_total;
+  info[2] = notifier.result.ldpc_decoder_stats.get_min();
+  info[3] = notifier.result.ldpc_decoder_stats.get_max();
+  info[4] = notifier.result.ldpc_decoder_stats.get_nof_observations();
+  return notifier.notified ? 0 : -2;
+}
+
+/// Peeks at the rx buffer of a transport block between transmissions: codeblock CRC flags and soft bits (cb_len each).
+/// Returns the number of codeblocks, or -1 when the buffer does not exist (released after a good TB CRC).
+int ref_tb_peek(void* h, unsigned buffer_id, unsigned nof_cbs, unsigned cb_len, uint8_t* crc_flags, int8_t* soft)
+{
+  ref_tb_ctx*      ctx = static_cast<ref_tb_ctx*>(h);
+  slot_point       slot(0, ctx->slot_count++ % 10240);
+  unique_rx_buffer buf = ctx->pool->get_pool().reserve(
+      slot, trx_buffer_identifier(static_cast<uint16_t>(buffer_id >> 8), static_cast<uint8_t>(buffer_id & 0xff)), nof_cbs, false);
+  if (!buf.is_valid()) {
+    return -1;
+  }
+  span<bool> crcs = buf->get_codeblocks_crc();
+  for (unsigned i = 0; i != nof_cbs; ++i) {
+    crc_flags[i] = crcs[i] ? 1 : 0;
+    if (soft != nullptr) {
+      span<log_likelihood_ratio> sb = buf->get_codeblock_soft_bits(i, cb_len);
+      std::memcpy(soft + size_t(i) * cb_len, sb.data(), cb_len);
+    }
+  }
+  buf.unlock();
+  return static_cast<int>(nof_cbs);
 }
 
 } // extern "C"

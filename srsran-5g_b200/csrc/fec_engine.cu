@@ -7,6 +7,7 @@
 #include "fec_device.cuh"
 #include "fec_kernel_generic.cuh"
 #include "fec_kernel_packed.cuh"
+#include "fec_tb.cuh"
 #include "ldpc_tables.h"
 #include <atomic>
 #include <cmath>
@@ -163,6 +164,15 @@ struct fec_engine {
   fec_cb_desc*   h_descs_pin = nullptr; // the host and serialise the chunk pipeline
   std::vector<queue_t>* queues = nullptr;
   std::mutex            queues_mtx;
+  // transport-block layer (allocated on first use)
+  std::atomic<uint8_t>* cb_ok    = nullptr; // per HARQ slot: the codeblock's CRC passed in an earlier transmission
+  uint8_t*              d_msg    = nullptr; // per HARQ slot: decoded message of the codeblock (FEC_MAX_CB_OUT_BYTES)
+  fec_tb_job*           d_jobs   = nullptr;
+  fec_tb_cb_ref*        d_map    = nullptr;
+  fec_tb_result*        d_tbres  = nullptr;
+  fec_tb_job*           h_jobs   = nullptr; // pinned
+  fec_tb_cb_ref*        h_map    = nullptr; // pinned
+  fec_tb_result*        h_tbres  = nullptr; // pinned
 };
 
 namespace {
@@ -423,6 +433,14 @@ void fec_engine_destroy(fec_engine* e)
   cudaFreeHost(e->h_res_pin);
   cudaFreeHost(e->h_descs_pin);
   delete[] e->fresh;
+  delete[] e->cb_ok;
+  cudaFree(e->d_msg);
+  cudaFree(e->d_jobs);
+  cudaFree(e->d_map);
+  cudaFree(e->d_tbres);
+  cudaFreeHost(e->h_jobs);
+  cudaFreeHost(e->h_map);
+  cudaFreeHost(e->h_tbres);
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
   if (e->stream) {
@@ -890,6 +908,274 @@ int fec_queue_fetch(fec_engine* e, uint32_t queue_id, uint64_t tag, uint8_t* dst
     }
   }
   return fail(FEC_ERR_BAD_ARG, "tag not found among completed operations of queue %u", queue_id);
+}
+
+} // extern "C"
+
+// ---- transport-block layer ----------------------------------------------------------------------------------------------
+namespace {
+
+int tb_state_alloc(fec_engine* e)
+{
+  if (e->d_msg != nullptr) {
+    return FEC_OK;
+  }
+  if ((size_t)e->cfg.harq_slots * FEC_MAX_CB_OUT_BYTES > 0xffffffffull) {
+    return fail(FEC_ERR_BAD_ARG, "transport-block interface: %u HARQ slots exceed the 32-bit message-store offsets",
+                e->cfg.harq_slots);
+  }
+  const uint32_t nc = e->cfg.max_batch_cbs;
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  CU_TRY(cudaMalloc((void**)&e->d_jobs, nc * sizeof(fec_tb_job)));
+  CU_TRY(cudaMalloc((void**)&e->d_map, nc * sizeof(fec_tb_cb_ref)));
+  CU_TRY(cudaMalloc((void**)&e->d_tbres, nc * sizeof(fec_tb_result)));
+  CU_TRY(cudaHostAlloc((void**)&e->h_jobs, nc * sizeof(fec_tb_job), cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&e->h_map, nc * sizeof(fec_tb_cb_ref), cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&e->h_tbres, nc * sizeof(fec_tb_result), cudaHostAllocDefault));
+  e->cb_ok = new (std::nothrow) std::atomic<uint8_t>[e->cfg.harq_slots];
+  for (uint32_t i = 0; i < e->cfg.harq_slots; ++i) {
+    e->cb_ok[i].store(0);
+  }
+  CU_TRY(cudaMalloc((void**)&e->d_msg, (size_t)e->cfg.harq_slots * FEC_MAX_CB_OUT_BYTES));
+  return FEC_OK;
+}
+
+uint32_t tb_slot_of(const fec_tb_desc& tb, const uint32_t* slots, uint32_t r)
+{
+  return (tb.slot_list != FEC_TB_SLOTS_CONTIGUOUS && slots != nullptr) ? slots[tb.slot_list + r] : tb.harq_slot + r;
+}
+
+// Codeblock r of a transport block as a CHAIN descriptor (not yet prepared). cw_off = sum of the rate-matched lengths
+// of the codeblocks before it.
+void tb_cb_desc(const fec_tb_desc& tb, const fec_tb_geometry& g, uint32_t r, uint32_t cw_off, uint32_t slot, fec_cb_desc& d)
+{
+  memset(&d, 0, sizeof(d));
+  d.llr_offset      = tb.llr_offset + cw_off;
+  d.out_offset      = slot * FEC_MAX_CB_OUT_BYTES;
+  d.harq_slot       = slot;
+  d.E               = fec_tb_rm_length(tb, g, r);
+  d.Nref            = tb.Nref;
+  d.nof_filler_bits = g.nof_filler_bits;
+  d.lifting_size    = (uint16_t)g.lifting_size;
+  d.base_graph      = tb.base_graph;
+  d.rv              = tb.rv;
+  d.qm              = tb.qm;
+  d.crc_type        = (uint8_t)g.crc_type;
+  d.max_iter        = tb.max_iter;
+  d.mode            = FEC_MODE_CHAIN;
+  d.flags           = tb.flags & (FEC_FLAG_NEW_DATA | FEC_FLAG_EARLY_STOP);
+}
+
+} // namespace
+
+extern "C" {
+
+int fec_tb_segment(const fec_tb_desc* tb, const uint32_t* slots, fec_cb_desc* cbs, uint32_t* nof_cbs, uint32_t* payload_bits)
+{
+  if (!tb || !cbs || !nof_cbs) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  fec_tb_geometry g;
+  if (!fec_tb_geometry_of(*tb, g)) {
+    return fail(FEC_ERR_BAD_ARG, "transport block: tbs=%u bg=%u rv=%u qm=%u layers=%u llrs=%u", tb->tbs, tb->base_graph,
+                tb->rv, tb->qm, tb->nof_layers, tb->nof_llrs);
+  }
+  uint32_t cw_off = 0, stream = 0;
+  for (uint32_t r = 0; r < g.nof_cbs; ++r) {
+    tb_cb_desc(*tb, g, r, cw_off, tb_slot_of(*tb, slots, r), cbs[r]);
+    cbs[r].llr_offset = cw_off; // relative to the codeword
+    cbs[r].out_offset = r * FEC_MAX_CB_OUT_BYTES;
+    cw_off += cbs[r].E;
+    int rc = fec_desc_prepare(&cbs[r]);
+    if (rc != FEC_OK) {
+      return rc;
+    }
+    if (payload_bits) {
+      const uint32_t left = g.stream_bits - stream;
+      payload_bits[r]     = left < g.data_bits ? left : g.data_bits;
+      stream += payload_bits[r];
+    }
+  }
+  if (cw_off != tb->nof_llrs) {
+    return fail(FEC_ERR_BAD_ARG, "transport block: rate-matched lengths sum to %u, codeword has %u LLRs", cw_off, tb->nof_llrs);
+  }
+  *nof_cbs = g.nof_cbs;
+  return FEC_OK;
+}
+
+int fec_tb_reset_slots(fec_engine* e, uint32_t first_slot, uint32_t n)
+{
+  if (!e || first_slot > e->cfg.harq_slots || n > e->cfg.harq_slots - first_slot) {
+    return fail(FEC_ERR_BAD_ARG, "bad slot range");
+  }
+  if (e->cb_ok) {
+    for (uint32_t i = 0; i < n; ++i) {
+      e->cb_ok[first_slot + i].store(0);
+    }
+  }
+  return FEC_OK;
+}
+
+int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr,
+                    size_t llr_bytes, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+{
+  if (!e || !tbs || !h_llr || !h_out || !h_results) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (n == 0) {
+    return FEC_OK;
+  }
+  if (n > e->cfg.max_batch_cbs) {
+    return fail(FEC_ERR_BAD_ARG, "%u transport blocks exceed the engine capacity", n);
+  }
+  std::lock_guard<std::mutex> lk(e->run_mtx);
+  int rc = tb_state_alloc(e);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  // Pass 1: segmentation; descriptors of the codeblocks that still need decoding, the codeblock map, the jobs.
+  uint32_t n_dec = 0, n_map = 0, max_Z = 0;
+  int      any1  = 0;
+  size_t   l0 = ~(size_t)0, l1 = 0;
+  std::vector<uint32_t> first_map(n);
+  for (uint32_t t = 0; t < n; ++t) {
+    const fec_tb_desc& tb = tbs[t];
+    fec_tb_geometry    g;
+    if (!fec_tb_geometry_of(tb, g)) {
+      return fail(FEC_ERR_BAD_ARG, "transport block %u: tbs=%u bg=%u rv=%u qm=%u layers=%u llrs=%u", t, tb.tbs,
+                  tb.base_graph, tb.rv, tb.qm, tb.nof_layers, tb.nof_llrs);
+    }
+    if (tb.llr_offset + tb.nof_llrs > llr_bytes || tb.out_offset + tb.tbs / 8 > out_bytes ||
+        tb.out_offset + tb.tbs / 8 > (size_t)e->cfg.max_batch_cbs * FEC_MAX_CB_OUT_BYTES) {
+      return fail(FEC_ERR_BAD_ARG, "transport block %u indexes outside the batch buffers", t);
+    }
+    if (n_map + g.nof_cbs > e->cfg.max_batch_cbs) {
+      return fail(FEC_ERR_BAD_ARG, "more than %u codeblocks in one call", e->cfg.max_batch_cbs);
+    }
+    first_map[t]   = n_map;
+    fec_tb_job& J  = e->h_jobs[t];
+    J.out_offset   = tb.out_offset;
+    J.nof_cbs      = g.nof_cbs;
+    J.data_bits    = g.data_bits;
+    J.stream_bits  = g.stream_bits;
+    J.tbs_bytes    = tb.tbs / 8;
+    J.map_first    = n_map;
+    J.max_iter     = tb.max_iter;
+    uint32_t cw_off = 0;
+    for (uint32_t r = 0; r < g.nof_cbs; ++r) {
+      const uint32_t slot = tb_slot_of(tb, slots, r);
+      if (slot >= e->cfg.harq_slots) {
+        return fail(FEC_ERR_BAD_ARG, "transport block %u codeblock %u: harq slot %u >= %u", t, r, slot, e->cfg.harq_slots);
+      }
+      if (tb.flags & FEC_FLAG_NEW_DATA) {
+        e->cb_ok[slot].store(0); // pusch_decoder_hw_impl.cpp:193-196
+      }
+      fec_tb_cb_ref& ref = e->h_map[n_map++];
+      ref.slot           = slot;
+      const uint32_t E   = fec_tb_rm_length(tb, g, r);
+      fec_cb_desc&   d   = e->h_descs_pin[n_dec];
+      tb_cb_desc(tb, g, r, cw_off, slot, d);
+      // A codeblock whose CRC passed in an earlier transmission is not decoded again, but the new LLRs are still
+      // combined into its soft buffer: the transport-block CRC may yet fail and put it back in play
+      // (pusch_decoder_impl.cpp:333-344).
+      const bool already_ok = e->cb_ok[slot].load() != 0;
+      if (already_ok) {
+        d.mode = FEC_MODE_DEMATCH;
+      }
+      rc = fec_desc_prepare(&d);
+      if (rc != FEC_OK) {
+        return rc;
+      }
+      apply_fresh(e, d);
+      ref.result_index = already_ok ? -1 : (int32_t)n_dec;
+      ++n_dec;
+      l0 = d.llr_offset < l0 ? (size_t)d.llr_offset : l0;
+      l1 = d.llr_offset + d.E > l1 ? (size_t)(d.llr_offset + d.E) : l1;
+      cw_off += E;
+    }
+    if (cw_off != tb.nof_llrs) {
+      return fail(FEC_ERR_BAD_ARG, "transport block %u: rate-matched lengths sum to %u, codeword has %u LLRs", t, cw_off,
+                  tb.nof_llrs);
+    }
+    max_Z = g.lifting_size > max_Z ? g.lifting_size : max_Z;
+    any1 |= (tb.base_graph == 1);
+  }
+  if (n_dec && l1 - l0 > e->cfg.max_batch_llrs) {
+    return fail(FEC_ERR_BAD_ARG, "%zu LLR bytes exceed the engine staging capacity", l1 - l0);
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = e->stream;
+  if (n_dec) {
+    // Staged LLRs start at l0: rebase the descriptors.
+    for (uint32_t i = 0; i < n_dec; ++i) {
+      e->h_descs_pin[i].llr_offset -= l0;
+    }
+    CU_TRY(cudaMemcpyAsync(e->d_descs, e->h_descs_pin, n_dec * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+  }
+  CU_TRY(cudaMemcpyAsync(e->d_jobs, e->h_jobs, n * sizeof(fec_tb_job), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(e->d_map, e->h_map, n_map * sizeof(fec_tb_cb_ref), cudaMemcpyHostToDevice, st));
+  if (n_dec) {
+    rc = launch(e, st, e->d_descs, n_dec, e->d_llr, e->d_msg, e->d_res, max_Z, any1);
+    if (rc != FEC_OK) {
+      return rc;
+    }
+    CU_TRY(cudaMemcpyAsync(e->h_res_pin, e->d_res, n_dec * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st));
+  }
+  fec_tb_assemble_kernel<<<n, 1024, 0, st>>>(e->d_jobs, e->d_map, e->d_res, e->d_msg, e->d_out, e->d_tbres);
+  CU_TRY(cudaGetLastError());
+  e->launches.fetch_add(1);
+  CU_TRY(cudaMemcpyAsync(e->h_tbres, e->d_tbres, n * sizeof(fec_tb_result), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  // Pass 2: deliver the transport blocks whose codeblocks are all good, update the per-codeblock state.
+  bool any_delivered = false;
+  for (uint32_t t = 0; t < n; ++t) {
+    const fec_tb_result& R = e->h_tbres[t];
+    if (R.tb_delivered) {
+      CU_TRY(cudaMemcpyAsync(h_out + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8, cudaMemcpyDeviceToHost, st));
+      any_delivered = true;
+    }
+  }
+  for (uint32_t t = 0; t < n; ++t) {
+    const fec_tb_result& R = e->h_tbres[t];
+    const fec_tb_job&    J = e->h_jobs[t];
+    h_results[t]           = R;
+    for (uint32_t r = 0; r < J.nof_cbs; ++r) {
+      const fec_tb_cb_ref& ref = e->h_map[J.map_first + r];
+      fec_cb_result        cr;
+      if (ref.result_index >= 0) {
+        cr = e->h_res_pin[ref.result_index];
+        if (cr.status & FEC_RES_CRC_PASS) {
+          e->cb_ok[ref.slot].store(1);
+        }
+      } else {
+        cr.nof_ldpc_iterations = 0;
+        cr.status              = FEC_RES_SKIPPED | FEC_RES_CRC_PASS | FEC_RES_DONE;
+        cr.nof_layers          = 0;
+        cr.reserved            = 0;
+      }
+      if (h_cb_results) {
+        h_cb_results[(size_t)t * FEC_MAX_TB_CBS + r] = cr;
+      }
+    }
+    if (R.tb_crc_ok) {
+      // copy_tb_and_notify: free the HARQ context entries, release the buffer.
+      for (uint32_t r = 0; r < J.nof_cbs; ++r) {
+        const uint32_t slot = e->h_map[J.map_first + r].slot;
+        e->fresh[slot].store(1);
+        e->cb_ok[slot].store(0);
+      }
+    } else if (R.tb_delivered) {
+      // All codeblock CRCs good but the TB CRC is not: at least one false positive, start over (reset_codeblocks_crc).
+      for (uint32_t r = 0; r < J.nof_cbs; ++r) {
+        e->cb_ok[e->h_map[J.map_first + r].slot].store(0);
+      }
+    }
+  }
+  if (any_delivered) {
+    CU_TRY(cudaStreamSynchronize(st));
+  }
+  return FEC_OK;
 }
 
 } // extern "C"

@@ -19,7 +19,9 @@ from . import build as _build
 CRC16, CRC24B, CRC24A = 0, 1, 2  # hal::hw_dec_cb_crc_type numbering
 MODE_CHAIN, MODE_DECODE, MODE_DEMATCH = 0, 1, 2
 FLAG_NEW_DATA, FLAG_EARLY_STOP, FLAG_NO_CRC, FLAG_HARQ_ZERO = 1, 2, 4, 8
-RES_CRC_PASS, RES_TOO_SHORT, RES_DONE = 1, 2, 0x80
+RES_CRC_PASS, RES_TOO_SHORT, RES_SKIPPED, RES_DONE = 1, 2, 4, 0x80
+MAX_TB_CBS = 162
+TB_SLOTS_CONTIGUOUS = 0xFFFFFFFF
 HARQ_SLOT_BYTES = 25344
 MAX_CB_OUT_BYTES = 1056
 
@@ -39,6 +41,20 @@ RESULT_DTYPE = np.dtype({"names": ["nof_ldpc_iterations", "status", "nof_layers"
                          "formats": ["<u2", "u1", "u1", "<u4"], "offsets": [0, 2, 3, 4], "itemsize": 8})
 
 
+# numpy mirrors of struct fec_tb_desc (48 bytes) and fec_tb_result (16 bytes)
+TB_DESC_DTYPE = np.dtype({
+    "names": ["llr_offset", "out_offset", "tbs", "nof_llrs", "Nref", "harq_slot", "slot_list", "base_graph", "rv", "qm",
+              "nof_layers", "max_iter", "flags"],
+    "formats": ["<u8", "<u8", "<u4", "<u4", "<u4", "<u4", "<u4", "u1", "u1", "u1", "u1", "u1", "u1"],
+    "offsets": [0, 8, 16, 20, 24, 28, 32, 36, 37, 38, 39, 40, 41],
+    "itemsize": 48})
+TB_RESULT_DTYPE = np.dtype({
+    "names": ["nof_codeblocks", "nof_cb_decoded", "nof_cb_crc_ok", "tb_crc_ok", "tb_delivered", "iter_sum", "iter_min",
+              "iter_max"],
+    "formats": ["<u2", "<u2", "<u2", "u1", "u1", "<u4", "<u2", "<u2"],
+    "offsets": [0, 2, 4, 6, 7, 8, 12, 14], "itemsize": 16})
+
+
 class EngineCfg(C.Structure):
     _fields_ = [("device", C.c_int32), ("harq_slots", C.c_uint32), ("max_batch_cbs", C.c_uint32),
                 ("max_batch_llrs", C.c_uint32), ("nof_queues", C.c_uint32), ("scaling_factor", C.c_float),
@@ -49,7 +65,7 @@ EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_e
            "fec_engine_stream", "fec_harq_slot_ptr", "fec_engine_launch_count", "fec_desc_prepare",
            "fec_launch_device", "fec_run_host", "fec_host_alloc", "fec_host_free", "fec_harq_free", "fec_harq_read",
            "fec_harq_write", "fec_harq_flush", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
-           "fec_queue_poll", "fec_queue_fetch"]
+           "fec_queue_poll", "fec_queue_fetch", "fec_tb_segment", "fec_tb_run_host", "fec_tb_reset_slots"]
 
 _lib = None
 
@@ -95,6 +111,10 @@ def load_library():
     lib.fec_queue_flush.argtypes = [C.c_void_p, C.c_uint32]
     lib.fec_queue_poll.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
     lib.fec_queue_fetch.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_uint32]
+    lib.fec_tb_segment.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p]
+    lib.fec_tb_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                    C.c_size_t, C.c_void_p, C.c_void_p]
+    lib.fec_tb_reset_slots.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
     _lib = lib
     return lib
 
@@ -112,6 +132,25 @@ def dims(bg, Z):
 
 def make_descs(n):
     return np.zeros(n, DESC_DTYPE)
+
+
+def make_tb_descs(n):
+    d = np.zeros(n, TB_DESC_DTYPE)
+    d["slot_list"] = TB_SLOTS_CONTIGUOUS
+    return d
+
+
+def tb_segment(tb, slots=None):
+    """fec_tb_segment: receive-side segmentation of ONE transport block descriptor, on the host (no GPU).
+    Returns (codeblock descriptors, payload bits per codeblock)."""
+    lib = load_library()
+    tb = np.atleast_1d(tb)
+    cbs = make_descs(MAX_TB_CBS)
+    payload = np.zeros(MAX_TB_CBS, np.uint32)
+    n = C.c_uint32()
+    sl = None if slots is None else np.ascontiguousarray(slots, np.uint32).ctypes.data
+    _check(lib, lib.fec_tb_segment(tb.ctypes.data, sl, cbs.ctypes.data, C.byref(n), payload.ctypes.data))
+    return cbs[:n.value].copy(), payload[:n.value].copy()
 
 
 def desc_prepare(desc):
@@ -185,6 +224,29 @@ class FecEngine:
         _check(self.lib, self.lib.fec_run_host(self.h, descs.ctypes.data, n, ptr(llr), size(llr), ptr(out), size(out),
                                                results.ctypes.data, ptr(soft_out)))
         return results
+
+    def tb_run_host(self, tbs, llr, out, slots=None, cb_results=False):
+        """fec_tb_run_host: whole transport blocks (segmentation, codeblock decoding, assembly, TB CRC), synchronous.
+        llr / out are host numpy buffers or raw pinned pointers given as (ptr, nbytes)."""
+        assert tbs.dtype == TB_DESC_DTYPE and tbs.flags.c_contiguous
+        n = tbs.size
+        res = np.zeros(n, TB_RESULT_DTYPE)
+        cbr = np.zeros(n * MAX_TB_CBS, RESULT_DTYPE) if cb_results else None
+
+        def ptr(a):
+            return a[0] if isinstance(a, tuple) else a.ctypes.data
+
+        def size(a):
+            return a[1] if isinstance(a, tuple) else a.nbytes
+
+        sl = None if slots is None else np.ascontiguousarray(slots, np.uint32)
+        _check(self.lib, self.lib.fec_tb_run_host(self.h, tbs.ctypes.data, n, None if sl is None else sl.ctypes.data,
+                                                  ptr(llr), size(llr), ptr(out), size(out), res.ctypes.data,
+                                                  None if cbr is None else cbr.ctypes.data))
+        return (res, cbr.reshape(n, MAX_TB_CBS)) if cb_results else res
+
+    def tb_reset_slots(self, first_slot, n):
+        _check(self.lib, self.lib.fec_tb_reset_slots(self.h, first_slot, n))
 
     def harq_free(self, slot):
         _check(self.lib, self.lib.fec_harq_free(self.h, slot))
@@ -395,6 +457,66 @@ class HwAcceleratorPuschDec:
 
     def is_harq_external(self):
         return True
+
+
+class PuschDecoderConfiguration:
+    """pusch_decoder::configuration (include/srsran/phy/upper/channel_processors/pusch/pusch_decoder.h)."""
+
+    def __init__(self, base_graph=1, rv=0, mod_order=2, Nref=0, nof_layers=1, nof_ldpc_iterations=6, use_early_stop=True,
+                 new_data=True):
+        self.base_graph = base_graph
+        self.rv = rv
+        self.mod_order = mod_order  # bits per symbol of `mod`
+        self.Nref = Nref
+        self.nof_layers = nof_layers
+        self.nof_ldpc_iterations = nof_ldpc_iterations
+        self.use_early_stop = use_early_stop
+        self.new_data = new_data
+
+
+class PuschDecoderResult:
+    """pusch_decoder_result: tb_crc_ok, nof_codeblocks_total, ldpc_decoder_stats (min / max / mean iterations)."""
+
+    def __init__(self, r):
+        self.tb_crc_ok = bool(r["tb_crc_ok"])
+        self.nof_codeblocks_total = int(r["nof_codeblocks"])
+        n = int(r["nof_cb_decoded"])
+        self.ldpc_decoder_stats = {"nof_observations": n, "min": int(r["iter_min"]), "max": int(r["iter_max"]),
+                                   "mean": (int(r["iter_sum"]) / n) if n else 0.0}
+
+
+class PuschDecoder:
+    """pusch_decoder + pusch_decoder_buffer (pusch_decoder.h, pusch_decoder_buffer.h) over the transport-block entry
+    point: new_data(transport_block, first_absolute_cb_id | list of ids, notifier, cfg) -> self (the buffer);
+    on_new_softbits(llrs)*; on_end_softbits() -> notifier(PuschDecoderResult). The rx buffer is represented by the
+    absolute codeblock ids it would hand out (rx_buffer::get_absolute_codeblock_id); soft bits, codeblock CRC flags and
+    decoded messages of earlier transmissions stay in the engine."""
+
+    def __init__(self, engine):
+        self.engine = engine
+
+    def new_data(self, transport_block, absolute_cb_ids, notifier, cfg):
+        self.tb, self.ids, self.notifier, self.cfg, self.soft = transport_block, absolute_cb_ids, notifier, cfg, []
+        return self
+
+    def on_new_softbits(self, softbits):
+        self.soft.append(np.ascontiguousarray(softbits, np.int8))
+
+    def on_end_softbits(self):
+        llr = np.concatenate(self.soft) if len(self.soft) != 1 else self.soft[0]
+        c = self.cfg
+        d = make_tb_descs(1)
+        d["tbs"], d["nof_llrs"], d["Nref"] = self.tb.size * 8, llr.size, c.Nref
+        d["base_graph"], d["rv"], d["qm"], d["nof_layers"] = c.base_graph, c.rv, c.mod_order, c.nof_layers
+        d["max_iter"] = c.nof_ldpc_iterations
+        d["flags"] = (FLAG_NEW_DATA if c.new_data else 0) | (FLAG_EARLY_STOP if c.use_early_stop else 0)
+        slots = None
+        if np.isscalar(self.ids):
+            d["harq_slot"] = self.ids
+        else:
+            d["slot_list"], slots = 0, np.asarray(self.ids, np.uint32)
+        r = self.engine.tb_run_host(d, llr, self.tb, slots)
+        self.notifier(PuschDecoderResult(r[0]))
 
 
 # ------------------------------------------------------------------------------------------------------------------

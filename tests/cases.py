@@ -43,3 +43,18 @@ def fill_chain_desc(fec, d, i, p, new_data, harq_slot, llr_offset, out_offset, m
     d["mode"][i] = fec.MODE_CHAIN if mode is None else mode
     d["flags"][i] = (fec.FLAG_NEW_DATA if new_data else 0) | (fec.FLAG_EARLY_STOP if p["early"] else 0)
     d["harq_slot"][i], d["llr_offset"][i], d["out_offset"][i] = harq_slot, llr_offset, out_offset
+
+
+def random_tb_params(rng, max_bits_bg1=30000, max_bits_bg2=9000):
+    """A random transport block: (tbs, bg, qm, nof_layers, nof_llrs G, Es/N0) with a code rate in (0.35, 0.93)."""
+    bg = int(rng.integers(1, 3))
+    qm = int(rng.choice([1, 2, 4, 6, 8]))
+    nl = int(rng.integers(1, 5))
+    tbs = int(rng.integers(3, (max_bits_bg1 if bg == 1 else max_bits_bg2) // 8)) * 8
+    B = tbs + (16 if tbs <= 3824 else 24)
+    seg = 8448 if bg == 1 else 3840
+    C_ = 1 if B <= seg else -(-B // (seg - 24))
+    rate = float(rng.uniform(0.35, 0.93))
+    nsym = max(1, int((B + 24 * C_) / rate / (qm * nl))) * nl
+    snr = float(rng.uniform(-1.0, 6.0)) + 10 * np.log10(rate)
+    return dict(tbs=tbs, bg=bg, qm=qm, nl=nl, G=nsym * qm, snr=snr)

@@ -1,0 +1,192 @@
+"""Transport-block layer on the GPU, through the C ABI (fec_tb_run_host) and the PuschDecoder mirror: parity with the TB
+oracle (pinned against the reference's pusch_decoder_impl in tests/test_tb_cpu.py) and with the committed fixture."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tb_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def tb_engine(fec):
+    eng = fec.FecEngine(device=0, harq_slots=2048, max_batch_cbs=1024)
+    yield eng
+    eng.close()
+
+
+def _tb_desc(fec, p, rv, new_data, slot, llr_offset=0, out_offset=0, max_iter=6, early=True):
+    d = fec.make_tb_descs(1)
+    d["tbs"], d["nof_llrs"], d["base_graph"], d["qm"], d["nof_layers"] = p["tbs"], p["G"], p["bg"], p["qm"], p["nl"]
+    d["rv"], d["max_iter"], d["harq_slot"] = rv, max_iter, slot
+    d["flags"] = (fec.FLAG_NEW_DATA if new_data else 0) | (fec.FLAG_EARLY_STOP if early else 0)
+    d["llr_offset"], d["out_offset"] = llr_offset, out_offset
+    return d
+
+
+def test_tb_golden_sequences(fec, tb_engine):
+    """The reference's own outputs (tests/golden/tb_golden.npz): delivered bytes, tb_crc_ok, soft buffers."""
+    G = np.load(GOLDEN)
+    for i, k in enumerate(sorted({k[:3] for k in G.files})):
+        tbs, bg, qm, nl, nllr, C_, ntx = [int(x) for x in G[k + "_params"]]
+        p = dict(tbs=tbs, bg=bg, qm=qm, nl=nl, G=nllr)
+        slot = 40 * i
+        for t in range(ntx):
+            rv, ok = [int(x) for x in G["%s_t%d_rv" % (k, t)]]
+            out = np.full(tbs // 8, 0xAA, np.uint8)
+            res, cbr = tb_engine.tb_run_host(_tb_desc(fec, p, rv, t == 0, slot), G["%s_t%d_llr" % (k, t)], out, cb_results=True)
+            assert bool(res["tb_crc_ok"][0]) == bool(ok) and int(res["nof_codeblocks"][0]) == C_, (k, t)
+            assert (out == G["%s_t%d_out" % (k, t)]).all(), (k, t)
+            if not ok:
+                flags, soft = G["%s_t%d_flags" % (k, t)], G["%s_t%d_soft" % (k, t)]
+                for r in range(C_):
+                    assert (tb_engine.harq_read(slot + r, soft.shape[1]) == soft[r]).all(), (k, t, r)
+                assert int(res["nof_cb_crc_ok"][0]) == int(flags.sum()), (k, t)
+
+
+def test_tb_random_harq_vs_oracle(fec, tb_engine, orc, oracle):
+    """Random transport blocks (both base graphs, 1-4 codeblocks, every Qm, 1-4 layers) over rv {0,2,3,1}, several per
+    call with explicit slot lists; everything compared with the TB oracle after every transmission."""
+    rng = np.random.default_rng(99)
+    to = orc.TbOracle(oracle)
+    n_fail = n_skip = 0
+    for rnd in range(8):
+        n_tb = 4
+        ps = [cases.random_tb_params(rng) for _ in range(n_tb)]
+        gs = [orc.tb_geometry(p["tbs"], p["bg"], p["qm"], p["nl"], p["G"]) for p in ps]
+        tbs_ = [rng.integers(0, 256, p["tbs"] // 8, dtype=np.uint8) for p in ps]
+        enc = [orc.tb_encode(oracle, tb, p["bg"]) for tb, p in zip(tbs_, ps)]
+        # scattered, non-contiguous slots
+        perm = rng.permutation(2048)[:sum(g["C"] for g in gs)].astype(np.uint32)
+        first = np.concatenate([[0], np.cumsum([g["C"] for g in gs])])
+        alive = list(range(n_tb))
+        for t, rv in enumerate([0, 2, 3, 1]):
+            if not alive:
+                break
+            llrs = [orc.tb_transmit(oracle, enc[i], ps[i]["tbs"], ps[i]["bg"], rv, ps[i]["qm"], 0, ps[i]["nl"], ps[i]["G"],
+                                    ps[i]["snr"] - 1.5, seed=rnd * 1000 + i * 16 + t) for i in alive]
+            lo = np.concatenate([[0], np.cumsum([(x.size + 63) // 64 * 64 for x in llrs])])
+            oo = np.concatenate([[0], np.cumsum([ps[i]["tbs"] // 8 for i in alive])])
+            buf = np.zeros(int(lo[-1]), np.int8)
+            d = fec.make_tb_descs(len(alive))
+            for j, i in enumerate(alive):
+                buf[lo[j]:lo[j] + llrs[j].size] = llrs[j]
+                d[j:j + 1] = _tb_desc(fec, ps[i], rv, t == 0, 0, int(lo[j]), int(oo[j]))
+                d["slot_list"][j] = first[i]
+            out = np.full(int(oo[-1]), 0xAA, np.uint8)
+            res, cbr = tb_engine.tb_run_host(d, buf, out, slots=perm, cb_results=True)
+            still = []
+            for j, i in enumerate(alive):
+                want = np.full(ps[i]["tbs"] // 8, 0xAA, np.uint8)
+                w = to.decode(i, ps[i]["tbs"], ps[i]["bg"], rv, ps[i]["qm"], 0, ps[i]["nl"], t == 0, 6, True, llrs[j], want)
+                got = out[oo[j]:oo[j + 1]]
+                assert bool(res["tb_crc_ok"][j]) == w["tb_crc_ok"] and bool(res["tb_delivered"][j]) == w["delivered"], (rnd, t, i)
+                assert int(res["nof_codeblocks"][j]) == gs[i]["C"] and (got == want).all(), (rnd, t, i)
+                dec = [r for r in range(gs[i]["C"]) if not (cbr[j, r]["status"] & fec.RES_SKIPPED)]
+                n_skip += gs[i]["C"] - len(dec)
+                assert int(res["nof_cb_decoded"][j]) == len(dec) == len(w["iters"])
+                its = [int(cbr[j, r]["nof_ldpc_iterations"]) if (cbr[j, r]["status"] & fec.RES_CRC_PASS) else 6 for r in dec]
+                assert its == w["iters"], (rnd, t, i)
+                assert int(res["iter_sum"][j]) == sum(its) and int(res["iter_min"][j]) == min(its) and int(res["iter_max"][j]) == max(its)
+                if w["tb_crc_ok"]:
+                    assert (got == tbs_[i]).all()
+                else:
+                    n_fail += 1
+                    still.append(i)
+                    mine = to.peek(i)
+                    for r in range(gs[i]["C"]):
+                        assert (tb_engine.harq_read(int(perm[first[i] + r]), gs[i]["N"]) == mine["soft"][r]).all(), (rnd, t, i, r)
+            alive = still
+    assert n_fail >= 8  # partially decoded blocks (skipped codeblocks) are forced in test_tb_config3_full_size
+
+
+def test_tb_config3_full_size(fec, orc, oracle):
+    """BASELINE config 3: one 273-PRB, 4-layer, 256QAM transport block (TBS 1 277 992, 152 codeblocks, Z = 384)."""
+    eng = fec.FecEngine(device=0, harq_slots=160, max_batch_cbs=160)
+    p = dict(tbs=1277992, bg=1, qm=8, nl=4, G=1362816)
+    g = orc.tb_geometry(p["tbs"], 1, 8, 4, p["G"])
+    rng = np.random.default_rng(3)
+    tb = rng.integers(0, 256, p["tbs"] // 8, dtype=np.uint8)
+    enc = orc.tb_encode(oracle, tb, 1)
+    llr = orc.tb_transmit(oracle, enc, p["tbs"], 1, 0, 8, 0, 4, p["G"], 8.0, seed=1)
+    out = np.full(p["tbs"] // 8, 0xAA, np.uint8)
+    res, cbr = eng.tb_run_host(_tb_desc(fec, p, 0, True, 0), llr, out, cb_results=True)
+    assert int(res["nof_codeblocks"][0]) == 152 and bool(res["tb_crc_ok"][0]) and (out == tb).all()
+    # per-codeblock iteration counts against the oracle on a sample of the codeblocks
+    for r in (0, 39, 40, 151):
+        soft = np.zeros(g["N"], np.int8)
+        it, _ = oracle.cb_chain(1, 384, soft, llr[g["cw_off"][r]:g["cw_off"][r] + g["rm"][r]], True, 0, 8, 0, g["fillers"],
+                                orc.CRC24B, 6, True)
+        assert it == int(cbr[0, r]["nof_ldpc_iterations"]) and (cbr[0, r]["status"] & fec.RES_CRC_PASS)
+    # a corrupted codeword fails the block and leaves the output alone
+    bad = llr.copy()
+    bad[g["cw_off"][7]:g["cw_off"][7] + g["rm"][7]] = 0
+    out2 = np.full(p["tbs"] // 8, 0xAA, np.uint8)
+    res2 = eng.tb_run_host(_tb_desc(fec, p, 0, True, 0), bad, out2)
+    assert not res2["tb_crc_ok"][0] and not res2["tb_delivered"][0] and int(res2["nof_cb_crc_ok"][0]) == 151
+    assert (out2 == 0xAA).all()
+    # the retransmission only decodes the missing codeblock and completes the block
+    # (rv 0 again: at this code rate rv 2 alone is not self-decodable and codeblock 7 has nothing to combine with)
+    llr3 = orc.tb_transmit(oracle, enc, p["tbs"], 1, 0, 8, 0, 4, p["G"], 8.0, seed=2)
+    res3 = eng.tb_run_host(_tb_desc(fec, p, 0, False, 0), llr3, out2)
+    assert int(res3["nof_cb_decoded"][0]) == 1 and bool(res3["tb_crc_ok"][0]) and (out2 == tb).all()
+    eng.close()
+
+
+def test_tb_crc_false_positive_resets_flags(fec, tb_engine, orc, oracle):
+    """All codeblock CRCs good but a bad TB CRC: the block is delivered, flagged bad, and every codeblock is decoded again
+    on the next transmission (rx_buffer::reset_codeblocks_crc)."""
+    p = dict(tbs=20000, bg=1, qm=2, nl=1, G=40000)
+    g = orc.tb_geometry(p["tbs"], 1, 2, 1, p["G"])
+    assert g["C"] == 3
+    rng = np.random.default_rng(8)
+    tb = rng.integers(0, 256, p["tbs"] // 8, dtype=np.uint8)
+    # corrupt the TB CRC before segmentation: re-encode a stream whose last byte differs
+    stream_tb = tb.copy()
+    enc = orc.tb_encode(oracle, stream_tb, 1)
+    # flip one payload bit of codeblock 1 and fix up its CRC24B so that only the TB CRC can notice
+    K = g["K"]
+    msg = np.zeros(K + 32, np.uint8)
+    per = g["data_bits"]
+    bits = np.unpackbits(tb)
+    msg[:per] = bits[per:2 * per]
+    msg[5] ^= 1
+    oracle.lib.orc_crc_attach_bits(orc.CRC24B, msg.ctypes.data_as(__import__("ctypes").c_void_p), per)
+    enc[1] = oracle.encode(1, g["Z"], msg[:K].copy())
+    to = orc.TbOracle(oracle)
+    slot = 1500
+    for t, rv in enumerate([0, 2]):
+        llr = orc.tb_transmit(oracle, enc, p["tbs"], 1, rv, 2, 0, 1, p["G"], 6.0, seed=50 + t)
+        out = np.full(p["tbs"] // 8, 0xAA, np.uint8)
+        want = out.copy()
+        res = tb_engine.tb_run_host(_tb_desc(fec, p, rv, t == 0, slot), llr, out)
+        w = to.decode(7, p["tbs"], 1, rv, 2, 0, 1, t == 0, 6, True, llr, want)
+        assert w["delivered"] and not w["tb_crc_ok"]
+        assert bool(res["tb_delivered"][0]) and not res["tb_crc_ok"][0] and (out == want).all()
+        assert int(res["nof_cb_decoded"][0]) == 3  # flags were reset after the first transmission
+
+
+def test_pusch_decoder_mirror(fec, tb_engine, orc, oracle):
+    """pusch_decoder call sequence: new_data -> on_new_softbits (in pieces) -> on_end_softbits -> notifier."""
+    p = dict(tbs=12000, bg=1, qm=4, nl=2, G=18000)
+    rng = np.random.default_rng(21)
+    tb = rng.integers(0, 256, p["tbs"] // 8, dtype=np.uint8)
+    enc = orc.tb_encode(oracle, tb, 1)
+    dec = fec.PuschDecoder(tb_engine)
+    got = []
+    for t, rv in enumerate([0, 2, 3, 1]):
+        llr = orc.tb_transmit(oracle, enc, p["tbs"], 1, rv, 4, 0, 2, p["G"], -0.5, seed=300 + t)
+        out = np.zeros(p["tbs"] // 8, np.uint8)
+        cfg = fec.PuschDecoderConfiguration(base_graph=1, rv=rv, mod_order=4, nof_layers=2, new_data=(t == 0))
+        buf = dec.new_data(out, 1700, got.append, cfg)
+        buf.on_new_softbits(llr[:7000])
+        buf.on_new_softbits(llr[7000:])
+        buf.on_end_softbits()
+        assert got[-1].nof_codeblocks_total == 2
+        if got[-1].tb_crc_ok:
+            assert (out == tb).all()
+            break
+    assert got[-1].tb_crc_ok and len(got) >= 2
