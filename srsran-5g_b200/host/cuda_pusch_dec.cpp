@@ -168,6 +168,96 @@ std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> srsran::b200::create_cuda
   return std::make_shared<cuda_pusch_dec_factory>(cfg);
 }
 
+pusch_decoder_cuda::pusch_decoder_cuda(std::shared_ptr<fec_engine_handle> engine_, unsigned max_nof_softbits) :
+  engine(std::move(engine_)), softbits_cap(max_nof_softbits)
+{
+  static_assert(sizeof(log_likelihood_ratio) == 1, "LLRs are int8 on both sides of the boundary.");
+  softbits = static_cast<log_likelihood_ratio*>(fec_host_alloc(max_nof_softbits));
+  report_fatal_error_if_not(softbits != nullptr, "B200 FEC engine: cannot pin {} bytes for the codeword buffer.", max_nof_softbits);
+}
+
+pusch_decoder_cuda::~pusch_decoder_cuda()
+{
+  fec_host_free(softbits);
+}
+
+pusch_decoder_buffer& pusch_decoder_cuda::new_data(span<uint8_t>           transport_block_,
+                                                   unique_rx_buffer        rm_buffer_,
+                                                   pusch_decoder_notifier& notifier_,
+                                                   const configuration&    cfg)
+{
+  transport_block = transport_block_;
+  rm_buffer       = std::move(rm_buffer_);
+  notifier        = &notifier_;
+  current_config  = cfg;
+  softbits_count  = 0;
+  return *this;
+}
+
+span<log_likelihood_ratio> pusch_decoder_cuda::get_next_block_view(unsigned block_size)
+{
+  srsran_assert(softbits_count + block_size <= softbits_cap, "Codeword of more than {} soft bits.", softbits_cap);
+  return span<log_likelihood_ratio>(softbits + softbits_count, block_size);
+}
+
+void pusch_decoder_cuda::on_new_softbits(span<const log_likelihood_ratio> in)
+{
+  span<log_likelihood_ratio> block = get_next_block_view(in.size());
+  if (block.data() != in.data()) {
+    std::memcpy(block.data(), in.data(), in.size());
+  }
+  softbits_count += in.size();
+}
+
+void pusch_decoder_cuda::on_end_softbits()
+{
+  const unsigned nof_cbs = rm_buffer->get_nof_codeblocks();
+  srsran_assert(nof_cbs <= MAX_NOF_SEGMENTS, "Too many codeblocks.");
+  for (unsigned i = 0; i != nof_cbs; ++i) {
+    slots[i] = rm_buffer->get_absolute_codeblock_id(i);
+  }
+  fec_tb_desc tb = {};
+  tb.tbs         = static_cast<uint32_t>(transport_block.size() * 8);
+  tb.nof_llrs    = softbits_count;
+  tb.Nref        = current_config.Nref;
+  tb.slot_list   = 0;
+  tb.base_graph  = (current_config.base_graph == ldpc_base_graph_type::BG1) ? 1 : 2;
+  tb.rv          = static_cast<uint8_t>(current_config.rv);
+  tb.qm          = static_cast<uint8_t>(get_bits_per_symbol(current_config.mod));
+  tb.nof_layers  = static_cast<uint8_t>(current_config.nof_layers);
+  tb.max_iter    = static_cast<uint8_t>(current_config.nof_ldpc_iterations);
+  tb.flags       = (current_config.new_data ? FEC_FLAG_NEW_DATA : 0u) | (current_config.use_early_stop ? FEC_FLAG_EARLY_STOP : 0u);
+  fec_tb_result res = {};
+  const int     rc  = fec_tb_run_host(engine->get(), &tb, 1, slots.data(), reinterpret_cast<const int8_t*>(softbits),
+                                      softbits_count, transport_block.data(), transport_block.size(), &res, cb_results.data());
+  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+  srsran_assert(res.nof_codeblocks == nof_cbs, "Wrong number of codeblocks {} (expected {}).", nof_cbs, res.nof_codeblocks);
+
+  pusch_decoder_result stats;
+  stats.tb_crc_ok            = res.tb_crc_ok != 0;
+  stats.nof_codeblocks_total = res.nof_codeblocks;
+  stats.ldpc_decoder_stats.reset();
+  // Keep the pool's view of the codeblock CRCs in step with the engine's (the engine is authoritative).
+  span<bool> cb_crcs = rm_buffer->get_codeblocks_crc();
+  for (unsigned i = 0; i != nof_cbs; ++i) {
+    const fec_cb_result& cr = cb_results[i];
+    const bool           ok = (cr.status & FEC_RES_CRC_PASS) != 0;
+    if (!(cr.status & FEC_RES_SKIPPED)) {
+      stats.ldpc_decoder_stats.update(ok ? cr.nof_ldpc_iterations : current_config.nof_ldpc_iterations);
+    }
+    cb_crcs[i] = ok;
+  }
+  if (!stats.tb_crc_ok && res.tb_delivered) {
+    rm_buffer->reset_codeblocks_crc();
+  }
+  if (stats.tb_crc_ok) {
+    rm_buffer.release();
+  } else {
+    rm_buffer.unlock();
+  }
+  notifier->on_sch_data(stats);
+}
+
 std::optional<unsigned> ldpc_decoder_cuda::decode(bit_buffer&                      output,
                                                   span<const log_likelihood_ratio> input,
                                                   crc_calculator*                  crc,

@@ -9,6 +9,10 @@
 //   cuda_pusch_dec_factory     : hal::hw_accelerator_pusch_dec_factory
 //        include/srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec_factory.h:31-36 -- what
 //        pusch_decoder_factory_hw_configuration::hw_decoder_factory expects (.../pusch/factories.h:74-83)
+//   pusch_decoder_cuda         : pusch_decoder + pusch_decoder_buffer
+//        include/srsran/phy/upper/channel_processors/pusch/pusch_decoder.h:54-101, pusch_decoder_buffer.h:36-63 -- whole
+//        transport blocks in one engine call (segmentation, codeblock decoding, TB assembly and TB CRC on the device);
+//        takes the place of pusch_decoder_impl / pusch_decoder_hw_impl (lib/phy/upper/channel_processors/pusch/)
 //   ldpc_decoder_cuda          : ldpc_decoder        include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:37-75
 //   ldpc_rate_dematcher_cuda   : ldpc_rate_dematcher include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:35-58
 //
@@ -21,6 +25,11 @@
 #include "srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec.h"
 #include "srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec_factory.h"
 #include "srsran/phy/upper/channel_coding/crc_calculator.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_buffer.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_notifier.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_result.h"
+#include "srsran/phy/upper/unique_rx_buffer.h"
 #include "srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h"
 #include "srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h"
 #include "srsran/ran/sch/sch_constants.h"
@@ -98,6 +107,42 @@ private:
 /// The call that replaces create_bbdev_pusch_dec_acc_factory (lib/hal/phy/upper/channel_processors/pusch/
 /// hw_accelerator_factories.cpp:28-36, a stub returning nullptr in the open-source tree).
 std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> create_cuda_pusch_dec_acc_factory(const fec_engine_cfg& cfg);
+
+/// pusch_decoder over the transport-block entry point of the C ABI (fec_tb_run_host). The rx buffer only supplies the
+/// absolute codeblock identifiers (the pool must be created with external_soft_bits = true): soft bits, codeblock CRC
+/// flags and the decoded messages of earlier transmissions live in the engine. Decoding starts at on_end_softbits and
+/// is synchronous; one instance per thread, as for pusch_decoder_impl.
+class pusch_decoder_cuda : public pusch_decoder, private pusch_decoder_buffer
+{
+public:
+  /// \param max_nof_softbits capacity of the (pinned) codeword buffer, e.g. pusch_constants::get_max_codeword_size().
+  pusch_decoder_cuda(std::shared_ptr<fec_engine_handle> engine_, unsigned max_nof_softbits);
+  ~pusch_decoder_cuda() override;
+
+  // See pusch_decoder for the documentation.
+  pusch_decoder_buffer& new_data(span<uint8_t>           transport_block,
+                                 unique_rx_buffer        rm_buffer,
+                                 pusch_decoder_notifier& notifier,
+                                 const configuration&    cfg) override;
+  void                  set_nof_softbits(units::bits /*nof_softbits*/) override {}
+
+private:
+  // See pusch_decoder_buffer for the documentation.
+  span<log_likelihood_ratio> get_next_block_view(unsigned block_size) override;
+  void                       on_new_softbits(span<const log_likelihood_ratio> softbits) override;
+  void                       on_end_softbits() override;
+
+  std::shared_ptr<fec_engine_handle> engine;
+  log_likelihood_ratio*              softbits       = nullptr; // pinned
+  unsigned                           softbits_cap   = 0;
+  unsigned                           softbits_count = 0;
+  span<uint8_t>                      transport_block;
+  unique_rx_buffer                   rm_buffer;
+  pusch_decoder_notifier*            notifier = nullptr;
+  configuration                      current_config;
+  std::array<uint32_t, MAX_NOF_SEGMENTS>      slots;
+  std::array<fec_cb_result, MAX_NOF_SEGMENTS> cb_results;
+};
 
 /// ldpc_decoder over FEC_MODE_DECODE (synchronous, one codeblock). The crc pointer only selects the polynomial.
 class ldpc_decoder_cuda : public ldpc_decoder
