@@ -1,11 +1,17 @@
-// tests/cpp/dropin_pusch_decoder.cpp -- TEST INFRASTRUCTURE: drop-in acceptance of srsran::b200::pusch_decoder_cuda.
+// tests/cpp/dropin_pusch_decoder.cpp -- TEST INFRASTRUCTURE: drop-in acceptance of the reference-side adapters.
 //
-// Drives the CUDA decoder and the reference's own software decoder (pusch_decoder_impl, from oracle/_ref) side by side
-// through the reference's interfaces only -- rx_buffer_pool::reserve, pusch_decoder::new_data, pusch_decoder_buffer::
+// Three decoders run side by side on the same HARQ transmissions:
+//   (1) the reference's own software decoder, pusch_decoder_impl (from oracle/_ref) -- the expected results;
+//   (2) srsran::b200::pusch_decoder_cuda -- whole transport blocks through fec_tb_run_host;
+//   (3) the reference's UNMODIFIED hardware-accelerated consumer, pusch_decoder_hw_impl (compiled for this test from the
+//       source where it lies), driving srsran::b200::cuda_pusch_dec_accelerator instances through the HAL
+//       (hal::hw_accelerator_pusch_dec: reserve_queue / configure / enqueue / dequeue / read outputs / free HARQ entry).
+// Everything goes through the reference's interfaces only -- rx_buffer_pool::reserve, pusch_decoder::new_data, pusch_decoder_buffer::
 // on_new_softbits / on_end_softbits, pusch_decoder_notifier::on_sch_data -- over the HARQ transmissions found in the
 // input file (written by tests/test_gpu_dropin.py), and compares transport block bytes, tb_crc_ok, the number of
 // codeblocks and the LDPC iteration statistics of every transmission. Exit code 0 = identical.
 #include "cuda_pusch_dec.h"
+#include "phy/upper/channel_processors/pusch/pusch_decoder_hw_impl.h"
 #include "phy/upper/channel_processors/pusch/pusch_decoder_impl.h"
 #include "srsran/phy/upper/channel_coding/channel_coding_factories.h"
 #include "srsran/phy/upper/rx_buffer_pool.h"
@@ -45,6 +51,19 @@ std::unique_ptr<pusch_decoder> make_reference_decoder()
   make_crcs(crcs);
   return std::make_unique<pusch_decoder_impl>(create_ldpc_segmenter_rx_factory_sw()->create(), pool, std::move(crcs), nullptr,
                                               MAX_RB, 4);
+}
+
+std::unique_ptr<pusch_decoder> make_hal_decoder(std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> factory)
+{
+  auto                           crcf = create_crc_calculator_factory_sw("auto");
+  pusch_decoder_hw_impl::sch_crc crcs;
+  crcs.crc16  = crcf->create(crc_generator_poly::CRC16);
+  crcs.crc24A = crcf->create(crc_generator_poly::CRC24A);
+  crcs.crc24B = crcf->create(crc_generator_poly::CRC24B);
+  std::vector<std::unique_ptr<hal::hw_accelerator_pusch_dec>> accs;
+  accs.push_back(factory->create());
+  auto pool = std::make_shared<pusch_decoder_hw_impl::hw_decoder_pool>(std::move(accs));
+  return std::make_unique<pusch_decoder_hw_impl>(create_ldpc_segmenter_rx_factory_sw()->create(), crcs, pool, nullptr);
 }
 
 modulation_scheme mod_of(unsigned qm)
@@ -91,9 +110,12 @@ int main(int argc, char** argv)
   auto pool_ref           = create_rx_buffer_pool(pc);
   pc.external_soft_bits   = true; // soft bits stay in HBM
   auto pool_cuda          = create_rx_buffer_pool(pc);
+  auto pool_hal           = create_rx_buffer_pool(pc);
 
   std::unique_ptr<pusch_decoder> dec_ref  = make_reference_decoder();
   std::unique_ptr<pusch_decoder> dec_cuda = std::make_unique<b200::pusch_decoder_cuda>(engine, 4u * 1024 * 1024);
+  ecfg.max_batch_cbs                      = 162; // one transport block per launch
+  std::unique_ptr<pusch_decoder> dec_hal  = make_hal_decoder(b200::create_cuda_pusch_dec_acc_factory(ecfg)); // own engine
 
   uint32_t nof_blocks = 0;
   if (std::fread(&nof_blocks, 4, 1, f) != 1) {
@@ -128,8 +150,8 @@ int main(int argc, char** argv)
       cfg.nof_ldpc_iterations = 6;
       cfg.use_early_stop      = true;
       cfg.new_data            = (t == 0);
-      std::vector<uint8_t> tb_ref(tbs / 8, 0xAA), tb_cuda(tbs / 8, 0xAA);
-      capture              n_ref, n_cuda;
+      std::vector<uint8_t> tb_ref(tbs / 8, 0xAA), tb_cuda(tbs / 8, 0xAA), tb_hal(tbs / 8, 0xAA);
+      capture              n_ref, n_cuda, n_hal;
       span<const log_likelihood_ratio> soft(reinterpret_cast<const log_likelihood_ratio*>(llr.data()), G);
       slot_point slot(0, slot_count++ % 10240);
       {
@@ -156,7 +178,28 @@ int main(int argc, char** argv)
         in.on_new_softbits(view);
         in.on_end_softbits();
       }
+      {
+        unique_rx_buffer buf = pool_hal->get_pool().reserve(slot, id, ncb, cfg.new_data);
+        if (!buf.is_valid()) {
+          std::fprintf(stderr, "hal pool: reservation failed\n");
+          return 3;
+        }
+        pusch_decoder_buffer& in = dec_hal->new_data(tb_hal, std::move(buf), n_hal, cfg);
+        in.on_new_softbits(soft);
+        in.on_end_softbits();
+      }
       ++nof_tx_total;
+      const bool hal_same = n_hal.got && n_ref.r.tb_crc_ok == n_hal.r.tb_crc_ok &&
+                            n_ref.r.nof_codeblocks_total == n_hal.r.nof_codeblocks_total && tb_ref == tb_hal &&
+                            ((t != 0) || (n_ref.r.ldpc_decoder_stats.get_min() == n_hal.r.ldpc_decoder_stats.get_min() &&
+                                          n_ref.r.ldpc_decoder_stats.get_max() == n_hal.r.ldpc_decoder_stats.get_max() &&
+                                          n_ref.r.ldpc_decoder_stats.get_mean() == n_hal.r.ldpc_decoder_stats.get_mean()));
+      if (!hal_same) {
+        std::fprintf(stderr, "MISMATCH (HAL path) block %u tx %u: crc %d/%d cbs %u/%u bytes %s\n", b, t, n_ref.r.tb_crc_ok,
+                     n_hal.r.tb_crc_ok, n_ref.r.nof_codeblocks_total, n_hal.r.nof_codeblocks_total,
+                     tb_ref == tb_hal ? "same" : "differ");
+        return 1;
+      }
       const bool same = n_ref.got && n_cuda.got && n_ref.r.tb_crc_ok == n_cuda.r.tb_crc_ok &&
                         n_ref.r.nof_codeblocks_total == n_cuda.r.nof_codeblocks_total && tb_ref == tb_cuda;
       // iteration statistics are comparable when every codeblock was decoded in this transmission
