@@ -226,6 +226,21 @@ def bench_transport_block(fec, eng, torch, dev, stream, args, rank):
         lat.append((time.perf_counter() - t0) * 1e6)
     lat = np.array(lat[20:])
     r1 = res[:n_cb].copy()
+    # the same transport block through the transport-block entry point: one descriptor, segmentation in the engine,
+    # TB assembly + TB CRC on the device, the TB bytes (not 152 codeblock buffers) come back
+    tbd = fec.make_tb_descs(1)
+    tbd["tbs"], tbd["nof_llrs"], tbd["base_graph"], tbd["qm"], tbd["nof_layers"] = info_bits, int(Es.sum()), BG, qm, 4
+    tbd["max_iter"], tbd["flags"], tbd["harq_slot"] = MAX_ITER, fec.FLAG_NEW_DATA | fec.FLAG_EARLY_STOP, 0
+    # (the synthetic codeword is all-zero: a zero payload has zero CRCs, so the TB CRC passes like the codeblock CRCs)
+    t_tb = torch.zeros(info_bits // 8, dtype=torch.uint8).pin_memory()
+    tb_llr = torch.from_numpy(np.concatenate([llr[0][offs[r]:offs[r] + Es[r]] for r in range(n_cb)])).pin_memory()
+    lat_tb, tb_ok = [], 0
+    for i in range(220):
+        t0 = time.perf_counter()
+        rr_tb = eng.tb_run_host(tbd, (tb_llr.data_ptr(), tb_llr.numel()), (t_tb.data_ptr(), t_tb.numel()))
+        lat_tb.append((time.perf_counter() - t0) * 1e6)
+        tb_ok += int(rr_tb["tb_crc_ok"][0])
+    lat_tb = np.array(lat_tb[20:])
     # device-resident throughput of n_tb transport blocks per launch
     d_llr = t_llr.to(dev)
     d_descs = torch.from_numpy(d.view(np.uint8).copy()).to(dev)
@@ -252,6 +267,10 @@ def bench_transport_block(fec, eng, torch, dev, stream, args, rank):
             "tb_latency_us": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
                               "max": float(lat.max()), "samples": int(lat.size),
                               "api": "fec_run_host, 152 codeblocks per call, pinned host buffers, H2D+kernel+D2H"},
+            "tb_api_latency_us": {"p50": float(np.percentile(lat_tb, 50)), "p99": float(np.percentile(lat_tb, 99)),
+                                  "max": float(lat_tb.max()), "samples": int(lat_tb.size), "tb_crc_ok_fraction": tb_ok / 220,
+                                  "api": "fec_tb_run_host: one descriptor per transport block, segmentation in the engine, "
+                                         "codeblock kernel + TB assembly/CRC24A kernel, TB bytes back"},
             "device_resident": {"value": n_tb * info_bits / (ms * 1e-3) / 1e9, "unit": "Gbit/s", "tbs_per_launch": n_tb,
                                 "ms_per_launch": ms},
             "cb_crc_pass_fraction": float(((rr["status"] & fec.RES_CRC_PASS) != 0).mean()),

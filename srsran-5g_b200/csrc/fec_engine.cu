@@ -167,12 +167,15 @@ struct fec_engine {
   // transport-block layer (allocated on first use)
   std::atomic<uint8_t>* cb_ok    = nullptr; // per HARQ slot: the codeblock's CRC passed in an earlier transmission
   uint8_t*              d_msg    = nullptr; // per HARQ slot: decoded message of the codeblock (FEC_MAX_CB_OUT_BYTES)
-  fec_tb_job*           d_jobs   = nullptr;
-  fec_tb_cb_ref*        d_map    = nullptr;
-  fec_tb_result*        d_tbres  = nullptr;
-  fec_tb_job*           h_jobs   = nullptr; // pinned
-  fec_tb_cb_ref*        h_map    = nullptr; // pinned
-  fec_tb_result*        h_tbres  = nullptr; // pinned
+  uint8_t*              h_meta   = nullptr; // pinned: jobs | codeblock map | scratch zeros | codeblock descriptors
+  uint8_t*              d_meta   = nullptr;
+  uint8_t*              h_rblk   = nullptr; // pinned: codeblock results | transport block results
+  uint8_t*              d_rblk   = nullptr;
+  uint8_t*              h_tbout  = nullptr; // pinned bounce buffer for the transport block bytes
+  std::vector<fec_tb_geometry> tb_geo;
+  // weights of the last transport-block geometry seen (the same allocation usually repeats slot after slot)
+  uint32_t              wc_key[3] = {0, 0, 0}; // nof_cbs, data_bits, stream_bits
+  std::vector<uint32_t> wc_weights;
 };
 
 namespace {
@@ -435,12 +438,11 @@ void fec_engine_destroy(fec_engine* e)
   delete[] e->fresh;
   delete[] e->cb_ok;
   cudaFree(e->d_msg);
-  cudaFree(e->d_jobs);
-  cudaFree(e->d_map);
-  cudaFree(e->d_tbres);
-  cudaFreeHost(e->h_jobs);
-  cudaFreeHost(e->h_map);
-  cudaFreeHost(e->h_tbres);
+  cudaFree(e->d_meta);
+  cudaFree(e->d_rblk);
+  cudaFreeHost(e->h_meta);
+  cudaFreeHost(e->h_rblk);
+  cudaFreeHost(e->h_tbout);
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
   if (e->stream) {
@@ -926,12 +928,13 @@ int tb_state_alloc(fec_engine* e)
   }
   const uint32_t nc = e->cfg.max_batch_cbs;
   CU_TRY(cudaSetDevice(e->cfg.device));
-  CU_TRY(cudaMalloc((void**)&e->d_jobs, nc * sizeof(fec_tb_job)));
-  CU_TRY(cudaMalloc((void**)&e->d_map, nc * sizeof(fec_tb_cb_ref)));
-  CU_TRY(cudaMalloc((void**)&e->d_tbres, nc * sizeof(fec_tb_result)));
-  CU_TRY(cudaHostAlloc((void**)&e->h_jobs, nc * sizeof(fec_tb_job), cudaHostAllocDefault));
-  CU_TRY(cudaHostAlloc((void**)&e->h_map, nc * sizeof(fec_tb_cb_ref), cudaHostAllocDefault));
-  CU_TRY(cudaHostAlloc((void**)&e->h_tbres, nc * sizeof(fec_tb_result), cudaHostAllocDefault));
+  const size_t meta = (size_t)nc * (sizeof(fec_tb_job) + sizeof(fec_tb_cb_ref) + 8 + sizeof(fec_cb_desc)) + 64;
+  const size_t rblk = (size_t)nc * (sizeof(fec_cb_result) + sizeof(fec_tb_result)) + 64;
+  CU_TRY(cudaMalloc((void**)&e->d_meta, meta));
+  CU_TRY(cudaMalloc((void**)&e->d_rblk, rblk));
+  CU_TRY(cudaHostAlloc((void**)&e->h_meta, meta, cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&e->h_rblk, rblk, cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&e->h_tbout, (size_t)nc * FEC_MAX_CB_OUT_BYTES, cudaHostAllocDefault));
   e->cb_ok = new (std::nothrow) std::atomic<uint8_t>[e->cfg.harq_slots];
   for (uint32_t i = 0; i < e->cfg.harq_slots; ++i) {
     e->cb_ok[i].store(0);
@@ -1033,14 +1036,14 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
   if (rc != FEC_OK) {
     return rc;
   }
-  // Pass 1: segmentation; descriptors of the codeblocks that still need decoding, the codeblock map, the jobs.
-  uint32_t n_dec = 0, n_map = 0, max_Z = 0;
+  // Pass 0: geometry of every block, so that the sizes of everything that follows are known.
+  e->tb_geo.resize(n);
+  uint32_t n_map = 0, max_Z = 0;
   int      any1  = 0;
-  size_t   l0 = ~(size_t)0, l1 = 0;
-  std::vector<uint32_t> first_map(n);
+  bool     aligned = true; // every payload is whole bytes: the one-CTA-per-codeblock gather applies
   for (uint32_t t = 0; t < n; ++t) {
     const fec_tb_desc& tb = tbs[t];
-    fec_tb_geometry    g;
+    fec_tb_geometry&   g  = e->tb_geo[t];
     if (!fec_tb_geometry_of(tb, g)) {
       return fail(FEC_ERR_BAD_ARG, "transport block %u: tbs=%u bg=%u rv=%u qm=%u layers=%u llrs=%u", t, tb.tbs,
                   tb.base_graph, tb.rv, tb.qm, tb.nof_layers, tb.nof_llrs);
@@ -1049,31 +1052,67 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
         tb.out_offset + tb.tbs / 8 > (size_t)e->cfg.max_batch_cbs * FEC_MAX_CB_OUT_BYTES) {
       return fail(FEC_ERR_BAD_ARG, "transport block %u indexes outside the batch buffers", t);
     }
-    if (n_map + g.nof_cbs > e->cfg.max_batch_cbs) {
-      return fail(FEC_ERR_BAD_ARG, "more than %u codeblocks in one call", e->cfg.max_batch_cbs);
+    n_map += g.nof_cbs;
+    aligned = aligned && (g.data_bits % 8 == 0);
+    max_Z   = g.lifting_size > max_Z ? g.lifting_size : max_Z;
+    any1 |= (tb.base_graph == 1);
+  }
+  if (n_map > e->cfg.max_batch_cbs) {
+    return fail(FEC_ERR_BAD_ARG, "%u codeblocks in one call, the engine takes %u", n_map, e->cfg.max_batch_cbs);
+  }
+  // One pinned block travels to the device in one copy: jobs | codeblock map | scratch (zeros) | codeblock descriptors.
+  auto           up16      = [](size_t x) { return (x + 15) & ~(size_t)15; };
+  const size_t   off_map   = up16((size_t)n * sizeof(fec_tb_job));
+  const size_t   off_scr   = up16(off_map + (size_t)n_map * sizeof(fec_tb_cb_ref));
+  const size_t   off_descs = up16(off_scr + (size_t)n * 2 * sizeof(uint32_t));
+  const size_t   meta_size = off_descs + (size_t)n_map * sizeof(fec_cb_desc);
+  fec_tb_job*    h_jobs    = reinterpret_cast<fec_tb_job*>(e->h_meta);
+  fec_tb_cb_ref* h_map     = reinterpret_cast<fec_tb_cb_ref*>(e->h_meta + off_map);
+  fec_cb_desc*   h_descs   = reinterpret_cast<fec_cb_desc*>(e->h_meta + off_descs);
+  memset(e->h_meta + off_scr, 0, (size_t)n * 2 * sizeof(uint32_t));
+  // Pass 1: segmentation -- one descriptor per codeblock, the codeblock map, the jobs.
+  size_t   l0 = ~(size_t)0, l1 = 0;
+  uint32_t m = 0;
+  for (uint32_t t = 0; t < n; ++t) {
+    const fec_tb_desc&     tb = tbs[t];
+    const fec_tb_geometry& g  = e->tb_geo[t];
+    fec_tb_job&            J  = h_jobs[t];
+    J.out_offset              = tb.out_offset;
+    J.nof_cbs                 = g.nof_cbs;
+    J.data_bits               = g.data_bits;
+    J.stream_bits             = g.stream_bits;
+    J.tbs_bytes               = tb.tbs / 8;
+    J.map_first               = m;
+    J.max_iter                = tb.max_iter;
+    if (g.data_bits % 8 == 0 && g.nof_cbs > 1 &&
+        (e->wc_key[0] != g.nof_cbs || e->wc_key[1] != g.data_bits || e->wc_key[2] != g.stream_bits)) {
+      // weight of codeblock r = x^(8 * stream bytes after its payload) mod g24A, built backwards with one multiply each
+      e->wc_key[0] = g.nof_cbs;
+      e->wc_key[1] = g.data_bits;
+      e->wc_key[2] = g.stream_bits;
+      e->wc_weights.assign(g.nof_cbs, 1u);
+      const uint32_t dbytes = g.data_bits / 8, last = g.stream_bits / 8 - (g.nof_cbs - 1) * dbytes;
+      uint32_t       w      = fec_tb_crc24a_xpow8_host(last); // after codeblock C-2 comes the last payload
+      const uint32_t step   = fec_tb_crc24a_xpow8_host(dbytes);
+      for (int r = (int)g.nof_cbs - 2; r >= 0; --r) {
+        e->wc_weights[r] = w;
+        w                = fec_tb_crc24a_mulmod_host(w, step);
+      }
     }
-    first_map[t]   = n_map;
-    fec_tb_job& J  = e->h_jobs[t];
-    J.out_offset   = tb.out_offset;
-    J.nof_cbs      = g.nof_cbs;
-    J.data_bits    = g.data_bits;
-    J.stream_bits  = g.stream_bits;
-    J.tbs_bytes    = tb.tbs / 8;
-    J.map_first    = n_map;
-    J.max_iter     = tb.max_iter;
     uint32_t cw_off = 0;
-    for (uint32_t r = 0; r < g.nof_cbs; ++r) {
+    for (uint32_t r = 0; r < g.nof_cbs; ++r, ++m) {
       const uint32_t slot = tb_slot_of(tb, slots, r);
       if (slot >= e->cfg.harq_slots) {
         return fail(FEC_ERR_BAD_ARG, "transport block %u codeblock %u: harq slot %u >= %u", t, r, slot, e->cfg.harq_slots);
       }
       if (tb.flags & FEC_FLAG_NEW_DATA) {
-        e->cb_ok[slot].store(0); // pusch_decoder_hw_impl.cpp:193-196
+        e->cb_ok[slot].store(0); // pusch_decoder_impl.cpp:124-128
       }
-      fec_tb_cb_ref& ref = e->h_map[n_map++];
+      fec_tb_cb_ref& ref = h_map[m];
       ref.slot           = slot;
-      const uint32_t E   = fec_tb_rm_length(tb, g, r);
-      fec_cb_desc&   d   = e->h_descs_pin[n_dec];
+      ref.tb             = t;
+      ref.weight         = (g.data_bits % 8 == 0 && g.nof_cbs > 1) ? e->wc_weights[r] : 1u;
+      fec_cb_desc& d     = h_descs[m];
       tb_cb_desc(tb, g, r, cw_off, slot, d);
       // A codeblock whose CRC passed in an earlier transmission is not decoded again, but the new LLRs are still
       // combined into its soft buffer: the transport-block CRC may yet fail and put it back in play
@@ -1087,64 +1126,68 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
         return rc;
       }
       apply_fresh(e, d);
-      ref.result_index = already_ok ? -1 : (int32_t)n_dec;
-      ++n_dec;
-      l0 = d.llr_offset < l0 ? (size_t)d.llr_offset : l0;
-      l1 = d.llr_offset + d.E > l1 ? (size_t)(d.llr_offset + d.E) : l1;
-      cw_off += E;
+      ref.result_index = already_ok ? -1 : (int32_t)m;
+      l0               = d.llr_offset < l0 ? (size_t)d.llr_offset : l0;
+      l1               = d.llr_offset + d.E > l1 ? (size_t)(d.llr_offset + d.E) : l1;
+      cw_off += d.E;
     }
     if (cw_off != tb.nof_llrs) {
       return fail(FEC_ERR_BAD_ARG, "transport block %u: rate-matched lengths sum to %u, codeword has %u LLRs", t, cw_off,
                   tb.nof_llrs);
     }
-    max_Z = g.lifting_size > max_Z ? g.lifting_size : max_Z;
-    any1 |= (tb.base_graph == 1);
   }
-  if (n_dec && l1 - l0 > e->cfg.max_batch_llrs) {
+  if (l1 - l0 > e->cfg.max_batch_llrs) {
     return fail(FEC_ERR_BAD_ARG, "%zu LLR bytes exceed the engine staging capacity", l1 - l0);
   }
+  for (uint32_t i = 0; i < n_map; ++i) {
+    h_descs[i].llr_offset -= l0; // the staged LLRs start at l0
+  }
   CU_TRY(cudaSetDevice(e->cfg.device));
-  cudaStream_t st = e->stream;
-  if (n_dec) {
-    // Staged LLRs start at l0: rebase the descriptors.
-    for (uint32_t i = 0; i < n_dec; ++i) {
-      e->h_descs_pin[i].llr_offset -= l0;
-    }
-    CU_TRY(cudaMemcpyAsync(e->d_descs, e->h_descs_pin, n_dec * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, st));
-    CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+  cudaStream_t         st      = e->stream;
+  const fec_tb_job*    d_jobs  = reinterpret_cast<const fec_tb_job*>(e->d_meta);
+  const fec_tb_cb_ref* d_map   = reinterpret_cast<const fec_tb_cb_ref*>(e->d_meta + off_map);
+  uint32_t*            d_scr   = reinterpret_cast<uint32_t*>(e->d_meta + off_scr);
+  const fec_cb_desc*   d_descs = reinterpret_cast<const fec_cb_desc*>(e->d_meta + off_descs);
+  // results come back in one copy too: codeblock results | transport block results
+  const size_t   off_tbres = up16((size_t)n_map * sizeof(fec_cb_result));
+  fec_cb_result* d_cbres   = reinterpret_cast<fec_cb_result*>(e->d_rblk);
+  fec_tb_result* d_tbres   = reinterpret_cast<fec_tb_result*>(e->d_rblk + off_tbres);
+  CU_TRY(cudaMemcpyAsync(e->d_meta, e->h_meta, meta_size, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+  rc = launch(e, st, d_descs, n_map, e->d_llr, e->d_msg, d_cbres, max_Z, any1);
+  if (rc != FEC_OK) {
+    return rc;
   }
-  CU_TRY(cudaMemcpyAsync(e->d_jobs, e->h_jobs, n * sizeof(fec_tb_job), cudaMemcpyHostToDevice, st));
-  CU_TRY(cudaMemcpyAsync(e->d_map, e->h_map, n_map * sizeof(fec_tb_cb_ref), cudaMemcpyHostToDevice, st));
-  if (n_dec) {
-    rc = launch(e, st, e->d_descs, n_dec, e->d_llr, e->d_msg, e->d_res, max_Z, any1);
-    if (rc != FEC_OK) {
-      return rc;
-    }
-    CU_TRY(cudaMemcpyAsync(e->h_res_pin, e->d_res, n_dec * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st));
+  if (aligned) {
+    fec_tb_gather_kernel<<<n_map, 256, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres, d_scr, e->d_tab);
+  } else {
+    fec_tb_assemble_kernel<<<n, 1024, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres);
   }
-  fec_tb_assemble_kernel<<<n, 1024, 0, st>>>(e->d_jobs, e->d_map, e->d_res, e->d_msg, e->d_out, e->d_tbres);
   CU_TRY(cudaGetLastError());
   e->launches.fetch_add(1);
-  CU_TRY(cudaMemcpyAsync(e->h_tbres, e->d_tbres, n * sizeof(fec_tb_result), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaMemcpyAsync(e->h_rblk, e->d_rblk, off_tbres + (size_t)n * sizeof(fec_tb_result), cudaMemcpyDeviceToHost, st));
+  // The transport block bytes come back unconditionally into a pinned bounce buffer (a block that is not delivered must
+  // leave the caller's buffer untouched, and waiting for the results first would cost a second round trip).
+  for (uint32_t t = 0; t < n; ++t) {
+    CU_TRY(cudaMemcpyAsync(e->h_tbout + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8,
+                           cudaMemcpyDeviceToHost, st));
+  }
   CU_TRY(cudaStreamSynchronize(st));
   // Pass 2: deliver the transport blocks whose codeblocks are all good, update the per-codeblock state.
-  bool any_delivered = false;
+  const fec_cb_result* h_cbres = reinterpret_cast<const fec_cb_result*>(e->h_rblk);
+  const fec_tb_result* h_tbres = reinterpret_cast<const fec_tb_result*>(e->h_rblk + off_tbres);
   for (uint32_t t = 0; t < n; ++t) {
-    const fec_tb_result& R = e->h_tbres[t];
-    if (R.tb_delivered) {
-      CU_TRY(cudaMemcpyAsync(h_out + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8, cudaMemcpyDeviceToHost, st));
-      any_delivered = true;
-    }
-  }
-  for (uint32_t t = 0; t < n; ++t) {
-    const fec_tb_result& R = e->h_tbres[t];
-    const fec_tb_job&    J = e->h_jobs[t];
+    const fec_tb_result& R = h_tbres[t];
+    const fec_tb_job&    J = h_jobs[t];
     h_results[t]           = R;
+    if (R.tb_delivered) {
+      memcpy(h_out + tbs[t].out_offset, e->h_tbout + tbs[t].out_offset, tbs[t].tbs / 8);
+    }
     for (uint32_t r = 0; r < J.nof_cbs; ++r) {
-      const fec_tb_cb_ref& ref = e->h_map[J.map_first + r];
+      const fec_tb_cb_ref& ref = h_map[J.map_first + r];
       fec_cb_result        cr;
       if (ref.result_index >= 0) {
-        cr = e->h_res_pin[ref.result_index];
+        cr = h_cbres[ref.result_index];
         if (cr.status & FEC_RES_CRC_PASS) {
           e->cb_ok[ref.slot].store(1);
         }
@@ -1159,21 +1202,18 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
       }
     }
     if (R.tb_crc_ok) {
-      // copy_tb_and_notify: free the HARQ context entries, release the buffer.
+      // join_and_notify: the buffer is released -> free the HARQ context entries.
       for (uint32_t r = 0; r < J.nof_cbs; ++r) {
-        const uint32_t slot = e->h_map[J.map_first + r].slot;
+        const uint32_t slot = h_map[J.map_first + r].slot;
         e->fresh[slot].store(1);
         e->cb_ok[slot].store(0);
       }
     } else if (R.tb_delivered) {
       // All codeblock CRCs good but the TB CRC is not: at least one false positive, start over (reset_codeblocks_crc).
       for (uint32_t r = 0; r < J.nof_cbs; ++r) {
-        e->cb_ok[e->h_map[J.map_first + r].slot].store(0);
+        e->cb_ok[h_map[J.map_first + r].slot].store(0);
       }
     }
-  }
-  if (any_delivered) {
-    CU_TRY(cudaStreamSynchronize(st));
   }
   return FEC_OK;
 }

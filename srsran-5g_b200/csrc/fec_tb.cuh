@@ -96,7 +96,36 @@ struct fec_tb_job {
 struct fec_tb_cb_ref {
   uint32_t slot;         // message store slot (= HARQ slot)
   int32_t  result_index; // index into the results of this launch, or -1: CRC passed in an earlier transmission
+  uint32_t tb;           // index of the transport block (job) this codeblock belongs to
+  uint32_t weight;       // x^(8 * stream bytes after this codeblock) mod g24A (byte-aligned payloads only)
 };
+
+// Host side of the weights: (a * b) mod g24A.
+static inline uint32_t fec_tb_crc24a_mulmod_host(uint32_t a, uint32_t b)
+{
+  uint32_t acc = 0;
+  for (int i = 0; i < 24; ++i) {
+    acc ^= (b & 1u) ? a : 0u;
+    b >>= 1;
+    a <<= 1;
+    a = (a & (1u << 24)) ? (a ^ 0x1864CFBu) : a;
+  }
+  return acc;
+}
+
+// x^(8 n) mod g24A by square and multiply.
+static inline uint32_t fec_tb_crc24a_xpow8_host(uint32_t n)
+{
+  uint32_t w = 1, base = 0x100;
+  while (n != 0) {
+    if (n & 1u) {
+      w = fec_tb_crc24a_mulmod_host(w, base);
+    }
+    base = fec_tb_crc24a_mulmod_host(base, base);
+    n >>= 1;
+  }
+  return w;
+}
 
 // 8 bits of the stream starting at bit b (b + 8 <= stream_bits not required: bits past the end read as zero).
 __device__ __forceinline__ uint32_t fec_tb_stream_byte(const uint8_t* __restrict__ msg_store, const fec_tb_cb_ref* __restrict__ map,
@@ -252,5 +281,109 @@ __global__ void __launch_bounds__(1024) fec_tb_assemble_kernel(const fec_tb_job*
     R.iter_min       = (uint16_t)(s_stats[1] ? s_min : 0);
     R.iter_max       = (uint16_t)s_max;
     tb_results[blockIdx.x] = R;
+  }
+}
+
+// Byte-aligned payloads (every TBS of TS 38.214): ONE CTA PER CODEBLOCK copies its payload into the transport block and
+// folds the payload's CRC24A remainder, weighted by its position, into a per-block accumulator; the last CTA of a block
+// to finish writes the result record. scratch: 2 words per transport block {accumulator, arrival counter}, zeroed by the
+// caller before the launch.
+__global__ void __launch_bounds__(256) fec_tb_gather_kernel(const fec_tb_job* __restrict__ jobs,
+                                                           const fec_tb_cb_ref* __restrict__ map,
+                                                           const fec_cb_result* __restrict__ cb_results,
+                                                           const uint8_t* __restrict__ msg_store,
+                                                           uint8_t* __restrict__ out_base,
+                                                           fec_tb_result* __restrict__ tb_results,
+                                                           uint32_t* __restrict__ scratch,
+                                                           const fec_dev_tables* __restrict__ tab)
+{
+  __shared__ uint32_t red[8];
+  __shared__ uint32_t s_stats[3]; // ok count, decoded count, iteration sum
+  __shared__ uint32_t s_min, s_max, s_last;
+  const fec_tb_cb_ref me  = map[blockIdx.x];
+  const fec_tb_job    J   = jobs[me.tb];
+  const uint32_t      r   = blockIdx.x - J.map_first;
+  const uint32_t      tid = threadIdx.x;
+  if (tid < 3) {
+    s_stats[tid] = 0;
+  }
+  if (tid == 0) {
+    s_min = 0xffffffffu;
+    s_max = 0;
+  }
+  __syncthreads();
+  for (uint32_t i = tid; i < J.nof_cbs; i += blockDim.x) {
+    const fec_tb_cb_ref ref = map[J.map_first + i];
+    bool                ok  = true;
+    if (ref.result_index >= 0) {
+      const fec_cb_result cr = cb_results[ref.result_index];
+      ok                     = (cr.status & FEC_RES_CRC_PASS) != 0;
+      const uint32_t it      = ok ? cr.nof_ldpc_iterations : J.max_iter;
+      atomicAdd(&s_stats[1], 1u);
+      atomicAdd(&s_stats[2], it);
+      atomicMin(&s_min, it);
+      atomicMax(&s_max, it);
+    }
+    if (ok) {
+      atomicAdd(&s_stats[0], 1u);
+    }
+  }
+  __syncthreads();
+  const bool all_ok = (s_stats[0] == J.nof_cbs);
+  uint32_t   acc    = 0;
+  if (all_ok) {
+    const uint32_t dbytes = J.data_bits / 8, nstream = J.stream_bits / 8;
+    const uint32_t first  = r * dbytes;                                   // stream position of this payload
+    const uint32_t nb     = min(dbytes, nstream - first);                 // the last codeblock contributes what is left
+    const uint8_t* m      = msg_store + (size_t)me.slot * FEC_MAX_CB_OUT_BYTES;
+    uint8_t*       out    = out_base + J.out_offset;
+    const uint32_t poly   = 0x1864CFBu, top = 1u << 24;
+    for (uint32_t i = tid; i < nb; i += blockDim.x) {
+      const uint32_t v = m[i];
+      if (first + i < J.tbs_bytes) {
+        out[first + i] = (uint8_t)v;
+      }
+      if (J.nof_cbs > 1) {
+        uint32_t a = tab->crc_x8[FEC_CRC24A][nb - 1 - i];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          acc ^= ((v >> s) & 1u) ? a : 0u;
+          a = fec_crc_shift1(a, poly, top);
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
+    }
+    if ((tid & 31) == 0) {
+      red[tid >> 5] = acc;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    if (all_ok && J.nof_cbs > 1) {
+      uint32_t rem = 0;
+      for (uint32_t i = 0; i < (blockDim.x >> 5); ++i) {
+        rem ^= red[i];
+      }
+      atomicXor(&scratch[2 * me.tb], fec_crc24a_mulmod(rem, me.weight));
+    }
+    __threadfence();
+    s_last = (atomicAdd(&scratch[2 * me.tb + 1], 1u) == J.nof_cbs - 1) ? 1u : 0u;
+    if (s_last) {
+      __threadfence();
+      const uint32_t total = atomicXor(&scratch[2 * me.tb], 0u);
+      fec_tb_result  R;
+      R.nof_codeblocks = (uint16_t)J.nof_cbs;
+      R.nof_cb_decoded = (uint16_t)s_stats[1];
+      R.nof_cb_crc_ok  = (uint16_t)s_stats[0];
+      R.tb_crc_ok      = (all_ok && total == 0) ? 1 : 0;
+      R.tb_delivered   = all_ok ? 1 : 0;
+      R.iter_sum       = s_stats[2];
+      R.iter_min       = (uint16_t)(s_stats[1] ? s_min : 0);
+      R.iter_max       = (uint16_t)s_max;
+      tb_results[me.tb] = R;
+    }
   }
 }
