@@ -297,6 +297,44 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   }
 }
 
+// One decoder iteration over the layers in use. Out of line on purpose: ptxas allocates registers for the row code on its
+// own, so changes to the dematcher or the tail cannot perturb the schedule of the hot loop (and vice versa).
+__device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
+                                                  uint32_t*              state,
+                                                  const fec_packed_edge* edges,
+                                                  const uint16_t*        soff,
+                                                  const uint16_t*        rs,
+                                                  const uint8_t*         deg,
+                                                  uint32_t               H,
+                                                  uint32_t               nlayers,
+                                                  uint32_t               smul,
+                                                  uint32_t               sadd)
+{
+  const uint32_t tid = threadIdx.x;
+  for (uint32_t l = 0; l < nlayers; ++l) {
+    if ((tid & ~31u) >= H) {
+      asm volatile("bar.sync 0;" ::: "memory"); // warps without work still take part in the row barrier
+    } else {
+      // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores) so that
+      // whole warps reach the barrier inside the row function.
+      const uint32_t         tq = min(tid, H - 1);
+      uint32_t*              st = state + (uint32_t)soff[l] * H + tq;
+      const fec_packed_edge* ed = edges + rs[l];
+      switch (deg[l]) {
+        case 3: fec_packed_row<3>(soft_s, st, ed, H, tq, smul, sadd); break;
+        case 4: fec_packed_row<4>(soft_s, st, ed, H, tq, smul, sadd); break;
+        case 5: fec_packed_row<5>(soft_s, st, ed, H, tq, smul, sadd); break;
+        case 6: fec_packed_row<6>(soft_s, st, ed, H, tq, smul, sadd); break;
+        case 7: fec_packed_row<7>(soft_s, st, ed, H, tq, smul, sadd); break;
+        case 8: fec_packed_row<8>(soft_s, st, ed, H, tq, smul, sadd); break;
+        case 9: fec_packed_row<9>(soft_s, st, ed, H, tq, smul, sadd); break;
+        case 10: fec_packed_row<10>(soft_s, st, ed, H, tq, smul, sadd); break;
+        default: fec_packed_row<19>(soft_s, st, ed, H, tq, smul, sadd); break;
+      }
+    }
+  }
+}
+
 // Byte address of variable j (0 <= j < Z) of column col in the interleaved soft layout.
 __device__ __forceinline__ uint32_t fec_packed_soft_addr(uint32_t col, uint32_t j, uint32_t Z, uint32_t H)
 {
@@ -881,28 +919,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
-    for (uint32_t l = 0; l < nlayers; ++l) {
-      if ((tid & ~31u) >= H) {
-        asm volatile("bar.sync 0;" ::: "memory"); // warps without work still take part in the row barrier
-      } else {
-        // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores) so that
-        // whole warps reach the barrier inside the row function.
-        const uint32_t         tq = min(tid, H - 1);
-        uint32_t*              st = state + (uint32_t)soff[l] * H + tq;
-        const fec_packed_edge* ed = edges + rs[l];
-        switch (deg[l]) {
-          case 3: fec_packed_row<3>(soft_s, st, ed, H, tq, smul, sadd); break;
-          case 4: fec_packed_row<4>(soft_s, st, ed, H, tq, smul, sadd); break;
-          case 5: fec_packed_row<5>(soft_s, st, ed, H, tq, smul, sadd); break;
-          case 6: fec_packed_row<6>(soft_s, st, ed, H, tq, smul, sadd); break;
-          case 7: fec_packed_row<7>(soft_s, st, ed, H, tq, smul, sadd); break;
-          case 8: fec_packed_row<8>(soft_s, st, ed, H, tq, smul, sadd); break;
-          case 9: fec_packed_row<9>(soft_s, st, ed, H, tq, smul, sadd); break;
-          case 10: fec_packed_row<10>(soft_s, st, ed, H, tq, smul, sadd); break;
-          default: fec_packed_row<19>(soft_s, st, ed, H, tq, smul, sadd); break;
-        }
-      }
-    }
+    fec_packed_iteration(soft_s, state, edges, soff, rs, deg, H, nlayers, smul, sadd);
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     if (early_stop) {
       const bool clean = fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
