@@ -15,7 +15,10 @@
 #include "phy/upper/channel_processors/pusch/pusch_decoder_impl.h"
 #include "srsran/phy/upper/channel_coding/channel_coding_factories.h"
 #include "srsran/phy/upper/rx_buffer_pool.h"
+#include <algorithm>
+#include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -121,6 +124,7 @@ int main(int argc, char** argv)
   if (std::fread(&nof_blocks, 4, 1, f) != 1) {
     return 2;
   }
+  const unsigned nof_timed = (argc > 2) ? std::atoi(argv[2]) : 0; // latency mode: repeat block 0 / transmission 0
   unsigned slot_count = 0, nof_tx_total = 0, nof_bad_tx = 0;
   for (uint32_t b = 0; b != nof_blocks; ++b) {
     uint32_t h[6]; // tbs, bg, qm, nof_layers, G, nof_tx
@@ -216,6 +220,41 @@ int main(int argc, char** argv)
       }
       nof_bad_tx += n_ref.r.tb_crc_ok ? 0 : 1;
       done = n_ref.r.tb_crc_ok;
+      if (nof_timed != 0 && b == 0 && t == 0) {
+        // Latency of one transport block (new data every time) through the reference's interfaces, call to notification.
+        auto timed = [&](pusch_decoder& dec, rx_buffer_pool_controller& pool, std::vector<uint8_t>& tb, const char* name,
+                         unsigned reps) {
+          std::vector<double> us;
+          for (unsigned i = 0; i != reps; ++i) {
+            capture          n;
+            slot_point       sl(0, slot_count++ % 10240);
+            unique_rx_buffer buf = pool.get_pool().reserve(sl, id, ncb, true);
+            if (!buf.is_valid()) {
+              std::fprintf(stderr, "%s: reservation failed in the timed loop\n", name);
+              return;
+            }
+            // The UL-SCH demultiplexer writes straight into the decoder's buffer (get_next_block_view); the clock starts
+            // when the soft bits are there.
+            pusch_decoder_buffer&      in   = dec.new_data(tb, std::move(buf), n, cfg);
+            span<log_likelihood_ratio> view = in.get_next_block_view(G);
+            std::memcpy(view.data(), soft.data(), G);
+            auto t0 = std::chrono::steady_clock::now();
+            in.on_new_softbits(view);
+            in.on_end_softbits();
+            us.push_back(std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count());
+            if (!n.got || !n.r.tb_crc_ok) {
+              std::fprintf(stderr, "%s: timed transmission failed\n", name);
+              return;
+            }
+          }
+          std::sort(us.begin(), us.end());
+          std::printf("LATENCY %s tbs=%u codeblocks=%u reps=%u p50_us=%.1f p99_us=%.1f max_us=%.1f\n", name, tbs, ncb, reps,
+                      us[us.size() / 2], us[std::min<size_t>(us.size() - 1, us.size() * 99 / 100)], us.back());
+        };
+        timed(*dec_cuda, *pool_cuda, tb_cuda, "pusch_decoder_cuda", nof_timed);
+        timed(*dec_hal, *pool_hal, tb_hal, "pusch_decoder_hw_impl+cuda_hal", nof_timed);
+        timed(*dec_ref, *pool_ref, tb_ref, "pusch_decoder_impl(cpu,1thread)", std::max(3u, nof_timed / 20));
+      }
     }
   }
   std::fclose(f);

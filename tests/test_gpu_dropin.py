@@ -37,8 +37,9 @@ def test_pusch_decoder_cuda_is_a_drop_in(orc, oracle, tmp_path):
             for rv, llr in txs:
                 f.write(struct.pack("<I", rv))
                 f.write(llr.tobytes())
-    r = subprocess.run([BIN, str(path)], capture_output=True, text=True, timeout=600)
+    r = subprocess.run([BIN, str(path), "100"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
-    assert r.stdout.startswith("OK blocks=8"), r.stdout
+    print(r.stdout)
+    assert "OK blocks=8" in r.stdout and r.stdout.count("LATENCY") == 3, r.stdout
     failed = int(r.stdout.split("failed_transmissions=")[1])
     assert failed >= 2, r.stdout  # the retransmission path was exercised
