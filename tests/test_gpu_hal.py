@@ -147,3 +147,71 @@ def test_full_size_batch_properties(fec, oracle, orc):
             assert (eng.harq_read(i, N) == soft).all()
     finally:
         eng.close()
+
+
+def test_hal_concurrent_instances(fec, oracle, orc):
+    """Four accelerator instances (one per thread, each with its own engine queue) share one engine and decode different
+    transport blocks at the same time, while a fifth thread runs fec_run_host batches: every result matches the oracle."""
+    import threading
+    eng = fec.FecEngine(device=0, harq_slots=256, max_batch_cbs=16, nof_queues=4)
+    try:
+        bg, Z, qm, n_cb, n_thr, n_rounds = 1, 96, 4, 10, 4, 3
+        K, N = cases.dims(bg, Z)
+        E = (K + 8 * Z) // qm * qm
+        work = {}
+        for th in range(n_thr + 1):
+            for rnd in range(n_rounds):
+                items = []
+                for i in range(n_cb):
+                    llr, _ = oracle.make_case(bg, Z, E, 0, qm, 0, 0, orc.CRC24B, -1.0 + 0.6 * i, seed=5000 + th * 100 + rnd * 10 + i)
+                    items.append((llr, oracle.cb_chain(bg, Z, np.zeros(N, np.int8), llr, True, 0, qm, 0, 0, orc.CRC24B, 6, True)))
+                work[th, rnd] = items
+        errors = []
+
+        def hal_worker(th):
+            try:
+                acc = fec.HwAcceleratorPuschDec(eng)
+                for rnd in range(n_rounds):
+                    items = work[th, rnd]
+                    cfgs = [fec.HwPuschDecoderConfiguration(
+                        base_graph_index=bg, modulation=qm, nof_segments=n_cb, rv=0, cw_length=E, lifting_size=Z, Ncb=N,
+                        nof_filler_bits=0, max_nof_ldpc_iterations=6, use_early_stop=True, new_data=True, cb_crc_len=24,
+                        cb_crc_type=fec.CRC24B, absolute_cb_id=th * 40 + i) for i in range(n_cb)]
+                    outs, results = _decode_tb_through_hal(fec, acc, cfgs, [x[0] for x in items], K)
+                    for i, (_, (it, ref_out)) in enumerate(items):
+                        if results[i].CRC_pass != (it > 0) or (it > 0 and results[i].nof_ldpc_iterations != it) or \
+                                not (outs[i] == ref_out).all():
+                            errors.append((th, rnd, i))
+            except Exception as ex:  # noqa: BLE001
+                errors.append((th, repr(ex)))
+
+        def batch_worker(th):
+            try:
+                for rnd in range(n_rounds):
+                    items = work[th, rnd]
+                    d = fec.make_descs(n_cb)
+                    d["base_graph"], d["lifting_size"], d["qm"], d["E"] = bg, Z, qm, E
+                    d["crc_type"], d["max_iter"], d["mode"] = fec.CRC24B, 6, fec.MODE_CHAIN
+                    d["flags"] = fec.FLAG_NEW_DATA | fec.FLAG_EARLY_STOP
+                    d["harq_slot"] = th * 40 + np.arange(n_cb)
+                    d["llr_offset"] = np.arange(n_cb, dtype=np.uint64) * E
+                    d["out_offset"] = np.arange(n_cb) * (K // 8)
+                    out = np.zeros((n_cb, K // 8), np.uint8)
+                    res = eng.run_host(d, np.stack([x[0] for x in items]), out)
+                    for i, (_, (it, ref_out)) in enumerate(items):
+                        ok = bool(res["status"][i] & fec.RES_CRC_PASS)
+                        if ok != (it > 0) or not (out[i] == ref_out).all():
+                            errors.append((th, rnd, i))
+            except Exception as ex:  # noqa: BLE001
+                errors.append((th, repr(ex)))
+
+        threads = [threading.Thread(target=hal_worker, args=(t,)) for t in range(n_thr)]
+        threads.append(threading.Thread(target=batch_worker, args=(n_thr,)))
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=120)
+        assert not any(t.is_alive() for t in threads), "a worker hung"
+        assert not errors, errors[:5]
+    finally:
+        eng.close()
