@@ -179,6 +179,13 @@ __device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
   asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
   return r;
 }
+// Right shifts: IMAD.HI runs at a quarter of the issue rate on sm_100a (measured: 0.25 warp instructions per clock and
+// scheduler; IMAD, HFMA2, LOP3, SHF, PRMT all 0.5), so shifts right stay on the ALU pipe.
+#ifdef FEC_SHR_IMADHI
+#define FEC_SHR(x, n) imul_hi((x), 1u << (32 - (n)))
+#else
+#define FEC_SHR(x, n) ((x) >> (n))
+#endif
 __device__ __forceinline__ uint32_t imul_hi(uint32_t a, uint32_t b)
 {
   uint32_t r;
@@ -255,8 +262,8 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   // ---- scale the two minima: scaled = (x * mul + add) >> 8, both lanes in one 32-bit multiply -----------------------------
   const uint32_t sp  = m1 & H2_SIGN; // product of all v2c signs
   const uint32_t a1  = m1 & H2_ABS;
-  const uint32_t s1  = imul_hi(imad(a1, scale_mul, scale_add), 1u << 24) & 0x00ff00ffu;
-  const uint32_t s2  = imul_hi(imad(m2 & H2_ABS, scale_mul, scale_add), 1u << 24) & 0x00ff00ffu;
+  const uint32_t s1  = FEC_SHR(imad(a1, scale_mul, scale_add), 8) & 0x00ff00ffu;
+  const uint32_t s2  = FEC_SHR(imad(m2 & H2_ABS, scale_mul, scale_add), 8) & 0x00ff00ffu;
   const uint32_t M1s = s1 | sp;
   const uint32_t dls = h2_add(s2, s1 ^ H2_SIGN) | sp;
 
@@ -273,14 +280,14 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     const uint32_t nw = h2_min_xs(tt, H2_P127);          // |.| > 120 is "infinity" from here on
     const uint32_t o  = h2_add(nw, H2_P128);             // offset binary in the low byte of each lane
     // sign(v2c) of the two lanes -> bit (e & 15) of the sign word
-    const uint32_t sh = ((e & 15) == 15) ? vv : imul_hi(vv, 1u << (17 + (e & 15)));
+    const uint32_t sh = ((e & 15) == 15) ? vv : FEC_SHR(vv, 15 - (e & 15));
     if (e < 16) {
       sg1 |= sh & (0x00010001u << (e & 15));
     } else {
       sg2 |= sh & (0x00010001u << (e & 15));
     }
     sts_u8(a0[e], o);
-    sts_u8(a0[e] ^ 1u, imul_hi(o, 65536u));
+    sts_u8(a0[e] ^ 1u, FEC_SHR(o, 16));
   }
 
   // ---- new state: c2v sign = sign product ^ sign(v2c) ----------------------------------------------------------------------

@@ -79,7 +79,8 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.build()
+    # FEC_B200_LIB: an explicitly chosen build of the same library (A/B runs of kernel variants); still no fallback.
+    path = os.environ.get("FEC_B200_LIB") or _build.build()
     if not os.path.exists(path):
         raise FecError("libfec_b200.so is missing: build the CUDA extension (__graft_entry__.build())")
     lib = C.CDLL(path)
