@@ -17,6 +17,14 @@
  *   ldpc_decoder::decode                  include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:73-74      -> FEC_MODE_DECODE
  *   ldpc_rate_dematcher::rate_dematch     include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:52-57 -> FEC_MODE_DEMATCH
  *   pusch_codeblock_decoder::decode       lib/phy/upper/channel_processors/pusch/pusch_codeblock_decoder.cpp:34-71  -> FEC_MODE_CHAIN
+ *   hal::hw_accelerator_pdsch_enc (downlink twin)
+ *                                         include/srsran/hal/phy/upper/channel_processors/hw_accelerator_pdsch_enc.h:81-106
+ *     configure_operation (CB mode)          hw_accelerator_pdsch_enc.h:95                      -> fec_enc_desc (one per CB)
+ *     enqueue_operation / dequeue_operation  include/srsran/hal/hw_accelerator.h:48,56         -> fec_encode_run_host
+ *   hal::hw_pdsch_encoder_configuration   hw_accelerator_pdsch_enc.h:37-78                      -> fec_enc_desc
+ *   ldpc_encoder::encode + ldpc_rate_matcher::rate_match
+ *                                         lib/phy/upper/channel_coding/ldpc/ldpc_encoder_impl.cpp, ldpc_rate_matcher_impl.cpp:36-160
+ *                                                                                               -> fec_encode_launch_device
  * The reference-side bindings (C++ adapter classes over this ABI) are shown in INTEGRATION.md and live in
  * srsran-5g_b200/host/.
  */
@@ -30,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 2
+#define FEC_B200_ABI_VERSION 3
 
 typedef enum {
   FEC_OK             = 0,
@@ -232,6 +240,44 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
 
 /* Forgets the codeblock CRC flags of a slot range (rx buffer released / expired). */
 int fec_tb_reset_slots(fec_engine* e, uint32_t first_slot, uint32_t n);
+
+/* ---- downlink twin: LDPC encoding + rate matching of PDSCH codeblocks ---------------------------- */
+/* One operation = one codeblock in the accelerator's CB mode (pdsch_encoder_hw_impl.cpp:96-111): the segment the
+ * reference's ldpc_segmenter_tx produced (payload + TB/CB CRC, K - nof_filler_bits bits, packed MSB first as in bit_buffer)
+ * is LDPC-encoded (ldpc_encoder_impl.cpp / ldpc_encoder_generic.cpp: systematic bits, four core parity blocks through the
+ * double-diagonal structure, extension parity blocks), E bits are selected from the circular buffer starting at k0(rv),
+ * skipping the filler bits, and interleaved over Qm rows (ldpc_rate_matcher_impl.cpp:36-160). */
+#define FEC_ENC_FLAG_UNPACKED 0x01u /* output one bit per byte (hw cfg .do_unpack) instead of packed MSB-first bytes      */
+
+typedef struct fec_enc_desc {
+  uint64_t out_offset;      /* byte offset of the output: ceil(E/8) packed bytes (4-byte aligned offsets are fastest) or  */
+                            /* E bytes with FEC_ENC_FLAG_UNPACKED                                                        */
+  uint32_t in_offset;       /* byte offset of the packed segment, ceil((K - nof_filler_bits)/8) bytes                     */
+  uint32_t E;               /* rate-matched length in bits (hw cfg .rm_length), a multiple of qm                          */
+  uint32_t Nref;            /* limited-buffer rate matching length, 0 = unlimited (hw cfg .Nref)                          */
+  uint32_t k0;              /* filled in by the engine                                                                   */
+  uint16_t lifting_size;    /* Z (hw cfg .lifting_size)                                                                  */
+  uint16_t nof_filler_bits; /* hw cfg .nof_filler_bits                                                                   */
+  uint16_t graph_index;     /* filled in by the engine                                                                   */
+  uint8_t  base_graph;      /* 1 or 2 (hw cfg .base_graph_index)                                                         */
+  uint8_t  rv;              /* 0..3                                                                                      */
+  uint8_t  qm;              /* 1, 2, 4, 6, 8 (hw cfg .modulation)                                                        */
+  uint8_t  flags;           /* FEC_ENC_FLAG_*                                                                            */
+  uint8_t  reserved[6];
+} fec_enc_desc; /* 40 bytes */
+
+#define FEC_MAX_CB_IN_BYTES 1056u /* 22 * 384 / 8 */
+
+/* Checks an encode descriptor and fills in k0 / graph_index (host only). */
+int fec_enc_desc_prepare(fec_enc_desc* d);
+/* Device-resident batch: n prepared descriptors, packed segments and output buffer already in HBM; asynchronous on
+ * fec_engine_stream(). */
+int fec_encode_launch_device(fec_engine* e, const fec_enc_desc* d_descs, uint32_t n, const uint8_t* d_in, uint8_t* d_out,
+                             uint32_t max_Z);
+/* Host buffers: H2D + kernel + D2H, synchronous. Descriptors need not be prepared. Only the span of h_out from the first
+ * output to the end of the last one is written; bytes between two outputs inside that span are set to zero. */
+int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const uint8_t* h_in, size_t in_bytes,
+                        uint8_t* h_out, size_t out_bytes);
 
 #ifdef __cplusplus
 }

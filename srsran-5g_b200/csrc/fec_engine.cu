@@ -9,6 +9,7 @@
 #include "fec_kernel_generic.cuh"
 #include "fec_kernel_packed.cuh"
 #include "fec_tb.cuh"
+#include "fec_encode.cuh"
 #include "ldpc_tables.h"
 #include <atomic>
 #include <cmath>
@@ -174,6 +175,11 @@ struct fec_engine {
   uint8_t*              d_rblk   = nullptr;
   uint8_t*              h_tbout  = nullptr; // pinned bounce buffer for the transport block bytes
   std::vector<fec_tb_geometry> tb_geo;
+  // downlink encoder staging (allocated on first use, grown on demand)
+  fec_enc_desc* d_enc_descs = nullptr;
+  uint8_t*      d_enc_in    = nullptr;
+  uint8_t*      d_enc_out   = nullptr;
+  size_t        enc_descs_cap = 0, enc_in_cap = 0, enc_out_cap = 0;
   // weights of the last transport-block geometry seen (the same allocation usually repeats slot after slot)
   uint32_t              wc_key[3] = {0, 0, 0}; // nof_cbs, data_bits, stream_bits
   std::vector<uint32_t> wc_weights;
@@ -444,6 +450,9 @@ void fec_engine_destroy(fec_engine* e)
   cudaFreeHost(e->h_meta);
   cudaFreeHost(e->h_rblk);
   cudaFreeHost(e->h_tbout);
+  cudaFree(e->d_enc_descs);
+  cudaFree(e->d_enc_in);
+  cudaFree(e->d_enc_out);
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
   if (e->stream) {
@@ -1216,6 +1225,128 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
       }
     }
   }
+  return FEC_OK;
+}
+
+// ---- downlink twin: PDSCH codeblock encoding ---------------------------------------------------------------------------------
+int fec_enc_desc_prepare(fec_enc_desc* d)
+{
+  if (d == nullptr) {
+    return fail(FEC_ERR_BAD_ARG, "null descriptor");
+  }
+  if (d->base_graph != 1 && d->base_graph != 2) {
+    return fail(FEC_ERR_BAD_ARG, "base_graph=%u", d->base_graph);
+  }
+  const int zi = z_index(d->lifting_size);
+  if (zi < 0) {
+    return fail(FEC_ERR_BAD_ARG, "lifting_size=%u is not one of the 51 NR lifting sizes", d->lifting_size);
+  }
+  const uint32_t Z = d->lifting_size, Kb = (d->base_graph == 1) ? 22 : 10, nb = (d->base_graph == 1) ? 66 : 50;
+  const uint32_t N = nb * Z;
+  d->graph_index   = (uint16_t)((d->base_graph - 1) * 51 + zi);
+  if (d->nof_filler_bits >= (Kb - 2) * Z) {
+    return fail(FEC_ERR_BAD_ARG, "nof_filler_bits=%u out of range", d->nof_filler_bits);
+  }
+  if (d->rv > 3 || (d->qm != 1 && d->qm != 2 && d->qm != 4 && d->qm != 6 && d->qm != 8) || d->E == 0 ||
+      (d->E % d->qm) != 0) {
+    return fail(FEC_ERR_BAD_ARG, "rv=%u qm=%u E=%u", d->rv, d->qm, d->E);
+  }
+  const uint32_t Ncb = (d->Nref > 0) ? (d->Nref < N ? d->Nref : N) : N;
+  if (Ncb <= (Kb - 2) * Z) {
+    return fail(FEC_ERR_BAD_ARG, "Nref=%u leaves no parity in the circular buffer", d->Nref);
+  }
+  // k0 as the reference computes it (ldpc_rate_matcher_impl.cpp:61-63): floor(f * Ncb / N) * Z in double precision.
+  static const double F1[4] = {0, 17, 33, 56};
+  static const double F2[4] = {0, 13, 25, 43};
+  const double        f     = (d->base_graph == 1) ? F1[d->rv] : F2[d->rv];
+  d->k0                     = (uint32_t)(uint16_t)std::floor(f * (double)Ncb / (double)N) * Z;
+  return FEC_OK;
+}
+
+int fec_encode_launch_device(fec_engine* e, const fec_enc_desc* d_descs, uint32_t n, const uint8_t* d_in, uint8_t* d_out,
+                             uint32_t max_Z)
+{
+  if (!e || !d_descs || !d_in || !d_out) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (n == 0) {
+    return FEC_OK;
+  }
+  if (z_index(max_Z) < 0) {
+    return fail(FEC_ERR_BAD_ARG, "max_Z=%u is not a lifting size", max_Z);
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  fec_encode_kernel<<<n, FEC_ENC_THREADS, 0, e->stream>>>(d_descs, d_in, d_out, e->d_tab);
+  CU_TRY(cudaGetLastError());
+  e->launches.fetch_add(1);
+  return FEC_OK;
+}
+
+namespace {
+int grow(void** p, size_t* cap, size_t need)
+{
+  if (need <= *cap) {
+    return FEC_OK;
+  }
+  if (*p) {
+    cudaFree(*p);
+    *p   = nullptr;
+    *cap = 0;
+  }
+  if (cudaMalloc(p, need) != cudaSuccess) {
+    cudaGetLastError();
+    return fail(FEC_ERR_NO_MEMORY, "cannot allocate %zu bytes of device memory", need);
+  }
+  *cap = need;
+  return FEC_OK;
+}
+} // namespace
+
+int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const uint8_t* h_in, size_t in_bytes,
+                        uint8_t* h_out, size_t out_bytes)
+{
+  if (!e || !h_descs || !h_in || !h_out) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (n == 0) {
+    return FEC_OK;
+  }
+  uint32_t max_Z = 0;
+  size_t   lo = out_bytes, hi = 0; // span of the output buffer this call writes
+  for (uint32_t i = 0; i < n; ++i) {
+    fec_enc_desc& d = h_descs[i];
+    int           r = fec_enc_desc_prepare(&d);
+    if (r != FEC_OK) {
+      return r;
+    }
+    const uint32_t Kb      = (d.base_graph == 1) ? 22 : 10;
+    const size_t   in_len  = ((size_t)Kb * d.lifting_size - d.nof_filler_bits + 7) / 8;
+    const size_t   out_len = (d.flags & FEC_ENC_FLAG_UNPACKED) ? (size_t)d.E : ((size_t)d.E + 7) / 8;
+    if ((size_t)d.in_offset + in_len > in_bytes || d.out_offset + out_len > out_bytes) {
+      return fail(FEC_ERR_BAD_ARG, "codeblock %u: buffers too small (in %u+%zu of %zu, out %llu+%zu of %zu)", i, d.in_offset,
+                  in_len, in_bytes, (unsigned long long)d.out_offset, out_len, out_bytes);
+    }
+    max_Z = d.lifting_size > max_Z ? d.lifting_size : max_Z;
+    lo    = d.out_offset < lo ? (size_t)d.out_offset : lo;
+    hi    = d.out_offset + out_len > hi ? (size_t)d.out_offset + out_len : hi;
+  }
+  std::lock_guard<std::mutex> lk(e->run_mtx);
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  int r = grow((void**)&e->d_enc_descs, &e->enc_descs_cap, (size_t)n * sizeof(fec_enc_desc));
+  r     = (r == FEC_OK) ? grow((void**)&e->d_enc_in, &e->enc_in_cap, in_bytes) : r;
+  r     = (r == FEC_OK) ? grow((void**)&e->d_enc_out, &e->enc_out_cap, out_bytes) : r;
+  if (r != FEC_OK) {
+    return r;
+  }
+  CU_TRY(cudaMemcpyAsync(e->d_enc_descs, h_descs, (size_t)n * sizeof(fec_enc_desc), cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemcpyAsync(e->d_enc_in, h_in, in_bytes, cudaMemcpyHostToDevice, e->stream));
+  CU_TRY(cudaMemsetAsync(e->d_enc_out + lo, 0, hi - lo, e->stream)); // bytes between two outputs read as zeros
+  r = fec_encode_launch_device(e, e->d_enc_descs, n, e->d_enc_in, e->d_enc_out, max_Z);
+  if (r != FEC_OK) {
+    return r;
+  }
+  CU_TRY(cudaMemcpyAsync(h_out + lo, e->d_enc_out + lo, hi - lo, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
   return FEC_OK;
 }
 

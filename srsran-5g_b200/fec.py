@@ -6,6 +6,8 @@ tests read like the reference's own tests (paths relative to the reference tree)
   LdpcDecoder.decode            <- ldpc_decoder::decode            include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:73
   LdpcRateDematcher.rate_dematch<- ldpc_rate_dematcher::rate_dematch include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:52
   HwAcceleratorPuschDec         <- hal::hw_accelerator_pusch_dec   include/srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec.h:83
+  HwAcceleratorPdschEnc         <- hal::hw_accelerator_pdsch_enc   include/srsran/hal/phy/upper/channel_processors/hw_accelerator_pdsch_enc.h:81
+  LdpcEncoderRateMatcher        <- ldpc_encoder::encode + ldpc_rate_matcher::rate_match (channel_coding/ldpc/ldpc_encoder.h, ldpc_rate_matcher.h)
 
 There is no CPU fallback: constructing FecEngine without the compiled extension or without a CUDA device raises.
 """
@@ -55,6 +57,17 @@ TB_RESULT_DTYPE = np.dtype({
     "offsets": [0, 2, 4, 6, 7, 8, 12, 14], "itemsize": 16})
 
 
+# numpy mirror of struct fec_enc_desc (40 bytes)
+ENC_FLAG_UNPACKED = 1
+MAX_CB_IN_BYTES = 1056
+ENC_DESC_DTYPE = np.dtype({
+    "names": ["out_offset", "in_offset", "E", "Nref", "k0", "lifting_size", "nof_filler_bits", "graph_index",
+              "base_graph", "rv", "qm", "flags"],
+    "formats": ["<u8", "<u4", "<u4", "<u4", "<u4", "<u2", "<u2", "<u2", "u1", "u1", "u1", "u1"],
+    "offsets": [0, 8, 12, 16, 20, 24, 26, 28, 30, 31, 32, 33],
+    "itemsize": 40})
+
+
 class EngineCfg(C.Structure):
     _fields_ = [("device", C.c_int32), ("harq_slots", C.c_uint32), ("max_batch_cbs", C.c_uint32),
                 ("max_batch_llrs", C.c_uint32), ("nof_queues", C.c_uint32), ("scaling_factor", C.c_float),
@@ -65,7 +78,8 @@ EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_e
            "fec_engine_stream", "fec_harq_slot_ptr", "fec_engine_launch_count", "fec_desc_prepare",
            "fec_launch_device", "fec_run_host", "fec_host_alloc", "fec_host_free", "fec_harq_free", "fec_harq_read",
            "fec_harq_write", "fec_harq_flush", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
-           "fec_queue_poll", "fec_queue_fetch", "fec_tb_segment", "fec_tb_run_host", "fec_tb_reset_slots"]
+           "fec_queue_poll", "fec_queue_fetch", "fec_tb_segment", "fec_tb_run_host", "fec_tb_reset_slots",
+           "fec_enc_desc_prepare", "fec_encode_launch_device", "fec_encode_run_host"]
 
 _lib = None
 
@@ -116,6 +130,10 @@ def load_library():
     lib.fec_tb_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
                                     C.c_size_t, C.c_void_p, C.c_void_p]
     lib.fec_tb_reset_slots.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+    lib.fec_enc_desc_prepare.argtypes = [C.c_void_p]
+    lib.fec_encode_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
+    lib.fec_encode_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p,
+                                        C.c_size_t]
     _lib = lib
     return lib
 
@@ -133,6 +151,19 @@ def dims(bg, Z):
 
 def make_descs(n):
     return np.zeros(n, DESC_DTYPE)
+
+
+def make_enc_descs(n):
+    return np.zeros(n, ENC_DESC_DTYPE)
+
+
+def enc_desc_prepare(desc):
+    """Validates encode descriptors in place (fills k0 / graph_index); raises FecError on invalid fields. Host only."""
+    lib = load_library()
+    arr = np.atleast_1d(desc)
+    for i in range(arr.size):
+        _check(lib, lib.fec_enc_desc_prepare(arr[i:i + 1].ctypes.data))
+    return desc
 
 
 def make_tb_descs(n):
@@ -225,6 +256,22 @@ class FecEngine:
         _check(self.lib, self.lib.fec_run_host(self.h, descs.ctypes.data, n, ptr(llr), size(llr), ptr(out), size(out),
                                                results.ctypes.data, ptr(soft_out)))
         return results
+
+    def encode_launch_device(self, d_descs_ptr, n, d_in_ptr, d_out_ptr, max_Z):
+        """Asynchronous encode launch on self.stream; all pointers are device addresses (ints)."""
+        _check(self.lib, self.lib.fec_encode_launch_device(self.h, d_descs_ptr, n, d_in_ptr, d_out_ptr, max_Z))
+
+    def encode_run_host(self, descs, data, out):
+        """fec_encode_run_host: LDPC encoding + rate matching of n codeblocks, H2D -> kernel -> D2H, synchronous.
+        `data` / `out` are host numpy uint8 buffers (or (pointer, nbytes) tuples of pinned memory)."""
+        assert descs.dtype == ENC_DESC_DTYPE and descs.flags.c_contiguous
+
+        def ps(a):
+            return (a[0], a[1]) if isinstance(a, tuple) else (a.ctypes.data, a.nbytes)
+
+        (ip, ib), (op, ob) = ps(data), ps(out)
+        _check(self.lib, self.lib.fec_encode_run_host(self.h, descs.ctypes.data, descs.size, ip, ib, op, ob))
+        return out
 
     def tb_run_host(self, tbs, llr, out, slots=None, cb_results=False):
         """fec_tb_run_host: whole transport blocks (segmentation, codeblock decoding, assembly, TB CRC), synchronous.
@@ -458,6 +505,130 @@ class HwAcceleratorPuschDec:
 
     def is_harq_external(self):
         return True
+
+
+class HwPdschEncoderConfiguration:
+    """hal::hw_pdsch_encoder_configuration (hw_accelerator_pdsch_enc.h:37-78), the fields the CB mode uses."""
+
+    def __init__(self, **kw):
+        self.base_graph_index = 1
+        self.modulation = 2          # bits per symbol
+        self.rv = 0
+        self.lifting_size = 2
+        self.Ncb = 0
+        self.Nref = 0
+        self.nof_segment_bits = 0
+        self.nof_filler_bits = 0
+        self.rm_length = 0
+        self.cb_mode = True
+        self.attach_cb_crc = False
+        self.attach_tb_crc = False
+        self.do_unpack = True
+        for k, v in kw.items():
+            if not hasattr(self, k):
+                raise AttributeError(k)
+            setattr(self, k, v)
+
+
+class HwAcceleratorPdschEnc:
+    """hal::hw_accelerator_pdsch_enc (hw_accelerator_pdsch_enc.h:81-106) in CB mode, as pdsch_encoder_hw_impl drives it
+    (lib/phy/upper/channel_processors/pdsch/pdsch_encoder_hw_impl.cpp:31-186): reserve_queue, {configure_operation,
+    enqueue_operation(packed segment)}*, {dequeue_operation(codeblock, codeblock_packed)}*, free_queue. Enqueued
+    operations are batched and encoded in one launch at the first dequeue."""
+
+    def __init__(self, engine, max_ops=162):
+        self.engine = engine
+        self.max_ops = max_ops
+        self.cfgs = {}
+        self.pending = []   # (cb_index, config, packed bytes)
+        self.done = {}
+
+    def reserve_queue(self):
+        pass
+
+    def free_queue(self):
+        self.cfgs.clear()
+        self.pending.clear()
+        self.done.clear()
+
+    def is_cb_mode_supported(self):
+        return True
+
+    def get_max_supported_buff_size(self):
+        return MAX_CB_IN_BYTES
+
+    def configure_operation(self, config, cb_index=0):
+        if not config.cb_mode or config.attach_cb_crc or config.attach_tb_crc:
+            raise FecError("configure_operation: only CB mode without CRC attachment is served (as pdsch_encoder_hw_impl "
+                           "configures it when is_cb_mode_supported())")
+        self.cfgs[cb_index] = config
+
+    def enqueue_operation(self, data, aux_data=None, cb_index=0):
+        if len(self.pending) >= self.max_ops:
+            return False
+        c = self.cfgs[cb_index]
+        kb = 22 if c.base_graph_index == 1 else 10
+        need = (kb * c.lifting_size - c.nof_filler_bits + 7) // 8
+        if len(data) != need:
+            raise FecError("enqueue_operation: %d bytes given, the segment has %d" % (len(data), need))
+        self.pending.append((cb_index, c, np.array(data, np.uint8, copy=True)))
+        return True
+
+    def _run(self):
+        n = len(self.pending)
+        d = make_enc_descs(n)
+        ins, in_off, out_off = [], 0, 0
+        for i, (idx, c, seg) in enumerate(self.pending):
+            d[i]["base_graph"], d[i]["lifting_size"], d[i]["rv"], d[i]["qm"] = c.base_graph_index, c.lifting_size, c.rv, c.modulation
+            d[i]["Nref"], d[i]["nof_filler_bits"], d[i]["E"] = c.Nref, c.nof_filler_bits, c.rm_length
+            d[i]["in_offset"], d[i]["out_offset"] = in_off, out_off
+            ins.append(seg)
+            pad = (-len(seg)) % 4
+            if pad:
+                ins.append(np.zeros(pad, np.uint8))
+            in_off += len(seg) + pad
+            out_off += ((c.rm_length + 7) // 8 + 3) & ~3
+        out = np.zeros(out_off, np.uint8)
+        self.engine.encode_run_host(d, np.concatenate(ins), out)
+        for i, (idx, c, seg) in enumerate(self.pending):
+            o = int(d[i]["out_offset"])
+            self.done[idx] = (out[o:o + (c.rm_length + 7) // 8].copy(), c)
+        self.pending.clear()
+
+    def dequeue_operation(self, data, aux_data=None, segment_index=0):
+        """Fills aux_data (codeblock_packed) with the packed rate-matched bits and, if do_unpack, data with one bit per byte."""
+        if segment_index not in self.done:
+            if not any(p[0] == segment_index for p in self.pending):
+                return False
+            self._run()
+        packed, c = self.done.pop(segment_index)
+        if aux_data is not None:
+            aux_data[:len(packed)] = packed
+        if c.do_unpack and data is not None:
+            data[:c.rm_length] = np.unpackbits(packed)[:c.rm_length]
+        return True
+
+
+class LdpcEncoderRateMatcher:
+    """ldpc_encoder::encode followed by ldpc_rate_matcher::rate_match for one codeblock
+    (lib/phy/upper/channel_coding/ldpc/ldpc_encoder_impl.cpp:64-120, ldpc_rate_matcher_impl.cpp:36-160), as
+    pdsch_encoder_impl chains them (lib/phy/upper/channel_processors/pdsch/pdsch_encoder_impl.cpp)."""
+
+    def __init__(self, engine):
+        self.engine = engine
+
+    def encode_rate_match(self, message_bits, rm_length, cfg):
+        """message_bits: K unpacked bits with the filler positions at the end (their values are ignored);
+        cfg: CodeblockMetadata. Returns rm_length unpacked bits."""
+        K, _ = dims(cfg.base_graph, cfg.lifting_size)
+        kp = K - cfg.nof_filler_bits
+        d = make_enc_descs(1)
+        d["base_graph"], d["lifting_size"], d["rv"], d["qm"] = cfg.base_graph, cfg.lifting_size, cfg.rv, cfg.mod_order
+        d["Nref"], d["nof_filler_bits"], d["E"], d["flags"] = cfg.Nref, cfg.nof_filler_bits, rm_length, ENC_FLAG_UNPACKED
+        seg = np.packbits(np.asarray(message_bits[:kp], np.uint8) & 1)
+        out = np.zeros(rm_length, np.uint8)
+        self.engine.encode_run_host(d, seg, out)
+        return out
 
 
 class PuschDecoderConfiguration:
