@@ -278,6 +278,79 @@ def bench_transport_block(fec, eng, torch, dev, stream, args, rank):
             "first_tb_pass_fraction": float(((r1["status"] & fec.RES_CRC_PASS) != 0).mean())}
 
 
+def bench_pdsch_encode(fec, eng, torch, dev, stream, args):
+    """Downlink twin: LDPC encoding + rate matching of PDSCH codeblocks, one CTA per codeblock.
+    Two shapes: the headline one (BG1 Z=384, E=25344, Qm=2) and the config-3 one (E=8960, Qm=8, 16 fillers). Reported as
+    encoded INFO Gbit/s (K - fillers bits per codeblock), device-resident and through fec_encode_run_host (pinned host)."""
+    out = {}
+    n = args.cbs
+    rng = np.random.default_rng(4242)
+    for name, e_bits, qm, fill in (("rate_1_3", E, QM, 0), ("config3", 8960, 8, 16)):
+        seg_bytes, out_bytes = (K - fill + 7) // 8, (e_bits + 7) // 8
+        out_stride = (out_bytes + 3) & ~3
+        d = fec.make_enc_descs(n)
+        d["base_graph"], d["lifting_size"], d["qm"], d["E"], d["rv"], d["nof_filler_bits"] = BG, Z, qm, e_bits, 0, fill
+        d["in_offset"] = np.arange(n) * seg_bytes
+        d["out_offset"] = np.arange(n, dtype=np.uint64) * out_stride
+        fec.enc_desc_prepare(d)
+        t_in = torch.from_numpy(rng.integers(0, 256, n * seg_bytes, dtype=np.uint8)).pin_memory()
+        t_out = torch.zeros(n * out_stride, dtype=torch.uint8).pin_memory()
+        d_in, d_o = t_in.to(dev), torch.zeros(n * out_stride, dtype=torch.uint8, device=dev)
+        d_descs = torch.from_numpy(d.view(np.uint8).copy()).to(dev)
+        torch.cuda.synchronize()
+
+        def step():
+            eng.encode_launch_device(d_descs.data_ptr(), n, d_in.data_ptr(), d_o.data_ptr(), Z)
+
+        for _ in range(3):
+            step()
+        reps = 20
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(reps):
+                step()
+            e1.record(stream)
+        stream.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        for _ in range(2):
+            eng.encode_run_host(d, (t_in.data_ptr(), t_in.numel()), (t_out.data_ptr(), t_out.numel()))
+        t0 = time.perf_counter()
+        for _ in range(5):
+            eng.encode_run_host(d, (t_in.data_ptr(), t_in.numel()), (t_out.data_ptr(), t_out.numel()))
+        e2e_s = (time.perf_counter() - t0) / 5
+        assert (t_out.numpy() == d_o.cpu().numpy()).all()
+        info = n * (K - fill)
+        algo = n * (seg_bytes + out_bytes + 40)
+        out[name] = {"workload": "BG1 Z=384, %d fillers, E=%d, Qm=%d, rv0, packed output, %d codeblocks per launch"
+                                 % (fill, e_bits, qm, n),
+                     "value": info / (ms * 1e-3) / 1e9, "unit": "Gbit/s (info bits encoded)",
+                     "coded_gbps": n * e_bits / (ms * 1e-3) / 1e9, "ms_per_launch": ms,
+                     "e2e": {"value": info / e2e_s / 1e9, "unit": "Gbit/s", "h2d_bytes_per_step": n * (seg_bytes + 40),
+                             "d2h_bytes_per_step": n * out_stride, "api": "fec_encode_run_host (pinned host buffers)"},
+                     "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "unit": "GB/s",
+                                  "algorithmic_bytes_per_cb": seg_bytes + out_bytes + 40,
+                                  "note": "bit gather out of shared memory: compute/LSU-bound, far from the HBM roof"}}
+    if not args.no_cpu_baseline:
+        try:
+            orc = ge.load_oracle()
+            if orc.Ref.available():
+                ref = orc.Ref()
+                msg = rng.integers(0, 2, K).astype(np.uint8)
+                ref.rate_match(BG, Z, ref.encode(BG, Z, msg), E, 0, QM, 0, 0)
+                t0, cnt = time.perf_counter(), 0
+                while time.perf_counter() - t0 < 2.0:
+                    ref.rate_match(BG, Z, ref.encode(BG, Z, msg), E, 0, QM, 0, 0)
+                    cnt += 1
+                out["cpu_baseline"] = {"value": cnt * K / (time.perf_counter() - t0) / 1e9, "unit": "Gbit/s", "cores": 1,
+                                       "kind": "reference", "sample": "%d codeblocks of the rate_1_3 shape through the "
+                                       "reference's ldpc_encoder + ldpc_rate_matcher (oracle/_ref shim, one thread, "
+                                       "bit pack/unpack of the shim included)" % cnt}
+        except Exception as ex:  # the checker is optional here
+            out["cpu_baseline"] = {"unavailable": str(ex)[:100]}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -378,6 +451,10 @@ def run_ours(args):
     if not args.no_tb:
         tb = bench_transport_block(fec, eng, torch, dev, stream, args, rank)
 
+    enc = None
+    if not args.no_enc and rank == 0:
+        enc = bench_pdsch_encode(fec, eng, torch, dev, stream, args)
+
     # ---- e2e: host buffers through fec_run_host (H2D + kernels + D2H inside the timed region) --------------------------
     res_h = np.zeros(n, fec.RESULT_DTYPE)
     llr_ptr, out_ptr = t_llr_pin.data_ptr(), t_out_pin.data_ptr()
@@ -417,7 +494,7 @@ def run_ours(args):
                 "crc_pass_fraction": float(passed.mean()),
                 "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + K // 8 + 48),
                         "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
-                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb,
+                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb, "pdsch_encode": enc,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                              "frac": achieved / peak_gbs,
                              # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture
@@ -458,6 +535,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-tb", action="store_true", help="skip the config-3 transport-block latency measurement")
+    ap.add_argument("--no-enc", action="store_true", help="skip the PDSCH encoder (downlink twin) measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     return run_reference(args) if args.impl == "reference" else run_ours(args)

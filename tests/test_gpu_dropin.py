@@ -43,3 +43,17 @@ def test_pusch_decoder_cuda_is_a_drop_in(orc, oracle, tmp_path):
     assert "OK blocks=8" in r.stdout and r.stdout.count("LATENCY") == 3, r.stdout
     failed = int(r.stdout.split("failed_transmissions=")[1])
     assert failed >= 2, r.stdout  # the retransmission path was exercised
+
+
+ENC_BIN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "dropin_pdsch_encoder")
+
+
+def test_pdsch_encoder_hw_impl_over_the_cuda_hal():
+    """The reference's unmodified pdsch_encoder_hw_impl over srsran::b200::cuda_pdsch_enc_accelerator gives the codeword
+    of the reference's software pdsch_encoder_impl, for the 152-codeblock config-3 block and 40 random blocks."""
+    if not os.path.exists(ENC_BIN):
+        pytest.skip("tests/cpp/_build/dropin_pdsch_encoder not built (needs the reference headers)")
+    r = subprocess.run([ENC_BIN, "40"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    print(r.stdout)
+    assert "OK transport_blocks=42" in r.stdout, r.stdout
