@@ -190,3 +190,74 @@ def test_pusch_decoder_mirror(fec, tb_engine, orc, oracle):
             assert (out == tb).all()
             break
     assert got[-1].tb_crc_ok and len(got) >= 2
+
+
+def test_multi_cell_batch_config5_sharded(fec, orc, oracle):
+    """BASELINE config 5: one uplink slot of 32 cells with an MCS mix (256QAM R948 full-slot block of 152 codeblocks, 64QAM
+    R873, QPSK R120 = BG2 with repetition), decoded (a) as one batch on one engine and (b) sharded by cell_id mod n over
+    n = 2, 4, 8 engines-worth of calls (one GPU here: the shards run one after the other). No data-path collective exists,
+    so every shard must reproduce the unsharded results bit for bit; every block must come back intact; a sample of the
+    codeblocks is compared with the oracle."""
+    nsym = 42588 * 4  # 273 PRB x 13 data symbols x 12 subcarriers x 4 layers
+    mcs = [dict(tbs=1277992, bg=1, qm=8, nl=4, G=nsym * 8, snr=8.0),
+           dict(tbs=871384, bg=1, qm=6, nl=4, G=nsym * 6, snr=6.0),
+           dict(tbs=39920, bg=2, qm=2, nl=4, G=nsym * 2, snr=-4.0)]
+    n_cells = 32
+    cell_mcs = [0 if c % 8 == 0 else (1 if c % 2 == 0 else 2) for c in range(n_cells)]  # 4 + 12 + 16 cells
+    rng = np.random.default_rng(55)
+    tbs, llrs, geos, slot0, nslots = [], [], [], [], 0
+    enc_cache = {}
+    for c in range(n_cells):
+        p = mcs[cell_mcs[c]]
+        g = orc.tb_geometry(p["tbs"], p["bg"], p["qm"], p["nl"], p["G"])
+        tb = rng.integers(0, 256, p["tbs"] // 8, dtype=np.uint8)
+        enc = orc.tb_encode(oracle, tb, p["bg"])
+        llrs.append(orc.tb_transmit(oracle, enc, p["tbs"], p["bg"], 0, p["qm"], 0, p["nl"], p["G"], p["snr"], seed=900 + c))
+        tbs.append(tb)
+        geos.append(g)
+        slot0.append(nslots)
+        nslots += g["C"]
+    assert any(g["rm"][0] > g["N"] for g in geos), "the QPSK R120 cells must exercise repetition (E > N)"
+    eng = fec.FecEngine(device=0, harq_slots=nslots, max_batch_cbs=nslots, max_batch_llrs=sum(x.size for x in llrs) + 64)
+
+    def run(cells):
+        d = fec.make_tb_descs(len(cells))
+        lo, oo, parts = 0, 0, []
+        for i, c in enumerate(cells):
+            p = mcs[cell_mcs[c]]
+            d[i:i + 1] = _tb_desc(fec, p, 0, True, slot0[c], lo, oo)
+            parts.append(llrs[c])
+            lo += llrs[c].size
+            oo += p["tbs"] // 8
+        out = np.zeros(oo, np.uint8)
+        res, cbr = eng.tb_run_host(d, np.concatenate(parts), out, cb_results=True)
+        outs, o = [], 0
+        for c in cells:
+            n = mcs[cell_mcs[c]]["tbs"] // 8
+            outs.append(out[o:o + n].copy())
+            o += n
+        return res, cbr, outs
+
+    res0, cbr0, out0 = run(list(range(n_cells)))
+    for c in range(n_cells):
+        assert bool(res0["tb_crc_ok"][c]) and (out0[c] == tbs[c]).all(), c
+        assert int(res0["nof_codeblocks"][c]) == geos[c]["C"]
+    # oracle sample: first and last codeblock of one cell per MCS
+    for c in (0, 2, 1):
+        p, g = mcs[cell_mcs[c]], geos[c]
+        for r in (0, g["C"] - 1):
+            soft = np.zeros(g["N"], np.int8)
+            it, _ = oracle.cb_chain(p["bg"], g["Z"], soft, llrs[c][g["cw_off"][r]:g["cw_off"][r] + g["rm"][r]], True, 0,
+                                    p["qm"], 0, g["fillers"], orc.CRC24B if g["C"] > 1 else (orc.CRC24A if p["tbs"] > 3824 else orc.CRC16),
+                                    6, True)
+            assert it == int(cbr0[c, r]["nof_ldpc_iterations"]), (c, r)
+            assert (eng.harq_read(slot0[c] + r, g["N"]) == soft).all() or bool(res0["tb_crc_ok"][c])  # slots are freed on success
+    for world in (2, 4, 8):
+        for rank in range(world):
+            cells = fec.cells_of_rank(n_cells, world, rank)
+            res, cbr, outs = run(cells)
+            for i, c in enumerate(cells):
+                assert res[i].tobytes() == res0[c].tobytes(), (world, rank, c)
+                assert (outs[i] == out0[c]).all(), (world, rank, c)
+                assert cbr[i].tobytes() == cbr0[c].tobytes(), (world, rank, c)
+    eng.close()
