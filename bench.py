@@ -113,7 +113,7 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
-NCU_DRAM_BYTES_PER_CB = 46250  # (180.608512 + 147.953152) MB / 7104 codeblocks, r01 capture
+NCU_DRAM_BYTES_PER_CB = 46200  # (180.619776 + 147.588864) MB / 7104 codeblocks, r01 capture (profiles/r01_ncu_packed_full_metrics.csv)
 
 
 def reference_cpu(llr, n_threads, seconds, early_stop, impl=None):
