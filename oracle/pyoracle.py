@@ -129,6 +129,99 @@ class Oracle:
         return self.awgn_llr(tx, esn0_db, seed + 7919), msg
 
 
+# ---- soft demodulation + descrambling ------------------------------------------------------------
+DEMOD_FLAVOURS = ("generic", "avx2", "avx512")  # what the reference was compiled for; index = flavour id
+
+
+def _demod_args(sym, noise):
+    sym = np.ascontiguousarray(sym, np.float32).reshape(-1, 2)
+    noise = np.ascontiguousarray(noise, np.float32).reshape(-1)
+    assert sym.shape[0] == noise.size
+    return sym, noise
+
+
+class DemodOracle:
+    """fec_demod.c: the C restatement of demodulate_soft (three compile-time flavours), the Gold sequence and descrambling."""
+
+    def __init__(self, oracle):
+        self.lib = oracle.lib
+        self.lib.orc_demodulate_soft.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.orc_gold_sequence.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+        self.lib.orc_descramble.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+
+    def demodulate_soft(self, flavour, qm, sym, noise, pi2=False):
+        sym, noise = _demod_args(sym, noise)
+        out = np.zeros(noise.size * qm, np.int8)
+        self.lib.orc_demodulate_soft(flavour, qm, int(pi2), noise.size, _p(sym), _p(noise), _p(out))
+        return out
+
+    def blocks(self, flavour, qm):
+        a, b = C.c_uint(), C.c_uint()
+        self.lib.orc_demod_blocks(flavour, qm, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def tables(self):
+        t = np.zeros((7, 36), np.float32)
+        self.lib.orc_demod_tables(_p(t))
+        return t
+
+    def gold_sequence(self, c_init, offset, nbits):
+        packed = np.zeros((nbits + 7) // 8, np.uint8)
+        self.lib.orc_gold_sequence(c_init, offset, nbits, _p(packed))
+        return packed
+
+    def descramble(self, packed_seq, llr):
+        llr = np.ascontiguousarray(llr, np.int8)
+        out = np.zeros_like(llr)
+        self.lib.orc_descramble(_p(packed_seq), llr.size, _p(llr), _p(out))
+        return out
+
+    def codeword(self, flavour, qm, blocks, sym, noise, c_init):
+        """pusch_demodulator_impl.cpp:262-400 without the equaliser: one demodulate_soft call per block of symbols (one
+        OFDM symbol each), the scrambling sequence running on across the blocks."""
+        sym, noise = _demod_args(sym, noise)
+        out, pos = [], 0
+        for n in blocks:
+            out.append(self.demodulate_soft(flavour, qm, sym[pos:pos + n], noise[pos:pos + n]))
+            pos += n
+        llr = np.concatenate(out) if out else np.zeros(0, np.int8)
+        return self.descramble(self.gold_sequence(c_init, 0, llr.size), llr)
+
+
+class RefDemod:
+    """The reference's demodulation_mapper_impl / pseudo_random_generator_impl compiled for one flavour."""
+
+    def __init__(self, flavour):
+        path = os.path.join(HERE, "_ref", "libref_demod_%s.so" % DEMOD_FLAVOURS[flavour])
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        self.lib.ref_demodulate_soft.argtypes = [C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.ref_prg_generate.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_void_p]
+        self.lib.ref_prg_apply_xor_llr.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_void_p]
+
+    @staticmethod
+    def available(flavour):
+        return os.path.exists(os.path.join(HERE, "_ref", "libref_demod_%s.so" % DEMOD_FLAVOURS[flavour]))
+
+    def demodulate_soft(self, qm, sym, noise, pi2=False):
+        sym, noise = _demod_args(sym, noise)
+        out = np.zeros(noise.size * qm, np.int8)
+        self.lib.ref_demodulate_soft(qm, int(pi2), noise.size, _p(sym), _p(noise), _p(out))
+        return out
+
+    def gold_sequence(self, c_init, offset, nbits):
+        packed = np.zeros((nbits + 7) // 8, np.uint8)
+        self.lib.ref_prg_generate(c_init, offset, nbits, _p(packed))
+        return packed
+
+    def apply_xor_llr(self, c_init, offset, llr):
+        llr = np.ascontiguousarray(llr, np.int8)
+        out = np.zeros_like(llr)
+        self.lib.ref_prg_apply_xor_llr(c_init, offset, llr.size, _p(llr), _p(out))
+        return out
+
+
 class Ref:
     """The reference itself (kind "reference"). impl: 0 generic, 1 avx2, 2 avx512, 3 auto."""
     GENERIC, AVX2, AVX512, AUTO = 0, 1, 2, 3

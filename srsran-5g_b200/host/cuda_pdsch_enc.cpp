@@ -64,9 +64,15 @@ bool cuda_pdsch_enc_accelerator::enqueue_operation(span<const uint8_t> data, spa
     return false; // the consumer drains what it has enqueued and retries
   }
   if (out_used + out_len > out_cap) {
-    if (!descs.empty()) {
+    // The staging may only be replaced while no encoded codeblock is waiting in it for its dequeue_operation().
+    bool busy = !descs.empty();
+    for (const operation& o : ops) {
+      busy = busy || (o.state == op_state::done);
+    }
+    if (busy) {
       return false;
     }
+    out_used = 0;
     fec_host_free(h_out);
     out_cap = std::max<size_t>(2 * out_cap, out_len);
     h_out   = static_cast<uint8_t*>(fec_host_alloc(out_cap));

@@ -58,3 +58,43 @@ def random_tb_params(rng, max_bits_bg1=30000, max_bits_bg2=9000):
     nsym = max(1, int((B + 24 * C_) / rate / (qm * nl))) * nl
     snr = float(rng.uniform(-1.0, 6.0)) + 10 * np.log10(rate)
     return dict(tbs=tbs, bg=bg, qm=qm, nl=nl, G=nsym * qm, snr=snr)
+
+
+# ---- soft demodulation ---------------------------------------------------------------------------
+def _around(x, k):
+    x = np.float32(x)
+    out, a, b = [x], x, x
+    for _ in range(k):
+        a = np.nextafter(a, np.float32(np.inf))
+        b = np.nextafter(b, np.float32(-np.inf))
+        out += [a, b]
+    return out
+
+
+def demod_crafted_symbols(qm, noise_var, dense=1):
+    """Symbols whose LLRs sit on the rounding decisions where the reference's code paths differ: the edges of the
+    piecewise-linear intervals (+- a few ulp), and values whose scaled LLR is k + 0.5 (round-half-even vs half-away,
+    divide vs reciprocal-multiply, fused vs separate multiply-add)."""
+    M = {1: 1 / np.sqrt(2), 2: 1 / np.sqrt(2), 4: 1 / np.sqrt(10), 6: 1 / np.sqrt(42), 8: 1 / np.sqrt(170)}[qm]
+    xs = []
+    for k in range(-18, 19):
+        xs += _around(np.float32(k) * np.float32(M), 4)
+    for s in (4, 8, 12, 16, 20, 24, 28, 32, 2.8284271):
+        for k in range(-121, 122, 3 * dense):
+            xs += _around((k + 0.5) / (6.0 * s * M) * noise_var if qm > 2 else (k + 0.5) / (5.0 * s) * noise_var, 2)
+    xs = np.array(xs, np.float32)
+    return np.stack([xs, np.roll(xs, 7)], 1)
+
+
+def demod_random_symbols(rng, qm, n, specials=True):
+    """Random equalised symbols and noise variances, with the special values the reference handles explicitly: zero,
+    negative and NaN noise variances (LLR = 0), exact-zero and near-zero symbols."""
+    amp = {1: 1.0, 2: 1.0, 4: 1.2, 6: 1.3, 8: 1.4}[qm]
+    sym = rng.uniform(-amp, amp, (n, 2)).astype(np.float32)
+    nv = (rng.choice([0.001, 0.01, 0.05, 0.2, 1.0], n) * rng.uniform(0.5, 1.5, n)).astype(np.float32)
+    if specials and n >= 16:
+        nv[rng.integers(0, n, 3)] = [0.0, -1.0, np.nan]
+        sym[rng.integers(0, n, 2)] = 0.0
+        sym[rng.integers(0, n, 1), 0] = 1e-10
+        sym[rng.integers(0, n, 1)] = [1e-6, -1e-6]
+    return sym, nv
