@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 3
+#define FEC_B200_ABI_VERSION 4
 
 typedef enum {
   FEC_OK             = 0,
@@ -278,6 +278,49 @@ int fec_encode_launch_device(fec_engine* e, const fec_enc_desc* d_descs, uint32_
  * output to the end of the last one is written; bytes between two outputs inside that span are set to zero. */
 int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const uint8_t* h_in, size_t in_bytes,
                         uint8_t* h_out, size_t out_bytes);
+
+/* ---- the step in front of the path: soft demodulation + descrambling on the device ---------------- */
+/* One descriptor = one demodulation_mapper::demodulate_soft call (include/srsran/phy/upper/channel_modulation/
+ * demodulation_mapper.h:47-69; pusch_demodulator_impl issues one per OFDM symbol, lib/phy/upper/channel_processors/pusch/
+ * pusch_demodulator_impl.cpp:355-375) followed by the descrambling of its soft bits with the TS 38.211 5.2.1 sequence
+ * initialised with c_init = rnti * 2^15 + n_id (ibid. 272-274, 377-382; pseudo_random_generator.h:46-101). Symbols are
+ * equalised complex samples (re, im float32), noise_vars the post-equalisation noise variance of each symbol.
+ *
+ * The reference picks its demodulator arithmetic when it is COMPILED (AVX-512 / AVX2 / scalar code, selected with #ifdef in
+ * lib/phy/upper/channel_modulation/demodulation_mapper_*.cpp) and the variants round differently in the last place; the
+ * `flavour` argument names the build the results must be identical to. */
+#define FEC_DEMOD_FLAVOUR_GENERIC 0u /* scalar code, no fused multiply-add (baseline x86-64 build)                          */
+#define FEC_DEMOD_FLAVOUR_AVX2    1u /* -mavx2 -mfma                                                                        */
+#define FEC_DEMOD_FLAVOUR_AVX512  2u /* -mavx512f -mavx512bw -mavx512vl -mavx2 -mfma: -march=native on the hosts used here  */
+
+#define FEC_DEMOD_FLAG_PI2_BPSK      0x01u /* qm == 1: pi/2-BPSK instead of BPSK                                           */
+#define FEC_DEMOD_FLAG_NO_DESCRAMBLE 0x02u /* plain demodulation_mapper::demodulate_soft                                   */
+
+typedef struct fec_demod_desc {
+  uint64_t sym_offset;   /* first symbol of the call: index into the symbol (re, im pairs) and noise-variance arrays       */
+  uint64_t llr_offset;   /* first of the nof_symbols * qm soft bits in the LLR buffer                                       */
+  uint32_t nof_symbols;
+  uint32_t c_init;       /* scrambling sequence initial state                                                              */
+  uint32_t seq_offset;   /* position of the call's first soft bit in the sequence (soft bits of the codeword before it)    */
+  uint8_t  qm;           /* 1, 2, 4, 6, 8                                                                                  */
+  uint8_t  flags;        /* FEC_DEMOD_FLAG_*                                                                               */
+  uint8_t  reserved[2];
+} fec_demod_desc; /* 32 bytes */
+
+/* Device-resident batch: n descriptors, symbols, noise variances and the LLR buffer already in HBM; asynchronous on
+ * fec_engine_stream(). max_symbols >= the largest nof_symbols of the batch. */
+int fec_demod_launch_device(fec_engine* e, const fec_demod_desc* d_descs, uint32_t n, uint32_t max_symbols,
+                            const float* d_symbols, const float* d_noise_vars, int8_t* d_llr, uint32_t flavour);
+/* Host buffers: H2D + kernel + D2H of the LLR span the descriptors cover, synchronous (the mirror of demodulate_soft;
+ * the production path is fec_tb_run_host_symbols, where the LLRs stay on the device). */
+int fec_demod_run_host(fec_engine* e, const fec_demod_desc* h_descs, uint32_t n, const float* h_symbols,
+                       const float* h_noise_vars, size_t nof_symbols, int8_t* h_llr, size_t llr_bytes, uint32_t flavour);
+/* fec_tb_run_host with the codeword LLRs produced on the device: the demodulation descriptors write the same LLR index space
+ * the transport blocks read (fec_tb_desc.llr_offset); together they must cover every LLR of every transport block. */
+int fec_tb_run_host_symbols(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots,
+                            const fec_demod_desc* h_demod, uint32_t n_demod, const float* h_symbols,
+                            const float* h_noise_vars, size_t nof_symbols, uint32_t flavour, uint8_t* h_out, size_t out_bytes,
+                            fec_tb_result* h_results, fec_cb_result* h_cb_results);
 
 #ifdef __cplusplus
 }

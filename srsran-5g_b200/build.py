@@ -7,7 +7,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libfec_b200.so")
 SOURCES = ["fec_engine.cu"]
-HEADERS = ["fec_device.cuh", "fec_kernel_generic.cuh", "fec_kernel_packed.cuh", "fec_tb.cuh", "fec_encode.cuh", "ldpc_tables.h",
+HEADERS = ["fec_device.cuh", "fec_kernel_generic.cuh", "fec_kernel_packed.cuh", "fec_tb.cuh", "fec_encode.cuh", "fec_demod.cuh", "ldpc_tables.h",
            os.path.join("..", "..", "include", "fec_b200.h")]
 NVCC_FLAGS = (["-DFEC_PROFILE=" + os.environ["FEC_PROFILE"]] if os.environ.get("FEC_PROFILE") else []) + \
     ["-D" + d for d in os.environ.get("FEC_DEFS", "").split()] + ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",

@@ -10,6 +10,7 @@
 #include "fec_kernel_packed.cuh"
 #include "fec_tb.cuh"
 #include "fec_encode.cuh"
+#include "fec_demod.cuh"
 #include "ldpc_tables.h"
 #include <atomic>
 #include <cmath>
@@ -180,6 +181,14 @@ struct fec_engine {
   uint8_t*      d_enc_in    = nullptr;
   uint8_t*      d_enc_out   = nullptr;
   size_t        enc_descs_cap = 0, enc_in_cap = 0, enc_out_cap = 0;
+  // soft demodulator: tables and staging (allocated on first use, grown on demand)
+  fec_demod_tables* d_dtab     = nullptr;
+  fec_demod_desc*   d_dm_descs = nullptr;
+  float*            d_dm_sym   = nullptr;
+  float*            d_dm_noise = nullptr;
+  int8_t*           d_dm_llr   = nullptr;
+  size_t            dm_descs_cap = 0, dm_sym_cap = 0, dm_noise_cap = 0, dm_llr_cap = 0;
+  std::vector<fec_demod_desc> dm_descs_host;
   // weights of the last transport-block geometry seen (the same allocation usually repeats slot after slot)
   uint32_t              wc_key[3] = {0, 0, 0}; // nof_cbs, data_bits, stream_bits
   std::vector<uint32_t> wc_weights;
@@ -453,6 +462,11 @@ void fec_engine_destroy(fec_engine* e)
   cudaFree(e->d_enc_descs);
   cudaFree(e->d_enc_in);
   cudaFree(e->d_enc_out);
+  cudaFree(e->d_dtab);
+  cudaFree(e->d_dm_descs);
+  cudaFree(e->d_dm_sym);
+  cudaFree(e->d_dm_noise);
+  cudaFree(e->d_dm_llr);
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
   if (e->stream) {
@@ -1029,10 +1043,22 @@ int fec_tb_reset_slots(fec_engine* e, uint32_t first_slot, uint32_t n)
   return FEC_OK;
 }
 
-int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr,
-                    size_t llr_bytes, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+namespace {
+// Where the codeword LLRs of a transport-block call come from when they are not host LLRs: demodulated on the device.
+struct demod_source {
+  const fec_demod_desc* descs;
+  uint32_t              n;
+  const float*          h_symbols;
+  const float*          h_noise;
+  size_t                nof_symbols;
+  uint32_t              flavour;
+};
+int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l0, size_t l1, int8_t* d_llr);
+
+int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr, size_t llr_bytes,
+           const demod_source* dm, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results, fec_cb_result* h_cb_results)
 {
-  if (!e || !tbs || !h_llr || !h_out || !h_results) {
+  if (!e || !tbs || (!h_llr && !dm) || !h_out || !h_results) {
     return fail(FEC_ERR_BAD_ARG, "null argument");
   }
   if (n == 0) {
@@ -1163,7 +1189,14 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
   fec_cb_result* d_cbres   = reinterpret_cast<fec_cb_result*>(e->d_rblk);
   fec_tb_result* d_tbres   = reinterpret_cast<fec_tb_result*>(e->d_rblk + off_tbres);
   CU_TRY(cudaMemcpyAsync(e->d_meta, e->h_meta, meta_size, cudaMemcpyHostToDevice, st));
-  CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+  if (dm) {
+    rc = demod_stage(e, st, *dm, l0, l1, e->d_llr);
+    if (rc != FEC_OK) {
+      return rc;
+    }
+  } else {
+    CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+  }
   rc = launch(e, st, d_descs, n_map, e->d_llr, e->d_msg, d_cbres, max_Z, any1);
   if (rc != FEC_OK) {
     return rc;
@@ -1226,6 +1259,16 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
     }
   }
   return FEC_OK;
+}
+} // namespace
+
+int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr,
+                    size_t llr_bytes, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+{
+  if (!h_llr) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  return tb_run(e, tbs, n, slots, h_llr, llr_bytes, nullptr, h_out, out_bytes, h_results, h_cb_results);
 }
 
 // ---- downlink twin: PDSCH codeblock encoding ---------------------------------------------------------------------------------
@@ -1348,6 +1391,185 @@ int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const 
   CU_TRY(cudaMemcpyAsync(h_out + lo, e->d_enc_out + lo, hi - lo, cudaMemcpyDeviceToHost, e->stream));
   CU_TRY(cudaStreamSynchronize(e->stream));
   return FEC_OK;
+}
+
+// ---- the step in front of the path: soft demodulation + descrambling ---------------------------------------------------------
+namespace {
+int demod_tables_alloc(fec_engine* e)
+{
+  if (e->d_dtab != nullptr) {
+    return FEC_OK;
+  }
+  fec_demod_tables* h = new (std::nothrow) fec_demod_tables;
+  if (h == nullptr) {
+    return fail(FEC_ERR_NO_MEMORY, "demodulator tables");
+  }
+  fec_demod_build_tables(h);
+  cudaError_t err = cudaMalloc((void**)&e->d_dtab, sizeof(fec_demod_tables));
+  if (err == cudaSuccess) {
+    err = cudaMemcpy(e->d_dtab, h, sizeof(fec_demod_tables), cudaMemcpyHostToDevice);
+  }
+  delete h;
+  if (err != cudaSuccess) {
+    cudaGetLastError();
+    return fail(FEC_ERR_CUDA, "demodulator tables: %s", cudaGetErrorString(err));
+  }
+  return FEC_OK;
+}
+
+int demod_check(const fec_demod_desc& d, uint32_t i, uint32_t flavour)
+{
+  if (flavour > FEC_DEMOD_FLAVOUR_AVX512) {
+    return fail(FEC_ERR_BAD_ARG, "flavour=%u", flavour);
+  }
+  if (d.qm != 1 && d.qm != 2 && d.qm != 4 && d.qm != 6 && d.qm != 8) {
+    return fail(FEC_ERR_BAD_ARG, "demodulation %u: qm=%u", i, d.qm);
+  }
+  if ((uint64_t)d.seq_offset + (uint64_t)d.nof_symbols * d.qm + 1600u > 0xffffffffull) {
+    return fail(FEC_ERR_BAD_ARG, "demodulation %u: sequence position beyond 2^32", i);
+  }
+  return FEC_OK;
+}
+
+int demod_launch(fec_engine* e, cudaStream_t st, const fec_demod_desc* d_descs, uint32_t n, uint32_t max_symbols,
+                 const float* d_symbols, const float* d_noise, int8_t* d_llr, uint32_t flavour)
+{
+  if (n == 0 || max_symbols == 0) {
+    return FEC_OK;
+  }
+  const uint32_t tiles = (max_symbols + FEC_DEMOD_THREADS - 1) / FEC_DEMOD_THREADS;
+  if (tiles > 65535u) {
+    return fail(FEC_ERR_BAD_ARG, "%u symbols in one demodulation call", max_symbols);
+  }
+  fec_demod_kernel<<<dim3(n, tiles), FEC_DEMOD_THREADS, 0, st>>>(d_descs, reinterpret_cast<const float2*>(d_symbols), d_noise,
+                                                                d_llr, e->d_dtab, flavour);
+  CU_TRY(cudaGetLastError());
+  e->launches.fetch_add(1);
+  return FEC_OK;
+}
+
+// Copies the symbols the descriptors use to the device and demodulates them into d_llr, whose first byte is LLR index l0.
+int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l0, size_t l1, int8_t* d_llr)
+{
+  if (!dm.descs || !dm.h_symbols || !dm.h_noise) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  int rc = demod_tables_alloc(e);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  size_t   s0 = ~(size_t)0, s1 = 0, covered = 0;
+  uint32_t max_symbols = 0;
+  e->dm_descs_host.assign(dm.descs, dm.descs + dm.n);
+  for (uint32_t i = 0; i < dm.n; ++i) {
+    fec_demod_desc& d = e->dm_descs_host[i];
+    rc                = demod_check(d, i, dm.flavour);
+    if (rc != FEC_OK) {
+      return rc;
+    }
+    const size_t bytes = (size_t)d.nof_symbols * d.qm;
+    if (d.sym_offset + d.nof_symbols > dm.nof_symbols || d.llr_offset < l0 || d.llr_offset + bytes > l1) {
+      return fail(FEC_ERR_BAD_ARG, "demodulation %u indexes outside the symbol or LLR buffers", i);
+    }
+    if (d.nof_symbols == 0) {
+      continue;
+    }
+    s0          = d.sym_offset < s0 ? (size_t)d.sym_offset : s0;
+    s1          = d.sym_offset + d.nof_symbols > s1 ? (size_t)(d.sym_offset + d.nof_symbols) : s1;
+    max_symbols = d.nof_symbols > max_symbols ? d.nof_symbols : max_symbols;
+    covered += bytes;
+  }
+  if (covered != l1 - l0) {
+    return fail(FEC_ERR_BAD_ARG, "the demodulation calls produce %zu LLRs, the transport blocks read %zu", covered, l1 - l0);
+  }
+  for (fec_demod_desc& d : e->dm_descs_host) {
+    d.sym_offset -= s0;
+    d.llr_offset -= l0;
+  }
+  rc = grow((void**)&e->d_dm_descs, &e->dm_descs_cap, (size_t)dm.n * sizeof(fec_demod_desc));
+  rc = (rc == FEC_OK) ? grow((void**)&e->d_dm_sym, &e->dm_sym_cap, (s1 - s0) * 2 * sizeof(float)) : rc;
+  rc = (rc == FEC_OK) ? grow((void**)&e->d_dm_noise, &e->dm_noise_cap, (s1 - s0) * sizeof(float)) : rc;
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  CU_TRY(cudaMemcpyAsync(e->d_dm_descs, e->dm_descs_host.data(), (size_t)dm.n * sizeof(fec_demod_desc), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(e->d_dm_sym, dm.h_symbols + 2 * s0, (s1 - s0) * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(e->d_dm_noise, dm.h_noise + s0, (s1 - s0) * sizeof(float), cudaMemcpyHostToDevice, st));
+  return demod_launch(e, st, e->d_dm_descs, dm.n, max_symbols, e->d_dm_sym, e->d_dm_noise, d_llr, dm.flavour);
+}
+} // namespace
+
+int fec_demod_launch_device(fec_engine* e, const fec_demod_desc* d_descs, uint32_t n, uint32_t max_symbols,
+                            const float* d_symbols, const float* d_noise_vars, int8_t* d_llr, uint32_t flavour)
+{
+  if (!e || !d_descs || !d_symbols || !d_noise_vars || !d_llr) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (flavour > FEC_DEMOD_FLAVOUR_AVX512) {
+    return fail(FEC_ERR_BAD_ARG, "flavour=%u", flavour);
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  int rc = demod_tables_alloc(e);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  return demod_launch(e, e->stream, d_descs, n, max_symbols, d_symbols, d_noise_vars, d_llr, flavour);
+}
+
+int fec_demod_run_host(fec_engine* e, const fec_demod_desc* h_descs, uint32_t n, const float* h_symbols,
+                       const float* h_noise_vars, size_t nof_symbols, int8_t* h_llr, size_t llr_bytes, uint32_t flavour)
+{
+  if (!e || !h_descs || !h_symbols || !h_noise_vars || !h_llr) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (n == 0) {
+    return FEC_OK;
+  }
+  size_t l0 = ~(size_t)0, l1 = 0, covered = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    const size_t bytes = (size_t)h_descs[i].nof_symbols * h_descs[i].qm;
+    if (h_descs[i].llr_offset + bytes > llr_bytes) {
+      return fail(FEC_ERR_BAD_ARG, "demodulation %u writes outside the LLR buffer", i);
+    }
+    if (bytes == 0) {
+      continue;
+    }
+    l0 = h_descs[i].llr_offset < l0 ? (size_t)h_descs[i].llr_offset : l0;
+    l1 = h_descs[i].llr_offset + bytes > l1 ? (size_t)(h_descs[i].llr_offset + bytes) : l1;
+    covered += bytes;
+  }
+  if (covered == 0) {
+    return FEC_OK;
+  }
+  if (covered != l1 - l0) {
+    return fail(FEC_ERR_BAD_ARG, "the demodulation calls must tile one contiguous span of the LLR buffer");
+  }
+  std::lock_guard<std::mutex> lk(e->run_mtx);
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  int rc = grow((void**)&e->d_dm_llr, &e->dm_llr_cap, l1 - l0);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  const demod_source dm = {h_descs, n, h_symbols, h_noise_vars, nof_symbols, flavour};
+  rc                    = demod_stage(e, e->stream, dm, l0, l1, e->d_dm_llr);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  CU_TRY(cudaMemcpyAsync(h_llr + l0, e->d_dm_llr, l1 - l0, cudaMemcpyDeviceToHost, e->stream));
+  CU_TRY(cudaStreamSynchronize(e->stream));
+  return FEC_OK;
+}
+
+int fec_tb_run_host_symbols(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots,
+                            const fec_demod_desc* h_demod, uint32_t n_demod, const float* h_symbols,
+                            const float* h_noise_vars, size_t nof_symbols, uint32_t flavour, uint8_t* h_out, size_t out_bytes,
+                            fec_tb_result* h_results, fec_cb_result* h_cb_results)
+{
+  if (!h_demod || !h_symbols || !h_noise_vars) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  const demod_source dm = {h_demod, n_demod, h_symbols, h_noise_vars, nof_symbols, flavour};
+  return tb_run(e, tbs, n, slots, nullptr, ~(size_t)0 >> 1, &dm, h_out, out_bytes, h_results, h_cb_results);
 }
 
 } // extern "C"

@@ -68,6 +68,16 @@ ENC_DESC_DTYPE = np.dtype({
     "itemsize": 40})
 
 
+# numpy mirror of struct fec_demod_desc (32 bytes)
+DEMOD_GENERIC, DEMOD_AVX2, DEMOD_AVX512 = 0, 1, 2
+DEMOD_FLAG_PI2_BPSK, DEMOD_FLAG_NO_DESCRAMBLE = 1, 2
+DEMOD_DESC_DTYPE = np.dtype({
+    "names": ["sym_offset", "llr_offset", "nof_symbols", "c_init", "seq_offset", "qm", "flags"],
+    "formats": ["<u8", "<u8", "<u4", "<u4", "<u4", "u1", "u1"],
+    "offsets": [0, 8, 16, 20, 24, 28, 29],
+    "itemsize": 32})
+
+
 class EngineCfg(C.Structure):
     _fields_ = [("device", C.c_int32), ("harq_slots", C.c_uint32), ("max_batch_cbs", C.c_uint32),
                 ("max_batch_llrs", C.c_uint32), ("nof_queues", C.c_uint32), ("scaling_factor", C.c_float),
@@ -79,7 +89,8 @@ EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_e
            "fec_launch_device", "fec_run_host", "fec_host_alloc", "fec_host_free", "fec_harq_free", "fec_harq_read",
            "fec_harq_write", "fec_harq_flush", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
            "fec_queue_poll", "fec_queue_fetch", "fec_tb_segment", "fec_tb_run_host", "fec_tb_reset_slots",
-           "fec_enc_desc_prepare", "fec_encode_launch_device", "fec_encode_run_host"]
+           "fec_enc_desc_prepare", "fec_encode_launch_device", "fec_encode_run_host", "fec_demod_launch_device",
+           "fec_demod_run_host", "fec_tb_run_host_symbols"]
 
 _lib = None
 
@@ -134,6 +145,13 @@ def load_library():
     lib.fec_encode_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
     lib.fec_encode_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p,
                                         C.c_size_t]
+    lib.fec_demod_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_uint32]
+    lib.fec_demod_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                       C.c_size_t, C.c_uint32]
+    lib.fec_tb_run_host_symbols.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32,
+                                            C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p, C.c_size_t,
+                                            C.c_void_p, C.c_void_p]
     _lib = lib
     return lib
 
@@ -164,6 +182,23 @@ def enc_desc_prepare(desc):
     for i in range(arr.size):
         _check(lib, lib.fec_enc_desc_prepare(arr[i:i + 1].ctypes.data))
     return desc
+
+
+def make_demod_descs(n):
+    return np.zeros(n, DEMOD_DESC_DTYPE)
+
+
+def codeword_demod_descs(blocks, qm, c_init, sym_offset=0, llr_offset=0, flags=0):
+    """The demodulation calls of one PUSCH codeword as pusch_demodulator_impl issues them (pusch_demodulator_impl.cpp:
+    262-400): one per block of symbols (one OFDM symbol each), the scrambling sequence running on across the blocks."""
+    d = make_demod_descs(len(blocks))
+    pos = 0
+    for i, n in enumerate(blocks):
+        d["sym_offset"][i], d["llr_offset"][i], d["nof_symbols"][i] = sym_offset + pos, llr_offset + pos * qm, n
+        d["seq_offset"][i] = pos * qm
+        pos += int(n)
+    d["c_init"], d["qm"], d["flags"] = c_init, qm, flags
+    return d
 
 
 def make_tb_descs(n):
@@ -293,6 +328,44 @@ class FecEngine:
                                                   None if cbr is None else cbr.ctypes.data))
         return (res, cbr.reshape(n, MAX_TB_CBS)) if cb_results else res
 
+    def demod_launch_device(self, d_descs_ptr, n, max_symbols, d_sym_ptr, d_noise_ptr, d_llr_ptr, flavour=DEMOD_AVX512):
+        """Asynchronous soft-demodulation launch on self.stream; all pointers are device addresses (ints)."""
+        _check(self.lib, self.lib.fec_demod_launch_device(self.h, d_descs_ptr, n, max_symbols, d_sym_ptr, d_noise_ptr,
+                                                          d_llr_ptr, flavour))
+
+    def demod_run_host(self, descs, symbols, noise_vars, llr, flavour=DEMOD_AVX512):
+        """fec_demod_run_host: soft demodulation + descrambling, H2D -> kernel -> D2H of the LLRs, synchronous."""
+        assert descs.dtype == DEMOD_DESC_DTYPE and descs.flags.c_contiguous
+        symbols = np.ascontiguousarray(symbols, np.float32).reshape(-1, 2)
+        noise_vars = np.ascontiguousarray(noise_vars, np.float32).reshape(-1)
+        assert symbols.shape[0] == noise_vars.size and llr.dtype == np.int8 and llr.flags.c_contiguous
+        _check(self.lib, self.lib.fec_demod_run_host(self.h, descs.ctypes.data, descs.size, symbols.ctypes.data,
+                                                     noise_vars.ctypes.data, noise_vars.size, llr.ctypes.data, llr.nbytes,
+                                                     flavour))
+        return llr
+
+    def tb_run_host_symbols(self, tbs, demod, symbols, noise_vars, out, slots=None, cb_results=False,
+                            flavour=DEMOD_AVX512):
+        """fec_tb_run_host_symbols: equalised symbols in, transport blocks out; the LLRs only exist on the device.
+        symbols / noise_vars are float32 numpy arrays or (ptr, nof_symbols) tuples of pinned memory."""
+        assert tbs.dtype == TB_DESC_DTYPE and tbs.flags.c_contiguous
+        assert demod.dtype == DEMOD_DESC_DTYPE and demod.flags.c_contiguous
+        n = tbs.size
+        res = np.zeros(n, TB_RESULT_DTYPE)
+        cbr = np.zeros(n * MAX_TB_CBS, RESULT_DTYPE) if cb_results else None
+        if isinstance(symbols, tuple):
+            sp, nsym, np_ = symbols[0], symbols[1], noise_vars[0]
+        else:
+            symbols = np.ascontiguousarray(symbols, np.float32).reshape(-1, 2)
+            noise_vars = np.ascontiguousarray(noise_vars, np.float32).reshape(-1)
+            sp, nsym, np_ = symbols.ctypes.data, noise_vars.size, noise_vars.ctypes.data
+        op, ob = (out[0], out[1]) if isinstance(out, tuple) else (out.ctypes.data, out.nbytes)
+        sl = None if slots is None else np.ascontiguousarray(slots, np.uint32)
+        _check(self.lib, self.lib.fec_tb_run_host_symbols(self.h, tbs.ctypes.data, n, None if sl is None else sl.ctypes.data,
+                                                          demod.ctypes.data, demod.size, sp, np_, nsym, flavour, op, ob,
+                                                          res.ctypes.data, None if cbr is None else cbr.ctypes.data))
+        return (res, cbr.reshape(n, MAX_TB_CBS)) if cb_results else res
+
     def tb_reset_slots(self, first_slot, n):
         _check(self.lib, self.lib.fec_tb_reset_slots(self.h, first_slot, n))
 
@@ -358,6 +431,30 @@ class CodeblockMetadata:
         self.nof_filler_bits = nof_filler_bits
         self.nof_crc_bits = nof_crc_bits
         self.rm_length = rm_length
+
+
+class DemodulationMapper:
+    """demodulation_mapper (include/srsran/phy/upper/channel_modulation/demodulation_mapper.h:47-69):
+    demodulate_soft(llrs, symbols, noise_vars, mod). `mod` is the modulation's name as the reference prints it
+    ("BPSK", "pi/2-BPSK", "QPSK", "16QAM", "64QAM", "256QAM"); `flavour` the reference build to be identical to."""
+
+    BITS = {"BPSK": 1, "pi/2-BPSK": 1, "QPSK": 2, "16QAM": 4, "64QAM": 6, "256QAM": 8}
+
+    def __init__(self, engine, flavour=DEMOD_AVX512):
+        self.engine = engine
+        self.flavour = flavour
+
+    def demodulate_soft(self, llrs, symbols, noise_vars, mod):
+        qm = self.BITS[mod]
+        symbols = np.ascontiguousarray(symbols).view(np.float32).reshape(-1, 2)
+        if symbols.shape[0] != np.size(noise_vars):
+            raise FecError("Inputs symbols and noise_vars must have the same length.")
+        if symbols.shape[0] * qm != llrs.size:
+            raise FecError("Input and output lengths are incompatible.")
+        d = make_demod_descs(1)
+        d["nof_symbols"], d["qm"] = symbols.shape[0], qm
+        d["flags"] = DEMOD_FLAG_NO_DESCRAMBLE | (DEMOD_FLAG_PI2_BPSK if mod == "pi/2-BPSK" else 0)
+        return self.engine.demod_run_host(d, symbols, noise_vars, llrs, self.flavour)
 
 
 class LdpcRateDematcher:
