@@ -351,6 +351,136 @@ def bench_pdsch_encode(fec, eng, torch, dev, stream, args):
     return out
 
 
+def measured_hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback 6650 GB/s"
+
+
+def gold_bits(c_init, nbits):
+    """TS 38.211 5.2.1 sequence, 28 bits per step on Python integers (input generation only)."""
+    x1, x2, out = 1, c_init & 0x7fffffff, []
+    m28 = (1 << 28) - 1
+
+    def step(x, taps):
+        nxt = 0
+        for t in taps:
+            nxt ^= x >> t
+        return ((x >> 28) | ((nxt & m28) << 3)) & 0x7fffffff
+
+    bits = np.zeros(((1600 + nbits) // 28 + 2) * 28, np.uint8)
+    for k in range(bits.size // 28):
+        c = (x1 ^ x2) & m28
+        bits[k * 28:(k + 1) * 28] = (c >> np.arange(28)) & 1
+        x1, x2 = step(x1, (0, 3)), step(x2, (0, 1, 2, 3))
+    return bits[1600:1600 + nbits]
+
+
+def qam_modulate(bits, qm):
+    """TS 38.211 5.1 mapper (input generation only)."""
+    s = 1 - 2 * bits.reshape(-1, qm).astype(np.int64)
+    m = qm // 2
+    re, im = s[:, qm - 2], s[:, qm - 1]
+    for i in range(m - 2, -1, -1):
+        re, im = s[:, 2 * i] * ((1 << (m - 1 - i)) - re), s[:, 2 * i + 1] * ((1 << (m - 1 - i)) - im)
+    return np.stack([re, im], 1).astype(np.float32) / np.float32(np.sqrt({2: 2.0, 4: 10.0, 6: 42.0, 8: 170.0}[qm]))
+
+
+def bench_pusch_demod(fec, eng, torch, dev, stream, args):
+    """The step in front of the path: soft demodulation + descrambling on the device. Workload: the
+    config-3 codeword (1,365,504 soft bits of 256QAM = 170,688 equalised symbols, one demodulation call per OFDM symbol of
+    273 PRB x 4 layers), all-zero transport block. Device-resident throughput of the kernel, and the latency of one
+    transport block from symbols (fec_tb_run_host_symbols) next to the LLR-input call of bench_transport_block."""
+    n_cb, fill, qm = 152, 16, 8
+    Es = np.array([8960] * 40 + [8992] * (n_cb - 40), np.uint32)
+    G = int(Es.sum())
+    info_bits = n_cb * (K - fill - 24) - 24
+    nsym = G // qm
+    blocks = [3276 * 4] * (nsym // (3276 * 4)) + ([nsym % (3276 * 4)] if nsym % (3276 * 4) else [])
+    c_init = 0x4601 * 32768 + 41
+    rng = np.random.default_rng(99)
+    nv = 10.0 ** (-args.demod_esn0 / 10.0)
+    sym = qam_modulate(gold_bits(c_init, G), qm)  # the all-zero codeword, scrambled
+    sym = sym + (np.sqrt(nv / 2) * rng.standard_normal(sym.shape)).astype(np.float32)
+    nvs = np.full(nsym, nv, np.float32)
+    n_tb = max(1, min(args.cbs // n_cb, 46))
+    dm1 = fec.codeword_demod_descs(blocks, qm, c_init)
+    dm = fec.make_demod_descs(n_tb * len(blocks))
+    for t in range(n_tb):
+        dm[t * len(blocks):(t + 1) * len(blocks)] = fec.codeword_demod_descs(blocks, qm, c_init, sym_offset=t * nsym,
+                                                                             llr_offset=t * G)
+    d_sym = torch.from_numpy(np.tile(sym, (n_tb, 1))).to(dev)
+    d_nv = torch.from_numpy(np.tile(nvs, n_tb)).to(dev)
+    d_llr = torch.zeros(n_tb * G, dtype=torch.int8, device=dev)
+    d_dm = torch.from_numpy(dm.view(np.uint8).copy()).to(dev)
+    torch.cuda.synchronize()
+
+    def step():
+        eng.demod_launch_device(d_dm.data_ptr(), dm.size, max(blocks), d_sym.data_ptr(), d_nv.data_ptr(), d_llr.data_ptr())
+
+    for _ in range(3):
+        step()
+    reps = 20
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(reps):
+            step()
+        e1.record(stream)
+    stream.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    # one transport block from symbols, pinned host buffers
+    tbd = fec.make_tb_descs(1)
+    tbd["tbs"], tbd["nof_llrs"], tbd["base_graph"], tbd["qm"], tbd["nof_layers"] = info_bits, G, BG, qm, 4
+    tbd["max_iter"], tbd["flags"], tbd["harq_slot"] = MAX_ITER, fec.FLAG_NEW_DATA | fec.FLAG_EARLY_STOP, 0
+    t_sym, t_nv = torch.from_numpy(sym).pin_memory(), torch.from_numpy(nvs).pin_memory()
+    t_tb = torch.zeros(info_bits // 8, dtype=torch.uint8).pin_memory()
+    lat, ok = [], 0
+    for i in range(220):
+        t0 = time.perf_counter()
+        r = eng.tb_run_host_symbols(tbd, dm1, (t_sym.data_ptr(), nsym), (t_nv.data_ptr(), nsym),
+                                    (t_tb.data_ptr(), t_tb.numel()))
+        lat.append((time.perf_counter() - t0) * 1e6)
+        ok += int(r["tb_crc_ok"][0])
+    lat = np.array(lat[20:])
+    algo = n_tb * nsym * (12 + qm)
+    peak, peak_src = measured_hbm_peak()
+    out = {"workload": "config-3 codeword: %d symbols of 256QAM -> %d soft bits, %d demodulation calls (one per OFDM symbol "
+                       "of 273 PRB x 4 layers), descrambling included, reference flavour avx512, Es/N0 %.1f dB"
+                       % (nsym, G, len(blocks), args.demod_esn0),
+           "value": n_tb * G / (ms * 1e-3) / 1e9, "unit": "G soft bits/s", "codewords_per_launch": n_tb, "ms_per_launch": ms,
+           "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "peak_source": peak_src,
+                        "unit": "GB/s", "frac": algo / (ms * 1e-3) / 1e9 / peak,
+                        "algorithmic_bytes_per_symbol": 12 + qm},
+           "tb_from_symbols_latency_us": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
+                                          "samples": int(lat.size), "tb_crc_ok_fraction": ok / 220,
+                                          "h2d_bytes": nsym * 12, "d2h_bytes": info_bits // 8,
+                                          "api": "fec_tb_run_host_symbols: symbols + noise variances in, demodulation, "
+                                                 "descrambling, segmentation, decoding, TB CRC on the device, TB bytes back"}}
+    if not args.no_cpu_baseline:
+        try:
+            orc = ge.load_oracle()
+            if orc.RefDemod.available(2):
+                ref = orc.RefDemod(2)
+                llr = np.zeros(G, np.int8)
+                t0, cnt = time.perf_counter(), 0
+                while time.perf_counter() - t0 < 2.0:
+                    pos = 0
+                    for b in blocks:
+                        llr[pos * qm:(pos + b) * qm] = ref.demodulate_soft(qm, sym[pos:pos + b], nvs[pos:pos + b])
+                        pos += b
+                    ref.apply_xor_llr(c_init, 0, llr)
+                    cnt += 1
+                out["cpu_baseline"] = {"value": cnt * G / (time.perf_counter() - t0) / 1e9, "unit": "G soft bits/s", "cores": 1,
+                                       "kind": "reference", "sample": "%d codewords through the reference's "
+                                       "demodulation_mapper_impl (AVX-512 build) + pseudo_random_generator apply_xor, "
+                                       "one thread (oracle/_ref/libref_demod_avx512.so)" % cnt}
+        except Exception as ex:  # the checker is optional here
+            out["cpu_baseline"] = {"unavailable": str(ex)[:100]}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -454,6 +584,9 @@ def run_ours(args):
     enc = None
     if not args.no_enc and rank == 0:
         enc = bench_pdsch_encode(fec, eng, torch, dev, stream, args)
+    dmd = None
+    if not args.no_demod and rank == 0:
+        dmd = bench_pusch_demod(fec, eng, torch, dev, stream, args)
 
     # ---- e2e: host buffers through fec_run_host (H2D + kernels + D2H inside the timed region) --------------------------
     res_h = np.zeros(n, fec.RESULT_DTYPE)
@@ -494,7 +627,7 @@ def run_ours(args):
                 "crc_pass_fraction": float(passed.mean()),
                 "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + K // 8 + 48),
                         "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
-                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb, "pdsch_encode": enc,
+                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb, "pdsch_encode": enc, "pusch_demod": dmd,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                              "frac": achieved / peak_gbs,
                              # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture
@@ -536,6 +669,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-tb", action="store_true", help="skip the config-3 transport-block latency measurement")
     ap.add_argument("--no-enc", action="store_true", help="skip the PDSCH encoder (downlink twin) measurement")
+    ap.add_argument("--no-demod", action="store_true", help="skip the soft demodulator measurement")
+    ap.add_argument("--demod-esn0", type=float, default=30.0, help="Es/N0 of the 256QAM symbols of the demodulator bench")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     return run_reference(args) if args.impl == "reference" else run_ours(args)

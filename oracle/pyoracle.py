@@ -389,6 +389,37 @@ def tb_transmit(oracle, cbs, tbs, bg, rv, qm, Nref, nof_layers, nof_llrs, esn0_d
     return oracle.awgn_llr(tx, esn0_db, seed)
 
 
+def modulate(bits, qm):
+    """TS 38.211 5.1.2-5.1.6 modulation mapper (input generation for the tests): bits -> complex64 symbols."""
+    b = np.asarray(bits, np.int64).reshape(-1, qm)
+    s = 1 - 2 * b
+    if qm == 1:
+        return ((s[:, 0] + 1j * s[:, 0]) / np.sqrt(2)).astype(np.complex64)
+    m = qm // 2
+    re, im = s[:, qm - 2], s[:, qm - 1]
+    for i in range(m - 2, -1, -1):
+        re = s[:, 2 * i] * ((1 << (m - 1 - i)) - re)
+        im = s[:, 2 * i + 1] * ((1 << (m - 1 - i)) - im)
+    norm = {1: 2.0, 2: 2.0, 4: 10.0, 6: 42.0, 8: 170.0}[qm]
+    return ((re + 1j * im) / np.sqrt(norm)).astype(np.complex64)
+
+
+def tb_transmit_symbols(oracle, demod, cbs, tbs, bg, rv, qm, Nref, nof_layers, nof_llrs, esn0_db, c_init, seed):
+    """Rate matching + concatenation + scrambling + modulation + complex AWGN: the equalised symbols (float32 re, im) and
+    the noise variance of each symbol for one (re)transmission."""
+    g = tb_geometry(tbs, bg, qm, nof_layers, nof_llrs)
+    tx = np.concatenate([oracle.rate_match(bg, g["Z"], cbs[r], g["rm"][r], rv, qm, Nref, g["fillers"])
+                         for r in range(g["C"])])
+    seq = np.unpackbits(demod.gold_sequence(c_init, 0, tx.size))[:tx.size]
+    x = modulate(tx ^ seq, qm)
+    rng = np.random.default_rng(seed)
+    nv = 10.0 ** (-esn0_db / 10.0)
+    noise = (rng.normal(0, np.sqrt(nv / 2), x.size) + 1j * rng.normal(0, np.sqrt(nv / 2), x.size)).astype(np.complex64)
+    # per-symbol noise variance estimates scatter around the truth, as a channel estimator's would
+    nvs = (nv * rng.uniform(0.8, 1.25, x.size)).astype(np.float32)
+    return np.ascontiguousarray((x + noise).astype(np.complex64)).view(np.float32).reshape(-1, 2), nvs
+
+
 class TbOracle:
     """Whole transport blocks over the C restatement: the flow of pusch_decoder_impl (new_data :88-130,
     fork_codeblock_task :308-372, join_and_notify :374-437, concatenate_codeblocks :439-493) with the rx buffer (soft bits,

@@ -111,3 +111,63 @@ def test_long_sequence_offsets(fec, engine, dorc):
         engine.demod_run_host(d, sym, nv, llr)
         seq = dorc.gold_sequence(0x5a5a5a5, seq_offset, n * qm)
         assert (llr == dorc.descramble(seq, dorc.demodulate_soft(2, qm, sym, nv))).all(), seq_offset
+
+
+def test_transport_blocks_from_symbols(fec, engine, oracle, orc, dorc):
+    """fec_tb_run_host_symbols: equalised symbols in, transport blocks out, the LLRs only ever on the device. Several
+    transport blocks per call (every modulation, 1-4 layers, per-OFDM-symbol demodulation calls), a first transmission
+    below the waterfall and a retransmission that combines; against the oracle chain demodulate -> descramble -> decode."""
+    rng = np.random.default_rng(21)
+    tbo = orc.TbOracle(oracle)
+    tbl = []
+    for i, (qm, nl, bg, tbs) in enumerate([(8, 4, 1, 60000), (6, 2, 1, 25000), (4, 1, 2, 3000), (2, 1, 2, 640), (1, 1, 2, 200),
+                                            (8, 1, 1, 9000)]):
+        B = tbs + (16 if tbs <= 3824 else 24)
+        nsym = -(-int(B / 0.6) // (qm * nl)) * nl
+        tb = rng.integers(0, 256, tbs // 8).astype(np.uint8)
+        tbl.append(dict(qm=qm, nl=nl, bg=bg, tbs=tbs, G=nsym * qm, tb=tb, cbs=orc.tb_encode(oracle, tb, bg),
+                        c_init=(1000 + i) * 32768 + 17 * i, slot=200 * i))
+    # Es/N0 a little under what the rate needs so that most blocks fail the first time and pass after combining
+    need = {1: -1.5, 2: 1.0, 4: 6.5, 6: 11.0, 8: 15.5}
+    delivered = 0
+    for t, rv in enumerate([0, 2]):
+        d = fec.make_tb_descs(len(tbl))
+        dm, syms, nvs, want_llr, pos_s, pos_l = [], [], [], [], 0, 0
+        for i, T in enumerate(tbl):
+            sym, nv = orc.tb_transmit_symbols(oracle, dorc, T["cbs"], T["tbs"], T["bg"], rv, T["qm"], 0, T["nl"], T["G"],
+                                              need[T["qm"]] - 1.0, T["c_init"], seed=100 * t + i)
+            nsym = T["G"] // T["qm"]
+            per = -(-nsym // 13)
+            blocks = [min(per, nsym - k) for k in range(0, nsym, per)]
+            dm.append(fec.codeword_demod_descs(blocks, T["qm"], T["c_init"], sym_offset=pos_s, llr_offset=pos_l))
+            syms.append(sym), nvs.append(nv)
+            want_llr.append(dorc.codeword(2, T["qm"], blocks, sym, nv, T["c_init"]))
+            d["tbs"][i], d["nof_llrs"][i], d["base_graph"][i], d["qm"][i], d["nof_layers"][i] = T["tbs"], T["G"], T["bg"], T["qm"], T["nl"]
+            d["rv"][i], d["max_iter"][i], d["harq_slot"][i] = rv, 6, T["slot"]
+            d["flags"][i] = (fec.FLAG_NEW_DATA if t == 0 else 0) | fec.FLAG_EARLY_STOP
+            d["llr_offset"][i], d["out_offset"][i] = pos_l, sum(x["tbs"] // 8 for x in tbl[:i])
+            pos_s += nsym
+            pos_l += T["G"]
+        alld = fec.make_demod_descs(sum(len(x) for x in dm))
+        k = 0
+        for x in dm:
+            alld[k:k + len(x)] = x
+            k += len(x)
+        out = np.zeros(sum(x["tbs"] // 8 for x in tbl), np.uint8)
+        res = engine.tb_run_host_symbols(d, alld, np.concatenate(syms), np.concatenate(nvs), out)
+        for i, T in enumerate(tbl):
+            if T.get("done"):
+                continue
+            want = np.zeros(T["tbs"] // 8, np.uint8)
+            w = tbo.decode(i, T["tbs"], T["bg"], rv, T["qm"], 0, T["nl"], t == 0, 6, True, want_llr[i], want)
+            assert bool(res["tb_crc_ok"][i]) == w["tb_crc_ok"], (t, i)
+            assert int(res["nof_cb_decoded"][i]) == len(w["iters"]) and int(res["nof_codeblocks"][i]) == w["nof_codeblocks"]
+            o0 = int(d["out_offset"][i])
+            if w["tb_crc_ok"]:
+                assert (out[o0:o0 + T["tbs"] // 8] == want).all() and (want == T["tb"]).all(), (t, i)
+                T["done"] = True
+                delivered += 1
+    assert delivered >= 4
+    # a gap in the demodulation calls is refused (the transport blocks would read stale LLRs)
+    with pytest.raises(fec.FecError):
+        engine.tb_run_host_symbols(d, alld[:-1], np.concatenate(syms), np.concatenate(nvs), out)
