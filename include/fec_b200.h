@@ -302,17 +302,22 @@ typedef struct fec_demod_desc {
   uint32_t nof_symbols;
   uint32_t c_init;       /* scrambling sequence initial state                                                              */
   uint32_t seq_offset;   /* position of the call's first soft bit in the sequence (soft bits of the codeword before it)    */
+  uint32_t x1_state;     /* filled by fec_demod_desc_prepare: the two LFSR states at that position                         */
+  uint32_t x2_state;
   uint8_t  qm;           /* 1, 2, 4, 6, 8                                                                                  */
   uint8_t  flags;        /* FEC_DEMOD_FLAG_*                                                                               */
   uint8_t  reserved[2];
-} fec_demod_desc; /* 32 bytes */
+} fec_demod_desc; /* 40 bytes */
 
-/* Device-resident batch: n descriptors, symbols, noise variances and the LLR buffer already in HBM; asynchronous on
- * fec_engine_stream(). max_symbols >= the largest nof_symbols of the batch. */
+/* Checks a demodulation descriptor and fills in x1_state / x2_state (host only, no GPU needed). */
+int fec_demod_desc_prepare(fec_demod_desc* d);
+
+/* Device-resident batch: n prepared descriptors, symbols, noise variances and the LLR buffer already in HBM; asynchronous
+ * on fec_engine_stream(). max_symbols >= the largest nof_symbols of the batch. */
 int fec_demod_launch_device(fec_engine* e, const fec_demod_desc* d_descs, uint32_t n, uint32_t max_symbols,
                             const float* d_symbols, const float* d_noise_vars, int8_t* d_llr, uint32_t flavour);
 /* Host buffers: H2D + kernel + D2H of the LLR span the descriptors cover, synchronous (the mirror of demodulate_soft;
- * the production path is fec_tb_run_host_symbols, where the LLRs stay on the device). */
+ * the production path is fec_tb_run_host_symbols, where the LLRs stay on the device). Descriptors need not be prepared. */
 int fec_demod_run_host(fec_engine* e, const fec_demod_desc* h_descs, uint32_t n, const float* h_symbols,
                        const float* h_noise_vars, size_t nof_symbols, int8_t* h_llr, size_t llr_bytes, uint32_t flavour);
 /* fec_tb_run_host with the codeword LLRs produced on the device: the demodulation descriptors write the same LLR index space

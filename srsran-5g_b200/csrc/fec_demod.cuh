@@ -10,9 +10,11 @@
 // operation spelled with an intrinsic (__fmul_rn, __fmaf_rn, __fdiv_rn ...): nvcc must neither fuse nor split anything.
 //
 // Work layout: one CTA per tile of 256 consecutive symbols of one call, one thread per symbol.
-//   1. warp 0 jumps the two 31-bit LFSRs to the first bit of the tile (matrix powers A^(2^k), one lane per state bit),
+//   1. warp 0 jumps the two 31-bit LFSRs from the call's first soft bit (states prepared on the host, in the descriptor) to
+//      the first bit of the tile (matrix powers A^(2^k), one lane per state bit, one product per set bit of the distance),
 //   2. all threads expand the tile's scrambling bits (row vectors B[q] = e0^T A^q, one parity per bit, ballot per word),
-//   3. each thread demodulates its symbol, flips signs, and parks the Qm bytes in shared memory,
+//   3. each thread demodulates its symbol (code specialised per modulation and flavour, tables in shared memory), flips
+//      signs four LLRs at a time, and parks the Qm bytes in shared memory,
 //   4. the tile is written out in 16-byte rows (shared memory staged at the destination's 16-byte phase).
 // HBM traffic: 12 bytes in (symbol + noise variance) and Qm bytes out per symbol.
 #pragma once
@@ -22,6 +24,7 @@
 
 #define FEC_DEMOD_THREADS 256
 #define FEC_DEMOD_TILE_WORDS 64 /* 256 symbols x 8 bits */
+static_assert(sizeof(fec_demod_desc) == 40, "fec_demod_desc layout");
 
 struct fec_demod_tables {
   // piecewise-linear max-log LLR, rows 0-2: 64QAM bit pairs (0,1) (2,3) (4,5); rows 3-6: 256QAM bit pairs
@@ -120,18 +123,57 @@ inline void fec_demod_build_tables(fec_demod_tables* t)
   }
 }
 
+// LFSR states (x1, x2) at sequence position `pos` are prepared on the host: the same 2^k-step matrices by COLUMN, so that a
+// jump is one XOR per set state bit.
+struct fec_demod_host_jump {
+  uint32_t col[2][32][32];
+};
+
+inline void fec_demod_build_jump(const fec_demod_tables* t, fec_demod_host_jump* j)
+{
+  memset(j, 0, sizeof(*j));
+  for (int g = 0; g < 2; ++g) {
+    for (int k = 0; k < 32; ++k) {
+      for (int r = 0; r < 31; ++r) {
+        for (int c = 0; c < 31; ++c) {
+          j->col[g][k][c] |= ((t->A[g][k][r] >> c) & 1u) << r;
+        }
+      }
+    }
+  }
+}
+
+// c(pos) = bit 0 of x1 ^ x2: 1600 + pos steps from the initial states (x1 = 1, x2 = c_init).
+inline void fec_demod_lfsr_states(const fec_demod_host_jump* j, uint32_t c_init, uint32_t pos, uint32_t* x1, uint32_t* x2)
+{
+  uint32_t s[2] = {1u, c_init & 0x7fffffffu};
+  for (uint64_t p = 1600ull + pos, k = 0; p != 0; p >>= 1, ++k) {
+    if (p & 1u) {
+      for (int g = 0; g < 2; ++g) {
+        uint32_t nx = 0;
+        for (uint32_t v = s[g]; v != 0; v &= v - 1) {
+          nx ^= j->col[g][k][__builtin_ctz(v)];
+        }
+        s[g] = nx;
+      }
+    }
+  }
+  *x1 = s[0];
+  *x2 = s[1];
+}
+
 // ---- device side ------------------------------------------------------------------------------------------------------------
 #define FEC_NEAR_ZERO 1e-9f /* include/srsran/support/math/math_utils.h:39 */
 
-// x86 float -> int32: out of range and NaN give 0x80000000 (CUDA's own conversion saturates instead).
-__device__ __forceinline__ int fec_cvt_i32(float f)
+// x86 float -> int32 of an already floored value: out of range and NaN give 0x80000000 (CUDA's conversion saturates).
+__device__ __forceinline__ int fec_x86_cvt(float f)
 {
-  return (f >= -2147483648.0f && f < 2147483648.0f) ? (int)f : (int)0x80000000;
+  return (f >= -2147483648.0f && f < 2147483648.0f) ? __float2int_rd(f) : (int)0x80000000;
 }
 
 __device__ __forceinline__ int fec_dm_clamp(int v, int lo, int hi)
 {
-  return v < lo ? lo : (v > hi ? hi : v);
+  return max(lo, min(v, hi));
 }
 
 __device__ __forceinline__ float fec_safe_rcp(float n)
@@ -139,168 +181,211 @@ __device__ __forceinline__ float fec_safe_rcp(float n)
   return (n > 0) ? __fdiv_rn(1.0f, n) : 0.0f;
 }
 
-// log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:90-99).
+// log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:90-99): clip, divide, multiply, round half away from zero.
 __device__ __forceinline__ int fec_quant_scalar(float v, float range)
 {
   float c = v;
   if (fabsf(v) > range) {
     c = copysignf(range, v);
   }
-  float q = __fdiv_rn(c, range);
-  q       = __fmul_rn(q, 120.0f);
-  q       = roundf(q);
+  const float q = roundf(__fmul_rn(__fdiv_rn(c, range), 120.0f));
   return (q != q) ? 0 : (int)q;
 }
 
-// mm256::quantize_ps (avx2_helpers.h:123-166). scale = 120 / range_limit (6 or 5, exact).
-__device__ __forceinline__ int fec_quant_256(float v, float scale)
+// mm256::quantize_ps (avx2_helpers.h:123-166) and mm512::quantize_ps (avx512_helpers.h:48-107) are the same function of one
+// value: a NaN gives 0 (bounds check after the conversion / masked multiply), otherwise scale, clamp to +-120, round to
+// nearest even. scale = 120 / range_limit (6 or 5, exact).
+__device__ __forceinline__ int fec_quant_simd(float v, float scale)
 {
-  float q = __fmul_rn(v, scale);
-  if (q > 120.0f) {
-    q = 120.0f;
-  }
-  if (q < -120.0f) {
-    q = -120.0f;
-  }
-  int i = fec_cvt_i32(rintf(q));
-  return (i > 120 || i < -120) ? 0 : i;
-}
-
-// mm512::quantize_ps (avx512_helpers.h:48-107).
-__device__ __forceinline__ int fec_quant_512(float v, float scale)
-{
-  if (v != v) {
-    return 0;
-  }
-  float q = __fmul_rn(scale, v);
-  q       = q < 120.0f ? q : 120.0f;
-  q       = q > -120.0f ? q : -120.0f;
-  return fec_cvt_i32(rintf(q));
+  const float q = __fmul_rn(v, scale);
+  return (q != q) ? 0 : __float2int_rn(fminf(fmaxf(q, -120.0f), 120.0f));
 }
 
 enum { FEC_PATH_SCALAR = 0, FEC_PATH_256 = 1, FEC_PATH_512 = 2 };
 
-// interval_function in its three spellings (demodulation_mapper_intervals.h:36-64, avx2_helpers.h:168-249,
-// avx512_helpers.h:156-241), then the matching quantiser.
-__device__ __forceinline__ int fec_interval_llr(const fec_demod_tables* __restrict__ T, int row, int path, bool fma, float x,
-                                                float rcp)
+// Per-CTA copy of the tables a tile needs: [row][interval] = (slope, intercept), then width and 1 / width of each row.
+struct fec_demod_smem_tab {
+  float2 lin[7][16];
+  float  width[7];
+  float  rcp_width[7];
+};
+
+// compute_interval_idx in its three spellings (demodulation_mapper_intervals.h:36-43, avx2_helpers.h:168-187,
+// avx512_helpers.h:156-171). Rows with the same interval width and count share the index. `tame` = |x| < 16384: the
+// conversion cannot leave the int32 range, so the x86 out-of-range rule needs no emulation.
+template <int PATH, int ROW, int N>
+__device__ __forceinline__ int fec_interval_idx(const fec_demod_smem_tab& T, float x, bool tame)
 {
-  const int n = T->nof[row];
-  int       idx;
-  if (path == FEC_PATH_512) {
-    idx = fec_dm_clamp(fec_cvt_i32(floorf(__fmaf_rn(x, T->rcp_width[row], (float)(n / 2)))), 0, n - 1);
-  } else if (path == FEC_PATH_256) {
-    idx = fec_dm_clamp((int)((uint32_t)fec_cvt_i32(floorf(__fmul_rn(x, T->rcp_width[row]))) + (uint32_t)(n / 2)), 0, n - 1);
-  } else {
-    idx = fec_dm_clamp(fec_cvt_i32(floorf(__fdiv_rn(x, T->width[row]))) + n / 2, 0, n - 1);
+  if (PATH == FEC_PATH_512) {
+    const float t = __fmaf_rn(x, T.rcp_width[ROW], (float)(N / 2));
+    return fec_dm_clamp(tame ? __float2int_rd(t) : fec_x86_cvt(floorf(t)), 0, N - 1);
   }
-  const float s = T->slope[row][idx], c = T->icpt[row][idx];
-  float       l = (fma || path == FEC_PATH_512) ? __fmaf_rn(s, x, c) : __fadd_rn(__fmul_rn(s, x), c);
-  l             = __fmul_rn(l, rcp);
-  if (path == FEC_PATH_512) {
-    return fec_quant_512((fabsf(x) > FEC_NEAR_ZERO) ? l : 0.0f, 6.0f);
+  if (PATH == FEC_PATH_256) {
+    const float t = __fmul_rn(x, T.rcp_width[ROW]);
+    return fec_dm_clamp((int)((uint32_t)(tame ? __float2int_rd(t) : fec_x86_cvt(floorf(t))) + (uint32_t)(N / 2)), 0, N - 1);
   }
-  if (path == FEC_PATH_256) {
-    return fec_quant_256((fabsf(x) <= FEC_NEAR_ZERO) ? 0.0f : l, 6.0f);
-  }
-  return fec_quant_scalar(l, 20.0f);
+  const float t = __fdiv_rn(x, T.width[ROW]);
+  return fec_dm_clamp((tame ? __float2int_rd(t) : fec_x86_cvt(floorf(t))) + N / 2, 0, N - 1);
 }
 
-// All Qm LLRs of one symbol (before descrambling) into out[0 .. qm).
-__device__ __forceinline__ void fec_demod_symbol(const fec_demod_tables* __restrict__ T, int qm, bool pi2_odd, int path, bool fma,
-                                                 float re, float im, float nv, int* out)
+// interval_function (demodulation_mapper_intervals.h:45-64, avx2_helpers.h:217-249, avx512_helpers.h:214-241) for a known
+// interval, then the matching quantiser. `live` = |x| > near_zero (the SIMD paths force 0 otherwise).
+template <int PATH, bool FMA, int ROW>
+__device__ __forceinline__ int fec_interval_llr(const fec_demod_smem_tab& T, int idx, float x, float rcp, bool live)
+{
+  const float2 sc = T.lin[ROW][idx];
+  float        l  = (FMA || PATH == FEC_PATH_512) ? __fmaf_rn(sc.x, x, sc.y) : __fadd_rn(__fmul_rn(sc.x, x), sc.y);
+  l               = __fmul_rn(l, rcp);
+  if (PATH == FEC_PATH_SCALAR) {
+    return fec_quant_scalar(l, 20.0f);
+  }
+  return fec_quant_simd(live ? l : 0.0f, 6.0f);
+}
+
+// All QM LLRs of one symbol (before descrambling), packed little-endian into two 32-bit words (LLR j = byte j).
+template <int QM, int PATH, bool FMA>
+__device__ __forceinline__ uint2 fec_demod_symbol(const fec_demod_smem_tab& T, float gain16, float thr16, bool pi2_odd, float re,
+                                                  float im, float nv)
 {
   const float gain2 = 2.0f * 1.41421356237309504880f; // 2.0F * M_SQRT2f32
-  if (qm == 1) {
+  int         o[8]  = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (QM == 1) {
     // demodulation_mapper_impl.cpp:33-75
     const float s = pi2_odd ? __fadd_rn(im, -re) : __fadd_rn(re, im);
-    out[0]        = !(nv > 0) ? 0 : fec_quant_scalar(__fdiv_rn(__fmul_rn(gain2, s), nv), 24.0f);
-    return;
-  }
-  const float xs[2] = {re, im};
-  if (qm == 2) {
+    o[0]          = !(nv > 0) ? 0 : fec_quant_scalar(__fdiv_rn(__fmul_rn(gain2, s), nv), 24.0f);
+  } else if (QM == 2) {
     // demodulation_mapper_qpsk.cpp:38-80 (AVX2), 119-127 (scalar)
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      if (path == FEC_PATH_256) {
-        out[c] = fec_quant_256(__fmul_rn(__fmul_rn(gain2, xs[c]), fec_safe_rcp(nv)), 5.0f);
-      } else {
-        out[c] = !(nv > 0) ? 0 : fec_quant_scalar(__fdiv_rn(__fmul_rn(gain2, xs[c]), nv), 24.0f);
-      }
+    if (PATH == FEC_PATH_256) {
+      const float rcp = fec_safe_rcp(nv);
+      o[0]            = fec_quant_simd(__fmul_rn(__fmul_rn(gain2, re), rcp), 5.0f);
+      o[1]            = fec_quant_simd(__fmul_rn(__fmul_rn(gain2, im), rcp), 5.0f);
+    } else if (nv > 0) {
+      o[0] = fec_quant_scalar(__fdiv_rn(__fmul_rn(gain2, re), nv), 24.0f);
+      o[1] = fec_quant_scalar(__fdiv_rn(__fmul_rn(gain2, im), nv), 24.0f);
     }
-    return;
-  }
-  const bool near_zero =
-      (fma ? __fmaf_rn(re, re, __fmul_rn(im, im)) : __fadd_rn(__fmul_rn(re, re), __fmul_rn(im, im))) < FEC_NEAR_ZERO;
-  if (qm == 4) {
-    // demodulation_mapper_qam16.cpp:42-121 (AVX2), 200-275 (scalar)
-    if (path == FEC_PATH_256) {
+  } else {
+    const bool near_zero =
+        (FMA ? __fmaf_rn(re, re, __fmul_rn(im, im)) : __fadd_rn(__fmul_rn(re, re), __fmul_rn(im, im))) < FEC_NEAR_ZERO;
+    const float xs[2] = {re, im};
+    if (QM == 4) {
+      // demodulation_mapper_qam16.cpp:42-121 (AVX2), 200-275 (scalar)
+      if (PATH == FEC_PATH_256) {
+        const float rcp = fec_safe_rcp(nv);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const float x     = xs[c];
+          const float first = __fmul_rn(gain16, x);
+          float       l01   = first;
+          if (fabsf(x) > thr16) {
+            l01 = __fsub_rn(__fmul_rn(2.0f, first), copysignf(0.8f, x));
+          }
+          float l23 = __fsub_rn(0.8f, fabsf(first));
+          l01       = __fmul_rn(l01, rcp);
+          l23       = __fmul_rn(l23, rcp);
+          if (fabsf(x) <= FEC_NEAR_ZERO) {
+            l01 = 0.0f;
+            l23 = 0.0f;
+          }
+          o[c]     = fec_quant_simd(l01, 6.0f);
+          o[2 + c] = fec_quant_simd(l23, 6.0f);
+        }
+      } else if (!near_zero && nv > 0) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const float x = xs[c];
+          float       l = __fmul_rn(gain16, x);
+          if (fabsf(x) > thr16) {
+            l = __fsub_rn(__fmul_rn(2.0f, l), copysignf(0.8f, x));
+          }
+          o[c]          = fec_quant_scalar(__fdiv_rn(l, nv), 20.0f);
+          const float m = FMA ? __fmaf_rn(-gain16, fabsf(x), 0.8f) : __fsub_rn(0.8f, __fmul_rn(gain16, fabsf(x)));
+          o[2 + c]      = fec_quant_scalar(__fdiv_rn(m, nv), 20.0f);
+        }
+      }
+    } else if (!(PATH == FEC_PATH_SCALAR && near_zero)) {
+      // 64QAM / 256QAM: demodulation_mapper_qam64.cpp:80-182, 184-279, 360-463; _qam256.cpp:163-209, 211-261, 319-425
       const float rcp = fec_safe_rcp(nv);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
-        const float x     = xs[c];
-        const float first = __fmul_rn(T->gain16, x);
-        float       l01   = first;
-        if (fabsf(x) > T->thr16) {
-          l01 = __fsub_rn(__fmul_rn(2.0f, first), copysignf(0.8f, x));
+        const float x    = xs[c];
+        const bool  tame = fabsf(x) < 16384.0f;
+        // avx512: !(|x| > near_zero) is forced to 0; avx2: |x| <= near_zero is (a NaN passes and ends as 0 in the quantiser)
+        const bool live = (PATH == FEC_PATH_512) ? (fabsf(x) > FEC_NEAR_ZERO) : !(fabsf(x) <= FEC_NEAR_ZERO);
+        if (QM == 6) {
+          const int i2 = fec_interval_idx<PATH, 0, 8>(T, x, tame), i4 = fec_interval_idx<PATH, 2, 4>(T, x, tame);
+          o[c]         = fec_interval_llr<PATH, FMA, 0>(T, i2, x, rcp, live);
+          o[2 + c]     = fec_interval_llr<PATH, FMA, 1>(T, i2, x, rcp, live);
+          o[4 + c]     = fec_interval_llr<PATH, FMA, 2>(T, i4, x, rcp, live);
+        } else {
+          const int i2 = fec_interval_idx<PATH, 3, 16>(T, x, tame), i4 = fec_interval_idx<PATH, 6, 8>(T, x, tame);
+          o[c]         = fec_interval_llr<PATH, FMA, 3>(T, i2, x, rcp, live);
+          o[2 + c]     = fec_interval_llr<PATH, FMA, 4>(T, i2, x, rcp, live);
+          o[4 + c]     = fec_interval_llr<PATH, FMA, 5>(T, i2, x, rcp, live);
+          o[6 + c]     = fec_interval_llr<PATH, FMA, 6>(T, i4, x, rcp, live);
         }
-        float l23 = __fsub_rn(0.8f, fabsf(first));
-        l01       = __fmul_rn(l01, rcp);
-        l23       = __fmul_rn(l23, rcp);
-        if (fabsf(x) <= FEC_NEAR_ZERO) {
-          l01 = 0.0f;
-          l23 = 0.0f;
-        }
-        out[c]     = fec_quant_256(l01, 6.0f);
-        out[2 + c] = fec_quant_256(l23, 6.0f);
-      }
-    } else {
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        const float x = xs[c];
-        if (near_zero || !(nv > 0)) {
-          out[c] = out[2 + c] = 0;
-          continue;
-        }
-        float l = __fmul_rn(T->gain16, x);
-        if (fabsf(x) > T->thr16) {
-          l = __fsub_rn(__fmul_rn(2.0f, l), copysignf(0.8f, x));
-        }
-        out[c]        = fec_quant_scalar(__fdiv_rn(l, nv), 20.0f);
-        const float m = fma ? __fmaf_rn(-T->gain16, fabsf(x), 0.8f) : __fsub_rn(0.8f, __fmul_rn(T->gain16, fabsf(x)));
-        out[2 + c]    = fec_quant_scalar(__fdiv_rn(m, nv), 20.0f);
       }
     }
-    return;
   }
-  // 64QAM / 256QAM: demodulation_mapper_qam64.cpp:80-182, 184-279, 360-463; _qam256.cpp:163-209, 211-261, 319-425
-  const int row0 = (qm == 6) ? 0 : 3, nt = qm / 2;
-  if (path == FEC_PATH_SCALAR && near_zero) {
-    for (int j = 0; j < qm; ++j) {
-      out[j] = 0;
-    }
-    return;
-  }
-  const float rcp = fec_safe_rcp(nv);
-  for (int t = 0; t < nt; ++t) {
-    out[2 * t]     = fec_interval_llr(T, row0 + t, path, fma, re, rcp);
-    out[2 * t + 1] = fec_interval_llr(T, row0 + t, path, fma, im, rcp);
-  }
+  uint2 r;
+  r.x = (uint32_t)(o[0] & 0xff) | ((uint32_t)(o[1] & 0xff) << 8) | ((uint32_t)(o[2] & 0xff) << 16) | ((uint32_t)(o[3] & 0xff) << 24);
+  r.y = (uint32_t)(o[4] & 0xff) | ((uint32_t)(o[5] & 0xff) << 8) | ((uint32_t)(o[6] & 0xff) << 16) | ((uint32_t)(o[7] & 0xff) << 24);
+  return r;
 }
 
-// Symbols per iteration of the reference's AVX-512 / AVX2 loops, by flavour (see the header comment).
-__host__ __device__ __forceinline__ void fec_demod_blocks(uint32_t flavour, uint32_t qm, uint32_t* v512, uint32_t* v256)
+// Negates the bytes of w whose mask bit is set (two's complement per byte, |LLR| <= 120 so nothing overflows).
+__device__ __forceinline__ uint32_t fec_negate_bytes(uint32_t w, uint32_t bits4)
 {
-  *v256 = (flavour >= 1) ? ((qm == 2) ? 16u : (qm == 4) ? 8u : (qm == 6) ? 16u : (qm == 8) ? 4u : 0u) : 0u;
-  *v512 = (flavour >= 2) ? ((qm == 6) ? 32u : (qm == 8) ? 8u : 0u) : 0u;
+  const uint32_t m = ((bits4 & 1u) * 0xffu) | ((bits4 & 2u) * (0xff00u >> 1)) | ((bits4 & 4u) * (0xff0000u >> 2)) |
+                     ((bits4 & 8u) * (0xff000000u >> 3));
+  return __vsub4(w ^ m, m); // (w ^ m) - m per byte: -w where m = 0xff
+}
+
+template <int QM, int FLAVOUR>
+__device__ __forceinline__ void fec_demod_tile(const fec_demod_desc& d, uint32_t tile, uint32_t nsym, const float2* __restrict__ symbols,
+                                               const float* __restrict__ noise, const fec_demod_smem_tab& T, float gain16,
+                                               float thr16, const uint32_t* seq, bool scramble, uint8_t* stage_at_phase)
+{
+  const uint32_t tid = threadIdx.x;
+  if (tid >= nsym) {
+    return;
+  }
+  const uint32_t     i    = tile + tid; // position in the demodulate_soft call
+  constexpr uint32_t V256 = (FLAVOUR >= 1) ? ((QM == 2) ? 16u : (QM == 4) ? 8u : (QM == 6) ? 16u : (QM == 8) ? 4u : 0u) : 0u;
+  constexpr uint32_t V512 = (FLAVOUR >= 2) ? ((QM == 6) ? 32u : (QM == 8) ? 8u : 0u) : 0u;
+  constexpr bool     FMA  = FLAVOUR >= 1;
+  const float2       s    = symbols[d.sym_offset + i];
+  const float        nv   = noise[d.sym_offset + i];
+  const bool         odd  = (d.flags & FEC_DEMOD_FLAG_PI2_BPSK) && (i & 1u);
+  uint2              r;
+  if (V512 != 0 && i < d.nof_symbols / (V512 ? V512 : 1u) * V512) {
+    r = fec_demod_symbol<QM, FEC_PATH_512, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
+  } else if (V256 != 0 && i < d.nof_symbols / (V256 ? V256 : 1u) * V256) {
+    r = fec_demod_symbol<QM, FEC_PATH_256, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
+  } else {
+    r = fec_demod_symbol<QM, FEC_PATH_SCALAR, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
+  }
+  if (scramble) {
+    const uint32_t b    = tid * QM; // QM <= 8 bits from bit b of the tile's sequence
+    const uint32_t bits = (uint32_t)((((uint64_t)seq[(b >> 5) + 1] << 32) | seq[b >> 5]) >> (b & 31u));
+    r.x                 = fec_negate_bytes(r.x, bits & 0xfu);
+    if (QM > 4) {
+      r.y = fec_negate_bytes(r.y, (bits >> 4) & 0xfu);
+    }
+  }
+  uint8_t* dst = stage_at_phase + tid * QM;
+#pragma unroll
+  for (int j = 0; j < QM; ++j) {
+    dst[j] = (uint8_t)(((j < 4) ? r.x : r.y) >> (8 * (j & 3)));
+  }
 }
 
 __global__ void __launch_bounds__(FEC_DEMOD_THREADS)
     fec_demod_kernel(const fec_demod_desc* __restrict__ descs, const float2* __restrict__ symbols, const float* __restrict__ noise,
                      int8_t* __restrict__ llr, const fec_demod_tables* __restrict__ T, uint32_t flavour)
 {
-  __shared__ uint32_t seq[FEC_DEMOD_TILE_WORDS];
-  __shared__ uint32_t state[2];
+  __shared__ uint32_t             seq[FEC_DEMOD_TILE_WORDS + 1];
+  __shared__ uint32_t             state[2];
+  __shared__ fec_demod_smem_tab   tab;
   __shared__ __align__(16) uint8_t stage[FEC_DEMOD_THREADS * 8 + 16];
 
   const fec_demod_desc d    = descs[blockIdx.x];
@@ -309,62 +394,65 @@ __global__ void __launch_bounds__(FEC_DEMOD_THREADS)
     return;
   }
   const uint32_t qm = d.qm, tid = threadIdx.x, lane = tid & 31u;
-  const uint32_t nsym  = min(d.nof_symbols - tile, (uint32_t)FEC_DEMOD_THREADS);
-  const uint32_t nbits = nsym * qm;
+  const uint32_t nsym     = min(d.nof_symbols - tile, (uint32_t)FEC_DEMOD_THREADS);
+  const uint32_t nbits    = nsym * qm;
   const bool     scramble = !(d.flags & FEC_DEMOD_FLAG_NO_DESCRAMBLE);
+  if (qm >= 6 && tid < 7 * 16) {
+    const uint32_t row = tid >> 4, k = tid & 15u;
+    tab.lin[row][k]    = make_float2(T->slope[row][k], T->icpt[row][k]);
+    if (k == 0) {
+      tab.width[row]     = T->width[row];
+      tab.rcp_width[row] = T->rcp_width[row];
+    }
+  }
   if (scramble) {
     if (tid < 32) {
-      // c(n) = x1(n + 1600) + x2(n + 1600); x1 starts from 1, x2 from c_init.
-      const uint32_t p = 1600u + d.seq_offset + tile * qm;
-      uint32_t s1 = 1u, s2 = d.c_init & 0x7fffffffu;
-      for (uint32_t k = 0; k < 32; ++k) {
-        if ((p >> k) & 1u) {
-          s1 = __ballot_sync(0xffffffffu, lane < 31 && (__popc(T->A[0][k][lane] & s1) & 1)) & 0x7fffffffu;
-          s2 = __ballot_sync(0xffffffffu, lane < 31 && (__popc(T->A[1][k][lane] & s2) & 1)) & 0x7fffffffu;
-        }
+      // The descriptor carries the LFSR states at the call's first soft bit (fec_demod_desc_prepare); the tile starts
+      // tile * qm bits further on: one matrix-vector product per set bit of that distance, one lane per state bit.
+      uint32_t s1 = d.x1_state, s2 = d.x2_state;
+      for (uint32_t p = tile * qm; p != 0; p &= p - 1) {
+        const uint32_t k = __ffs(p) - 1;
+        s1 = __ballot_sync(0xffffffffu, lane < 31 && (__popc(T->A[0][k][lane] & s1) & 1)) & 0x7fffffffu;
+        s2 = __ballot_sync(0xffffffffu, lane < 31 && (__popc(T->A[1][k][lane] & s2) & 1)) & 0x7fffffffu;
       }
       if (tid == 0) {
-        state[0] = s1;
-        state[1] = s2;
+        state[0]                  = s1;
+        state[1]                  = s2;
+        seq[FEC_DEMOD_TILE_WORDS] = 0;
       }
     }
     __syncthreads();
     const uint32_t s1 = state[0], s2 = state[1], nwords = (nbits + 31) / 32;
-    for (uint32_t w = tid >> 5; w < nwords; w += FEC_DEMOD_THREADS / 32) {
-      const uint32_t q   = w * 32 + lane;
-      const uint32_t bit = (__popc(T->B[0][q] & s1) ^ __popc(T->B[1][q] & s2)) & 1u;
-      const uint32_t wd  = __ballot_sync(0xffffffffu, bit);
+    for (uint32_t w = tid >> 5; w < FEC_DEMOD_TILE_WORDS; w += FEC_DEMOD_THREADS / 32) {
+      uint32_t wd = 0;
+      if (w < nwords) {
+        const uint32_t q   = w * 32 + lane;
+        const uint32_t bit = (__popc(T->B[0][q] & s1) ^ __popc(T->B[1][q] & s2)) & 1u;
+        wd                 = __ballot_sync(0xffffffffu, bit);
+      }
       if (lane == 0) {
         seq[w] = wd;
       }
     }
-    __syncthreads();
   }
+  __syncthreads();
   int8_t*        dst   = llr + d.llr_offset + (uint64_t)tile * qm;
   const uint32_t phase = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
-  if (tid < nsym) {
-    const uint32_t i = tile + tid; // position in the demodulate_soft call
-    uint32_t       v512, v256;
-    fec_demod_blocks(flavour, qm, &v512, &v256);
-    const uint32_t end512 = v512 ? (d.nof_symbols / v512) * v512 : 0u;
-    const uint32_t end256 = v256 ? (d.nof_symbols / v256) * v256 : 0u;
-    const int      path   = (i < end512) ? FEC_PATH_512 : (i < end256) ? FEC_PATH_256 : FEC_PATH_SCALAR;
-    const float2   s      = symbols[d.sym_offset + i];
-    const float    nv     = noise[d.sym_offset + i];
-    int            out[8];
-    fec_demod_symbol(T, (int)qm, (d.flags & FEC_DEMOD_FLAG_PI2_BPSK) && (i & 1u), path, flavour >= 1, s.x, s.y, nv, out);
-#pragma unroll
-    for (uint32_t j = 0; j < 8; ++j) {
-      if (j < qm) {
-        const uint32_t b = tid * qm + j;
-        int            v = out[j];
-        if (scramble && ((seq[b >> 5] >> (b & 31u)) & 1u)) {
-          v = -v;
-        }
-        stage[phase + b] = (uint8_t)(int8_t)v;
-      }
-    }
+  const float    g16 = T->gain16, t16 = T->thr16;
+#define FEC_DEMOD_CASE(Q, F)                                                                                                  \
+  case (Q) * 4 + (F):                                                                                                          \
+    fec_demod_tile<Q, F>(d, tile, nsym, symbols, noise, tab, g16, t16, seq, scramble, stage + phase);                          \
+    break;
+  switch (qm * 4 + flavour) {
+    FEC_DEMOD_CASE(1, 0) FEC_DEMOD_CASE(1, 1) FEC_DEMOD_CASE(1, 2)
+    FEC_DEMOD_CASE(2, 0) FEC_DEMOD_CASE(2, 1) FEC_DEMOD_CASE(2, 2)
+    FEC_DEMOD_CASE(4, 0) FEC_DEMOD_CASE(4, 1) FEC_DEMOD_CASE(4, 2)
+    FEC_DEMOD_CASE(6, 0) FEC_DEMOD_CASE(6, 1) FEC_DEMOD_CASE(6, 2)
+    FEC_DEMOD_CASE(8, 0) FEC_DEMOD_CASE(8, 1) FEC_DEMOD_CASE(8, 2)
+    default:
+      break;
   }
+#undef FEC_DEMOD_CASE
   __syncthreads();
   // Rows of 16 bytes at the destination's alignment; the first and the last row may be partial.
   const uint32_t total = phase + nbits;

@@ -1395,38 +1395,38 @@ int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const 
 
 // ---- the step in front of the path: soft demodulation + descrambling ---------------------------------------------------------
 namespace {
+const fec_demod_tables* demod_host_tables()
+{
+  static const fec_demod_tables* tab = [] {
+    fec_demod_tables* t = new fec_demod_tables;
+    fec_demod_build_tables(t);
+    return t;
+  }();
+  return tab;
+}
+
+const fec_demod_host_jump* demod_host_jump()
+{
+  static const fec_demod_host_jump* jump = [] {
+    fec_demod_host_jump* j = new fec_demod_host_jump;
+    fec_demod_build_jump(demod_host_tables(), j);
+    return j;
+  }();
+  return jump;
+}
+
 int demod_tables_alloc(fec_engine* e)
 {
   if (e->d_dtab != nullptr) {
     return FEC_OK;
   }
-  fec_demod_tables* h = new (std::nothrow) fec_demod_tables;
-  if (h == nullptr) {
-    return fail(FEC_ERR_NO_MEMORY, "demodulator tables");
-  }
-  fec_demod_build_tables(h);
   cudaError_t err = cudaMalloc((void**)&e->d_dtab, sizeof(fec_demod_tables));
   if (err == cudaSuccess) {
-    err = cudaMemcpy(e->d_dtab, h, sizeof(fec_demod_tables), cudaMemcpyHostToDevice);
+    err = cudaMemcpy(e->d_dtab, demod_host_tables(), sizeof(fec_demod_tables), cudaMemcpyHostToDevice);
   }
-  delete h;
   if (err != cudaSuccess) {
     cudaGetLastError();
     return fail(FEC_ERR_CUDA, "demodulator tables: %s", cudaGetErrorString(err));
-  }
-  return FEC_OK;
-}
-
-int demod_check(const fec_demod_desc& d, uint32_t i, uint32_t flavour)
-{
-  if (flavour > FEC_DEMOD_FLAVOUR_AVX512) {
-    return fail(FEC_ERR_BAD_ARG, "flavour=%u", flavour);
-  }
-  if (d.qm != 1 && d.qm != 2 && d.qm != 4 && d.qm != 6 && d.qm != 8) {
-    return fail(FEC_ERR_BAD_ARG, "demodulation %u: qm=%u", i, d.qm);
-  }
-  if ((uint64_t)d.seq_offset + (uint64_t)d.nof_symbols * d.qm + 1600u > 0xffffffffull) {
-    return fail(FEC_ERR_BAD_ARG, "demodulation %u: sequence position beyond 2^32", i);
   }
   return FEC_OK;
 }
@@ -1454,6 +1454,9 @@ int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l
   if (!dm.descs || !dm.h_symbols || !dm.h_noise) {
     return fail(FEC_ERR_BAD_ARG, "null argument");
   }
+  if (dm.flavour > FEC_DEMOD_FLAVOUR_AVX512) {
+    return fail(FEC_ERR_BAD_ARG, "flavour=%u", dm.flavour);
+  }
   int rc = demod_tables_alloc(e);
   if (rc != FEC_OK) {
     return rc;
@@ -1463,7 +1466,7 @@ int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l
   e->dm_descs_host.assign(dm.descs, dm.descs + dm.n);
   for (uint32_t i = 0; i < dm.n; ++i) {
     fec_demod_desc& d = e->dm_descs_host[i];
-    rc                = demod_check(d, i, dm.flavour);
+    rc                = fec_demod_desc_prepare(&d);
     if (rc != FEC_OK) {
       return rc;
     }
@@ -1498,6 +1501,21 @@ int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l
   return demod_launch(e, st, e->d_dm_descs, dm.n, max_symbols, e->d_dm_sym, e->d_dm_noise, d_llr, dm.flavour);
 }
 } // namespace
+
+int fec_demod_desc_prepare(fec_demod_desc* d)
+{
+  if (d == nullptr) {
+    return fail(FEC_ERR_BAD_ARG, "null descriptor");
+  }
+  if (d->qm != 1 && d->qm != 2 && d->qm != 4 && d->qm != 6 && d->qm != 8) {
+    return fail(FEC_ERR_BAD_ARG, "demodulation: qm=%u", d->qm);
+  }
+  if ((uint64_t)d->seq_offset + (uint64_t)d->nof_symbols * d->qm + 1600u > 0xffffffffull) {
+    return fail(FEC_ERR_BAD_ARG, "demodulation: sequence position beyond 2^32");
+  }
+  fec_demod_lfsr_states(demod_host_jump(), d->c_init, d->seq_offset, &d->x1_state, &d->x2_state);
+  return FEC_OK;
+}
 
 int fec_demod_launch_device(fec_engine* e, const fec_demod_desc* d_descs, uint32_t n, uint32_t max_symbols,
                             const float* d_symbols, const float* d_noise_vars, int8_t* d_llr, uint32_t flavour)

@@ -68,14 +68,14 @@ ENC_DESC_DTYPE = np.dtype({
     "itemsize": 40})
 
 
-# numpy mirror of struct fec_demod_desc (32 bytes)
+# numpy mirror of struct fec_demod_desc (40 bytes)
 DEMOD_GENERIC, DEMOD_AVX2, DEMOD_AVX512 = 0, 1, 2
 DEMOD_FLAG_PI2_BPSK, DEMOD_FLAG_NO_DESCRAMBLE = 1, 2
 DEMOD_DESC_DTYPE = np.dtype({
-    "names": ["sym_offset", "llr_offset", "nof_symbols", "c_init", "seq_offset", "qm", "flags"],
-    "formats": ["<u8", "<u8", "<u4", "<u4", "<u4", "u1", "u1"],
-    "offsets": [0, 8, 16, 20, 24, 28, 29],
-    "itemsize": 32})
+    "names": ["sym_offset", "llr_offset", "nof_symbols", "c_init", "seq_offset", "x1_state", "x2_state", "qm", "flags"],
+    "formats": ["<u8", "<u8", "<u4", "<u4", "<u4", "<u4", "<u4", "u1", "u1"],
+    "offsets": [0, 8, 16, 20, 24, 28, 32, 36, 37],
+    "itemsize": 40})
 
 
 class EngineCfg(C.Structure):
@@ -89,8 +89,8 @@ EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_e
            "fec_launch_device", "fec_run_host", "fec_host_alloc", "fec_host_free", "fec_harq_free", "fec_harq_read",
            "fec_harq_write", "fec_harq_flush", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
            "fec_queue_poll", "fec_queue_fetch", "fec_tb_segment", "fec_tb_run_host", "fec_tb_reset_slots",
-           "fec_enc_desc_prepare", "fec_encode_launch_device", "fec_encode_run_host", "fec_demod_launch_device",
-           "fec_demod_run_host", "fec_tb_run_host_symbols"]
+           "fec_enc_desc_prepare", "fec_encode_launch_device", "fec_encode_run_host", "fec_demod_desc_prepare",
+           "fec_demod_launch_device", "fec_demod_run_host", "fec_tb_run_host_symbols"]
 
 _lib = None
 
@@ -145,6 +145,7 @@ def load_library():
     lib.fec_encode_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
     lib.fec_encode_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p,
                                         C.c_size_t]
+    lib.fec_demod_desc_prepare.argtypes = [C.c_void_p]
     lib.fec_demod_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_uint32]
     lib.fec_demod_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
@@ -188,6 +189,15 @@ def make_demod_descs(n):
     return np.zeros(n, DEMOD_DESC_DTYPE)
 
 
+def demod_desc_prepare(descs):
+    """Validates demodulation descriptors in place and fills the LFSR states; raises FecError on invalid fields. Host only."""
+    lib = load_library()
+    arr = np.atleast_1d(descs)
+    for i in range(arr.size):
+        _check(lib, lib.fec_demod_desc_prepare(arr[i:i + 1].ctypes.data))
+    return descs
+
+
 def codeword_demod_descs(blocks, qm, c_init, sym_offset=0, llr_offset=0, flags=0):
     """The demodulation calls of one PUSCH codeword as pusch_demodulator_impl issues them (pusch_demodulator_impl.cpp:
     262-400): one per block of symbols (one OFDM symbol each), the scrambling sequence running on across the blocks."""
@@ -198,7 +208,7 @@ def codeword_demod_descs(blocks, qm, c_init, sym_offset=0, llr_offset=0, flags=0
         d["seq_offset"][i] = pos * qm
         pos += int(n)
     d["c_init"], d["qm"], d["flags"] = c_init, qm, flags
-    return d
+    return demod_desc_prepare(d)
 
 
 def make_tb_descs(n):

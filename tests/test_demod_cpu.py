@@ -66,3 +66,23 @@ def test_oracle_vs_reference_live(orc, dorc, flavour):
 def test_block_layout(dorc):
     assert dorc.blocks(0, 8) == (0, 0) and dorc.blocks(1, 8) == (0, 4) and dorc.blocks(2, 8) == (8, 4)
     assert dorc.blocks(2, 6) == (32, 16) and dorc.blocks(2, 4) == (0, 8) and dorc.blocks(2, 2) == (0, 16)
+
+
+def test_desc_prepare_lfsr_states(fec, dorc):
+    """fec_demod_desc_prepare (host only): the LFSR states it stores reproduce the next 31 sequence bits at any position."""
+    rng = np.random.default_rng(3)
+    for _ in range(40):
+        d = fec.make_demod_descs(1)
+        d["c_init"], d["qm"], d["nof_symbols"] = int(rng.integers(0, 1 << 31)), 2, 10
+        d["seq_offset"] = int(rng.choice([0, 1, 1599, 1600, 40000, int(rng.integers(0, 1 << 22))]))
+        fec.demod_desc_prepare(d)
+        got = ((int(d["x1_state"][0]) ^ int(d["x2_state"][0])) >> np.arange(31)) & 1
+        want = np.unpackbits(dorc.gold_sequence(int(d["c_init"][0]), int(d["seq_offset"][0]), 31))[:31]
+        assert (got == want).all()
+    bad = fec.make_demod_descs(1)
+    bad["qm"] = 3
+    with pytest.raises(fec.FecError):
+        fec.demod_desc_prepare(bad)
+    bad["qm"], bad["seq_offset"], bad["nof_symbols"] = 8, 0xffffff00, 1000
+    with pytest.raises(fec.FecError):
+        fec.demod_desc_prepare(bad)
