@@ -57,3 +57,18 @@ def test_pdsch_encoder_hw_impl_over_the_cuda_hal():
     assert r.returncode == 0, r.stdout + r.stderr
     print(r.stdout)
     assert "OK transport_blocks=42" in r.stdout, r.stdout
+
+
+DEMOD_BIN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "dropin_demodulation_mapper")
+
+
+def test_demodulation_mapper_over_the_cuda_engine():
+    """The reference's own demodulation_mapper_impl (built into the test binary for AVX-512, the flavour of the hosts used
+    here) against srsran::b200::cuda_demodulation_mapper obtained through the demodulation_mapper_factory interface:
+    every modulation, lengths around the SIMD block sizes, zero / negative / NaN noise variances, bit for bit."""
+    if not os.path.exists(DEMOD_BIN):
+        pytest.skip("tests/cpp/_build/dropin_demodulation_mapper not built (needs the reference sources)")
+    r = subprocess.run([DEMOD_BIN, "120"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    print(r.stdout)
+    assert "OK cases=120" in r.stdout, r.stdout
