@@ -36,7 +36,7 @@ struct fec_demod_tables {
   float    gain16;  // 4 / sqrt(10)
   float    thr16;   // 2 / sqrt(10)
   uint32_t A[2][32][32];                       // [lfsr][k][state bit]: row of the 2^k-step transition matrix
-  uint32_t B[2][FEC_DEMOD_TILE_WORDS * 32];    // [lfsr][q]: mask whose parity with the state gives x(p + q)
+  uint2    B[FEC_DEMOD_TILE_WORDS * 32];       // [q]: masks (x1, x2) whose parity with the states gives c(p + q)
 };
 
 // ---- host side: tables derived from the constellation (TS 38.211 5.1.4-5.1.6) and the generator polynomials (5.2.1) -----
@@ -111,7 +111,7 @@ inline void fec_demod_build_tables(fec_demod_tables* t)
     }
     uint32_t r = 1u; // e0^T A^0
     for (int q = 0; q < FEC_DEMOD_TILE_WORDS * 32; ++q) {
-      t->B[g][q] = r;
+      (g == 0 ? t->B[q].x : t->B[q].y) = r;
       uint32_t nx = 0;
       for (int j = 0; j < 31; ++j) {
         if ((r >> j) & 1u) {
@@ -195,10 +195,19 @@ __device__ __forceinline__ int fec_quant_scalar(float v, float range)
 // mm256::quantize_ps (avx2_helpers.h:123-166) and mm512::quantize_ps (avx512_helpers.h:48-107) are the same function of one
 // value: a NaN gives 0 (bounds check after the conversion / masked multiply), otherwise scale, clamp to +-120, round to
 // nearest even. scale = 120 / range_limit (6 or 5, exact).
+// CHK = false: the caller knows v cannot be a NaN (finite symbol, finite 1 / noise variance).
+template <bool CHK>
 __device__ __forceinline__ int fec_quant_simd(float v, float scale)
 {
   const float q = __fmul_rn(v, scale);
-  return (q != q) ? 0 : __float2int_rn(fminf(fmaxf(q, -120.0f), 120.0f));
+  const int   i = __float2int_rn(fminf(fmaxf(q, -120.0f), 120.0f));
+  return (CHK && q != q) ? 0 : i;
+}
+
+// Four soft bits (low bytes of a..d) into one word, a in byte 0.
+__device__ __forceinline__ uint32_t fec_pack4(int a, int b, int c, int d)
+{
+  return __byte_perm(__byte_perm((uint32_t)a, (uint32_t)b, 0x0040), __byte_perm((uint32_t)c, (uint32_t)d, 0x0040), 0x5410);
 }
 
 enum { FEC_PATH_SCALAR = 0, FEC_PATH_256 = 1, FEC_PATH_512 = 2 };
@@ -211,26 +220,26 @@ struct fec_demod_smem_tab {
 };
 
 // compute_interval_idx in its three spellings (demodulation_mapper_intervals.h:36-43, avx2_helpers.h:168-187,
-// avx512_helpers.h:156-171). Rows with the same interval width and count share the index. `tame` = |x| < 16384: the
+// avx512_helpers.h:156-171). Rows with the same interval width and count share the index. TAME = |x| < 16384: the
 // conversion cannot leave the int32 range, so the x86 out-of-range rule needs no emulation.
-template <int PATH, int ROW, int N>
-__device__ __forceinline__ int fec_interval_idx(const fec_demod_smem_tab& T, float x, bool tame)
+template <int PATH, int ROW, int N, bool TAME>
+__device__ __forceinline__ int fec_interval_idx(const fec_demod_smem_tab& T, float x)
 {
   if (PATH == FEC_PATH_512) {
     const float t = __fmaf_rn(x, T.rcp_width[ROW], (float)(N / 2));
-    return fec_dm_clamp(tame ? __float2int_rd(t) : fec_x86_cvt(floorf(t)), 0, N - 1);
+    return fec_dm_clamp(TAME ? __float2int_rd(t) : fec_x86_cvt(floorf(t)), 0, N - 1);
   }
   if (PATH == FEC_PATH_256) {
     const float t = __fmul_rn(x, T.rcp_width[ROW]);
-    return fec_dm_clamp((int)((uint32_t)(tame ? __float2int_rd(t) : fec_x86_cvt(floorf(t))) + (uint32_t)(N / 2)), 0, N - 1);
+    return fec_dm_clamp((int)((uint32_t)(TAME ? __float2int_rd(t) : fec_x86_cvt(floorf(t))) + (uint32_t)(N / 2)), 0, N - 1);
   }
   const float t = __fdiv_rn(x, T.width[ROW]);
-  return fec_dm_clamp((tame ? __float2int_rd(t) : fec_x86_cvt(floorf(t))) + N / 2, 0, N - 1);
+  return fec_dm_clamp((TAME ? __float2int_rd(t) : fec_x86_cvt(floorf(t))) + N / 2, 0, N - 1);
 }
 
 // interval_function (demodulation_mapper_intervals.h:45-64, avx2_helpers.h:217-249, avx512_helpers.h:214-241) for a known
 // interval, then the matching quantiser. `live` = |x| > near_zero (the SIMD paths force 0 otherwise).
-template <int PATH, bool FMA, int ROW>
+template <int PATH, bool FMA, int ROW, bool TAME>
 __device__ __forceinline__ int fec_interval_llr(const fec_demod_smem_tab& T, int idx, float x, float rcp, bool live)
 {
   const float2 sc = T.lin[ROW][idx];
@@ -239,13 +248,15 @@ __device__ __forceinline__ int fec_interval_llr(const fec_demod_smem_tab& T, int
   if (PATH == FEC_PATH_SCALAR) {
     return fec_quant_scalar(l, 20.0f);
   }
-  return fec_quant_simd(live ? l : 0.0f, 6.0f);
+  return fec_quant_simd<!TAME>(live ? l : 0.0f, 6.0f);
 }
 
 // All QM LLRs of one symbol (before descrambling), packed little-endian into two 32-bit words (LLR j = byte j).
-template <int QM, int PATH, bool FMA>
+// rcp = safe 1 / nv (used by the SIMD paths and the interval functions). TAME: both components below 16384 in magnitude
+// and rcp finite, so neither the x86 conversion rule nor a NaN can come into play on the SIMD paths.
+template <int QM, int PATH, bool FMA, bool TAME>
 __device__ __forceinline__ uint2 fec_demod_symbol(const fec_demod_smem_tab& T, float gain16, float thr16, bool pi2_odd, float re,
-                                                  float im, float nv)
+                                                  float im, float nv, float rcp)
 {
   const float gain2 = 2.0f * 1.41421356237309504880f; // 2.0F * M_SQRT2f32
   int         o[8]  = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -256,9 +267,8 @@ __device__ __forceinline__ uint2 fec_demod_symbol(const fec_demod_smem_tab& T, f
   } else if (QM == 2) {
     // demodulation_mapper_qpsk.cpp:38-80 (AVX2), 119-127 (scalar)
     if (PATH == FEC_PATH_256) {
-      const float rcp = fec_safe_rcp(nv);
-      o[0]            = fec_quant_simd(__fmul_rn(__fmul_rn(gain2, re), rcp), 5.0f);
-      o[1]            = fec_quant_simd(__fmul_rn(__fmul_rn(gain2, im), rcp), 5.0f);
+      o[0] = fec_quant_simd<!TAME>(__fmul_rn(__fmul_rn(gain2, re), rcp), 5.0f);
+      o[1] = fec_quant_simd<!TAME>(__fmul_rn(__fmul_rn(gain2, im), rcp), 5.0f);
     } else if (nv > 0) {
       o[0] = fec_quant_scalar(__fdiv_rn(__fmul_rn(gain2, re), nv), 24.0f);
       o[1] = fec_quant_scalar(__fdiv_rn(__fmul_rn(gain2, im), nv), 24.0f);
@@ -270,7 +280,6 @@ __device__ __forceinline__ uint2 fec_demod_symbol(const fec_demod_smem_tab& T, f
     if (QM == 4) {
       // demodulation_mapper_qam16.cpp:42-121 (AVX2), 200-275 (scalar)
       if (PATH == FEC_PATH_256) {
-        const float rcp = fec_safe_rcp(nv);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           const float x     = xs[c];
@@ -286,8 +295,8 @@ __device__ __forceinline__ uint2 fec_demod_symbol(const fec_demod_smem_tab& T, f
             l01 = 0.0f;
             l23 = 0.0f;
           }
-          o[c]     = fec_quant_simd(l01, 6.0f);
-          o[2 + c] = fec_quant_simd(l23, 6.0f);
+          o[c]     = fec_quant_simd<!TAME>(l01, 6.0f);
+          o[2 + c] = fec_quant_simd<!TAME>(l23, 6.0f);
         }
       } else if (!near_zero && nv > 0) {
 #pragma unroll
@@ -304,32 +313,46 @@ __device__ __forceinline__ uint2 fec_demod_symbol(const fec_demod_smem_tab& T, f
       }
     } else if (!(PATH == FEC_PATH_SCALAR && near_zero)) {
       // 64QAM / 256QAM: demodulation_mapper_qam64.cpp:80-182, 184-279, 360-463; _qam256.cpp:163-209, 211-261, 319-425
-      const float rcp = fec_safe_rcp(nv);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
-        const float x    = xs[c];
-        const bool  tame = fabsf(x) < 16384.0f;
+        const float x = xs[c];
         // avx512: !(|x| > near_zero) is forced to 0; avx2: |x| <= near_zero is (a NaN passes and ends as 0 in the quantiser)
         const bool live = (PATH == FEC_PATH_512) ? (fabsf(x) > FEC_NEAR_ZERO) : !(fabsf(x) <= FEC_NEAR_ZERO);
         if (QM == 6) {
-          const int i2 = fec_interval_idx<PATH, 0, 8>(T, x, tame), i4 = fec_interval_idx<PATH, 2, 4>(T, x, tame);
-          o[c]         = fec_interval_llr<PATH, FMA, 0>(T, i2, x, rcp, live);
-          o[2 + c]     = fec_interval_llr<PATH, FMA, 1>(T, i2, x, rcp, live);
-          o[4 + c]     = fec_interval_llr<PATH, FMA, 2>(T, i4, x, rcp, live);
+          const int i2 = fec_interval_idx<PATH, 0, 8, TAME>(T, x), i4 = fec_interval_idx<PATH, 2, 4, TAME>(T, x);
+          o[c]         = fec_interval_llr<PATH, FMA, 0, TAME>(T, i2, x, rcp, live);
+          o[2 + c]     = fec_interval_llr<PATH, FMA, 1, TAME>(T, i2, x, rcp, live);
+          o[4 + c]     = fec_interval_llr<PATH, FMA, 2, TAME>(T, i4, x, rcp, live);
         } else {
-          const int i2 = fec_interval_idx<PATH, 3, 16>(T, x, tame), i4 = fec_interval_idx<PATH, 6, 8>(T, x, tame);
-          o[c]         = fec_interval_llr<PATH, FMA, 3>(T, i2, x, rcp, live);
-          o[2 + c]     = fec_interval_llr<PATH, FMA, 4>(T, i2, x, rcp, live);
-          o[4 + c]     = fec_interval_llr<PATH, FMA, 5>(T, i2, x, rcp, live);
-          o[6 + c]     = fec_interval_llr<PATH, FMA, 6>(T, i4, x, rcp, live);
+          const int i2 = fec_interval_idx<PATH, 3, 16, TAME>(T, x), i4 = fec_interval_idx<PATH, 6, 8, TAME>(T, x);
+          o[c]         = fec_interval_llr<PATH, FMA, 3, TAME>(T, i2, x, rcp, live);
+          o[2 + c]     = fec_interval_llr<PATH, FMA, 4, TAME>(T, i2, x, rcp, live);
+          o[4 + c]     = fec_interval_llr<PATH, FMA, 5, TAME>(T, i2, x, rcp, live);
+          o[6 + c]     = fec_interval_llr<PATH, FMA, 6, TAME>(T, i4, x, rcp, live);
         }
       }
     }
   }
   uint2 r;
-  r.x = (uint32_t)(o[0] & 0xff) | ((uint32_t)(o[1] & 0xff) << 8) | ((uint32_t)(o[2] & 0xff) << 16) | ((uint32_t)(o[3] & 0xff) << 24);
-  r.y = (uint32_t)(o[4] & 0xff) | ((uint32_t)(o[5] & 0xff) << 8) | ((uint32_t)(o[6] & 0xff) << 16) | ((uint32_t)(o[7] & 0xff) << 24);
+  r.x = fec_pack4(o[0], o[1], o[2], o[3]);
+  r.y = (QM > 4) ? fec_pack4(o[4], o[5], o[6], o[7]) : 0u;
   return r;
+}
+
+// One symbol on one path: 1 / noise variance where the path uses it, then the common case (TAME) without the emulation of
+// x86's out-of-range conversions and without NaN checks, anything else through the fully general instantiation.
+template <int QM, int PATH, bool FMA>
+__device__ __forceinline__ uint2 fec_demod_dispatch(const fec_demod_smem_tab& T, float gain16, float thr16, bool pi2_odd, float re,
+                                                    float im, float nv)
+{
+  if (QM == 1 || (PATH == FEC_PATH_SCALAR && QM <= 4)) {
+    return fec_demod_symbol<QM, PATH, FMA, false>(T, gain16, thr16, pi2_odd, re, im, nv, 0.0f); // these divide by nv itself
+  }
+  const float rcp = fec_safe_rcp(nv);
+  if (fabsf(re) < 16384.0f && fabsf(im) < 16384.0f && rcp <= 3.402823466e+38f) {
+    return fec_demod_symbol<QM, PATH, FMA, true>(T, gain16, thr16, pi2_odd, re, im, nv, rcp);
+  }
+  return fec_demod_symbol<QM, PATH, FMA, false>(T, gain16, thr16, pi2_odd, re, im, nv, rcp);
 }
 
 // Negates the bytes of w whose mask bit is set (two's complement per byte, |LLR| <= 120 so nothing overflows).
@@ -358,11 +381,11 @@ __device__ __forceinline__ void fec_demod_tile(const fec_demod_desc& d, uint32_t
   const bool         odd  = (d.flags & FEC_DEMOD_FLAG_PI2_BPSK) && (i & 1u);
   uint2              r;
   if (V512 != 0 && i < d.nof_symbols / (V512 ? V512 : 1u) * V512) {
-    r = fec_demod_symbol<QM, FEC_PATH_512, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
+    r = fec_demod_dispatch<QM, FEC_PATH_512, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
   } else if (V256 != 0 && i < d.nof_symbols / (V256 ? V256 : 1u) * V256) {
-    r = fec_demod_symbol<QM, FEC_PATH_256, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
+    r = fec_demod_dispatch<QM, FEC_PATH_256, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
   } else {
-    r = fec_demod_symbol<QM, FEC_PATH_SCALAR, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
+    r = fec_demod_dispatch<QM, FEC_PATH_SCALAR, FMA>(T, gain16, thr16, odd, s.x, s.y, nv);
   }
   if (scramble) {
     const uint32_t b    = tid * QM; // QM <= 8 bits from bit b of the tile's sequence
@@ -422,16 +445,18 @@ __global__ void __launch_bounds__(FEC_DEMOD_THREADS)
       }
     }
     __syncthreads();
-    const uint32_t s1 = state[0], s2 = state[1], nwords = (nbits + 31) / 32;
-    for (uint32_t w = tid >> 5; w < FEC_DEMOD_TILE_WORDS; w += FEC_DEMOD_THREADS / 32) {
-      uint32_t wd = 0;
-      if (w < nwords) {
-        const uint32_t q   = w * 32 + lane;
-        const uint32_t bit = (__popc(T->B[0][q] & s1) ^ __popc(T->B[1][q] & s2)) & 1u;
-        wd                 = __ballot_sync(0xffffffffu, bit);
-      }
-      if (lane == 0) {
-        seq[w] = wd;
+    // c(p + q) = parity((B[q].x & s1) ^ (B[q].y & s2)): one lane per bit, one ballot per word, warp w takes words w, w + 8 ...
+    // (all 8 * qm words of a full tile, also where the call ends earlier: the surplus is never read)
+    const uint32_t s1 = state[0], s2 = state[1];
+    const uint2*   Bq = T->B + tid;
+#pragma unroll
+    for (uint32_t r = 0; r < FEC_DEMOD_TILE_WORDS * 32 / FEC_DEMOD_THREADS; ++r) {
+      if (r < qm) { // a full tile holds 256 * qm bits = qm rounds of 8 words
+        const uint2    m  = Bq[r * FEC_DEMOD_THREADS];
+        const uint32_t wd = __ballot_sync(0xffffffffu, __popc((m.x & s1) ^ (m.y & s2)) & 1);
+        if (lane == 0) {
+          seq[(tid >> 5) + r * (FEC_DEMOD_THREADS / 32)] = wd;
+        }
       }
     }
   }
