@@ -12,7 +12,8 @@
 // Work layout: one CTA per tile of 256 consecutive symbols of one call, one thread per symbol.
 //   1. warp 0 jumps the two 31-bit LFSRs from the call's first soft bit (states prepared on the host, in the descriptor) to
 //      the first bit of the tile (matrix powers A^(2^k), one lane per state bit, one product per set bit of the distance),
-//   2. all threads expand the tile's scrambling bits (row vectors B[q] = e0^T A^q, one parity per bit, ballot per word),
+//   2. threads 0 .. 8 Qm - 1 expand the tile's scrambling bits, one 32-bit word each: the XOR of 16 table rows selected by the
+//      nibbles of the combined 62-bit LFSR state (the table holds e0^T A^q, q < 2048, summed per nibble value),
 //   3. each thread demodulates its symbol (code specialised per modulation and flavour, tables in shared memory), flips
 //      signs four LLRs at a time, and parks the Qm bytes in shared memory,
 //   4. the tile is written out in 16-byte rows (shared memory staged at the destination's 16-byte phase).
@@ -36,7 +37,9 @@ struct fec_demod_tables {
   float    gain16;  // 4 / sqrt(10)
   float    thr16;   // 2 / sqrt(10)
   uint32_t A[2][32][32];                       // [lfsr][k][state bit]: row of the 2^k-step transition matrix
-  uint2    B[FEC_DEMOD_TILE_WORDS * 32];       // [q]: masks (x1, x2) whose parity with the states gives c(p + q)
+  // Sequence expansion: word w of the tile (bits c(p + 32 w ...)) = XOR over the 16 nibbles of the 62-bit state (x1 | x2 << 31)
+  // of L[nibble position][nibble value][w].
+  uint32_t L[16][16][FEC_DEMOD_TILE_WORDS];
 };
 
 // ---- host side: tables derived from the constellation (TS 38.211 5.1.4-5.1.6) and the generator polynomials (5.2.1) -----
@@ -109,9 +112,20 @@ inline void fec_demod_build_tables(fec_demod_tables* t)
         A[k][i] = r;
       }
     }
-    uint32_t r = 1u; // e0^T A^0
+    // Row vectors e0^T A^q: x(p + q) = parity(row_q & state). Column j of the 32-bit output word w collects bit q = 32 w + i.
+    uint32_t r = 1u;
     for (int q = 0; q < FEC_DEMOD_TILE_WORDS * 32; ++q) {
-      (g == 0 ? t->B[q].x : t->B[q].y) = r;
+      for (int j = 0; j < 31; ++j) {
+        if ((r >> j) & 1u) {
+          // state bit j of LFSR g is bit (31 g + j) of the combined state: nibble (31 g + j) / 4, value bit (31 g + j) % 4
+          const int sb = 31 * g + j;
+          for (int v = 0; v < 16; ++v) {
+            if ((v >> (sb & 3)) & 1) {
+              t->L[sb >> 2][v][q >> 5] ^= 1u << (q & 31);
+            }
+          }
+        }
+      }
       uint32_t nx = 0;
       for (int j = 0; j < 31; ++j) {
         if ((r >> j) & 1u) {
@@ -445,19 +459,16 @@ __global__ void __launch_bounds__(FEC_DEMOD_THREADS)
       }
     }
     __syncthreads();
-    // c(p + q) = parity((B[q].x & s1) ^ (B[q].y & s2)): one lane per bit, one ballot per word, warp w takes words w, w + 8 ...
-    // (all 8 * qm words of a full tile, also where the call ends earlier: the surplus is never read)
-    const uint32_t s1 = state[0], s2 = state[1];
-    const uint2*   Bq = T->B + tid;
+    // Word w of the tile's sequence = XOR of one table row per nibble of the combined state: threads 0 .. 8 qm - 1, one word
+    // each (a full tile holds 256 * qm bits; where the call ends earlier the surplus is never read).
+    if (tid < 8 * qm) {
+      const uint64_t S  = (uint64_t)state[0] | ((uint64_t)state[1] << 31);
+      uint32_t       wd = 0;
 #pragma unroll
-    for (uint32_t r = 0; r < FEC_DEMOD_TILE_WORDS * 32 / FEC_DEMOD_THREADS; ++r) {
-      if (r < qm) { // a full tile holds 256 * qm bits = qm rounds of 8 words
-        const uint2    m  = Bq[r * FEC_DEMOD_THREADS];
-        const uint32_t wd = __ballot_sync(0xffffffffu, __popc((m.x & s1) ^ (m.y & s2)) & 1);
-        if (lane == 0) {
-          seq[(tid >> 5) + r * (FEC_DEMOD_THREADS / 32)] = wd;
-        }
+      for (int n = 0; n < 16; ++n) {
+        wd ^= T->L[n][(uint32_t)(S >> (4 * n)) & 15u][tid];
       }
+      seq[tid] = wd;
     }
   }
   __syncthreads();

@@ -188,7 +188,8 @@ struct fec_engine {
   float*            d_dm_noise = nullptr;
   int8_t*           d_dm_llr   = nullptr;
   size_t            dm_descs_cap = 0, dm_sym_cap = 0, dm_noise_cap = 0, dm_llr_cap = 0;
-  std::vector<fec_demod_desc> dm_descs_host;
+  fec_demod_desc*   h_dm_descs   = nullptr; // pinned copy of the call's descriptors, prepared and rebased
+  size_t            h_dm_descs_cap = 0;
   // weights of the last transport-block geometry seen (the same allocation usually repeats slot after slot)
   uint32_t              wc_key[3] = {0, 0, 0}; // nof_cbs, data_bits, stream_bits
   std::vector<uint32_t> wc_weights;
@@ -467,6 +468,7 @@ void fec_engine_destroy(fec_engine* e)
   cudaFree(e->d_dm_sym);
   cudaFree(e->d_dm_noise);
   cudaFree(e->d_dm_llr);
+  cudaFreeHost(e->h_dm_descs);
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
   if (e->stream) {
@@ -1463,9 +1465,20 @@ int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l
   }
   size_t   s0 = ~(size_t)0, s1 = 0, covered = 0;
   uint32_t max_symbols = 0;
-  e->dm_descs_host.assign(dm.descs, dm.descs + dm.n);
+  if ((size_t)dm.n > e->h_dm_descs_cap) {
+    cudaFreeHost(e->h_dm_descs);
+    e->h_dm_descs     = nullptr;
+    e->h_dm_descs_cap = 0;
+    const size_t cap  = (size_t)dm.n * 2;
+    if (cudaHostAlloc((void**)&e->h_dm_descs, cap * sizeof(fec_demod_desc), cudaHostAllocDefault) != cudaSuccess) {
+      cudaGetLastError();
+      return fail(FEC_ERR_NO_MEMORY, "cannot allocate pinned memory for %u demodulation descriptors", dm.n);
+    }
+    e->h_dm_descs_cap = cap;
+  }
+  memcpy(e->h_dm_descs, dm.descs, (size_t)dm.n * sizeof(fec_demod_desc));
   for (uint32_t i = 0; i < dm.n; ++i) {
-    fec_demod_desc& d = e->dm_descs_host[i];
+    fec_demod_desc& d = e->h_dm_descs[i];
     rc                = fec_demod_desc_prepare(&d);
     if (rc != FEC_OK) {
       return rc;
@@ -1485,9 +1498,9 @@ int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l
   if (covered != l1 - l0) {
     return fail(FEC_ERR_BAD_ARG, "the demodulation calls produce %zu LLRs, the transport blocks read %zu", covered, l1 - l0);
   }
-  for (fec_demod_desc& d : e->dm_descs_host) {
-    d.sym_offset -= s0;
-    d.llr_offset -= l0;
+  for (uint32_t i = 0; i < dm.n; ++i) {
+    e->h_dm_descs[i].sym_offset -= s0;
+    e->h_dm_descs[i].llr_offset -= l0;
   }
   rc = grow((void**)&e->d_dm_descs, &e->dm_descs_cap, (size_t)dm.n * sizeof(fec_demod_desc));
   rc = (rc == FEC_OK) ? grow((void**)&e->d_dm_sym, &e->dm_sym_cap, (s1 - s0) * 2 * sizeof(float)) : rc;
@@ -1495,7 +1508,7 @@ int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l
   if (rc != FEC_OK) {
     return rc;
   }
-  CU_TRY(cudaMemcpyAsync(e->d_dm_descs, e->dm_descs_host.data(), (size_t)dm.n * sizeof(fec_demod_desc), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(e->d_dm_descs, e->h_dm_descs, (size_t)dm.n * sizeof(fec_demod_desc), cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(e->d_dm_sym, dm.h_symbols + 2 * s0, (s1 - s0) * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(e->d_dm_noise, dm.h_noise + s0, (s1 - s0) * sizeof(float), cudaMemcpyHostToDevice, st));
   return demod_launch(e, st, e->d_dm_descs, dm.n, max_symbols, e->d_dm_sym, e->d_dm_noise, d_llr, dm.flavour);
