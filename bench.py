@@ -482,7 +482,14 @@ def bench_pusch_demod(fec, eng, torch, dev, stream, args):
            "value": n_tb * G / (ms * 1e-3) / 1e9, "unit": "G soft bits/s", "codewords_per_launch": n_tb, "ms_per_launch": ms,
            "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "peak_source": peak_src,
                         "unit": "GB/s", "frac": algo / (ms * 1e-3) / 1e9 / peak,
-                        "algorithmic_bytes_per_symbol": 12 + qm},
+                        "algorithmic_bytes_per_symbol": 12 + qm,
+                        # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this workload (ncu --set full,
+                        # profiles/r01_ncu_demod_full_metrics.csv: 94.4 MB read + 30.6 MB written for 7 851 648 symbols; the
+                        # rest of the 62.8 MB of soft bits is still in L2 when the kernel ends), scaled to this launch
+                        "traffic": n_tb * nsym * 15.9, "traffic_unit": "bytes/launch",
+                        "kernel": "fec_demod_kernel (1 launch/step)",
+                        "note": "issue-bound: 66 % of the issue slots busy, ALU pipe 54 %; exact emulation of the "
+                                "reference's float pipeline costs ~330 instructions per 256QAM symbol"},
            "symbols_to_codeblocks_device_resident": {
                "value": n_tb * info_bits / (ms_fused * 1e-3) / 1e9, "unit": "Gbit/s (decoded info bits)", "ms_per_step": ms_fused,
                "launches_per_step": 2, "cb_crc_pass_fraction": float(((rr["status"] & fec.RES_CRC_PASS) != 0).mean()),

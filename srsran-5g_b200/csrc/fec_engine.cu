@@ -13,6 +13,7 @@
 #include "fec_demod.cuh"
 #include "ldpc_tables.h"
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -1074,6 +1075,11 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   if (rc != FEC_OK) {
     return rc;
   }
+  // FEC_B200_TRACE=1: host timestamps of the call's phases on stderr (diagnostic; off by default).
+  static const bool trace = getenv("FEC_B200_TRACE") != nullptr;
+  const auto        now   = [] { return std::chrono::steady_clock::now(); };
+  const auto        t_in  = now();
+  auto              t_seg = t_in, t_enq = t_in, t_sync = t_in;
   // Pass 0: geometry of every block, so that the sizes of everything that follows are known.
   e->tb_geo.resize(n);
   uint32_t n_map = 0, max_Z = 0;
@@ -1180,6 +1186,7 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   for (uint32_t i = 0; i < n_map; ++i) {
     h_descs[i].llr_offset -= l0; // the staged LLRs start at l0
   }
+  t_seg = now();
   CU_TRY(cudaSetDevice(e->cfg.device));
   cudaStream_t         st      = e->stream;
   const fec_tb_job*    d_jobs  = reinterpret_cast<const fec_tb_job*>(e->d_meta);
@@ -1217,7 +1224,9 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
     CU_TRY(cudaMemcpyAsync(e->h_tbout + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8,
                            cudaMemcpyDeviceToHost, st));
   }
+  t_enq = now();
   CU_TRY(cudaStreamSynchronize(st));
+  t_sync = now();
   // Pass 2: deliver the transport blocks whose codeblocks are all good, update the per-codeblock state.
   const fec_cb_result* h_cbres = reinterpret_cast<const fec_cb_result*>(e->h_rblk);
   const fec_tb_result* h_tbres = reinterpret_cast<const fec_tb_result*>(e->h_rblk + off_tbres);
@@ -1259,6 +1268,13 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
         e->cb_ok[h_map[J.map_first + r].slot].store(0);
       }
     }
+  }
+  if (trace) {
+    const auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+      return std::chrono::duration<double, std::micro>(b - a).count();
+    };
+    fprintf(stderr, "fec_b200 trace: tb_run n=%u cbs=%u segment %.1f us, enqueue %.1f us, wait %.1f us, deliver %.1f us\n", n, n_map,
+            us(t_in, t_seg), us(t_seg, t_enq), us(t_enq, t_sync), us(t_sync, now()));
   }
   return FEC_OK;
 }
