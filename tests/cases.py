@@ -98,3 +98,16 @@ def demod_random_symbols(rng, qm, n, specials=True):
         sym[rng.integers(0, n, 1), 0] = 1e-10
         sym[rng.integers(0, n, 1)] = [1e-6, -1e-6]
     return sym, nv
+
+
+def demod_extreme_symbols(rng, qm, n=4099):
+    """Inputs outside anything an equaliser produces, where the reference's behaviour comes from x86 conversion rules and
+    IEEE special values rather than from its formulas: huge, infinite and NaN symbols (float -> int32 out of range gives
+    0x80000000 and the interval index clamps to 0), denormal noise variances (1 / var = inf, 0 * inf = NaN -> LLR 0)."""
+    sym, nv = demod_random_symbols(rng, qm, n)
+    special = np.array([1e5, -1e5, 3e9, -3e9, 16384.0, -16383.9, np.inf, -np.inf, np.nan, 1e30, -1e30, 2.5e8, -2.5e8],
+                       np.float32)
+    idx = rng.choice(n, 60, replace=False)
+    sym[idx[:40], rng.integers(0, 2, 40)] = rng.choice(special, 40)
+    nv[idx[40:]] = rng.choice(np.array([1e-42, 1e-39, 1e38, 3e38, np.inf, 1e-30], np.float32), 20)
+    return sym, nv

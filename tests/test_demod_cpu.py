@@ -51,6 +51,8 @@ def test_oracle_vs_reference_live(orc, dorc, flavour):
             sym, nv = cases.demod_random_symbols(rng, qm, n)
             for pi2 in ((False, True) if qm == 1 else (False,)):
                 assert (dorc.demodulate_soft(flavour, qm, sym, nv, pi2) == ref.demodulate_soft(qm, sym, nv, pi2)).all(), (qm, n)
+        sym, nv = cases.demod_extreme_symbols(rng, qm)
+        assert (dorc.demodulate_soft(flavour, qm, sym, nv) == ref.demodulate_soft(qm, sym, nv)).all(), ("extreme", qm)
         for nvv in (1.0, 0.5, 0.1, 0.3):
             for shift in range(3):  # moves every crafted symbol through the positions of the SIMD block
                 sym = np.concatenate([np.full((shift, 2), 0.3, np.float32), cases.demod_crafted_symbols(qm, nvv)])

@@ -63,6 +63,11 @@ def test_mapper_interface_random_lengths(fec, engine, dorc):
                 llr = np.zeros(n * qm, np.int8)
                 dm.demodulate_soft(llr, sym.view(np.complex64).reshape(-1), nv, MODS[qm])
                 assert (llr == dorc.demodulate_soft(flavour, qm, sym, nv)).all(), (flavour, qm, n)
+            # the fully general instantiation: huge / infinite / NaN symbols, denormal and huge noise variances
+            sym, nv = cases.demod_extreme_symbols(rng, qm)
+            llr = np.zeros(len(nv) * qm, np.int8)
+            dm.demodulate_soft(llr, sym, nv, MODS[qm])
+            assert (llr == dorc.demodulate_soft(flavour, qm, sym, nv)).all(), ("extreme", flavour, qm)
         llr = np.zeros(101, np.int8)
         sym, nv = cases.demod_random_symbols(rng, 1, 101)
         dm.demodulate_soft(llr, sym, nv, "pi/2-BPSK")
