@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 4
+#define FEC_B200_ABI_VERSION 5
 
 typedef enum {
   FEC_OK             = 0,
@@ -240,6 +240,48 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
 
 /* Forgets the codeblock CRC flags of a slot range (rx buffer released / expired). */
 int fec_tb_reset_slots(fec_engine* e, uint32_t first_slot, uint32_t n);
+
+/* ---- HARQ buffer pool: the reference's rx_buffer_pool over the engine's HARQ slots ---------------- */
+/* Mirror of rx_buffer_pool / unique_rx_buffer (include/srsran/phy/upper/rx_buffer_pool.h:60-127, unique_rx_buffer.h:36-170;
+ * lib/phy/upper/rx_buffer_pool_impl.cpp:36-155, rx_buffer_impl.h:40-258, rx_buffer_codeblock_pool.h:62-103): a fixed number of
+ * buffers, each bound to an identifier (RNTI, HARQ process) while it is in use, each holding the HARQ slots ("absolute
+ * codeblock identifiers") of one transport block, taken from and returned to a FIFO free list. A reservation comes back
+ * LOCKED; the owner unlocks it (more transmissions may follow) or releases it (transport block delivered); run_slot expires
+ * reservations that were not renewed. Freed slots are handed to fec_harq_free / fec_tb_reset_slots. The slot lists go into
+ * fec_tb_run_host (fec_tb_desc.slot_list). */
+typedef struct fec_harq_pool fec_harq_pool;
+
+typedef struct fec_harq_pool_cfg {
+  uint32_t nof_buffers;          /* rx_buffer_pool_config::nof_buffers                                                      */
+  uint32_t first_slot;           /* the pool owns engine HARQ slots [first_slot, first_slot + nof_codeblocks)               */
+  uint32_t nof_codeblocks;       /* rx_buffer_pool_config::nof_codeblocks                                                   */
+  uint32_t expire_timeout_slots; /* rx_buffer_pool_config::expire_timeout_slots                                             */
+  uint32_t numerology;           /* 0..4: slot counts wrap at 10240 << numerology (slot_point)                              */
+  uint32_t reserved[3];
+} fec_harq_pool_cfg;
+
+/* fec_harq_pool_reserve results: 0 = reserved; > 0 = the reason the reference returns an invalid unique_rx_buffer for. */
+#define FEC_POOL_OK            0
+#define FEC_POOL_STOPPED       1 /* the pool was stopped                                                                    */
+#define FEC_POOL_RETX_UNKNOWN  2 /* "identifier for retransmissions not found"                                              */
+#define FEC_POOL_NO_BUFFER     3 /* "insufficient buffers in the pool"                                                      */
+#define FEC_POOL_CB_MISMATCH   4 /* "number of codeblocks for retransmission do not match"                                  */
+#define FEC_POOL_IN_USE        5 /* "HARQ already in use" (the buffer is locked)                                            */
+#define FEC_POOL_NO_CODEBLOCKS 6 /* "exhausted CB pool"                                                                     */
+#define FEC_POOL_INVALID_BUFFER 0xffffffffu
+
+/* e may be NULL: the pool then only keeps the books (no engine notifications; host-only use and tests). */
+int  fec_harq_pool_create(fec_engine* e, const fec_harq_pool_cfg* cfg, fec_harq_pool** out);
+void fec_harq_pool_destroy(fec_harq_pool* p);
+/* rx_buffer_pool::reserve(slot, id, nof_codeblocks, new_data). slot = slot_point::system_slot(); id != 0xffffffff. */
+int fec_harq_pool_reserve(fec_harq_pool* p, uint32_t slot, uint32_t id, uint32_t nof_codeblocks, int new_data, uint32_t* buffer);
+/* unique_rx_buffer::get_absolute_codeblock_id for every codeblock: returns their number, copies up to max of them. */
+int fec_harq_pool_codeblocks(fec_harq_pool* p, uint32_t buffer, uint32_t* slots, uint32_t max);
+int fec_harq_pool_unlock(fec_harq_pool* p, uint32_t buffer);  /* unique_rx_buffer::unlock / destructor                      */
+int fec_harq_pool_release(fec_harq_pool* p, uint32_t buffer); /* unique_rx_buffer::release                                  */
+int fec_harq_pool_run_slot(fec_harq_pool* p, uint32_t slot);  /* rx_buffer_pool::run_slot                                   */
+int fec_harq_pool_stop(fec_harq_pool* p);                     /* rx_buffer_pool_controller::stop (no more reservations)     */
+int fec_harq_pool_nof_free_codeblocks(fec_harq_pool* p);
 
 /* ---- downlink twin: LDPC encoding + rate matching of PDSCH codeblocks ---------------------------- */
 /* One operation = one codeblock in the accelerator's CB mode (pdsch_encoder_hw_impl.cpp:96-111): the segment the

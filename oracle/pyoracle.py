@@ -476,6 +476,45 @@ class TbOracle:
         return self.buffers.get(buffer_id)
 
 
+class RefPool:
+    """The reference's rx_buffer_pool_impl alone (oracle/_ref): reserve returns a handle or None."""
+
+    def __init__(self, ref, nof_buffers, nof_codeblocks, expire_timeout_slots, numerology=0):
+        self.lib = ref.lib
+        self.lib.ref_pool_create.restype = C.c_void_p
+        self.lib.ref_pool_create.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_uint]
+        self.lib.ref_pool_destroy.argtypes = [C.c_void_p]
+        self.lib.ref_pool_reserve.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_int]
+        self.lib.ref_pool_codeblocks.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
+        for f in (self.lib.ref_pool_unlock, self.lib.ref_pool_release, self.lib.ref_pool_run_slot):
+            f.argtypes = [C.c_void_p, C.c_uint]
+            f.restype = None
+        self.h = self.lib.ref_pool_create(nof_buffers, nof_codeblocks, expire_timeout_slots, numerology)
+
+    def close(self):
+        if self.h:
+            self.lib.ref_pool_destroy(self.h)
+            self.h = None
+
+    def reserve(self, slot, identifier, nof_codeblocks, new_data):
+        h = self.lib.ref_pool_reserve(self.h, slot, identifier, nof_codeblocks, int(new_data))
+        return None if h < 0 else h
+
+    def codeblocks(self, handle):
+        ids = np.zeros(256, np.uint32)
+        n = self.lib.ref_pool_codeblocks(self.h, handle, _p(ids))
+        return ids[:n].copy()
+
+    def unlock(self, handle):
+        self.lib.ref_pool_unlock(self.h, handle)
+
+    def release(self, handle):
+        self.lib.ref_pool_release(self.h, handle)
+
+    def run_slot(self, slot):
+        self.lib.ref_pool_run_slot(self.h, slot)
+
+
 class RefTb:
     """The reference's pusch_decoder_impl + rx buffer pool (oracle/_ref, generic LDPC kernels)."""
 

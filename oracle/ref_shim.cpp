@@ -571,4 +571,84 @@ int ref_tb_peek(void* h, unsigned buffer_id, unsigned nof_cbs, unsigned cb_len, 
   return static_cast<int>(nof_cbs);
 }
 
+// ---- rx buffer pool alone (differential test of the engine's HARQ buffer pool) ---------------------------------------------
+namespace {
+struct ref_pool_ctx {
+  std::unique_ptr<rx_buffer_pool_controller> pool;
+  unsigned                                   numerology = 0;
+  std::map<unsigned, unique_rx_buffer>       held; // reservations handed out and not yet unlocked / released
+  unsigned                                   next = 0;
+};
+} // namespace
+
+void* ref_pool_create(unsigned nof_buffers, unsigned nof_codeblocks, unsigned expire_timeout_slots, unsigned numerology)
+{
+  auto                  ctx = new ref_pool_ctx();
+  rx_buffer_pool_config pc;
+  pc.max_codeblock_size   = ldpc::MAX_CODEBLOCK_SIZE;
+  pc.nof_buffers          = nof_buffers;
+  pc.nof_codeblocks       = nof_codeblocks;
+  pc.expire_timeout_slots = expire_timeout_slots;
+  pc.external_soft_bits   = true;
+  ctx->pool               = create_rx_buffer_pool(pc);
+  ctx->numerology         = numerology;
+  return ctx;
+}
+
+void ref_pool_destroy(void* h)
+{
+  auto ctx = static_cast<ref_pool_ctx*>(h);
+  ctx->held.clear();
+  delete ctx;
+}
+
+/// rx_buffer_pool::reserve. Returns a handle >= 0 for a valid unique_rx_buffer, -1 for an invalid one.
+int ref_pool_reserve(void* h, unsigned slot, unsigned id, unsigned nof_codeblocks, int new_data)
+{
+  auto             ctx = static_cast<ref_pool_ctx*>(h);
+  unique_rx_buffer buf =
+      ctx->pool->get_pool().reserve(slot_point(ctx->numerology, slot), trx_buffer_identifier((uint16_t)(id >> 8), (uint8_t)(id & 0xffu)), nof_codeblocks, new_data != 0);
+  if (!buf.is_valid()) {
+    return -1;
+  }
+  unsigned handle = ctx->next++;
+  ctx->held.emplace(handle, std::move(buf));
+  return (int)handle;
+}
+
+int ref_pool_codeblocks(void* h, unsigned handle, unsigned* ids)
+{
+  auto ctx = static_cast<ref_pool_ctx*>(h);
+  auto it  = ctx->held.find(handle);
+  if (it == ctx->held.end()) {
+    return -1;
+  }
+  unsigned n = it->second.get().get_nof_codeblocks();
+  for (unsigned i = 0; i != n; ++i) {
+    ids[i] = it->second.get().get_absolute_codeblock_id(i);
+  }
+  return (int)n;
+}
+
+void ref_pool_unlock(void* h, unsigned handle)
+{
+  static_cast<ref_pool_ctx*>(h)->held.erase(handle); // the destructor unlocks
+}
+
+void ref_pool_release(void* h, unsigned handle)
+{
+  auto ctx = static_cast<ref_pool_ctx*>(h);
+  auto it  = ctx->held.find(handle);
+  if (it != ctx->held.end()) {
+    it->second.release();
+    ctx->held.erase(it);
+  }
+}
+
+void ref_pool_run_slot(void* h, unsigned slot)
+{
+  auto ctx = static_cast<ref_pool_ctx*>(h);
+  ctx->pool->get_pool().run_slot(slot_point(ctx->numerology, slot));
+}
+
 } // extern "C"

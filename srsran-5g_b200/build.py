@@ -6,7 +6,7 @@ import subprocess
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libfec_b200.so")
-SOURCES = ["fec_engine.cu"]
+SOURCES = ["fec_engine.cu", "fec_harq_pool.cpp"]
 HEADERS = ["fec_device.cuh", "fec_kernel_generic.cuh", "fec_kernel_packed.cuh", "fec_tb.cuh", "fec_encode.cuh", "fec_demod.cuh", "ldpc_tables.h",
            os.path.join("..", "..", "include", "fec_b200.h")]
 NVCC_FLAGS = (["-DFEC_PROFILE=" + os.environ["FEC_PROFILE"]] if os.environ.get("FEC_PROFILE") else []) + \

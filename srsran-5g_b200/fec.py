@@ -84,13 +84,23 @@ class EngineCfg(C.Structure):
                 ("kernel_variant", C.c_uint32), ("reserved", C.c_uint32)]
 
 
+class HarqPoolCfg(C.Structure):
+    _fields_ = [("nof_buffers", C.c_uint32), ("first_slot", C.c_uint32), ("nof_codeblocks", C.c_uint32),
+                ("expire_timeout_slots", C.c_uint32), ("numerology", C.c_uint32), ("reserved", C.c_uint32 * 3)]
+
+
+POOL_OK, POOL_STOPPED, POOL_RETX_UNKNOWN, POOL_NO_BUFFER, POOL_CB_MISMATCH, POOL_IN_USE, POOL_NO_CODEBLOCKS = range(7)
+
+
 EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_engine_create", "fec_engine_destroy",
            "fec_engine_stream", "fec_harq_slot_ptr", "fec_engine_launch_count", "fec_desc_prepare",
            "fec_launch_device", "fec_run_host", "fec_host_alloc", "fec_host_free", "fec_harq_free", "fec_harq_read",
            "fec_harq_write", "fec_harq_flush", "fec_queue_reserve", "fec_queue_free", "fec_queue_enqueue", "fec_queue_flush",
            "fec_queue_poll", "fec_queue_fetch", "fec_tb_segment", "fec_tb_run_host", "fec_tb_reset_slots",
            "fec_enc_desc_prepare", "fec_encode_launch_device", "fec_encode_run_host", "fec_demod_desc_prepare",
-           "fec_demod_launch_device", "fec_demod_run_host", "fec_tb_run_host_symbols"]
+           "fec_demod_launch_device", "fec_demod_run_host", "fec_tb_run_host_symbols", "fec_harq_pool_create",
+           "fec_harq_pool_destroy", "fec_harq_pool_reserve", "fec_harq_pool_codeblocks", "fec_harq_pool_unlock",
+           "fec_harq_pool_release", "fec_harq_pool_run_slot", "fec_harq_pool_stop", "fec_harq_pool_nof_free_codeblocks"]
 
 _lib = None
 
@@ -145,6 +155,15 @@ def load_library():
     lib.fec_encode_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
     lib.fec_encode_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p,
                                         C.c_size_t]
+    lib.fec_harq_pool_create.argtypes = [C.c_void_p, C.POINTER(HarqPoolCfg), C.POINTER(C.c_void_p)]
+    lib.fec_harq_pool_destroy.argtypes = [C.c_void_p]
+    lib.fec_harq_pool_destroy.restype = None
+    lib.fec_harq_pool_reserve.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(C.c_uint32)]
+    lib.fec_harq_pool_codeblocks.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+    for f in (lib.fec_harq_pool_unlock, lib.fec_harq_pool_release, lib.fec_harq_pool_run_slot):
+        f.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_harq_pool_stop.argtypes = [C.c_void_p]
+    lib.fec_harq_pool_nof_free_codeblocks.argtypes = [C.c_void_p]
     lib.fec_demod_desc_prepare.argtypes = [C.c_void_p]
     lib.fec_demod_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_uint32]
@@ -441,6 +460,47 @@ class CodeblockMetadata:
         self.nof_filler_bits = nof_filler_bits
         self.nof_crc_bits = nof_crc_bits
         self.rm_length = rm_length
+
+
+class HarqPool:
+    """rx_buffer_pool over the engine's HARQ slots (include/srsran/phy/upper/rx_buffer_pool.h:60-127): reserve returns
+    (status, buffer); a reserved buffer is locked until unlock() or release(). `engine` may be None (bookkeeping only)."""
+
+    def __init__(self, engine, nof_buffers, nof_codeblocks, expire_timeout_slots, first_slot=0, numerology=0):
+        self.lib = load_library()
+        cfg = HarqPoolCfg(nof_buffers, first_slot, nof_codeblocks, expire_timeout_slots, numerology)
+        self.h = C.c_void_p()
+        _check(self.lib, self.lib.fec_harq_pool_create(None if engine is None else engine.h, C.byref(cfg), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.fec_harq_pool_destroy(self.h)
+            self.h = None
+
+    def reserve(self, slot, identifier, nof_codeblocks, new_data):
+        buf = C.c_uint32()
+        st = _check(self.lib, self.lib.fec_harq_pool_reserve(self.h, slot, identifier, nof_codeblocks, int(new_data), C.byref(buf)))
+        return st, (buf.value if st == POOL_OK else None)
+
+    def codeblocks(self, buffer):
+        ids = np.zeros(MAX_TB_CBS, np.uint32)
+        n = _check(self.lib, self.lib.fec_harq_pool_codeblocks(self.h, buffer, ids.ctypes.data, ids.size))
+        return ids[:n].copy()
+
+    def unlock(self, buffer):
+        _check(self.lib, self.lib.fec_harq_pool_unlock(self.h, buffer))
+
+    def release(self, buffer):
+        _check(self.lib, self.lib.fec_harq_pool_release(self.h, buffer))
+
+    def run_slot(self, slot):
+        _check(self.lib, self.lib.fec_harq_pool_run_slot(self.h, slot))
+
+    def stop(self):
+        _check(self.lib, self.lib.fec_harq_pool_stop(self.h))
+
+    def nof_free_codeblocks(self):
+        return _check(self.lib, self.lib.fec_harq_pool_nof_free_codeblocks(self.h))
 
 
 class DemodulationMapper:

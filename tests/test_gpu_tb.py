@@ -261,3 +261,70 @@ def test_multi_cell_batch_config5_sharded(fec, orc, oracle):
                 assert (outs[i] == out0[c]).all(), (world, rank, c)
                 assert cbr[i].tobytes() == cbr0[c].tobytes(), (world, rank, c)
     eng.close()
+
+
+def test_harq_pool_drives_the_tb_interface(fec, orc, oracle):
+    """HARQ processes of several UEs through the engine's buffer pool (fec_harq_pool_*), the way
+    pusch_processor uses rx_buffer_pool: reserve(new data) -> decode -> unlock on a failed CRC / release on a good one,
+    retransmissions find their buffer by identifier, freed slots are reused by other processes and read as zeros, a
+    process that is never retransmitted expires. Results against the TB oracle (one oracle buffer per HARQ process)."""
+    rng = np.random.default_rng(314)
+    eng = fec.FecEngine(device=0, harq_slots=64, max_batch_cbs=64)
+    pool = fec.HarqPool(eng, nof_buffers=6, nof_codeblocks=64, expire_timeout_slots=8)
+    to = orc.TbOracle(oracle)
+    procs = []
+    for i in range(6):
+        p = cases.random_tb_params(rng, max_bits_bg1=26000, max_bits_bg2=9000)
+        tb = rng.integers(0, 256, p["tbs"] // 8, dtype=np.uint8)
+        procs.append(dict(p=p, g=orc.tb_geometry(p["tbs"], p["bg"], p["qm"], p["nl"], p["G"]), tb=tb, ident=(0x4600 + i) << 8 | (i % 4),
+                          enc=orc.tb_encode(oracle, tb, p["bg"]), tx=0, done=False, obuf=i))
+    delivered = expired_checked = 0
+    slot = 0
+    for rnd in range(5):
+        for i, P in enumerate(procs):
+            if P["done"] or (i == 5 and rnd > 0):  # process 5 sends once, fails, and is left to expire
+                continue
+            p, rv = P["p"], [0, 2, 3, 1][P["tx"] % 4]
+            st, buf = pool.reserve(slot, P["ident"], P["g"]["C"], P["tx"] == 0)
+            assert st == fec.POOL_OK, (rnd, i, st)
+            slots = pool.codeblocks(buf)
+            snr = p["snr"] - (9.0 if i == 5 else 2.0)
+            llr = orc.tb_transmit(oracle, P["enc"], p["tbs"], p["bg"], rv, p["qm"], 0, p["nl"], p["G"], snr, seed=rnd * 50 + i)
+            d = fec.make_tb_descs(1)
+            d[0:1] = _tb_desc(fec, p, rv, P["tx"] == 0, 0, 0, 0)
+            d["slot_list"][0] = 0
+            out = np.zeros(p["tbs"] // 8, np.uint8)
+            res = eng.tb_run_host(d, llr, out, slots=slots)
+            want = np.zeros(p["tbs"] // 8, np.uint8)
+            w = to.decode(P["obuf"], p["tbs"], p["bg"], rv, p["qm"], 0, p["nl"], P["tx"] == 0, 6, True, llr, want)
+            assert bool(res["tb_crc_ok"][0]) == w["tb_crc_ok"], (rnd, i)
+            if w["tb_crc_ok"]:
+                assert (out == P["tb"]).all()
+                pool.release(buf)
+                P["done"] = True
+                delivered += 1
+            else:
+                mine = to.peek(P["obuf"])
+                for r in range(P["g"]["C"]):
+                    assert (eng.harq_read(int(slots[r]), P["g"]["N"]) == mine["soft"][r]).all(), (rnd, i, r)
+                pool.unlock(buf)
+                P["tx"] += 1
+        slot += 3
+        pool.run_slot(slot)
+        if rnd == 3:
+            # process 5 was reserved at slot 0 with a timeout of 8 slots: gone by now, its retransmission is refused and its
+            # slots are back in the free list, zeroed for the next owner
+            assert pool.reserve(slot, procs[5]["ident"], procs[5]["g"]["C"], False)[0] == fec.POOL_RETX_UNKNOWN
+            expired_checked += 1
+    assert delivered >= 4 and expired_checked == 1
+    assert pool.nof_free_codeblocks() == 64 - sum(P["g"]["C"] for P in procs[:5] if not P["done"])
+    # a new process on recycled slots starts from zeros: decoding a clean block from them must match a fresh oracle buffer
+    P = procs[0]
+    st, buf = pool.reserve(slot, 0x7777 << 8, P["g"]["C"], True)
+    assert st == fec.POOL_OK
+    slots = pool.codeblocks(buf)
+    for s in slots:
+        assert (eng.harq_read(int(s), 64) == 0).all()
+    pool.release(buf)
+    pool.close()
+    eng.close()
