@@ -176,3 +176,31 @@ def test_transport_blocks_from_symbols(fec, engine, oracle, orc, dorc):
     # a gap in the demodulation calls is refused (the transport blocks would read stale LLRs)
     with pytest.raises(fec.FecError):
         engine.tb_run_host_symbols(d, alld[:-1], np.concatenate(syms), np.concatenate(nvs), out)
+
+
+def test_argument_checks(fec, engine):
+    """Invalid calls are refused with an error, never executed: unknown flavour, unsupported modulation order, descriptors
+    that index outside the symbol or LLR buffers, calls that do not tile one contiguous LLR span."""
+    sym, nv = np.zeros((64, 2), np.float32), np.ones(64, np.float32)
+    llr = np.zeros(64 * 2, np.int8)
+    d = fec.codeword_demod_descs([64], 2, 1)
+    with pytest.raises(fec.FecError):
+        engine.demod_run_host(d, sym, nv, llr, flavour=3)
+    bad = d.copy()
+    bad["qm"] = 3
+    with pytest.raises(fec.FecError):
+        engine.demod_run_host(bad, sym, nv, llr)
+    bad = d.copy()
+    bad["nof_symbols"] = 65  # one symbol more than the buffers hold
+    with pytest.raises(fec.FecError):
+        engine.demod_run_host(bad, sym, nv, np.zeros(130, np.int8))
+    bad = d.copy()
+    bad["llr_offset"] = 8  # writes past the end of the LLR buffer
+    with pytest.raises(fec.FecError):
+        engine.demod_run_host(bad, sym, nv, llr)
+    two = fec.make_demod_descs(2)
+    two[0:1], two[1:2] = fec.codeword_demod_descs([16], 2, 1), fec.codeword_demod_descs([16], 2, 1, sym_offset=16, llr_offset=40)
+    with pytest.raises(fec.FecError):  # a gap between the two calls
+        engine.demod_run_host(two, sym, nv, llr)
+    engine.demod_run_host(d, sym, nv, llr)  # and the engine is still usable afterwards
+    assert (llr == 0).all()  # zero symbols give zero soft bits
