@@ -378,9 +378,9 @@ __device__ __forceinline__ uint32_t fec_negate_bytes(uint32_t w, uint32_t bits4)
 }
 
 template <int QM, int FLAVOUR>
-__device__ __forceinline__ void fec_demod_tile(const fec_demod_desc& d, uint32_t tile, uint32_t nsym, const float2* __restrict__ symbols,
-                                               const float* __restrict__ noise, const fec_demod_smem_tab& T, float gain16,
-                                               float thr16, const uint32_t* seq, bool scramble, uint8_t* stage_at_phase)
+__device__ __forceinline__ void fec_demod_tile(const fec_demod_desc& d, uint32_t tile, uint32_t nsym, float2 s, float nv,
+                                               const fec_demod_smem_tab& T, float gain16, float thr16, const uint32_t* seq,
+                                               bool scramble, uint8_t* stage_at_phase)
 {
   const uint32_t tid = threadIdx.x;
   if (tid >= nsym) {
@@ -390,8 +390,6 @@ __device__ __forceinline__ void fec_demod_tile(const fec_demod_desc& d, uint32_t
   constexpr uint32_t V256 = (FLAVOUR >= 1) ? ((QM == 2) ? 16u : (QM == 4) ? 8u : (QM == 6) ? 16u : (QM == 8) ? 4u : 0u) : 0u;
   constexpr uint32_t V512 = (FLAVOUR >= 2) ? ((QM == 6) ? 32u : (QM == 8) ? 8u : 0u) : 0u;
   constexpr bool     FMA  = FLAVOUR >= 1;
-  const float2       s    = symbols[d.sym_offset + i];
-  const float        nv   = noise[d.sym_offset + i];
   const bool         odd  = (d.flags & FEC_DEMOD_FLAG_PI2_BPSK) && (i & 1u);
   uint2              r;
   if (V512 != 0 && i < d.nof_symbols / (V512 ? V512 : 1u) * V512) {
@@ -434,6 +432,13 @@ __global__ void __launch_bounds__(FEC_DEMOD_THREADS)
   const uint32_t nsym     = min(d.nof_symbols - tile, (uint32_t)FEC_DEMOD_THREADS);
   const uint32_t nbits    = nsym * qm;
   const bool     scramble = !(d.flags & FEC_DEMOD_FLAG_NO_DESCRAMBLE);
+  // The thread's symbol is requested first: its trip to HBM overlaps the sequence work below.
+  float2 sym = make_float2(0.0f, 0.0f);
+  float  nv  = 0.0f;
+  if (tid < nsym) {
+    sym = symbols[d.sym_offset + tile + tid];
+    nv  = noise[d.sym_offset + tile + tid];
+  }
   if (qm >= 6 && tid < 7 * 16) {
     const uint32_t row = tid >> 4, k = tid & 15u;
     tab.lin[row][k]    = make_float2(T->slope[row][k], T->icpt[row][k]);
@@ -477,7 +482,7 @@ __global__ void __launch_bounds__(FEC_DEMOD_THREADS)
   const float    g16 = T->gain16, t16 = T->thr16;
 #define FEC_DEMOD_CASE(Q, F)                                                                                                  \
   case (Q) * 4 + (F):                                                                                                          \
-    fec_demod_tile<Q, F>(d, tile, nsym, symbols, noise, tab, g16, t16, seq, scramble, stage + phase);                          \
+    fec_demod_tile<Q, F>(d, tile, nsym, sym, nv, tab, g16, t16, seq, scramble, stage + phase);                          \
     break;
   switch (qm * 4 + flavour) {
     FEC_DEMOD_CASE(1, 0) FEC_DEMOD_CASE(1, 1) FEC_DEMOD_CASE(1, 2)
