@@ -43,14 +43,23 @@ int fail(int code, const char* fmt, ...)
     }                                                                                                                  \
   } while (0)
 
+// Index of a lifting size in the table of the 51 NR lifting sizes, -1 if it is not one. Table look-up: this runs once per
+// descriptor of every host-side call (7104 times per step of the headline batch).
 int z_index(unsigned Z)
 {
-  for (int i = 0; i < 51; ++i) {
-    if (FEC_ALL_Z[i] == Z) {
-      return i;
+  static const struct lut_t {
+    int8_t idx[385];
+    lut_t()
+    {
+      for (int8_t& v : idx) {
+        v = -1;
+      }
+      for (int i = 0; i < 51; ++i) {
+        idx[FEC_ALL_Z[i]] = (int8_t)i;
+      }
     }
-  }
-  return -1;
+  } lut;
+  return (Z <= 384) ? lut.idx[Z] : -1;
 }
 
 const uint32_t CRC_POLY[3] = {0x11021u, 0x1800063u, 0x1864CFBu}; // FEC_CRC16, FEC_CRC24B, FEC_CRC24A
@@ -233,10 +242,19 @@ int launch(fec_engine*          e,
   return FEC_OK;
 }
 
+// Same operation parameters (everything fec_desc_prepare looks at), placement fields aside.
+inline bool same_shape(const fec_cb_desc& a, const fec_cb_desc& b)
+{
+  return a.E == b.E && a.Nref == b.Nref && a.nof_filler_bits == b.nof_filler_bits && a.lifting_size == b.lifting_size &&
+         a.base_graph == b.base_graph && a.rv == b.rv && a.qm == b.qm && a.crc_type == b.crc_type && a.max_iter == b.max_iter &&
+         a.mode == b.mode && a.flags == b.flags;
+}
+
 // Freed slots are zeroed lazily: the first host-driven operation on one carries FEC_FLAG_HARQ_ZERO.
 void apply_fresh(fec_engine* e, fec_cb_desc& d)
 {
-  if (d.mode != FEC_MODE_DECODE && d.harq_slot < e->cfg.harq_slots && e->fresh[d.harq_slot].exchange(0)) {
+  if (d.mode != FEC_MODE_DECODE && d.harq_slot < e->cfg.harq_slots && e->fresh[d.harq_slot].load(std::memory_order_relaxed) &&
+      e->fresh[d.harq_slot].exchange(0)) {
     d.flags |= FEC_FLAG_HARQ_ZERO;
   }
 }
@@ -530,9 +548,17 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   uint32_t max_Z = 0;
   int      any1  = 0;
   for (uint32_t i = 0; i < n; ++i) {
-    int r = fec_desc_prepare(&h_descs[i]);
-    if (r != FEC_OK) {
-      return r;
+    // A descriptor with the parameters of its predecessor (the usual case: the codeblocks of one transport block) inherits
+    // its checked and derived fields instead of going through fec_desc_prepare again.
+    fec_cb_desc& cur = h_descs[i];
+    if (i > 0 && same_shape(cur, h_descs[i - 1])) {
+      cur.k0          = h_descs[i - 1].k0;
+      cur.graph_index = h_descs[i - 1].graph_index;
+    } else {
+      int r = fec_desc_prepare(&cur);
+      if (r != FEC_OK) {
+        return r;
+      }
     }
     const fec_cb_desc& d  = h_descs[i];
     const uint32_t     kb = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
