@@ -667,7 +667,7 @@ def run_ours(args):
                 "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
                 "config": workload_config(n), "per_gpu_gbps": value / world,
                 "crc_pass_fraction": float(passed.mean()),
-                "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + K // 8 + 48),
+                "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + 48),
                         "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
                 "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb, "pdsch_encode": enc, "pusch_demod": dmd,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",

@@ -545,6 +545,8 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     return fail(FEC_ERR_BAD_ARG, "batch of %u CBs / %zu LLR bytes / %zu output bytes exceeds the engine capacity", n,
                 llr_bytes, out_bytes);
   }
+  static const bool trace = getenv("FEC_B200_TRACE") != nullptr; // host timestamps of the call's phases on stderr
+  const auto        t_in  = std::chrono::steady_clock::now();
   uint32_t max_Z = 0;
   int      any1  = 0;
   for (uint32_t i = 0; i < n; ++i) {
@@ -575,11 +577,13 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     apply_fresh(e, h_descs[i]);
   }
   std::lock_guard<std::mutex> lk(e->run_mtx);
+  const auto                  t_prep = std::chrono::steady_clock::now();
   CU_TRY(cudaSetDevice(e->cfg.device));
   // Large batches are cut into chunks of one kernel wave (2 CTAs per SM) that travel on three streams, so that the H2D copy of one
   // chunk overlaps the kernels of the previous one and the D2H copy of the one before (PCIe is full duplex).
   const uint32_t wave  = 2u * (uint32_t)e->sm_count;
   uint32_t       chunk = (n >= 2 * wave) ? wave : n; // measured on B200: 1 wave beats 2, 3, 4 and 6 (e2e 11.4 vs 10.8 Gbit/s at 3)
+  // (also measured: 1/2, 3/4, 5/4, 3/2 and 2 waves per chunk, and a finer-cut first wave: all 1-3 % slower end to end)
   if (chunk != n) {
     // Chunks may only run concurrently if their slices of the batch buffers do not interleave.
     size_t prev_l1 = 0, prev_o1 = 0;
@@ -615,6 +619,10 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     size_t   l0 = ~(size_t)0, l1 = 0, o0 = ~(size_t)0, o1 = 0;
     uint32_t cz = 0;
     int      c1 = 0;
+    // Only an early-stop operation can leave its output bytes as they were; when none is in the chunk and the outputs tile
+    // the span without gaps, every byte of it is overwritten and the caller's bytes need not travel to the device first.
+    bool   keep     = false;
+    size_t next_out = h_descs[c0].out_offset;
     for (uint32_t i = c0; i < c0 + cn; ++i) {
       const fec_cb_desc& d  = h_descs[i];
       const uint32_t     kb = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
@@ -623,12 +631,15 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       if (d.mode != FEC_MODE_DEMATCH) {
         o0 = d.out_offset < o0 ? (size_t)d.out_offset : o0;
         o1 = (size_t)d.out_offset + kb > o1 ? (size_t)d.out_offset + kb : o1;
+        keep |= (d.out_offset != next_out);
+        next_out = (size_t)d.out_offset + kb;
       }
       cz = d.lifting_size > cz ? d.lifting_size : cz;
       c1 |= (d.base_graph == 1);
+      keep |= (d.flags & FEC_FLAG_EARLY_STOP) != 0;
     }
     CU_TRY(cudaMemcpyAsync(e->d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
-    if (out_bytes && o1 > o0) {
+    if (out_bytes && o1 > o0 && keep) {
       // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
       CU_TRY(cudaMemcpyAsync(e->d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, st));
     }
@@ -656,8 +667,17 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       }
     }
   }
+  const auto t_enq = std::chrono::steady_clock::now();
   CU_TRY(cudaStreamSynchronize(e->stream));
+  const auto t_sync = std::chrono::steady_clock::now();
   memcpy(h_results, e->h_res_pin, n * sizeof(fec_cb_result));
+  if (trace) {
+    const auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+      return std::chrono::duration<double, std::micro>(b - a).count();
+    };
+    fprintf(stderr, "fec_b200 trace: run_host n=%u chunks=%u prepare %.1f us, enqueue %.1f us, wait %.1f us, results %.1f us\n", n,
+            nchunks, us(t_in, t_prep), us(t_prep, t_enq), us(t_enq, t_sync), us(t_sync, std::chrono::steady_clock::now()));
+  }
   return FEC_OK;
 }
 
