@@ -167,6 +167,8 @@ struct fec_engine {
   std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
   cudaStream_t          pipe[3]      = {nullptr, nullptr, nullptr}; // fec_run_host chunk pipeline (copy/compute overlap)
   cudaEvent_t           pipe_done[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t          copy_in      = nullptr; // all input copies of a chunked call, in chunk order (one FIFO)
+  std::vector<cudaEvent_t> chunk_in;            // chunk c's inputs have arrived
   std::mutex            run_mtx; // serialises fec_run_host users of the shared staging below
   // staging for fec_run_host
   fec_cb_desc*   d_descs = nullptr;
@@ -408,6 +410,7 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   CU_TRY(cudaGetDeviceProperties(&prop, cfg->device));
   e->sm_count = prop.multiProcessorCount;
   CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  CU_TRY(cudaStreamCreateWithFlags(&e->copy_in, cudaStreamNonBlocking));
   for (int i = 0; i < 3; ++i) {
     CU_TRY(cudaStreamCreateWithFlags(&e->pipe[i], cudaStreamNonBlocking));
     CU_TRY(cudaEventCreateWithFlags(&e->pipe_done[i], cudaEventDisableTiming));
@@ -493,6 +496,12 @@ void fec_engine_destroy(fec_engine* e)
   if (e->stream) {
     cudaStreamDestroy(e->stream);
   }
+  if (e->copy_in) {
+    cudaStreamDestroy(e->copy_in);
+  }
+  for (cudaEvent_t ev : e->chunk_in) {
+    cudaEventDestroy(ev);
+  }
   for (int i = 0; i < 3; ++i) {
     if (e->pipe[i]) {
       cudaStreamDestroy(e->pipe[i]);
@@ -546,6 +555,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
                 llr_bytes, out_bytes);
   }
   static const bool trace = getenv("FEC_B200_TRACE") != nullptr; // host timestamps of the call's phases on stderr
+  static std::vector<cudaEvent_t> trace_ev;                      // and, per chunk, when its kernel started and ended
   const auto        t_in  = std::chrono::steady_clock::now();
   uint32_t max_Z = 0;
   int      any1  = 0;
@@ -584,11 +594,21 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   const uint32_t wave  = 2u * (uint32_t)e->sm_count;
   uint32_t       chunk = (n >= 2 * wave) ? wave : n; // measured on B200: 1 wave beats 2, 3, 4 and 6 (e2e 11.4 vs 10.8 Gbit/s at 3)
   // (also measured: 1/2, 3/4, 5/4, 3/2 and 2 waves per chunk, and a finer-cut first wave: all 1-3 % slower end to end)
+  // The first wave is cut finer (1/4, 1/4, 1/2 of a wave): the first kernel starts after a quarter of the first wave's copy
+  // instead of all of it; from then on the copy engine stays ahead of the SMs.
+  const auto chunk_len = [&](uint32_t c0) -> uint32_t {
+    if (chunk == n) {
+      return n;
+    }
+    const uint32_t q   = wave / 4;
+    const uint32_t len = (c0 < 2 * q) ? q : (c0 < wave) ? wave - 2 * q : wave;
+    return (n - c0 < len) ? (n - c0) : len;
+  };
   if (chunk != n) {
     // Chunks may only run concurrently if their slices of the batch buffers do not interleave.
     size_t prev_l1 = 0, prev_o1 = 0;
-    for (uint32_t c0 = 0; c0 < n && chunk != n; c0 += chunk) {
-      const uint32_t cn = (n - c0 < chunk) ? (n - c0) : chunk;
+    for (uint32_t c0 = 0, cn = 0; c0 < n && chunk != n; c0 += cn) {
+      cn = chunk_len(c0);
       size_t         l0 = ~(size_t)0, l1 = 0, o0 = ~(size_t)0, o1 = 0;
       for (uint32_t i = c0; i < c0 + cn; ++i) {
         const fec_cb_desc& d = h_descs[i];
@@ -612,9 +632,12 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     CU_TRY(cudaStreamWaitEvent(e->pipe[k], e->pipe_done[0], 0));
   }
   uint32_t nchunks = 0;
-  for (uint32_t c0 = 0; c0 < n; c0 += chunk, ++nchunks) {
-    const uint32_t cn = (n - c0 < chunk) ? (n - c0) : chunk;
-    cudaStream_t   st = (chunk == n) ? e->stream : e->pipe[nchunks % 3];
+  for (uint32_t c0 = 0, cn = 0; c0 < n; c0 += cn, ++nchunks) {
+    cn              = chunk_len(c0);
+    cudaStream_t st = (chunk == n) ? e->stream : e->pipe[nchunks % 3];
+    // Chunked calls send every input through ONE copy stream, in chunk order: copies issued on the three kernel streams
+    // were observed to complete out of order (chunk 0 third), which delays the first kernel by two chunk copies.
+    cudaStream_t in = (chunk == n) ? e->stream : e->copy_in;
     // byte ranges of the batch buffers this chunk touches
     size_t   l0 = ~(size_t)0, l1 = 0, o0 = ~(size_t)0, o1 = 0;
     uint32_t cz = 0;
@@ -638,14 +661,38 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       c1 |= (d.base_graph == 1);
       keep |= (d.flags & FEC_FLAG_EARLY_STOP) != 0;
     }
-    CU_TRY(cudaMemcpyAsync(e->d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaMemcpyAsync(e->d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, in));
     if (out_bytes && o1 > o0 && keep) {
       // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
-      CU_TRY(cudaMemcpyAsync(e->d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, st));
+      CU_TRY(cudaMemcpyAsync(e->d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, in));
+    }
+    if (in != st) {
+      if (e->chunk_in.size() <= nchunks) {
+        cudaEvent_t ev = nullptr;
+        CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        e->chunk_in.push_back(ev);
+      }
+      CU_TRY(cudaEventRecord(e->chunk_in[nchunks], in));
+      CU_TRY(cudaStreamWaitEvent(st, e->chunk_in[nchunks], 0));
+    }
+    if (trace && nchunks < 32) {
+      if (trace_ev.empty()) {
+        trace_ev.resize(65);
+        for (cudaEvent_t& ev : trace_ev) {
+          cudaEventCreate(&ev);
+        }
+      }
+      if (nchunks == 0) {
+        cudaEventRecord(trace_ev[64], e->stream); // after the descriptor copy
+      }
+      cudaEventRecord(trace_ev[2 * nchunks], st);
     }
     int r = launch(e, st, e->d_descs + c0, cn, e->d_llr, e->d_out, e->d_res + c0, cz, c1);
     if (r != FEC_OK) {
       return r;
+    }
+    if (trace && nchunks < 32) {
+      cudaEventRecord(trace_ev[2 * nchunks + 1], st);
     }
     if (out_bytes && o1 > o0) {
       CU_TRY(cudaMemcpyAsync(h_out + o0, e->d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, st));
@@ -677,6 +724,16 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     };
     fprintf(stderr, "fec_b200 trace: run_host n=%u chunks=%u prepare %.1f us, enqueue %.1f us, wait %.1f us, results %.1f us\n", n,
             nchunks, us(t_in, t_prep), us(t_prep, t_enq), us(t_enq, t_sync), us(t_sync, std::chrono::steady_clock::now()));
+    if (nchunks > 1 && !trace_ev.empty()) {
+      fprintf(stderr, "fec_b200 trace: chunk kernels [start, end] in us after the descriptor copy:");
+      for (uint32_t c = 0; c < nchunks && c < 32; ++c) {
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, trace_ev[64], trace_ev[2 * c]);
+        cudaEventElapsedTime(&b, trace_ev[64], trace_ev[2 * c + 1]);
+        fprintf(stderr, " [%.0f, %.0f]", a * 1e3f, b * 1e3f);
+      }
+      fprintf(stderr, "\n");
+    }
   }
   return FEC_OK;
 }
