@@ -77,8 +77,42 @@ class ClockSampler:
 
     def __init__(self, device):
         self.device, self.rows, self.proc = device, [], None
+        self.nvml_rows, self.nvml_stop, self.nvml_thread = [], None, None
+
+    def _start_nvml(self):
+        """NVML in-process, one sample every 2 ms: a 50 ms timed region still gets a couple of dozen samples under load
+        (nvidia-smi -lms 100 gets one at best; it stays as the fallback)."""
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            import torch
+            uuid = "GPU-" + str(torch.cuda.get_device_properties(self.device).uuid)
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.device)
+        smax = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+        self.nvml_stop = threading.Event()
+
+        def loop():
+            while not self.nvml_stop.is_set():
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    self.nvml_rows.append((time.time(), float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)), smax,
+                                           pynvml.nvmlDeviceGetPowerUsage(h) / 1e3, [k for k, b in bits.items() if r & b]))
+                except Exception:
+                    pass
+                time.sleep(0.002)
+
+        self.nvml_thread = threading.Thread(target=loop, daemon=True)
+        self.nvml_thread.start()
 
     def start(self):
+        try:
+            self._start_nvml()
+            return
+        except Exception:
+            self.nvml_thread = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + ",".join(self.FIELDS),
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
@@ -93,6 +127,14 @@ class ClockSampler:
             self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
 
     def stop(self, t0, t1):
+        if self.nvml_thread is not None:
+            self.nvml_stop.set()
+            self.nvml_thread.join(timeout=1.0)
+            rows = [r for r in self.nvml_rows if t0 <= r[0] <= t1] or self.nvml_rows[-3:]
+            if rows:
+                return {"sm_mhz": float(np.median([r[1] for r in rows])), "sm_max_mhz": rows[0][2],
+                        "power_w_max": max(r[3] for r in rows), "samples": len(rows),
+                        "reasons": sorted({x for r in rows for x in r[4]}), "source": "NVML, one sample per 2 ms inside the timed region"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
