@@ -169,6 +169,8 @@ struct fec_engine {
   cudaEvent_t           pipe_done[3] = {nullptr, nullptr, nullptr};
   cudaStream_t          copy_in      = nullptr; // all input copies of a chunked call, in chunk order (one FIFO)
   std::vector<cudaEvent_t> chunk_in;            // chunk c's inputs have arrived
+  std::vector<cudaEvent_t> chunk_out;           // chunk c's results and transport block bytes are back on the host
+  std::vector<uint32_t>    tb_chunk_end;        // pipelined transport-block call: one-past-last block of each chunk
   std::mutex            run_mtx; // serialises fec_run_host users of the shared staging below
   // staging for fec_run_host
   fec_cb_desc*   d_descs = nullptr;
@@ -500,6 +502,9 @@ void fec_engine_destroy(fec_engine* e)
     cudaStreamDestroy(e->copy_in);
   }
   for (cudaEvent_t ev : e->chunk_in) {
+    cudaEventDestroy(ev);
+  }
+  for (cudaEvent_t ev : e->chunk_out) {
     cudaEventDestroy(ev);
   }
   for (int i = 0; i < 3; ++i) {
@@ -1301,39 +1306,95 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   fec_cb_result* d_cbres   = reinterpret_cast<fec_cb_result*>(e->d_rblk);
   fec_tb_result* d_tbres   = reinterpret_cast<fec_tb_result*>(e->d_rblk + off_tbres);
   CU_TRY(cudaMemcpyAsync(e->d_meta, e->h_meta, meta_size, cudaMemcpyHostToDevice, st));
-  if (dm) {
-    rc = demod_stage(e, st, *dm, l0, l1, e->d_llr);
+  // Batches of two kernel waves or more (many cells per slot) are pipelined like fec_run_host: groups of whole transport
+  // blocks of about one wave, LLR copies in order on the copy stream, codeblock + gather kernels and the copy back of the
+  // block bytes on three streams. Needs the byte-aligned gather and LLR spans that follow one another in block order.
+  const uint32_t wave      = 2u * (uint32_t)e->sm_count;
+  bool           pipelined = !dm && aligned && n > 1 && n_map >= 2 * wave;
+  for (uint32_t t = 1; t < n && pipelined; ++t) {
+    pipelined = tbs[t].llr_offset >= tbs[t - 1].llr_offset + tbs[t - 1].nof_llrs;
+  }
+  e->tb_chunk_end.clear();
+  if (pipelined) {
+    CU_TRY(cudaEventRecord(e->pipe_done[0], st));
+    for (int k = 0; k < 3; ++k) {
+      CU_TRY(cudaStreamWaitEvent(e->pipe[k], e->pipe_done[0], 0));
+    }
+    uint32_t c = 0;
+    for (uint32_t t0 = 0, t1 = 0; t0 < n; t0 = t1, ++c) {
+      uint32_t cn = 0;
+      for (t1 = t0; t1 < n && (cn < wave || t1 == t0); ++t1) {
+        cn += h_jobs[t1].nof_cbs;
+      }
+      const uint32_t m0 = h_jobs[t0].map_first;
+      const size_t   a = (size_t)tbs[t0].llr_offset, b = (size_t)tbs[t1 - 1].llr_offset + tbs[t1 - 1].nof_llrs;
+      cudaStream_t   ps = e->pipe[c % 3];
+      CU_TRY(cudaMemcpyAsync(e->d_llr + (a - l0), h_llr + a, b - a, cudaMemcpyHostToDevice, e->copy_in));
+      if (e->chunk_in.size() <= c) {
+        cudaEvent_t ev = nullptr;
+        CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        e->chunk_in.push_back(ev);
+      }
+      CU_TRY(cudaEventRecord(e->chunk_in[c], e->copy_in));
+      CU_TRY(cudaStreamWaitEvent(ps, e->chunk_in[c], 0));
+      rc = launch(e, ps, d_descs + m0, cn, e->d_llr, e->d_msg, d_cbres + m0, max_Z, any1);
+      if (rc != FEC_OK) {
+        return rc;
+      }
+      fec_tb_gather_kernel<<<cn, 256, 0, ps>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres, d_scr, e->d_tab, m0);
+      CU_TRY(cudaGetLastError());
+      e->launches.fetch_add(1);
+      for (uint32_t t = t0; t < t1; ++t) {
+        CU_TRY(cudaMemcpyAsync(e->h_tbout + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8,
+                               cudaMemcpyDeviceToHost, ps));
+      }
+      // The chunk's own slice of the results follows, so that its blocks can be handed over while later chunks still run.
+      CU_TRY(cudaMemcpyAsync(e->h_rblk + (size_t)m0 * sizeof(fec_cb_result), e->d_rblk + (size_t)m0 * sizeof(fec_cb_result),
+                             (size_t)cn * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, ps));
+      CU_TRY(cudaMemcpyAsync(e->h_rblk + off_tbres + (size_t)t0 * sizeof(fec_tb_result),
+                             e->d_rblk + off_tbres + (size_t)t0 * sizeof(fec_tb_result), (size_t)(t1 - t0) * sizeof(fec_tb_result),
+                             cudaMemcpyDeviceToHost, ps));
+      if (e->chunk_out.size() <= c) {
+        cudaEvent_t ev = nullptr;
+        CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        e->chunk_out.push_back(ev);
+      }
+      CU_TRY(cudaEventRecord(e->chunk_out[c], ps));
+      e->tb_chunk_end.push_back(t1);
+    }
+  } else {
+    if (dm) {
+      rc = demod_stage(e, st, *dm, l0, l1, e->d_llr);
+      if (rc != FEC_OK) {
+        return rc;
+      }
+    } else {
+      CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+    }
+    rc = launch(e, st, d_descs, n_map, e->d_llr, e->d_msg, d_cbres, max_Z, any1);
     if (rc != FEC_OK) {
       return rc;
     }
-  } else {
-    CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
-  }
-  rc = launch(e, st, d_descs, n_map, e->d_llr, e->d_msg, d_cbres, max_Z, any1);
-  if (rc != FEC_OK) {
-    return rc;
-  }
-  if (aligned) {
-    fec_tb_gather_kernel<<<n_map, 256, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres, d_scr, e->d_tab);
-  } else {
-    fec_tb_assemble_kernel<<<n, 1024, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres);
-  }
-  CU_TRY(cudaGetLastError());
-  e->launches.fetch_add(1);
-  CU_TRY(cudaMemcpyAsync(e->h_rblk, e->d_rblk, off_tbres + (size_t)n * sizeof(fec_tb_result), cudaMemcpyDeviceToHost, st));
-  // The transport block bytes come back unconditionally into a pinned bounce buffer (a block that is not delivered must
-  // leave the caller's buffer untouched, and waiting for the results first would cost a second round trip).
-  for (uint32_t t = 0; t < n; ++t) {
-    CU_TRY(cudaMemcpyAsync(e->h_tbout + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8,
-                           cudaMemcpyDeviceToHost, st));
+    if (aligned) {
+      fec_tb_gather_kernel<<<n_map, 256, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres, d_scr, e->d_tab, 0u);
+    } else {
+      fec_tb_assemble_kernel<<<n, 1024, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres);
+    }
+    CU_TRY(cudaGetLastError());
+    e->launches.fetch_add(1);
+    CU_TRY(cudaMemcpyAsync(e->h_rblk, e->d_rblk, off_tbres + (size_t)n * sizeof(fec_tb_result), cudaMemcpyDeviceToHost, st));
+    // The transport block bytes come back unconditionally into a pinned bounce buffer (a block that is not delivered must
+    // leave the caller's buffer untouched, and waiting for the results first would cost a second round trip).
+    for (uint32_t t = 0; t < n; ++t) {
+      CU_TRY(cudaMemcpyAsync(e->h_tbout + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8,
+                             cudaMemcpyDeviceToHost, st));
+    }
   }
   t_enq = now();
-  CU_TRY(cudaStreamSynchronize(st));
-  t_sync = now();
   // Pass 2: deliver the transport blocks whose codeblocks are all good, update the per-codeblock state.
   const fec_cb_result* h_cbres = reinterpret_cast<const fec_cb_result*>(e->h_rblk);
   const fec_tb_result* h_tbres = reinterpret_cast<const fec_tb_result*>(e->h_rblk + off_tbres);
-  for (uint32_t t = 0; t < n; ++t) {
+  const auto           deliver = [&](uint32_t t) {
     const fec_tb_result& R = h_tbres[t];
     const fec_tb_job&    J = h_jobs[t];
     h_results[t]           = R;
@@ -1370,6 +1431,26 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       for (uint32_t r = 0; r < J.nof_cbs; ++r) {
         e->cb_ok[h_map[J.map_first + r].slot].store(0);
       }
+    }
+  };
+  if (pipelined) {
+    // chunk by chunk, as each one's results land: the host copies of the early chunks overlap the kernels of the late ones
+    uint32_t t = 0;
+    for (size_t c = 0; c < e->tb_chunk_end.size(); ++c) {
+      CU_TRY(cudaEventSynchronize(e->chunk_out[c]));
+      if (c + 1 == e->tb_chunk_end.size()) {
+        t_sync = now();
+      }
+      for (; t < e->tb_chunk_end[c]; ++t) {
+        deliver(t);
+      }
+    }
+    CU_TRY(cudaStreamSynchronize(st));
+  } else {
+    CU_TRY(cudaStreamSynchronize(st));
+    t_sync = now();
+    for (uint32_t t = 0; t < n; ++t) {
+      deliver(t);
     }
   }
   if (trace) {

@@ -295,14 +295,16 @@ __global__ void __launch_bounds__(256) fec_tb_gather_kernel(const fec_tb_job* __
                                                            uint8_t* __restrict__ out_base,
                                                            fec_tb_result* __restrict__ tb_results,
                                                            uint32_t* __restrict__ scratch,
-                                                           const fec_dev_tables* __restrict__ tab)
+                                                           const fec_dev_tables* __restrict__ tab,
+                                                           uint32_t first)
 {
   __shared__ uint32_t red[8];
   __shared__ uint32_t s_stats[3]; // ok count, decoded count, iteration sum
   __shared__ uint32_t s_min, s_max, s_last;
-  const fec_tb_cb_ref me  = map[blockIdx.x];
+  const uint32_t      mi  = blockIdx.x + first; // the launch covers the codeblocks [first, first + gridDim.x) of the map
+  const fec_tb_cb_ref me  = map[mi];
   const fec_tb_job    J   = jobs[me.tb];
-  const uint32_t      r   = blockIdx.x - J.map_first;
+  const uint32_t      r   = mi - J.map_first;
   const uint32_t      tid = threadIdx.x;
   if (tid < 3) {
     s_stats[tid] = 0;
