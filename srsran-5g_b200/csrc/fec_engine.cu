@@ -1617,13 +1617,73 @@ int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const 
     return r;
   }
   CU_TRY(cudaMemcpyAsync(e->d_enc_descs, h_descs, (size_t)n * sizeof(fec_enc_desc), cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaMemcpyAsync(e->d_enc_in, h_in, in_bytes, cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaMemsetAsync(e->d_enc_out + lo, 0, hi - lo, e->stream)); // bytes between two outputs read as zeros
-  r = fec_encode_launch_device(e, e->d_enc_descs, n, e->d_enc_in, e->d_enc_out, max_Z);
-  if (r != FEC_OK) {
-    return r;
+  // Large batches are pipelined in chunks of one kernel wave (8 CTAs per SM): segment copies in order on the copy stream,
+  // kernels and the (three times larger) copies of the rate-matched output on three streams. The chunks' input and output
+  // spans must follow one another; each output span runs up to the next chunk's so that together they tile [lo, hi).
+  struct span_t {
+    size_t i0, i1, o0, o1;
+  };
+  const uint32_t      wave  = 8u * (uint32_t)e->sm_count;
+  uint32_t            chunk = (n >= 2 * wave) ? wave : n;
+  std::vector<span_t> spans;
+  for (uint32_t c0 = 0; c0 < n && chunk != n; c0 += chunk) {
+    span_t         sp = {~(size_t)0, 0, ~(size_t)0, 0};
+    const uint32_t c1 = (n - c0 < chunk) ? n : c0 + chunk;
+    for (uint32_t i = c0; i < c1; ++i) {
+      const fec_enc_desc& d       = h_descs[i];
+      const size_t        in_len  = ((size_t)((d.base_graph == 1) ? 22 : 10) * d.lifting_size - d.nof_filler_bits + 7) / 8;
+      const size_t        out_len = (d.flags & FEC_ENC_FLAG_UNPACKED) ? (size_t)d.E : ((size_t)d.E + 7) / 8;
+      sp.i0 = d.in_offset < sp.i0 ? (size_t)d.in_offset : sp.i0;
+      sp.i1 = d.in_offset + in_len > sp.i1 ? (size_t)d.in_offset + in_len : sp.i1;
+      sp.o0 = d.out_offset < sp.o0 ? (size_t)d.out_offset : sp.o0;
+      sp.o1 = d.out_offset + out_len > sp.o1 ? (size_t)d.out_offset + out_len : sp.o1;
+    }
+    if (!spans.empty() && (sp.i0 < spans.back().i1 || sp.o0 < spans.back().o1)) {
+      chunk = n; // interleaved buffers: one launch
+      break;
+    }
+    if (!spans.empty()) {
+      spans.back().o1 = sp.o0;
+    }
+    spans.push_back(sp);
   }
-  CU_TRY(cudaMemcpyAsync(h_out + lo, e->d_enc_out + lo, hi - lo, cudaMemcpyDeviceToHost, e->stream));
+  if (chunk == n) {
+    CU_TRY(cudaMemcpyAsync(e->d_enc_in, h_in, in_bytes, cudaMemcpyHostToDevice, e->stream));
+    CU_TRY(cudaMemsetAsync(e->d_enc_out + lo, 0, hi - lo, e->stream)); // bytes between two outputs read as zeros
+    r = fec_encode_launch_device(e, e->d_enc_descs, n, e->d_enc_in, e->d_enc_out, max_Z);
+    if (r != FEC_OK) {
+      return r;
+    }
+    CU_TRY(cudaMemcpyAsync(h_out + lo, e->d_enc_out + lo, hi - lo, cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(cudaStreamSynchronize(e->stream));
+    return FEC_OK;
+  }
+  CU_TRY(cudaEventRecord(e->pipe_done[0], e->stream));
+  for (int k = 0; k < 3; ++k) {
+    CU_TRY(cudaStreamWaitEvent(e->pipe[k], e->pipe_done[0], 0));
+  }
+  for (uint32_t c = 0; c < spans.size(); ++c) {
+    const span_t&  sp = spans[c];
+    const uint32_t c0 = c * chunk, cn = (c + 1 == spans.size()) ? n - c0 : chunk;
+    cudaStream_t   ps = e->pipe[c % 3];
+    CU_TRY(cudaMemcpyAsync(e->d_enc_in + sp.i0, h_in + sp.i0, sp.i1 - sp.i0, cudaMemcpyHostToDevice, e->copy_in));
+    if (e->chunk_in.size() <= c) {
+      cudaEvent_t ev = nullptr;
+      CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+      e->chunk_in.push_back(ev);
+    }
+    CU_TRY(cudaEventRecord(e->chunk_in[c], e->copy_in));
+    CU_TRY(cudaStreamWaitEvent(ps, e->chunk_in[c], 0));
+    CU_TRY(cudaMemsetAsync(e->d_enc_out + sp.o0, 0, sp.o1 - sp.o0, ps));
+    fec_encode_kernel<<<cn, FEC_ENC_THREADS, 0, ps>>>(e->d_enc_descs + c0, e->d_enc_in, e->d_enc_out, e->d_tab);
+    CU_TRY(cudaGetLastError());
+    e->launches.fetch_add(1);
+    CU_TRY(cudaMemcpyAsync(h_out + sp.o0, e->d_enc_out + sp.o0, sp.o1 - sp.o0, cudaMemcpyDeviceToHost, ps));
+  }
+  for (int k = 0; k < 3; ++k) {
+    CU_TRY(cudaEventRecord(e->pipe_done[k], e->pipe[k]));
+    CU_TRY(cudaStreamWaitEvent(e->stream, e->pipe_done[k], 0));
+  }
   CU_TRY(cudaStreamSynchronize(e->stream));
   return FEC_OK;
 }
