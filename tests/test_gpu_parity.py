@@ -190,3 +190,51 @@ def test_rate_dematcher_interface(fec, engine, oracle):
             oracle.rate_dematch(bg, Z, a, llr, t == 0, p["rv"], p["qm"], p["Nref"], p["fill"])
             dm.rate_dematch(b, llr, t == 0, cfg)
             assert (a == b).all(), (trial, t, p, E)
+
+
+def test_large_batch_chunked_pipeline_vs_oracle(fec, engine, oracle, orc):
+    """Batches of two kernel waves or more take the chunked three-stream pipeline of fec_run_host. 700 small codeblocks,
+    once without early stop (every output byte is overwritten: the caller's bytes are not sent to the device) and once
+    with early stop at an Es/N0 where some blocks fail, plus three blocks whose input is all zeros (the decoder returns
+    without iterating and their output bytes must stay the caller's), against the oracle."""
+    rng = np.random.default_rng(2024)
+    for early in (False, True):
+        items, want = [], []
+        for i in range(700):
+            bg = int(rng.integers(1, 3))
+            Z = int(rng.choice([8, 12, 16, 20, 28, 36]))
+            p = cases.random_chain_params(rng, bg=bg, Z=Z)
+            K, N = cases.dims(bg, Z)
+            p["E"] = max(p["qm"], min(p["E"], N + 64) // p["qm"] * p["qm"])
+            p["early"], p["max_iter"] = early, 4
+            llr, _ = oracle.make_case(bg, Z, p["E"], p["rv"], p["qm"], p["Nref"], p["fill"], p["poly"], p["snr"] - 1.0, seed=5000 + i)
+            if early and i in (5, 300, 650):
+                llr[:] = 0
+            soft = np.zeros(N, np.int8)
+            it, ref_out = oracle.cb_chain(bg, Z, soft, llr, True, p["rv"], p["qm"], p["Nref"], p["fill"], p["poly"], 4, early)
+            items.append(dict(p=p, llr=llr, new_data=True, slot=i))
+            want.append((it, ref_out, soft))
+        n = len(items)
+        d = fec.make_descs(n)
+        offs = np.cumsum([0] + [((it["llr"].size + 15) // 16) * 16 for it in items])
+        llr = np.zeros(int(offs[-1]) + 16, np.int8)
+        out_off = np.cumsum([0] + [(cases.dims(it["p"]["bg"], it["p"]["Z"])[0] + 7) // 8 for it in items])
+        for i, it in enumerate(items):
+            engine.harq_free(it["slot"])
+            cases.fill_chain_desc(fec, d, i, it["p"], True, it["slot"], int(offs[i]), int(out_off[i]))
+            llr[offs[i]:offs[i] + it["llr"].size] = it["llr"]
+        out = np.full(int(out_off[-1]), 0x5A, np.uint8)
+        res = engine.run_host(d, llr, out)
+        n_fail = 0
+        for i, (it, ref_out, ref_soft) in enumerate(want):
+            K, N = cases.dims(items[i]["p"]["bg"], items[i]["p"]["Z"])
+            assert got_iterations(fec, res, i) == it, (early, i)
+            got = out[out_off[i]:out_off[i + 1]]
+            n_fail += it < 0
+            if early and i in (5, 300, 650):
+                assert it < 0 and (got == 0x5A).all(), (early, i)  # nothing to decode: the caller's bytes are left alone
+                assert res["status"][i] & fec.RES_TOO_SHORT
+            else:
+                assert (got == ref_out).all(), (early, i)
+            assert (engine.harq_read(items[i]["slot"], N) == ref_soft).all(), (early, i)
+        assert not early or n_fail > 10
