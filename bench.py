@@ -36,7 +36,7 @@ import __graft_entry__ as ge  # noqa: E402
 BG, Z, QM, MAX_ITER = 1, 384, 2, 6
 K, N = 22 * Z, 66 * Z
 E = N
-INFO_BITS = K  # no fillers
+INFO_BITS = K - 24  # decoded information bits per codeblock: no fillers, the 24-bit codeblock CRC is not information
 # Algorithmic HBM bytes per codeblock of this workload: E LLRs in + N soft-buffer bytes out + K/8 decoded
 # bytes + 8 result bytes + 48 descriptor bytes.
 ALGO_BYTES_PER_CB = E + N + K // 8 + 8 + 48

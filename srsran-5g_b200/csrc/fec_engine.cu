@@ -12,6 +12,7 @@
 #include "fec_encode.cuh"
 #include "fec_demod.cuh"
 #include "ldpc_tables.h"
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cmath>
@@ -238,7 +239,6 @@ int launch(fec_engine*          e,
     const fec_generic_smem_layout L = fec_generic_layout(max_Z, any_bg1);
     unsigned                      threads = ((max_Z + 31) / 32) * 32;
     threads                               = threads > 384 ? 384 : threads;
-    CU_TRY(cudaFuncSetAttribute(fec_cb_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
     fec_cb_generic_kernel<<<n, threads, L.total, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab);
     CU_TRY(cudaGetLastError());
   }
@@ -255,13 +255,40 @@ inline bool same_shape(const fec_cb_desc& a, const fec_cb_desc& b)
 }
 
 // Freed slots are zeroed lazily: the first host-driven operation on one carries FEC_FLAG_HARQ_ZERO.
-void apply_fresh(fec_engine* e, fec_cb_desc& d)
+void apply_fresh(fec_engine* e, fec_cb_desc& d, std::vector<uint32_t>* taken = nullptr)
 {
   if (d.mode != FEC_MODE_DECODE && d.harq_slot < e->cfg.harq_slots && e->fresh[d.harq_slot].load(std::memory_order_relaxed) &&
       e->fresh[d.harq_slot].exchange(0)) {
     d.flags |= FEC_FLAG_HARQ_ZERO;
+    if (taken) {
+      taken->push_back(d.harq_slot);
+    }
   }
 }
+
+// Error exits of the host-buffer entry points: no copy into or out of the caller's buffers may still be in flight, and the
+// "reads as zeros" marks this call consumed are put back (the operation that would have rewritten the slots did not run).
+struct run_guard {
+  fec_engine*           e;
+  std::vector<uint32_t> taken;
+  bool                  ok = false;
+  explicit run_guard(fec_engine* e_) : e(e_) {}
+  ~run_guard()
+  {
+    if (ok) {
+      return;
+    }
+    cudaStreamSynchronize(e->copy_in);
+    for (int k = 0; k < 3; ++k) {
+      cudaStreamSynchronize(e->pipe[k]);
+    }
+    cudaStreamSynchronize(e->stream);
+    cudaGetLastError();
+    for (uint32_t s : taken) {
+      e->fresh[s].store(1);
+    }
+  }
+};
 
 int slot_alloc(fec_engine* e, batch_slot& s)
 {
@@ -416,6 +443,13 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   for (int i = 0; i < 3; ++i) {
     CU_TRY(cudaStreamCreateWithFlags(&e->pipe[i], cudaStreamNonBlocking));
     CU_TRY(cudaEventCreateWithFlags(&e->pipe_done[i], cudaEventDisableTiming));
+  }
+  {
+    // Largest dynamic shared-memory layouts (BG1, Z = 384), set once and never lowered: the attribute is global per function
+    // and queues / host entry points launch concurrently from several threads.
+    const uint32_t g = fec_generic_layout(384, 1).total, p = fec_packed_layout(384, 1).total;
+    CU_TRY(cudaFuncSetAttribute(fec_cb_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(g > p ? g : p)));
+    CU_TRY(cudaFuncSetAttribute(fec_cb_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g));
   }
   fec_dev_tables* h = new (std::nothrow) fec_dev_tables();
   build_tables(*h, cfg->scaling_factor);
@@ -588,9 +622,6 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     max_Z = d.lifting_size > max_Z ? d.lifting_size : max_Z;
     any1 |= (d.base_graph == 1);
   }
-  for (uint32_t i = 0; i < n; ++i) {
-    apply_fresh(e, h_descs[i]);
-  }
   std::lock_guard<std::mutex> lk(e->run_mtx);
   const auto                  t_prep = std::chrono::steady_clock::now();
   CU_TRY(cudaSetDevice(e->cfg.device));
@@ -631,6 +662,12 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     }
   }
   memcpy(e->h_descs_pin, h_descs, n * sizeof(fec_cb_desc));
+  // FEC_FLAG_HARQ_ZERO goes into the engine's copy only: the caller's array gets k0 / graph_index written back and nothing
+  // else, so it can be reused for a retransmission (rv, flags edited) without carrying a stale "slot reads as zeros".
+  run_guard guard(e);
+  for (uint32_t i = 0; i < n; ++i) {
+    apply_fresh(e, e->h_descs_pin[i], &guard.taken);
+  }
   CU_TRY(cudaMemcpyAsync(e->d_descs, e->h_descs_pin, n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, e->stream));
   CU_TRY(cudaEventRecord(e->pipe_done[0], e->stream));
   for (int k = 0; k < 3; ++k) {
@@ -723,6 +760,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   CU_TRY(cudaStreamSynchronize(e->stream));
   const auto t_sync = std::chrono::steady_clock::now();
   memcpy(h_results, e->h_res_pin, n * sizeof(fec_cb_result));
+  guard.ok = true;
   if (trace) {
     const auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
       return std::chrono::duration<double, std::micro>(b - a).count();
@@ -1307,9 +1345,6 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       if (slot >= e->cfg.harq_slots) {
         return fail(FEC_ERR_BAD_ARG, "transport block %u codeblock %u: harq slot %u >= %u", t, r, slot, e->cfg.harq_slots);
       }
-      if (tb.flags & FEC_FLAG_NEW_DATA) {
-        e->cb_ok[slot].store(0); // pusch_decoder_impl.cpp:124-128
-      }
       fec_tb_cb_ref& ref = h_map[m];
       ref.slot           = slot;
       ref.tb             = t;
@@ -1319,7 +1354,8 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       // A codeblock whose CRC passed in an earlier transmission is not decoded again, but the new LLRs are still
       // combined into its soft buffer: the transport-block CRC may yet fail and put it back in play
       // (pusch_decoder_impl.cpp:333-344).
-      const bool already_ok = e->cb_ok[slot].load() != 0;
+      // (new data resets the flags, pusch_decoder_impl.cpp:124-128; the reset itself is committed after validation)
+      const bool already_ok = !(tb.flags & FEC_FLAG_NEW_DATA) && e->cb_ok[slot].load() != 0;
       if (already_ok) {
         d.mode = FEC_MODE_DEMATCH;
       }
@@ -1327,7 +1363,6 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       if (rc != FEC_OK) {
         return rc;
       }
-      apply_fresh(e, d);
       ref.result_index = already_ok ? -1 : (int32_t)m;
       l0               = d.llr_offset < l0 ? (size_t)d.llr_offset : l0;
       l1               = d.llr_offset + d.E > l1 ? (size_t)(d.llr_offset + d.E) : l1;
@@ -1341,7 +1376,18 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   if (l1 - l0 > e->cfg.max_batch_llrs) {
     return fail(FEC_ERR_BAD_ARG, "%zu LLR bytes exceed the engine staging capacity", l1 - l0);
   }
+  // Every check has passed: only now does the call change engine state (codeblock CRC flags of new transmissions, the
+  // "reads as zeros" marks of freed slots). A CUDA failure further down puts the marks back (run_guard).
+  run_guard rg(e);
+  for (uint32_t t = 0; t < n; ++t) {
+    if (tbs[t].flags & FEC_FLAG_NEW_DATA) {
+      for (uint32_t r = 0; r < h_jobs[t].nof_cbs; ++r) {
+        e->cb_ok[h_map[h_jobs[t].map_first + r].slot].store(0);
+      }
+    }
+  }
   for (uint32_t i = 0; i < n_map; ++i) {
+    apply_fresh(e, h_descs[i], &rg.taken);
     h_descs[i].llr_offset -= l0; // the staged LLRs start at l0
   }
   t_seg = now();
@@ -1486,6 +1532,7 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       deliver(t);
     }
   }
+  rg.ok = true;
   if (trace) {
     const auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
       return std::chrono::duration<double, std::micro>(b - a).count();
@@ -1743,6 +1790,28 @@ int demod_launch(fec_engine* e, cudaStream_t st, const fec_demod_desc* d_descs, 
   return FEC_OK;
 }
 
+// True when the non-empty demodulation calls tile [l0, l1) exactly: each starts where the previous one (by LLR offset) ended.
+// (A sum-of-lengths test alone would accept two overlapping calls plus a gap of the same size.)
+bool demod_calls_tile(const fec_demod_desc* d, uint32_t n, size_t l0, size_t l1)
+{
+  std::vector<std::pair<size_t, size_t>> span;
+  span.reserve(n);
+  for (uint32_t i = 0; i < n; ++i) {
+    if (d[i].nof_symbols != 0) {
+      span.emplace_back((size_t)d[i].llr_offset, (size_t)d[i].nof_symbols * d[i].qm);
+    }
+  }
+  std::sort(span.begin(), span.end());
+  size_t at = l0;
+  for (const auto& sp : span) {
+    if (sp.first != at) {
+      return false;
+    }
+    at += sp.second;
+  }
+  return at == l1;
+}
+
 // Copies the symbols the descriptors use to the device and demodulates them into d_llr, whose first byte is LLR index l0.
 int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l0, size_t l1, int8_t* d_llr)
 {
@@ -1788,8 +1857,9 @@ int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l
     max_symbols = d.nof_symbols > max_symbols ? d.nof_symbols : max_symbols;
     covered += bytes;
   }
-  if (covered != l1 - l0) {
-    return fail(FEC_ERR_BAD_ARG, "the demodulation calls produce %zu LLRs, the transport blocks read %zu", covered, l1 - l0);
+  if (covered != l1 - l0 || !demod_calls_tile(e->h_dm_descs, dm.n, l0, l1)) {
+    return fail(FEC_ERR_BAD_ARG, "the demodulation calls (%zu LLRs) do not tile the %zu LLRs the transport blocks read", covered,
+                l1 - l0);
   }
   for (uint32_t i = 0; i < dm.n; ++i) {
     e->h_dm_descs[i].sym_offset -= s0;
@@ -1865,7 +1935,7 @@ int fec_demod_run_host(fec_engine* e, const fec_demod_desc* h_descs, uint32_t n,
   if (covered == 0) {
     return FEC_OK;
   }
-  if (covered != l1 - l0) {
+  if (covered != l1 - l0 || !demod_calls_tile(h_descs, n, l0, l1)) {
     return fail(FEC_ERR_BAD_ARG, "the demodulation calls must tile one contiguous span of the LLR buffer");
   }
   std::lock_guard<std::mutex> lk(e->run_mtx);
@@ -1895,5 +1965,6 @@ int fec_tb_run_host_symbols(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, c
   const demod_source dm = {h_demod, n_demod, h_symbols, h_noise_vars, nof_symbols, flavour};
   return tb_run(e, tbs, n, slots, nullptr, ~(size_t)0 >> 1, &dm, h_out, out_bytes, h_results, h_cb_results);
 }
+
 
 } // extern "C"

@@ -162,10 +162,11 @@ __device__ __forceinline__ uint32_t fec_reg_const(uint32_t x)
 }
 
 // Shared-memory byte accesses by 32-bit shared-window address (lets the two lanes of a halfword be addressed A and A^1).
+// "memory" clobber: ordinary C++ stores to shared memory surround these accesses and must not be moved across them.
 __device__ __forceinline__ uint32_t lds_u8(uint32_t a)
 {
   uint32_t r;
-  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r) : "r"(a));
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r) : "r"(a) : "memory");
   return r;
 }
 __device__ __forceinline__ void sts_u8(uint32_t a, uint32_t v)
@@ -1062,9 +1063,8 @@ static inline int fec_packed_launch(cudaStream_t             st,
   const uint32_t a = fec_generic_layout(max_Z, any_bg1).total;
   const uint32_t b = (max_Z % 2 == 0 && max_Z >= 4) ? fec_packed_layout(max_Z, any_bg1).total : 0;
   const uint32_t smem = a > b ? a : b;
-  if (cudaFuncSetAttribute(fec_cb_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
-    return FEC_ERR_CUDA;
-  }
+  // cudaFuncAttributeMaxDynamicSharedMemorySize is set ONCE, to the largest layout, in fec_engine_create: the attribute is
+  // per-function global state and launches from several queues / threads would otherwise race on it.
   fec_cb_packed_kernel<<<n, threads, smem, st>>>(descs, llr, out, res, harq, tab, ptab);
   return cudaGetLastError() == cudaSuccess ? FEC_OK : FEC_ERR_CUDA;
 }
