@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 5
+#define FEC_B200_ABI_VERSION 6
 
 typedef enum {
   FEC_OK             = 0,
@@ -240,6 +240,25 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
 
 /* Forgets the codeblock CRC flags of a slot range (rx buffer released / expired). */
 int fec_tb_reset_slots(fec_engine* e, uint32_t first_slot, uint32_t n);
+
+/* Allocation-free transport-block assembly + TB CRC over DEVICE buffers. This entry point has no counterpart in the
+ * reference; it was added for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it). It runs the same one-CTA-per-codeblock gather kernel as
+ * fec_tb_run_host, with the kernel's scratch (jobs, codeblock map, per-block CRC accumulators and arrival counters) in a
+ * file-scope static __device__ array of FEC_NOALLOC_MAX_TBS blocks / FEC_NOALLOC_MAX_CBS codeblocks (about 36 KB, held by every
+ * GPU that loads the library until exit). It calls no cudaMalloc / cudaFree / allocating routine; larger calls are rejected
+ * with FEC_ERR_BAD_ARG. Inputs: tbs = n HOST descriptors (tbs, nof_llrs, base_graph, qm, nof_layers, max_iter, out_offset are
+ * read; payloads must be whole bytes, as every TS 38.214 transport block size gives); d_cb_msgs = the decoded codeblock
+ * messages, FEC_MAX_CB_OUT_BYTES apart, the codeblocks of block 0 first, in order; d_cb_results = their fec_cb_result, same
+ * order. Outputs: tbs/8 bytes per delivered block at d_out + out_offset (untouched otherwise), d_tb_results[n].
+ * Asynchronous on fec_engine_stream(). Every call shares the one array (it keeps the last call's contents; the call clears
+ * what must start at zero): calls are serialised on the host, but two calls whose GPU work overlaps -- two engines on the
+ * same device, whose streams differ -- race on it. */
+#define FEC_NOALLOC_MAX_TBS 64u
+#define FEC_NOALLOC_MAX_CBS 2048u
+int fec_tb_assemble_device_noalloc(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint8_t* d_cb_msgs,
+                                   const fec_cb_result* d_cb_results, uint8_t* d_out, size_t out_bytes,
+                                   fec_tb_result* d_tb_results);
 
 /* ---- HARQ buffer pool: the reference's rx_buffer_pool over the engine's HARQ slots ---------------- */
 /* Mirror of rx_buffer_pool / unique_rx_buffer (include/srsran/phy/upper/rx_buffer_pool.h:60-127, unique_rx_buffer.h:36-170;

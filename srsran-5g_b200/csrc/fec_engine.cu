@@ -1967,4 +1967,111 @@ int fec_tb_run_host_symbols(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, c
 }
 
 
+// ---- allocation-free transport-block assembly (no counterpart in the reference) ----
+// fec_tb_gather_kernel with its scratch (jobs | codeblock map | per-block {CRC accumulator, arrival counter}) in a file-scope
+// device array instead of cudaMalloc'ed engine memory. Every GPU that loads this library holds the array until exit.
+namespace {
+constexpr size_t NOALLOC_OFF_MAP   = ((size_t)FEC_NOALLOC_MAX_TBS * sizeof(fec_tb_job) + 255) & ~(size_t)255;
+constexpr size_t NOALLOC_OFF_ACC   = (NOALLOC_OFF_MAP + (size_t)FEC_NOALLOC_MAX_CBS * sizeof(fec_tb_cb_ref) + 255) & ~(size_t)255;
+constexpr size_t NOALLOC_BYTES     = (NOALLOC_OFF_ACC + (size_t)FEC_NOALLOC_MAX_TBS * 2 * sizeof(uint32_t) + 255) & ~(size_t)255;
+}
+static __device__ __align__(256) unsigned char fec_noalloc_scratch[NOALLOC_BYTES];
+namespace {
+// In host code `fec_noalloc_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, once per device,
+// with that device current.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex     noalloc_mtx;                                  // guards the two arrays below and serialises the calls
+unsigned char* noalloc_dev_ptr[NOALLOC_MAX_DEVICES] = {};
+unsigned char  noalloc_host_stage[NOALLOC_BYTES];            // host image of the scratch, rebuilt by every call
+}
+
+int fec_tb_assemble_device_noalloc(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint8_t* d_cb_msgs,
+                                   const fec_cb_result* d_cb_results, uint8_t* d_out, size_t out_bytes,
+                                   fec_tb_result* d_tb_results)
+{
+  if (!e || !tbs || !d_cb_msgs || !d_cb_results || !d_out || !d_tb_results) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (n == 0) {
+    return FEC_OK;
+  }
+  if (n > FEC_NOALLOC_MAX_TBS) {
+    return fail(FEC_ERR_BAD_ARG, "fec_tb_assemble_device_noalloc: %u transport blocks, the static scratch takes %u", n,
+                FEC_NOALLOC_MAX_TBS);
+  }
+  if (e->cfg.device < 0 || e->cfg.device >= NOALLOC_MAX_DEVICES) {
+    return fail(FEC_ERR_BAD_ARG, "fec_tb_assemble_device_noalloc: device ordinal %d", e->cfg.device);
+  }
+  std::lock_guard<std::mutex> lk(noalloc_mtx);
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  if (noalloc_dev_ptr[e->cfg.device] == nullptr) {
+    void* p = nullptr;
+    CU_TRY(cudaGetSymbolAddress(&p, fec_noalloc_scratch));
+    noalloc_dev_ptr[e->cfg.device] = static_cast<unsigned char*>(p);
+  }
+  unsigned char* d_scr = noalloc_dev_ptr[e->cfg.device];
+  fec_tb_job*    jobs  = reinterpret_cast<fec_tb_job*>(noalloc_host_stage);
+  fec_tb_cb_ref* map   = reinterpret_cast<fec_tb_cb_ref*>(noalloc_host_stage + NOALLOC_OFF_MAP);
+  uint32_t       m     = 0;
+  for (uint32_t t = 0; t < n; ++t) {
+    fec_tb_geometry g;
+    if (!fec_tb_geometry_of(tbs[t], g)) {
+      return fail(FEC_ERR_BAD_ARG, "transport block %u: tbs=%u bg=%u rv=%u qm=%u layers=%u llrs=%u", t, tbs[t].tbs, tbs[t].base_graph,
+                  tbs[t].rv, tbs[t].qm, tbs[t].nof_layers, tbs[t].nof_llrs);
+    }
+    if (g.data_bits % 8 != 0) {
+      return fail(FEC_ERR_BAD_ARG, "transport block %u: payloads of %u bits are not whole bytes (use fec_tb_run_host)", t, g.data_bits);
+    }
+    if (m + g.nof_cbs > FEC_NOALLOC_MAX_CBS) {
+      return fail(FEC_ERR_BAD_ARG, "fec_tb_assemble_device_noalloc: more than %u codeblocks in one call", FEC_NOALLOC_MAX_CBS);
+    }
+    if (tbs[t].out_offset + tbs[t].tbs / 8 > out_bytes) {
+      return fail(FEC_ERR_BAD_ARG, "transport block %u does not fit the output buffer", t);
+    }
+    fec_tb_job& J = jobs[t];
+    memset(&J, 0, sizeof(J));
+    J.out_offset  = tbs[t].out_offset;
+    J.nof_cbs     = g.nof_cbs;
+    J.data_bits   = g.data_bits;
+    J.stream_bits = g.stream_bits;
+    J.tbs_bytes   = tbs[t].tbs / 8;
+    J.map_first   = m;
+    J.max_iter    = tbs[t].max_iter;
+    // weight of codeblock r = x^(8 * stream bytes after its payload) mod g24A, built backwards (as tb_run does)
+    const uint32_t dbytes = g.data_bits / 8;
+    uint32_t       w      = 1;
+    const uint32_t step   = fec_tb_crc24a_xpow8_host(dbytes);
+    if (g.nof_cbs > 1) {
+      w = fec_tb_crc24a_xpow8_host(g.stream_bits / 8 - (g.nof_cbs - 1) * dbytes);
+    }
+    for (int r = (int)g.nof_cbs - 1; r >= 0; --r) {
+      fec_tb_cb_ref& ref = map[m + r];
+      ref.slot           = m + r; // codeblock messages are densely packed in call order
+      ref.result_index   = (int32_t)(m + r);
+      ref.tb             = t;
+      if (r == (int)g.nof_cbs - 1) {
+        ref.weight = 1u;
+      } else {
+        ref.weight = w;
+        w          = fec_tb_crc24a_mulmod_host(w, step);
+      }
+    }
+    m += g.nof_cbs;
+  }
+  // The array keeps the previous call's contents: the accumulators and arrival counters must start at zero.
+  memset(noalloc_host_stage + NOALLOC_OFF_ACC, 0, (size_t)n * 2 * sizeof(uint32_t));
+  const cudaStream_t st = e->stream;
+  CU_TRY(cudaMemcpyAsync(d_scr, noalloc_host_stage, (size_t)n * sizeof(fec_tb_job), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_scr + NOALLOC_OFF_MAP, noalloc_host_stage + NOALLOC_OFF_MAP, (size_t)m * sizeof(fec_tb_cb_ref),
+                         cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_scr + NOALLOC_OFF_ACC, noalloc_host_stage + NOALLOC_OFF_ACC, (size_t)n * 2 * sizeof(uint32_t),
+                         cudaMemcpyHostToDevice, st));
+  fec_tb_gather_kernel<<<m, 256, 0, st>>>(reinterpret_cast<const fec_tb_job*>(d_scr),
+                                          reinterpret_cast<const fec_tb_cb_ref*>(d_scr + NOALLOC_OFF_MAP), d_cb_results, d_cb_msgs,
+                                          d_out, d_tb_results, reinterpret_cast<uint32_t*>(d_scr + NOALLOC_OFF_ACC), e->d_tab, 0u);
+  CU_TRY(cudaGetLastError());
+  e->launches.fetch_add(1);
+  return FEC_OK;
+}
+
 } // extern "C"

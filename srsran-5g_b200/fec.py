@@ -26,6 +26,8 @@ MAX_TB_CBS = 162
 TB_SLOTS_CONTIGUOUS = 0xFFFFFFFF
 HARQ_SLOT_BYTES = 25344
 MAX_CB_OUT_BYTES = 1056
+ABI_VERSION = 6
+NOALLOC_MAX_TBS, NOALLOC_MAX_CBS = 64, 2048
 
 ALL_Z = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48, 52, 56, 60,
          64, 72, 80, 88, 96, 104, 112, 120, 128, 144, 160, 176, 192, 208, 224, 240, 256, 288, 320, 352, 384]
@@ -100,7 +102,8 @@ EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_e
            "fec_enc_desc_prepare", "fec_encode_launch_device", "fec_encode_run_host", "fec_demod_desc_prepare",
            "fec_demod_launch_device", "fec_demod_run_host", "fec_tb_run_host_symbols", "fec_harq_pool_create",
            "fec_harq_pool_destroy", "fec_harq_pool_reserve", "fec_harq_pool_codeblocks", "fec_harq_pool_unlock",
-           "fec_harq_pool_release", "fec_harq_pool_run_slot", "fec_harq_pool_stop", "fec_harq_pool_nof_free_codeblocks"]
+           "fec_harq_pool_release", "fec_harq_pool_run_slot", "fec_harq_pool_stop", "fec_harq_pool_nof_free_codeblocks",
+           "fec_tb_assemble_device_noalloc"]
 
 _lib = None
 
@@ -151,6 +154,8 @@ def load_library():
     lib.fec_tb_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
                                     C.c_size_t, C.c_void_p, C.c_void_p]
     lib.fec_tb_reset_slots.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+    lib.fec_tb_assemble_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                   C.c_size_t, C.c_void_p]
     lib.fec_enc_desc_prepare.argtypes = [C.c_void_p]
     lib.fec_encode_launch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
     lib.fec_encode_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p,
@@ -356,6 +361,13 @@ class FecEngine:
                                                   ptr(llr), size(llr), ptr(out), size(out), res.ctypes.data,
                                                   None if cbr is None else cbr.ctypes.data))
         return (res, cbr.reshape(n, MAX_TB_CBS)) if cb_results else res
+
+    def tb_assemble_device_noalloc(self, tbs, d_cb_msgs_ptr, d_cb_results_ptr, d_out_ptr, out_bytes, d_tb_results_ptr):
+        """fec_tb_assemble_device_noalloc: allocation-free TB assembly + TB CRC over device buffers (pointers as ints),
+        asynchronous on self.stream."""
+        assert tbs.dtype == TB_DESC_DTYPE and tbs.flags.c_contiguous
+        _check(self.lib, self.lib.fec_tb_assemble_device_noalloc(self.h, tbs.ctypes.data, tbs.size, d_cb_msgs_ptr,
+                                                                 d_cb_results_ptr, d_out_ptr, out_bytes, d_tb_results_ptr))
 
     def demod_launch_device(self, d_descs_ptr, n, max_symbols, d_sym_ptr, d_noise_ptr, d_llr_ptr, flavour=DEMOD_AVX512):
         """Asynchronous soft-demodulation launch on self.stream; all pointers are device addresses (ints)."""

@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol(fec):
     for name in sorted(declared):
         assert hasattr(lib, name), name
     assert set(fec.EXPORTS) <= declared
-    assert lib.fec_abi_version() == 5
+    assert lib.fec_abi_version() == fec.ABI_VERSION
 
 
 def test_struct_layouts_match_header(fec):
