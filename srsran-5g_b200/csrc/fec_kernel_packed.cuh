@@ -49,10 +49,26 @@ __host__ __device__ inline uint32_t fec_packed_row_words(uint32_t d)
   return d <= 8 ? 2u : 3u;
 }
 
+// Where the check state lives. The LAST FEC_PACKED_TMEM_ROWS base rows of a graph (all of degree <= 8: two words per thread)
+// keep their state in TENSOR MEMORY: thread t of warp w owns TMEM lane 32 (w % 4) + (t % 32), columns
+// 64 (w / 4) + 2 (row - first_tmem_row) + {0, 1} of the CTA's allocation (tcgen05.alloc / ld / st as a private per-thread
+// scratchpad; no MMA is ever issued). Every thread reads back only what it wrote itself. The first rows (the dense core of
+// the graph) stay in shared memory. This takes 49 KB of check state out of shared memory at BG1 / Z = 384, which is what lets
+// three codeblocks instead of two be resident per SM.
+#define FEC_PACKED_TMEM_ROWS 32u
+#define FEC_PACKED_TMEM_COLS_PER_WARPSLOT (2u * FEC_PACKED_TMEM_ROWS)
+
+__host__ __device__ inline uint32_t fec_packed_first_tmem_row(int bg1)
+{
+  return (bg1 ? 46u : 42u) - FEC_PACKED_TMEM_ROWS;
+}
+
+// State words per thread kept in SHARED memory (rows before the first TMEM row).
 __host__ __device__ inline uint32_t fec_packed_state_words(int bg1)
 {
-  // BG1: 7 rows of degree > 8 (3 words), 39 rows of degree <= 8 (2 words). BG2: 2 rows of degree 10, 40 rows <= 8.
-  return bg1 ? (7u * 3u + 39u * 2u) : (2u * 3u + 40u * 2u);
+  // BG1 rows 0..13: degrees 19,19,19,19,3,8,9,7,10,9,7,8,7,6 -> 7 rows of 3 words, 7 rows of 2.
+  // BG2 rows 0..9: degrees 8,10,8,10,4,6,6,6,4,5 -> 2 rows of 3 words, 8 rows of 2.
+  return bg1 ? (7u * 3u + 7u * 2u) : (2u * 3u + 8u * 2u);
 }
 
 __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, int bg1)
@@ -139,6 +155,38 @@ __device__ __forceinline__ uint32_t prmt_f4e(uint32_t a, uint32_t b, uint32_t c)
   return r;
 }
 
+// ---- tensor memory as per-thread scratch (32x32b shape: thread i of the warp <-> lane base + i, consecutive columns) ------
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols)
+{
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols)
+{
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// Load + wait in ONE asm statement: the registers must not be read before tcgen05.wait::ld.
+__device__ __forceinline__ void tmem_ld2(uint32_t taddr, uint32_t& a, uint32_t& b)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];\n\ttcgen05.wait::ld.sync.aligned;"
+               : "=r"(a), "=r"(b)
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st2(uint32_t taddr, uint32_t a, uint32_t b)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void tmem_st8_zero(uint32_t taddr)
+{
+  const uint32_t z = 0;
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(z) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st()
+{
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
 // Constants of the number format.
 #define H2_SIGN 0x80008000u
 #define H2_ABS 0x7fff7fffu
@@ -198,9 +246,10 @@ __device__ __forceinline__ uint32_t imul_hi(uint32_t a, uint32_t b)
 // D = row degree (compile time so that the per-edge values stay in registers). Lane 0 = check t, lane 1 = check t+H.
 // Instruction budget per edge and thread: ALU pipe 14 (ISETP, SEL, IADD3, LOP3 for the addresses; 2 HSET2,
 // 5 HMNMX2, 3 LOP3), FMA pipe 15 (HFMA2 / HADD2 / IMAD), LSU 5.
-template <int D>
+template <int D, bool TM>
 __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, // shared-window address of the soft array
-                                               uint32_t*              st,     // state words of this row for thread t
+                                               uint32_t*              st,     // state words of this row for thread t (!TM)
+                                               uint32_t               taddr,  // tensor-memory address of the row's 2 words (TM)
                                                const fec_packed_edge* ed,     // D edge records (shared memory)
                                                uint32_t               H,
                                                uint32_t               t,
@@ -208,6 +257,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
                                                uint32_t               scale_add)
 {
   constexpr int  NW = (D <= 8) ? 2 : 3;
+  static_assert(!TM || NW == 2, "rows kept in tensor memory have two state words");
   const uint32_t tb = soft_s + t * 2;
 
   // ---- pre-phase: everything that does not depend on the soft bits (addresses, the previous c2v messages of this row).
@@ -215,10 +265,16 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   // early do useful work instead of waiting, and the table / state load latency overlaps the other warps' tail.
   uint32_t a0[D], cneg[D];
   {
-    const uint32_t w0 = st[0], w1 = st[H];
-    uint32_t       w2 = 0;
-    if (NW == 3) {
-      w2 = st[2 * H];
+    uint32_t w0, w1, w2 = 0;
+    if (TM) {
+      tmem_wait_st(); // this thread's store of the previous tensor-memory row
+      tmem_ld2(taddr, w0, w1);
+    } else {
+      w0 = st[0];
+      w1 = st[H];
+      if (NW == 3) {
+        w2 = st[2 * H];
+      }
     }
 #pragma unroll
     for (int e = 0; e < D; ++e) {
@@ -293,7 +349,11 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
 
   // ---- new state: c2v sign = sign product ^ sign(v2c) ----------------------------------------------------------------------
   const uint32_t pm = prmt(m1, 0u, 0xbb99); // 0xffff in the lanes whose sign product is negative
-  st[0]             = __byte_perm(s1, s2, 0x6420);
+  if (TM) {
+    tmem_st2(taddr, __byte_perm(s1, s2, 0x6420), ((sg1 ^ pm) & 0x00ff00ffu) | (nid << 8));
+    return;
+  }
+  st[0] = __byte_perm(s1, s2, 0x6420);
   if (D <= 8) {
     st[H] = ((sg1 ^ pm) & 0x00ff00ffu) | (nid << 8);
   } else if (D <= 16) {
@@ -316,28 +376,42 @@ __device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
                                                   uint32_t               H,
                                                   uint32_t               nlayers,
                                                   uint32_t               smul,
-                                                  uint32_t               sadd)
+                                                  uint32_t               sadd,
+                                                  uint32_t               row_tm, // first base row whose state is in tensor memory
+                                                  uint32_t               tm_row0) // this warp's tensor-memory address of that row
 {
   const uint32_t tid = threadIdx.x;
   for (uint32_t l = 0; l < nlayers; ++l) {
     if ((tid & ~31u) >= H) {
       asm volatile("bar.sync 0;" ::: "memory"); // warps without work still take part in the row barrier
     } else {
-      // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores) so that
-      // whole warps reach the barrier inside the row function.
+      // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores; their own, identical
+      // copy of the tensor-memory state) so that whole warps reach the barrier inside the row function.
       const uint32_t         tq = min(tid, H - 1);
-      uint32_t*              st = state + (uint32_t)soff[l] * H + tq;
       const fec_packed_edge* ed = edges + rs[l];
-      switch (deg[l]) {
-        case 3: fec_packed_row<3>(soft_s, st, ed, H, tq, smul, sadd); break;
-        case 4: fec_packed_row<4>(soft_s, st, ed, H, tq, smul, sadd); break;
-        case 5: fec_packed_row<5>(soft_s, st, ed, H, tq, smul, sadd); break;
-        case 6: fec_packed_row<6>(soft_s, st, ed, H, tq, smul, sadd); break;
-        case 7: fec_packed_row<7>(soft_s, st, ed, H, tq, smul, sadd); break;
-        case 8: fec_packed_row<8>(soft_s, st, ed, H, tq, smul, sadd); break;
-        case 9: fec_packed_row<9>(soft_s, st, ed, H, tq, smul, sadd); break;
-        case 10: fec_packed_row<10>(soft_s, st, ed, H, tq, smul, sadd); break;
-        default: fec_packed_row<19>(soft_s, st, ed, H, tq, smul, sadd); break;
+      if (l >= row_tm) {
+        const uint32_t ta = tm_row0 + 2u * (l - row_tm);
+        switch (deg[l]) {
+          case 3: fec_packed_row<3, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          case 4: fec_packed_row<4, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          case 5: fec_packed_row<5, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          case 6: fec_packed_row<6, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          case 7: fec_packed_row<7, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          default: fec_packed_row<8, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+        }
+      } else {
+        uint32_t* st = state + (uint32_t)soff[l] * H + tq;
+        switch (deg[l]) {
+          case 3: fec_packed_row<3, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          case 4: fec_packed_row<4, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          case 5: fec_packed_row<5, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          case 6: fec_packed_row<6, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          case 7: fec_packed_row<7, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          case 8: fec_packed_row<8, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          case 9: fec_packed_row<9, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          case 10: fec_packed_row<10, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+          default: fec_packed_row<19, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
+        }
       }
     }
   }
@@ -356,9 +430,14 @@ struct fec_soft_store_packed {
   uint32_t Z, H, invZ;
   __device__ __forceinline__ void operator()(uint32_t o, int acc) const
   {
+    raw(o, fec_clampi(acc, -64, 64));
+  }
+  // Without the clamp: the partial last node of a decoder input that is not a multiple of Z (ldpc_decoder_impl.cpp:186-193).
+  __device__ __forceinline__ void raw(uint32_t o, int acc) const
+  {
     const uint32_t op  = o + 2 * Z;
     const uint32_t col = __umulhi(op, invZ);
-    soft[fec_packed_soft_addr(col, op - col * Z, Z, H)] = (uint8_t)(fec_clampi(acc, -64, 64) + 128);
+    soft[fec_packed_soft_addr(col, op - col * Z, Z, H)] = (uint8_t)(acc + 128);
   }
 };
 
@@ -783,10 +862,9 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
 
 __device__ __forceinline__ bool fec_packed_cb_supported(const fec_cb_desc& D)
 {
-  // Z must split into 2 interleaved lanes; the unclamped-tail corner (input not a multiple of Z, never produced by
-  // PUSCH) stays on the generic path.
-  return (D.lifting_size % 2 == 0) && (D.lifting_size >= 4) && (D.lifting_size / 2 <= blockDim.x) &&
-         !(D.mode == FEC_MODE_DECODE && (D.E % D.lifting_size) != 0) && D.mode != FEC_MODE_DEMATCH;
+  // Z must split into 2 interleaved lanes: every even lifting size, all three modes. Odd Z (<= 15) and Z = 2 take the
+  // generic per-check code, whose shared-memory layout is tiny at those sizes.
+  return (D.lifting_size % 2 == 0) && (D.lifting_size >= 4) && (D.lifting_size / 2 <= blockDim.x);
 }
 
 __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
@@ -797,7 +875,8 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
                                            fec_cb_result* __restrict__ results,
                                            int8_t* __restrict__ harq_base,
                                            const fec_dev_tables* __restrict__ tab,
-                                           const fec_packed_tables* __restrict__ ptab)
+                                           const fec_packed_tables* __restrict__ ptab,
+                                           uint32_t tmem_base)
 {
   __shared__ uint32_t s_nsig_arr[2];
 #define s_nsig s_nsig_arr[0]
@@ -865,7 +944,8 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   // ---- stage 1: soft bits into shared memory -----------------------------------------------------------------------------
   const fec_soft_store_packed store{soft, Z, H, invZ};
   if (D.mode == FEC_MODE_DECODE) {
-    const uint32_t n_in   = D.E; // a multiple of Z on this path
+    const uint32_t n_in   = D.E;
+    const uint32_t n_node = (n_in / Z) * Z; // full nodes are clamped to +-64, a partial last node is copied as it is
     uint32_t       my_sig = 0;
     for (uint32_t o = tid; o < N; o += blockDim.x) {
       int vv = 0;
@@ -875,14 +955,26 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
           my_sig = o + 1;
         }
       }
-      store(o, vv);
+      if (o < n_node || o >= n_in) {
+        store(o, vv);
+      } else {
+        store.raw(o, vv);
+      }
     }
     if (my_sig != 0) {
       atomicMax(&s_nsig, my_sig);
     }
   } else {
     int8_t* harq = harq_base + (size_t)D.harq_slot * FEC_HARQ_SLOT_BYTES;
-    fec_dematch_packed(D, in, harq, soft, H, reinterpret_cast<int8_t*>(state), L.edges - L.state, &s_nsig);
+    fec_dematch_packed(D, in, harq, (D.mode == FEC_MODE_CHAIN) ? soft : nullptr, H, reinterpret_cast<int8_t*>(state),
+                       L.edges - L.state, &s_nsig);
+    if (D.mode == FEC_MODE_DEMATCH) {
+      if (tid == 0) {
+        res.status  = FEC_RES_DONE;
+        results[cb] = res;
+      }
+      return;
+    }
   }
   __syncthreads();
 
@@ -908,12 +1000,22 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   cbl          = ((cbl + Z - 1) / Z) * Z;
   const uint32_t nlayers = cbl / Z - Kb;
   const uint32_t T       = K - D.nof_filler_bits;
+  // Tensor-memory home of this warp's check state: lane quadrant of the warp, 64 columns per group of four warps.
+  const uint32_t row_tm  = fec_packed_first_tmem_row(bg1);
+  const uint32_t tm_row0 = tmem_base + ((((tid >> 5) & 3u) * 32u) << 16) + (tid >> 7) * FEC_PACKED_TMEM_COLS_PER_WARPSLOT;
   {
     // The check state doubles as the dematcher's staging area: clear the rows in use ("no c2v messages yet").
     uint4*         s4 = reinterpret_cast<uint4*>(state);
-    const uint32_t n4 = ((uint32_t)soff[nlayers] * H * 4 + 15) / 16;
+    const uint32_t n4 = ((uint32_t)soff[min(nlayers, row_tm)] * H * 4 + 15) / 16;
     for (uint32_t i = tid; i < n4; i += blockDim.x) {
       s4[i] = make_uint4(0, 0, 0, 0);
+    }
+    // ... and the tensor-memory rows in use, eight columns per store (every thread clears its own lane)
+    if (nlayers > row_tm) {
+      for (uint32_t c = 0; c < 2u * (nlayers - row_tm); c += 8) {
+        tmem_st8_zero(tm_row0 + c);
+      }
+      tmem_wait_st();
     }
   }
   const uint32_t crc_poly = tab->crc_poly[D.crc_type], crc_top = 1u << tab->crc_len[D.crc_type];
@@ -927,7 +1029,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
-    fec_packed_iteration(soft_s, state, edges, soff, rs, deg, H, nlayers, smul, sadd);
+    fec_packed_iteration(soft_s, state, edges, soff, rs, deg, H, nlayers, smul, sadd, row_tm, tm_row0);
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     if (early_stop) {
       const bool clean = fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
@@ -976,7 +1078,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #undef s_nsig
 // Dispatcher: every codeblock the packed path covers goes there, the rest (odd Z, dematch-only
 // operations, unaligned decoder inputs) runs the generic per-check code in the same launch.
-__global__ void __launch_bounds__(FEC_PACKED_MAX_THREADS, 2)
+__global__ void __launch_bounds__(FEC_PACKED_MAX_THREADS, 3)
 fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
                      const int8_t* __restrict__ llr_base,
                      uint8_t* __restrict__ out_base,
@@ -986,11 +1088,27 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
                      const fec_packed_tables* __restrict__ ptab)
 {
   extern __shared__ __align__(16) uint8_t smem_raw[];
+  __shared__ uint32_t s_tmem_base;
   const fec_cb_desc D = descs[blockIdx.x];
-  if (fec_packed_cb_supported(D)) {
-    fec_packed_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab, ptab);
-  } else {
+  if (!fec_packed_cb_supported(D)) {
     fec_generic_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab);
+    return;
+  }
+  // Tensor memory for the check state of the last 32 base rows: 64 columns per group of four warps (3 resident CTAs of
+  // six warps take 3 x 128 of the SM's 512 columns; smaller CTAs take 64 each). One warp allocates and later frees.
+  const uint32_t tm_cols = (blockDim.x > 128) ? 2u * FEC_PACKED_TMEM_COLS_PER_WARPSLOT : FEC_PACKED_TMEM_COLS_PER_WARPSLOT;
+  if (threadIdx.x < 32) {
+    tmem_alloc((uint32_t)__cvta_generic_to_shared(&s_tmem_base), tm_cols);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = s_tmem_base;
+  fec_packed_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab, ptab, tmem_base);
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    tmem_dealloc(tmem_base, tm_cols);
   }
 }
 
@@ -1022,8 +1140,14 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
       off += fec_packed_row_words(t.deg[bg][m]);
     }
     pt.state_off[bg][M] = (uint16_t)off;
-    if (off != fec_packed_state_words(bg == 0)) {
+    const uint32_t row_tm = fec_packed_first_tmem_row(bg == 0);
+    if (pt.state_off[bg][row_tm] != fec_packed_state_words(bg == 0)) {
       return false;
+    }
+    for (uint32_t m = row_tm; m < (uint32_t)M; ++m) {
+      if (t.deg[bg][m] > 8) {
+        return false; // tensor-memory rows hold two state words
+      }
     }
     const int ne = t.row_start[bg][M];
     for (int zi = 0; zi < 51; ++zi) {
@@ -1060,8 +1184,9 @@ static inline int fec_packed_launch(cudaStream_t             st,
 {
   uint32_t threads = ((max_Z / 2 + 31) / 32) * 32;
   threads          = threads < 32 ? 32 : (threads > FEC_PACKED_MAX_THREADS ? FEC_PACKED_MAX_THREADS : threads);
-  const uint32_t a = fec_generic_layout(max_Z, any_bg1).total;
-  const uint32_t b = (max_Z % 2 == 0 && max_Z >= 4) ? fec_packed_layout(max_Z, any_bg1).total : 0;
+  // The generic per-check code only runs for odd lifting sizes and Z = 2 (all <= 15): its layout is sized for those.
+  const uint32_t a = fec_generic_layout(max_Z < 15 ? max_Z : 15, any_bg1).total;
+  const uint32_t b = (max_Z >= 4) ? fec_packed_layout(max_Z & ~1u, any_bg1).total : 0;
   const uint32_t smem = a > b ? a : b;
   // cudaFuncAttributeMaxDynamicSharedMemorySize is set ONCE, to the largest layout, in fec_engine_create: the attribute is
   // per-function global state and launches from several queues / threads would otherwise race on it.
