@@ -7,14 +7,17 @@
 // (min(|a|,|b|) with sign(a)^sign(b)), HSET2.BF gives 1.0/0.0 select masks that feed HFMA2, negation is an XOR and |x| an
 // AND. No tensor cores, no floating-point rounding anywhere (every intermediate is an integer below 2048).
 //
-// Shared-memory layout per codeblock (Z = 2H, H "halfwords" per column):
-//   soft   nfull*Z bytes. Column b occupies H halfwords; halfword w holds variables {w, w+H} of the column in bytes 0/1,
-//          stored offset-binary (value + 128). Magnitudes 121..127 all mean the reference's +-127 "infinity".
-//          With this interleave the cyclic shift s = q*H + r of an edge becomes ONE aligned 16-bit load at (t + r) mod H
-//          plus a byte swap when q + wrap is odd, and the write-back is one aligned 16-bit store.
+// Per-codeblock working set (Z = 2H, H 32-bit "pair words" per column):
+//   soft   nfull*H words in SHARED memory. Word w of column b holds variables {w, w+H} of the column as its two 16-bit
+//          lanes, already in the sign-magnitude number format above (no conversion on load or store). Finite values are
+//          <= 120 in magnitude; anything above 120 is the reference's +-127 "infinity" (sticky: it only grows).
+//          With this interleave the cyclic shift s = q*H + r of an edge is ONE aligned 32-bit load at word (t + r) mod H
+//          plus a lane swap when q + wrap is odd. The swap bit rides in bit 1 of the edge's byte address, where
+//          PRMT.F4E (rotate by address bits 1:0) finds it: one PRMT after the load, one before the store.
 //   state  per base row and thread: word0 = scaled min1 / min2 of both checks; then index of the min1 edge and the c2v
 //          sign bits (1 more word for rows of degree <= 8, 2 otherwise). All-zero = "row not initialised" (c2v = 0).
-//   edges  per edge {byte address of (col*H + r), H - r, unpack/pack selectors}: uniform per CTA, read by broadcast.
+//          The dense first rows keep it in shared memory; every later row keeps it in TENSOR MEMORY (see below).
+//   edges  per edge {byte address of word (col*H + r) + swap bit, same for threads that wrap, H - r}: uniform per CTA.
 //
 // Bit-exactness with the reference's generic decoder is argued step by step in DESIGN.md ("packed kernel algebra").
 #pragma once
@@ -26,10 +29,10 @@
 #define FEC_PACKED_MAX_THREADS 192
 
 struct fec_packed_edge {
-  uint32_t aN;  // byte offset of lane 0 for thread 0 when it does not wrap: (col * H + r) * 2 + (q & 1)
-  uint32_t aW;  // same for threads that wrap around the column: (col * H + r - H) * 2 + ((q + 1) & 1)
+  uint32_t aN;  // thread 0, no wrap: byte offset of pair word col * H + r, plus 2 if the lanes come swapped (q odd)
+  uint32_t aW;  // threads that wrap around the column: pair word col * H + r - H, plus 2 if q + 1 is odd
   uint32_t thr; // H - r : threads t >= thr wrap
-  uint32_t pad; // lane 1 always sits at the lane-0 address ^ 1
+  uint32_t pad;
 };
 
 // Device-global tables for the packed kernel (built once per engine).
@@ -41,7 +44,7 @@ struct fec_packed_tables {
 };
 
 struct fec_packed_smem_layout {
-  uint32_t state, edges, soff, rs, deg, bitsw, red, x8, soft, total;
+  uint32_t state, edges, soff, rs, deg, bitsw, red, soft, total;
 };
 
 __host__ __device__ inline uint32_t fec_packed_row_words(uint32_t d)
@@ -49,26 +52,32 @@ __host__ __device__ inline uint32_t fec_packed_row_words(uint32_t d)
   return d <= 8 ? 2u : 3u;
 }
 
-// Where the check state lives. The LAST FEC_PACKED_TMEM_ROWS base rows of a graph (all of degree <= 8: two words per thread)
-// keep their state in TENSOR MEMORY: thread t of warp w owns TMEM lane 32 (w % 4) + (t % 32), columns
-// 64 (w / 4) + 2 (row - first_tmem_row) + {0, 1} of the CTA's allocation (tcgen05.alloc / ld / st as a private per-thread
-// scratchpad; no MMA is ever issued). Every thread reads back only what it wrote itself. The first rows (the dense core of
-// the graph) stay in shared memory. This takes 49 KB of check state out of shared memory at BG1 / Z = 384, which is what lets
-// three codeblocks instead of two be resident per SM.
-#define FEC_PACKED_TMEM_ROWS 32u
-#define FEC_PACKED_TMEM_COLS_PER_WARPSLOT (2u * FEC_PACKED_TMEM_ROWS)
+// Where the check state lives. Only the first rows of a graph (BG1: 7, BG2: 3) keep it in shared memory; all later rows
+// keep it in TENSOR MEMORY, used as a private per-thread scratchpad (tcgen05.alloc / ld / st in the 32x32b shape; no MMA is
+// ever issued): thread t of warp w owns TMEM lane 32 (w % 4) + (t % 32) and reads back only what it wrote itself.
+//   region A (64 columns per group of four warps): the last 32 base rows, two words each;
+//   region B (16 columns per group of four warps): the 7 rows before them, two or three words each (<= 16 words).
+// At BG1 / Z = 384 that takes 61 of the 76 KB of check state out of shared memory, which pays for the 16-bit soft-bit
+// format (52 KB) while THREE codeblocks stay resident per SM (3 x 74 KB of shared memory, 3 x 160 of 512 TMEM columns).
+#define FEC_PACKED_TMEM_A_ROWS 32u
+#define FEC_PACKED_TMEM_B_ROWS 7u
+#define FEC_PACKED_TMEM_A_COLS 64u // per warp slot (group of four warps)
+#define FEC_PACKED_TMEM_B_COLS 16u
 
-__host__ __device__ inline uint32_t fec_packed_first_tmem_row(int bg1)
+__host__ __device__ inline uint32_t fec_packed_row_a(int bg1) // first row of region A
 {
-  return (bg1 ? 46u : 42u) - FEC_PACKED_TMEM_ROWS;
+  return (bg1 ? 46u : 42u) - FEC_PACKED_TMEM_A_ROWS;
+}
+__host__ __device__ inline uint32_t fec_packed_row_b(int bg1) // first row of region B = number of rows in shared memory
+{
+  return fec_packed_row_a(bg1) - FEC_PACKED_TMEM_B_ROWS;
 }
 
-// State words per thread kept in SHARED memory (rows before the first TMEM row).
+// State words per thread kept in SHARED memory (rows before region B).
 __host__ __device__ inline uint32_t fec_packed_state_words(int bg1)
 {
-  // BG1 rows 0..13: degrees 19,19,19,19,3,8,9,7,10,9,7,8,7,6 -> 7 rows of 3 words, 7 rows of 2.
-  // BG2 rows 0..9: degrees 8,10,8,10,4,6,6,6,4,5 -> 2 rows of 3 words, 8 rows of 2.
-  return bg1 ? (7u * 3u + 7u * 2u) : (2u * 3u + 8u * 2u);
+  // BG1 rows 0..6: degrees 19,19,19,19,3,8,9 -> 3,3,3,3,2,2,3. BG2 rows 0..2: degrees 8,10,8 -> 2,3,2.
+  return bg1 ? 19u : 7u;
 }
 
 __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, int bg1)
@@ -91,11 +100,9 @@ __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, 
   o += ((Kb * Z + 31) / 32 + 1) * 4;
   L.red = o;
   o += 64 * 4;
-  L.x8 = o;
-  o += (Kb * Z / 8 + 2) * 4;
   o      = (o + 15) & ~15u;
   L.soft = o;
-  o += (nfull * Z + 15) & ~15u;
+  o += (nfull * H * 4 + 15) & ~15u;
   L.total = o;
   return L;
 }
@@ -159,6 +166,9 @@ __device__ __forceinline__ uint32_t prmt_f4e(uint32_t a, uint32_t b, uint32_t c)
 __device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols)
 {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish()
+{
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols)
@@ -171,6 +181,23 @@ __device__ __forceinline__ void tmem_ld2(uint32_t taddr, uint32_t& a, uint32_t& 
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];\n\ttcgen05.wait::ld.sync.aligned;"
                : "=r"(a), "=r"(b)
                : "r"(taddr)
+               : "memory");
+}
+// Three consecutive columns (rows of degree 9 / 10): x2 + x1, one wait.
+__device__ __forceinline__ void tmem_ld3(uint32_t taddr, uint32_t& a, uint32_t& b, uint32_t& c)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%3];\n\t"
+               "tcgen05.ld.sync.aligned.32x32b.x1.b32 {%2}, [%4];\n\t"
+               "tcgen05.wait::ld.sync.aligned;"
+               : "=r"(a), "=r"(b), "=r"(c)
+               : "r"(taddr), "r"(taddr + 2u)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st3(uint32_t taddr, uint32_t a, uint32_t b, uint32_t c)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%2, %3};\n\t"
+               "tcgen05.st.sync.aligned.32x32b.x1.b32 [%1], {%4};" ::"r"(taddr),
+               "r"(taddr + 2u), "r"(a), "r"(b), "r"(c)
                : "memory");
 }
 __device__ __forceinline__ void tmem_st2(uint32_t taddr, uint32_t a, uint32_t b)
@@ -209,17 +236,17 @@ __device__ __forceinline__ uint32_t fec_reg_const(uint32_t x)
   return r;
 }
 
-// Shared-memory byte accesses by 32-bit shared-window address (lets the two lanes of a halfword be addressed A and A^1).
+// Shared-memory pair-word accesses by 32-bit shared-window address.
 // "memory" clobber: ordinary C++ stores to shared memory surround these accesses and must not be moved across them.
-__device__ __forceinline__ uint32_t lds_u8(uint32_t a)
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a)
 {
   uint32_t r;
-  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r) : "r"(a) : "memory");
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r) : "r"(a) : "memory");
   return r;
 }
-__device__ __forceinline__ void sts_u8(uint32_t a, uint32_t v)
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v)
 {
-  asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
 // Integer helpers pinned to the FMA pipe (IMAD / IMAD.HI), which this kernel under-uses, instead of SHF / PRMT on the ALU.
 __device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
@@ -244,12 +271,11 @@ __device__ __forceinline__ uint32_t imul_hi(uint32_t a, uint32_t b)
 
 // ---- one base row for the 2 checks {t, t+H} of this thread -------------------------------------------------------------
 // D = row degree (compile time so that the per-edge values stay in registers). Lane 0 = check t, lane 1 = check t+H.
-// Instruction budget per edge and thread: ALU pipe 14 (ISETP, SEL, IADD3, LOP3 for the addresses; 2 HSET2,
-// 5 HMNMX2, 3 LOP3), FMA pipe 15 (HFMA2 / HADD2 / IMAD), LSU 5.
+// TM: the row's state words live in tensor memory at taddr (2 or 3 consecutive columns of this thread's lane).
 template <int D, bool TM>
 __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, // shared-window address of the soft array
                                                uint32_t*              st,     // state words of this row for thread t (!TM)
-                                               uint32_t               taddr,  // tensor-memory address of the row's 2 words (TM)
+                                               uint32_t               taddr,  // tensor-memory address of the row's words (TM)
                                                const fec_packed_edge* ed,     // D edge records (shared memory)
                                                uint32_t               H,
                                                uint32_t               t,
@@ -257,8 +283,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
                                                uint32_t               scale_add)
 {
   constexpr int  NW = (D <= 8) ? 2 : 3;
-  static_assert(!TM || NW == 2, "rows kept in tensor memory have two state words");
-  const uint32_t tb = soft_s + t * 2;
+  const uint32_t tb = soft_s + t * 4;
 
   // ---- pre-phase: everything that does not depend on the soft bits (addresses, the previous c2v messages of this row).
   // It runs BEFORE the CTA barrier that orders this row after the previous one, so warps that finished the previous row
@@ -268,7 +293,11 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     uint32_t w0, w1, w2 = 0;
     if (TM) {
       tmem_wait_st(); // this thread's store of the previous tensor-memory row
-      tmem_ld2(taddr, w0, w1);
+      if (NW == 3) {
+        tmem_ld3(taddr, w0, w1, w2);
+      } else {
+        tmem_ld2(taddr, w0, w1);
+      }
     } else {
       w0 = st[0];
       w1 = st[H];
@@ -279,7 +308,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
 #pragma unroll
     for (int e = 0; e < D; ++e) {
       const uint4 E = *reinterpret_cast<const uint4*>(&ed[e]);
-      a0[e]         = ((t >= E.z) ? E.y : E.x) + tb;
+      a0[e]         = imad((t >= E.z) ? E.y : E.x, 1u, tb); // the add on the FMA pipe: the ALU pipe is the busier one
     }
     const uint32_t om1 = __byte_perm(w0, 0, 0x4140), om2 = __byte_perm(w0, 0, 0x4342);
     const uint32_t odl = h2_add(om2, om1 ^ H2_SIGN); // m2 - m1 >= 0
@@ -296,18 +325,18 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   asm volatile("bar.sync 0;" ::: "memory");
 
   // ---- phase A: variable-to-check messages and the min1 / min2 / sign-product analysis -----------------------------------
-  uint32_t up[D];
+  uint32_t S[D];
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    up[e] = imad(lds_u8(a0[e] ^ 1u), 65536u, lds_u8(a0[e])); // lane 0 at A, lane 1 at A ^ 1
+    const uint32_t x = lds_u32(a0[e] & ~2u);
+    S[e]             = prmt_f4e(x, x, a0[e]); // address bit 1 set: the two lanes come swapped
   }
   uint32_t v[D];
   uint32_t m1 = H2_P120, m2 = H2_P120;
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint32_t S    = h2_add(up[e], H2_M128);                                    // soft value
-    const uint32_t vraw = h2_add(S, cneg[e]);                                        // soft - c2v, |.| <= 223
-    const uint32_t y    = h2_add(h2_fma(S, H2_F4352, H2_F96), H2_FM96);              // +-1/16 iff |S| > 120
+    const uint32_t vraw = h2_add(S[e], cneg[e]);                                     // soft - c2v
+    const uint32_t y    = h2_add(h2_fma(S[e], H2_F4352, H2_F96), H2_FM96);           // nonzero, sign of S, iff |S| > 120
     const uint32_t vcl  = h2_min_xs(vraw, H2_P120);                                  // saturate at +-120
     const uint32_t vv   = h2_fma(y, H2_F2M11, vcl);                                  // "infinite" soft bits stay huge
     v[e]                = vv;
@@ -333,9 +362,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     const uint32_t mg = h2_fma(eq, dls, M1s);            // sign product * scaled magnitude
     const uint32_t c  = mg ^ (vv & H2_SIGN);             // new c2v
     nid               = h2_fma(eq, FEC_H2(e), nid);      // index of the min1 edge (any value if min1 == min2)
-    const uint32_t tt = h2_add(c, vv);                   // c2v + v2c
-    const uint32_t nw = h2_min_xs(tt, H2_P127);          // |.| > 120 is "infinity" from here on
-    const uint32_t o  = h2_add(nw, H2_P128);             // offset binary in the low byte of each lane
+    const uint32_t tt = h2_add(c, vv);                   // c2v + v2c: above 120 in magnitude it IS the "infinity" from here on
     // sign(v2c) of the two lanes -> bit (e & 15) of the sign word
     const uint32_t sh = ((e & 15) == 15) ? vv : FEC_SHR(vv, 15 - (e & 15));
     if (e < 16) {
@@ -343,25 +370,34 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     } else {
       sg2 |= sh & (0x00010001u << (e & 15));
     }
-    sts_u8(a0[e], o);
-    sts_u8(a0[e] ^ 1u, FEC_SHR(o, 16));
+    sts_u32(a0[e] & ~2u, prmt_f4e(tt, tt, a0[e]));
   }
 
   // ---- new state: c2v sign = sign product ^ sign(v2c) ----------------------------------------------------------------------
-  const uint32_t pm = prmt(m1, 0u, 0xbb99); // 0xffff in the lanes whose sign product is negative
-  if (TM) {
-    tmem_st2(taddr, __byte_perm(s1, s2, 0x6420), ((sg1 ^ pm) & 0x00ff00ffu) | (nid << 8));
-    return;
-  }
-  st[0] = __byte_perm(s1, s2, 0x6420);
+  const uint32_t pm  = prmt(m1, 0u, 0xbb99); // 0xffff in the lanes whose sign product is negative
+  const uint32_t nw0 = __byte_perm(s1, s2, 0x6420);
+  uint32_t       nw1, nw2 = 0;
   if (D <= 8) {
-    st[H] = ((sg1 ^ pm) & 0x00ff00ffu) | (nid << 8);
+    nw1 = ((sg1 ^ pm) & 0x00ff00ffu) | (nid << 8);
   } else if (D <= 16) {
-    st[H]     = sg1 ^ pm;
-    st[2 * H] = nid;
+    nw1 = sg1 ^ pm;
+    nw2 = nid;
   } else {
-    st[H]     = sg1 ^ pm;
-    st[2 * H] = ((sg2 ^ pm) & 0x00070007u) | (nid << 8);
+    nw1 = sg1 ^ pm;
+    nw2 = ((sg2 ^ pm) & 0x00070007u) | (nid << 8);
+  }
+  if (TM) {
+    if (NW == 3) {
+      tmem_st3(taddr, nw0, nw1, nw2);
+    } else {
+      tmem_st2(taddr, nw0, nw1);
+    }
+  } else {
+    st[0] = nw0;
+    st[H] = nw1;
+    if (NW == 3) {
+      st[2 * H] = nw2;
+    }
   }
 }
 
@@ -377,8 +413,10 @@ __device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
                                                   uint32_t               nlayers,
                                                   uint32_t               smul,
                                                   uint32_t               sadd,
-                                                  uint32_t               row_tm, // first base row whose state is in tensor memory
-                                                  uint32_t               tm_row0) // this warp's tensor-memory address of that row
+                                                  uint32_t               row_b, // first base row of tensor-memory region B
+                                                  uint32_t               row_a, // first base row of tensor-memory region A
+                                                  uint32_t               tm_b,  // this warp's address of region B / A
+                                                  uint32_t               tm_a)
 {
   const uint32_t tid = threadIdx.x;
   for (uint32_t l = 0; l < nlayers; ++l) {
@@ -389,24 +427,22 @@ __device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
       // copy of the tensor-memory state) so that whole warps reach the barrier inside the row function.
       const uint32_t         tq = min(tid, H - 1);
       const fec_packed_edge* ed = edges + rs[l];
-      if (l >= row_tm) {
-        const uint32_t ta = tm_row0 + 2u * (l - row_tm);
+      if (l >= row_b) {
+        const uint32_t ta = (l >= row_a) ? tm_a + 2u * (l - row_a) : tm_b + soff[l];
         switch (deg[l]) {
           case 3: fec_packed_row<3, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
           case 4: fec_packed_row<4, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
           case 5: fec_packed_row<5, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
           case 6: fec_packed_row<6, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
           case 7: fec_packed_row<7, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          default: fec_packed_row<8, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          case 8: fec_packed_row<8, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          case 9: fec_packed_row<9, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+          default: fec_packed_row<10, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
         }
       } else {
         uint32_t* st = state + (uint32_t)soff[l] * H + tq;
-        switch (deg[l]) {
+        switch (deg[l]) { // the degrees of the rows kept in shared memory: BG1 19,19,19,19,3,8,9; BG2 8,10,8
           case 3: fec_packed_row<3, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          case 4: fec_packed_row<4, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          case 5: fec_packed_row<5, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          case 6: fec_packed_row<6, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          case 7: fec_packed_row<7, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
           case 8: fec_packed_row<8, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
           case 9: fec_packed_row<9, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
           case 10: fec_packed_row<10, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
@@ -417,17 +453,23 @@ __device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
   }
 }
 
-// Byte address of variable j (0 <= j < Z) of column col in the interleaved soft layout.
-__device__ __forceinline__ uint32_t fec_packed_soft_addr(uint32_t col, uint32_t j, uint32_t Z, uint32_t H)
+// Index, in 16-bit units, of variable j (0 <= j < Z) of column col in the pair-word soft layout.
+__device__ __forceinline__ uint32_t fec_packed_soft_idx(uint32_t col, uint32_t j, uint32_t H)
 {
   const uint32_t lane = (j >= H) ? 1u : 0u;
-  return col * Z + (j - lane * H) * 2 + lane;
+  return (col * H + (j - lane * H)) * 2 + lane;
 }
 
-// Dematcher / loader target: clamp to +-64 (ldpc_decoder_impl.cpp:168-169) and store offset-binary in the packed layout.
+// An integer LLR in the 16-bit sign-magnitude number format.
+__device__ __forceinline__ uint16_t fec_sm16(int v)
+{
+  return (uint16_t)((v < 0) ? (0x8000 | (-v)) : v);
+}
+
+// Loader target: clamp to +-64 (ldpc_decoder_impl.cpp:168-169) and store in the pair-word layout.
 struct fec_soft_store_packed {
-  uint8_t* soft;
-  uint32_t Z, H, invZ;
+  uint16_t* soft16;
+  uint32_t  Z, H, invZ;
   __device__ __forceinline__ void operator()(uint32_t o, int acc) const
   {
     raw(o, fec_clampi(acc, -64, 64));
@@ -437,12 +479,52 @@ struct fec_soft_store_packed {
   {
     const uint32_t op  = o + 2 * Z;
     const uint32_t col = __umulhi(op, invZ);
-    soft[fec_packed_soft_addr(col, op - col * Z, Z, H)] = (uint8_t)(acc + 128);
+    soft16[fec_packed_soft_idx(col, op - col * Z, H)] = fec_sm16(acc);
   }
 };
 
+// The decoder's soft bits from the soft buffer the dematcher has just written (natural int8 layout in HBM, L2-hot): the two
+// punctured columns are zero, buffer positions [0, npos) are clamped to +-64 and converted; nothing beyond the columns the
+// layers in use touch is needed. Four positions per thread and step (npos is a multiple of Z, Z is even: npos % 4 == 0 except
+// for Z = 2 (mod 4) with an odd number of columns -- the last two positions are then handled one by one).
+// The loads bypass L1 (ld.global.cg): other threads of the CTA wrote these bytes earlier in this kernel.
+__device__ __forceinline__ void fec_soft_fill_from_harq(const int8_t* harq, uint16_t* soft16, uint32_t npos, uint32_t Z, uint32_t H,
+                                                        uint32_t invZ)
+{
+  uint32_t* soft32 = reinterpret_cast<uint32_t*>(soft16);
+  for (uint32_t i = threadIdx.x; i < Z; i += blockDim.x) {
+    soft32[i] = 0; // columns 0 and 1: H pair words each
+  }
+  const fec_soft_store_packed store{soft16, Z, H, invZ};
+  const uint32_t*             h4 = reinterpret_cast<const uint32_t*>(harq);
+  const uint32_t              ng = npos / 4;
+  for (uint32_t g = threadIdx.x; g < ng; g += blockDim.x) {
+    const uint32_t w   = __ldcg(h4 + g);
+    const uint32_t o0  = g * 4;
+    const uint32_t op0 = o0 + 2 * Z;
+    const uint32_t col = __umulhi(op0, invZ);
+    const uint32_t j0  = op0 - col * Z;
+    if (j0 + 3 < H || (j0 >= H && j0 + 3 < Z)) {
+      const uint32_t lane = (j0 >= H) ? 1u : 0u;
+      uint16_t*      dst  = soft16 + (col * H + (j0 - lane * H)) * 2 + lane;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        dst[2 * b] = fec_sm16(fec_clampi((int)(int8_t)(w >> (8 * b)), -64, 64));
+      }
+    } else {
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        store(o0 + b, (int)(int8_t)(w >> (8 * b)));
+      }
+    }
+  }
+  for (uint32_t o = ng * 4 + threadIdx.x; o < npos; o += blockDim.x) {
+    store(o, (int)__ldcg(harq + o));
+  }
+}
+
 // Hard decision of the first K soft bits (bit = soft <= 0) into bitsw, big-endian bit order; true if no soft bit is zero.
-__device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32_t* bitsw, uint32_t K, uint32_t Z, uint32_t H,
+__device__ __forceinline__ bool fec_hard_bits_packed(const uint16_t* soft16, uint32_t* bitsw, uint32_t K, uint32_t Z, uint32_t H,
                                                      uint32_t invZ)
 {
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -450,21 +532,22 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32
   if ((H & 31u) == 0) {
     // One column per step: thread t holds variables t and t+H of the column; a ballot yields 32 consecutive bits.
     // Kb is 22 or 10: batches of 11 / 10 loads in flight, then the ballots.
-    const uint32_t Kb = K / Z, nb = (Kb == 22) ? 11u : 10u;
+    const uint32_t* soft32 = reinterpret_cast<const uint32_t*>(soft16);
+    const uint32_t  Kb = K / Z, nb = (Kb == 22) ? 11u : 10u;
     if (threadIdx.x < H) {
       for (uint32_t c0 = 0; c0 < Kb; c0 += nb) {
         uint32_t hw[11];
 #pragma unroll
         for (uint32_t c = 0; c < 11; ++c) {
-          hw[c] = (c < nb) ? *reinterpret_cast<const uint16_t*>(soft + (c0 + c) * Z + threadIdx.x * 2) : 0x8181u;
+          hw[c] = (c < nb) ? soft32[(c0 + c) * H + threadIdx.x] : 0x00010001u;
         }
 #pragma unroll
         for (uint32_t c = 0; c < 11; ++c) {
           if (c < nb) {
-            const uint32_t b0 = hw[c] & 0xffu, b1 = hw[c] >> 8;
-            zero |= (b0 == 128) | (b1 == 128);
-            const uint32_t bal0 = __ballot_sync(0xffffffffu, b0 <= 128);
-            const uint32_t bal1 = __ballot_sync(0xffffffffu, b1 <= 128);
+            const uint32_t m0 = hw[c] & 0x7fffu, m1 = hw[c] & 0x7fff0000u;
+            zero |= (m0 == 0) | (m1 == 0);
+            const uint32_t bal0 = __ballot_sync(0xffffffffu, (m0 == 0) | ((hw[c] & 0x8000u) != 0));
+            const uint32_t bal1 = __ballot_sync(0xffffffffu, (m1 == 0) | ((hw[c] & 0x80000000u) != 0));
             if (lane == 0) {
               bitsw[((c0 + c) * Z + warp * 32) >> 5]     = __brev(bal0);
               bitsw[((c0 + c) * Z + H + warp * 32) >> 5] = __brev(bal1);
@@ -478,13 +561,13 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32
   const uint32_t nw = (K + 31) / 32;
   for (uint32_t w = warp; w < nw; w += nwarps) {
     const uint32_t i = w * 32 + lane;
-    uint32_t       b = 129; // positive
+    uint32_t       b = 1; // positive
     if (i < K) {
       const uint32_t col = __umulhi(i, invZ);
-      b                  = soft[fec_packed_soft_addr(col, i - col * Z, Z, H)];
+      b                  = soft16[fec_packed_soft_idx(col, i - col * Z, H)];
     }
-    zero |= (b == 128);
-    const uint32_t bal = __ballot_sync(0xffffffffu, b <= 128);
+    zero |= ((b & 0x7fffu) == 0);
+    const uint32_t bal = __ballot_sync(0xffffffffu, ((b & 0x7fffu) == 0) | ((b & 0x8000u) != 0));
     if (lane == 0) {
       bitsw[w] = __brev(bal);
     }
@@ -493,10 +576,11 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint8_t* soft, uint32
 }
 
 // CRC remainder == 0 test of the first T bits of bitsw (crc_calculator_generic_impl.cpp:111-133 computes the same
-// remainder bytewise). Byte i of the message contributes byte_i(x) * x^(8 (nb-1-i)) mod g; x8[j] = x^(8 j) mod g is staged
-// in shared memory once per codeblock. Up to six independent 8-step multiply chains per thread, one barrier.
+// remainder bytewise). Byte i of the message contributes byte_i(x) * x^(8 (nb-1-i)) mod g; x8[j] = x^(8 j) mod g comes from
+// the engine's table in HBM (4 KB per polynomial, L1 / L2 resident; shared memory has no room for it beside the 16-bit
+// soft bits). Up to six independent 8-step multiply chains per thread, one barrier.
 // Kept out of line: inlined into the codeblock function it changes ptxas' register allocation of the row code for the worse.
-__device__ __noinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T, const uint32_t* x8, uint32_t poly,
+__device__ __noinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T, const uint32_t* __restrict__ x8, uint32_t poly,
                                                   uint32_t top, uint32_t* red)
 {
   const uint32_t nb = T / 8, r = T % 8;
@@ -507,7 +591,7 @@ __device__ __noinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T
     for (int k = 0; k < 6; ++k) {
       const uint32_t i = i0 + k * blockDim.x;
       const bool     v = (i < nb);
-      a[k]             = v ? x8[nb - 1 - i] : 0u;
+      a[k]             = v ? __ldg(x8 + (nb - 1 - i)) : 0u;
       w[k]             = v ? (bitsw[i >> 2] >> (24 - 8 * (i & 3))) : 0u;
     }
 #pragma unroll
@@ -546,16 +630,17 @@ __device__ __noinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T
 // Same arithmetic as fec_dematch_cta (the per-byte statement of ldpc_rate_dematcher_impl.cpp:46-257), organised for
 // throughput:
 //  1. the E input LLRs are read once with coalesced 16-byte loads and scattered into shared memory (`stage`: the not yet
-//     used check-state area) in RATE-MATCHED order, i.e. the bit de-interleaver of TS 38.212 5.4.2.2 is undone while
+//     used soft-bit area) in RATE-MATCHED order, i.e. the bit de-interleaver of TS 38.212 5.4.2.2 is undone while
 //     staging. The staged position of LLR p is p + d, d in {d1, d2} chosen so that a staged 32-bit word lines up with a
 //     32-bit word of the soft buffer inside either data run of a non-wrapping transmission;
-//  2. the zero tail [zero_from, N) of a first transmission is stored without looking at anything (the decoder's soft bits
-//     were preset to zero);
-//  3. groups of four soft-buffer bytes inside a data run take one 32-bit shared load, one 32-bit HBM store (plus a 32-bit
-//     load and four saturating sums when combining) and four byte stores into the decoder's interleaved layout;
+//  2. the zero tail [zero_from, N) of a first transmission is stored without looking at anything;
+//  3. groups of four soft-buffer bytes inside a data run take one 32-bit shared load and one 32-bit HBM store (plus a 32-bit
+//     load and four saturating sums when combining);
 //  4. every other group (region boundaries, fillers, kept parts of the buffer, wrapping transmissions) takes the general
 //     path: still four bytes per thread, per-byte rules.
-// Inputs that do not fit the staging area (E > 76 KB at Z = 384: heavy repetition) are read from global memory per byte.
+// The dematcher writes the soft buffer (HBM) only; the decoder's own 16-bit copy is filled from it afterwards
+// (fec_soft_fill_from_harq: the lines are L2-hot, and only the columns of the layers in use are needed).
+// Inputs that do not fit the staging area (E > 52 KB at Z = 384: heavy repetition) are read from global memory per byte.
 struct fec_dematch_geom {
   uint32_t Z, N, Ncb, fillers, sys, info, E, qm, Kp, invKp, Lc, k0c, zero_lo, zero_from, kstart;
   bool     newd, hzero, wrapped;
@@ -648,33 +733,6 @@ __device__ __forceinline__ int fec_dematch_byte(const fec_dematch_geom& G, const
   return (o >= G.zero_from) ? 0 : acc;
 }
 
-// Four consecutive soft-buffer values (packed little-endian in w, as in the HARQ buffer) into the decoder's soft array.
-__device__ __forceinline__ void fec_soft_store4(const fec_soft_store_packed& store, uint32_t o0, uint32_t w)
-{
-  const uint32_t Z = store.Z, H = store.H;
-  const uint32_t op0 = o0 + 2 * Z;
-  const uint32_t col = __umulhi(op0, store.invZ);
-  const uint32_t j0  = op0 - col * Z;
-  int            val[4];
-#pragma unroll
-  for (int b = 0; b < 4; ++b) {
-    val[b] = (int)(int8_t)(w >> (8 * b));
-  }
-  if (j0 + 3 < H || (j0 >= H && j0 + 3 < Z)) {
-    const uint32_t lane = (j0 >= H) ? 1u : 0u;
-    uint8_t*       dst  = store.soft + col * Z + (j0 - lane * H) * 2 + lane;
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      dst[2 * b] = (uint8_t)(fec_clampi(val[b], -64, 64) + 128);
-    }
-  } else {
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      store(o0 + b, val[b]);
-    }
-  }
-}
-
 __device__ __forceinline__ uint32_t fec_pack4(const int* val)
 {
   return (uint32_t)(uint8_t)val[0] | ((uint32_t)(uint8_t)val[1] << 8) | ((uint32_t)(uint8_t)val[2] << 16) |
@@ -690,15 +748,11 @@ __device__ __forceinline__ uint32_t fec_last_sig(uint32_t o0, uint32_t w)
 // The soft buffer of one codeblock, four bytes per thread and step. Returns position + 1 of this thread's last non-zero value.
 __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G,
                                                        const fec_dematch_src&  S,
-                                                       int8_t* __restrict__    harq,
-                                                       uint8_t*                soft,
-                                                       uint32_t                H,
-                                                       uint32_t                invZ)
+                                                       int8_t* __restrict__    harq)
 {
-  uint32_t                    my_sig  = 0;
-  const uint32_t              ngroups = G.N / 4; // Z is even and N = 66Z or 50Z, so N % 4 == 0
-  uint32_t*                   harq4   = reinterpret_cast<uint32_t*>(harq);
-  const fec_soft_store_packed store{soft, G.Z, H, invZ};
+  uint32_t       my_sig  = 0;
+  const uint32_t ngroups = G.N / 4; // Z is even and N = 66Z or 50Z, so N % 4 == 0
+  uint32_t*      harq4   = reinterpret_cast<uint32_t*>(harq);
 
   // Data runs of a non-wrapping transmission: rate-matched LLR p = o - off lands at buffer position o for o in [lo, hi),
   // once before the filler gap and once after it. hg0 / hg1: the groups entirely inside a run (staged inputs only).
@@ -719,7 +773,7 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
 
   // (2) zero tail
   for (uint32_t g = gz0 + threadIdx.x; g < ngroups; g += blockDim.x) {
-    harq4[g] = 0; // the decoder's soft bits were preset to zero
+    harq4[g] = 0;
   }
 
   // (3) groups inside a data run
@@ -739,9 +793,6 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
       }
       harq4[g] = w;
       my_sig   = max(my_sig, fec_last_sig(o0, w));
-      if (soft != nullptr) {
-        fec_soft_store4(store, o0, w);
-      }
     }
   }
 
@@ -798,9 +849,6 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
     const uint32_t w = fec_pack4(val);
     harq4[g]         = w;
     my_sig           = max(my_sig, fec_last_sig(o0, w));
-    if (soft != nullptr) {
-      fec_soft_store4(store, o0, w);
-    }
   }
   return my_sig;
 }
@@ -808,14 +856,11 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
 __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
                                                    const int8_t* __restrict__ in,
                                                    int8_t* __restrict__ harq,
-                                                   uint8_t*  soft, // interleaved decoder layout, nullptr = do not fill
-                                                   uint32_t  H,
                                                    int8_t*   stage,
                                                    uint32_t  stage_cap,
                                                    uint32_t* n_sig_smem)
 {
   const fec_dematch_geom G = fec_dematch_geometry(D);
-  const uint32_t         Z = G.Z, invZ = 0xffffffffu / Z + 1;
 
   fec_dematch_src S;
   S.base   = in;
@@ -853,7 +898,7 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
     S.staged = true;
   }
 
-  const uint32_t my_sig = fec_dematch_groups(G, S, harq, soft, H, invZ);
+  const uint32_t my_sig = fec_dematch_groups(G, S, harq);
   if (my_sig != 0) {
     atomicMax(n_sig_smem, my_sig);
   }
@@ -876,7 +921,8 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
                                            int8_t* __restrict__ harq_base,
                                            const fec_dev_tables* __restrict__ tab,
                                            const fec_packed_tables* __restrict__ ptab,
-                                           uint32_t tmem_base)
+                                           uint32_t tmem_a,
+                                           uint32_t tmem_b)
 {
   __shared__ uint32_t s_nsig_arr[2];
 #define s_nsig s_nsig_arr[0]
@@ -893,17 +939,16 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   long long tp0 = clock64(), tp1 = 0, tp2 = 0, tp3 = 0;
 #endif
   const fec_packed_smem_layout L = fec_packed_layout(Z, bg1);
-  uint32_t*        state = reinterpret_cast<uint32_t*>(smem_raw + L.state);
-  fec_packed_edge* edges = reinterpret_cast<fec_packed_edge*>(smem_raw + L.edges);
-  uint16_t*        soff  = reinterpret_cast<uint16_t*>(smem_raw + L.soff);
-  uint16_t*        rs    = reinterpret_cast<uint16_t*>(smem_raw + L.rs);
-  uint8_t*         deg   = smem_raw + L.deg;
-  uint32_t*        bitsw = reinterpret_cast<uint32_t*>(smem_raw + L.bitsw);
-  uint32_t*        red   = reinterpret_cast<uint32_t*>(smem_raw + L.red);
-  uint32_t*        x8    = reinterpret_cast<uint32_t*>(smem_raw + L.x8);
-  uint8_t*         soft  = smem_raw + L.soft;
+  uint32_t*        state  = reinterpret_cast<uint32_t*>(smem_raw + L.state);
+  fec_packed_edge* edges  = reinterpret_cast<fec_packed_edge*>(smem_raw + L.edges);
+  uint16_t*        soff   = reinterpret_cast<uint16_t*>(smem_raw + L.soff);
+  uint16_t*        rs     = reinterpret_cast<uint16_t*>(smem_raw + L.rs);
+  uint8_t*         deg    = smem_raw + L.deg;
+  uint32_t*        bitsw  = reinterpret_cast<uint32_t*>(smem_raw + L.bitsw);
+  uint32_t*        red    = reinterpret_cast<uint32_t*>(smem_raw + L.red);
+  uint16_t*        soft16 = reinterpret_cast<uint16_t*>(smem_raw + L.soft);
 
-  // Stage the graph of this codeblock and clear the check state.
+  // Stage the graph of this codeblock.
   {
     const uint4* src = reinterpret_cast<const uint4*>(ptab->edges[D.graph_index]);
     uint4*       dst = reinterpret_cast<uint4*>(edges);
@@ -914,16 +959,6 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
       rs[i]   = tab->row_start[bg1 ? 0 : 1][i];
       deg[i]  = tab->deg[bg1 ? 0 : 1][i];
       soff[i] = ptab->state_off[bg1 ? 0 : 1][i];
-    }
-    // All soft bits start at zero (offset-binary 128): the two punctured columns, and whatever the dematcher skips.
-    uint4*         p4  = reinterpret_cast<uint4*>(soft);
-    const uint32_t ns4 = (L.total - L.soft) / 16;
-    for (uint32_t i = tid; i < ns4; i += blockDim.x) {
-      p4[i] = make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
-    }
-    const uint32_t nx8 = (K - D.nof_filler_bits) / 8;
-    for (uint32_t i = tid; i < nx8; i += blockDim.x) {
-      x8[i] = tab->crc_x8[D.crc_type][i];
     }
     if (tid == 0) {
       s_nsig = 0;
@@ -941,12 +976,16 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #ifdef FEC_PROFILE
   tp1 = clock64();
 #endif
-  // ---- stage 1: soft bits into shared memory -----------------------------------------------------------------------------
-  const fec_soft_store_packed store{soft, Z, H, invZ};
+  // ---- stage 1: the soft buffer (rate dematching + HARQ combining), or the decoder input as given --------------------------
+  const fec_soft_store_packed store{soft16, Z, H, invZ};
+  const int8_t*               harq = nullptr;
   if (D.mode == FEC_MODE_DECODE) {
     const uint32_t n_in   = D.E;
     const uint32_t n_node = (n_in / Z) * Z; // full nodes are clamped to +-64, a partial last node is copied as it is
     uint32_t       my_sig = 0;
+    for (uint32_t i = tid; i < Z; i += blockDim.x) {
+      reinterpret_cast<uint32_t*>(soft16)[i] = 0; // the two punctured columns
+    }
     for (uint32_t o = tid; o < N; o += blockDim.x) {
       int vv = 0;
       if (o < n_in) {
@@ -965,9 +1004,10 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
       atomicMax(&s_nsig, my_sig);
     }
   } else {
-    int8_t* harq = harq_base + (size_t)D.harq_slot * FEC_HARQ_SLOT_BYTES;
-    fec_dematch_packed(D, in, harq, (D.mode == FEC_MODE_CHAIN) ? soft : nullptr, H, reinterpret_cast<int8_t*>(state),
-                       L.edges - L.state, &s_nsig);
+    int8_t* hq = harq_base + (size_t)D.harq_slot * FEC_HARQ_SLOT_BYTES;
+    harq       = hq;
+    // the soft-bit area is the staging area of the dematcher: the decoder's copy is filled afterwards
+    fec_dematch_packed(D, in, hq, reinterpret_cast<int8_t*>(soft16), L.total - L.soft, &s_nsig);
     if (D.mode == FEC_MODE_DEMATCH) {
       if (tid == 0) {
         res.status  = FEC_RES_DONE;
@@ -1000,28 +1040,37 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   cbl          = ((cbl + Z - 1) / Z) * Z;
   const uint32_t nlayers = cbl / Z - Kb;
   const uint32_t T       = K - D.nof_filler_bits;
-  // Tensor-memory home of this warp's check state: lane quadrant of the warp, 64 columns per group of four warps.
-  const uint32_t row_tm  = fec_packed_first_tmem_row(bg1);
-  const uint32_t tm_row0 = tmem_base + ((((tid >> 5) & 3u) * 32u) << 16) + (tid >> 7) * FEC_PACKED_TMEM_COLS_PER_WARPSLOT;
+  // Tensor-memory home of this warp's check state: lane quadrant of the warp, one column slot per group of four warps.
+  const uint32_t row_b = fec_packed_row_b(bg1), row_a = fec_packed_row_a(bg1);
+  const uint32_t tm_q  = (((tid >> 5) & 3u) * 32u) << 16;
+  const uint32_t tm_a  = tmem_a + tm_q + (tid >> 7) * FEC_PACKED_TMEM_A_COLS;
+  const uint32_t tm_b  = tmem_b + tm_q + (tid >> 7) * FEC_PACKED_TMEM_B_COLS;
+  if (harq != nullptr) {
+    // every staged LLR has been consumed (barrier above): the decoder's soft bits, columns of the layers in use only
+    fec_soft_fill_from_harq(harq, soft16, cbl - 2 * Z, Z, H, invZ);
+  }
   {
-    // The check state doubles as the dematcher's staging area: clear the rows in use ("no c2v messages yet").
+    // Clear the check state of the rows in use ("no c2v messages yet"): shared memory, region B, region A.
     uint4*         s4 = reinterpret_cast<uint4*>(state);
-    const uint32_t n4 = ((uint32_t)soff[min(nlayers, row_tm)] * H * 4 + 15) / 16;
+    const uint32_t nw = (nlayers >= row_b) ? fec_packed_state_words(bg1) : (uint32_t)soff[nlayers];
+    const uint32_t n4 = (nw * H * 4 + 15) / 16;
     for (uint32_t i = tid; i < n4; i += blockDim.x) {
       s4[i] = make_uint4(0, 0, 0, 0);
     }
-    // ... and the tensor-memory rows in use, eight columns per store (every thread clears its own lane)
-    if (nlayers > row_tm) {
-      for (uint32_t c = 0; c < 2u * (nlayers - row_tm); c += 8) {
-        tmem_st8_zero(tm_row0 + c);
+    if (nlayers > row_b) { // every thread clears its own lane, eight columns per store
+      tmem_st8_zero(tm_b);
+      tmem_st8_zero(tm_b + 8);
+      for (uint32_t c = 0; nlayers > row_a && c < 2u * (nlayers - row_a); c += 8) {
+        tmem_st8_zero(tm_a + c);
       }
       tmem_wait_st();
     }
   }
-  const uint32_t crc_poly = tab->crc_poly[D.crc_type], crc_top = 1u << tab->crc_len[D.crc_type];
+  const uint32_t* x8       = tab->crc_x8[D.crc_type];
+  const uint32_t  crc_poly = tab->crc_poly[D.crc_type], crc_top = 1u << tab->crc_len[D.crc_type];
   __syncthreads();
   const uint32_t smul = ptab->scale_mul, sadd = ptab->scale_add;
-  const uint32_t soft_s = (uint32_t)__cvta_generic_to_shared(soft);
+  const uint32_t soft_s = (uint32_t)__cvta_generic_to_shared(soft16);
 
 #ifdef FEC_PROFILE
   tp2 = clock64();
@@ -1029,10 +1078,10 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
-    fec_packed_iteration(soft_s, state, edges, soff, rs, deg, H, nlayers, smul, sadd, row_tm, tm_row0);
+    fec_packed_iteration(soft_s, state, edges, soff, rs, deg, H, nlayers, smul, sadd, row_b, row_a, tm_b, tm_a);
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     if (early_stop) {
-      const bool clean = fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
+      const bool clean = fec_hard_bits_packed(soft16, bitsw, K, Z, H, invZ);
       const bool crc   = fec_crc_ok_packed(bitsw, T, x8, crc_poly, crc_top, red);
       if (clean && crc) {
         pass = true;
@@ -1045,7 +1094,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   tp3 = clock64();
 #endif
   if (!early_stop) {
-    fec_hard_bits_packed(soft, bitsw, K, Z, H, invZ);
+    fec_hard_bits_packed(soft16, bitsw, K, Z, H, invZ);
     pass = fec_crc_ok_packed(bitsw, T, x8, crc_poly, crc_top, red) && !(D.flags & FEC_FLAG_NO_CRC);
   }
   if ((reinterpret_cast<uintptr_t>(out) & 3u) == 0) {
@@ -1088,27 +1137,32 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
                      const fec_packed_tables* __restrict__ ptab)
 {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  __shared__ uint32_t s_tmem_base;
+  __shared__ uint32_t s_tmem_base[2];
   const fec_cb_desc D = descs[blockIdx.x];
   if (!fec_packed_cb_supported(D)) {
     fec_generic_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab);
     return;
   }
-  // Tensor memory for the check state of the last 32 base rows: 64 columns per group of four warps (3 resident CTAs of
-  // six warps take 3 x 128 of the SM's 512 columns; smaller CTAs take 64 each). One warp allocates and later frees.
-  const uint32_t tm_cols = (blockDim.x > 128) ? 2u * FEC_PACKED_TMEM_COLS_PER_WARPSLOT : FEC_PACKED_TMEM_COLS_PER_WARPSLOT;
+  // Tensor memory for the check state (see the layout notes at the top): region A takes 64 columns per group of four warps,
+  // region B 16 (allocations are powers of two >= 32). Three resident CTAs of six warps take 3 x (128 + 32) of the SM's 512
+  // columns. One warp allocates and later frees.
+  const uint32_t slots  = (blockDim.x > 128) ? 2u : 1u;
+  const uint32_t cols_a = slots * FEC_PACKED_TMEM_A_COLS, cols_b = 32u;
   if (threadIdx.x < 32) {
-    tmem_alloc((uint32_t)__cvta_generic_to_shared(&s_tmem_base), tm_cols);
+    tmem_alloc((uint32_t)__cvta_generic_to_shared(&s_tmem_base[0]), cols_a);
+    tmem_alloc((uint32_t)__cvta_generic_to_shared(&s_tmem_base[1]), cols_b);
+    tmem_relinquish();
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_base = s_tmem_base;
-  fec_packed_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab, ptab, tmem_base);
+  const uint32_t tmem_a = s_tmem_base[0], tmem_b = s_tmem_base[1];
+  fec_packed_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab, ptab, tmem_a, tmem_b);
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (threadIdx.x < 32) {
-    tmem_dealloc(tmem_base, tm_cols);
+    tmem_dealloc(tmem_a, cols_a);
+    tmem_dealloc(tmem_b, cols_b);
   }
 }
 
@@ -1140,13 +1194,23 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
       off += fec_packed_row_words(t.deg[bg][m]);
     }
     pt.state_off[bg][M] = (uint16_t)off;
-    const uint32_t row_tm = fec_packed_first_tmem_row(bg == 0);
-    if (pt.state_off[bg][row_tm] != fec_packed_state_words(bg == 0)) {
+    // Rows in shared memory: word offset (above). Region B rows: column offset inside the region. Region A rows: two
+    // columns each (the kernel computes 2 (row - row_a) itself).
+    const uint32_t row_b = fec_packed_row_b(bg == 0), row_a = fec_packed_row_a(bg == 0);
+    if (pt.state_off[bg][row_b] != fec_packed_state_words(bg == 0)) {
       return false;
     }
-    for (uint32_t m = row_tm; m < (uint32_t)M; ++m) {
+    uint32_t boff = 0;
+    for (uint32_t m = row_b; m < row_a; ++m) {
+      pt.state_off[bg][m] = (uint16_t)boff;
+      boff += fec_packed_row_words(t.deg[bg][m]);
+    }
+    if (boff > FEC_PACKED_TMEM_B_COLS) {
+      return false;
+    }
+    for (uint32_t m = row_a; m < (uint32_t)M; ++m) {
       if (t.deg[bg][m] > 8) {
-        return false; // tensor-memory rows hold two state words
+        return false; // region A rows hold two state words
       }
     }
     const int ne = t.row_start[bg][M];
@@ -1160,8 +1224,8 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
         const uint32_t   s = t.shift[bg * 51 + zi][i], col = t.col[bg][i];
         const uint32_t   q = s / H, r = s % H;
         fec_packed_edge& e = pt.edges[bg * 51 + zi][i];
-        e.aN  = (col * H + r) * 2 + (q & 1);
-        e.aW  = (col * H + r - H) * 2 + ((q + 1) & 1); // only used by threads t >= H - r, so t + r - H >= 0
+        e.aN  = (col * H + r) * 4 + 2 * (q & 1);
+        e.aW  = (col * H + r - H) * 4 + 2 * ((q + 1) & 1); // only used by threads t >= H - r, so t + r - H >= 0
         e.thr = H - r;
         e.pad = 0;
       }

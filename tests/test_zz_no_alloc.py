@@ -40,7 +40,7 @@ def _one_call(fec, eng, orc, oracle, params, seed):
     for j in range(n):
         c, _ = fec.tb_segment(d[j:j + 1])
         c["llr_offset"] += np.uint64(lo[j])
-        c["harq_slot"] = 1000 + len(cbs) * 8 + np.arange(c.size)
+        c["harq_slot"] = 1000 + len(cbs) * 32 + np.arange(c.size)  # disjoint slots: at most 11 codeblocks per block here
         cbs.append(c)
     cb = np.concatenate(cbs)
     cb["out_offset"] = np.arange(cb.size) * fec.MAX_CB_OUT_BYTES
