@@ -458,6 +458,9 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   {
     fec_packed_tables* hp = new (std::nothrow) fec_packed_tables();
     e->packed_ok          = fec_packed_build_tables(*hp, *h, FEC_ALL_Z);
+    uint32_t rowinfo[2][48];
+    e->packed_ok = e->packed_ok && fec_packed_build_rowinfo(rowinfo, *h, *hp);
+    CU_TRY(cudaMemcpyToSymbol(fec_c_rowinfo, rowinfo, sizeof(rowinfo))); // constant memory of this device: the row schedule
     CU_TRY(cudaMalloc((void**)&e->d_ptab, sizeof(fec_packed_tables)));
     CU_TRY(cudaMemcpy(e->d_ptab, hp, sizeof(fec_packed_tables), cudaMemcpyHostToDevice));
     delete hp;

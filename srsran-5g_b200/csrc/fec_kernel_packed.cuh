@@ -28,10 +28,15 @@
 
 #define FEC_PACKED_MAX_THREADS 192
 
+// Edge (shift s = q * H + r into column col): thread t reads pair word (t + r) mod H of the column; its lanes come swapped
+// when q + [t + r >= H] is odd. The wrap is ONE unsigned min: with u = 4 t + c0 (negative, i.e. huge, while t + r < H),
+//   rel = min(u + c1, u)   is the byte offset of the pair word inside the column, plus 2 if the lanes come swapped,
+// (VIADDMNMX.U32) and the byte address is rel + base. Bit 1 of the address is the swap bit PRMT.F4E consumes; the access
+// itself uses the address with that bit cleared.
 struct fec_packed_edge {
-  uint32_t aN;  // thread 0, no wrap: byte offset of pair word col * H + r, plus 2 if the lanes come swapped (q odd)
-  uint32_t aW;  // threads that wrap around the column: pair word col * H + r - H, plus 2 if q + 1 is odd
-  uint32_t thr; // H - r : threads t >= thr wrap
+  uint32_t c0;   // 4 (r - H) + 2 ((q + 1) & 1)                      : offset of a thread that wraps
+  uint32_t c1;   // 4 H + 2 (q & 1) - 2 ((q + 1) & 1)                : what a thread that does not wrap adds to it
+  uint32_t base; // 4 col H (the kernel adds the shared-window address of the soft array while staging the records)
   uint32_t pad;
 };
 
@@ -44,7 +49,7 @@ struct fec_packed_tables {
 };
 
 struct fec_packed_smem_layout {
-  uint32_t state, edges, soff, rs, deg, bitsw, red, soft, total;
+  uint32_t state, edges, bitsw, red, soft, total;
 };
 
 __host__ __device__ inline uint32_t fec_packed_row_words(uint32_t d)
@@ -90,12 +95,6 @@ __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, 
   o       = (o + 15) & ~15u;
   L.edges = o;
   o += ne * 16;
-  L.soff = o;
-  o += 48 * 2;
-  L.rs = o;
-  o += 48 * 2;
-  L.deg = o;
-  o += 48;
   L.bitsw = o;
   o += ((Kb * Z + 31) / 32 + 1) * 4;
   L.red = o;
@@ -120,6 +119,12 @@ __device__ __forceinline__ uint32_t h2_fma(uint32_t a, uint32_t b, uint32_t c)
 {
   uint32_t r;
   asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t h2_sub(uint32_t a, uint32_t b)
+{
+  uint32_t r;
+  asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
   return r;
 }
 // min(|a|, |b|) with sign(a) ^ sign(b)
@@ -282,13 +287,13 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
                                                uint32_t               scale_mul,
                                                uint32_t               scale_add)
 {
-  constexpr int  NW = (D <= 8) ? 2 : 3;
-  const uint32_t tb = soft_s + t * 4;
+  constexpr int  NW   = (D <= 8) ? 2 : 3;
+  const uint32_t t4   = t * 4;
 
   // ---- pre-phase: everything that does not depend on the soft bits (addresses, the previous c2v messages of this row).
   // It runs BEFORE the CTA barrier that orders this row after the previous one, so warps that finished the previous row
   // early do useful work instead of waiting, and the table / state load latency overlaps the other warps' tail.
-  uint32_t a0[D], cneg[D];
+  uint32_t a0[D], cneg[D]; // a0: byte address of the pair word, bit 1 = swap bit
   {
     uint32_t w0, w1, w2 = 0;
     if (TM) {
@@ -307,11 +312,12 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     }
 #pragma unroll
     for (int e = 0; e < D; ++e) {
-      const uint4 E = *reinterpret_cast<const uint4*>(&ed[e]);
-      a0[e]         = imad((t >= E.z) ? E.y : E.x, 1u, tb); // the add on the FMA pipe: the ALU pipe is the busier one
+      const uint4    E = *reinterpret_cast<const uint4*>(&ed[e]);
+      const uint32_t u = imad(t4, 1u, E.x);               // the adds on the FMA pipe: the ALU pipe is the busier one
+      a0[e]            = imad(min(u + E.y, u), 1u, E.z);  // VIADDMNMX.U32: the cyclic wrap and the swap bit in one
     }
     const uint32_t om1 = __byte_perm(w0, 0, 0x4140), om2 = __byte_perm(w0, 0, 0x4342);
-    const uint32_t odl = h2_add(om2, om1 ^ H2_SIGN); // m2 - m1 >= 0
+    const uint32_t odl = h2_sub(om2, om1); // m2 - m1 >= 0
     const uint32_t oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 16) ? w2 : __byte_perm(w2, 0, 0x4341));
 #pragma unroll
     for (int e = 0; e < D; ++e) {
@@ -348,10 +354,10 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   // ---- scale the two minima: scaled = (x * mul + add) >> 8, both lanes in one 32-bit multiply -----------------------------
   const uint32_t sp  = m1 & H2_SIGN; // product of all v2c signs
   const uint32_t a1  = m1 & H2_ABS;
-  const uint32_t s1  = FEC_SHR(imad(a1, scale_mul, scale_add), 8) & 0x00ff00ffu;
-  const uint32_t s2  = FEC_SHR(imad(m2 & H2_ABS, scale_mul, scale_add), 8) & 0x00ff00ffu;
+  const uint32_t s1  = __byte_perm(imad(a1, scale_mul, scale_add), 0, 0x4341); // byte 1 of each lane = (.) >> 8
+  const uint32_t s2  = __byte_perm(imad(m2 & H2_ABS, scale_mul, scale_add), 0, 0x4341);
   const uint32_t M1s = s1 | sp;
-  const uint32_t dls = h2_add(s2, s1 ^ H2_SIGN) | sp;
+  const uint32_t dls = h2_sub(s2, s1) | sp;
 
   // ---- phase B: new check-to-variable messages, soft-bit update, write-back ------------------------------------------------
   uint32_t nid = 0, sg1 = 0, sg2 = 0;
@@ -401,54 +407,64 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   }
 }
 
+// ---- the row schedule of a base graph -------------------------------------------------------------------------------------
+// One word per base row in CONSTANT memory (filled by the engine at creation, read through the uniform datapath):
+//   bits 0-8 first edge of the row, bits 9-16 state offset (shared memory: in units of H words; region B: column inside the
+//   region; region A: 2 (row - first row of A)), bits 17-20 which instantiation of the row body runs it (below).
+// (A fully unrolled schedule -- one straight run of 46 row bodies, 150 KB of code -- was measured: 3 % faster when the three
+// codeblocks of an SM run in lockstep, 30 % slower when they do not, as with early stop, because their instruction streams
+// then compete for the 32 KB L1.5 instruction cache. The loop keeps the hot code at 13 row bodies.)
+__constant__ uint32_t fec_c_rowinfo[2][48];
+
+enum { // instantiation codes: tensor-memory rows of degree 3..10, then the shared-memory rows
+  FEC_ROW_T3 = 0, FEC_ROW_T4, FEC_ROW_T5, FEC_ROW_T6, FEC_ROW_T7, FEC_ROW_T8, FEC_ROW_T9, FEC_ROW_T10,
+  FEC_ROW_S3, FEC_ROW_S8, FEC_ROW_S9, FEC_ROW_S10, FEC_ROW_S19, FEC_ROW_NONE
+};
+
 // One decoder iteration over the layers in use. Out of line on purpose: ptxas allocates registers for the row code on its
 // own, so changes to the dematcher or the tail cannot perturb the schedule of the hot loop (and vice versa).
 __device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
                                                   uint32_t*              state,
                                                   const fec_packed_edge* edges,
-                                                  const uint16_t*        soff,
-                                                  const uint16_t*        rs,
-                                                  const uint8_t*         deg,
+                                                  uint32_t               bg, // 0 = BG1, 1 = BG2
                                                   uint32_t               H,
                                                   uint32_t               nlayers,
                                                   uint32_t               smul,
                                                   uint32_t               sadd,
-                                                  uint32_t               row_b, // first base row of tensor-memory region B
-                                                  uint32_t               row_a, // first base row of tensor-memory region A
-                                                  uint32_t               tm_b,  // this warp's address of region B / A
+                                                  uint32_t               tm_b, // this warp's address of region B / A
                                                   uint32_t               tm_a)
 {
   const uint32_t tid = threadIdx.x;
+  if ((tid & ~31u) >= H) {
+    for (uint32_t l = 0; l < nlayers; ++l) {
+      asm volatile("bar.sync 0;" ::: "memory"); // warps without work still take part in the row barriers
+    }
+    return;
+  }
+  // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores; their own, identical
+  // copy of the tensor-memory state) so that whole warps reach the barrier inside the row function.
+  const uint32_t tq  = min(tid, H - 1);
+  uint32_t*      stq = state + tq;
+  const uint32_t row_a = (bg ? 42u : 46u) - FEC_PACKED_TMEM_A_ROWS;
   for (uint32_t l = 0; l < nlayers; ++l) {
-    if ((tid & ~31u) >= H) {
-      asm volatile("bar.sync 0;" ::: "memory"); // warps without work still take part in the row barrier
-    } else {
-      // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores; their own, identical
-      // copy of the tensor-memory state) so that whole warps reach the barrier inside the row function.
-      const uint32_t         tq = min(tid, H - 1);
-      const fec_packed_edge* ed = edges + rs[l];
-      if (l >= row_b) {
-        const uint32_t ta = (l >= row_a) ? tm_a + 2u * (l - row_a) : tm_b + soff[l];
-        switch (deg[l]) {
-          case 3: fec_packed_row<3, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          case 4: fec_packed_row<4, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          case 5: fec_packed_row<5, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          case 6: fec_packed_row<6, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          case 7: fec_packed_row<7, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          case 8: fec_packed_row<8, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          case 9: fec_packed_row<9, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-          default: fec_packed_row<10, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-        }
-      } else {
-        uint32_t* st = state + (uint32_t)soff[l] * H + tq;
-        switch (deg[l]) { // the degrees of the rows kept in shared memory: BG1 19,19,19,19,3,8,9; BG2 8,10,8
-          case 3: fec_packed_row<3, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          case 8: fec_packed_row<8, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          case 9: fec_packed_row<9, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          case 10: fec_packed_row<10, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-          default: fec_packed_row<19, false>(soft_s, st, 0u, ed, H, tq, smul, sadd); break;
-        }
-      }
+    const uint32_t         info = fec_c_rowinfo[bg][l];
+    const fec_packed_edge* ed   = edges + (info & 0x1ffu);
+    const uint32_t         so   = (info >> 9) & 0xffu;
+    const uint32_t         ta   = ((l >= row_a) ? tm_a : tm_b) + so;
+    switch (info >> 17) {
+      case FEC_ROW_T3: fec_packed_row<3, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_T4: fec_packed_row<4, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_T5: fec_packed_row<5, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_T6: fec_packed_row<6, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_T7: fec_packed_row<7, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_T8: fec_packed_row<8, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_T9: fec_packed_row<9, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_T10: fec_packed_row<10, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_S3: fec_packed_row<3, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_S8: fec_packed_row<8, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_S9: fec_packed_row<9, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
+      case FEC_ROW_S10: fec_packed_row<10, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
+      default: fec_packed_row<19, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
     }
   }
 }
@@ -941,24 +957,19 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   const fec_packed_smem_layout L = fec_packed_layout(Z, bg1);
   uint32_t*        state  = reinterpret_cast<uint32_t*>(smem_raw + L.state);
   fec_packed_edge* edges  = reinterpret_cast<fec_packed_edge*>(smem_raw + L.edges);
-  uint16_t*        soff   = reinterpret_cast<uint16_t*>(smem_raw + L.soff);
-  uint16_t*        rs     = reinterpret_cast<uint16_t*>(smem_raw + L.rs);
-  uint8_t*         deg    = smem_raw + L.deg;
   uint32_t*        bitsw  = reinterpret_cast<uint32_t*>(smem_raw + L.bitsw);
   uint32_t*        red    = reinterpret_cast<uint32_t*>(smem_raw + L.red);
   uint16_t*        soft16 = reinterpret_cast<uint16_t*>(smem_raw + L.soft);
 
   // Stage the graph of this codeblock.
   {
-    const uint4* src = reinterpret_cast<const uint4*>(ptab->edges[D.graph_index]);
-    uint4*       dst = reinterpret_cast<uint4*>(edges);
+    const uint4*   src     = reinterpret_cast<const uint4*>(ptab->edges[D.graph_index]);
+    uint4*         dst     = reinterpret_cast<uint4*>(edges);
+    const uint32_t soft_sw = (uint32_t)__cvta_generic_to_shared(soft16);
     for (uint32_t i = tid; i < ne; i += blockDim.x) {
-      dst[i] = src[i];
-    }
-    for (uint32_t i = tid; i <= M; i += blockDim.x) {
-      rs[i]   = tab->row_start[bg1 ? 0 : 1][i];
-      deg[i]  = tab->deg[bg1 ? 0 : 1][i];
-      soff[i] = ptab->state_off[bg1 ? 0 : 1][i];
+      uint4 E = src[i];
+      E.z += soft_sw; // column base as a shared-window address
+      dst[i] = E;
     }
     if (tid == 0) {
       s_nsig = 0;
@@ -1052,7 +1063,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   {
     // Clear the check state of the rows in use ("no c2v messages yet"): shared memory, region B, region A.
     uint4*         s4 = reinterpret_cast<uint4*>(state);
-    const uint32_t nw = (nlayers >= row_b) ? fec_packed_state_words(bg1) : (uint32_t)soff[nlayers];
+    const uint32_t nw = (nlayers >= row_b) ? fec_packed_state_words(bg1) : ((fec_c_rowinfo[bg1 ? 0 : 1][nlayers] >> 9) & 0xffu);
     const uint32_t n4 = (nw * H * 4 + 15) / 16;
     for (uint32_t i = tid; i < n4; i += blockDim.x) {
       s4[i] = make_uint4(0, 0, 0, 0);
@@ -1078,7 +1089,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
-    fec_packed_iteration(soft_s, state, edges, soff, rs, deg, H, nlayers, smul, sadd, row_b, row_a, tm_b, tm_a);
+    fec_packed_iteration(soft_s, state, edges, bg1 ? 0u : 1u, H, nlayers, smul, sadd, tm_b, tm_a);
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     if (early_stop) {
       const bool clean = fec_hard_bits_packed(soft16, bitsw, K, Z, H, invZ);
@@ -1169,6 +1180,33 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
 // ---- host side ---------------------------------------------------------------------------------------------------------
 // Fills the packed tables from the generic ones. Returns false if the scaling LUT cannot be written as
 // (x * mul + add) >> 8 on 0..120 (then the engine keeps to the generic kernel).
+// Row schedule words for fec_c_rowinfo (see there). Returns false if a row has no instantiation of the row body.
+static inline bool fec_packed_build_rowinfo(uint32_t (*info)[48], const fec_dev_tables& t, const fec_packed_tables& pt)
+{
+  for (int bg = 0; bg < 2; ++bg) {
+    const uint32_t M = bg ? 42 : 46, row_b = fec_packed_row_b(bg == 0), row_a = fec_packed_row_a(bg == 0);
+    for (uint32_t m = 0; m < 48; ++m) {
+      info[bg][m] = 0;
+    }
+    for (uint32_t m = 0; m < M; ++m) {
+      const uint32_t d = t.deg[bg][m];
+      uint32_t       code = FEC_ROW_NONE, so = pt.state_off[bg][m];
+      if (m >= row_b) {
+        code = (d >= 3 && d <= 10) ? FEC_ROW_T3 + (d - 3) : FEC_ROW_NONE;
+        so   = (m >= row_a) ? 2 * (m - row_a) : so;
+      } else {
+        code = (d == 3) ? FEC_ROW_S3 : (d == 8) ? FEC_ROW_S8 : (d == 9) ? FEC_ROW_S9 : (d == 10) ? FEC_ROW_S10 :
+               (d == 19) ? FEC_ROW_S19 : FEC_ROW_NONE;
+      }
+      if (code == FEC_ROW_NONE || so > 0xff || t.row_start[bg][m] > 0x1ff) {
+        return false;
+      }
+      info[bg][m] = t.row_start[bg][m] | (so << 9) | (code << 17);
+    }
+  }
+  return true;
+}
+
 static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_tables& t, const uint16_t* all_z)
 {
   memset(&pt, 0, sizeof(pt));
@@ -1200,6 +1238,7 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
     if (pt.state_off[bg][row_b] != fec_packed_state_words(bg == 0)) {
       return false;
     }
+
     uint32_t boff = 0;
     for (uint32_t m = row_b; m < row_a; ++m) {
       pt.state_off[bg][m] = (uint16_t)boff;
@@ -1224,10 +1263,10 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
         const uint32_t   s = t.shift[bg * 51 + zi][i], col = t.col[bg][i];
         const uint32_t   q = s / H, r = s % H;
         fec_packed_edge& e = pt.edges[bg * 51 + zi][i];
-        e.aN  = (col * H + r) * 4 + 2 * (q & 1);
-        e.aW  = (col * H + r - H) * 4 + 2 * ((q + 1) & 1); // only used by threads t >= H - r, so t + r - H >= 0
-        e.thr = H - r;
-        e.pad = 0;
+        e.c0   = 4u * r - 4u * H + 2u * ((q + 1) & 1); // modulo 2^32
+        e.c1   = 4u * H + 2u * (q & 1) - 2u * ((q + 1) & 1);
+        e.base = 4u * col * H;
+        e.pad  = 0;
       }
     }
   }
