@@ -293,7 +293,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   // ---- pre-phase: everything that does not depend on the soft bits (addresses, the previous c2v messages of this row).
   // It runs BEFORE the CTA barrier that orders this row after the previous one, so warps that finished the previous row
   // early do useful work instead of waiting, and the table / state load latency overlaps the other warps' tail.
-  uint32_t a0[D], cneg[D]; // a0: byte address of the pair word, bit 1 = swap bit
+  uint32_t a0[D], cold[D]; // a0: byte address of the pair word, bit 1 = swap bit
   {
     uint32_t w0, w1, w2 = 0;
     if (TM) {
@@ -318,16 +318,21 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     }
     const uint32_t om1 = __byte_perm(w0, 0, 0x4140), om2 = __byte_perm(w0, 0, 0x4342);
     const uint32_t odl = h2_sub(om2, om1); // m2 - m1 >= 0
-    const uint32_t oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 16) ? w2 : __byte_perm(w2, 0, 0x4341));
+    // state words: D <= 8: w1 = sign bits 0..7 | index << 8; D = 9, 10: w1 = sign bits 0..9, w2 = index;
+    // D = 19: w1 = sign bits of edges 0..9, w2 = sign bits of edges 10..18 | index << 9 (all per 16-bit lane)
+    const uint32_t oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 10) ? w2 : ((w2 >> 9) & 0x001f001fu));
 #pragma unroll
     for (int e = 0; e < D; ++e) {
-      const uint32_t sw  = (e < 16) ? w1 : w2;
+      const uint32_t sw  = (e < 10) ? w1 : w2;
       const uint32_t ism = h2_eq_bf(oid, FEC_H2(e));                   // edge e was the min1 edge
       const uint32_t mag = h2_fma(ism, odl, om1);                      // |old c2v|
-      const uint32_t sgs = imad(sw, 1u << (15 - (e & 15)), 0u);        // its sign bits at 15 / 31
-      cneg[e]            = mag ^ (~sgs & H2_SIGN);                     // -(old c2v)
+      const uint32_t sgs = imad(sw, 1u << (15 - (e % 10)), 0u);        // its sign bits at 15 / 31
+      cold[e]            = mag ^ (sgs & H2_SIGN);                      // old c2v (one LOP3; the subtraction negates for free)
     }
   }
+  // Orders this row after the rows that wrote the columns it reads. (In the extension part of both base graphs every other
+  // row shares no column with its predecessor and could skip the barrier; measured: 1.5 % SLOWER -- the six warps of a
+  // codeblock drift apart and run different row bodies, which costs more in the instruction cache than the barrier does.)
   asm volatile("bar.sync 0;" ::: "memory");
 
   // ---- phase A: variable-to-check messages and the min1 / min2 / sign-product analysis -----------------------------------
@@ -341,7 +346,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   uint32_t m1 = H2_P120, m2 = H2_P120;
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint32_t vraw = h2_add(S[e], cneg[e]);                                     // soft - c2v
+    const uint32_t vraw = h2_sub(S[e], cold[e]);                                     // soft - c2v
     const uint32_t y    = h2_add(h2_fma(S[e], H2_F4352, H2_F96), H2_FM96);           // nonzero, sign of S, iff |S| > 120
     const uint32_t vcl  = h2_min_xs(vraw, H2_P120);                                  // saturate at +-120
     const uint32_t vv   = h2_fma(y, H2_F2M11, vcl);                                  // "infinite" soft bits stay huge
@@ -369,12 +374,13 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     const uint32_t c  = mg ^ (vv & H2_SIGN);             // new c2v
     nid               = h2_fma(eq, FEC_H2(e), nid);      // index of the min1 edge (any value if min1 == min2)
     const uint32_t tt = h2_add(c, vv);                   // c2v + v2c: above 120 in magnitude it IS the "infinity" from here on
-    // sign(v2c) of the two lanes -> bit (e & 15) of the sign word
-    const uint32_t sh = ((e & 15) == 15) ? vv : FEC_SHR(vv, 15 - (e & 15));
-    if (e < 16) {
-      sg1 |= sh & (0x00010001u << (e & 15));
+    // sign(v2c) of the two lanes -> bit (e % 10) of the sign word (gathering them on the FMA pipe instead -- HSET2 + HFMA2 into
+    // a 1024.0-biased accumulator -- was measured: no difference)
+    const uint32_t sh = FEC_SHR(vv, 15 - (e % 10));
+    if (e < 10) {
+      sg1 |= sh & (0x00010001u << (e % 10));
     } else {
-      sg2 |= sh & (0x00010001u << (e & 15));
+      sg2 |= sh & (0x00010001u << (e % 10));
     }
     sts_u32(a0[e] & ~2u, prmt_f4e(tt, tt, a0[e]));
   }
@@ -385,12 +391,12 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   uint32_t       nw1, nw2 = 0;
   if (D <= 8) {
     nw1 = ((sg1 ^ pm) & 0x00ff00ffu) | (nid << 8);
-  } else if (D <= 16) {
-    nw1 = sg1 ^ pm;
+  } else if (D <= 10) {
+    nw1 = (sg1 ^ pm) & 0x03ff03ffu;
     nw2 = nid;
   } else {
-    nw1 = sg1 ^ pm;
-    nw2 = ((sg2 ^ pm) & 0x00070007u) | (nid << 8);
+    nw1 = (sg1 ^ pm) & 0x03ff03ffu;
+    nw2 = ((sg2 ^ pm) & 0x01ff01ffu) | (nid << 9);
   }
   if (TM) {
     if (NW == 3) {
@@ -451,7 +457,7 @@ __device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
     const fec_packed_edge* ed   = edges + (info & 0x1ffu);
     const uint32_t         so   = (info >> 9) & 0xffu;
     const uint32_t         ta   = ((l >= row_a) ? tm_a : tm_b) + so;
-    switch (info >> 17) {
+    switch ((info >> 17) & 15u) {
       case FEC_ROW_T3: fec_packed_row<3, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
       case FEC_ROW_T4: fec_packed_row<4, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
       case FEC_ROW_T5: fec_packed_row<5, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
@@ -945,7 +951,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 
   const uint32_t Z = D.lifting_size, H = Z / 2;
   const int      bg1 = (D.base_graph == 1);
-  const uint32_t Kb = bg1 ? 22u : 10u, nfull = bg1 ? 68u : 52u, M = bg1 ? 46u : 42u;
+  const uint32_t Kb = bg1 ? 22u : 10u, nfull = bg1 ? 68u : 52u;
   const uint32_t K = Kb * Z, N = (nfull - 2) * Z;
   const uint32_t ne = bg1 ? 316u : 197u;
   const uint32_t invZ = 0xffffffffu / Z + 1;
