@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 6
+#define FEC_B200_ABI_VERSION 7
 
 typedef enum {
   FEC_OK             = 0,
@@ -114,6 +114,13 @@ typedef struct fec_engine_cfg {
   float    scaling_factor;  /* normalised min-sum factor, 0 < sf < 1 (reference default 0.8)                          */
   uint32_t kernel_variant;  /* 0 = auto; 1 = force the generic one-thread-per-check kernel (debug / A-B comparison)   */
   uint32_t reserved;
+  uint32_t host_contexts;   /* host-buffer calls (fec_run_host, fec_tb_run_host) that run concurrently, each on its own  */
+                            /* streams and staging = asynchronous transport-block calls in flight; 0 = 4               */
+  uint32_t queue_batch_cbs; /* codeblocks per queue batch (a batch is dispatched when it is full or on flush);          */
+                            /* 0 = max_batch_cbs. Small values start the GPU while the consumer is still enqueuing.     */
+  uint32_t queue_batches;   /* batches a queue can have staged / in flight (ring depth); 0 = 4                          */
+  uint32_t max_wait_us;     /* cross-queue batcher: a dispatch that holds less than one kernel wave of codeblocks waits  */
+                            /* up to this long for batches of other queues to join its launch; 0 = never wait           */
 } fec_engine_cfg;
 
 #define FEC_HARQ_SLOT_BYTES 25344u /* 66 * 384, the largest codeblock; slots are contiguous in HBM                    */
@@ -133,6 +140,29 @@ void*       fec_engine_stream(fec_engine* e);
 void*       fec_harq_slot_ptr(fec_engine* e, uint32_t slot);
 /* Number of kernels this engine has launched so far (bench.py's gpu_launches). */
 uint64_t    fec_engine_launch_count(fec_engine* e);
+
+/* Engine counters since creation (the reference's per-decoder metrics -- include/srsran/phy/metrics/phy_metrics_reports.h:70-79,
+ * lib/phy/metrics/phy_metrics_ldpc_decoder_decorator.h:34-71 -- kept inside the engine, plus what only a batching engine has). */
+#define FEC_STATS_ITER_BINS 16
+typedef struct fec_engine_stats {
+  uint64_t launches;         /* kernels of any kind                                                                     */
+  uint64_t cb_launches;      /* launches of the codeblock kernel                                                        */
+  uint64_t codeblocks;       /* codeblock operations launched; codeblocks / cb_launches = mean batch occupancy          */
+  uint64_t results;          /* codeblock results harvested by the host entry points                                   */
+  uint64_t crc_pass;         /* of those, CRC passed                                                                    */
+  uint64_t iterations_hist[FEC_STATS_ITER_BINS]; /* their nof_ldpc_iterations (last bin: that many or more)              */
+  uint64_t queue_full;       /* enqueue calls refused with FEC_ERR_QUEUE_FULL                                           */
+  uint64_t max_queue_depth;  /* largest number of operations staged or in flight in one queue                           */
+  uint64_t dispatches;       /* cross-queue batcher: launches, and the queue batches they carried                       */
+  uint64_t dispatch_batches;
+  uint64_t tb_calls;         /* transport-block calls, blocks in them, blocks whose CRC passed                          */
+  uint64_t transport_blocks;
+  uint64_t tb_crc_ok;
+  uint64_t faults;           /* CUDA failures turned into failed codeblocks / blocks                                    */
+} fec_engine_stats;
+int fec_engine_get_stats(fec_engine* e, fec_engine_stats* out);
+/* Test hook: the next n codeblock-kernel launches are refused by the driver (a launch error, not sticky). */
+int fec_engine_debug_fail_launches(fec_engine* e, uint32_t n);
 
 /* ---- validation helper (host only, no GPU work) -------------------------------------------------------------------- */
 /* Checks a descriptor and fills in k0 / graph_index exactly as the engine will. Returns FEC_OK or FEC_ERR_BAD_ARG. */
@@ -237,6 +267,23 @@ int fec_tb_segment(const fec_tb_desc* tb, const uint32_t* slots, fec_cb_desc* cb
 int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr,
                     size_t llr_bytes, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results,
                     fec_cb_result* h_cb_results);
+
+/* Asynchronous form (what pusch_decoder_impl does with its executor, lib/phy/upper/channel_processors/pusch/
+ * pusch_decoder_impl.cpp:372-381: on_end_softbits returns, the notifier fires later): fec_tb_enqueue validates, segments and
+ * puts every copy and kernel of the call on the streams of a free host-call context (fec_engine_cfg.host_contexts), then
+ * returns without waiting for the GPU; FEC_ERR_QUEUE_FULL when every context is in flight (back-pressure, never blocks).
+ * Calls of different threads run concurrently on the GPU. h_llr and h_out must stay valid until the call has completed; tbs
+ * and slots are copied. Completion, either way:
+ *   callback == NULL: the caller collects with fec_tb_poll (1 = done and results written, 0 = still running, < 0 = error;
+ *                     non-blocking) or fec_tb_wait (blocking); both take the ticket exactly once;
+ *   callback != NULL: an engine thread waits for the GPU, hands the blocks over and calls
+ *                     callback(user, ticket, status, results, n) -- status FEC_OK or the error; on a device fault the
+ *                     results say "nothing delivered" for the blocks that were lost. */
+typedef void (*fec_tb_callback)(void* user, uint64_t ticket, int status, const fec_tb_result* results, uint32_t n);
+int fec_tb_enqueue(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr, size_t llr_bytes,
+                   uint8_t* h_out, size_t out_bytes, fec_tb_callback callback, void* user, uint64_t* ticket);
+int fec_tb_poll(fec_engine* e, uint64_t ticket, fec_tb_result* h_results, fec_cb_result* h_cb_results);
+int fec_tb_wait(fec_engine* e, uint64_t ticket, fec_tb_result* h_results, fec_cb_result* h_cb_results);
 
 /* Forgets the codeblock CRC flags of a slot range (rx buffer released / expired). */
 int fec_tb_reset_slots(fec_engine* e, uint32_t first_slot, uint32_t n);

@@ -14,6 +14,8 @@
 #include "ldpc_tables.h"
 #include <algorithm>
 #include <atomic>
+#include <condition_variable>
+#include <thread>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -154,25 +156,40 @@ struct queue_t {
   uint64_t     next_seq = 1;
 };
 
-} // namespace
+// One host-call context: the stream set, device staging and pinned bounce buffers one fec_run_host / transport-block call
+// works in. An engine owns several, so that calls from different threads run concurrently (each on its own streams) instead
+// of queueing behind one mutex; the asynchronous transport-block interface keeps a context from fec_tb_enqueue to completion.
+// State of a submitted transport-block call, from tb_submit to tb_complete (one per context).
+struct tb_pending {
+  std::vector<fec_tb_desc> tbs; // the call's descriptors (the caller's array need not outlive fec_tb_enqueue)
+  uint32_t                 n = 0, n_map = 0;
+  size_t                   off_map = 0, off_tbres = 0;
+  bool                     pipelined = false;
+  uint8_t*                 h_out     = nullptr;
+  std::vector<uint32_t>    taken; // "reads as zeros" marks this call consumed: put back if the call fails
+  uint64_t                 ticket = 0;
+  fec_tb_callback          cb     = nullptr;
+  void*                    user   = nullptr;
+  std::vector<fec_tb_result> res; // callback mode: where the results are assembled
+  std::chrono::steady_clock::time_point t_in, t_seg, t_enq;
+};
 
-struct fec_engine {
-  fec_engine_cfg        cfg;
-  int                   sm_count     = 0;
+void tb_pending_free(tb_pending* p)
+{
+  delete p;
+}
+
+struct host_ctx {
+  uint32_t              index        = 0;
+  bool                  busy         = false; // guarded by fec_engine::ctx_mtx
   cudaStream_t          stream       = nullptr;
-  fec_dev_tables*       d_tab        = nullptr;
-  fec_packed_tables*    d_ptab       = nullptr;
-  bool                  packed_ok    = false;
-  int8_t*               d_harq       = nullptr;
-  std::atomic<uint64_t> launches{0};
-  std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
-  cudaStream_t          pipe[3]      = {nullptr, nullptr, nullptr}; // fec_run_host chunk pipeline (copy/compute overlap)
+  cudaStream_t          pipe[3]      = {nullptr, nullptr, nullptr}; // chunk pipeline (copy/compute overlap)
   cudaEvent_t           pipe_done[3] = {nullptr, nullptr, nullptr};
   cudaStream_t          copy_in      = nullptr; // all input copies of a chunked call, in chunk order (one FIFO)
+  cudaEvent_t           done         = nullptr; // everything the call put on its streams has finished
   std::vector<cudaEvent_t> chunk_in;            // chunk c's inputs have arrived
   std::vector<cudaEvent_t> chunk_out;           // chunk c's results and transport block bytes are back on the host
   std::vector<uint32_t>    tb_chunk_end;        // pipelined transport-block call: one-past-last block of each chunk
-  std::mutex            run_mtx; // serialises fec_run_host users of the shared staging below
   // staging for fec_run_host
   fec_cb_desc*   d_descs = nullptr;
   int8_t*        d_llr   = nullptr;
@@ -180,17 +197,41 @@ struct fec_engine {
   fec_cb_result* d_res   = nullptr;
   fec_cb_result* h_res_pin   = nullptr; // pinned bounce buffers: async copies from/to pageable memory would block
   fec_cb_desc*   h_descs_pin = nullptr; // the host and serialise the chunk pipeline
+  // transport-block layer (allocated on first use)
+  uint8_t*       h_meta  = nullptr; // pinned: jobs | codeblock map | scratch zeros | codeblock descriptors
+  uint8_t*       d_meta  = nullptr;
+  uint8_t*       h_rblk  = nullptr; // pinned: codeblock results | transport block results
+  uint8_t*       d_rblk  = nullptr;
+  uint8_t*       h_tbout = nullptr; // pinned bounce buffer for the transport block bytes
+  std::vector<fec_tb_geometry> tb_geo;
+  // weights of the last transport-block geometry seen (the same allocation usually repeats slot after slot)
+  uint32_t              wc_key[3] = {0, 0, 0}; // nof_cbs, data_bits, stream_bits
+  std::vector<uint32_t> wc_weights;
+  tb_pending*           pending = nullptr;
+};
+
+} // namespace
+
+struct fec_engine {
+  fec_engine_cfg        cfg;
+  int                   sm_count     = 0;
+  cudaStream_t          stream       = nullptr; // device-resident entry points (fec_launch_device, encoder, demodulator)
+  fec_dev_tables*       d_tab        = nullptr;
+  fec_packed_tables*    d_ptab       = nullptr;
+  bool                  packed_ok    = false;
+  int8_t*               d_harq       = nullptr;
+  std::atomic<uint64_t> launches{0};
+  std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
+  // host-call contexts: ctxs[0] also serves the encoder / demodulator host paths (their staging is engine-wide)
+  std::vector<host_ctx*>  ctxs;
+  std::mutex              ctx_mtx;
+  std::condition_variable ctx_cv;
   std::vector<queue_t>* queues = nullptr;
   std::mutex            queues_mtx;
   // transport-block layer (allocated on first use)
+  std::mutex            tb_alloc_mtx;
   std::atomic<uint8_t>* cb_ok    = nullptr; // per HARQ slot: the codeblock's CRC passed in an earlier transmission
   uint8_t*              d_msg    = nullptr; // per HARQ slot: decoded message of the codeblock (FEC_MAX_CB_OUT_BYTES)
-  uint8_t*              h_meta   = nullptr; // pinned: jobs | codeblock map | scratch zeros | codeblock descriptors
-  uint8_t*              d_meta   = nullptr;
-  uint8_t*              h_rblk   = nullptr; // pinned: codeblock results | transport block results
-  uint8_t*              d_rblk   = nullptr;
-  uint8_t*              h_tbout  = nullptr; // pinned bounce buffer for the transport block bytes
-  std::vector<fec_tb_geometry> tb_geo;
   // downlink encoder staging (allocated on first use, grown on demand)
   fec_enc_desc* d_enc_descs = nullptr;
   uint8_t*      d_enc_in    = nullptr;
@@ -205,12 +246,32 @@ struct fec_engine {
   size_t            dm_descs_cap = 0, dm_sym_cap = 0, dm_noise_cap = 0, dm_llr_cap = 0;
   fec_demod_desc*   h_dm_descs   = nullptr; // pinned copy of the call's descriptors, prepared and rebased
   size_t            h_dm_descs_cap = 0;
-  // weights of the last transport-block geometry seen (the same allocation usually repeats slot after slot)
-  uint32_t              wc_key[3] = {0, 0, 0}; // nof_cbs, data_bits, stream_bits
-  std::vector<uint32_t> wc_weights;
+  // counters (fec_engine_get_stats)
+  std::atomic<uint64_t> st_codeblocks{0}, st_batches{0}, st_results{0}, st_crc_pass{0}, st_queue_full{0}, st_faults{0},
+      st_tb_calls{0}, st_tbs{0}, st_tb_crc_ok{0}, st_max_depth{0}, st_dispatches{0}, st_dispatch_slots{0};
+  std::atomic<uint64_t> st_iter_hist[FEC_STATS_ITER_BINS];
+  std::atomic<uint32_t> debug_fail_launches{0}; // fec_engine_debug_fail_launches: the next n codeblock launches fail
+  // asynchronous transport-block interface: completion thread for calls that carry a callback
+  std::thread             tb_thread;
+  std::mutex              tb_mtx;
+  std::condition_variable tb_cv;
+  std::vector<host_ctx*>  tb_fifo; // contexts in flight that carry a callback, in submission order
+  bool                    tb_stop = false;
+  std::atomic<uint64_t>   tb_ticket{1};
 };
 
 namespace {
+
+// Counters of harvested codeblock results (fec_engine_get_stats).
+inline void stats_result(fec_engine* e, const fec_cb_result& r)
+{
+  e->st_results.fetch_add(1, std::memory_order_relaxed);
+  if (r.status & FEC_RES_CRC_PASS) {
+    e->st_crc_pass.fetch_add(1, std::memory_order_relaxed);
+  }
+  const uint32_t it = r.nof_ldpc_iterations < FEC_STATS_ITER_BINS ? r.nof_ldpc_iterations : FEC_STATS_ITER_BINS - 1;
+  e->st_iter_hist[it].fetch_add(1, std::memory_order_relaxed);
+}
 
 int launch(fec_engine*          e,
            cudaStream_t         st,
@@ -229,6 +290,20 @@ int launch(fec_engine*          e,
     return fail(FEC_ERR_BAD_ARG, "max_Z=%u is not a lifting size", max_Z);
   }
   CU_TRY(cudaSetDevice(e->cfg.device));
+  e->st_batches.fetch_add(1, std::memory_order_relaxed);
+  e->st_codeblocks.fetch_add(n, std::memory_order_relaxed);
+  if (e->debug_fail_launches.load(std::memory_order_relaxed) != 0) {
+    // fec_engine_debug_fail_launches: a launch the driver refuses (more dynamic shared memory than the SM has), to exercise
+    // the fault paths. The error is not sticky.
+    uint32_t left = e->debug_fail_launches.load();
+    while (left != 0 && !e->debug_fail_launches.compare_exchange_weak(left, left - 1)) {
+    }
+    if (left != 0) {
+      fec_cb_generic_kernel<<<n, 32, 1u << 20, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab);
+      const cudaError_t err = cudaGetLastError();
+      return fail(FEC_ERR_CUDA, "codeblock kernel launch failed (injected): %s", cudaGetErrorString(err));
+    }
+  }
   const bool packed_ok = (e->cfg.kernel_variant != 1) && e->packed_ok;
   if (packed_ok) {
     int r = fec_packed_launch(st, d_descs, n, d_llr, d_out, d_res, e->d_harq, e->d_tab, e->d_ptab, max_Z, any_bg1);
@@ -270,23 +345,158 @@ void apply_fresh(fec_engine* e, fec_cb_desc& d, std::vector<uint32_t>* taken = n
 // "reads as zeros" marks this call consumed are put back (the operation that would have rewritten the slots did not run).
 struct run_guard {
   fec_engine*           e;
+  host_ctx*             c;
   std::vector<uint32_t> taken;
   bool                  ok = false;
-  explicit run_guard(fec_engine* e_) : e(e_) {}
+  // codeblock calls: on failure every operation of the call is reported as a failed codeblock (a device fault must
+  // surface as failed codeblocks, never as a hang or a crash), beside the error code
+  fec_cb_result*     fail_results = nullptr;
+  const fec_cb_desc* fail_descs   = nullptr;
+  uint32_t           fail_n       = 0;
+  run_guard(fec_engine* e_, host_ctx* c_) : e(e_), c(c_) {}
   ~run_guard()
   {
     if (ok) {
       return;
     }
-    cudaStreamSynchronize(e->copy_in);
-    for (int k = 0; k < 3; ++k) {
-      cudaStreamSynchronize(e->pipe[k]);
+    e->st_faults.fetch_add(1, std::memory_order_relaxed);
+    for (uint32_t i = 0; fail_results && i < fail_n; ++i) {
+      fail_results[i]                     = fec_cb_result();
+      fail_results[i].status              = FEC_RES_DONE;
+      fail_results[i].nof_ldpc_iterations = fail_descs[i].max_iter;
     }
-    cudaStreamSynchronize(e->stream);
+    cudaStreamSynchronize(c->copy_in);
+    for (int k = 0; k < 3; ++k) {
+      cudaStreamSynchronize(c->pipe[k]);
+    }
+    cudaStreamSynchronize(c->stream);
     cudaGetLastError();
     for (uint32_t s : taken) {
       e->fresh[s].store(1);
     }
+  }
+};
+
+// ---- host-call contexts ----------------------------------------------------------------------------------------------------
+int ctx_create(fec_engine* e, uint32_t index, host_ctx** out)
+{
+  host_ctx* c = new (std::nothrow) host_ctx();
+  if (!c) {
+    return fail(FEC_ERR_NO_MEMORY, "host allocation failed");
+  }
+  *out     = c;
+  c->index = index;
+  CU_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CU_TRY(cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking));
+  CU_TRY(cudaEventCreateWithFlags(&c->done, cudaEventDisableTiming));
+  for (int i = 0; i < 3; ++i) {
+    CU_TRY(cudaStreamCreateWithFlags(&c->pipe[i], cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreateWithFlags(&c->pipe_done[i], cudaEventDisableTiming));
+  }
+  const uint32_t nc = e->cfg.max_batch_cbs;
+  CU_TRY(cudaMalloc((void**)&c->d_descs, nc * sizeof(fec_cb_desc)));
+  CU_TRY(cudaMalloc((void**)&c->d_llr, e->cfg.max_batch_llrs));
+  CU_TRY(cudaMalloc((void**)&c->d_out, (size_t)nc * FEC_MAX_CB_OUT_BYTES));
+  CU_TRY(cudaMalloc((void**)&c->d_res, nc * sizeof(fec_cb_result)));
+  CU_TRY(cudaHostAlloc((void**)&c->h_res_pin, nc * sizeof(fec_cb_result), cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&c->h_descs_pin, nc * sizeof(fec_cb_desc), cudaHostAllocDefault));
+  return FEC_OK;
+}
+
+void ctx_destroy(host_ctx* c)
+{
+  if (!c) {
+    return;
+  }
+  cudaFree(c->d_descs);
+  cudaFree(c->d_llr);
+  cudaFree(c->d_out);
+  cudaFree(c->d_res);
+  cudaFreeHost(c->h_res_pin);
+  cudaFreeHost(c->h_descs_pin);
+  cudaFree(c->d_meta);
+  cudaFree(c->d_rblk);
+  cudaFreeHost(c->h_meta);
+  cudaFreeHost(c->h_rblk);
+  cudaFreeHost(c->h_tbout);
+  for (cudaEvent_t ev : c->chunk_in) {
+    cudaEventDestroy(ev);
+  }
+  for (cudaEvent_t ev : c->chunk_out) {
+    cudaEventDestroy(ev);
+  }
+  for (int i = 0; i < 3; ++i) {
+    if (c->pipe[i]) {
+      cudaStreamDestroy(c->pipe[i]);
+    }
+    if (c->pipe_done[i]) {
+      cudaEventDestroy(c->pipe_done[i]);
+    }
+  }
+  if (c->done) {
+    cudaEventDestroy(c->done);
+  }
+  if (c->copy_in) {
+    cudaStreamDestroy(c->copy_in);
+  }
+  if (c->stream) {
+    cudaStreamDestroy(c->stream);
+  }
+  tb_pending_free(c->pending);
+  delete c;
+}
+
+// A free context: `index` >= 0 asks for that one (the encoder / demodulator paths, whose staging is engine-wide, use 0).
+// Blocks until one is free unless `block` is false (then nullptr).
+host_ctx* ctx_acquire(fec_engine* e, int index, bool block)
+{
+  std::unique_lock<std::mutex> lk(e->ctx_mtx);
+  for (;;) {
+    if (index >= 0) {
+      if (!e->ctxs[index]->busy) {
+        e->ctxs[index]->busy = true;
+        return e->ctxs[index];
+      }
+    } else {
+      // highest index first, so that context 0 stays free for the callers that need it
+      for (size_t i = e->ctxs.size(); i-- > 0;) {
+        if (!e->ctxs[i]->busy) {
+          e->ctxs[i]->busy = true;
+          return e->ctxs[i];
+        }
+      }
+    }
+    if (!block) {
+      return nullptr;
+    }
+    e->ctx_cv.wait(lk);
+  }
+}
+
+void ctx_release(fec_engine* e, host_ctx* c)
+{
+  {
+    std::lock_guard<std::mutex> lk(e->ctx_mtx);
+    c->busy = false;
+  }
+  e->ctx_cv.notify_all();
+}
+
+struct ctx_lease {
+  fec_engine* e;
+  host_ctx*   c;
+  ctx_lease(fec_engine* e_, int index) : e(e_), c(ctx_acquire(e_, index, true)) {}
+  ~ctx_lease()
+  {
+    if (c) {
+      ctx_release(e, c);
+    }
+  }
+  host_ctx* keep() // the context outlives the lease (asynchronous calls)
+  {
+    host_ctx* k = c;
+    c           = nullptr;
+    return k;
   }
 };
 
@@ -439,10 +649,8 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   CU_TRY(cudaGetDeviceProperties(&prop, cfg->device));
   e->sm_count = prop.multiProcessorCount;
   CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
-  CU_TRY(cudaStreamCreateWithFlags(&e->copy_in, cudaStreamNonBlocking));
-  for (int i = 0; i < 3; ++i) {
-    CU_TRY(cudaStreamCreateWithFlags(&e->pipe[i], cudaStreamNonBlocking));
-    CU_TRY(cudaEventCreateWithFlags(&e->pipe_done[i], cudaEventDisableTiming));
+  for (auto& h : e->st_iter_hist) {
+    h.store(0);
   }
   {
     // Largest dynamic shared-memory layouts (BG1, Z = 384), set once and never lowered: the attribute is global per function
@@ -477,12 +685,20 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   for (uint32_t i = 0; i < cfg->harq_slots; ++i) {
     e->fresh[i].store(0);
   }
-  CU_TRY(cudaMalloc((void**)&e->d_descs, e->cfg.max_batch_cbs * sizeof(fec_cb_desc)));
-  CU_TRY(cudaMalloc((void**)&e->d_llr, e->cfg.max_batch_llrs));
-  CU_TRY(cudaMalloc((void**)&e->d_out, (size_t)e->cfg.max_batch_cbs * FEC_MAX_CB_OUT_BYTES));
-  CU_TRY(cudaMalloc((void**)&e->d_res, e->cfg.max_batch_cbs * sizeof(fec_cb_result)));
-  CU_TRY(cudaHostAlloc((void**)&e->h_res_pin, e->cfg.max_batch_cbs * sizeof(fec_cb_result), cudaHostAllocDefault));
-  CU_TRY(cudaHostAlloc((void**)&e->h_descs_pin, e->cfg.max_batch_cbs * sizeof(fec_cb_desc), cudaHostAllocDefault));
+  if (e->cfg.host_contexts == 0) {
+    e->cfg.host_contexts = 4;
+  }
+  for (uint32_t i = 0; i < e->cfg.host_contexts; ++i) {
+    host_ctx* c  = nullptr;
+    const int rc = ctx_create(e, i, &c);
+    if (c) {
+      e->ctxs.push_back(c);
+    }
+    if (rc != FEC_OK) {
+      fec_engine_destroy(e);
+      return rc;
+    }
+  }
   e->queues = new std::vector<queue_t>(cfg->nof_queues);
   *out      = e;
   return FEC_OK;
@@ -494,6 +710,14 @@ void fec_engine_destroy(fec_engine* e)
     return;
   }
   cudaSetDevice(e->cfg.device);
+  if (e->tb_thread.joinable()) {
+    {
+      std::lock_guard<std::mutex> lk(e->tb_mtx);
+      e->tb_stop = true;
+    }
+    e->tb_cv.notify_all();
+    e->tb_thread.join(); // finishes what is in flight first
+  }
   cudaDeviceSynchronize();
   if (e->queues) {
     for (auto& q : *e->queues) {
@@ -506,21 +730,13 @@ void fec_engine_destroy(fec_engine* e)
     }
     delete e->queues;
   }
-  cudaFree(e->d_descs);
-  cudaFree(e->d_llr);
-  cudaFree(e->d_out);
-  cudaFree(e->d_res);
+  for (host_ctx* c : e->ctxs) {
+    ctx_destroy(c);
+  }
   cudaFree(e->d_harq);
-  cudaFreeHost(e->h_res_pin);
-  cudaFreeHost(e->h_descs_pin);
   delete[] e->fresh;
   delete[] e->cb_ok;
   cudaFree(e->d_msg);
-  cudaFree(e->d_meta);
-  cudaFree(e->d_rblk);
-  cudaFreeHost(e->h_meta);
-  cudaFreeHost(e->h_rblk);
-  cudaFreeHost(e->h_tbout);
   cudaFree(e->d_enc_descs);
   cudaFree(e->d_enc_in);
   cudaFree(e->d_enc_out);
@@ -534,23 +750,6 @@ void fec_engine_destroy(fec_engine* e)
   cudaFree(e->d_ptab);
   if (e->stream) {
     cudaStreamDestroy(e->stream);
-  }
-  if (e->copy_in) {
-    cudaStreamDestroy(e->copy_in);
-  }
-  for (cudaEvent_t ev : e->chunk_in) {
-    cudaEventDestroy(ev);
-  }
-  for (cudaEvent_t ev : e->chunk_out) {
-    cudaEventDestroy(ev);
-  }
-  for (int i = 0; i < 3; ++i) {
-    if (e->pipe[i]) {
-      cudaStreamDestroy(e->pipe[i]);
-    }
-    if (e->pipe_done[i]) {
-      cudaEventDestroy(e->pipe_done[i]);
-    }
   }
   delete e;
 }
@@ -625,12 +824,13 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     max_Z = d.lifting_size > max_Z ? d.lifting_size : max_Z;
     any1 |= (d.base_graph == 1);
   }
-  std::lock_guard<std::mutex> lk(e->run_mtx);
-  const auto                  t_prep = std::chrono::steady_clock::now();
+  ctx_lease lease(e, -1);
+  host_ctx& c      = *lease.c;
+  const auto t_prep = std::chrono::steady_clock::now();
   CU_TRY(cudaSetDevice(e->cfg.device));
   // Large batches are cut into chunks of one kernel wave (2 CTAs per SM) that travel on three streams, so that the H2D copy of one
   // chunk overlaps the kernels of the previous one and the D2H copy of the one before (PCIe is full duplex).
-  const uint32_t wave  = 2u * (uint32_t)e->sm_count;
+  const uint32_t wave  = FEC_PACKED_CTAS_PER_SM * (uint32_t)e->sm_count;
   uint32_t       chunk = (n >= 2 * wave) ? wave : n; // measured on B200: 1 wave beats 2, 3, 4 and 6 (e2e 11.4 vs 10.8 Gbit/s at 3)
   // (also measured: 1/2, 3/4, 5/4, 3/2 and 2 waves per chunk, and a finer-cut first wave: all 1-3 % slower end to end)
   // The first wave is cut finer (1/4, 1/4, 1/2 of a wave): the first kernel starts after a quarter of the first wave's copy
@@ -664,25 +864,28 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       prev_o1 = o1;
     }
   }
-  memcpy(e->h_descs_pin, h_descs, n * sizeof(fec_cb_desc));
+  memcpy(c.h_descs_pin, h_descs, n * sizeof(fec_cb_desc));
   // FEC_FLAG_HARQ_ZERO goes into the engine's copy only: the caller's array gets k0 / graph_index written back and nothing
   // else, so it can be reused for a retransmission (rv, flags edited) without carrying a stale "slot reads as zeros".
-  run_guard guard(e);
+  run_guard guard(e, &c);
+  guard.fail_results = h_results;
+  guard.fail_descs   = h_descs;
+  guard.fail_n       = n;
   for (uint32_t i = 0; i < n; ++i) {
-    apply_fresh(e, e->h_descs_pin[i], &guard.taken);
+    apply_fresh(e, c.h_descs_pin[i], &guard.taken);
   }
-  CU_TRY(cudaMemcpyAsync(e->d_descs, e->h_descs_pin, n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, e->stream));
-  CU_TRY(cudaEventRecord(e->pipe_done[0], e->stream));
+  CU_TRY(cudaMemcpyAsync(c.d_descs, c.h_descs_pin, n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, c.stream));
+  CU_TRY(cudaEventRecord(c.pipe_done[0], c.stream));
   for (int k = 0; k < 3; ++k) {
-    CU_TRY(cudaStreamWaitEvent(e->pipe[k], e->pipe_done[0], 0));
+    CU_TRY(cudaStreamWaitEvent(c.pipe[k], c.pipe_done[0], 0));
   }
   uint32_t nchunks = 0;
   for (uint32_t c0 = 0, cn = 0; c0 < n; c0 += cn, ++nchunks) {
     cn              = chunk_len(c0);
-    cudaStream_t st = (chunk == n) ? e->stream : e->pipe[nchunks % 3];
+    cudaStream_t st = (chunk == n) ? c.stream : c.pipe[nchunks % 3];
     // Chunked calls send every input through ONE copy stream, in chunk order: copies issued on the three kernel streams
     // were observed to complete out of order (chunk 0 third), which delays the first kernel by two chunk copies.
-    cudaStream_t in = (chunk == n) ? e->stream : e->copy_in;
+    cudaStream_t in = (chunk == n) ? c.stream : c.copy_in;
     // byte ranges of the batch buffers this chunk touches
     size_t   l0 = ~(size_t)0, l1 = 0, o0 = ~(size_t)0, o1 = 0;
     uint32_t cz = 0;
@@ -706,19 +909,19 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       c1 |= (d.base_graph == 1);
       keep |= (d.flags & FEC_FLAG_EARLY_STOP) != 0;
     }
-    CU_TRY(cudaMemcpyAsync(e->d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, in));
+    CU_TRY(cudaMemcpyAsync(c.d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, in));
     if (out_bytes && o1 > o0 && keep) {
       // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
-      CU_TRY(cudaMemcpyAsync(e->d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, in));
+      CU_TRY(cudaMemcpyAsync(c.d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, in));
     }
     if (in != st) {
-      if (e->chunk_in.size() <= nchunks) {
+      if (c.chunk_in.size() <= nchunks) {
         cudaEvent_t ev = nullptr;
         CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        e->chunk_in.push_back(ev);
+        c.chunk_in.push_back(ev);
       }
-      CU_TRY(cudaEventRecord(e->chunk_in[nchunks], in));
-      CU_TRY(cudaStreamWaitEvent(st, e->chunk_in[nchunks], 0));
+      CU_TRY(cudaEventRecord(c.chunk_in[nchunks], in));
+      CU_TRY(cudaStreamWaitEvent(st, c.chunk_in[nchunks], 0));
     }
     if (trace && nchunks < 32) {
       if (trace_ev.empty()) {
@@ -728,11 +931,11 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
         }
       }
       if (nchunks == 0) {
-        cudaEventRecord(trace_ev[64], e->stream); // after the descriptor copy
+        cudaEventRecord(trace_ev[64], c.stream); // after the descriptor copy
       }
       cudaEventRecord(trace_ev[2 * nchunks], st);
     }
-    int r = launch(e, st, e->d_descs + c0, cn, e->d_llr, e->d_out, e->d_res + c0, cz, c1);
+    int r = launch(e, st, c.d_descs + c0, cn, c.d_llr, c.d_out, c.d_res + c0, cz, c1);
     if (r != FEC_OK) {
       return r;
     }
@@ -740,14 +943,14 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       cudaEventRecord(trace_ev[2 * nchunks + 1], st);
     }
     if (out_bytes && o1 > o0) {
-      CU_TRY(cudaMemcpyAsync(h_out + o0, e->d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, st));
+      CU_TRY(cudaMemcpyAsync(h_out + o0, c.d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, st));
     }
-    CU_TRY(cudaMemcpyAsync(e->h_res_pin + c0, e->d_res + c0, cn * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(c.h_res_pin + c0, c.d_res + c0, cn * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st));
   }
   if (chunk != n) {
     for (int k = 0; k < 3; ++k) {
-      CU_TRY(cudaEventRecord(e->pipe_done[k], e->pipe[k]));
-      CU_TRY(cudaStreamWaitEvent(e->stream, e->pipe_done[k], 0));
+      CU_TRY(cudaEventRecord(c.pipe_done[k], c.pipe[k]));
+      CU_TRY(cudaStreamWaitEvent(c.stream, c.pipe_done[k], 0));
     }
   }
   if (h_soft_out) {
@@ -755,15 +958,18 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       if (h_descs[i].mode != FEC_MODE_DECODE) {
         CU_TRY(cudaMemcpyAsync(h_soft_out + (size_t)i * FEC_HARQ_SLOT_BYTES,
                                e->d_harq + (size_t)h_descs[i].harq_slot * FEC_HARQ_SLOT_BYTES, FEC_HARQ_SLOT_BYTES,
-                               cudaMemcpyDeviceToHost, e->stream));
+                               cudaMemcpyDeviceToHost, c.stream));
       }
     }
   }
   const auto t_enq = std::chrono::steady_clock::now();
-  CU_TRY(cudaStreamSynchronize(e->stream));
+  CU_TRY(cudaStreamSynchronize(c.stream));
   const auto t_sync = std::chrono::steady_clock::now();
-  memcpy(h_results, e->h_res_pin, n * sizeof(fec_cb_result));
+  memcpy(h_results, c.h_res_pin, n * sizeof(fec_cb_result));
   guard.ok = true;
+  for (uint32_t i = 0; i < n; ++i) {
+    stats_result(e, h_results[i]);
+  }
   if (trace) {
     const auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
       return std::chrono::duration<double, std::micro>(b - a).count();
@@ -1093,29 +1299,34 @@ int fec_queue_fetch(fec_engine* e, uint32_t queue_id, uint64_t tag, uint8_t* dst
 // ---- transport-block layer ----------------------------------------------------------------------------------------------
 namespace {
 
-int tb_state_alloc(fec_engine* e)
+int tb_state_alloc(fec_engine* e, host_ctx& hx)
 {
-  if (e->d_msg != nullptr) {
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  {
+    std::lock_guard<std::mutex> lk(e->tb_alloc_mtx);
+    if (e->d_msg == nullptr) {
+      if ((size_t)e->cfg.harq_slots * FEC_MAX_CB_OUT_BYTES > 0xffffffffull) {
+        return fail(FEC_ERR_BAD_ARG, "transport-block interface: %u HARQ slots exceed the 32-bit message-store offsets",
+                    e->cfg.harq_slots);
+      }
+      e->cb_ok = new (std::nothrow) std::atomic<uint8_t>[e->cfg.harq_slots];
+      for (uint32_t i = 0; i < e->cfg.harq_slots; ++i) {
+        e->cb_ok[i].store(0);
+      }
+      CU_TRY(cudaMalloc((void**)&e->d_msg, (size_t)e->cfg.harq_slots * FEC_MAX_CB_OUT_BYTES));
+    }
+  }
+  if (hx.h_meta != nullptr) {
     return FEC_OK;
   }
-  if ((size_t)e->cfg.harq_slots * FEC_MAX_CB_OUT_BYTES > 0xffffffffull) {
-    return fail(FEC_ERR_BAD_ARG, "transport-block interface: %u HARQ slots exceed the 32-bit message-store offsets",
-                e->cfg.harq_slots);
-  }
-  const uint32_t nc = e->cfg.max_batch_cbs;
-  CU_TRY(cudaSetDevice(e->cfg.device));
-  const size_t meta = (size_t)nc * (sizeof(fec_tb_job) + sizeof(fec_tb_cb_ref) + 8 + sizeof(fec_cb_desc)) + 64;
-  const size_t rblk = (size_t)nc * (sizeof(fec_cb_result) + sizeof(fec_tb_result)) + 64;
-  CU_TRY(cudaMalloc((void**)&e->d_meta, meta));
-  CU_TRY(cudaMalloc((void**)&e->d_rblk, rblk));
-  CU_TRY(cudaHostAlloc((void**)&e->h_meta, meta, cudaHostAllocDefault));
-  CU_TRY(cudaHostAlloc((void**)&e->h_rblk, rblk, cudaHostAllocDefault));
-  CU_TRY(cudaHostAlloc((void**)&e->h_tbout, (size_t)nc * FEC_MAX_CB_OUT_BYTES, cudaHostAllocDefault));
-  e->cb_ok = new (std::nothrow) std::atomic<uint8_t>[e->cfg.harq_slots];
-  for (uint32_t i = 0; i < e->cfg.harq_slots; ++i) {
-    e->cb_ok[i].store(0);
-  }
-  CU_TRY(cudaMalloc((void**)&e->d_msg, (size_t)e->cfg.harq_slots * FEC_MAX_CB_OUT_BYTES));
+  const uint32_t nc   = e->cfg.max_batch_cbs;
+  const size_t   meta = (size_t)nc * (sizeof(fec_tb_job) + sizeof(fec_tb_cb_ref) + 8 + sizeof(fec_cb_desc)) + 64;
+  const size_t   rblk = (size_t)nc * (sizeof(fec_cb_result) + sizeof(fec_tb_result)) + 64;
+  CU_TRY(cudaMalloc((void**)&hx.d_meta, meta));
+  CU_TRY(cudaMalloc((void**)&hx.d_rblk, rblk));
+  CU_TRY(cudaHostAlloc((void**)&hx.h_rblk, rblk, cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&hx.h_tbout, (size_t)nc * FEC_MAX_CB_OUT_BYTES, cudaHostAllocDefault));
+  CU_TRY(cudaHostAlloc((void**)&hx.h_meta, meta, cudaHostAllocDefault)); // last: marks the context as allocated
   return FEC_OK;
 }
 
@@ -1207,36 +1418,38 @@ struct demod_source {
 };
 int demod_stage(fec_engine* e, cudaStream_t st, const demod_source& dm, size_t l0, size_t l1, int8_t* d_llr);
 
-int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr, size_t llr_bytes,
-           const demod_source* dm, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+// First half of a transport-block call: validation, segmentation, every copy and kernel put on the context's streams,
+// hx.done recorded behind all of it. Nothing here waits for the GPU.
+int tb_submit(fec_engine* e, host_ctx& hx, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr,
+              size_t llr_bytes, const demod_source* dm, uint8_t* h_out, size_t out_bytes)
 {
-  if (!e || !tbs || (!h_llr && !dm) || !h_out || !h_results) {
+  if (!e || !tbs || (!h_llr && !dm) || !h_out) {
     return fail(FEC_ERR_BAD_ARG, "null argument");
   }
-  if (n == 0) {
-    return FEC_OK;
+  if (n == 0 || n > e->cfg.max_batch_cbs) {
+    return fail(FEC_ERR_BAD_ARG, "%u transport blocks in one call (the engine takes 1 .. %u)", n, e->cfg.max_batch_cbs);
   }
-  if (n > e->cfg.max_batch_cbs) {
-    return fail(FEC_ERR_BAD_ARG, "%u transport blocks exceed the engine capacity", n);
-  }
-  std::lock_guard<std::mutex> lk(e->run_mtx);
-  int rc = tb_state_alloc(e);
+  int rc = tb_state_alloc(e, hx);
   if (rc != FEC_OK) {
     return rc;
   }
+  if (hx.pending == nullptr) {
+    hx.pending = new tb_pending();
+  }
+  tb_pending& P = *hx.pending;
   // FEC_B200_TRACE=1: host timestamps of the call's phases on stderr (diagnostic; off by default).
   static const bool trace = getenv("FEC_B200_TRACE") != nullptr;
   const auto        now   = [] { return std::chrono::steady_clock::now(); };
   const auto        t_in  = now();
-  auto              t_seg = t_in, t_enq = t_in, t_sync = t_in;
+  auto              t_seg = t_in;
   // Pass 0: geometry of every block, so that the sizes of everything that follows are known.
-  e->tb_geo.resize(n);
+  hx.tb_geo.resize(n);
   uint32_t n_map = 0, max_Z = 0;
   int      any1  = 0;
   bool     aligned = true; // every payload is whole bytes: the one-CTA-per-codeblock gather applies
   for (uint32_t t = 0; t < n; ++t) {
     const fec_tb_desc& tb = tbs[t];
-    fec_tb_geometry&   g  = e->tb_geo[t];
+    fec_tb_geometry&   g  = hx.tb_geo[t];
     if (!fec_tb_geometry_of(tb, g)) {
       return fail(FEC_ERR_BAD_ARG, "transport block %u: tbs=%u bg=%u rv=%u qm=%u layers=%u llrs=%u", t, tb.tbs,
                   tb.base_graph, tb.rv, tb.qm, tb.nof_layers, tb.nof_llrs);
@@ -1258,7 +1471,7 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   // block bytes on three streams. Needs the byte-aligned gather and LLR spans that follow one another in block order.
   // Everything the LLR copies need is known after pass 0, so the first of them are put on the wire BEFORE the host segments
   // the blocks (0.17 ms for 46 config-3 blocks).
-  const uint32_t wave      = 2u * (uint32_t)e->sm_count;
+  const uint32_t wave      = FEC_PACKED_CTAS_PER_SM * (uint32_t)e->sm_count;
   bool           pipelined = !dm && aligned && n > 1 && n_map >= 2 * wave;
   for (uint32_t t = 1; t < n && pipelined; ++t) {
     pipelined = tbs[t].llr_offset >= tbs[t - 1].llr_offset + tbs[t - 1].nof_llrs;
@@ -1273,8 +1486,8 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
         cudaStreamSynchronize(s);
       }
     }
-  } guard{e->copy_in, false};
-  e->tb_chunk_end.clear();
+  } guard{hx.copy_in, false};
+  hx.tb_chunk_end.clear();
   if (pipelined) {
     const size_t pl0 = (size_t)tbs[0].llr_offset, pl1 = (size_t)tbs[n - 1].llr_offset + tbs[n - 1].nof_llrs;
     if (pl1 - pl0 > e->cfg.max_batch_llrs) {
@@ -1286,21 +1499,21 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
     for (uint32_t t0 = 0, t1 = 0; t0 < n; t0 = t1, ++c) {
       uint32_t cn = 0;
       for (t1 = t0; t1 < n && (cn < wave || t1 == t0); ++t1) {
-        cn += e->tb_geo[t1].nof_cbs;
+        cn += hx.tb_geo[t1].nof_cbs;
       }
-      if (e->chunk_in.size() <= c) {
+      if (hx.chunk_in.size() <= c) {
         cudaEvent_t ev = nullptr;
         CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        e->chunk_in.push_back(ev);
+        hx.chunk_in.push_back(ev);
       }
       // Only the first three groups go now (about the transfer time of the segmentation that follows): the descriptor
       // block has to reach the device before the first kernel, and one copy engine serves the queue in issue order.
       if (c < 3) {
         const size_t a = (size_t)tbs[t0].llr_offset, b = (size_t)tbs[t1 - 1].llr_offset + tbs[t1 - 1].nof_llrs;
-        CU_TRY(cudaMemcpyAsync(e->d_llr + (a - pl0), h_llr + a, b - a, cudaMemcpyHostToDevice, e->copy_in));
-        CU_TRY(cudaEventRecord(e->chunk_in[c], e->copy_in));
+        CU_TRY(cudaMemcpyAsync(hx.d_llr + (a - pl0), h_llr + a, b - a, cudaMemcpyHostToDevice, hx.copy_in));
+        CU_TRY(cudaEventRecord(hx.chunk_in[c], hx.copy_in));
       }
-      e->tb_chunk_end.push_back(t1);
+      hx.tb_chunk_end.push_back(t1);
     }
   }
   // One pinned block travels to the device in one copy: jobs | codeblock map | scratch (zeros) | codeblock descriptors.
@@ -1309,16 +1522,16 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   const size_t   off_scr   = up16(off_map + (size_t)n_map * sizeof(fec_tb_cb_ref));
   const size_t   off_descs = up16(off_scr + (size_t)n * 2 * sizeof(uint32_t));
   const size_t   meta_size = off_descs + (size_t)n_map * sizeof(fec_cb_desc);
-  fec_tb_job*    h_jobs    = reinterpret_cast<fec_tb_job*>(e->h_meta);
-  fec_tb_cb_ref* h_map     = reinterpret_cast<fec_tb_cb_ref*>(e->h_meta + off_map);
-  fec_cb_desc*   h_descs   = reinterpret_cast<fec_cb_desc*>(e->h_meta + off_descs);
-  memset(e->h_meta + off_scr, 0, (size_t)n * 2 * sizeof(uint32_t));
+  fec_tb_job*    h_jobs    = reinterpret_cast<fec_tb_job*>(hx.h_meta);
+  fec_tb_cb_ref* h_map     = reinterpret_cast<fec_tb_cb_ref*>(hx.h_meta + off_map);
+  fec_cb_desc*   h_descs   = reinterpret_cast<fec_cb_desc*>(hx.h_meta + off_descs);
+  memset(hx.h_meta + off_scr, 0, (size_t)n * 2 * sizeof(uint32_t));
   // Pass 1: segmentation -- one descriptor per codeblock, the codeblock map, the jobs.
   size_t   l0 = ~(size_t)0, l1 = 0;
   uint32_t m = 0;
   for (uint32_t t = 0; t < n; ++t) {
     const fec_tb_desc&     tb = tbs[t];
-    const fec_tb_geometry& g  = e->tb_geo[t];
+    const fec_tb_geometry& g  = hx.tb_geo[t];
     fec_tb_job&            J  = h_jobs[t];
     J.out_offset              = tb.out_offset;
     J.nof_cbs                 = g.nof_cbs;
@@ -1328,17 +1541,17 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
     J.map_first               = m;
     J.max_iter                = tb.max_iter;
     if (g.data_bits % 8 == 0 && g.nof_cbs > 1 &&
-        (e->wc_key[0] != g.nof_cbs || e->wc_key[1] != g.data_bits || e->wc_key[2] != g.stream_bits)) {
+        (hx.wc_key[0] != g.nof_cbs || hx.wc_key[1] != g.data_bits || hx.wc_key[2] != g.stream_bits)) {
       // weight of codeblock r = x^(8 * stream bytes after its payload) mod g24A, built backwards with one multiply each
-      e->wc_key[0] = g.nof_cbs;
-      e->wc_key[1] = g.data_bits;
-      e->wc_key[2] = g.stream_bits;
-      e->wc_weights.assign(g.nof_cbs, 1u);
+      hx.wc_key[0] = g.nof_cbs;
+      hx.wc_key[1] = g.data_bits;
+      hx.wc_key[2] = g.stream_bits;
+      hx.wc_weights.assign(g.nof_cbs, 1u);
       const uint32_t dbytes = g.data_bits / 8, last = g.stream_bits / 8 - (g.nof_cbs - 1) * dbytes;
       uint32_t       w      = fec_tb_crc24a_xpow8_host(last); // after codeblock C-2 comes the last payload
       const uint32_t step   = fec_tb_crc24a_xpow8_host(dbytes);
       for (int r = (int)g.nof_cbs - 2; r >= 0; --r) {
-        e->wc_weights[r] = w;
+        hx.wc_weights[r] = w;
         w                = fec_tb_crc24a_mulmod_host(w, step);
       }
     }
@@ -1351,7 +1564,7 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       fec_tb_cb_ref& ref = h_map[m];
       ref.slot           = slot;
       ref.tb             = t;
-      ref.weight         = (g.data_bits % 8 == 0 && g.nof_cbs > 1) ? e->wc_weights[r] : 1u;
+      ref.weight         = (g.data_bits % 8 == 0 && g.nof_cbs > 1) ? hx.wc_weights[r] : 1u;
       fec_cb_desc& d     = h_descs[m];
       tb_cb_desc(tb, g, r, cw_off, slot, d);
       // A codeblock whose CRC passed in an earlier transmission is not decoded again, but the new LLRs are still
@@ -1381,7 +1594,7 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   }
   // Every check has passed: only now does the call change engine state (codeblock CRC flags of new transmissions, the
   // "reads as zeros" marks of freed slots). A CUDA failure further down puts the marks back (run_guard).
-  run_guard rg(e);
+  run_guard rg(e, &hx);
   for (uint32_t t = 0; t < n; ++t) {
     if (tbs[t].flags & FEC_FLAG_NEW_DATA) {
       for (uint32_t r = 0; r < h_jobs[t].nof_cbs; ++r) {
@@ -1395,93 +1608,131 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
   }
   t_seg = now();
   CU_TRY(cudaSetDevice(e->cfg.device));
-  cudaStream_t         st      = e->stream;
-  const fec_tb_job*    d_jobs  = reinterpret_cast<const fec_tb_job*>(e->d_meta);
-  const fec_tb_cb_ref* d_map   = reinterpret_cast<const fec_tb_cb_ref*>(e->d_meta + off_map);
-  uint32_t*            d_scr   = reinterpret_cast<uint32_t*>(e->d_meta + off_scr);
-  const fec_cb_desc*   d_descs = reinterpret_cast<const fec_cb_desc*>(e->d_meta + off_descs);
+  cudaStream_t         st      = hx.stream;
+  const fec_tb_job*    d_jobs  = reinterpret_cast<const fec_tb_job*>(hx.d_meta);
+  const fec_tb_cb_ref* d_map   = reinterpret_cast<const fec_tb_cb_ref*>(hx.d_meta + off_map);
+  uint32_t*            d_scr   = reinterpret_cast<uint32_t*>(hx.d_meta + off_scr);
+  const fec_cb_desc*   d_descs = reinterpret_cast<const fec_cb_desc*>(hx.d_meta + off_descs);
   // results come back in one copy too: codeblock results | transport block results
   const size_t   off_tbres = up16((size_t)n_map * sizeof(fec_cb_result));
-  fec_cb_result* d_cbres   = reinterpret_cast<fec_cb_result*>(e->d_rblk);
-  fec_tb_result* d_tbres   = reinterpret_cast<fec_tb_result*>(e->d_rblk + off_tbres);
-  CU_TRY(cudaMemcpyAsync(e->d_meta, e->h_meta, meta_size, cudaMemcpyHostToDevice, st));
+  fec_cb_result* d_cbres   = reinterpret_cast<fec_cb_result*>(hx.d_rblk);
+  fec_tb_result* d_tbres   = reinterpret_cast<fec_tb_result*>(hx.d_rblk + off_tbres);
+  CU_TRY(cudaMemcpyAsync(hx.d_meta, hx.h_meta, meta_size, cudaMemcpyHostToDevice, st));
   if (pipelined) {
-    CU_TRY(cudaEventRecord(e->pipe_done[0], st));
+    CU_TRY(cudaEventRecord(hx.pipe_done[0], st));
     for (int k = 0; k < 3; ++k) {
-      CU_TRY(cudaStreamWaitEvent(e->pipe[k], e->pipe_done[0], 0));
+      CU_TRY(cudaStreamWaitEvent(hx.pipe[k], hx.pipe_done[0], 0));
     }
-    for (uint32_t c = 0, t0 = 0; c < e->tb_chunk_end.size(); t0 = e->tb_chunk_end[c], ++c) {
-      const uint32_t t1 = e->tb_chunk_end[c];
+    for (uint32_t c = 0, t0 = 0; c < hx.tb_chunk_end.size(); t0 = hx.tb_chunk_end[c], ++c) {
+      const uint32_t t1 = hx.tb_chunk_end[c];
       const uint32_t m0 = h_jobs[t0].map_first, cn = h_jobs[t1 - 1].map_first + h_jobs[t1 - 1].nof_cbs - m0;
-      cudaStream_t   ps = e->pipe[c % 3];
+      cudaStream_t   ps = hx.pipe[c % 3];
       if (c >= 3) { // the first three groups' LLRs went on the wire before the segmentation
         const size_t a = (size_t)tbs[t0].llr_offset, b = (size_t)tbs[t1 - 1].llr_offset + tbs[t1 - 1].nof_llrs;
-        CU_TRY(cudaMemcpyAsync(e->d_llr + (a - l0), h_llr + a, b - a, cudaMemcpyHostToDevice, e->copy_in));
-        CU_TRY(cudaEventRecord(e->chunk_in[c], e->copy_in));
+        CU_TRY(cudaMemcpyAsync(hx.d_llr + (a - l0), h_llr + a, b - a, cudaMemcpyHostToDevice, hx.copy_in));
+        CU_TRY(cudaEventRecord(hx.chunk_in[c], hx.copy_in));
       }
-      CU_TRY(cudaStreamWaitEvent(ps, e->chunk_in[c], 0));
-      rc = launch(e, ps, d_descs + m0, cn, e->d_llr, e->d_msg, d_cbres + m0, max_Z, any1);
+      CU_TRY(cudaStreamWaitEvent(ps, hx.chunk_in[c], 0));
+      rc = launch(e, ps, d_descs + m0, cn, hx.d_llr, e->d_msg, d_cbres + m0, max_Z, any1);
       if (rc != FEC_OK) {
         return rc;
       }
-      fec_tb_gather_kernel<<<cn, 256, 0, ps>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres, d_scr, e->d_tab, m0);
+      fec_tb_gather_kernel<<<cn, 256, 0, ps>>>(d_jobs, d_map, d_cbres, e->d_msg, hx.d_out, d_tbres, d_scr, e->d_tab, m0);
       CU_TRY(cudaGetLastError());
       e->launches.fetch_add(1);
       for (uint32_t t = t0; t < t1; ++t) {
-        CU_TRY(cudaMemcpyAsync(e->h_tbout + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8,
+        CU_TRY(cudaMemcpyAsync(hx.h_tbout + tbs[t].out_offset, hx.d_out + tbs[t].out_offset, tbs[t].tbs / 8,
                                cudaMemcpyDeviceToHost, ps));
       }
       // The chunk's own slice of the results follows, so that its blocks can be handed over while later chunks still run.
-      CU_TRY(cudaMemcpyAsync(e->h_rblk + (size_t)m0 * sizeof(fec_cb_result), e->d_rblk + (size_t)m0 * sizeof(fec_cb_result),
+      CU_TRY(cudaMemcpyAsync(hx.h_rblk + (size_t)m0 * sizeof(fec_cb_result), hx.d_rblk + (size_t)m0 * sizeof(fec_cb_result),
                              (size_t)cn * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, ps));
-      CU_TRY(cudaMemcpyAsync(e->h_rblk + off_tbres + (size_t)t0 * sizeof(fec_tb_result),
-                             e->d_rblk + off_tbres + (size_t)t0 * sizeof(fec_tb_result), (size_t)(t1 - t0) * sizeof(fec_tb_result),
+      CU_TRY(cudaMemcpyAsync(hx.h_rblk + off_tbres + (size_t)t0 * sizeof(fec_tb_result),
+                             hx.d_rblk + off_tbres + (size_t)t0 * sizeof(fec_tb_result), (size_t)(t1 - t0) * sizeof(fec_tb_result),
                              cudaMemcpyDeviceToHost, ps));
-      if (e->chunk_out.size() <= c) {
+      if (hx.chunk_out.size() <= c) {
         cudaEvent_t ev = nullptr;
         CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        e->chunk_out.push_back(ev);
+        hx.chunk_out.push_back(ev);
       }
-      CU_TRY(cudaEventRecord(e->chunk_out[c], ps));
+      CU_TRY(cudaEventRecord(hx.chunk_out[c], ps));
     }
   } else {
     if (dm) {
-      rc = demod_stage(e, st, *dm, l0, l1, e->d_llr);
+      rc = demod_stage(e, st, *dm, l0, l1, hx.d_llr);
       if (rc != FEC_OK) {
         return rc;
       }
     } else {
-      CU_TRY(cudaMemcpyAsync(e->d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+      CU_TRY(cudaMemcpyAsync(hx.d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
     }
-    rc = launch(e, st, d_descs, n_map, e->d_llr, e->d_msg, d_cbres, max_Z, any1);
+    rc = launch(e, st, d_descs, n_map, hx.d_llr, e->d_msg, d_cbres, max_Z, any1);
     if (rc != FEC_OK) {
       return rc;
     }
     if (aligned) {
-      fec_tb_gather_kernel<<<n_map, 256, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres, d_scr, e->d_tab, 0u);
+      fec_tb_gather_kernel<<<n_map, 256, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, hx.d_out, d_tbres, d_scr, e->d_tab, 0u);
     } else {
-      fec_tb_assemble_kernel<<<n, 1024, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, e->d_out, d_tbres);
+      fec_tb_assemble_kernel<<<n, 1024, 0, st>>>(d_jobs, d_map, d_cbres, e->d_msg, hx.d_out, d_tbres);
     }
     CU_TRY(cudaGetLastError());
     e->launches.fetch_add(1);
-    CU_TRY(cudaMemcpyAsync(e->h_rblk, e->d_rblk, off_tbres + (size_t)n * sizeof(fec_tb_result), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(hx.h_rblk, hx.d_rblk, off_tbres + (size_t)n * sizeof(fec_tb_result), cudaMemcpyDeviceToHost, st));
     // The transport block bytes come back unconditionally into a pinned bounce buffer (a block that is not delivered must
     // leave the caller's buffer untouched, and waiting for the results first would cost a second round trip).
     for (uint32_t t = 0; t < n; ++t) {
-      CU_TRY(cudaMemcpyAsync(e->h_tbout + tbs[t].out_offset, e->d_out + tbs[t].out_offset, tbs[t].tbs / 8,
+      CU_TRY(cudaMemcpyAsync(hx.h_tbout + tbs[t].out_offset, hx.d_out + tbs[t].out_offset, tbs[t].tbs / 8,
                              cudaMemcpyDeviceToHost, st));
     }
   }
-  t_enq = now();
-  // Pass 2: deliver the transport blocks whose codeblocks are all good, update the per-codeblock state.
-  const fec_cb_result* h_cbres = reinterpret_cast<const fec_cb_result*>(e->h_rblk);
-  const fec_tb_result* h_tbres = reinterpret_cast<const fec_tb_result*>(e->h_rblk + off_tbres);
+  // One event behind everything: the pipelined groups ran on three streams.
+  if (pipelined) {
+    for (size_t c = 0; c < hx.tb_chunk_end.size(); ++c) {
+      CU_TRY(cudaStreamWaitEvent(st, hx.chunk_out[c], 0));
+    }
+  }
+  CU_TRY(cudaEventRecord(hx.done, st));
+  rg.ok = true; // from here on tb_complete owns the marks
+  guard.armed = false; // and the wait for the copies out of the caller's LLR buffer
+  P.tbs.assign(tbs, tbs + n);
+  P.n         = n;
+  P.n_map     = n_map;
+  P.off_map   = off_map;
+  P.off_tbres = off_tbres;
+  P.pipelined = pipelined;
+  P.h_out     = h_out;
+  P.taken.swap(rg.taken);
+  P.t_in  = t_in;
+  P.t_seg = t_seg;
+  P.t_enq = now();
+  e->st_tb_calls.fetch_add(1, std::memory_order_relaxed);
+  e->st_tbs.fetch_add(n, std::memory_order_relaxed);
+  (void)trace;
+  return FEC_OK;
+}
+
+// Second half: waits for the GPU (chunk by chunk for a pipelined call, so that the host copies of the early groups overlap the
+// kernels of the late ones), hands over the transport blocks whose codeblocks are all good and updates the per-codeblock
+// state. A CUDA failure comes back as failed blocks (nothing delivered, every codeblock failed) AND as FEC_ERR_CUDA.
+int tb_complete(fec_engine* e, host_ctx& hx, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+{
+  static const bool trace = getenv("FEC_B200_TRACE") != nullptr;
+  const auto        now   = [] { return std::chrono::steady_clock::now(); };
+  tb_pending&       P     = *hx.pending;
+  const uint32_t    n     = P.n;
+  const fec_tb_desc* tbs  = P.tbs.data();
+  uint8_t*          h_out = P.h_out;
+  const fec_tb_job*    h_jobs  = reinterpret_cast<const fec_tb_job*>(hx.h_meta);
+  const fec_tb_cb_ref* h_map   = reinterpret_cast<const fec_tb_cb_ref*>(hx.h_meta + P.off_map);
+  const fec_cb_result* h_cbres = reinterpret_cast<const fec_cb_result*>(hx.h_rblk);
+  const fec_tb_result* h_tbres = reinterpret_cast<const fec_tb_result*>(hx.h_rblk + P.off_tbres);
+  auto                 t_sync  = P.t_enq;
   const auto           deliver = [&](uint32_t t) {
     const fec_tb_result& R = h_tbres[t];
     const fec_tb_job&    J = h_jobs[t];
     h_results[t]           = R;
     if (R.tb_delivered) {
-      memcpy(h_out + tbs[t].out_offset, e->h_tbout + tbs[t].out_offset, tbs[t].tbs / 8);
+      memcpy(h_out + tbs[t].out_offset, hx.h_tbout + tbs[t].out_offset, tbs[t].tbs / 8);
     }
     for (uint32_t r = 0; r < J.nof_cbs; ++r) {
       const fec_tb_cb_ref& ref = h_map[J.map_first + r];
@@ -1491,6 +1742,7 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
         if (cr.status & FEC_RES_CRC_PASS) {
           e->cb_ok[ref.slot].store(1);
         }
+        stats_result(e, cr);
       } else {
         cr.nof_ldpc_iterations = 0;
         cr.status              = FEC_RES_SKIPPED | FEC_RES_CRC_PASS | FEC_RES_DONE;
@@ -1502,6 +1754,7 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       }
     }
     if (R.tb_crc_ok) {
+      e->st_tb_crc_ok.fetch_add(1, std::memory_order_relaxed);
       // join_and_notify: the buffer is released -> free the HARQ context entries.
       for (uint32_t r = 0; r < J.nof_cbs; ++r) {
         const uint32_t slot = h_map[J.map_first + r].slot;
@@ -1515,35 +1768,73 @@ int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* sl
       }
     }
   };
-  if (pipelined) {
-    // chunk by chunk, as each one's results land: the host copies of the early chunks overlap the kernels of the late ones
-    uint32_t t = 0;
-    for (size_t c = 0; c < e->tb_chunk_end.size(); ++c) {
-      CU_TRY(cudaEventSynchronize(e->chunk_out[c]));
-      if (c + 1 == e->tb_chunk_end.size()) {
-        t_sync = now();
-      }
-      for (; t < e->tb_chunk_end[c]; ++t) {
+  cudaSetDevice(e->cfg.device);
+  cudaError_t err = cudaSuccess;
+  uint32_t    t   = 0;
+  if (P.pipelined) {
+    for (size_t c = 0; c < hx.tb_chunk_end.size() && err == cudaSuccess; ++c) {
+      err = cudaEventSynchronize(hx.chunk_out[c]);
+      for (; err == cudaSuccess && t < hx.tb_chunk_end[c]; ++t) {
         deliver(t);
       }
     }
-    CU_TRY(cudaStreamSynchronize(st));
-  } else {
-    CU_TRY(cudaStreamSynchronize(st));
-    t_sync = now();
-    for (uint32_t t = 0; t < n; ++t) {
-      deliver(t);
-    }
   }
-  rg.ok = true;
+  if (err == cudaSuccess) {
+    err    = cudaEventSynchronize(hx.done);
+    t_sync = now();
+  }
+  for (; err == cudaSuccess && t < n; ++t) {
+    deliver(t);
+  }
+  if (err != cudaSuccess) {
+    // The device faulted: whatever was not handed over yet failed; the freed-slot marks this call consumed are put back.
+    cudaGetLastError();
+    cudaStreamSynchronize(hx.copy_in);
+    e->st_faults.fetch_add(1, std::memory_order_relaxed);
+    for (; t < n; ++t) {
+      fec_tb_result R = {};
+      R.nof_codeblocks = (uint16_t)h_jobs[t].nof_cbs;
+      h_results[t]     = R;
+      for (uint32_t r = 0; h_cb_results && r < h_jobs[t].nof_cbs; ++r) {
+        fec_cb_result cr = {};
+        cr.nof_ldpc_iterations = (uint16_t)tbs[t].max_iter;
+        cr.status              = FEC_RES_DONE;
+        h_cb_results[(size_t)t * FEC_MAX_TB_CBS + r] = cr;
+      }
+    }
+    for (uint32_t sl : P.taken) {
+      e->fresh[sl].store(1);
+    }
+    P.taken.clear();
+    return fail(FEC_ERR_CUDA, "transport-block call failed on the device: %s", cudaGetErrorString(err));
+  }
+  P.taken.clear();
   if (trace) {
     const auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
       return std::chrono::duration<double, std::micro>(b - a).count();
     };
-    fprintf(stderr, "fec_b200 trace: tb_run n=%u cbs=%u segment %.1f us, enqueue %.1f us, wait %.1f us, deliver %.1f us\n", n, n_map,
-            us(t_in, t_seg), us(t_seg, t_enq), us(t_enq, t_sync), us(t_sync, now()));
+    fprintf(stderr, "fec_b200 trace: tb_run n=%u cbs=%u segment %.1f us, enqueue %.1f us, wait %.1f us, deliver %.1f us\n", n, P.n_map,
+            us(P.t_in, P.t_seg), us(P.t_seg, P.t_enq), us(P.t_enq, t_sync), us(t_sync, now()));
   }
   return FEC_OK;
+}
+
+// Synchronous call: a free context, submit, complete. dm (device-side demodulation) uses engine-wide staging: context 0.
+int tb_run(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr, size_t llr_bytes,
+           const demod_source* dm, uint8_t* h_out, size_t out_bytes, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+{
+  if (!e || !h_results) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  if (n == 0) {
+    return FEC_OK;
+  }
+  ctx_lease lease(e, dm ? 0 : -1);
+  int       rc = tb_submit(e, *lease.c, tbs, n, slots, h_llr, llr_bytes, dm, h_out, out_bytes);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  return tb_complete(e, *lease.c, h_results, h_cb_results);
 }
 } // namespace
 
@@ -1554,6 +1845,156 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
     return fail(FEC_ERR_BAD_ARG, "null argument");
   }
   return tb_run(e, tbs, n, slots, h_llr, llr_bytes, nullptr, h_out, out_bytes, h_results, h_cb_results);
+}
+
+// ---- asynchronous transport-block interface ------------------------------------------------------------------------------------
+namespace {
+// Completion thread: takes the in-flight calls that carry a callback in submission order, waits for each on its event,
+// hands the blocks over and calls back. Started by the first such call.
+void tb_completion_loop(fec_engine* e)
+{
+  cudaSetDevice(e->cfg.device);
+  for (;;) {
+    host_ctx* c = nullptr;
+    {
+      std::unique_lock<std::mutex> lk(e->tb_mtx);
+      e->tb_cv.wait(lk, [e] { return e->tb_stop || !e->tb_fifo.empty(); });
+      if (e->tb_fifo.empty()) {
+        return; // stop requested and nothing in flight
+      }
+      c = e->tb_fifo.front();
+      e->tb_fifo.erase(e->tb_fifo.begin());
+    }
+    tb_pending& P = *c->pending;
+    P.res.assign(P.n, fec_tb_result());
+    const int             rc     = tb_complete(e, *c, P.res.data(), nullptr);
+    const fec_tb_callback cb     = P.cb;
+    void*                 user   = P.user;
+    const uint64_t        ticket = P.ticket;
+    std::vector<fec_tb_result> res;
+    res.swap(P.res);
+    P.ticket = 0;
+    ctx_release(e, c); // before the callback: it may enqueue the next block
+    cb(user, ticket, rc, res.data(), (uint32_t)res.size());
+  }
+}
+} // namespace
+
+int fec_tb_enqueue(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint32_t* slots, const int8_t* h_llr, size_t llr_bytes,
+                   uint8_t* h_out, size_t out_bytes, fec_tb_callback callback, void* user, uint64_t* ticket)
+{
+  if (!e || !tbs || !h_llr || !h_out || !ticket || n == 0) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  host_ctx* c = ctx_acquire(e, -1, false);
+  if (c == nullptr) {
+    e->st_queue_full.fetch_add(1, std::memory_order_relaxed);
+    return fail(FEC_ERR_QUEUE_FULL, "all %zu host-call contexts are in flight", e->ctxs.size());
+  }
+  const int rc = tb_submit(e, *c, tbs, n, slots, h_llr, llr_bytes, nullptr, h_out, out_bytes);
+  if (rc != FEC_OK) {
+    ctx_release(e, c);
+    return rc;
+  }
+  tb_pending& P = *c->pending;
+  P.ticket      = ((uint64_t)e->tb_ticket.fetch_add(1) << 8) | c->index;
+  P.cb          = callback;
+  P.user        = user;
+  *ticket       = P.ticket;
+  if (callback != nullptr) {
+    std::lock_guard<std::mutex> lk(e->tb_mtx);
+    if (!e->tb_thread.joinable()) {
+      e->tb_thread = std::thread(tb_completion_loop, e);
+    }
+    e->tb_fifo.push_back(c);
+    e->tb_cv.notify_one();
+  }
+  return FEC_OK;
+}
+
+namespace {
+int tb_ticket_ctx(fec_engine* e, uint64_t ticket, host_ctx** out)
+{
+  const uint32_t idx = (uint32_t)(ticket & 0xff);
+  if (!e || ticket == 0 || idx >= e->ctxs.size() || e->ctxs[idx]->pending == nullptr || e->ctxs[idx]->pending->ticket != ticket ||
+      e->ctxs[idx]->pending->cb != nullptr) {
+    return fail(FEC_ERR_BAD_ARG, "unknown transport-block ticket (already collected, or a call with a callback)");
+  }
+  *out = e->ctxs[idx];
+  return FEC_OK;
+}
+} // namespace
+
+int fec_tb_poll(fec_engine* e, uint64_t ticket, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+{
+  host_ctx* c  = nullptr;
+  int       rc = tb_ticket_ctx(e, ticket, &c);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  if (!h_results) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  cudaSetDevice(e->cfg.device);
+  const cudaError_t q = cudaEventQuery(c->done);
+  if (q == cudaErrorNotReady) {
+    return 0;
+  }
+  rc                 = tb_complete(e, *c, h_results, h_cb_results); // an error state of the event is reported from in there
+  c->pending->ticket = 0;
+  ctx_release(e, c);
+  return rc == FEC_OK ? 1 : rc;
+}
+
+int fec_tb_wait(fec_engine* e, uint64_t ticket, fec_tb_result* h_results, fec_cb_result* h_cb_results)
+{
+  host_ctx* c  = nullptr;
+  int       rc = tb_ticket_ctx(e, ticket, &c);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  if (!h_results) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  rc                 = tb_complete(e, *c, h_results, h_cb_results);
+  c->pending->ticket = 0;
+  ctx_release(e, c);
+  return rc;
+}
+
+// ---- counters ---------------------------------------------------------------------------------------------------------------
+int fec_engine_get_stats(fec_engine* e, fec_engine_stats* out)
+{
+  if (!e || !out) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  memset(out, 0, sizeof(*out));
+  out->launches            = e->launches.load();
+  out->cb_launches         = e->st_batches.load();
+  out->codeblocks          = e->st_codeblocks.load();
+  out->results             = e->st_results.load();
+  out->crc_pass            = e->st_crc_pass.load();
+  out->queue_full          = e->st_queue_full.load();
+  out->faults              = e->st_faults.load();
+  out->tb_calls            = e->st_tb_calls.load();
+  out->transport_blocks    = e->st_tbs.load();
+  out->tb_crc_ok           = e->st_tb_crc_ok.load();
+  out->max_queue_depth     = e->st_max_depth.load();
+  out->dispatches          = e->st_dispatches.load();
+  out->dispatch_batches    = e->st_dispatch_slots.load();
+  for (int i = 0; i < FEC_STATS_ITER_BINS; ++i) {
+    out->iterations_hist[i] = e->st_iter_hist[i].load();
+  }
+  return FEC_OK;
+}
+
+int fec_engine_debug_fail_launches(fec_engine* e, uint32_t n)
+{
+  if (!e) {
+    return fail(FEC_ERR_BAD_ARG, "null engine");
+  }
+  e->debug_fail_launches.store(n);
+  return FEC_OK;
 }
 
 // ---- downlink twin: PDSCH codeblock encoding ---------------------------------------------------------------------------------
@@ -1658,7 +2099,8 @@ int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const 
     lo    = d.out_offset < lo ? (size_t)d.out_offset : lo;
     hi    = d.out_offset + out_len > hi ? (size_t)d.out_offset + out_len : hi;
   }
-  std::lock_guard<std::mutex> lk(e->run_mtx);
+  ctx_lease lease(e, 0); // the encoder staging is engine-wide: one call at a time, on context 0's pipeline streams
+  host_ctx& hx = *lease.c;
   CU_TRY(cudaSetDevice(e->cfg.device));
   int r = grow((void**)&e->d_enc_descs, &e->enc_descs_cap, (size_t)n * sizeof(fec_enc_desc));
   r     = (r == FEC_OK) ? grow((void**)&e->d_enc_in, &e->enc_in_cap, in_bytes) : r;
@@ -1708,22 +2150,22 @@ int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const 
     CU_TRY(cudaStreamSynchronize(e->stream));
     return FEC_OK;
   }
-  CU_TRY(cudaEventRecord(e->pipe_done[0], e->stream));
+  CU_TRY(cudaEventRecord(hx.pipe_done[0], e->stream));
   for (int k = 0; k < 3; ++k) {
-    CU_TRY(cudaStreamWaitEvent(e->pipe[k], e->pipe_done[0], 0));
+    CU_TRY(cudaStreamWaitEvent(hx.pipe[k], hx.pipe_done[0], 0));
   }
   for (uint32_t c = 0; c < spans.size(); ++c) {
     const span_t&  sp = spans[c];
     const uint32_t c0 = c * chunk, cn = (c + 1 == spans.size()) ? n - c0 : chunk;
-    cudaStream_t   ps = e->pipe[c % 3];
-    CU_TRY(cudaMemcpyAsync(e->d_enc_in + sp.i0, h_in + sp.i0, sp.i1 - sp.i0, cudaMemcpyHostToDevice, e->copy_in));
-    if (e->chunk_in.size() <= c) {
+    cudaStream_t   ps = hx.pipe[c % 3];
+    CU_TRY(cudaMemcpyAsync(e->d_enc_in + sp.i0, h_in + sp.i0, sp.i1 - sp.i0, cudaMemcpyHostToDevice, hx.copy_in));
+    if (hx.chunk_in.size() <= c) {
       cudaEvent_t ev = nullptr;
       CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-      e->chunk_in.push_back(ev);
+      hx.chunk_in.push_back(ev);
     }
-    CU_TRY(cudaEventRecord(e->chunk_in[c], e->copy_in));
-    CU_TRY(cudaStreamWaitEvent(ps, e->chunk_in[c], 0));
+    CU_TRY(cudaEventRecord(hx.chunk_in[c], hx.copy_in));
+    CU_TRY(cudaStreamWaitEvent(ps, hx.chunk_in[c], 0));
     CU_TRY(cudaMemsetAsync(e->d_enc_out + sp.o0, 0, sp.o1 - sp.o0, ps));
     fec_encode_kernel<<<cn, FEC_ENC_THREADS, 0, ps>>>(e->d_enc_descs + c0, e->d_enc_in, e->d_enc_out, e->d_tab);
     CU_TRY(cudaGetLastError());
@@ -1731,8 +2173,8 @@ int fec_encode_run_host(fec_engine* e, fec_enc_desc* h_descs, uint32_t n, const 
     CU_TRY(cudaMemcpyAsync(h_out + sp.o0, e->d_enc_out + sp.o0, sp.o1 - sp.o0, cudaMemcpyDeviceToHost, ps));
   }
   for (int k = 0; k < 3; ++k) {
-    CU_TRY(cudaEventRecord(e->pipe_done[k], e->pipe[k]));
-    CU_TRY(cudaStreamWaitEvent(e->stream, e->pipe_done[k], 0));
+    CU_TRY(cudaEventRecord(hx.pipe_done[k], hx.pipe[k]));
+    CU_TRY(cudaStreamWaitEvent(e->stream, hx.pipe_done[k], 0));
   }
   CU_TRY(cudaStreamSynchronize(e->stream));
   return FEC_OK;
@@ -1941,7 +2383,7 @@ int fec_demod_run_host(fec_engine* e, const fec_demod_desc* h_descs, uint32_t n,
   if (covered != l1 - l0 || !demod_calls_tile(h_descs, n, l0, l1)) {
     return fail(FEC_ERR_BAD_ARG, "the demodulation calls must tile one contiguous span of the LLR buffer");
   }
-  std::lock_guard<std::mutex> lk(e->run_mtx);
+  ctx_lease lease(e, 0); // the demodulator staging is engine-wide: one call at a time
   CU_TRY(cudaSetDevice(e->cfg.device));
   int rc = grow((void**)&e->d_dm_llr, &e->dm_llr_cap, l1 - l0);
   if (rc != FEC_OK) {

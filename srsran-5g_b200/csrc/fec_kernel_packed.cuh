@@ -27,6 +27,7 @@
 #include <string.h>
 
 #define FEC_PACKED_MAX_THREADS 192
+#define FEC_PACKED_CTAS_PER_SM 3u // resident codeblocks per SM at the largest lifting size (__launch_bounds__ below)
 
 // Edge (shift s = q * H + r into column col): thread t reads pair word (t + r) mod H of the column; its lanes come swapped
 // when q + [t + r >= H] is odd. The wrap is ONE unsigned min: with u = 4 t + c0 (negative, i.e. huge, while t + r < H),
@@ -1144,7 +1145,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #undef s_nsig
 // Dispatcher: every codeblock the packed path covers goes there, the rest (odd Z, dematch-only
 // operations, unaligned decoder inputs) runs the generic per-check code in the same launch.
-__global__ void __launch_bounds__(FEC_PACKED_MAX_THREADS, 3)
+__global__ void __launch_bounds__(FEC_PACKED_MAX_THREADS, FEC_PACKED_CTAS_PER_SM)
 fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
                      const int8_t* __restrict__ llr_base,
                      uint8_t* __restrict__ out_base,

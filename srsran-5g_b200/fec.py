@@ -26,7 +26,7 @@ MAX_TB_CBS = 162
 TB_SLOTS_CONTIGUOUS = 0xFFFFFFFF
 HARQ_SLOT_BYTES = 25344
 MAX_CB_OUT_BYTES = 1056
-ABI_VERSION = 6
+ABI_VERSION = 7
 NOALLOC_MAX_TBS, NOALLOC_MAX_CBS = 64, 2048
 
 ALL_Z = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48, 52, 56, 60,
@@ -83,7 +83,21 @@ DEMOD_DESC_DTYPE = np.dtype({
 class EngineCfg(C.Structure):
     _fields_ = [("device", C.c_int32), ("harq_slots", C.c_uint32), ("max_batch_cbs", C.c_uint32),
                 ("max_batch_llrs", C.c_uint32), ("nof_queues", C.c_uint32), ("scaling_factor", C.c_float),
-                ("kernel_variant", C.c_uint32), ("reserved", C.c_uint32)]
+                ("kernel_variant", C.c_uint32), ("reserved", C.c_uint32), ("host_contexts", C.c_uint32),
+                ("queue_batch_cbs", C.c_uint32), ("queue_batches", C.c_uint32), ("max_wait_us", C.c_uint32)]
+
+
+STATS_ITER_BINS = 16
+
+
+class EngineStats(C.Structure):
+    _fields_ = [("launches", C.c_uint64), ("cb_launches", C.c_uint64), ("codeblocks", C.c_uint64), ("results", C.c_uint64),
+                ("crc_pass", C.c_uint64), ("iterations_hist", C.c_uint64 * STATS_ITER_BINS), ("queue_full", C.c_uint64),
+                ("max_queue_depth", C.c_uint64), ("dispatches", C.c_uint64), ("dispatch_batches", C.c_uint64),
+                ("tb_calls", C.c_uint64), ("transport_blocks", C.c_uint64), ("tb_crc_ok", C.c_uint64), ("faults", C.c_uint64)]
+
+
+TB_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_uint32)
 
 
 class HarqPoolCfg(C.Structure):
@@ -103,7 +117,8 @@ EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_e
            "fec_demod_launch_device", "fec_demod_run_host", "fec_tb_run_host_symbols", "fec_harq_pool_create",
            "fec_harq_pool_destroy", "fec_harq_pool_reserve", "fec_harq_pool_codeblocks", "fec_harq_pool_unlock",
            "fec_harq_pool_release", "fec_harq_pool_run_slot", "fec_harq_pool_stop", "fec_harq_pool_nof_free_codeblocks",
-           "fec_tb_assemble_device_noalloc"]
+           "fec_tb_assemble_device_noalloc", "fec_engine_get_stats", "fec_engine_debug_fail_launches", "fec_tb_enqueue",
+           "fec_tb_poll", "fec_tb_wait"]
 
 _lib = None
 
@@ -154,6 +169,12 @@ def load_library():
     lib.fec_tb_run_host.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
                                     C.c_size_t, C.c_void_p, C.c_void_p]
     lib.fec_tb_reset_slots.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+    lib.fec_engine_get_stats.argtypes = [C.c_void_p, C.POINTER(EngineStats)]
+    lib.fec_engine_debug_fail_launches.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_tb_enqueue.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                   C.c_size_t, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+    lib.fec_tb_poll.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    lib.fec_tb_wait.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
     lib.fec_tb_assemble_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                                    C.c_size_t, C.c_void_p]
     lib.fec_enc_desc_prepare.argtypes = [C.c_void_p]
@@ -267,7 +288,7 @@ class FecEngine:
     """One engine per GPU (fec_engine_create). All decode work happens in the CUDA kernels behind the C ABI."""
 
     def __init__(self, device=0, harq_slots=4096, max_batch_cbs=2048, max_batch_llrs=0, nof_queues=8,
-                 scaling_factor=0.8, kernel_variant=0):
+                 scaling_factor=0.8, kernel_variant=0, host_contexts=0, queue_batch_cbs=0, queue_batches=0, max_wait_us=0):
         self.lib = load_library()
         cfg = EngineCfg()
         self.lib.fec_engine_default_cfg(C.byref(cfg))
@@ -278,6 +299,8 @@ class FecEngine:
         cfg.nof_queues = nof_queues
         cfg.scaling_factor = scaling_factor
         cfg.kernel_variant = kernel_variant
+        cfg.host_contexts, cfg.queue_batch_cbs, cfg.queue_batches = host_contexts, queue_batch_cbs, queue_batches
+        cfg.max_wait_us = max_wait_us
         self.cfg = cfg
         self.h = C.c_void_p()
         _check(self.lib, self.lib.fec_engine_create(C.byref(cfg), C.byref(self.h)))
@@ -360,6 +383,44 @@ class FecEngine:
         _check(self.lib, self.lib.fec_tb_run_host(self.h, tbs.ctypes.data, n, None if sl is None else sl.ctypes.data,
                                                   ptr(llr), size(llr), ptr(out), size(out), res.ctypes.data,
                                                   None if cbr is None else cbr.ctypes.data))
+        return (res, cbr.reshape(n, MAX_TB_CBS)) if cb_results else res
+
+    def stats(self):
+        """fec_engine_get_stats as a dict (iterations_hist as a list)."""
+        st = EngineStats()
+        _check(self.lib, self.lib.fec_engine_get_stats(self.h, C.byref(st)))
+        out = {name: int(getattr(st, name)) for name, _ in EngineStats._fields_ if name != "iterations_hist"}
+        out["iterations_hist"] = [int(x) for x in st.iterations_hist]
+        return out
+
+    def debug_fail_launches(self, n):
+        _check(self.lib, self.lib.fec_engine_debug_fail_launches(self.h, n))
+
+    def tb_enqueue(self, tbs, llr, out, slots=None, callback=None):
+        """fec_tb_enqueue: asynchronous transport-block call. llr / out: numpy buffers or (ptr, nbytes) of pinned memory; they
+        (and `callback`, a TB_CALLBACK instance) must stay alive until completion. Returns the ticket; raises FecError with
+        code FEC_ERR_QUEUE_FULL (-5) in the message when every host-call context is in flight."""
+        assert tbs.dtype == TB_DESC_DTYPE and tbs.flags.c_contiguous
+
+        def ps(a):
+            return (a[0], a[1]) if isinstance(a, tuple) else (a.ctypes.data, a.nbytes)
+
+        (lp, lb), (op, ob) = ps(llr), ps(out)
+        sl = None if slots is None else np.ascontiguousarray(slots, np.uint32)
+        ticket = C.c_uint64()
+        _check(self.lib, self.lib.fec_tb_enqueue(self.h, tbs.ctypes.data, tbs.size, None if sl is None else sl.ctypes.data,
+                                                 lp, lb, op, ob, C.cast(callback, C.c_void_p) if callback else None, None,
+                                                 C.byref(ticket)))
+        return ticket.value
+
+    def tb_poll(self, ticket, n, cb_results=False, wait=False):
+        """fec_tb_poll / fec_tb_wait: None while the call is still running, else the results (and codeblock results)."""
+        res = np.zeros(n, TB_RESULT_DTYPE)
+        cbr = np.zeros(n * MAX_TB_CBS, RESULT_DTYPE) if cb_results else None
+        f = self.lib.fec_tb_wait if wait else self.lib.fec_tb_poll
+        rc = _check(self.lib, f(self.h, ticket, res.ctypes.data, None if cbr is None else cbr.ctypes.data))
+        if not wait and rc == 0:
+            return None
         return (res, cbr.reshape(n, MAX_TB_CBS)) if cb_results else res
 
     def tb_assemble_device_noalloc(self, tbs, d_cb_msgs_ptr, d_cb_results_ptr, d_out_ptr, out_bytes, d_tb_results_ptr):
