@@ -87,7 +87,7 @@ typedef struct fec_cb_desc {
   uint8_t  mode;            /* FEC_MODE_*                                                                             */
   uint8_t  flags;           /* FEC_FLAG_*                                                                             */
   uint8_t  reserved0;
-  uint32_t reserved1;
+  uint32_t reserved1;       /* bits 32..63 of out_offset (0 for output buffers below 4 GiB; the engine's batcher uses it)  */
 } fec_cb_desc;
 
 /* fec_cb_result.status bits */
@@ -197,12 +197,20 @@ int fec_harq_write(fec_engine* e, uint32_t slot, const int8_t* h_src, uint32_t n
 
 /* ---- queue interface: the shape hal::hw_accelerator_pusch_dec needs ----------------------------------------------- */
 /* One queue per accelerator instance / submitting thread. enqueue copies the LLRs into pinned staging and returns
- * immediately (FEC_ERR_QUEUE_FULL when the staging ring is full: the caller retries, it never blocks). A batch is
- * launched when it reaches max_batch_cbs or on fec_queue_flush(). poll is non-blocking and returns the number of
- * completed operations written to tags/results (at most `max`); decoded bytes are copied out with fec_queue_fetch(). */
+ * immediately (FEC_ERR_QUEUE_FULL when the staging ring is full: the caller retries, it never blocks). A batch is handed
+ * to the engine's cross-queue batcher when it reaches fec_engine_cfg.queue_batch_cbs or on fec_queue_flush(): whichever
+ * thread finds the batcher free launches EVERY batch that is waiting, of every queue, as one kernel (many codeblocks of
+ * many UEs and cells per wave); fec_engine_cfg.max_wait_us lets a launch that is less than one wave wait for company.
+ * poll is non-blocking and returns the number of completed operations written to tags/results (at most `max`); decoded
+ * bytes are copied out with fec_queue_fetch(). */
 int fec_queue_reserve(fec_engine* e, uint32_t* queue_id);
 int fec_queue_free(fec_engine* e, uint32_t queue_id);
 int fec_queue_enqueue(fec_engine* e, uint32_t queue_id, const fec_cb_desc* desc, const int8_t* llr, uint64_t tag);
+/* Several operations in one call (one lock, parameters shared by consecutive descriptors checked once): the codeblocks of a
+ * transport block. *accepted = how many were taken, in order; fewer than n means the ring filled up (FEC_OK if any was
+ * taken, FEC_ERR_QUEUE_FULL if none): poll, then come back with the rest. */
+int fec_queue_enqueue_batch(fec_engine* e, uint32_t queue_id, const fec_cb_desc* descs, const int8_t* const* llrs,
+                            const uint64_t* tags, uint32_t n, uint32_t* accepted);
 int fec_queue_flush(fec_engine* e, uint32_t queue_id);
 int fec_queue_poll(fec_engine* e, uint32_t queue_id, uint64_t* tags, fec_cb_result* results, uint32_t max);
 /* Copies the decoded bytes of a completed (polled) operation; valid until the next fec_queue_enqueue after a poll

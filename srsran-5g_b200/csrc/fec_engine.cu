@@ -123,8 +123,14 @@ void build_tables(fec_dev_tables& t, float sf)
   }
 }
 
+// One batch of a queue: pinned host staging, its own slice of device memory, and the state machine
+//   FREE -> FILLING (enqueue) -> PENDING (handed to the batcher) -> INFLIGHT (copies and kernel issued) -> DONE (event seen).
+// The owner of the queue touches a batch under queue_t::mtx; the batcher (whichever thread holds fec_engine::disp_mtx) only
+// moves PENDING batches to INFLIGHT, publishing with a release store of `state`.
 struct batch_slot {
-  enum state_t { FREE, FILLING, INFLIGHT, DONE } state = FREE;
+  enum state_t { FREE, FILLING, PENDING, INFLIGHT, DONE };
+  std::atomic<int> state{FREE};
+  std::atomic<bool> failed{false}; // the dispatch that carried this batch failed: every operation reports a failed codeblock
   uint32_t      n        = 0;
   uint32_t      llr_used = 0;
   uint32_t      out_used = 0;
@@ -132,29 +138,36 @@ struct batch_slot {
   uint32_t      max_Z    = 0;
   int           any_bg1  = 0;
   uint64_t      seq      = 0;
-  fec_cb_desc*  h_descs  = nullptr; // pinned
+  fec_cb_desc*  h_descs  = nullptr; // pinned; llr_offset / out_offset relative to this batch's d_llr / d_out
   uint64_t*     tags     = nullptr;
   int8_t*       h_llr    = nullptr; // pinned
   uint8_t*      h_out    = nullptr; // pinned
   fec_cb_result* h_res   = nullptr; // pinned
-  fec_cb_desc*  d_descs  = nullptr;
   int8_t*       d_llr    = nullptr;
   uint8_t*      d_out    = nullptr;
-  fec_cb_result* d_res   = nullptr;
   cudaEvent_t   done     = nullptr;
+  std::chrono::steady_clock::time_point t_pending;
 };
-
-constexpr int SLOTS_PER_QUEUE = 4;
 
 struct queue_t {
   std::mutex   mtx;
   bool         reserved = false;
   bool         inited   = false;
-  cudaStream_t stream   = nullptr;
-  batch_slot   slots[SLOTS_PER_QUEUE];
+  std::vector<batch_slot*> slots;
   int          filling  = -1;
   uint64_t     next_seq = 1;
+  uint32_t     depth    = 0; // operations staged or in flight (not yet polled)
 };
+
+// Resources of one dispatch of the cross-queue batcher: the combined descriptor array and the results of one launch.
+struct dispatch_res {
+  fec_cb_desc*   h_descs = nullptr; // pinned
+  fec_cb_desc*   d_descs = nullptr;
+  fec_cb_result* d_res   = nullptr;
+  cudaEvent_t    done    = nullptr; // the launch and every copy of the dispatch have finished: the set can be reused
+  bool           used    = false;
+};
+constexpr int DISPATCH_RING = 8;
 
 // One host-call context: the stream set, device staging and pinned bounce buffers one fec_run_host / transport-block call
 // works in. An engine owns several, so that calls from different threads run concurrently (each on its own streams) instead
@@ -228,6 +241,15 @@ struct fec_engine {
   std::condition_variable ctx_cv;
   std::vector<queue_t>* queues = nullptr;
   std::mutex            queues_mtx;
+  // cross-queue batcher: batches handed over by the queues, dispatched by whichever thread gets disp_mtx (no thread of its own)
+  std::mutex               pend_mtx;
+  std::vector<batch_slot*> pending;
+  std::atomic<uint32_t>    pending_count{0};
+  std::mutex               disp_mtx;
+  dispatch_res             disp[DISPATCH_RING];
+  uint32_t                 disp_next = 0;
+  cudaStream_t             disp_stream[3] = {nullptr, nullptr, nullptr};
+  uint32_t                 disp_cap = 0; // codeblocks one dispatch can carry
   // transport-block layer (allocated on first use)
   std::mutex            tb_alloc_mtx;
   std::atomic<uint8_t>* cb_ok    = nullptr; // per HARQ slot: the codeblock's CRC passed in an earlier transmission
@@ -500,54 +522,196 @@ struct ctx_lease {
   }
 };
 
+uint32_t queue_batch_cbs(const fec_engine* e)
+{
+  return e->cfg.queue_batch_cbs ? e->cfg.queue_batch_cbs : e->cfg.max_batch_cbs;
+}
+
+size_t queue_batch_llrs(const fec_engine* e)
+{
+  // staging bytes of one batch: every codeblock of it at the largest rate-matched length the engine stages, capped by the
+  // engine-wide staging limit
+  const size_t all = (size_t)queue_batch_cbs(e) * 25344u;
+  return all < e->cfg.max_batch_llrs ? all : e->cfg.max_batch_llrs;
+}
+
 int slot_alloc(fec_engine* e, batch_slot& s)
 {
-  const uint32_t nc = e->cfg.max_batch_cbs;
-  const size_t   nl = e->cfg.max_batch_llrs;
+  const uint32_t nc = queue_batch_cbs(e);
+  const size_t   nl = queue_batch_llrs(e);
   CU_TRY(cudaHostAlloc((void**)&s.h_descs, nc * sizeof(fec_cb_desc), cudaHostAllocDefault));
   CU_TRY(cudaHostAlloc((void**)&s.h_llr, nl, cudaHostAllocDefault));
   CU_TRY(cudaHostAlloc((void**)&s.h_out, (size_t)nc * FEC_MAX_CB_OUT_BYTES, cudaHostAllocDefault));
   CU_TRY(cudaHostAlloc((void**)&s.h_res, nc * sizeof(fec_cb_result), cudaHostAllocDefault));
   s.tags = new (std::nothrow) uint64_t[nc];
-  CU_TRY(cudaMalloc((void**)&s.d_descs, nc * sizeof(fec_cb_desc)));
   CU_TRY(cudaMalloc((void**)&s.d_llr, nl));
   CU_TRY(cudaMalloc((void**)&s.d_out, (size_t)nc * FEC_MAX_CB_OUT_BYTES));
-  CU_TRY(cudaMalloc((void**)&s.d_res, nc * sizeof(fec_cb_result)));
   CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
   return FEC_OK;
 }
 
-void slot_free(batch_slot& s)
+void slot_free(batch_slot* s)
 {
-  cudaFreeHost(s.h_descs);
-  cudaFreeHost(s.h_llr);
-  cudaFreeHost(s.h_out);
-  cudaFreeHost(s.h_res);
-  delete[] s.tags;
-  cudaFree(s.d_descs);
-  cudaFree(s.d_llr);
-  cudaFree(s.d_out);
-  cudaFree(s.d_res);
-  if (s.done) {
-    cudaEventDestroy(s.done);
+  if (!s) {
+    return;
   }
-  s = batch_slot();
+  cudaFreeHost(s->h_descs);
+  cudaFreeHost(s->h_llr);
+  cudaFreeHost(s->h_out);
+  cudaFreeHost(s->h_res);
+  delete[] s->tags;
+  cudaFree(s->d_llr);
+  cudaFree(s->d_out);
+  if (s->done) {
+    cudaEventDestroy(s->done);
+  }
+  delete s;
 }
 
-int queue_launch_slot(fec_engine* e, queue_t& q, batch_slot& s)
+// ---- cross-queue batcher ---------------------------------------------------------------------------------------------------
+// Queues hand their full (or flushed) batches over; whichever thread gets disp_mtx dispatches EVERYTHING that is pending, of
+// every queue, as one launch: one combined descriptor array (buffer positions as absolute device addresses: the kernel is given
+// null base pointers), one kernel over all the codeblocks, the copies of each batch in front of and behind it, one event per
+// batch. A thread that finds the lock taken leaves its batch to the holder and returns at once; progress is guaranteed
+// because every poll tries again. With max_wait_us > 0 a dispatch that holds less than one kernel wave waits that long
+// (since its oldest batch was handed over) for other queues to join: fewer, fuller launches under load, bounded added latency.
+int disp_resources(fec_engine* e)
 {
-  CU_TRY(cudaSetDevice(e->cfg.device));
-  CU_TRY(cudaMemcpyAsync(s.d_descs, s.h_descs, s.n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, q.stream));
-  CU_TRY(cudaMemcpyAsync(s.d_llr, s.h_llr, s.llr_used, cudaMemcpyHostToDevice, q.stream));
-  int r = launch(e, q.stream, s.d_descs, s.n, s.d_llr, s.d_out, s.d_res, s.max_Z, s.any_bg1);
-  if (r != FEC_OK) {
-    return r;
+  if (e->disp_cap != 0) {
+    return FEC_OK;
   }
-  CU_TRY(cudaMemcpyAsync(s.h_out, s.d_out, s.out_used, cudaMemcpyDeviceToHost, q.stream));
-  CU_TRY(cudaMemcpyAsync(s.h_res, s.d_res, s.n * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, q.stream));
-  CU_TRY(cudaEventRecord(s.done, q.stream));
-  s.state = batch_slot::INFLIGHT;
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  const uint32_t cap = queue_batch_cbs(e) * 8u > e->cfg.max_batch_cbs ? queue_batch_cbs(e) * 8u : e->cfg.max_batch_cbs;
+  for (dispatch_res& r : e->disp) {
+    CU_TRY(cudaHostAlloc((void**)&r.h_descs, (size_t)cap * sizeof(fec_cb_desc), cudaHostAllocDefault));
+    CU_TRY(cudaMalloc((void**)&r.d_descs, (size_t)cap * sizeof(fec_cb_desc)));
+    CU_TRY(cudaMalloc((void**)&r.d_res, (size_t)cap * sizeof(fec_cb_result)));
+    CU_TRY(cudaEventCreateWithFlags(&r.done, cudaEventDisableTiming));
+  }
+  for (cudaStream_t& st : e->disp_stream) {
+    CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  }
+  e->disp_cap = cap;
   return FEC_OK;
+}
+
+// Issues one launch for the given batches (all PENDING). On failure they are marked failed and still become INFLIGHT / done.
+void dispatch_batches(fec_engine* e, batch_slot** b, size_t nb)
+{
+  cudaSetDevice(e->cfg.device);
+  dispatch_res& r = e->disp[e->disp_next % DISPATCH_RING];
+  cudaStream_t  st = e->disp_stream[e->disp_next % 3];
+  ++e->disp_next;
+  bool ok = true;
+  if (r.used) {
+    ok = cudaEventSynchronize(r.done) == cudaSuccess; // eight dispatches ago: normally long done
+  }
+  uint32_t n = 0, max_Z = 0;
+  int      any1 = 0;
+  for (size_t k = 0; k < nb; ++k) {
+    batch_slot& s = *b[k];
+    for (uint32_t i = 0; i < s.n; ++i) {
+      fec_cb_desc d = s.h_descs[i];
+      const uint64_t out = (uint64_t)(uintptr_t)s.d_out + d.out_offset;
+      d.llr_offset += (uint64_t)(uintptr_t)s.d_llr; // absolute device addresses: the launch passes null base pointers
+      d.out_offset = (uint32_t)out;
+      d.reserved1  = (uint32_t)(out >> 32);
+      r.h_descs[n + i] = d;
+    }
+    n += s.n;
+    max_Z = s.max_Z > max_Z ? s.max_Z : max_Z;
+    any1 |= s.any_bg1;
+  }
+  ok = ok && cudaMemcpyAsync(r.d_descs, r.h_descs, (size_t)n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, st) == cudaSuccess;
+  for (size_t k = 0; k < nb && ok; ++k) {
+    ok = cudaMemcpyAsync(b[k]->d_llr, b[k]->h_llr, b[k]->llr_used, cudaMemcpyHostToDevice, st) == cudaSuccess;
+  }
+  ok = ok && launch(e, st, r.d_descs, n, nullptr, nullptr, r.d_res, max_Z, any1) == FEC_OK;
+  uint32_t at = 0;
+  for (size_t k = 0; k < nb; ++k) {
+    batch_slot& s = *b[k];
+    if (ok) {
+      ok = cudaMemcpyAsync(s.h_out, s.d_out, s.out_used, cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+           cudaMemcpyAsync(s.h_res, r.d_res + at, s.n * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st) == cudaSuccess;
+    }
+    at += s.n;
+    if (!ok) {
+      cudaGetLastError();
+      s.failed.store(true);
+    }
+    cudaEventRecord(s.done, st);
+    s.state.store(batch_slot::INFLIGHT, std::memory_order_release);
+  }
+  cudaEventRecord(r.done, st);
+  r.used = true;
+  if (!ok) {
+    e->st_faults.fetch_add(1, std::memory_order_relaxed);
+  }
+  e->st_dispatches.fetch_add(1, std::memory_order_relaxed);
+  e->st_dispatch_slots.fetch_add(nb, std::memory_order_relaxed);
+}
+
+void dispatch_try(fec_engine* e)
+{
+  while (e->pending_count.load(std::memory_order_acquire) != 0) {
+    if (!e->disp_mtx.try_lock()) {
+      return; // the holder looks at the list again before it lets go, and every poll comes back here
+    }
+    std::vector<batch_slot*> take;
+    {
+      std::lock_guard<std::mutex> lk(e->pend_mtx);
+      take.swap(e->pending);
+      e->pending_count.store(0, std::memory_order_release);
+    }
+    if (!take.empty() && e->cfg.max_wait_us != 0) {
+      const uint32_t wave = FEC_PACKED_CTAS_PER_SM * (uint32_t)e->sm_count;
+      const auto     until = take.front()->t_pending + std::chrono::microseconds(e->cfg.max_wait_us);
+      for (;;) {
+        uint32_t n = 0;
+        for (batch_slot* s : take) {
+          n += s->n;
+        }
+        if (n >= wave || std::chrono::steady_clock::now() >= until) {
+          break;
+        }
+        if (e->pending_count.load(std::memory_order_acquire) != 0) {
+          std::lock_guard<std::mutex> lk(e->pend_mtx);
+          take.insert(take.end(), e->pending.begin(), e->pending.end());
+          e->pending.clear();
+          e->pending_count.store(0, std::memory_order_release);
+        } else {
+          std::this_thread::yield();
+        }
+      }
+    }
+    // as many launches as the combined descriptor array asks for (normally one)
+    size_t k0 = 0;
+    while (k0 < take.size()) {
+      size_t   k1 = k0;
+      uint32_t n  = 0;
+      while (k1 < take.size() && (k1 == k0 || n + take[k1]->n <= e->disp_cap)) {
+        n += take[k1]->n;
+        ++k1;
+      }
+      dispatch_batches(e, take.data() + k0, k1 - k0);
+      k0 = k1;
+    }
+    e->disp_mtx.unlock();
+  }
+}
+
+// Hands a filled batch to the batcher and tries to dispatch.
+void queue_submit_slot(fec_engine* e, batch_slot& s)
+{
+  s.t_pending = std::chrono::steady_clock::now();
+  s.failed.store(false);
+  s.state.store(batch_slot::PENDING, std::memory_order_release);
+  {
+    std::lock_guard<std::mutex> lk(e->pend_mtx);
+    e->pending.push_back(&s);
+    e->pending_count.fetch_add(1, std::memory_order_release);
+  }
+  dispatch_try(e);
 }
 
 } // namespace
@@ -721,14 +885,24 @@ void fec_engine_destroy(fec_engine* e)
   cudaDeviceSynchronize();
   if (e->queues) {
     for (auto& q : *e->queues) {
-      if (q.inited) {
-        for (auto& s : q.slots) {
-          slot_free(s);
-        }
-        cudaStreamDestroy(q.stream);
+      for (batch_slot* s : q.slots) {
+        slot_free(s);
       }
     }
     delete e->queues;
+  }
+  for (dispatch_res& r : e->disp) {
+    cudaFreeHost(r.h_descs);
+    cudaFree(r.d_descs);
+    cudaFree(r.d_res);
+    if (r.done) {
+      cudaEventDestroy(r.done);
+    }
+  }
+  for (cudaStream_t st : e->disp_stream) {
+    if (st) {
+      cudaStreamDestroy(st);
+    }
   }
   for (host_ctx* c : e->ctxs) {
     ctx_destroy(c);
@@ -815,7 +989,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     }
     const fec_cb_desc& d  = h_descs[i];
     const uint32_t     kb = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
-    if (d.llr_offset + d.E > llr_bytes || (d.mode != FEC_MODE_DEMATCH && (size_t)d.out_offset + kb > out_bytes)) {
+    if (d.reserved1 != 0 || d.llr_offset + d.E > llr_bytes || (d.mode != FEC_MODE_DEMATCH && (size_t)d.out_offset + kb > out_bytes)) {
       return fail(FEC_ERR_BAD_ARG, "descriptor %u indexes outside the batch buffers", i);
     }
     if (d.mode != FEC_MODE_DECODE && d.harq_slot >= e->cfg.harq_slots) {
@@ -1069,16 +1243,25 @@ int fec_queue_reserve(fec_engine* e, uint32_t* queue_id)
     return fail(FEC_ERR_BAD_ARG, "null argument");
   }
   std::lock_guard<std::mutex> lk(e->queues_mtx);
+  int rc = disp_resources(e);
+  if (rc != FEC_OK) {
+    return rc;
+  }
   for (uint32_t i = 0; i < e->queues->size(); ++i) {
     queue_t& q = (*e->queues)[i];
     if (!q.reserved) {
       if (!q.inited) {
         CU_TRY(cudaSetDevice(e->cfg.device));
-        CU_TRY(cudaStreamCreateWithFlags(&q.stream, cudaStreamNonBlocking));
-        for (auto& s : q.slots) {
-          int r = slot_alloc(e, s);
-          if (r != FEC_OK) {
-            return r;
+        const uint32_t nb = e->cfg.queue_batches ? e->cfg.queue_batches : 4u;
+        for (uint32_t k = 0; k < nb; ++k) {
+          batch_slot* s = new (std::nothrow) batch_slot();
+          if (!s) {
+            return fail(FEC_ERR_NO_MEMORY, "host allocation failed");
+          }
+          q.slots.push_back(s);
+          rc = slot_alloc(e, *s);
+          if (rc != FEC_OK) {
+            return rc;
           }
         }
         q.inited = true;
@@ -1098,72 +1281,69 @@ int fec_queue_free(fec_engine* e, uint32_t queue_id)
   }
   queue_t&                    q = (*e->queues)[queue_id];
   std::lock_guard<std::mutex> lk(q.mtx);
-  if (q.inited) {
-    cudaStreamSynchronize(q.stream);
-    for (auto& s : q.slots) {
-      s.state = batch_slot::FREE;
-      s.n = s.llr_used = s.out_used = s.polled = 0;
+  for (batch_slot* s : q.slots) {
+    // whatever was handed to the batcher gets dispatched and finishes before the batch is recycled
+    while (s->state.load(std::memory_order_acquire) == batch_slot::PENDING) {
+      dispatch_try(e);
+      std::this_thread::yield();
     }
+    if (s->state.load(std::memory_order_acquire) == batch_slot::INFLIGHT) {
+      cudaEventSynchronize(s->done);
+    }
+    s->state.store(batch_slot::FREE);
+    s->n = s->llr_used = s->out_used = s->polled = 0;
   }
   q.filling  = -1;
+  q.depth    = 0;
   q.reserved = false;
   return FEC_OK;
 }
 
-int fec_queue_enqueue(fec_engine* e, uint32_t queue_id, const fec_cb_desc* desc, const int8_t* llr, uint64_t tag)
+namespace {
+// Under q.mtx. Stages one prepared operation; FEC_ERR_QUEUE_FULL when every batch of the ring is taken.
+int queue_stage(fec_engine* e, uint32_t queue_id, queue_t& q, fec_cb_desc& d, const int8_t* llr, uint64_t tag)
 {
-  if (!e || queue_id >= e->queues->size() || !desc || !llr) {
-    return fail(FEC_ERR_BAD_QUEUE, "bad queue %u or null argument", queue_id);
-  }
-  fec_cb_desc d = *desc;
-  int         r = fec_desc_prepare(&d);
-  if (r != FEC_OK) {
-    return r;
-  }
-  if (d.mode != FEC_MODE_DECODE && d.harq_slot >= e->cfg.harq_slots) {
-    return fail(FEC_ERR_BAD_ARG, "harq_slot %u >= %u", d.harq_slot, e->cfg.harq_slots);
-  }
   const uint32_t kb      = (((d.base_graph == 1) ? 22u : 10u) * d.lifting_size + 7) / 8;
   const uint32_t llr_pad = (d.E + 15u) & ~15u;
-  if (llr_pad > e->cfg.max_batch_llrs) {
-    return fail(FEC_ERR_BAD_ARG, "E=%u exceeds the staging capacity", d.E);
-  }
-  queue_t&                    q = (*e->queues)[queue_id];
-  std::lock_guard<std::mutex> lk(q.mtx);
-  if (!q.reserved) {
-    return fail(FEC_ERR_BAD_QUEUE, "queue %u is not reserved", queue_id);
+  const uint32_t cap_cbs = queue_batch_cbs(e);
+  const size_t   cap_llr = queue_batch_llrs(e);
+  if (llr_pad > cap_llr) {
+    return fail(FEC_ERR_BAD_ARG, "E=%u exceeds the staging capacity of a queue batch", d.E);
   }
   for (int attempt = 0; attempt < 2; ++attempt) {
     if (q.filling < 0) {
-      // Recycle the oldest fully polled slot, or take a free one.
+      // Recycle the oldest fully polled batch, or take a free one.
       int      pick = -1;
       uint64_t best = ~0ull;
-      for (int i = 0; i < SLOTS_PER_QUEUE; ++i) {
-        batch_slot& s = q.slots[i];
-        if (s.state == batch_slot::FREE) {
-          pick = i;
+      for (size_t i = 0; i < q.slots.size(); ++i) {
+        batch_slot& s  = *q.slots[i];
+        const int   st = s.state.load(std::memory_order_acquire);
+        if (st == batch_slot::FREE) {
+          pick = (int)i;
           break;
         }
-        if (s.state == batch_slot::DONE && s.polled == s.n && s.seq < best) {
+        if (st == batch_slot::DONE && s.polled == s.n && s.seq < best) {
           best = s.seq;
-          pick = i;
+          pick = (int)i;
         }
       }
       if (pick < 0) {
-        return fail(FEC_ERR_QUEUE_FULL, "queue %u: all batch slots are in flight", queue_id);
+        e->st_queue_full.fetch_add(1, std::memory_order_relaxed);
+        return fail(FEC_ERR_QUEUE_FULL, "queue %u: all batches are staged or in flight", queue_id);
       }
-      batch_slot& s = q.slots[pick];
-      s.state       = batch_slot::FILLING;
+      batch_slot& s = *q.slots[pick];
+      s.state.store(batch_slot::FILLING);
       s.n = s.llr_used = s.out_used = s.polled = 0;
       s.max_Z                                  = 0;
       s.any_bg1                                = 0;
       s.seq                                    = q.next_seq++;
       q.filling                                = pick;
     }
-    batch_slot& s = q.slots[q.filling];
-    if (s.n < e->cfg.max_batch_cbs && s.llr_used + llr_pad <= e->cfg.max_batch_llrs) {
+    batch_slot& s = *q.slots[q.filling];
+    if (s.n < cap_cbs && s.llr_used + llr_pad <= cap_llr) {
       d.llr_offset = s.llr_used;
       d.out_offset = s.out_used;
+      d.reserved1  = 0;
       memcpy(s.h_llr + s.llr_used, llr, d.E);
       apply_fresh(e, d); // only once the operation is certain to be accepted
       s.h_descs[s.n] = d;
@@ -1174,20 +1354,76 @@ int fec_queue_enqueue(fec_engine* e, uint32_t queue_id, const fec_cb_desc* desc,
       s.out_used += (kb + 15u) & ~15u;
       s.max_Z = d.lifting_size > s.max_Z ? d.lifting_size : s.max_Z;
       s.any_bg1 |= (d.base_graph == 1);
-      if (s.n == e->cfg.max_batch_cbs) {
+      ++q.depth;
+      uint64_t seen = e->st_max_depth.load(std::memory_order_relaxed);
+      while (q.depth > seen && !e->st_max_depth.compare_exchange_weak(seen, q.depth)) {
+      }
+      if (s.n == cap_cbs) {
         q.filling = -1;
-        return queue_launch_slot(e, q, s);
+        queue_submit_slot(e, s); // a full batch goes out while the consumer is still enqueuing
       }
       return FEC_OK;
     }
-    // Current batch cannot take it: launch it and try a fresh slot.
+    // Current batch cannot take it: hand it over and try a fresh one.
     q.filling = -1;
-    r         = queue_launch_slot(e, q, s);
+    queue_submit_slot(e, s);
+  }
+  e->st_queue_full.fetch_add(1, std::memory_order_relaxed);
+  return fail(FEC_ERR_QUEUE_FULL, "queue %u: no room", queue_id);
+}
+} // namespace
+
+int fec_queue_enqueue_batch(fec_engine* e, uint32_t queue_id, const fec_cb_desc* descs, const int8_t* const* llrs,
+                            const uint64_t* tags, uint32_t n, uint32_t* accepted)
+{
+  if (accepted) {
+    *accepted = 0;
+  }
+  if (!e || queue_id >= e->queues->size() || !descs || !llrs || !tags || !accepted) {
+    return fail(FEC_ERR_BAD_QUEUE, "bad queue %u or null argument", queue_id);
+  }
+  queue_t&                    q = (*e->queues)[queue_id];
+  std::lock_guard<std::mutex> lk(q.mtx);
+  if (!q.reserved) {
+    return fail(FEC_ERR_BAD_QUEUE, "queue %u is not reserved", queue_id);
+  }
+  fec_cb_desc prev = {};
+  for (uint32_t i = 0; i < n; ++i) {
+    fec_cb_desc d = descs[i];
+    // the codeblocks of one transport block share their parameters: checked and derived fields are inherited
+    if (i > 0 && same_shape(d, descs[i - 1])) {
+      d.k0          = prev.k0;
+      d.graph_index = prev.graph_index;
+    } else {
+      const int r = fec_desc_prepare(&d);
+      if (r != FEC_OK) {
+        return r;
+      }
+    }
+    prev = d;
+    if (d.mode != FEC_MODE_DECODE && d.harq_slot >= e->cfg.harq_slots) {
+      return fail(FEC_ERR_BAD_ARG, "operation %u: harq_slot %u >= %u", i, d.harq_slot, e->cfg.harq_slots);
+    }
+    if (!llrs[i]) {
+      return fail(FEC_ERR_BAD_ARG, "operation %u: null LLR pointer", i);
+    }
+    const int r = queue_stage(e, queue_id, q, d, llrs[i], tags[i]);
+    if (r == FEC_ERR_QUEUE_FULL) {
+      return (*accepted != 0) ? FEC_OK : r; // the caller drains and comes back with the rest
+    }
     if (r != FEC_OK) {
       return r;
     }
+    ++*accepted;
   }
-  return fail(FEC_ERR_QUEUE_FULL, "queue %u: no room", queue_id);
+  return FEC_OK;
+}
+
+int fec_queue_enqueue(fec_engine* e, uint32_t queue_id, const fec_cb_desc* desc, const int8_t* llr, uint64_t tag)
+{
+  uint32_t  accepted = 0;
+  const int r        = fec_queue_enqueue_batch(e, queue_id, desc, &llr, &tag, 1, &accepted);
+  return (r == FEC_OK && accepted == 0) ? FEC_ERR_QUEUE_FULL : r;
 }
 
 int fec_queue_flush(fec_engine* e, uint32_t queue_id)
@@ -1195,16 +1431,20 @@ int fec_queue_flush(fec_engine* e, uint32_t queue_id)
   if (!e || queue_id >= e->queues->size()) {
     return fail(FEC_ERR_BAD_QUEUE, "bad queue %u", queue_id);
   }
-  queue_t&                    q = (*e->queues)[queue_id];
-  std::lock_guard<std::mutex> lk(q.mtx);
-  if (q.filling >= 0) {
-    batch_slot& s = q.slots[q.filling];
-    q.filling     = -1;
-    if (s.n > 0) {
-      return queue_launch_slot(e, q, s);
+  queue_t& q = (*e->queues)[queue_id];
+  {
+    std::lock_guard<std::mutex> lk(q.mtx);
+    if (q.filling >= 0) {
+      batch_slot& s = *q.slots[q.filling];
+      q.filling     = -1;
+      if (s.n > 0) {
+        queue_submit_slot(e, s);
+        return FEC_OK;
+      }
+      s.state.store(batch_slot::FREE);
     }
-    s.state = batch_slot::FREE;
   }
+  dispatch_try(e);
   return FEC_OK;
 }
 
@@ -1213,44 +1453,53 @@ int fec_queue_poll(fec_engine* e, uint32_t queue_id, uint64_t* tags, fec_cb_resu
   if (!e || queue_id >= e->queues->size() || !tags || !results) {
     return fail(FEC_ERR_BAD_QUEUE, "bad queue %u or null argument", queue_id);
   }
+  dispatch_try(e); // batches left with a busy batcher (this queue's or another's) go out now
   queue_t&                    q = (*e->queues)[queue_id];
   std::lock_guard<std::mutex> lk(q.mtx);
   uint32_t                    got = 0;
   // Report in submission order.
-  for (int pass = 0; pass < SLOTS_PER_QUEUE && got < max; ++pass) {
+  for (size_t pass = 0; pass < q.slots.size() && got < max; ++pass) {
     int      pick = -1;
     uint64_t best = ~0ull;
-    for (int i = 0; i < SLOTS_PER_QUEUE; ++i) {
-      batch_slot& s = q.slots[i];
-      if ((s.state == batch_slot::INFLIGHT || (s.state == batch_slot::DONE && s.polled < s.n)) && s.seq < best) {
+    for (size_t i = 0; i < q.slots.size(); ++i) {
+      batch_slot& s  = *q.slots[i];
+      const int   st = s.state.load(std::memory_order_acquire);
+      if ((st == batch_slot::PENDING || st == batch_slot::INFLIGHT || (st == batch_slot::DONE && s.polled < s.n)) && s.seq < best) {
         best = s.seq;
-        pick = i;
+        pick = (int)i;
       }
     }
     if (pick < 0) {
       break;
     }
-    batch_slot& s = q.slots[pick];
-    if (s.state == batch_slot::INFLIGHT) {
+    batch_slot& s = *q.slots[pick];
+    if (s.state.load(std::memory_order_acquire) == batch_slot::PENDING) {
+      break; // not dispatched yet
+    }
+    if (s.state.load(std::memory_order_acquire) == batch_slot::INFLIGHT) {
       cudaError_t st = cudaEventQuery(s.done);
       if (st == cudaErrorNotReady) {
         break;
       }
-      if (st != cudaSuccess) {
+      if (st != cudaSuccess || s.failed.load()) {
         // A device fault must surface as failed codeblocks, never as a hang (the consumer's poll loop has no timeout).
         cudaGetLastError();
         for (uint32_t i = 0; i < s.n; ++i) {
           s.h_res[i].status              = FEC_RES_DONE;
           s.h_res[i].nof_ldpc_iterations = s.h_descs[i].max_iter;
+          s.h_res[i].nof_layers          = 0;
+          s.h_res[i].reserved            = 0;
         }
       }
-      s.state = batch_slot::DONE;
+      s.state.store(batch_slot::DONE);
     }
     while (s.polled < s.n && got < max) {
       tags[got]    = s.tags[s.polled];
       results[got] = s.h_res[s.polled];
+      stats_result(e, results[got]);
       ++got;
       ++s.polled;
+      --q.depth;
     }
   }
   return (int)got;
@@ -1265,21 +1514,21 @@ int fec_queue_fetch(fec_engine* e, uint32_t queue_id, uint64_t tag, uint8_t* dst
   std::lock_guard<std::mutex> lk(q.mtx);
   // Newest batch first: tags are caller-chosen (the HAL uses the codeblock index) and repeat from one transport block to
   // the next, while an older, fully polled batch may still sit in its slot.
-  bool seen[SLOTS_PER_QUEUE] = {};
-  for (int pass = 0; pass < SLOTS_PER_QUEUE; ++pass) {
+  std::vector<char> seen(q.slots.size(), 0);
+  for (size_t pass = 0; pass < q.slots.size(); ++pass) {
     int      pick = -1;
     uint64_t best = 0;
-    for (int i = 0; i < SLOTS_PER_QUEUE; ++i) {
-      if (!seen[i] && q.slots[i].state == batch_slot::DONE && q.slots[i].seq >= best) {
-        best = q.slots[i].seq;
-        pick = i;
+    for (size_t i = 0; i < q.slots.size(); ++i) {
+      if (!seen[i] && q.slots[i]->state.load() == batch_slot::DONE && q.slots[i]->seq >= best) {
+        best = q.slots[i]->seq;
+        pick = (int)i;
       }
     }
     if (pick < 0) {
       break;
     }
-    seen[pick]    = true;
-    batch_slot& s = q.slots[pick];
+    seen[pick]    = 1;
+    batch_slot& s = *q.slots[pick];
     for (uint32_t i = s.polled; i-- > 0;) {
       if (s.tags[i] == tag) {
         const fec_cb_desc& d = s.h_descs[i];

@@ -363,7 +363,7 @@ __device__ __noinline__ void fec_generic_cb(const fec_cb_desc& D,
   // ---- stage 2: layered scaled min-sum ---------------------------------------------------------------------------------
   const uint32_t n_sig      = s_nsig;
   const bool     early_stop = (D.flags & FEC_FLAG_EARLY_STOP) != 0;
-  uint8_t*       out        = out_base + D.out_offset;
+  uint8_t*       out        = out_base + (((size_t)D.reserved1 << 32) | D.out_offset); // reserved1: bits 32.. of the offset
   const uint32_t kbytes     = (K + 7) / 8;
   if (n_sig < K) {
     if (!early_stop) {

@@ -118,7 +118,7 @@ EXPORTS = ["fec_abi_version", "fec_last_error", "fec_engine_default_cfg", "fec_e
            "fec_harq_pool_destroy", "fec_harq_pool_reserve", "fec_harq_pool_codeblocks", "fec_harq_pool_unlock",
            "fec_harq_pool_release", "fec_harq_pool_run_slot", "fec_harq_pool_stop", "fec_harq_pool_nof_free_codeblocks",
            "fec_tb_assemble_device_noalloc", "fec_engine_get_stats", "fec_engine_debug_fail_launches", "fec_tb_enqueue",
-           "fec_tb_poll", "fec_tb_wait"]
+           "fec_tb_poll", "fec_tb_wait", "fec_queue_enqueue_batch"]
 
 _lib = None
 
@@ -163,6 +163,8 @@ def load_library():
     lib.fec_queue_free.argtypes = [C.c_void_p, C.c_uint32]
     lib.fec_queue_enqueue.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64]
     lib.fec_queue_flush.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_queue_enqueue_batch.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
+                                            C.POINTER(C.c_uint32)]
     lib.fec_queue_poll.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
     lib.fec_queue_fetch.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_uint32]
     lib.fec_tb_segment.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p]
@@ -503,6 +505,18 @@ class FecEngine:
             return False
         _check(self.lib, rc)
         return True
+
+    def queue_enqueue_batch(self, q, descs, llrs, tags):
+        """fec_queue_enqueue_batch: descs (DESC_DTYPE array), llrs (list of int8 arrays), tags. Returns how many were taken."""
+        llrs = [np.ascontiguousarray(x, np.int8) for x in llrs]
+        ptrs = (C.c_void_p * len(llrs))(*[x.ctypes.data for x in llrs])
+        tg = np.ascontiguousarray(tags, np.uint64)
+        acc = C.c_uint32()
+        rc = self.lib.fec_queue_enqueue_batch(self.h, q, descs.ctypes.data, ptrs, tg.ctypes.data, len(llrs), C.byref(acc))
+        if rc == -5:
+            return 0
+        _check(self.lib, rc)
+        return acc.value
 
     def queue_flush(self, q):
         _check(self.lib, self.lib.fec_queue_flush(self.h, q))

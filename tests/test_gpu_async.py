@@ -281,3 +281,70 @@ def test_refused_launch_comes_back_as_failed_codeblocks(fec, orc, oracle, blocks
         assert st["codeblocks"] >= st["results"] and st["cb_launches"] >= 5
     finally:
         eng.close()
+
+
+@pytest.mark.parametrize("max_wait_us", [0, 200])
+def test_cross_queue_batcher_many_threads(fec, oracle, orc, max_wait_us):
+    """Eight threads, one queue each, batches of 6 codeblocks and batch enqueue: the batcher coalesces what several queues
+    hand over into shared launches; every result equals the one-call reference; back-pressure is reported, never blocks."""
+    eng = fec.FecEngine(device=0, harq_slots=2048, max_batch_cbs=256, nof_queues=8, queue_batch_cbs=6, queue_batches=3,
+                        max_wait_us=max_wait_us)
+    try:
+        bg, Z, qm, fill, E = 1, 384, 8, 16, 8960
+        K, N = cases.dims(bg, Z)
+        n_cb = 20
+        llrs = []
+        for i in range(n_cb):
+            llr, _ = oracle.make_case(bg, Z, E, 0, qm, 0, fill, orc.CRC24B, 3.0 + 0.4 * i, seed=900 + i)
+            llrs.append(llr)
+        d = fec.make_descs(n_cb)
+        d["base_graph"], d["lifting_size"], d["qm"], d["E"], d["nof_filler_bits"] = bg, Z, qm, E, fill
+        d["crc_type"], d["max_iter"], d["mode"] = fec.CRC24B, 6, fec.MODE_CHAIN
+        d["flags"] = fec.FLAG_NEW_DATA | fec.FLAG_EARLY_STOP
+        d["harq_slot"] = 1900 + np.arange(n_cb)
+        d["llr_offset"], d["out_offset"] = np.arange(n_cb, dtype=np.uint64) * E, np.arange(n_cb) * 1056
+        ref_out = np.zeros(n_cb * 1056, np.uint8)
+        ref = eng.run_host(d, np.concatenate(llrs), ref_out).copy()
+        assert 0 < int((ref["status"] & fec.RES_CRC_PASS).sum()) < n_cb  # both outcomes present
+        errors, full = [], [0]
+
+        def worker(k):
+            try:
+                q = eng.queue_reserve()
+                mine = d.copy()
+                mine["harq_slot"] = 200 * k + np.arange(n_cb)
+                for rep in range(12):
+                    seen, nxt = {}, 0
+                    t0 = time.time()
+                    while len(seen) < n_cb:
+                        assert time.time() - t0 < 30
+                        if nxt < n_cb:
+                            took = eng.queue_enqueue_batch(q, mine[nxt:], llrs[nxt:], np.arange(nxt, n_cb))
+                            full[0] += (took < n_cb - nxt)
+                            nxt += took
+                            if nxt == n_cb:
+                                eng.queue_flush(q)
+                        tags, rs = eng.queue_poll(q)
+                        for tag, r in zip(tags, rs):
+                            out = np.zeros(K // 8, np.uint8)
+                            eng.queue_fetch(q, tag, out)
+                            seen[int(tag)] = (r.copy(), out)
+                    for i in range(n_cb):
+                        r, out = seen[i]
+                        assert r["status"] == ref["status"][i] and r["nof_ldpc_iterations"] == ref["nof_ldpc_iterations"][i]
+                        if r["status"] & fec.RES_CRC_PASS:
+                            assert (out == ref_out[i * 1056:i * 1056 + K // 8]).all()
+                eng.queue_free(q)
+            except Exception as err:  # noqa: BLE001
+                errors.append(err)
+
+        threads = [threading.Thread(target=worker, args=(k,)) for k in range(8)]
+        [t.start() for t in threads]
+        [t.join() for t in threads]
+        assert not errors, errors
+        st = eng.stats()
+        assert full[0] > 0 and st["queue_full"] > 0  # 20 codeblocks against a ring of 3 x 6
+        assert st["dispatches"] >= 1 and st["dispatch_batches"] >= st["dispatches"]
+        assert st["max_queue_depth"] <= 18
+    finally:
+        eng.close()
