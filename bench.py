@@ -155,7 +155,6 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
-NCU_DRAM_BYTES_PER_CB = 46200  # (180.619776 + 147.588864) MB / 7104 codeblocks, r01 capture (profiles/r01_ncu_packed_full_metrics.csv)
 
 
 def reference_cpu(llr, n_threads, seconds, early_stop, impl=None):
@@ -585,6 +584,208 @@ def bench_pusch_demod(fec, eng, torch, dev, stream, args):
     return out
 
 
+def ncu_capture_numbers():
+    """DRAM traffic per codeblock and issue statistics of the committed ncu --set full capture of the decode kernel
+    (profiles/r02_ncu_packed_full_metrics.csv: raw page of the .ncu-rep, filtered), read at run time so that the line can be
+    recomputed from profiles/. Returns {} if the file is not there."""
+    path = os.path.join(ROOT, "profiles", "r02_ncu_packed_full_metrics.csv")
+    out = {}
+    try:
+        import csv
+        rows = list(csv.reader(open(path)))
+        vals = dict(zip(rows[0], rows[2]))
+        units = dict(zip(rows[0], rows[1]))
+
+        def num(k):
+            v = float(vals[k].replace(",", ""))
+            return v * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(units.get(k, ""), 1)
+
+        grid = float(vals.get("launch__grid_size", "0").replace(",", "") or 0)
+        out = {"dram_bytes": num("dram__bytes_read.sum") + num("dram__bytes_write.sum"), "codeblocks": grid,
+               "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+               "warp_instructions": num("smsp__inst_executed.sum"), "source": os.path.relpath(path, ROOT)}
+    except Exception:
+        pass
+    return out
+
+
+def sass_instructions_per_edge():
+    """Instructions per edge and thread (two checks) of the row bodies, from the committed SASS histogram."""
+    try:
+        for line in open(os.path.join(ROOT, "profiles", "r02_sass_row_hist.txt")):
+            if "instructions per edge" in line:
+                return float(line.split("->")[1].split()[0])
+    except Exception:
+        pass
+    return None
+
+
+def bench_config4(fec, eng, torch, dev, stream, args, rank):
+    """BASELINE config 4: HARQ retransmissions with soft-buffer combining below the waterfall, 10 iterations at most, early
+    stop. n codeblocks (BG1 Z=384, E=11268: rate 0.75 at the first transmission, 64QAM interleaving) go through rv 0, 2, 3, 1;
+    every pass rate-dematches and COMBINES into the soft buffers in HBM and decodes all of them again (device-resident, one
+    launch per pass). Goodput counts the information bits of the codeblocks whose CRC has passed by the last pass."""
+    n, E4, qm, iters = 148 * 3 * 8, 11268, 6, 10
+    rng = np.random.default_rng(4 + rank)
+    sigma2 = 0.5 * 10.0 ** (-args.harq_esn0 / 10.0)
+    llr = np.empty((4, n, E4), np.int8)
+    for t in range(4):
+        for i in range(0, n, 512):
+            y = 1.0 + np.sqrt(sigma2) * rng.standard_normal((min(512, n - i), E4), dtype=np.float32)
+            llr[t, i:i + 512] = np.round(np.clip(2.0 * y / sigma2, -20.0, 20.0) * 6.0).astype(np.int8)
+    d_llr = [torch.from_numpy(llr[t]).to(dev) for t in range(4)]
+    d_descs = []
+    for t, rv in enumerate((0, 2, 3, 1)):
+        d = fec.make_descs(n)
+        d["base_graph"], d["lifting_size"], d["qm"], d["E"], d["rv"] = BG, Z, qm, E4, rv
+        d["crc_type"], d["max_iter"], d["mode"] = fec.CRC24B, iters, fec.MODE_CHAIN
+        d["flags"] = (fec.FLAG_NEW_DATA if t == 0 else 0) | fec.FLAG_EARLY_STOP
+        d["harq_slot"], d["llr_offset"], d["out_offset"] = np.arange(n), np.arange(n, dtype=np.uint64) * E4, np.arange(n) * (K // 8)
+        fec.desc_prepare(d)
+        d_descs.append(torch.from_numpy(d.view(np.uint8).copy()).to(dev))
+    d_out = torch.zeros(n * (K // 8), dtype=torch.uint8, device=dev)
+    d_res = [torch.zeros(n * 8, dtype=torch.uint8, device=dev) for _ in range(4)]
+    torch.cuda.synchronize()
+
+    def sequence():
+        for t in range(4):
+            eng.launch_device(d_descs[t].data_ptr(), n, d_llr[t].data_ptr(), d_out.data_ptr(), d_res[t].data_ptr(), Z, True)
+
+    sequence()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    reps = 3
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        evs[0].record(stream)
+        for _ in range(reps):
+            sequence()
+        evs[1].record(stream)
+    stream.synchronize()
+    sec = evs[0].elapsed_time(evs[1]) / 1e3 / reps
+    res = [np.frombuffer(r.cpu().numpy().tobytes(), fec.RESULT_DTYPE) for r in d_res]
+    ok = [(r["status"] & fec.RES_CRC_PASS) != 0 for r in res]
+    passed_by = np.cumsum([o.mean() for o in ok])  # a codeblock the bench keeps decoding may pass more than once: use any()
+    any_ok = np.zeros(n, bool)
+    frac = []
+    for o in ok:
+        any_ok |= o
+        frac.append(float(any_ok.mean()))
+    out = {"workload": "HARQ rv 0,2,3,1 with combining in HBM, BG1 Z=384 E=%d Qm=%d, Es/N0 %.1f dB, max %d iterations, early "
+                       "stop, %d codeblocks per pass, device-resident" % (E4, qm, args.harq_esn0, iters, n),
+           "ms_per_pass": sec / 4 * 1e3, "codeblock_passes_per_s": 4 * n / sec,
+           "goodput_gbps": float(any_ok.sum()) * INFO_BITS / sec / 1e9,
+           "crc_pass_fraction_after_pass": frac, "mean_iterations_per_pass": [float(r["nof_ldpc_iterations"].mean()) for r in res]}
+    del passed_by
+    if not args.no_cpu_baseline and rank == 0:
+        try:
+            import ctypes as C
+            orc = ge.load_oracle()
+            ref = orc.Ref()
+            impl = orc.Ref.AVX512 if ref.impl_available(orc.Ref.AVX512) else orc.Ref.AVX2
+            m, th = 32 * host_threads(), host_threads()
+            soft = np.zeros((m, N), np.int8)
+            outb = np.zeros((m, K // 8), np.uint8)
+            it = np.zeros(m, np.int32)
+            ref.lib.ref_batch_chain.restype = C.c_double
+            tot, cnt, t0 = 0.0, 0, time.time()
+            while time.time() - t0 < 4.0:
+                for t, rv in enumerate((0, 2, 3, 1)):
+                    x = np.ascontiguousarray(llr[t, :m])
+                    tot += ref.lib.ref_batch_chain(impl, th, C.c_uint(m), BG, Z, soft.ctypes.data_as(C.c_void_p),
+                                                   x.ctypes.data_as(C.c_void_p), C.c_uint(E4), int(t == 0), C.c_uint(rv),
+                                                   C.c_uint(qm), C.c_uint(0), C.c_uint(0), orc.CRC24B, C.c_uint(iters), 1,
+                                                   outb.ctypes.data_as(C.c_void_p), it.ctypes.data_as(C.c_void_p))
+                cnt += 4 * m
+            out["cpu_baseline"] = {"codeblock_passes_per_s": cnt / tot, "cores": th, "kind": "reference",
+                                   "sample": "%d codeblock passes of the same HARQ sequence through the reference's AVX "
+                                             "dematcher + decoder + CRC on all host threads" % cnt}
+        except Exception as ex:
+            out["cpu_baseline"] = {"unavailable": str(ex)[:120]}
+    return out
+
+
+def bench_config5(fec, torch, dev, args, rank, world, barrier, max_over_ranks):
+    """BASELINE config 5: one uplink slot of 32 cells (100 MHz, 273 PRB, 4 layers; MCS mix of tests/test_gpu_tb.py: 4 cells
+    256QAM R948 = 152 codeblocks, 12 cells 64QAM R873, 16 cells QPSK R120 = BG2 with repetition), cells sharded `cell mod N`
+    over the ranks, each rank's cells in ONE fec_tb_run_host call per slot from pinned host memory (copies inside the timed
+    region). No collective on the data path; value = information bits of all cells / max over ranks of the time."""
+    nsym = 42588 * 4
+    mcs = [dict(tbs=1277992, bg=1, qm=8, nl=4, G=nsym * 8, snr=8.0), dict(tbs=871384, bg=1, qm=6, nl=4, G=nsym * 6, snr=6.0),
+           dict(tbs=39920, bg=2, qm=2, nl=4, G=nsym * 2, snr=-4.0)]
+    n_cells = 32
+    cell_mcs = [0 if c % 8 == 0 else (1 if c % 2 == 0 else 2) for c in range(n_cells)]
+    mine = fec.cells_of_rank(n_cells, world, rank)
+    rng = np.random.default_rng(500 + rank)
+    d = fec.make_tb_descs(len(mine))
+    lo, oo, parts, slot, bits = 0, 0, [], 0, 0
+    for i, c in enumerate(mine):
+        p = mcs[cell_mcs[c]]
+        sigma2 = 0.5 * 10.0 ** (-p["snr"] / 10.0)
+        y = 1.0 + np.sqrt(sigma2) * rng.standard_normal(p["G"], dtype=np.float32)
+        parts.append(np.round(np.clip(2.0 * y / sigma2, -20.0, 20.0) * 6.0).astype(np.int8))
+        d["tbs"][i], d["nof_llrs"][i], d["base_graph"][i], d["qm"][i], d["nof_layers"][i] = p["tbs"], p["G"], p["bg"], p["qm"], p["nl"]
+        d["max_iter"][i], d["flags"][i], d["harq_slot"][i] = MAX_ITER, fec.FLAG_NEW_DATA | fec.FLAG_EARLY_STOP, slot
+        d["llr_offset"][i], d["out_offset"][i] = lo, oo
+        lo += (p["G"] + 63) // 64 * 64
+        oo += p["tbs"] // 8
+        slot += 162
+        bits += p["tbs"]
+    buf = np.zeros(lo, np.int8)
+    for i, x in enumerate(parts):
+        buf[int(d["llr_offset"][i]):int(d["llr_offset"][i]) + x.size] = x
+    eng = fec.FecEngine(device=dev.index, harq_slots=slot + 162, max_batch_cbs=max(slot, 512), max_batch_llrs=lo + 4096)
+    t_llr = torch.from_numpy(buf).pin_memory()
+    t_out = torch.zeros(oo, dtype=torch.uint8).pin_memory()
+    ok = 0
+    for _ in range(2):
+        r = eng.tb_run_host(d, (t_llr.data_ptr(), t_llr.numel()), (t_out.data_ptr(), t_out.numel()))
+    barrier()
+    reps = 10
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        r = eng.tb_run_host(d, (t_llr.data_ptr(), t_llr.numel()), (t_out.data_ptr(), t_out.numel()))
+        ok += int(r["tb_crc_ok"].sum())
+    sec = time.perf_counter() - t0
+    barrier()
+    sec = max_over_ranks(sec)
+    total_bits = bits
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([float(bits), float(ok), float(len(mine) * reps)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t)
+        total_bits, ok_all, n_all = float(t[0]), float(t[1]), float(t[2])
+    else:
+        ok_all, n_all = float(ok), float(len(mine) * reps)
+    eng.close()
+    return {"workload": "32 cells x one full-slot transport block (4 x 256QAM R948, 12 x 64QAM R873, 16 x QPSK R120), cell mod N "
+                        "sharding, one fec_tb_run_host call per rank and slot from pinned host memory",
+            "value": total_bits * reps / sec / 1e9, "unit": "Gbit/s", "ms_per_slot": sec / reps * 1e3, "cells": n_cells,
+            "tb_crc_ok_fraction": ok_all / max(n_all, 1.0), "h2d_bytes_per_slot_rank0": int(lo), "d2h_bytes_per_slot_rank0": int(oo),
+            "slot_budget_ms": 0.5}
+
+
+def bench_hal(args):
+    """Throughput and LOADED latency through the reference's interfaces: tests/cpp/_build/bench_hal (C++; the reference's
+    unmodified pusch_decoder_hw_impl over the CUDA HAL adapter, and pusch_decoder_cuda synchronous / asynchronous), T threads
+    decoding config-3 transport blocks back to back. Built by __graft_entry__.build() where the reference tree is present."""
+    exe = os.path.join(ROOT, "tests", "cpp", "_build", "bench_hal")
+    if not os.path.exists(exe):
+        return {"unavailable": "tests/cpp/_build/bench_hal is not built (needs the reference headers at build time)"}
+    try:
+        p = subprocess.run([exe, str(args.hal_seconds), args.hal_threads, "hal,tb,tb_async", str(args.tb_esn0)],
+                           capture_output=True, text=True, timeout=240)
+        rows = [json.loads(x) for x in p.stdout.splitlines() if x.startswith("{")]
+        best = {}
+        for r in rows:
+            if r["mode"] not in best or r["gbps"] > best[r["mode"]]["gbps"]:
+                best[r["mode"]] = r
+        return {"host_threads": host_threads(), "points": rows,
+                "best_gbps": {m: {"gbps": r["gbps"], "threads": r["threads"], "lat_us_p99": r["lat_us_p99"]} for m, r in best.items()},
+                "note": "latency = on_end_softbits to notification while all threads load the GPU; exit code %d" % p.returncode}
+    except Exception as ex:
+        return {"unavailable": str(ex)[:160]}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -685,12 +886,17 @@ def run_ours(args):
     if not args.no_tb:
         tb = bench_transport_block(fec, eng, torch, dev, stream, args, rank)
 
+    # the side legs (downlink twin, demodulator, HAL bench) run at N = 1 only: in a multi-GPU run the other ranks would sit in
+    # a barrier while rank 0 works alone; there the time goes to the multi-cell workload (config 5) instead
     enc = None
-    if not args.no_enc and rank == 0:
+    if not args.no_enc and world == 1:
         enc = bench_pdsch_encode(fec, eng, torch, dev, stream, args)
     dmd = None
-    if not args.no_demod and rank == 0:
+    if not args.no_demod and world == 1:
         dmd = bench_pusch_demod(fec, eng, torch, dev, stream, args)
+    cfg4 = None
+    if not args.no_config4 and world == 1:
+        cfg4 = bench_config4(fec, eng, torch, dev, stream, args, rank)
 
     # ---- e2e: host buffers through fec_run_host (H2D + kernels + D2H inside the timed region) --------------------------
     res_h = np.zeros(n, fec.RESULT_DTYPE)
@@ -711,6 +917,14 @@ def run_ours(args):
     e2e_val = n * e2e_steps * world * INFO_BITS / e2e_sec / 1e9
     assert (res_h["status"] & fec.RES_DONE).all()
 
+    stats = eng.stats()
+    cfg5 = None
+    if not args.no_config5:
+        cfg5 = bench_config5(fec, torch, dev, args, rank, world, barrier, max_over_ranks)
+    hal = None
+    if not args.no_hal and world == 1 and rank == 0:
+        eng.close()  # the C++ bench creates its own engines
+        hal = bench_hal(args)
     line = None
     if rank == 0:
         peaks = {}
@@ -724,6 +938,19 @@ def run_ours(args):
         sm_mhz = clocks.get("sm_mhz") or 1965.0
         upd_per_s = n * EDGE_UPDATES_PER_CB / kernel_s
         alu_peak = sm_count * 128 * sm_mhz * 1e6 * 4  # packed int8 lane-ops/s if every INT32 lane did 4 bytes per clock
+        # What binds this kernel is instruction ISSUE (integer / half2 work on shared memory, one warp instruction per clock and
+        # scheduler at best): the roof is the edge updates per second the SMs could issue if every issue slot carried an
+        # instruction of the row bodies as compiled (instructions per edge and thread of two checks: SASS histogram in profiles/).
+        ipe = sass_instructions_per_edge() or 34.7
+        issue_peak = sm_count * 4 * sm_mhz * 1e6 * 64.0 / ipe  # 32 threads x 2 checks per warp instruction
+        cap = ncu_capture_numbers()
+        traffic = (cap["dram_bytes"] / cap["codeblocks"] * n) if cap.get("codeblocks") else None
+        tb_lat = None
+        if tb:
+            tb_lat = {"unloaded": dict(tb["tb_api_latency_us"], what="one config-3 transport block per fec_tb_run_host call, idle GPU")}
+            if hal and hal.get("points"):
+                tb_lat["loaded"] = [{"consumer": r["mode"], "threads": r["threads"], "p50": r["lat_us_p50"], "p99": r["lat_us_p99"],
+                                     "gbps": r["gbps"]} for r in hal["points"]]
         line = {"metric": "decoded_info_gbps", "value": value, "unit": "Gbit/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
@@ -731,27 +958,34 @@ def run_ours(args):
                 "crc_pass_fraction": float(passed.mean()),
                 "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + 48),
                         "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
-                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early, "transport_block": tb, "pdsch_encode": enc, "pusch_demod": dmd,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
-                             "frac": achieved / peak_gbs,
-                             # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture
-                             # in profiles/ (46 250 B per codeblock at 7104 codeblocks), scaled to this launch
-                             "traffic": n * NCU_DRAM_BYTES_PER_CB, "traffic_unit": "bytes/launch",
-                             "traffic_source": "profiles/r01_ncu_packed_full_metrics.csv",
-                             "kernel": "fec_cb_packed_kernel (1 launch/step)",
-                             "kernel_ms": kernel_s * 1e3, "algorithmic_bytes_per_cb": ALGO_BYTES_PER_CB,
-                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                             "alu": {"edge_updates_per_s": upd_per_s,
-                                     "lane_ops_per_s": upd_per_s * LANE_OPS_PER_UPDATE, "peak_lane_ops_per_s": alu_peak,
-                                     "frac": upd_per_s * LANE_OPS_PER_UPDATE / alu_peak, "sm_count": sm_count,
-                                     "note": "canonical 26 int8 lane-ops per edge update vs SMs x 128 lanes x 4 bytes "
-                                             "x sampled SM clock"}}}
+                "gpu_launches": int(launches), "clocks": clocks, "early_stop": early,
+                "tb_latency_us": tb_lat, "transport_block": tb, "config4_harq": cfg4, "config5_multicell": cfg5, "hal": hal,
+                "pdsch_encode": enc, "pusch_demod": dmd, "stats": stats,
+                "roofline": {"bound": "issue", "achieved": upd_per_s / 1e9, "peak": issue_peak / 1e9,
+                             "unit": "G edge updates/s", "frac": upd_per_s / issue_peak,
+                             "peak_definition": "SMs x 4 schedulers x sampled SM clock x 64 checks per warp instruction / "
+                                                "%.1f instructions per edge (profiles/r02_sass_row_hist.txt)" % ipe,
+                             # dram__bytes_read.sum + dram__bytes_write.sum of one launch of the committed ncu --set full capture,
+                             # per codeblock, scaled to this launch
+                             "traffic": traffic, "traffic_unit": "bytes/launch", "traffic_source": cap.get("source"),
+                             "kernel": "fec_cb_packed_kernel (1 launch/step)", "kernel_ms": kernel_s * 1e3,
+                             "ncu_issue_active_pct": cap.get("issue_active_pct"),
+                             "alu": {"edge_updates_per_s": upd_per_s, "lane_ops_per_s": upd_per_s * LANE_OPS_PER_UPDATE,
+                                     "peak_lane_ops_per_s": alu_peak, "frac": upd_per_s * LANE_OPS_PER_UPDATE / alu_peak,
+                                     "sm_count": sm_count,
+                                     "note": "SURVEY 8(d) form: canonical 26 int8 lane-ops per edge update vs SMs x 128 "
+                                             "lanes x 4 bytes x sampled SM clock"},
+                             "hbm": {"achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
+                                     "algorithmic_bytes_per_cb": ALGO_BYTES_PER_CB,
+                                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                                     "note": "secondary: the decode needs 9 % of HBM at the 100 Gbit/s target"}}}
         if world == 1 and not args.no_cpu_baseline:
             gbps, desc = reference_cpu(llr_h[:max(32 * host_threads(), 256)], host_threads(), args.cpu_seconds, False)
             if gbps is not None:
                 desc["value"], desc["unit"] = gbps, "Gbit/s"
             line["cpu_baseline"] = desc
-    eng.close()
+    if hal is None:
+        eng.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -775,6 +1009,12 @@ def main():
     ap.add_argument("--no-enc", action="store_true", help="skip the PDSCH encoder (downlink twin) measurement")
     ap.add_argument("--no-demod", action="store_true", help="skip the soft demodulator measurement")
     ap.add_argument("--demod-esn0", type=float, default=30.0, help="Es/N0 of the 256QAM symbols of the demodulator bench")
+    ap.add_argument("--no-config4", action="store_true", help="skip the HARQ retransmission workload (BASELINE config 4)")
+    ap.add_argument("--no-config5", action="store_true", help="skip the 32-cell slot workload (BASELINE config 5)")
+    ap.add_argument("--no-hal", action="store_true", help="skip the multi-threaded C++ bench through the reference's interfaces")
+    ap.add_argument("--harq-esn0", type=float, default=0.5, help="Es/N0 (dB) of the config-4 HARQ workload (rate 0.75: below the waterfall)")
+    ap.add_argument("--hal-seconds", type=float, default=1.5)
+    ap.add_argument("--hal-threads", default="1,4,16,32")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     return run_reference(args) if args.impl == "reference" else run_ours(args)

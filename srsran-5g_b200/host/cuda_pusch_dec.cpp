@@ -2,6 +2,7 @@
 #include "cuda_pusch_dec.h"
 #include "srsran/support/error_handling.h"
 #include <cstring>
+#include <thread>
 #include <vector>
 
 using namespace srsran;
@@ -69,6 +70,7 @@ void cuda_pusch_dec_accelerator::free_queue()
   for (operation& op : ops) {
     op.enqueued = false;
     op.done     = false;
+    op.rejected = false;
   }
   dirty = false;
 }
@@ -79,6 +81,7 @@ void cuda_pusch_dec_accelerator::configure_operation(const hal::hw_pusch_decoder
   ops[cb_index].cfg      = config;
   ops[cb_index].enqueued = false;
   ops[cb_index].done     = false;
+  ops[cb_index].rejected = false;
 }
 
 bool cuda_pusch_dec_accelerator::enqueue_operation(span<const int8_t> data, span<const int8_t> /*aux_data*/, unsigned cb_index)
@@ -104,9 +107,18 @@ bool cuda_pusch_dec_accelerator::enqueue_operation(span<const int8_t> data, span
   if (rc == FEC_ERR_QUEUE_FULL) {
     return false; // the consumer stops enqueuing and drains (pusch_decoder_hw_impl.cpp:253-257)
   }
-  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
   ops[cb_index].enqueued = true;
-  dirty                  = true;
+  if (rc != FEC_OK) {
+    // Anything else (a parameter the engine rejects, a CUDA failure) is a failed codeblock, not a dead DU: the operation
+    // counts as accepted and completes at once with CRC_pass = false (the consumer then treats it like any decoding failure).
+    ops[cb_index].result                     = {};
+    ops[cb_index].result.nof_ldpc_iterations = static_cast<uint16_t>(c.max_nof_ldpc_iterations);
+    ops[cb_index].result.status              = FEC_RES_DONE;
+    ops[cb_index].done                       = true;
+    ops[cb_index].rejected                   = true;
+    return true;
+  }
+  dirty = true;
   return true;
 }
 
@@ -142,10 +154,18 @@ bool cuda_pusch_dec_accelerator::dequeue_operation(span<uint8_t> data, span<int8
     }
     poll();
     if (!op.done) {
+      // The consumer spins on dequeue_operation (pusch_decoder_hw_impl.cpp:289-317): give the core away between two looks, so
+      // that more decoder threads than cores do not starve the threads that still have codeblocks to enqueue.
+      if (++idle_polls >= 64) {
+        idle_polls = 0;
+        std::this_thread::yield();
+      }
       return false;
     }
   }
-  fec_queue_fetch(engine->get(), queue, segment_index, data.data(), static_cast<uint32_t>(data.size()));
+  if (!op.rejected) {
+    fec_queue_fetch(engine->get(), queue, segment_index, data.data(), static_cast<uint32_t>(data.size()));
+  }
   return true;
 }
 
@@ -168,8 +188,8 @@ std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> srsran::b200::create_cuda
   return std::make_shared<cuda_pusch_dec_factory>(cfg);
 }
 
-pusch_decoder_cuda::pusch_decoder_cuda(std::shared_ptr<fec_engine_handle> engine_, unsigned max_nof_softbits) :
-  engine(std::move(engine_)), softbits_cap(max_nof_softbits)
+pusch_decoder_cuda::pusch_decoder_cuda(std::shared_ptr<fec_engine_handle> engine_, unsigned max_nof_softbits, bool asynchronous_) :
+  engine(std::move(engine_)), softbits_cap(max_nof_softbits), asynchronous(asynchronous_)
 {
   static_assert(sizeof(log_likelihood_ratio) == 1, "LLRs are int8 on both sides of the boundary.");
   softbits = static_cast<log_likelihood_ratio*>(fec_host_alloc(max_nof_softbits));
@@ -211,7 +231,7 @@ void pusch_decoder_cuda::on_new_softbits(span<const log_likelihood_ratio> in)
 
 void pusch_decoder_cuda::on_end_softbits()
 {
-  const unsigned nof_cbs = rm_buffer->get_nof_codeblocks();
+  nof_cbs = rm_buffer->get_nof_codeblocks();
   srsran_assert(nof_cbs <= MAX_NOF_SEGMENTS, "Too many codeblocks.");
   for (unsigned i = 0; i != nof_cbs; ++i) {
     slots[i] = rm_buffer->get_absolute_codeblock_id(i);
@@ -227,25 +247,81 @@ void pusch_decoder_cuda::on_end_softbits()
   tb.nof_layers  = static_cast<uint8_t>(current_config.nof_layers);
   tb.max_iter    = static_cast<uint8_t>(current_config.nof_ldpc_iterations);
   tb.flags       = (current_config.new_data ? FEC_FLAG_NEW_DATA : 0u) | (current_config.use_early_stop ? FEC_FLAG_EARLY_STOP : 0u);
+  if (asynchronous) {
+    // The call returns once the work is on the GPU's queues; the engine's completion thread hands the block over and
+    // notifies, as pusch_decoder_impl does from its executor (pusch_decoder_impl.cpp:372-381). When every host-call context
+    // of the engine is in flight the block is decoded synchronously instead (back-pressure, never a drop).
+    uint64_t  ticket = 0;
+    const int rc = fec_tb_enqueue(engine->get(), &tb, 1, slots.data(), reinterpret_cast<const int8_t*>(softbits), softbits_count,
+                                  transport_block.data(), transport_block.size(), &pusch_decoder_cuda::on_completion, this, &ticket);
+    if (rc == FEC_OK) {
+      return;
+    }
+    if (rc != FEC_ERR_QUEUE_FULL) {
+      finish(rc, fec_tb_result{});
+      return;
+    }
+  }
   fec_tb_result res = {};
   const int     rc  = fec_tb_run_host(engine->get(), &tb, 1, slots.data(), reinterpret_cast<const int8_t*>(softbits),
                                       softbits_count, transport_block.data(), transport_block.size(), &res, cb_results.data());
-  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
-  srsran_assert(res.nof_codeblocks == nof_cbs, "Wrong number of codeblocks {} (expected {}).", nof_cbs, res.nof_codeblocks);
+  have_cb_results   = (rc == FEC_OK);
+  finish(rc, res);
+}
 
+void pusch_decoder_cuda::on_completion(void* user, uint64_t /*ticket*/, int status, const fec_tb_result* results, uint32_t n)
+{
+  pusch_decoder_cuda* self = static_cast<pusch_decoder_cuda*>(user);
+  self->have_cb_results    = false;
+  self->finish(status, (n != 0) ? results[0] : fec_tb_result{});
+}
+
+void pusch_decoder_cuda::finish(int rc, const fec_tb_result& res)
+{
   pusch_decoder_result stats;
+  stats.ldpc_decoder_stats.reset();
+  if (rc != FEC_OK) {
+    // A failure of the engine (a rejected configuration, a CUDA fault) is a failed transport block, not a dead DU
+    // (pusch_decoder_hw_impl.cpp:319-332 treats a codeblock the accelerator could not decode the same way).
+    stats.tb_crc_ok            = false;
+    stats.nof_codeblocks_total = nof_cbs;
+    for (unsigned i = 0; i != nof_cbs; ++i) {
+      stats.ldpc_decoder_stats.update(current_config.nof_ldpc_iterations);
+    }
+    rm_buffer.unlock();
+    notifier->on_sch_data(stats);
+    return;
+  }
+  srsran_assert(res.nof_codeblocks == nof_cbs, "Wrong number of codeblocks {} (expected {}).", nof_cbs, res.nof_codeblocks);
   stats.tb_crc_ok            = res.tb_crc_ok != 0;
   stats.nof_codeblocks_total = res.nof_codeblocks;
-  stats.ldpc_decoder_stats.reset();
-  // Keep the pool's view of the codeblock CRCs in step with the engine's (the engine is authoritative).
-  span<bool> cb_crcs = rm_buffer->get_codeblocks_crc();
-  for (unsigned i = 0; i != nof_cbs; ++i) {
-    const fec_cb_result& cr = cb_results[i];
-    const bool           ok = (cr.status & FEC_RES_CRC_PASS) != 0;
-    if (!(cr.status & FEC_RES_SKIPPED)) {
-      stats.ldpc_decoder_stats.update(ok ? cr.nof_ldpc_iterations : current_config.nof_ldpc_iterations);
+  if (have_cb_results) {
+    // Keep the pool's view of the codeblock CRCs in step with the engine's (the engine is authoritative).
+    span<bool> cb_crcs = rm_buffer->get_codeblocks_crc();
+    for (unsigned i = 0; i != nof_cbs; ++i) {
+      const fec_cb_result& cr = cb_results[i];
+      const bool           ok = (cr.status & FEC_RES_CRC_PASS) != 0;
+      if (!(cr.status & FEC_RES_SKIPPED)) {
+        stats.ldpc_decoder_stats.update(ok ? cr.nof_ldpc_iterations : current_config.nof_ldpc_iterations);
+      }
+      cb_crcs[i] = ok;
     }
-    cb_crcs[i] = ok;
+  } else {
+    // Asynchronous completion carries the block summary only: the same statistics from its sum / minimum / maximum (the
+    // reference's sample statistics expose count, mean, min and max; one observation each of min and max and the rest at
+    // the value that restores the sum reproduces all four).
+    const unsigned nd = res.nof_cb_decoded;
+    if (nd == 1) {
+      stats.ldpc_decoder_stats.update(res.iter_sum);
+    } else if (nd >= 2) {
+      stats.ldpc_decoder_stats.update(res.iter_min);
+      stats.ldpc_decoder_stats.update(res.iter_max);
+      const unsigned rest = res.iter_sum - res.iter_min - res.iter_max;
+      for (unsigned i = 2; i != nd; ++i) {
+        const unsigned v = rest / (nd - 2) + ((i - 2) < rest % (nd - 2) ? 1 : 0);
+        stats.ldpc_decoder_stats.update(v);
+      }
+    }
   }
   if (!stats.tb_crc_ok && res.tb_delivered) {
     rm_buffer->reset_codeblocks_crc();
@@ -278,7 +354,9 @@ std::optional<unsigned> ldpc_decoder_cuda::decode(bit_buffer&                   
   static_assert(sizeof(log_likelihood_ratio) == 1, "LLRs are int8 on both sides of the boundary.");
   const int rc = fec_run_host(engine->get(), &d, 1, reinterpret_cast<const int8_t*>(input.data()), input.size(),
                               bytes.data(), bytes.size(), &res, nullptr);
-  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+  if (rc != FEC_OK) {
+    return std::nullopt; // an engine failure is a decoding failure (fec_last_error() has the reason)
+  }
   if ((crc != nullptr) && (res.status & FEC_RES_CRC_PASS)) {
     return res.nof_ldpc_iterations;
   }
@@ -311,5 +389,9 @@ void ldpc_rate_dematcher_cuda::rate_dematch(span<log_likelihood_ratio>       out
                                          &res, nullptr)
                           : rc;
   rc                = (rc == FEC_OK) ? fec_harq_read(engine->get(), scratch_slot, out, static_cast<uint32_t>(output.size())) : rc;
-  report_fatal_error_if_not(rc == FEC_OK, "B200 FEC engine: {}", fec_last_error());
+  if (rc != FEC_OK) {
+    // The interface has no failure channel: an engine failure leaves erasures (LLR 0 = no information), which the decoder
+    // downstream turns into a failed codeblock; fec_last_error() has the reason.
+    std::memset(out, 0, output.size());
+  }
 }

@@ -79,6 +79,7 @@ private:
     fec_cb_result                       result   = {};
     bool                                enqueued = false;
     bool                                done     = false;
+    bool                                rejected = false; // the engine refused it: completes as a failed codeblock
   };
 
   void poll();
@@ -87,6 +88,7 @@ private:
   uint32_t                                 queue     = 0;
   bool                                     has_queue = false;
   bool                                     dirty     = false; // operations enqueued since the last flush
+  unsigned                                 idle_polls = 0;    // consecutive dequeue attempts that found nothing
   std::array<operation, MAX_NOF_SEGMENTS>  ops;
 };
 
@@ -95,6 +97,8 @@ class cuda_pusch_dec_factory : public hal::hw_accelerator_pusch_dec_factory
 {
 public:
   explicit cuda_pusch_dec_factory(const fec_engine_cfg& cfg) : engine(std::make_shared<fec_engine_handle>(cfg)) {}
+  /// Accelerators over an engine that other adapters (transport-block decoder, encoder, demodulator) share.
+  explicit cuda_pusch_dec_factory(std::shared_ptr<fec_engine_handle> engine_) : engine(std::move(engine_)) {}
   std::unique_ptr<hal::hw_accelerator_pusch_dec> create() override
   {
     return std::make_unique<cuda_pusch_dec_accelerator>(engine);
@@ -110,13 +114,15 @@ std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> create_cuda_pusch_dec_acc
 
 /// pusch_decoder over the transport-block entry point of the C ABI (fec_tb_run_host). The rx buffer only supplies the
 /// absolute codeblock identifiers (the pool must be created with external_soft_bits = true): soft bits, codeblock CRC
-/// flags and the decoded messages of earlier transmissions live in the engine. Decoding starts at on_end_softbits and
-/// is synchronous; one instance per thread, as for pusch_decoder_impl.
+/// flags and the decoded messages of earlier transmissions live in the engine. Decoding starts at on_end_softbits; calls
+/// of different instances (threads) run concurrently on the GPU. Synchronous by default, asynchronous on request.
 class pusch_decoder_cuda : public pusch_decoder, private pusch_decoder_buffer
 {
 public:
   /// \param max_nof_softbits capacity of the (pinned) codeword buffer, e.g. pusch_constants::get_max_codeword_size().
-  pusch_decoder_cuda(std::shared_ptr<fec_engine_handle> engine_, unsigned max_nof_softbits);
+  /// \param asynchronous     on_end_softbits returns as soon as the work is queued on the GPU (fec_tb_enqueue) and the notifier
+  ///                         is called from the engine's completion thread; the instance is busy until then.
+  pusch_decoder_cuda(std::shared_ptr<fec_engine_handle> engine_, unsigned max_nof_softbits, bool asynchronous = false);
   ~pusch_decoder_cuda() override;
 
   // See pusch_decoder for the documentation.
@@ -142,6 +148,12 @@ private:
   configuration                      current_config;
   std::array<uint32_t, MAX_NOF_SEGMENTS>      slots;
   std::array<fec_cb_result, MAX_NOF_SEGMENTS> cb_results;
+  bool                                        asynchronous    = false;
+  bool                                        have_cb_results = false;
+  unsigned                                    nof_cbs         = 0;
+
+  static void on_completion(void* user, uint64_t ticket, int status, const fec_tb_result* results, uint32_t n);
+  void        finish(int rc, const fec_tb_result& res);
 };
 
 /// ldpc_decoder over FEC_MODE_DECODE (synchronous, one codeblock). The crc pointer only selects the polynomial.
