@@ -15,22 +15,21 @@ ALU = {"LOP3", "SHF", "PRMT", "HMNMX2", "HSET2", "HSETP2", "ISETP", "SEL", "IADD
        "P2R", "R2P", "VHMNMX", "VIMNMX3", "CS2R", "HMNMX2.XORSIGN"}
 LSU = {"LDS", "STS", "LDG", "STG", "LD", "ST", "LDSM", "ATOMS", "ATOMG", "RED", "LDL", "STL", "LDC"}
 TM = {"LDTM", "STTM"}
-# The iteration function is a __noinline__ device function: its code sits inside the kernel's listing, at a CALL target.
 kern = [f for f in re.split(r"\n\s*Function : ", sass)[1:] if f.startswith("_Z20fec_cb_packed_kernel")][0]
 lines = []
 for line in kern.split("\n"):
     m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(@!?U?P\d+\s+)?([A-Z0-9_.]+)(.*?);", line)
     if m:
         lines.append((int(m.group(1), 16), m.group(3), m.group(4)))
-targets = sorted({int(x, 16) for _, op, rest in lines if op.startswith("CALL") for x in re.findall(r"0x([0-9a-f]+)", rest)[:1]})
-targets.append(lines[-1][0] + 16)
-best = None
-for lo, hi in zip(targets, targets[1:]):
-    body = [(a, op) for a, op, _ in lines if lo <= a < hi]
-    n = sum(1 for _, op in body if op.startswith("HMNMX2"))
-    if best is None or n > best[0]:
-        best = (n, lo, hi, body)
-_, lo, hi, body = best
+# The iteration loop is inlined into the kernel: its code is the span from the load of the row schedule word (constant bank 3)
+# in front of the first HMNMX2.XORSIGN to the backward branch that closes the loop behind the last one.
+idx = [i for i, (_, op, _) in enumerate(lines) if op.startswith("HMNMX2")]
+first, last = idx[0], idx[-1]
+lo_i = max(i for i in range(first) if "c[0x3]" in lines[i][2])
+hi_i = next(i for i in range(last, len(lines)) if lines[i][1].startswith("BRA") and
+            int(re.findall(r"0x([0-9a-f]+)", lines[i][2])[-1], 16) <= lines[lo_i][0])
+lo, hi = lines[lo_i][0], lines[hi_i][0] + 16
+body = [(a_, op) for a_, op, _ in lines[lo_i:hi_i + 1]]
 ops = collections.Counter(op for _, op in body)
 by = collections.Counter()
 for op, n in ops.items():

@@ -27,6 +27,20 @@
 #include <string.h>
 
 #define FEC_PACKED_MAX_THREADS 192
+// -DFEC_DEBUG_CHECKS: bounds checks on every shared-memory / tensor-memory access of the hot path (compute-sanitizer is closed
+// on the B200 pool used here, so the checks are the kernel's own: a violation prints and traps, which fails the call).
+#ifdef FEC_DEBUG_CHECKS
+#include <cstdio>
+#define FEC_CHECK(cond, what, v)                                                                                        \
+  do {                                                                                                                  \
+    if (!(cond)) {                                                                                                      \
+      printf("FEC_CHECK failed: %s (%u) block %u thread %u\n", what, (unsigned)(v), blockIdx.x, threadIdx.x);           \
+      __trap();                                                                                                         \
+    }                                                                                                                   \
+  } while (0)
+#else
+#define FEC_CHECK(cond, what, v) ((void)0)
+#endif
 #define FEC_PACKED_CTAS_PER_SM 3u // resident codeblocks per SM at the largest lifting size (__launch_bounds__ below)
 
 // Edge (shift s = q * H + r into column col): thread t reads pair word (t + r) mod H of the column; its lanes come swapped
@@ -298,6 +312,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   {
     uint32_t w0, w1, w2 = 0;
     if (TM) {
+      FEC_CHECK((taddr & 0xffffu) + NW <= 512u && ((taddr >> 16) & 0x1fu) == 0, "row: tensor-memory address", taddr);
       tmem_wait_st(); // this thread's store of the previous tensor-memory row
       if (NW == 3) {
         tmem_ld3(taddr, w0, w1, w2);
@@ -340,6 +355,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   uint32_t S[D];
 #pragma unroll
   for (int e = 0; e < D; ++e) {
+    FEC_CHECK((a0[e] & 1u) == 0 && (a0[e] & ~2u) >= soft_s && (a0[e] & ~2u) + 4 <= soft_s + 68u * 4u * H, "row: soft address", a0[e] - soft_s);
     const uint32_t x = lds_u32(a0[e] & ~2u);
     S[e]             = prmt_f4e(x, x, a0[e]); // address bit 1 set: the two lanes come swapped
   }
@@ -428,9 +444,8 @@ enum { // instantiation codes: tensor-memory rows of degree 3..10, then the shar
   FEC_ROW_S3, FEC_ROW_S8, FEC_ROW_S9, FEC_ROW_S10, FEC_ROW_S19, FEC_ROW_NONE
 };
 
-// One decoder iteration over the layers in use. Out of line on purpose: ptxas allocates registers for the row code on its
-// own, so changes to the dematcher or the tail cannot perturb the schedule of the hot loop (and vice versa).
-__device__ __noinline__ void fec_packed_iteration(uint32_t               soft_s,
+// One decoder iteration over the layers in use.
+__device__ __forceinline__ void fec_packed_iteration(uint32_t               soft_s,
                                                   uint32_t*              state,
                                                   const fec_packed_edge* edges,
                                                   uint32_t               bg, // 0 = BG1, 1 = BG2
@@ -502,6 +517,7 @@ struct fec_soft_store_packed {
   {
     const uint32_t op  = o + 2 * Z;
     const uint32_t col = __umulhi(op, invZ);
+    FEC_CHECK(col < 68u && fec_packed_soft_idx(col, op - col * Z, H) < 68u * Z, "soft store: index", op);
     soft16[fec_packed_soft_idx(col, op - col * Z, H)] = fec_sm16(acc);
   }
 };
@@ -602,8 +618,10 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint16_t* soft16, uin
 // remainder bytewise). Byte i of the message contributes byte_i(x) * x^(8 (nb-1-i)) mod g; x8[j] = x^(8 j) mod g comes from
 // the engine's table in HBM (4 KB per polynomial, L1 / L2 resident; shared memory has no room for it beside the 16-bit
 // soft bits). Up to six independent 8-step multiply chains per thread, one barrier.
-// Kept out of line: inlined into the codeblock function it changes ptxas' register allocation of the row code for the worse.
-__device__ __noinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T, const uint32_t* __restrict__ x8, uint32_t poly,
+// (Round 1 kept this out of line because an inlined build decoded wrongly. That no longer reproduces: the suspect, a byte
+// load in inline asm without a "memory" clobber next to plain C++ shared-memory stores, is gone, every asm access here
+// clobbers memory, and the inlined build passes the whole parity suite. Inlined, the kernel is 2 % faster.)
+__device__ __forceinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_t T, const uint32_t* __restrict__ x8, uint32_t poly,
                                                   uint32_t top, uint32_t* red)
 {
   const uint32_t nb = T / 8, r = T % 8;
@@ -897,6 +915,7 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
     auto           put    = [&](uint32_t s, uint32_t byte) {
       const uint32_t i = (G.qm == 1) ? s : __umulhi(s, inv_qm);
       const uint32_t p = (s - i * G.qm) * G.Kp + i;
+      FEC_CHECK(fec_dematch_stage_pos(S, p) < stage_cap, "dematch: staging position", p);
       stage[fec_dematch_stage_pos(S, p)] = (int8_t)byte;
     };
     uint32_t done = 0;
