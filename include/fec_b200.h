@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 7
+#define FEC_B200_ABI_VERSION 8
 
 typedef enum {
   FEC_OK             = 0,
@@ -159,6 +159,8 @@ typedef struct fec_engine_stats {
   uint64_t transport_blocks;
   uint64_t tb_crc_ok;
   uint64_t faults;           /* CUDA failures turned into failed codeblocks / blocks                                    */
+  uint64_t generic_launches; /* of cb_launches, those that took the generic kernel (kernel_variant 1, or a scaling_factor   */
+                             /* whose rounding the packed kernel's 8-bit multiply-add cannot reproduce, e.g. 0.9)          */
 } fec_engine_stats;
 int fec_engine_get_stats(fec_engine* e, fec_engine_stats* out);
 /* Test hook: the next n codeblock-kernel launches are refused by the driver (a launch error, not sticky). */

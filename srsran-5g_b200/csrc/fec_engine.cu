@@ -269,7 +269,7 @@ struct fec_engine {
   fec_demod_desc*   h_dm_descs   = nullptr; // pinned copy of the call's descriptors, prepared and rebased
   size_t            h_dm_descs_cap = 0;
   // counters (fec_engine_get_stats)
-  std::atomic<uint64_t> st_codeblocks{0}, st_batches{0}, st_results{0}, st_crc_pass{0}, st_queue_full{0}, st_faults{0},
+  std::atomic<uint64_t> st_codeblocks{0}, st_batches{0}, st_results{0}, st_crc_pass{0}, st_queue_full{0}, st_faults{0}, st_generic{0},
       st_tb_calls{0}, st_tbs{0}, st_tb_crc_ok{0}, st_max_depth{0}, st_dispatches{0}, st_dispatch_slots{0};
   std::atomic<uint64_t> st_iter_hist[FEC_STATS_ITER_BINS];
   std::atomic<uint32_t> debug_fail_launches{0}; // fec_engine_debug_fail_launches: the next n codeblock launches fail
@@ -338,6 +338,7 @@ int launch(fec_engine*          e,
     threads                               = threads > 384 ? 384 : threads;
     fec_cb_generic_kernel<<<n, threads, L.total, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab);
     CU_TRY(cudaGetLastError());
+    e->st_generic.fetch_add(1, std::memory_order_relaxed);
   }
   e->launches.fetch_add(1);
   return FEC_OK;
@@ -2225,6 +2226,7 @@ int fec_engine_get_stats(fec_engine* e, fec_engine_stats* out)
   out->crc_pass            = e->st_crc_pass.load();
   out->queue_full          = e->st_queue_full.load();
   out->faults              = e->st_faults.load();
+  out->generic_launches    = e->st_generic.load();
   out->tb_calls            = e->st_tb_calls.load();
   out->transport_blocks    = e->st_tbs.load();
   out->tb_crc_ok           = e->st_tb_crc_ok.load();

@@ -26,7 +26,7 @@ MAX_TB_CBS = 162
 TB_SLOTS_CONTIGUOUS = 0xFFFFFFFF
 HARQ_SLOT_BYTES = 25344
 MAX_CB_OUT_BYTES = 1056
-ABI_VERSION = 7
+ABI_VERSION = 8
 NOALLOC_MAX_TBS, NOALLOC_MAX_CBS = 64, 2048
 
 ALL_Z = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48, 52, 56, 60,
@@ -94,7 +94,8 @@ class EngineStats(C.Structure):
     _fields_ = [("launches", C.c_uint64), ("cb_launches", C.c_uint64), ("codeblocks", C.c_uint64), ("results", C.c_uint64),
                 ("crc_pass", C.c_uint64), ("iterations_hist", C.c_uint64 * STATS_ITER_BINS), ("queue_full", C.c_uint64),
                 ("max_queue_depth", C.c_uint64), ("dispatches", C.c_uint64), ("dispatch_batches", C.c_uint64),
-                ("tb_calls", C.c_uint64), ("transport_blocks", C.c_uint64), ("tb_crc_ok", C.c_uint64), ("faults", C.c_uint64)]
+                ("tb_calls", C.c_uint64), ("transport_blocks", C.c_uint64), ("tb_crc_ok", C.c_uint64), ("faults", C.c_uint64),
+                ("generic_launches", C.c_uint64)]
 
 
 TB_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_uint32)
