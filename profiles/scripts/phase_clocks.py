@@ -5,6 +5,8 @@ import os
 import subprocess
 import sys
 
+import ctypes as C
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -26,6 +28,7 @@ rng = np.random.default_rng(1)
 
 
 def run(name, n, E, qm, fill, early, esn0):
+    eng.lib.fec_debug_profile_read((C.c_uint64 * 16)(), 1)
     K, N = fec.dims(1, 384)
     sigma2 = 0.5 * 10.0 ** (-esn0 / 10.0)
     pad = (E + 15) // 16 * 16
@@ -41,10 +44,16 @@ def run(name, n, E, qm, fill, early, esn0):
         res = eng.run_host(d, llr, out)
     r = res["reserved"]
     ph = np.stack([(r & 0xff) << 8, ((r >> 8) & 0xff) << 10, ((r >> 16) & 0xff) << 12, ((r >> 24) & 0xff) << 8], 1)
+    acc = (C.c_uint64 * 16)()
+    eng.lib.fec_debug_profile_read(acc, 1)
+    cnt = max(1, acc[15])
+    names = ["setup", "stage", "groups+sig", "fill", "state clear", "rows", "hard bits", "crc", "tail"]
+    print("  fine: " + "  ".join("%s %.0f" % (nm, acc[k] / cnt) for k, nm in enumerate(names)) + "  (clocks per codeblock, both runs)")
     print("%-28s n=%d  setup %6.0f  dematch+fill %6.0f  decode %7.0f  tail %5.0f  clocks/codeblock (mean); iterations %.2f layers %d" %
           (name, n, *ph.mean(0), res["nof_ldpc_iterations"].mean(), res["nof_layers"][0]))
 
 
 run("headline (E=N, forced 6)", 444 * 4, 25344, 2, 0, False, -2.0)
-run("config 3 (E=8960, early stop)", 444 * 4, 8960, 8, 16, True, 10.0)
+run("config 3 (E=8992, early stop, 8 dB)", 444 * 4, 8992, 8, 16, True, 8.0)
+run("headline early stop", 444 * 4, 25344, 2, 0, True, -2.0)
 eng.close()

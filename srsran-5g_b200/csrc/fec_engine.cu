@@ -2771,3 +2771,19 @@ int fec_tb_assemble_device_noalloc(fec_engine* e, const fec_tb_desc* tbs, uint32
 }
 
 } // extern "C"
+
+#ifdef FEC_PROFILE
+// Profiling build only (profiles/scripts/phase_clocks.py): the phase clocks accumulated by fec_cb_packed_kernel.
+extern "C" int fec_debug_profile_read(unsigned long long* out, int reset)
+{
+  cudaDeviceSynchronize();
+  if (cudaMemcpyFromSymbol(out, fec_prof_acc, sizeof(fec_prof_acc)) != cudaSuccess) {
+    return FEC_ERR_CUDA;
+  }
+  if (reset) {
+    unsigned long long zero[FEC_PROF_PHASES] = {};
+    cudaMemcpyToSymbol(fec_prof_acc, zero, sizeof(zero));
+  }
+  return FEC_OK;
+}
+#endif

@@ -121,6 +121,22 @@ __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, 
   return L;
 }
 
+// ---- FEC_PROFILE build: phase clocks accumulated over all codeblocks (thread 0 of each CTA) ----------------------------------
+#ifdef FEC_PROFILE
+#define FEC_PROF_PHASES 16
+__device__ unsigned long long fec_prof_acc[FEC_PROF_PHASES];
+#define FEC_PROF_MARK(k)                                                                                                        \
+  do {                                                                                                                          \
+    if (threadIdx.x == 0) {                                                                                                     \
+      const long long now_ = clock64();                                                                                         \
+      atomicAdd(&fec_prof_acc[k], (unsigned long long)(now_ - fec_prof_t));                                                     \
+      fec_prof_t = now_;                                                                                                        \
+    }                                                                                                                           \
+  } while (0)
+#else
+#define FEC_PROF_MARK(k)
+#endif
+
 // ---- 16-bit sign-magnitude SIMD primitives (all single SASS instructions) --------------------------------------------
 #define FEC_H2(x) (((uint32_t)(x) & 0xffffu) * 0x10001u)
 
@@ -153,6 +169,18 @@ __device__ __forceinline__ uint32_t h2_max_xs(uint32_t a, uint32_t b)
 {
   uint32_t r;
   asm("max.xorsign.abs.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t h2_min(uint32_t a, uint32_t b)
+{
+  uint32_t r;
+  asm("min.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t h2_max(uint32_t a, uint32_t b)
+{
+  uint32_t r;
+  asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
   return r;
 }
 // per lane: 1.0 (0x3c00) if a == b else 0.0
@@ -569,32 +597,42 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint16_t* soft16, uin
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   int            zero = 0;
   if ((H & 31u) == 0) {
-    // One column per step: thread t holds variables t and t+H of the column; a ballot yields 32 consecutive bits.
-    // Kb is 22 or 10: batches of 11 / 10 loads in flight, then the ballots.
+    // One column per step: thread t holds variables t and t+H of the column as one f16x2 word. One HSETP2 (x <= 0 on both
+    // lanes; -0 and +0 both count) feeds two ballots of 32 consecutive bits each; lane c of the warp keeps the two words of
+    // column c and stores them at the end. A zero magnitude anywhere is found with a running f16x2 minimum of |x|.
     const uint32_t* soft32 = reinterpret_cast<const uint32_t*>(soft16);
-    const uint32_t  Kb = K / Z, nb = (Kb == 22) ? 11u : 10u;
+    const uint32_t  Kb     = K / Z; // 22 or 10
+    uint32_t        zacc   = 0x7c007c00u, keep0 = 0, keep1 = 0;
     if (threadIdx.x < H) {
-      for (uint32_t c0 = 0; c0 < Kb; c0 += nb) {
-        uint32_t hw[11];
+      uint32_t hw[22];
 #pragma unroll
-        for (uint32_t c = 0; c < 11; ++c) {
-          hw[c] = (c < nb) ? soft32[(c0 + c) * H + threadIdx.x] : 0x00010001u;
-        }
+      for (uint32_t c = 0; c < 22; ++c) {
+        hw[c] = (c < Kb) ? soft32[c * H + threadIdx.x] : 0x00010001u;
+      }
 #pragma unroll
-        for (uint32_t c = 0; c < 11; ++c) {
-          if (c < nb) {
-            const uint32_t m0 = hw[c] & 0x7fffu, m1 = hw[c] & 0x7fff0000u;
-            zero |= (m0 == 0) | (m1 == 0);
-            const uint32_t bal0 = __ballot_sync(0xffffffffu, (m0 == 0) | ((hw[c] & 0x8000u) != 0));
-            const uint32_t bal1 = __ballot_sync(0xffffffffu, (m1 == 0) | ((hw[c] & 0x80000000u) != 0));
-            if (lane == 0) {
-              bitsw[((c0 + c) * Z + warp * 32) >> 5]     = __brev(bal0);
-              bitsw[((c0 + c) * Z + H + warp * 32) >> 5] = __brev(bal1);
-            }
+      for (uint32_t c = 0; c < 22; ++c) {
+        if (c < Kb) {
+          uint32_t b0, b1;
+          asm volatile("{\n\t"
+                       ".reg .pred p, q;\n\t"
+                       "setp.le.f16x2 p|q, %2, %3;\n\t"
+                       "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t"
+                       "vote.sync.ballot.b32 %1, q, 0xffffffff;\n\t"
+                       "}"
+                       : "=r"(b0), "=r"(b1)
+                       : "r"(hw[c]), "r"(0u));
+          zacc = h2_min(zacc, h2_abs(hw[c]));
+          if (lane == c) {
+            keep0 = b0, keep1 = b1;
           }
         }
       }
+      if (lane < Kb) {
+        bitsw[(lane * Z + warp * 32) >> 5]     = __brev(keep0);
+        bitsw[(lane * Z + H + warp * 32) >> 5] = __brev(keep1);
+      }
     }
+    zero = ((zacc & 0x7fffu) == 0) | ((zacc & 0x7fff0000u) == 0);
     return __syncthreads_or(zero) == 0;
   }
   const uint32_t nw = (K + 31) / 32;
@@ -894,12 +932,166 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
   return my_sig;
 }
 
-__device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
+// ---- staging by transposition -------------------------------------------------------------------------------------------
+// The bit de-interleaver (TS 38.212 5.4.2.2) undone four symbols at a time: the 4 QM input bytes of symbols i0 .. i0+3 are
+// loaded as QM words, and for every bit position j the four bytes {s = i QM + j} are gathered with three PRMTs into one
+// word that lands at staged byte j Kp + i0. Needs Kp % 4 == 0, no staging shifts (d1 = d2 = 0) and an 8-byte aligned
+// input; 1.3 instructions per LLR instead of the 9 of the byte-wise scatter.
+template <uint32_t QM>
+__device__ __forceinline__ void fec_stage_transposed(const int8_t* __restrict__ in, int8_t* stage, uint32_t Kp)
+{
+  constexpr uint32_t U   = (QM <= 4) ? 4u : 2u; // units in flight per thread: 32 bytes of loads (QM 2), 64 (QM 4, 8), 48 (QM 6)
+  uint32_t*          st4 = reinterpret_cast<uint32_t*>(stage);
+  const uint32_t     ng = Kp / 4, kw = Kp / 4;
+  for (uint32_t g0 = threadIdx.x; g0 < ng; g0 += U * blockDim.x) {
+    uint32_t W[U][QM];
+#pragma unroll
+    for (uint32_t u = 0; u < U; ++u) {
+      const uint32_t g = g0 + u * blockDim.x;
+      if (g < ng) {
+        if constexpr (QM % 4 == 0) {
+          const uint4* src = reinterpret_cast<const uint4*>(in) + (size_t)g * (QM / 4);
+#pragma unroll
+          for (uint32_t k = 0; k < QM / 4; ++k) {
+            const uint4 v = __ldg(src + k);
+            W[u][4 * k] = v.x, W[u][4 * k + 1] = v.y, W[u][4 * k + 2] = v.z, W[u][4 * k + 3] = v.w;
+          }
+        } else {
+          const uint2* src = reinterpret_cast<const uint2*>(in) + (size_t)g * (QM / 2);
+#pragma unroll
+          for (uint32_t k = 0; k < QM / 2; ++k) {
+            const uint2 v = __ldg(src + k);
+            W[u][2 * k] = v.x, W[u][2 * k + 1] = v.y;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (uint32_t u = 0; u < U; ++u) {
+      const uint32_t g = g0 + u * blockDim.x;
+      if (g < ng) {
+#pragma unroll
+        for (uint32_t j = 0; j < QM; ++j) {
+          const uint32_t s0 = j, s1 = QM + j, s2 = 2 * QM + j, s3 = 3 * QM + j; // input byte of symbol i0 + 0..3
+          const uint32_t lo = prmt(W[u][s0 / 4], W[u][s1 / 4], (s0 % 4) | ((4 + s1 % 4) << 4));
+          const uint32_t hi = prmt(W[u][s2 / 4], W[u][s3 / 4], (s2 % 4) | ((4 + s3 % 4) << 4));
+          st4[j * kw + g]   = prmt(lo, hi, 0x5410);
+        }
+      }
+    }
+  }
+}
+
+// Four int8 values (one word) -> two f16x2 words in the 16-bit sign-magnitude format, clamped to +-64, without integer
+// arithmetic: byte b becomes the half-precision number 1152 + b (bits 0x6400 | (b ^ 0x80)); times 2^-24 (bits 0x0001) minus
+// 1152 * 2^-24 (bits 0x0480) leaves b * 2^-24, whose bit pattern is |b| with the sign bit of b. All exact.
+__device__ __forceinline__ void fec_cvt4_sm16(uint32_t w, uint32_t& v01, uint32_t& v23)
+{
+  const uint32_t x = w ^ 0x80808080u;
+  v01 = h2_fma(prmt(x, 0x64646464u, 0x4140), 0x00010001u, 0x84808480u);
+  v23 = h2_fma(prmt(x, 0x64646464u, 0x4342), 0x00010001u, 0x84808480u);
+  v01 = h2_min_xs(v01, 0x00400040u); // min(|v|, 64) with the sign of v
+  v23 = h2_min_xs(v23, 0x00400040u);
+}
+
+// ---- the direct path: first transmission from the start of the buffer (new data, rv 0, no wrap-around), Z % 8 == 0 --------
+// The soft buffer in HBM and the decoder's 16-bit copy in shared memory are written in the same pass: a thread takes the
+// 4-byte groups at positions o and o + H of one column (two 32-bit loads from the staged LLRs, two 32-bit HBM stores) and
+// stores the four pair words {o + k, o + H + k} with one 128-bit shared store. The staged LLRs live in the same shared
+// memory the pair words go to: pair words of column c occupy bytes [2 c Z, 2 (c + 1) Z) and the staged LLRs of that column
+// lie below byte (c - 1) Z + 8, so the columns are processed from the top in chunks [c0, c1) with 2 c0 Z >= (c1 - 2) Z + 8
+// (nothing a chunk writes is still to be read by it or by a later chunk) and a barrier between chunks: five chunks for 64
+// columns. Columns the decoder cannot reach (beyond cbl_max) only get their zeros in HBM.
+// Groups that are not entirely inside a data run (the fillers, the run ends, the start of the zero tail) take the per-byte
+// rules of fec_dematch_byte.
+__device__ __forceinline__ uint32_t fec_dematch_direct(const fec_dematch_geom& G,
+                                                       const fec_dematch_src&  S,
+                                                       int8_t* __restrict__    harq,
+                                                       uint16_t*               soft16,
+                                                       uint32_t                K)
+{
+  const uint32_t Z = G.Z, H = Z / 2, upc = H / 4; // units (pairs of groups) per column
+  const uint32_t inv_upc = 0xffffffffu / upc + 1; // unused when upc == 1 (Z = 8)
+  uint32_t*      harq4   = reinterpret_cast<uint32_t*>(harq);
+  uint4*         soft128 = reinterpret_cast<uint4*>(soft16);
+  const uint32_t run0_hi = min(G.E, G.info);                   // data run before the filler gap: positions [0, run0_hi)
+  const uint32_t run1_hi = (G.E > G.info) ? G.E + G.fillers : 0u; // after it: [sys, run1_hi), read at position - fillers
+  uint32_t       cbl_max = max(G.zero_from + 2 * Z, K + 4 * Z);
+  cbl_max                = min(((cbl_max + Z - 1) / Z) * Z, G.N + 2 * Z);
+  const uint32_t cproc   = cbl_max / Z; // columns [2, cproc) get pair words
+  uint32_t       sig_o = 0, sig_w = 0;  // this thread's highest group with a non-zero value
+
+  // HBM zeros of the columns the decoder cannot reach
+  {
+    uint2*         h8 = reinterpret_cast<uint2*>(harq);
+    const uint32_t n8 = G.N / 8;
+    for (uint32_t i = (cproc - 2) * Z / 8 + threadIdx.x; i < n8; i += blockDim.x) {
+      h8[i] = make_uint2(0, 0);
+    }
+  }
+
+  auto group_value = [&](uint32_t o0) -> uint32_t {
+    if (o0 + 4 <= run0_hi) {
+      return *reinterpret_cast<const uint32_t*>(S.base + o0);
+    }
+    if (o0 >= G.sys && o0 + 4 <= run1_hi) {
+      return *reinterpret_cast<const uint32_t*>(S.base + (o0 - G.fillers));
+    }
+    if (o0 >= G.zero_from) {
+      return 0u;
+    }
+    const uint32_t old = G.hzero ? 0u : harq4[o0 / 4];
+    int            val[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      val[b] = fec_dematch_byte(G, S, o0 + b, (int)(int8_t)(old >> (8 * b)));
+    }
+    return fec_pack4(val);
+  };
+
+  for (uint32_t c1 = cproc; c1 > 2;) {
+    uint32_t c0 = ((c1 - 2) * Z + 8 + 2 * Z - 1) / (2 * Z);
+    c0          = max(c0, 2u);
+    const uint32_t nu = (c1 - c0) * upc;
+    for (uint32_t u = threadIdx.x; u < nu; u += blockDim.x) {
+      const uint32_t cc  = (upc == 1) ? u : __umulhi(u, inv_upc);
+      const uint32_t k   = u - cc * upc;
+      const uint32_t col = c0 + cc;
+      const uint32_t olo = (col - 2) * Z + 4 * k, ohi = olo + H;
+      const uint32_t wlo = group_value(olo), whi = group_value(ohi);
+      harq4[olo / 4] = wlo;
+      harq4[ohi / 4] = whi;
+      if (whi != 0 && ohi >= sig_o) {
+        sig_o = ohi, sig_w = whi;
+      } else if (wlo != 0 && olo >= sig_o) {
+        sig_o = olo, sig_w = wlo;
+      }
+      uint32_t l01, l23, h01, h23;
+      fec_cvt4_sm16(wlo, l01, l23);
+      fec_cvt4_sm16(whi, h01, h23);
+      FEC_CHECK(col * upc + k < 68u * upc, "direct dematch: pair word index", col * upc + k);
+      soft128[col * upc + k] = make_uint4(prmt(l01, h01, 0x5410), prmt(l01, h01, 0x7632), prmt(l23, h23, 0x5410),
+                                          prmt(l23, h23, 0x7632));
+    }
+    __syncthreads();
+    c1 = c0;
+  }
+  return fec_last_sig(sig_o, sig_w);
+}
+
+// Returns true if the decoder's soft bits (columns 2 .. of the pair-word array) have been written as well (direct path).
+__device__ __forceinline__ bool fec_dematch_packed(const fec_cb_desc& D,
                                                    const int8_t* __restrict__ in,
                                                    int8_t* __restrict__ harq,
                                                    int8_t*   stage,
                                                    uint32_t  stage_cap,
-                                                   uint32_t* n_sig_smem)
+                                                   uint32_t* n_sig_smem,
+                                                   uint32_t  K
+#ifdef FEC_PROFILE
+                                                   ,
+                                                   long long& fec_prof_t
+#endif
+)
 {
   const fec_dematch_geom G = fec_dematch_geometry(D);
 
@@ -909,7 +1101,29 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
   S.split  = (G.k0c < G.info) ? min(G.E, G.info - G.k0c) : 0u;
   S.d1     = G.k0c & 3u;
   S.d2     = S.d1 + (G.fillers & 3u);
-  if (G.E + 8 <= stage_cap) {
+  const bool transposed = (G.E + 8 <= stage_cap) && (G.Kp % 4 == 0) && (S.d1 == 0) && (S.d2 == 0) &&
+                          ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) && (G.qm == 2 || G.qm == 4 || G.qm == 6 || G.qm == 8);
+  // direct path (fec_dematch_direct): also fills the decoder's soft bits
+  const bool direct = transposed && G.newd && !G.wrapped && (D.k0 == 0) && (G.Z % 8 == 0) && (D.mode == FEC_MODE_CHAIN);
+  if (transposed) {
+    switch (G.qm) {
+      case 2:
+        fec_stage_transposed<2>(in, stage, G.Kp);
+        break;
+      case 4:
+        fec_stage_transposed<4>(in, stage, G.Kp);
+        break;
+      case 6:
+        fec_stage_transposed<6>(in, stage, G.Kp);
+        break;
+      default:
+        fec_stage_transposed<8>(in, stage, G.Kp);
+        break;
+    }
+    __syncthreads();
+    S.base   = stage;
+    S.staged = true;
+  } else if (G.E + 8 <= stage_cap) {
     // (1) stage and de-interleave: input byte s = i * Qm + j is rate-matched LLR p = j * (E / Qm) + i.
     const uint32_t inv_qm = 0xffffffffu / G.qm + 1;
     auto           put    = [&](uint32_t s, uint32_t byte) {
@@ -939,11 +1153,14 @@ __device__ __forceinline__ void fec_dematch_packed(const fec_cb_desc& D,
     S.base   = stage;
     S.staged = true;
   }
+  FEC_PROF_MARK(1);
 
-  const uint32_t my_sig = fec_dematch_groups(G, S, harq);
+  const uint32_t my_sig = direct ? fec_dematch_direct(G, S, harq, reinterpret_cast<uint16_t*>(stage), K)
+                                 : fec_dematch_groups(G, S, harq);
   if (my_sig != 0) {
     atomicMax(n_sig_smem, my_sig);
   }
+  return direct;
 }
 
 
@@ -979,6 +1196,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 
 #ifdef FEC_PROFILE
   long long tp0 = clock64(), tp1 = 0, tp2 = 0, tp3 = 0;
+  long long fec_prof_t = tp0;
 #endif
   const fec_packed_smem_layout L = fec_packed_layout(Z, bg1);
   uint32_t*        state  = reinterpret_cast<uint32_t*>(smem_raw + L.state);
@@ -1013,9 +1231,11 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #ifdef FEC_PROFILE
   tp1 = clock64();
 #endif
+  FEC_PROF_MARK(0);
   // ---- stage 1: the soft buffer (rate dematching + HARQ combining), or the decoder input as given --------------------------
   const fec_soft_store_packed store{soft16, Z, H, invZ};
   const int8_t*               harq = nullptr;
+  bool                        direct_fill = false;
   if (D.mode == FEC_MODE_DECODE) {
     const uint32_t n_in   = D.E;
     const uint32_t n_node = (n_in / Z) * Z; // full nodes are clamped to +-64, a partial last node is copied as it is
@@ -1044,7 +1264,12 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
     int8_t* hq = harq_base + (size_t)D.harq_slot * FEC_HARQ_SLOT_BYTES;
     harq       = hq;
     // the soft-bit area is the staging area of the dematcher: the decoder's copy is filled afterwards
-    fec_dematch_packed(D, in, hq, reinterpret_cast<int8_t*>(soft16), L.total - L.soft, &s_nsig);
+    direct_fill = fec_dematch_packed(D, in, hq, reinterpret_cast<int8_t*>(soft16), L.total - L.soft, &s_nsig, K
+#ifdef FEC_PROFILE
+                       ,
+                       fec_prof_t
+#endif
+    );
     if (D.mode == FEC_MODE_DEMATCH) {
       if (tid == 0) {
         res.status  = FEC_RES_DONE;
@@ -1054,6 +1279,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
     }
   }
   __syncthreads();
+  FEC_PROF_MARK(2);
 
   // ---- stage 2: layered scaled min-sum -------------------------------------------------------------------------------------
   const uint32_t n_sig      = s_nsig;
@@ -1082,10 +1308,15 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   const uint32_t tm_q  = (((tid >> 5) & 3u) * 32u) << 16;
   const uint32_t tm_a  = tmem_a + tm_q + (tid >> 7) * FEC_PACKED_TMEM_A_COLS;
   const uint32_t tm_b  = tmem_b + tm_q + (tid >> 7) * FEC_PACKED_TMEM_B_COLS;
-  if (harq != nullptr) {
+  if (direct_fill) {
+    for (uint32_t i = tid; i < Z; i += blockDim.x) {
+      reinterpret_cast<uint32_t*>(soft16)[i] = 0; // the two punctured columns (the dematcher has written the others)
+    }
+  } else if (harq != nullptr) {
     // every staged LLR has been consumed (barrier above): the decoder's soft bits, columns of the layers in use only
     fec_soft_fill_from_harq(harq, soft16, cbl - 2 * Z, Z, H, invZ);
   }
+  FEC_PROF_MARK(3);
   {
     // Clear the check state of the rows in use ("no c2v messages yet"): shared memory, region B, region A.
     uint4*         s4 = reinterpret_cast<uint4*>(state);
@@ -1112,14 +1343,18 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #ifdef FEC_PROFILE
   tp2 = clock64();
 #endif
+  FEC_PROF_MARK(4);
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
     fec_packed_iteration(soft_s, state, edges, bg1 ? 0u : 1u, H, nlayers, smul, sadd, tm_b, tm_a);
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
+    FEC_PROF_MARK(5);
     if (early_stop) {
       const bool clean = fec_hard_bits_packed(soft16, bitsw, K, Z, H, invZ);
+      FEC_PROF_MARK(6);
       const bool crc   = fec_crc_ok_packed(bitsw, T, x8, crc_poly, crc_top, red);
+      FEC_PROF_MARK(7);
       if (clean && crc) {
         pass = true;
         ++it;
@@ -1154,6 +1389,8 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
 #ifdef FEC_PROFILE
     // phase clocks / 256: [7:0] setup, [15:8] dematch / 4, [23:16] decode / 16, [31:24] tail
     const long long tp4 = clock64();
+    FEC_PROF_MARK(8);
+    atomicAdd(&fec_prof_acc[15], 1ull);
     res.reserved = (uint32_t)min(255ll, (tp1 - tp0) >> 8) | ((uint32_t)min(255ll, (tp2 - tp1) >> 10) << 8) |
                    ((uint32_t)min(255ll, (tp3 - tp2) >> 12) << 16) | ((uint32_t)min(255ll, (tp4 - tp3) >> 8) << 24);
 #endif

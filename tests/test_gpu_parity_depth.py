@@ -103,7 +103,7 @@ def test_scaling_factors_other_than_default(fec, oracle, orc, sf, packed):
         n_pass = n_fail = 0
         for trial in range(60):
             bg = int(rng.choice([1, 2]))
-            Z = int(rng.choice([2, 6, 9, 16, 28, 52, 104, 224, 384, 384]))
+            Z = int(rng.choice([4, 6, 9, 16, 28, 52, 104, 224, 384, 384]))
             K, N = cases.dims(bg, Z)
             n_in = int(rng.integers(K + 4 * Z, N + 1))
             snr = 10 * np.log10(2 ** (2 * K / n_in) - 1) - 0.5 + float(rng.uniform(-2.0, 3.0))
