@@ -305,7 +305,7 @@ def bench_transport_block(fec, eng, torch, dev, stream, args, rank):
     torch.cuda.synchronize()
 
     def step():
-        eng.launch_device(d_descs.data_ptr(), n_tb * n_cb, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True)
+        eng.launch_device(d_descs.data_ptr(), n_tb * n_cb, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True, even_z=True)
 
     for _ in range(3):
         step()
@@ -509,7 +509,7 @@ def bench_pusch_demod(fec, eng, torch, dev, stream, args):
 
     def fused():
         step()
-        eng.launch_device(d_cbd.data_ptr(), n_tb * n_cb, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True)
+        eng.launch_device(d_cbd.data_ptr(), n_tb * n_cb, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True, even_z=True)
 
     for _ in range(3):
         fused()
@@ -649,7 +649,7 @@ def bench_config4(fec, eng, torch, dev, stream, args, rank):
 
     def sequence():
         for t in range(4):
-            eng.launch_device(d_descs[t].data_ptr(), n, d_llr[t].data_ptr(), d_out.data_ptr(), d_res[t].data_ptr(), Z, True)
+            eng.launch_device(d_descs[t].data_ptr(), n, d_llr[t].data_ptr(), d_out.data_ptr(), d_res[t].data_ptr(), Z, True, even_z=True)
 
     sequence()
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
@@ -822,7 +822,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step_device(dd=d_descs):
-        eng.launch_device(dd.data_ptr(), n, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True)
+        eng.launch_device(dd.data_ptr(), n, d_llr.data_ptr(), d_out.data_ptr(), d_res.data_ptr(), Z, True, even_z=True)
 
     def timed(fn, steps, per_step_events=False):
         """Barrier + sync both sides, CUDA events on the engine stream; returns (seconds, per-step ms list)."""

@@ -172,8 +172,12 @@ int fec_desc_prepare(fec_cb_desc* d);
 
 /* ---- device-resident batch: everything already in HBM (bench.py "value") ------------------------------------------ */
 /* d_descs: n prepared descriptors in device memory; d_llr / d_out / d_results: device buffers the descriptors index
- * into. Asynchronous on fec_engine_stream(); max_Z / max_bg1 size the launch (largest lifting size in the batch and
- * whether any CB uses BG1). */
+ * into. Asynchronous on fec_engine_stream(); max_Z / any_bg1 size the launch: the largest lifting size in the batch, and
+ * bit 0 of any_bg1 = some codeblock uses base graph 1. FEC_LAUNCH_EVEN_Z in any_bg1: the caller guarantees that every
+ * lifting size of the batch is even and >= 4 (true for every codeblock of 3 800 bits or more); the engine then launches the
+ * packed kernel alone. Without it a second, small kernel covers the odd lifting sizes and Z = 2 (it finds nothing to do
+ * otherwise; the results are the same either way). */
+#define FEC_LAUNCH_EVEN_Z 0x2
 int fec_launch_device(fec_engine* e, const fec_cb_desc* d_descs, uint32_t n, const int8_t* d_llr, uint8_t* d_out,
                       fec_cb_result* d_results, uint32_t max_Z, int any_bg1);
 

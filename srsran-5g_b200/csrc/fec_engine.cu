@@ -8,6 +8,14 @@
 #include <cstdlib>
 #include "fec_kernel_generic.cuh"
 #include "fec_kernel_packed.cuh"
+// launch() flags, accumulated over the descriptors of a batch
+#define FEC_LF_BG1 1      // some codeblock uses base graph 1 (sizes the shared-memory layout)
+#define FEC_LF_SMALL_Z 2  // some lifting size is outside the packed kernel (odd, or 2): the generic kernel runs beside it
+static inline int launch_flags_of(uint32_t base_graph, uint32_t Z)
+{
+  return ((base_graph == 1) ? FEC_LF_BG1 : 0) | (fec_packed_covers(Z) ? 0 : FEC_LF_SMALL_Z);
+}
+#define FEC_WORK_SLOTS 1024u // counter pairs of the persistent codeblock kernel: one per launch that can be in flight
 #include "fec_tb.cuh"
 #include "fec_encode.cuh"
 #include "fec_demod.cuh"
@@ -231,6 +239,8 @@ struct fec_engine {
   cudaStream_t          stream       = nullptr; // device-resident entry points (fec_launch_device, encoder, demodulator)
   fec_dev_tables*       d_tab        = nullptr;
   fec_packed_tables*    d_ptab       = nullptr;
+  uint32_t*             d_work       = nullptr; // FEC_WORK_SLOTS x {next, done} counters of the persistent kernel
+  std::atomic<uint32_t> work_slot{0};
   bool                  packed_ok    = false;
   int8_t*               d_harq       = nullptr;
   std::atomic<uint64_t> launches{0};
@@ -321,22 +331,28 @@ int launch(fec_engine*          e,
     while (left != 0 && !e->debug_fail_launches.compare_exchange_weak(left, left - 1)) {
     }
     if (left != 0) {
-      fec_cb_generic_kernel<<<n, 32, 1u << 20, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab);
+      fec_cb_generic_kernel<<<n, 32, 1u << 20, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab, 0);
       const cudaError_t err = cudaGetLastError();
       return fail(FEC_ERR_CUDA, "codeblock kernel launch failed (injected): %s", cudaGetErrorString(err));
     }
   }
   const bool packed_ok = (e->cfg.kernel_variant != 1) && e->packed_ok;
   if (packed_ok) {
-    int r = fec_packed_launch(st, d_descs, n, d_llr, d_out, d_res, e->d_harq, e->d_tab, e->d_ptab, max_Z, any_bg1);
+    // one counter pair per launch in flight (the kernel leaves its pair zeroed): far more slots than streams
+    uint32_t* work = e->d_work + 2 * (e->work_slot.fetch_add(1, std::memory_order_relaxed) % FEC_WORK_SLOTS);
+    int r = fec_packed_launch(st, d_descs, n, d_llr, d_out, d_res, e->d_harq, e->d_tab, e->d_ptab, max_Z, any_bg1 & FEC_LF_BG1,
+                              (uint32_t)e->sm_count, work, (any_bg1 & FEC_LF_SMALL_Z) != 0);
+    if ((any_bg1 & FEC_LF_SMALL_Z) != 0) {
+      e->st_generic.fetch_add(1, std::memory_order_relaxed);
+    }
     if (r != FEC_OK) {
       return fail(r, "packed kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
     }
   } else {
-    const fec_generic_smem_layout L = fec_generic_layout(max_Z, any_bg1);
+    const fec_generic_smem_layout L = fec_generic_layout(max_Z, any_bg1 & FEC_LF_BG1);
     unsigned                      threads = ((max_Z + 31) / 32) * 32;
     threads                               = threads > 384 ? 384 : threads;
-    fec_cb_generic_kernel<<<n, threads, L.total, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab);
+    fec_cb_generic_kernel<<<n, threads, L.total, st>>>(d_descs, d_llr, d_out, d_res, e->d_harq, e->d_tab, 0);
     CU_TRY(cudaGetLastError());
     e->st_generic.fetch_add(1, std::memory_order_relaxed);
   }
@@ -835,6 +851,8 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
     e->packed_ok = e->packed_ok && fec_packed_build_rowinfo(rowinfo, *h, *hp);
     CU_TRY(cudaMemcpyToSymbol(fec_c_rowinfo, rowinfo, sizeof(rowinfo))); // constant memory of this device: the row schedule
     CU_TRY(cudaMalloc((void**)&e->d_ptab, sizeof(fec_packed_tables)));
+    CU_TRY(cudaMalloc((void**)&e->d_work, FEC_WORK_SLOTS * 2 * sizeof(uint32_t)));
+    CU_TRY(cudaMemset(e->d_work, 0, FEC_WORK_SLOTS * 2 * sizeof(uint32_t)));
     CU_TRY(cudaMemcpy(e->d_ptab, hp, sizeof(fec_packed_tables), cudaMemcpyHostToDevice));
     delete hp;
   }
@@ -923,6 +941,7 @@ void fec_engine_destroy(fec_engine* e)
   cudaFreeHost(e->h_dm_descs);
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
+  cudaFree(e->d_work);
   if (e->stream) {
     cudaStreamDestroy(e->stream);
   }
@@ -953,7 +972,10 @@ int fec_launch_device(fec_engine* e, const fec_cb_desc* d_descs, uint32_t n, con
   if (!e || !d_descs || !d_results) {
     return fail(FEC_ERR_BAD_ARG, "null argument");
   }
-  return launch(e, e->stream, d_descs, n, d_llr, d_out, d_results, max_Z, any_bg1);
+  // The descriptors are in device memory: whether a lifting size outside the packed kernel is among them is the caller's
+  // knowledge (FEC_LAUNCH_EVEN_Z); without it the generic kernel is launched beside the packed one, to be safe.
+  const int flags = ((any_bg1 & 1) ? FEC_LF_BG1 : 0) | ((any_bg1 & FEC_LAUNCH_EVEN_Z) ? 0 : FEC_LF_SMALL_Z);
+  return launch(e, e->stream, d_descs, n, d_llr, d_out, d_results, max_Z, flags);
 }
 
 int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* h_llr, size_t llr_bytes, uint8_t* h_out,
@@ -997,7 +1019,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       return fail(FEC_ERR_BAD_ARG, "descriptor %u: harq_slot %u >= %u", i, d.harq_slot, e->cfg.harq_slots);
     }
     max_Z = d.lifting_size > max_Z ? d.lifting_size : max_Z;
-    any1 |= (d.base_graph == 1);
+    any1 |= launch_flags_of(d.base_graph, d.lifting_size);
   }
   ctx_lease lease(e, -1);
   host_ctx& c      = *lease.c;
@@ -1081,7 +1103,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
         next_out = (size_t)d.out_offset + kb;
       }
       cz = d.lifting_size > cz ? d.lifting_size : cz;
-      c1 |= (d.base_graph == 1);
+      c1 |= launch_flags_of(d.base_graph, d.lifting_size);
       keep |= (d.flags & FEC_FLAG_EARLY_STOP) != 0;
     }
     CU_TRY(cudaMemcpyAsync(c.d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, in));
@@ -1354,7 +1376,7 @@ int queue_stage(fec_engine* e, uint32_t queue_id, queue_t& q, fec_cb_desc& d, co
       s.llr_used += llr_pad;
       s.out_used += (kb + 15u) & ~15u;
       s.max_Z = d.lifting_size > s.max_Z ? d.lifting_size : s.max_Z;
-      s.any_bg1 |= (d.base_graph == 1);
+      s.any_bg1 |= launch_flags_of(d.base_graph, d.lifting_size);
       ++q.depth;
       uint64_t seen = e->st_max_depth.load(std::memory_order_relaxed);
       while (q.depth > seen && !e->st_max_depth.compare_exchange_weak(seen, q.depth)) {
@@ -1711,7 +1733,7 @@ int tb_submit(fec_engine* e, host_ctx& hx, const fec_tb_desc* tbs, uint32_t n, c
     n_map += g.nof_cbs;
     aligned = aligned && (g.data_bits % 8 == 0);
     max_Z   = g.lifting_size > max_Z ? g.lifting_size : max_Z;
-    any1 |= (tb.base_graph == 1);
+    any1 |= launch_flags_of(tb.base_graph, g.lifting_size);
   }
   if (n_map > e->cfg.max_batch_cbs) {
     return fail(FEC_ERR_BAD_ARG, "%u codeblocks in one call, the engine takes %u", n_map, e->cfg.max_batch_cbs);
@@ -2782,6 +2804,7 @@ extern "C" int fec_debug_profile_read(unsigned long long* out, int reset)
   }
   if (reset) {
     unsigned long long zero[FEC_PROF_PHASES] = {};
+    zero[11] = ~0ull; // earliest CTA start (atomicMin)
     cudaMemcpyToSymbol(fec_prof_acc, zero, sizeof(zero));
   }
   return FEC_OK;

@@ -422,15 +422,28 @@ __device__ __noinline__ void fec_generic_cb(const fec_cb_desc& D,
   }
 }
 
+// Lifting sizes the packed kernel (fec_kernel_packed.cuh) decodes: Z must split into two interleaved lanes of >= 2 checks.
+// Every other codeblock (odd Z, all <= 15, and Z = 2) is left to this kernel.
+__host__ __device__ inline bool fec_packed_covers(uint32_t Z)
+{
+  return (Z % 2 == 0) && (Z >= 4);
+}
+
+// leftovers_only: the launch that accompanies the packed kernel. A CTA whose codeblock the packed kernel covers returns at
+// once (the two kernels run on the same descriptor array and share the work by lifting size).
 __global__ void __launch_bounds__(384, 2)
 fec_cb_generic_kernel(const fec_cb_desc* __restrict__ descs,
                       const int8_t* __restrict__ llr_base,
                       uint8_t* __restrict__ out_base,
                       fec_cb_result* __restrict__ results,
                       int8_t* __restrict__ harq_base,
-                      const fec_dev_tables* __restrict__ tab)
+                      const fec_dev_tables* __restrict__ tab,
+                      int leftovers_only)
 {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const fec_cb_desc D = descs[blockIdx.x];
+  if (leftovers_only && fec_packed_covers(D.lifting_size)) {
+    return;
+  }
   fec_generic_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab);
 }

@@ -25,6 +25,10 @@
 #include "fec_kernel_generic.cuh"
 #include <cuda_fp16.h>
 #include <string.h>
+#include <algorithm>
+#include <cstdlib>
+#include <map>
+#include <mutex>
 
 #define FEC_PACKED_MAX_THREADS 192
 // -DFEC_DEBUG_CHECKS: bounds checks on every shared-memory / tensor-memory access of the hot path (compute-sanitizer is closed
@@ -336,7 +340,22 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   // ---- pre-phase: everything that does not depend on the soft bits (addresses, the previous c2v messages of this row).
   // It runs BEFORE the CTA barrier that orders this row after the previous one, so warps that finished the previous row
   // early do useful work instead of waiting, and the table / state load latency overlaps the other warps' tail.
-  uint32_t a0[D], cold[D]; // a0: byte address of the pair word, bit 1 = swap bit
+  // The degree-19 rows hold 19 addresses and 19 soft words at once: their old messages are rebuilt one by one in phase A
+  // instead (19 registers less at the barrier; the persistent kernel has none to spare and spilt 28 there).
+#ifdef FEC_COLD_LATE
+  constexpr bool COLD_LATE = (D > 10);
+#else
+  constexpr bool COLD_LATE = false;
+#endif
+  uint32_t       a0[D], cold[COLD_LATE ? 1 : D]; // a0: byte address of the pair word, bit 1 = swap bit
+  uint32_t       oid, cw1, cw2, codl, com1;
+  auto           old_c2v = [&](int e) -> uint32_t {
+    const uint32_t sw  = (e < 10) ? cw1 : cw2;
+    const uint32_t ism = h2_eq_bf(oid, FEC_H2(e));            // edge e was the min1 edge
+    const uint32_t mag = h2_fma(ism, codl, com1);             // |old c2v|
+    const uint32_t sgs = imad(sw, 1u << (15 - (e % 10)), 0u); // its sign bits at 15 / 31
+    return mag ^ (sgs & H2_SIGN);                             // old c2v (one LOP3; the subtraction negates for free)
+  };
   {
     uint32_t w0, w1, w2 = 0;
     if (TM) {
@@ -364,14 +383,13 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
     const uint32_t odl = h2_sub(om2, om1); // m2 - m1 >= 0
     // state words: D <= 8: w1 = sign bits 0..7 | index << 8; D = 9, 10: w1 = sign bits 0..9, w2 = index;
     // D = 19: w1 = sign bits of edges 0..9, w2 = sign bits of edges 10..18 | index << 9 (all per 16-bit lane)
-    const uint32_t oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 10) ? w2 : ((w2 >> 9) & 0x001f001fu));
+    oid = (D <= 8) ? __byte_perm(w1, 0, 0x4341) : ((D <= 10) ? w2 : ((w2 >> 9) & 0x001f001fu));
+    cw1 = w1, cw2 = w2, codl = odl, com1 = om1;
+    if (!COLD_LATE) {
 #pragma unroll
-    for (int e = 0; e < D; ++e) {
-      const uint32_t sw  = (e < 10) ? w1 : w2;
-      const uint32_t ism = h2_eq_bf(oid, FEC_H2(e));                   // edge e was the min1 edge
-      const uint32_t mag = h2_fma(ism, odl, om1);                      // |old c2v|
-      const uint32_t sgs = imad(sw, 1u << (15 - (e % 10)), 0u);        // its sign bits at 15 / 31
-      cold[e]            = mag ^ (sgs & H2_SIGN);                      // old c2v (one LOP3; the subtraction negates for free)
+      for (int e = 0; e < D; ++e) {
+        cold[e] = old_c2v(e);
+      }
     }
   }
   // Orders this row after the rows that wrote the columns it reads. (In the extension part of both base graphs every other
@@ -391,7 +409,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   uint32_t m1 = H2_P120, m2 = H2_P120;
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    const uint32_t vraw = h2_sub(S[e], cold[e]);                                     // soft - c2v
+    const uint32_t vraw = h2_sub(S[e], COLD_LATE ? old_c2v(e) : cold[e]);            // soft - c2v
     const uint32_t y    = h2_add(h2_fma(S[e], H2_F4352, H2_F96), H2_FM96);           // nonzero, sign of S, iff |S| > 120
     const uint32_t vcl  = h2_min_xs(vraw, H2_P120);                                  // saturate at +-120
     const uint32_t vv   = h2_fma(y, H2_F2M11, vcl);                                  // "infinite" soft bits stay huge
@@ -604,10 +622,14 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint16_t* soft16, uin
     const uint32_t  Kb     = K / Z; // 22 or 10
     uint32_t        zacc   = 0x7c007c00u, keep0 = 0, keep1 = 0;
     if (threadIdx.x < H) {
+      // (the empty asm keeps the compiler from computing the 22 addresses once, outside the iteration loop, and holding
+      // them in registers through every row body)
+      uint32_t tix = threadIdx.x;
+      asm volatile("" : "+r"(tix));
       uint32_t hw[22];
 #pragma unroll
       for (uint32_t c = 0; c < 22; ++c) {
-        hw[c] = (c < Kb) ? soft32[c * H + threadIdx.x] : 0x00010001u;
+        hw[c] = (c < Kb) ? soft32[c * H + tix] : 0x00010001u;
       }
 #pragma unroll
       for (uint32_t c = 0; c < 22; ++c) {
@@ -944,10 +966,16 @@ __device__ __forceinline__ void fec_stage_transposed(const int8_t* __restrict__ 
   uint32_t*          st4 = reinterpret_cast<uint32_t*>(stage);
   const uint32_t     ng = Kp / 4, kw = Kp / 4;
   for (uint32_t g0 = threadIdx.x; g0 < ng; g0 += U * blockDim.x) {
+    // (every element is defined on every path: in the persistent kernel a register that is only written under a condition
+    // counts as live around the whole codeblock loop)
     uint32_t W[U][QM];
 #pragma unroll
     for (uint32_t u = 0; u < U; ++u) {
       const uint32_t g = g0 + u * blockDim.x;
+#pragma unroll
+      for (uint32_t k = 0; k < QM; ++k) {
+        W[u][k] = 0;
+      }
       if (g < ng) {
         if constexpr (QM % 4 == 0) {
           const uint4* src = reinterpret_cast<const uint4*>(in) + (size_t)g * (QM / 4);
@@ -1166,10 +1194,21 @@ __device__ __forceinline__ bool fec_dematch_packed(const fec_cb_desc& D,
 
 __device__ __forceinline__ bool fec_packed_cb_supported(const fec_cb_desc& D)
 {
-  // Z must split into 2 interleaved lanes: every even lifting size, all three modes. Odd Z (<= 15) and Z = 2 take the
-  // generic per-check code, whose shared-memory layout is tiny at those sizes.
-  return (D.lifting_size % 2 == 0) && (D.lifting_size >= 4) && (D.lifting_size / 2 <= blockDim.x);
+  // Z must split into 2 interleaved lanes: every even lifting size from 4, all three modes. Odd Z (<= 15) and Z = 2 are left
+  // to the generic kernel, launched beside this one when a batch can hold such codeblocks (fec_packed_launch).
+  return fec_packed_covers(D.lifting_size) && (D.lifting_size / 2 <= blockDim.x);
 }
+
+// The result store at the end of a codeblock. In the persistent kernel the codeblock index is re-read from shared memory
+// (s_cur) and the pointer is made opaque here, so that neither occupies a register through the row bodies, which are at the
+// register limit (a D = 19 row spilt 28 registers with them live).
+#define FEC_LATE_RESULT_STORE(results_, cb_, res_)                                                                             \
+  do {                                                                                                                         \
+    fec_cb_result* r_ = (results_);                                                                                            \
+    asm volatile("" : "+l"(r_));                                                                                               \
+    r_[*reinterpret_cast<volatile uint32_t*>(fec_s_cur)] = (res_);                                                             \
+    (void)(cb_);                                                                                                               \
+  } while (0)
 
 __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
                                            uint32_t           cb,
@@ -1181,7 +1220,8 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
                                            const fec_dev_tables* __restrict__ tab,
                                            const fec_packed_tables* __restrict__ ptab,
                                            uint32_t tmem_a,
-                                           uint32_t tmem_b)
+                                           uint32_t tmem_b,
+                                           uint32_t* fec_s_cur)
 {
   __shared__ uint32_t s_nsig_arr[2];
 #define s_nsig s_nsig_arr[0]
@@ -1192,7 +1232,10 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   const uint32_t K = Kb * Z, N = (nfull - 2) * Z;
   const uint32_t ne = bg1 ? 316u : 197u;
   const uint32_t invZ = 0xffffffffu / Z + 1;
-  const uint32_t tid = threadIdx.x;
+  uint32_t tid = threadIdx.x;
+#ifndef FEC_EXP_NOOPAQUE
+  asm volatile("" : "+r"(tid)); // opaque: nothing derived from it is hoisted out of the persistent loop and kept in registers
+#endif
 
 #ifdef FEC_PROFILE
   long long tp0 = clock64(), tp1 = 0, tp2 = 0, tp3 = 0;
@@ -1394,29 +1437,38 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
     res.reserved = (uint32_t)min(255ll, (tp1 - tp0) >> 8) | ((uint32_t)min(255ll, (tp2 - tp1) >> 10) << 8) |
                    ((uint32_t)min(255ll, (tp3 - tp2) >> 12) << 16) | ((uint32_t)min(255ll, (tp4 - tp3) >> 8) << 24);
 #endif
-    results[cb]            = res;
+    FEC_LATE_RESULT_STORE(results, cb, res);
   }
 }
 
 #undef s_nsig
 // Dispatcher: every codeblock the packed path covers goes there, the rest (odd Z, dematch-only
 // operations, unaligned decoder inputs) runs the generic per-check code in the same launch.
+// Persistent: the grid is no larger than what the device holds at once (fec_packed_launch) and every CTA takes codeblocks
+// from a counter until the batch is empty. A wave of 444 CTAs ending together and 444 new ones starting costs about 18 us
+// on a B200 (measured with %globaltimer, profiles/r02_phase_clocks.txt): 7 % of the headline launch and 27 % of a launch of
+// high-rate codeblocks that take 28 us each. Tensor memory is allocated once per CTA.
+// work[0]: next codeblock - gridDim.x (the first one of a CTA is blockIdx.x); work[1]: CTAs that are done. The last CTA
+// to finish clears both, so a slot is ready for the next launch without a memset.
 __global__ void __launch_bounds__(FEC_PACKED_MAX_THREADS, FEC_PACKED_CTAS_PER_SM)
 fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
+                     uint32_t n,
                      const int8_t* __restrict__ llr_base,
                      uint8_t* __restrict__ out_base,
                      fec_cb_result* __restrict__ results,
                      int8_t* __restrict__ harq_base,
                      const fec_dev_tables* __restrict__ tab,
-                     const fec_packed_tables* __restrict__ ptab)
+                     const fec_packed_tables* __restrict__ ptab,
+                     uint32_t* __restrict__ work)
 {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   __shared__ uint32_t s_tmem_base[2];
-  const fec_cb_desc D = descs[blockIdx.x];
-  if (!fec_packed_cb_supported(D)) {
-    fec_generic_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab);
-    return;
-  }
+  __shared__ uint32_t s_next, s_cur;
+#ifdef FEC_PROFILE
+  unsigned long long prof_g0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prof_g0));
+  const long long prof_c0 = clock64();
+#endif
   // Tensor memory for the check state (see the layout notes at the top): region A takes 64 columns per group of four warps,
   // region B 16 (allocations are powers of two >= 32). Three resident CTAs of six warps take 3 x (128 + 32) of the SM's 512
   // columns. One warp allocates and later frees.
@@ -1430,14 +1482,68 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_a = s_tmem_base[0], tmem_b = s_tmem_base[1];
-  fec_packed_cb(D, blockIdx.x, smem_raw, llr_base, out_base, results, harq_base, tab, ptab, tmem_a, tmem_b);
+#ifdef FEC_PROFILE
+  const long long prof_c1 = clock64();
+#endif
+  if (threadIdx.x == 0) {
+    s_next = blockIdx.x;
+  }
+  __syncthreads();
+  for (;;) {
+    // Nothing is kept in registers from one codeblock to the next, and the codeblock index lives in shared memory (s_cur):
+    // the row bodies are at the register limit.
+    const fec_cb_desc* p_descs = descs;
+    uint32_t*          p_work  = work;
+    asm volatile("" : "+l"(p_descs), "+l"(p_work));
+    const uint32_t cb = *reinterpret_cast<volatile uint32_t*>(&s_next);
+    if (cb >= n) {
+      break;
+    }
+    __syncthreads(); // s_next has been read by every thread before thread 0 draws the next number
+    const fec_cb_desc D = p_descs[cb];
+    if (threadIdx.x == 0) {
+      s_cur  = cb;
+      // in flight while this codeblock is decoded (work == nullptr: fixed stride, for measurements)
+      s_next = p_work ? gridDim.x + atomicAdd(&p_work[0], 1u) : cb + gridDim.x;
+    }
+    // (No call of the generic per-check code from here: a function call inside this loop makes the compiler save and restore
+    // 28 registers around the degree-19 row bodies. Codeblocks this kernel does not cover are skipped; the generic kernel,
+    // launched beside this one, decodes them.)
+    if (fec_packed_cb_supported(D)) {
+      fec_packed_cb(D, cb, smem_raw, llr_base, out_base, results, harq_base, tab, ptab,
+                    *reinterpret_cast<volatile uint32_t*>(&s_tmem_base[0]), *reinterpret_cast<volatile uint32_t*>(&s_tmem_base[1]),
+                    &s_cur);
+    }
+    __syncthreads(); // every warp is done with this codeblock's shared memory; s_next is visible
+  }
+#ifdef FEC_PROFILE
+  const long long prof_c2 = clock64();
+#endif
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (threadIdx.x < 32) {
-    tmem_dealloc(tmem_a, cols_a);
-    tmem_dealloc(tmem_b, cols_b);
+    tmem_dealloc(s_tmem_base[0], cols_a);
+    tmem_dealloc(s_tmem_base[1], cols_b);
   }
+  if (threadIdx.x == 0 && work != nullptr) {
+    if (atomicAdd(&work[1], 1u) == gridDim.x - 1) {
+      // every CTA has drawn its last (out of range) number: nobody touches the counters of this launch any more
+      work[0] = 0;
+      work[1] = 0;
+    }
+  }
+#ifdef FEC_PROFILE
+  if (threadIdx.x == 0) {
+    unsigned long long prof_g1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prof_g1));
+    atomicAdd(&fec_prof_acc[9], (unsigned long long)(prof_c1 - prof_c0));
+    atomicAdd(&fec_prof_acc[10], (unsigned long long)(clock64() - prof_c2));
+    atomicMin(&fec_prof_acc[11], prof_g0);
+    atomicMax(&fec_prof_acc[12], prof_g1);
+    atomicAdd(&fec_prof_acc[13], prof_g1 - prof_g0);
+    atomicAdd(&fec_prof_acc[14], 1ull);
+  }
+#endif
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------------------
@@ -1536,6 +1642,36 @@ static inline bool fec_packed_build_tables(fec_packed_tables& pt, const fec_dev_
   return found;
 }
 
+// CTAs of `threads` threads and `smem` bytes one SM holds at once (registers, shared memory, tensor memory columns).
+static inline uint32_t fec_packed_ctas_per_sm(uint32_t threads, uint32_t smem)
+{
+  static std::mutex                    mtx;
+  static std::map<uint64_t, uint32_t>  cache; // per (threads, smem): the occupancy query costs a few microseconds
+  const uint64_t                       key = ((uint64_t)threads << 32) | smem;
+  std::lock_guard<std::mutex>          lk(mtx);
+  auto                                 it = cache.find(key);
+  if (it != cache.end()) {
+    return it->second;
+  }
+  // Shared memory and tensor memory bound the residency (registers: 96 x 192 threads x 3 fits). Computed from the device
+  // attributes rather than cudaOccupancyMaxActiveBlocksPerMultiprocessor, which answered 1 for the 73 KB layout although
+  // three CTAs are resident (it does not assume the carve-out the launch picks). An overestimate is harmless: a CTA that is
+  // not resident at first starts when another one exits, finds the batch empty and exits too.
+  int dev = 0, smem_sm = 0, smem_rsv = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+  cudaDeviceGetAttribute(&smem_rsv, cudaDevAttrReservedSharedMemoryPerBlock, dev);
+  cudaFuncAttributes fa{};
+  cudaFuncGetAttributes(&fa, fec_cb_packed_kernel);
+  const uint32_t per_cta   = smem + (uint32_t)fa.sharedSizeBytes + (uint32_t)smem_rsv;
+  const uint32_t by_smem   = per_cta ? (uint32_t)smem_sm / per_cta : 1u;
+  const uint32_t by_warps  = 64u / (threads / 32u);
+  const uint32_t tmem_cols = ((threads > 128) ? 2u : 1u) * FEC_PACKED_TMEM_A_COLS + 32u;
+  const uint32_t r         = std::max(1u, std::min(std::min(by_smem, by_warps), std::min(512u / tmem_cols, 32u)));
+  cache[key]               = r;
+  return r;
+}
+
 static inline int fec_packed_launch(cudaStream_t             st,
                                     const fec_cb_desc*       descs,
                                     uint32_t                 n,
@@ -1546,16 +1682,35 @@ static inline int fec_packed_launch(cudaStream_t             st,
                                     const fec_dev_tables*    tab,
                                     const fec_packed_tables* ptab,
                                     uint32_t                 max_Z,
-                                    int                      any_bg1)
+                                    int                      any_bg1,
+                                    uint32_t                 sm_count,
+                                    uint32_t*                work,
+                                    bool                     leftovers)
 {
   uint32_t threads = ((max_Z / 2 + 31) / 32) * 32;
   threads          = threads < 32 ? 32 : (threads > FEC_PACKED_MAX_THREADS ? FEC_PACKED_MAX_THREADS : threads);
-  // The generic per-check code only runs for odd lifting sizes and Z = 2 (all <= 15): its layout is sized for those.
-  const uint32_t a = fec_generic_layout(max_Z < 15 ? max_Z : 15, any_bg1).total;
-  const uint32_t b = (max_Z >= 4) ? fec_packed_layout(max_Z & ~1u, any_bg1).total : 0;
-  const uint32_t smem = a > b ? a : b;
+  const uint32_t smem = (max_Z >= 4) ? fec_packed_layout(max_Z & ~1u, any_bg1).total : 0;
   // cudaFuncAttributeMaxDynamicSharedMemorySize is set ONCE, to the largest layout, in fec_engine_create: the attribute is
   // per-function global state and launches from several queues / threads would otherwise race on it.
-  fec_cb_packed_kernel<<<n, threads, smem, st>>>(descs, llr, out, res, harq, tab, ptab);
-  return cudaGetLastError() == cudaSuccess ? FEC_OK : FEC_ERR_CUDA;
+  if (max_Z >= 4) {
+    // FEC_B200_ONE_CTA_PER_CB=1 (measurements only): one CTA per codeblock, as before the kernel became persistent
+    static const bool one_per_cb = getenv("FEC_B200_ONE_CTA_PER_CB") != nullptr;
+    const uint32_t    resident   = sm_count * fec_packed_ctas_per_sm(threads, smem);
+    const uint32_t    grid       = (n < resident || one_per_cb) ? n : resident;
+    static const bool fixed_stride = getenv("FEC_B200_FIXED_STRIDE") != nullptr; // measurements only
+    fec_cb_packed_kernel<<<grid, threads, smem, st>>>(descs, n, llr, out, res, harq, tab, ptab, fixed_stride ? nullptr : work);
+    if (cudaGetLastError() != cudaSuccess) {
+      return FEC_ERR_CUDA;
+    }
+  }
+  if (leftovers) {
+    // Odd lifting sizes and Z = 2 (all <= 15): one small CTA per codeblock of the batch; those the packed kernel covers
+    // return at once. The two kernels touch disjoint codeblocks, HARQ slots and outputs: no ordering between them matters.
+    const uint32_t zl = max_Z < 15 ? max_Z : 15;
+    fec_cb_generic_kernel<<<n, 32, fec_generic_layout(zl, any_bg1).total, st>>>(descs, llr, out, res, harq, tab, 1);
+    if (cudaGetLastError() != cudaSuccess) {
+      return FEC_ERR_CUDA;
+    }
+  }
+  return FEC_OK;
 }

@@ -27,6 +27,7 @@ TB_SLOTS_CONTIGUOUS = 0xFFFFFFFF
 HARQ_SLOT_BYTES = 25344
 MAX_CB_OUT_BYTES = 1056
 ABI_VERSION = 8
+LAUNCH_EVEN_Z = 2  # fec_launch_device: any_bg1 flag bit
 NOALLOC_MAX_TBS, NOALLOC_MAX_CBS = 64, 2048
 
 ALL_Z = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48, 52, 56, 60,
@@ -330,10 +331,11 @@ class FecEngine:
     def harq_slot_ptr(self, slot):
         return self.lib.fec_harq_slot_ptr(self.h, slot)
 
-    def launch_device(self, d_descs_ptr, n, d_llr_ptr, d_out_ptr, d_res_ptr, max_Z, any_bg1):
-        """Asynchronous launch on self.stream; all pointers are device addresses (ints)."""
-        _check(self.lib, self.lib.fec_launch_device(self.h, d_descs_ptr, n, d_llr_ptr, d_out_ptr, d_res_ptr, max_Z,
-                                                    int(any_bg1)))
+    def launch_device(self, d_descs_ptr, n, d_llr_ptr, d_out_ptr, d_res_ptr, max_Z, any_bg1, even_z=False):
+        """Asynchronous launch on self.stream; all pointers are device addresses (ints). even_z: every lifting size of the
+        batch is even and >= 4 (FEC_LAUNCH_EVEN_Z: the packed kernel is launched alone)."""
+        flags = (1 if any_bg1 else 0) | (LAUNCH_EVEN_Z if even_z else 0)
+        _check(self.lib, self.lib.fec_launch_device(self.h, d_descs_ptr, n, d_llr_ptr, d_out_ptr, d_res_ptr, max_Z, flags))
 
     def run_host(self, descs, llr, out, results=None, soft_out=None):
         """Synchronous H2D -> kernels -> D2H over host numpy buffers (or raw pinned pointers given as ints)."""

@@ -100,10 +100,11 @@ def test_scaling_factors_other_than_default(fec, oracle, orc, sf, packed):
     try:
         dec = fec.LdpcDecoder(eng)
         rng = np.random.default_rng(int(sf * 1000))
-        n_pass = n_fail = 0
+        n_pass = n_fail = n_odd = 0
         for trial in range(60):
             bg = int(rng.choice([1, 2]))
             Z = int(rng.choice([4, 6, 9, 16, 28, 52, 104, 224, 384, 384]))
+            n_odd += 2 * (Z % 2)  # odd lifting sizes always take the generic kernel (launched beside the packed one)
             K, N = cases.dims(bg, Z)
             n_in = int(rng.integers(K + 4 * Z, N + 1))
             snr = 10 * np.log10(2 ** (2 * K / n_in) - 1) - 0.5 + float(rng.uniform(-2.0, 3.0))
@@ -122,7 +123,7 @@ def test_scaling_factors_other_than_default(fec, oracle, orc, sf, packed):
         assert n_pass >= 10 and n_fail >= 3, (n_pass, n_fail)
         st = eng.stats()
         assert st["cb_launches"] == 120
-        assert st["generic_launches"] == (0 if packed else 120), st
+        assert st["generic_launches"] == (n_odd if packed else 120), st
     finally:
         eng.close()
 
