@@ -22,8 +22,9 @@ for line in kern.split("\n"):
     if m:
         lines.append((int(m.group(1), 16), m.group(3), m.group(4)))
 # The iteration loop is inlined into the kernel: its code is the span from the load of the row schedule word (constant bank 3)
-# in front of the first HMNMX2.XORSIGN to the backward branch that closes the loop behind the last one.
-idx = [i for i, (_, op, _) in enumerate(lines) if op.startswith("HMNMX2")]
+# in front of the first HSET2 (only the row bodies use it: "edge e was the min1 edge") to the backward branch that closes the
+# loop behind the last one.
+idx = [i for i, (_, op, _) in enumerate(lines) if op.startswith("HSET2")]
 first, last = idx[0], idx[-1]
 lo_i = max(i for i in range(first) if "c[0x3]" in lines[i][2])
 hi_i = next(i for i in range(last, len(lines)) if lines[i][1].startswith("BRA") and
