@@ -600,8 +600,11 @@ def ncu_capture_numbers():
             v = float(vals[k].replace(",", ""))
             return v * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(units.get(k, ""), 1)
 
-        grid = float(vals.get("launch__grid_size", "0").replace(",", "") or 0)
-        out = {"dram_bytes": num("dram__bytes_read.sum") + num("dram__bytes_write.sum"), "codeblocks": grid,
+        # the kernel is persistent (the grid is the resident CTAs, not the codeblocks): the codeblocks of the captured launch
+        # are recorded beside the capture
+        meta = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_packed_full_meta.json")))
+        out = {"dram_bytes": num("dram__bytes_read.sum") + num("dram__bytes_write.sum"),
+               "codeblocks": float(meta["codeblocks_per_launch"]),
                "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
                "warp_instructions": num("smsp__inst_executed.sum"), "source": os.path.relpath(path, ROOT)}
     except Exception:
