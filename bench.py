@@ -328,7 +328,11 @@ def bench_transport_block(fec, eng, torch, dev, stream, args, rank):
                                   "api": "fec_tb_run_host: one descriptor per transport block, segmentation in the engine, "
                                          "codeblock kernel + TB assembly/CRC24A kernel, TB bytes back"},
             "device_resident": {"value": n_tb * info_bits / (ms * 1e-3) / 1e9, "unit": "Gbit/s", "tbs_per_launch": n_tb,
-                                "ms_per_launch": ms},
+                                "ms_per_launch": ms,
+                                # this shape against its two roofs: HBM with the algorithmic bytes of SURVEY 8(d) (E in, N soft
+                                # buffer out, K/8 out, descriptor and result), and instruction issue with the edge updates the
+                                # rows actually ran (iterations x layers x 19 edges of the first base rows x Z)
+                                "roofline": config3_roofline(fec, rr, Es, n_tb, ms, torch, dev)},
             "batch_e2e": {"value": n_tb * info_bits / batch_s / 1e9, "unit": "Gbit/s", "transport_blocks_per_call": n_tb,
                           "ms_per_call": batch_s * 1e3, "tb_crc_ok": batch_ok, "h2d_bytes_per_call": int(n_tb * tb_bytes),
                           "d2h_bytes_per_call": int(n_tb * (info_bits // 8)),
@@ -337,6 +341,31 @@ def bench_transport_block(fec, eng, torch, dev, stream, args, rank):
             "cb_crc_pass_fraction": float(((rr["status"] & fec.RES_CRC_PASS) != 0).mean()),
             "mean_iterations": float(rr["nof_ldpc_iterations"].mean()), "layers": int(rr["nof_layers"].max()),
             "first_tb_pass_fraction": float(((r1["status"] & fec.RES_CRC_PASS) != 0).mean())}
+
+
+def config3_roofline(fec, rr, Es, n_tb, ms, torch, dev):
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    n_cb = Es.size
+    algo = float(n_tb * (Es.astype(np.float64) + N + K // 8 + 8 + 48).sum())
+    sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    ipe = sass_instructions_per_edge() or 34.7
+    # BG1 rows 0..3 have 19 edges each; rows beyond have fewer, counted exactly from the layer count of each codeblock
+    deg = np.array([19, 19, 19, 19, 3, 8, 9, 7, 10, 9, 7, 8, 7, 6, 7, 7, 6, 6, 6, 6, 6, 6, 5, 5, 6, 5, 5, 4, 5, 5, 5, 5, 5, 5, 5,
+                    5, 5, 4, 5, 5, 4, 5, 4, 5, 5, 4])
+    cum = np.concatenate([[0], np.cumsum(deg)])
+    upd = float((rr["nof_ldpc_iterations"].astype(np.float64) * cum[np.minimum(rr["nof_layers"], 46)] * Z).sum())
+    issue_peak = sm * 4 * 1965e6 * 64.0 / ipe
+    return {"bound": "issue", "achieved": upd / (ms * 1e-3) / 1e9, "peak": issue_peak / 1e9, "unit": "G edge updates/s",
+            "frac": upd / (ms * 1e-3) / issue_peak,
+            "note": "the row bodies are 45 % of this shape's instructions (profiles/r02_phase_clocks.txt): dematcher, hard decision "
+                    "and CRC per iteration are the rest",
+            "hbm": {"achieved": algo / (ms * 1e-3) / 1e9, "peak": peak_gbs, "unit": "GB/s", "frac": algo / (ms * 1e-3) / 1e9 / peak_gbs,
+                    "algorithmic_bytes_per_cb": algo / (n_tb * n_cb)}}
 
 
 def bench_pdsch_encode(fec, eng, torch, dev, stream, args):
@@ -707,6 +736,44 @@ def bench_config4(fec, eng, torch, dev, stream, args, rank):
     return out
 
 
+def config5_cpu_baseline(fec, d, buf):
+    """The same slot on the host cores with the reference's own code (oracle/_ref): every codeblock of every cell through the
+    AVX-512 (or AVX2) rate dematcher + LDPC decoder + CRC, all host threads, codeblocks grouped by their parameters. The
+    reference's segmentation, TB assembly and TB CRC (microseconds per block) are not in the sample. N = 1 only."""
+    orc = ge.load_oracle()
+    if not orc.Ref.available():
+        return {"unavailable": "oracle/_ref/libref_fec.so was not shipped"}
+    ref = orc.Ref()
+    impl = orc.Ref.AVX512 if ref.impl_available(orc.Ref.AVX512) else (
+        orc.Ref.AVX2 if ref.impl_available(orc.Ref.AVX2) else orc.Ref.GENERIC)
+    nthr = host_threads()
+    groups = {}
+    for i in range(d.size):
+        cbs, _ = fec.tb_segment(d[i:i + 1])
+        for c in cbs:
+            key = (int(c["base_graph"]), int(c["lifting_size"]), int(c["E"]), int(c["qm"]), int(c["nof_filler_bits"]),
+                   int(c["crc_type"]))
+            off = int(d["llr_offset"][i]) + int(c["llr_offset"])
+            groups.setdefault(key, []).append(buf[off:off + int(c["E"])])
+    hal_to_orc = {0: orc.CRC16, 1: orc.CRC24B, 2: orc.CRC24A}
+    sec, n_cb, n_pass = 0.0, 0, 0
+    for rep in range(3):  # first pass warms the decoder objects of every thread
+        tot = 0.0
+        for (bg, z, e, qm, fill, crc), rows in groups.items():
+            s_, iters, _ = ref.batch_chain(impl, nthr, bg, z, np.stack(rows), True, 0, qm, 0, fill, hal_to_orc[crc], MAX_ITER, True)
+            tot += s_
+            if rep:
+                n_cb += len(rows)
+                n_pass += int((iters > 0).sum())
+        if rep:
+            sec += tot
+    bits = float(d["tbs"].astype(np.float64).sum())
+    return {"kind": "reference", "cores": nthr, "impl": {orc.Ref.GENERIC: "generic", orc.Ref.AVX2: "avx2", orc.Ref.AVX512: "avx512"}[impl],
+            "value": bits * 2 / sec / 1e9, "unit": "Gbit/s", "ms_per_slot": sec / 2 * 1e3, "crc_pass_fraction": n_pass / max(n_cb, 1),
+            "sample": "2 slots of the same 32 cells (%d codeblocks each, %d parameter groups), parallel decode time of the "
+                      "reference's dematcher + decoder + CRC per codeblock" % (n_cb // 2, len(groups))}
+
+
 def bench_config5(fec, torch, dev, args, rank, world, barrier, max_over_ranks):
     """BASELINE config 5: one uplink slot of 32 cells (100 MHz, 273 PRB, 4 layers; MCS mix of tests/test_gpu_tb.py: 4 cells
     256QAM R948 = 152 codeblocks, 12 cells 64QAM R873, 16 cells QPSK R120 = BG2 with repetition), cells sharded `cell mod N`
@@ -760,7 +827,11 @@ def bench_config5(fec, torch, dev, args, rank, world, barrier, max_over_ranks):
     else:
         ok_all, n_all = float(ok), float(len(mine) * reps)
     eng.close()
-    return {"workload": "32 cells x one full-slot transport block (4 x 256QAM R948, 12 x 64QAM R873, 16 x QPSK R120), cell mod N "
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu = config5_cpu_baseline(fec, d, buf)
+    return {"cpu_baseline": cpu,
+            "workload": "32 cells x one full-slot transport block (4 x 256QAM R948, 12 x 64QAM R873, 16 x QPSK R120), cell mod N "
                         "sharding, one fec_tb_run_host call per rank and slot from pinned host memory",
             "value": total_bits * reps / sec / 1e9, "unit": "Gbit/s", "ms_per_slot": sec / reps * 1e3, "cells": n_cells,
             "tb_crc_ok_fraction": ok_all / max(n_all, 1.0), "h2d_bytes_per_slot_rank0": int(lo), "d2h_bytes_per_slot_rank0": int(oo),
@@ -920,6 +991,27 @@ def run_ours(args):
     e2e_val = n * e2e_steps * world * INFO_BITS / e2e_sec / 1e9
     assert (res_h["status"] & fec.RES_DONE).all()
 
+    # ---- what the host can feed this GPU while every rank copies at once: pinned -> device, the ceiling of `e2e` ---------
+    # (profiles/ubench/h2d_bw.cu measures the same outside Python; here it is part of the line so that pcie_frac recomputes)
+    h2d_peak = None
+    try:
+        nb = min(t_llr_pin.numel(), 128 << 20)
+        src, dst = t_llr_pin.view(-1)[:nb], d_llr.view(-1)[:nb]
+        cs = torch.cuda.Stream(device=dev)
+        with torch.cuda.stream(cs):
+            dst.copy_(src, non_blocking=True)
+        cs.synchronize()
+        barrier()
+        tc0 = time.perf_counter()
+        with torch.cuda.stream(cs):
+            for _ in range(8):
+                dst.copy_(src, non_blocking=True)
+        cs.synchronize()
+        gbs = 8 * nb / (time.perf_counter() - tc0) / 1e9
+        barrier()
+        h2d_peak = -max_over_ranks(-gbs)  # the slowest rank's rate
+    except Exception:
+        pass
     stats = eng.stats()
     cfg5 = None
     if not args.no_config5:
@@ -960,7 +1052,12 @@ def run_ours(args):
                 "config": workload_config(n), "per_gpu_gbps": value / world,
                 "crc_pass_fraction": float(passed.mean()),
                 "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": n * (E + 48),
-                        "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)"},
+                        "d2h_bytes_per_step": n * (K // 8 + 8), "api": "fec_run_host (pinned host buffers)",
+                        # host -> device rate of the slowest rank with all ranks copying at once (128 MB pinned copies), the
+                        # rate the e2e steps achieved per rank, and their ratio
+                        "h2d_peak_gbs_per_gpu": h2d_peak,
+                        "h2d_achieved_gbs_per_gpu": n * (E + 48) * e2e_steps / e2e_sec / 1e9,
+                        "pcie_frac": (n * (E + 48) * e2e_steps / e2e_sec / 1e9 / h2d_peak) if h2d_peak else None},
                 "gpu_launches": int(launches), "clocks": clocks, "early_stop": early,
                 "tb_latency_us": tb_lat, "transport_block": tb, "config4_harq": cfg4, "config5_multicell": cfg5, "hal": hal,
                 "pdsch_encode": enc, "pusch_demod": dmd, "stats": stats,

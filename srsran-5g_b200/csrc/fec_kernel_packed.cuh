@@ -1221,7 +1221,8 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
                                            const fec_packed_tables* __restrict__ ptab,
                                            uint32_t tmem_a,
                                            uint32_t tmem_b,
-                                           uint32_t* fec_s_cur)
+                                           uint32_t* fec_s_cur,
+                                           bool      same_graph)
 {
   __shared__ uint32_t s_nsig_arr[2];
 #define s_nsig s_nsig_arr[0]
@@ -1248,8 +1249,10 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   uint32_t*        red    = reinterpret_cast<uint32_t*>(smem_raw + L.red);
   uint16_t*        soft16 = reinterpret_cast<uint16_t*>(smem_raw + L.soft);
 
-  // Stage the graph of this codeblock.
-  {
+  // Stage the graph of this codeblock, unless the codeblock this CTA decoded before had the same (BG, Z): the edge records
+  // are still in place (nothing else writes that part of shared memory, and the layout is a function of (BG, Z)). The 152
+  // codeblocks of a transport block share one graph.
+  if (!same_graph) {
     const uint4*   src     = reinterpret_cast<const uint4*>(ptab->edges[D.graph_index]);
     uint4*         dst     = reinterpret_cast<uint4*>(edges);
     const uint32_t soft_sw = (uint32_t)__cvta_generic_to_shared(soft16);
@@ -1258,9 +1261,9 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
       E.z += soft_sw; // column base as a shared-window address
       dst[i] = E;
     }
-    if (tid == 0) {
-      s_nsig = 0;
-    }
+  }
+  if (tid == 0) {
+    s_nsig = 0;
   }
   __syncthreads();
 
@@ -1463,7 +1466,7 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
 {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   __shared__ uint32_t s_tmem_base[2];
-  __shared__ uint32_t s_next, s_cur;
+  __shared__ uint32_t s_next, s_cur, s_graph;
 #ifdef FEC_PROFILE
   unsigned long long prof_g0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prof_g0));
@@ -1486,7 +1489,8 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
   const long long prof_c1 = clock64();
 #endif
   if (threadIdx.x == 0) {
-    s_next = blockIdx.x;
+    s_next  = blockIdx.x;
+    s_graph = 0xffffffffu; // no graph staged yet
   }
   __syncthreads();
   for (;;) {
@@ -1495,11 +1499,12 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
     const fec_cb_desc* p_descs = descs;
     uint32_t*          p_work  = work;
     asm volatile("" : "+l"(p_descs), "+l"(p_work));
-    const uint32_t cb = *reinterpret_cast<volatile uint32_t*>(&s_next);
+    const uint32_t cb         = *reinterpret_cast<volatile uint32_t*>(&s_next);
+    const uint32_t last_graph = *reinterpret_cast<volatile uint32_t*>(&s_graph);
     if (cb >= n) {
       break;
     }
-    __syncthreads(); // s_next has been read by every thread before thread 0 draws the next number
+    __syncthreads(); // s_next / s_graph have been read by every thread before thread 0 writes them again
     const fec_cb_desc D = p_descs[cb];
     if (threadIdx.x == 0) {
       s_cur  = cb;
@@ -1512,7 +1517,10 @@ fec_cb_packed_kernel(const fec_cb_desc* __restrict__ descs,
     if (fec_packed_cb_supported(D)) {
       fec_packed_cb(D, cb, smem_raw, llr_base, out_base, results, harq_base, tab, ptab,
                     *reinterpret_cast<volatile uint32_t*>(&s_tmem_base[0]), *reinterpret_cast<volatile uint32_t*>(&s_tmem_base[1]),
-                    &s_cur);
+                    &s_cur, last_graph == D.graph_index);
+      if (threadIdx.x == 0) {
+        s_graph = D.graph_index;
+      }
     }
     __syncthreads(); // every warp is done with this codeblock's shared memory; s_next is visible
   }
