@@ -27,16 +27,16 @@ eng = fec.FecEngine(device=0, harq_slots=8192, max_batch_cbs=8192)
 rng = np.random.default_rng(1)
 
 
-def run(name, n, E, qm, fill, early, esn0):
+def run(name, n, E, qm, fill, early, esn0, bg=1):
     eng.lib.fec_debug_profile_read((C.c_uint64 * 16)(), 1)
-    K, N = fec.dims(1, 384)
+    K, N = fec.dims(bg, 384)
     sigma2 = 0.5 * 10.0 ** (-esn0 / 10.0)
     pad = (E + 15) // 16 * 16
     y = 1.0 + np.sqrt(sigma2) * rng.standard_normal((n, pad), dtype=np.float32)
     llr = np.round(np.clip(2.0 * y / sigma2, -20.0, 20.0) * 6.0).astype(np.int8)
     d = fec.make_descs(n)
-    d["base_graph"], d["lifting_size"], d["qm"], d["E"], d["nof_filler_bits"] = 1, 384, qm, E, fill
-    d["crc_type"], d["max_iter"], d["mode"] = fec.CRC24B, 6, fec.MODE_CHAIN
+    d["base_graph"], d["lifting_size"], d["qm"], d["E"], d["nof_filler_bits"] = bg, 384, qm, E, fill
+    d["crc_type"], d["max_iter"], d["mode"] = (fec.CRC24B if bg == 1 else fec.CRC24A), 6, fec.MODE_CHAIN
     d["flags"] = fec.FLAG_NEW_DATA | (fec.FLAG_EARLY_STOP if early else 0)
     d["harq_slot"], d["llr_offset"], d["out_offset"] = np.arange(n), np.arange(n, dtype=np.uint64) * pad, np.arange(n) * (K // 8)
     out = np.zeros(n * (K // 8), np.uint8)
@@ -79,4 +79,6 @@ def run(name, n, E, qm, fill, early, esn0):
 run("headline (E=N, forced 6)", 444 * 4, 25344, 2, 0, False, -2.0)
 run("config 3 (E=8992, early stop, 8 dB)", 444 * 4, 8992, 8, 16, True, 8.0)
 run("headline early stop", 444 * 4, 25344, 2, 0, True, -2.0)
+run("config 5: 64QAM R873 (E=9816, 45 fillers)", 444 * 4, 9816, 6, 45, True, 6.0)
+run("config 5: QPSK R120, BG2 with repetition (E=30976)", 444 * 4, 30976, 2, 184, True, -4.0, bg=2)
 eng.close()

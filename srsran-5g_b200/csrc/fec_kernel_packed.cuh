@@ -870,6 +870,16 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
       hoff[1] = G.k0c + G.fillers - S.d2;
     }
   }
+  // Repetition (a first transmission from the start of the buffer that wraps around it, E > Ncb - fillers): position q of
+  // the circular buffer takes the LLRs p = q, q + Lc, q + 2 Lc, ... < E in that order -- the first is copied, the others are
+  // added with the saturating sum. Groups wholly inside [0, info) or [sys, Ncb) do that on words.
+  const bool wfast = G.wrapped && G.newd && S.staged && (G.k0c == 0) && (G.kstart == 0);
+  if (wfast) {
+    hg0[0] = 0;
+    hg1[0] = G.info / 4;
+    hg0[1] = (G.sys + 3) / 4;
+    hg1[1] = G.Ncb / 4;
+  }
   const uint32_t gz0 = (G.zero_from + 3) / 4; // groups from here on are all zero
 
   // (2) zero tail
@@ -877,9 +887,54 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
     harq4[g] = 0;
   }
 
+  // (3w) groups inside a data run, repetition
+  if (wfast) {
+    // four staged LLRs p .. p+3 (rate-matched order) as one word; the staging shift changes at `split`
+    auto ldw = [&](uint32_t p) -> uint32_t {
+      if (p + 3 < S.split || p >= S.split) {
+        const uint32_t x = p + ((p < S.split) ? S.d1 : S.d2), k8 = (x & 3u) * 8u;
+        const uint32_t lo = *reinterpret_cast<const uint32_t*>(S.base + (x & ~3u));
+        return (k8 == 0) ? lo : __funnelshift_r(lo, *reinterpret_cast<const uint32_t*>(S.base + (x & ~3u) + 4), k8);
+      }
+      int val[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        val[b] = fec_dematch_fetch(G, S, p + b);
+      }
+      return fec_pack4(val);
+    };
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      for (uint32_t g = hg0[r] + threadIdx.x; g < hg1[r]; g += blockDim.x) {
+        const uint32_t o0 = g * 4;
+        const uint32_t q0 = (r == 0) ? o0 : (o0 - G.fillers);
+        uint32_t       w  = ldw(q0); // E > Lc: the first pass covers every position
+        for (uint32_t p = q0 + G.Lc; p < G.E; p += G.Lc) {
+          int val[4];
+          if (p + 3 < G.E) {
+            const uint32_t x = ldw(p);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              val[b] = fec_sat_add((int)(int8_t)(w >> (8 * b)), (int)(int8_t)(x >> (8 * b)));
+            }
+          } else { // the transmission ends inside this group
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const int acc = (int)(int8_t)(w >> (8 * b));
+              val[b]        = (p + b < G.E) ? fec_sat_add(acc, fec_dematch_fetch(G, S, p + b)) : acc;
+            }
+          }
+          w = fec_pack4(val);
+        }
+        harq4[g] = w;
+        my_sig   = max(my_sig, fec_last_sig(o0, w));
+      }
+    }
+  }
+
   // (3) groups inside a data run
 #pragma unroll
-  for (int r = 0; r < 2; ++r) {
+  for (int r = 0; r < 2 && !wfast; ++r) {
     for (uint32_t g = hg0[r] + threadIdx.x; g < hg1[r]; g += blockDim.x) {
       const uint32_t o0 = g * 4;
       uint32_t       w  = *reinterpret_cast<const uint32_t*>(S.base + (o0 - hoff[r]));
@@ -1063,7 +1118,12 @@ __device__ __forceinline__ uint32_t fec_dematch_direct(const fec_dematch_geom& G
       return *reinterpret_cast<const uint32_t*>(S.base + o0);
     }
     if (o0 >= G.sys && o0 + 4 <= run1_hi) {
-      return *reinterpret_cast<const uint32_t*>(S.base + (o0 - G.fillers));
+      const uint32_t x = o0 - G.fillers, k8 = (x & 3u) * 8u; // k8 is the same for every group of the codeblock
+      const uint32_t lo = *reinterpret_cast<const uint32_t*>(S.base + (x & ~3u));
+      if (k8 == 0) {
+        return lo;
+      }
+      return __funnelshift_r(lo, *reinterpret_cast<const uint32_t*>(S.base + (x & ~3u) + 4), k8);
     }
     if (o0 >= G.zero_from) {
       return 0u;
@@ -1129,10 +1189,15 @@ __device__ __forceinline__ bool fec_dematch_packed(const fec_cb_desc& D,
   S.split  = (G.k0c < G.info) ? min(G.E, G.info - G.k0c) : 0u;
   S.d1     = G.k0c & 3u;
   S.d2     = S.d1 + (G.fillers & 3u);
-  const bool transposed = (G.E + 8 <= stage_cap) && (G.Kp % 4 == 0) && (S.d1 == 0) && (S.d2 == 0) &&
-                          ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) && (G.qm == 2 || G.qm == 4 || G.qm == 6 || G.qm == 8);
-  // direct path (fec_dematch_direct): also fills the decoder's soft bits
-  const bool direct = transposed && G.newd && !G.wrapped && (D.k0 == 0) && (G.Z % 8 == 0) && (D.mode == FEC_MODE_CHAIN);
+  const bool can_transpose = (G.E + 8 <= stage_cap) && (G.Kp % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) &&
+                             (G.qm == 2 || G.qm == 4 || G.qm == 6 || G.qm == 8);
+  // direct path (fec_dematch_direct): also fills the decoder's soft bits. It reads the run behind the filler gap with
+  // unaligned word loads when the number of fillers is not a multiple of four, so it never needs the staging shifts.
+  const bool direct = can_transpose && G.newd && !G.wrapped && (D.k0 == 0) && (G.Z % 8 == 0) && (D.mode == FEC_MODE_CHAIN);
+  if (direct) {
+    S.d1 = S.d2 = 0;
+  }
+  const bool transposed = can_transpose && (S.d1 == 0) && (S.d2 == 0);
   if (transposed) {
     switch (G.qm) {
       case 2:

@@ -92,6 +92,27 @@ def test_config3_shape_512_codeblocks(fec, engine, oracle, orc):
     assert n_pass >= 100 and n_fail >= 30, (n_pass, n_fail)
 
 
+def test_config5_shapes(fec, engine, oracle, orc):
+    """The other two codeblock shapes of BASELINE config 5: 64QAM R873 (45 fillers: not a multiple of four, so the run behind
+    the filler gap is read with unaligned word loads) and QPSK R120 on BG2 with repetition (E > N: the transmission wraps
+    around the circular buffer and the passes are summed in order)."""
+    rng = np.random.default_rng(55)
+    items = []
+    for i in range(192):
+        E = 9816 if i % 2 else 9840
+        p = dict(bg=1, Z=384, E=E, rv=0, qm=6, Nref=0, fill=45, poly=orc.CRC24B, max_iter=6, early=bool(i % 3))
+        snr = 10 * np.log10(2 ** (2 * (8448 - 45) / E) - 1) - 0.5 + float(rng.uniform(-1.5, 3.0))
+        llr, _ = oracle.make_case(1, 384, E, 0, 6, 0, 45, orc.CRC24B, snr, seed=120000 + i)
+        items.append(dict(p=p, llr=llr, slot=i))
+    for i in range(48):
+        E = 30976 if i % 2 else 30968
+        p = dict(bg=2, Z=384, E=E, rv=0, qm=2, Nref=0, fill=184, poly=orc.CRC24B, max_iter=6, early=bool(i % 3))
+        llr, _ = oracle.make_case(2, 384, E, 0, 2, 0, 184, orc.CRC24B, float(rng.uniform(-8.5, -4.0)), seed=130000 + i)
+        items.append(dict(p=p, llr=llr, slot=200 + i))
+    n_pass, n_fail, _ = _check(fec, engine, oracle, items, "config5")
+    assert n_pass >= 60 and n_fail >= 10, (n_pass, n_fail)
+
+
 @pytest.mark.parametrize("sf,packed", [(0.5, True), (0.75, True), (0.9, False)])
 def test_scaling_factors_other_than_default(fec, oracle, orc, sf, packed):
     """The decoder alone (LdpcDecoder mirror, MODE_DECODE) with another normalisation factor against the oracle's decoder
