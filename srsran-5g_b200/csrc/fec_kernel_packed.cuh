@@ -937,7 +937,13 @@ __device__ __forceinline__ uint32_t fec_dematch_groups(const fec_dematch_geom& G
   for (int r = 0; r < 2 && !wfast; ++r) {
     for (uint32_t g = hg0[r] + threadIdx.x; g < hg1[r]; g += blockDim.x) {
       const uint32_t o0 = g * 4;
-      uint32_t       w  = *reinterpret_cast<const uint32_t*>(S.base + (o0 - hoff[r]));
+      // (aligned by construction after the byte-wise staging, whose shifts d1 / d2 exist for that; the transposed staging
+      // has no shifts and the word is put together from two)
+      const uint32_t x = o0 - hoff[r], k8 = (x & 3u) * 8u;
+      uint32_t       w = *reinterpret_cast<const uint32_t*>(S.base + (x & ~3u));
+      if (k8 != 0) {
+        w = __funnelshift_r(w, *reinterpret_cast<const uint32_t*>(S.base + (x & ~3u) + 4), k8);
+      }
       if (!G.newd) {
         const uint32_t old = G.hzero ? 0u : harq4[g];
         int            val[4];
@@ -1194,10 +1200,10 @@ __device__ __forceinline__ bool fec_dematch_packed(const fec_cb_desc& D,
   // direct path (fec_dematch_direct): also fills the decoder's soft bits. It reads the run behind the filler gap with
   // unaligned word loads when the number of fillers is not a multiple of four, so it never needs the staging shifts.
   const bool direct = can_transpose && G.newd && !G.wrapped && (D.k0 == 0) && (G.Z % 8 == 0) && (D.mode == FEC_MODE_CHAIN);
-  if (direct) {
-    S.d1 = S.d2 = 0;
+  if (can_transpose) {
+    S.d1 = S.d2 = 0; // no staging shifts: the readers put unaligned words together themselves
   }
-  const bool transposed = can_transpose && (S.d1 == 0) && (S.d2 == 0);
+  const bool transposed = can_transpose;
   if (transposed) {
     switch (G.qm) {
       case 2:
