@@ -21,14 +21,20 @@ for line in kern.split("\n"):
     m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(@!?U?P\d+\s+)?([A-Z0-9_.]+)(.*?);", line)
     if m:
         lines.append((int(m.group(1), 16), m.group(3), m.group(4)))
-# The iteration loop is inlined into the kernel: its code is the span from the load of the row schedule word (constant bank 3)
-# in front of the first HSET2 (only the row bodies use it: "edge e was the min1 edge") to the backward branch that closes the
-# loop behind the last one.
+# The iteration loop is inlined into the kernel: its code is the span of the row loop -- from the target of the backward branch
+# that closes the loop behind the last HSET2 (only the row bodies use that opcode: "edge e was the min1 edge") to that branch.
 idx = [i for i, (_, op, _) in enumerate(lines) if op.startswith("HSET2")]
 first, last = idx[0], idx[-1]
-lo_i = max(i for i in range(first) if "c[0x3]" in lines[i][2])
-hi_i = next(i for i in range(last, len(lines)) if lines[i][1].startswith("BRA") and
-            int(re.findall(r"0x([0-9a-f]+)", lines[i][2])[-1], 16) <= lines[lo_i][0])
+
+
+def bra_target(i):
+    t = re.findall(r"0x([0-9a-f]+)", lines[i][2])
+    return int(t[-1], 16) if t else None
+
+
+hi_i = next(i for i in range(last, len(lines)) if lines[i][1].startswith("BRA") and bra_target(i) is not None and
+            bra_target(i) <= lines[first][0])
+lo_i = next(i for i in range(len(lines)) if lines[i][0] >= bra_target(hi_i))
 lo, hi = lines[lo_i][0], lines[hi_i][0] + 16
 body = [(a_, op) for a_, op, _ in lines[lo_i:hi_i + 1]]
 ops = collections.Counter(op for _, op in body)

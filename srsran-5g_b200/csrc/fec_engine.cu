@@ -1032,12 +1032,15 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   // (also measured: 1/2, 3/4, 5/4, 3/2 and 2 waves per chunk, and a finer-cut first wave: all 1-3 % slower end to end)
   // The first wave is cut finer (1/4, 1/4, 1/2 of a wave): the first kernel starts after a quarter of the first wave's copy
   // instead of all of it; from then on the copy engine stays ahead of the SMs.
+  // FEC_B200_CHUNK_WAVES (measurements): waves per chunk after the first wave
+  static const double chunk_waves  = getenv("FEC_B200_CHUNK_WAVES") ? atof(getenv("FEC_B200_CHUNK_WAVES")) : 1.0;
+  const uint32_t      chunk_steady = std::max<uint32_t>(1u, (uint32_t)(chunk_waves * wave));
   const auto chunk_len = [&](uint32_t c0) -> uint32_t {
     if (chunk == n) {
       return n;
     }
     const uint32_t q   = wave / 4;
-    const uint32_t len = (c0 < 2 * q) ? q : (c0 < wave) ? wave - 2 * q : wave;
+    const uint32_t len = (c0 < 2 * q) ? q : (c0 < wave) ? wave - 2 * q : chunk_steady;
     return (n - c0 < len) ? (n - c0) : len;
   };
   if (chunk != n) {

@@ -68,7 +68,7 @@ struct fec_packed_tables {
 };
 
 struct fec_packed_smem_layout {
-  uint32_t state, edges, bitsw, red, soft, total;
+  uint32_t state, edges, prog, bitsw, red, soft, total;
 };
 
 __host__ __device__ inline uint32_t fec_packed_row_words(uint32_t d)
@@ -114,6 +114,8 @@ __host__ __device__ inline fec_packed_smem_layout fec_packed_layout(uint32_t Z, 
   o       = (o + 15) & ~15u;
   L.edges = o;
   o += ne * 16;
+  L.prog = o; // row program: one 16-byte record per base row (fec_packed_iteration)
+  o += 48 * 16;
   L.bitsw = o;
   o += ((Kb * Z + 31) / 32 + 1) * 4;
   L.red = o;
@@ -296,6 +298,12 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t a)
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r) : "r"(a) : "memory");
   return r;
 }
+__device__ __forceinline__ uint4 lds_u128(uint32_t a)
+{
+  uint4 r;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a) : "memory");
+  return r;
+}
 __device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v)
 {
   asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
@@ -325,14 +333,13 @@ __device__ __forceinline__ uint32_t imul_hi(uint32_t a, uint32_t b)
 // D = row degree (compile time so that the per-edge values stay in registers). Lane 0 = check t, lane 1 = check t+H.
 // TM: the row's state words live in tensor memory at taddr (2 or 3 consecutive columns of this thread's lane).
 template <int D, bool TM>
-__device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, // shared-window address of the soft array
-                                               uint32_t*              st,     // state words of this row for thread t (!TM)
-                                               uint32_t               taddr,  // tensor-memory address of the row's words (TM)
-                                               const fec_packed_edge* ed,     // D edge records (shared memory)
-                                               uint32_t               H,
-                                               uint32_t               t,
-                                               uint32_t               scale_mul,
-                                               uint32_t               scale_add)
+__device__ __forceinline__ void fec_packed_row(uint32_t st,    // !TM: shared-window address of this thread's first state word
+                                               uint32_t h4,    //      distance in bytes between the state words of a row (4 H)
+                                               uint32_t taddr, // TM: tensor-memory address of this thread's state words
+                                               uint32_t ed,    // shared-window address of the row's D edge records
+                                               uint32_t t,
+                                               uint32_t scale_mul,
+                                               uint32_t scale_add)
 {
   constexpr int  NW   = (D <= 8) ? 2 : 3;
   const uint32_t t4   = t * 4;
@@ -367,15 +374,15 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
         tmem_ld2(taddr, w0, w1);
       }
     } else {
-      w0 = st[0];
-      w1 = st[H];
+      w0 = lds_u32(st);
+      w1 = lds_u32(st + h4);
       if (NW == 3) {
-        w2 = st[2 * H];
+        w2 = lds_u32(st + 2 * h4);
       }
     }
 #pragma unroll
     for (int e = 0; e < D; ++e) {
-      const uint4    E = *reinterpret_cast<const uint4*>(&ed[e]);
+      const uint4    E = lds_u128(ed + 16 * e);
       const uint32_t u = imad(t4, 1u, E.x);               // the adds on the FMA pipe: the ALU pipe is the busier one
       a0[e]            = imad(min(u + E.y, u), 1u, E.z);  // VIADDMNMX.U32: the cyclic wrap and the swap bit in one
     }
@@ -401,7 +408,7 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
   uint32_t S[D];
 #pragma unroll
   for (int e = 0; e < D; ++e) {
-    FEC_CHECK((a0[e] & 1u) == 0 && (a0[e] & ~2u) >= soft_s && (a0[e] & ~2u) + 4 <= soft_s + 68u * 4u * H, "row: soft address", a0[e] - soft_s);
+    FEC_CHECK((a0[e] & 1u) == 0 && (a0[e] & ~2u) + 4 <= 233472u, "row: soft address", a0[e]);
     const uint32_t x = lds_u32(a0[e] & ~2u);
     S[e]             = prmt_f4e(x, x, a0[e]); // address bit 1 set: the two lanes come swapped
   }
@@ -468,10 +475,10 @@ __device__ __forceinline__ void fec_packed_row(uint32_t               soft_s, //
       tmem_st2(taddr, nw0, nw1);
     }
   } else {
-    st[0] = nw0;
-    st[H] = nw1;
+    sts_u32(st, nw0);
+    sts_u32(st + h4, nw1);
     if (NW == 3) {
-      st[2 * H] = nw2;
+      sts_u32(st + 2 * h4, nw2);
     }
   }
 }
@@ -491,16 +498,14 @@ enum { // instantiation codes: tensor-memory rows of degree 3..10, then the shar
 };
 
 // One decoder iteration over the layers in use.
-__device__ __forceinline__ void fec_packed_iteration(uint32_t               soft_s,
-                                                  uint32_t*              state,
-                                                  const fec_packed_edge* edges,
-                                                  uint32_t               bg, // 0 = BG1, 1 = BG2
-                                                  uint32_t               H,
-                                                  uint32_t               nlayers,
-                                                  uint32_t               smul,
-                                                  uint32_t               sadd,
-                                                  uint32_t               tm_b, // this warp's address of region B / A
-                                                  uint32_t               tm_a)
+__device__ __forceinline__ void fec_packed_iteration(uint32_t prog,  // shared-window address of the row program
+                                                     uint32_t state, // shared-window address of the state area
+                                                     uint32_t H,
+                                                     uint32_t nlayers,
+                                                     uint32_t smul,
+                                                     uint32_t sadd,
+                                                     uint32_t tm_b, // this warp's address of region B / A
+                                                     uint32_t tm_a)
 {
   const uint32_t tid = threadIdx.x;
   if ((tid & ~31u) >= H) {
@@ -511,28 +516,30 @@ __device__ __forceinline__ void fec_packed_iteration(uint32_t               soft
   }
   // Lanes past H in the last warp repeat the work of thread H-1 (identical loads, identical stores; their own, identical
   // copy of the tensor-memory state) so that whole warps reach the barrier inside the row function.
-  const uint32_t tq  = min(tid, H - 1);
-  uint32_t*      stq = state + tq;
-  const uint32_t row_a = (bg ? 42u : 46u) - FEC_PACKED_TMEM_A_ROWS;
+  const uint32_t tq = min(tid, H - 1);
+  const uint32_t h4 = 4 * H;
+  const uint32_t sq = state + 4 * tq;
+  const uint32_t dab = tm_a - tm_b;
   for (uint32_t l = 0; l < nlayers; ++l) {
-    const uint32_t         info = fec_c_rowinfo[bg][l];
-    const fec_packed_edge* ed   = edges + (info & 0x1ffu);
-    const uint32_t         so   = (info >> 9) & 0xffu;
-    const uint32_t         ta   = ((l >= row_a) ? tm_a : tm_b) + so;
-    switch ((info >> 17) & 15u) {
-      case FEC_ROW_T3: fec_packed_row<3, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_T4: fec_packed_row<4, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_T5: fec_packed_row<5, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_T6: fec_packed_row<6, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_T7: fec_packed_row<7, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_T8: fec_packed_row<8, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_T9: fec_packed_row<9, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_T10: fec_packed_row<10, true>(soft_s, nullptr, ta, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_S3: fec_packed_row<3, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_S8: fec_packed_row<8, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_S9: fec_packed_row<9, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
-      case FEC_ROW_S10: fec_packed_row<10, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
-      default: fec_packed_row<19, false>(soft_s, stq + so * H, 0u, ed, H, tq, smul, sadd); break;
+    // row program record: x = address of the row's edge records, y = state offset (shared memory: bytes from the state
+    // area; tensor memory: column inside the region), z = instantiation, w = 1 for region A
+    const uint4    P  = lds_u128(prog + 16 * l);
+    const uint32_t ta = imad(P.w, dab, tm_b + P.y);
+    const uint32_t sa = sq + P.y;
+    switch (P.z) {
+      case FEC_ROW_T3: fec_packed_row<3, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_T4: fec_packed_row<4, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_T5: fec_packed_row<5, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_T6: fec_packed_row<6, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_T7: fec_packed_row<7, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_T8: fec_packed_row<8, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_T9: fec_packed_row<9, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_T10: fec_packed_row<10, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
+      case FEC_ROW_S3: fec_packed_row<3, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
+      case FEC_ROW_S8: fec_packed_row<8, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
+      case FEC_ROW_S9: fec_packed_row<9, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
+      case FEC_ROW_S10: fec_packed_row<10, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
+      default: fec_packed_row<19, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
     }
   }
 }
@@ -1332,6 +1339,20 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
       E.z += soft_sw; // column base as a shared-window address
       dst[i] = E;
     }
+    // The row program (what fec_packed_iteration reads, one 16-byte record per base row): the row schedule word of constant
+    // memory decoded once per graph instead of once per row and iteration.
+    const uint32_t nrows = bg1 ? 46u : 42u, row_a0 = fec_packed_row_a(bg1), row_b0 = fec_packed_row_b(bg1);
+    const uint32_t edges_sw = (uint32_t)__cvta_generic_to_shared(edges);
+    for (uint32_t l = tid; l < nrows; l += blockDim.x) {
+      const uint32_t info = fec_c_rowinfo[bg1 ? 0 : 1][l];
+      const uint32_t so   = (info >> 9) & 0xffu;
+      uint4          P;
+      P.x = edges_sw + 16u * (info & 0x1ffu);
+      P.y = (l >= row_b0) ? so : so * H * 4u;
+      P.z = (info >> 17) & 15u;
+      P.w = (l >= row_a0) ? 1u : 0u;
+      reinterpret_cast<uint4*>(smem_raw + L.prog)[l] = P;
+    }
   }
   if (tid == 0) {
     s_nsig = 0;
@@ -1455,7 +1476,8 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   const uint32_t  crc_poly = tab->crc_poly[D.crc_type], crc_top = 1u << tab->crc_len[D.crc_type];
   __syncthreads();
   const uint32_t smul = ptab->scale_mul, sadd = ptab->scale_add;
-  const uint32_t soft_s = (uint32_t)__cvta_generic_to_shared(soft16);
+  const uint32_t prog_s  = (uint32_t)__cvta_generic_to_shared(smem_raw + L.prog);
+  const uint32_t state_s = (uint32_t)__cvta_generic_to_shared(state);
 
 #ifdef FEC_PROFILE
   tp2 = clock64();
@@ -1464,7 +1486,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
-    fec_packed_iteration(soft_s, state, edges, bg1 ? 0u : 1u, H, nlayers, smul, sadd, tm_b, tm_a);
+    fec_packed_iteration(prog_s, state_s, H, nlayers, smul, sadd, tm_b, tm_a);
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     FEC_PROF_MARK(5);
     if (early_stop) {
