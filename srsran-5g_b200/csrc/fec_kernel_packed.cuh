@@ -498,8 +498,7 @@ enum { // instantiation codes: tensor-memory rows of degree 3..10, then the shar
 };
 
 // One decoder iteration over the layers in use.
-__device__ __forceinline__ void fec_packed_iteration(uint32_t prog,  // shared-window address of the row program
-                                                     uint32_t state, // shared-window address of the state area
+__device__ __forceinline__ void fec_packed_iteration(uint32_t prog, // shared-window address of the row program
                                                      uint32_t H,
                                                      uint32_t nlayers,
                                                      uint32_t smul,
@@ -518,14 +517,14 @@ __device__ __forceinline__ void fec_packed_iteration(uint32_t prog,  // shared-w
   // copy of the tensor-memory state) so that whole warps reach the barrier inside the row function.
   const uint32_t tq = min(tid, H - 1);
   const uint32_t h4 = 4 * H;
-  const uint32_t sq = state + 4 * tq;
   const uint32_t dab = tm_a - tm_b;
   for (uint32_t l = 0; l < nlayers; ++l) {
-    // row program record: x = address of the row's edge records, y = state offset (shared memory: bytes from the state
-    // area; tensor memory: column inside the region), z = instantiation, w = 1 for region A
+    // row program record: x = address of the row's edge records, y = where the state is (shared memory: shared-window address
+    // of thread 0's first word; tensor memory: column inside the region), z = instantiation, w = 1 for region A
     const uint4    P  = lds_u128(prog + 16 * l);
     const uint32_t ta = imad(P.w, dab, tm_b + P.y);
-    const uint32_t sa = sq + P.y;
+    const uint32_t sa = imad(tq, 4u, P.y);
+    __builtin_assume(P.z <= FEC_ROW_S19);
     switch (P.z) {
       case FEC_ROW_T3: fec_packed_row<3, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
       case FEC_ROW_T4: fec_packed_row<4, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
@@ -1343,12 +1342,13 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
     // memory decoded once per graph instead of once per row and iteration.
     const uint32_t nrows = bg1 ? 46u : 42u, row_a0 = fec_packed_row_a(bg1), row_b0 = fec_packed_row_b(bg1);
     const uint32_t edges_sw = (uint32_t)__cvta_generic_to_shared(edges);
+    const uint32_t state_sw = (uint32_t)__cvta_generic_to_shared(state);
     for (uint32_t l = tid; l < nrows; l += blockDim.x) {
       const uint32_t info = fec_c_rowinfo[bg1 ? 0 : 1][l];
       const uint32_t so   = (info >> 9) & 0xffu;
       uint4          P;
       P.x = edges_sw + 16u * (info & 0x1ffu);
-      P.y = (l >= row_b0) ? so : so * H * 4u;
+      P.y = (l >= row_b0) ? so : (state_sw + so * H * 4u);
       P.z = (info >> 17) & 15u;
       P.w = (l >= row_a0) ? 1u : 0u;
       reinterpret_cast<uint4*>(smem_raw + L.prog)[l] = P;
@@ -1477,7 +1477,6 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   __syncthreads();
   const uint32_t smul = ptab->scale_mul, sadd = ptab->scale_add;
   const uint32_t prog_s  = (uint32_t)__cvta_generic_to_shared(smem_raw + L.prog);
-  const uint32_t state_s = (uint32_t)__cvta_generic_to_shared(state);
 
 #ifdef FEC_PROFILE
   tp2 = clock64();
@@ -1486,7 +1485,7 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
   bool     pass = false;
   uint32_t it   = 0;
   for (; it < D.max_iter; ++it) {
-    fec_packed_iteration(prog_s, state_s, H, nlayers, smul, sadd, tm_b, tm_a);
+    fec_packed_iteration(prog_s, H, nlayers, smul, sadd, tm_b, tm_a);
     __syncthreads(); // the last row's stores, before the hard decision or the next iteration
     FEC_PROF_MARK(5);
     if (early_stop) {
