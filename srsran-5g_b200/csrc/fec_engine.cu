@@ -305,6 +305,27 @@ inline void stats_result(fec_engine* e, const fec_cb_result& r)
   e->st_iter_hist[it].fetch_add(1, std::memory_order_relaxed);
 }
 
+// The same for a batch: counted locally, then a handful of atomic adds (7104 results cost 100 us one by one).
+struct stats_batch {
+  uint64_t results = 0, crc_pass = 0, hist[FEC_STATS_ITER_BINS] = {};
+  void     add(const fec_cb_result& r)
+  {
+    ++results;
+    crc_pass += (r.status & FEC_RES_CRC_PASS) ? 1 : 0;
+    ++hist[r.nof_ldpc_iterations < FEC_STATS_ITER_BINS ? r.nof_ldpc_iterations : FEC_STATS_ITER_BINS - 1];
+  }
+  void flush(fec_engine* e)
+  {
+    e->st_results.fetch_add(results, std::memory_order_relaxed);
+    e->st_crc_pass.fetch_add(crc_pass, std::memory_order_relaxed);
+    for (int b = 0; b < FEC_STATS_ITER_BINS; ++b) {
+      if (hist[b]) {
+        e->st_iter_hist[b].fetch_add(hist[b], std::memory_order_relaxed);
+      }
+    }
+  }
+};
+
 int launch(fec_engine*          e,
            cudaStream_t         st,
            const fec_cb_desc*   d_descs,
@@ -313,7 +334,8 @@ int launch(fec_engine*          e,
            uint8_t*             d_out,
            fec_cb_result*       d_res,
            uint32_t             max_Z,
-           int                  any_bg1)
+           int                  any_bg1,
+           uint32_t             grid_div = 1) // > 1: use 1/grid_div of the resident CTAs (chunks that overlap each other)
 {
   if (n == 0) {
     return FEC_OK;
@@ -341,7 +363,7 @@ int launch(fec_engine*          e,
     // one counter pair per launch in flight (the kernel leaves its pair zeroed): far more slots than streams
     uint32_t* work = e->d_work + 2 * (e->work_slot.fetch_add(1, std::memory_order_relaxed) % FEC_WORK_SLOTS);
     int r = fec_packed_launch(st, d_descs, n, d_llr, d_out, d_res, e->d_harq, e->d_tab, e->d_ptab, max_Z, any_bg1 & FEC_LF_BG1,
-                              (uint32_t)e->sm_count, work, (any_bg1 & FEC_LF_SMALL_Z) != 0);
+                              (uint32_t)e->sm_count, work, (any_bg1 & FEC_LF_SMALL_Z) != 0, grid_div);
     if ((any_bg1 & FEC_LF_SMALL_Z) != 0) {
       e->st_generic.fetch_add(1, std::memory_order_relaxed);
     }
@@ -1135,7 +1157,9 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       }
       cudaEventRecord(trace_ev[2 * nchunks], st);
     }
-    int r = launch(e, st, c.d_descs + c0, cn, c.d_llr, c.d_out, c.d_res + c0, cz, c1);
+    // FEC_B200_CHUNK_GRID_DIV (measurements): chunk kernels on fewer CTAs so that consecutive chunks interleave on the SMs
+    static const uint32_t chunk_grid_div = getenv("FEC_B200_CHUNK_GRID_DIV") ? (uint32_t)atoi(getenv("FEC_B200_CHUNK_GRID_DIV")) : 1u;
+    int r = launch(e, st, c.d_descs + c0, cn, c.d_llr, c.d_out, c.d_res + c0, cz, c1, (chunk != n) ? chunk_grid_div : 1u);
     if (r != FEC_OK) {
       return r;
     }
@@ -1167,8 +1191,12 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   const auto t_sync = std::chrono::steady_clock::now();
   memcpy(h_results, c.h_res_pin, n * sizeof(fec_cb_result));
   guard.ok = true;
-  for (uint32_t i = 0; i < n; ++i) {
-    stats_result(e, h_results[i]);
+  {
+    stats_batch sb;
+    for (uint32_t i = 0; i < n; ++i) {
+      sb.add(h_results[i]);
+    }
+    sb.flush(e);
   }
   if (trace) {
     const auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
@@ -2002,6 +2030,8 @@ int tb_complete(fec_engine* e, host_ctx& hx, fec_tb_result* h_results, fec_cb_re
   const fec_cb_result* h_cbres = reinterpret_cast<const fec_cb_result*>(hx.h_rblk);
   const fec_tb_result* h_tbres = reinterpret_cast<const fec_tb_result*>(hx.h_rblk + P.off_tbres);
   auto                 t_sync  = P.t_enq;
+  stats_batch          sb;
+  // (the per-slot flags below are published by the mutex of the context release that follows this call: relaxed stores)
   const auto           deliver = [&](uint32_t t) {
     const fec_tb_result& R = h_tbres[t];
     const fec_tb_job&    J = h_jobs[t];
@@ -2015,9 +2045,9 @@ int tb_complete(fec_engine* e, host_ctx& hx, fec_tb_result* h_results, fec_cb_re
       if (ref.result_index >= 0) {
         cr = h_cbres[ref.result_index];
         if (cr.status & FEC_RES_CRC_PASS) {
-          e->cb_ok[ref.slot].store(1);
+          e->cb_ok[ref.slot].store(1, std::memory_order_relaxed);
         }
-        stats_result(e, cr);
+        sb.add(cr);
       } else {
         cr.nof_ldpc_iterations = 0;
         cr.status              = FEC_RES_SKIPPED | FEC_RES_CRC_PASS | FEC_RES_DONE;
@@ -2033,8 +2063,8 @@ int tb_complete(fec_engine* e, host_ctx& hx, fec_tb_result* h_results, fec_cb_re
       // join_and_notify: the buffer is released -> free the HARQ context entries.
       for (uint32_t r = 0; r < J.nof_cbs; ++r) {
         const uint32_t slot = h_map[J.map_first + r].slot;
-        e->fresh[slot].store(1);
-        e->cb_ok[slot].store(0);
+        e->fresh[slot].store(1, std::memory_order_relaxed);
+        e->cb_ok[slot].store(0, std::memory_order_relaxed);
       }
     } else if (R.tb_delivered) {
       // All codeblock CRCs good but the TB CRC is not: at least one false positive, start over (reset_codeblocks_crc).
@@ -2061,6 +2091,7 @@ int tb_complete(fec_engine* e, host_ctx& hx, fec_tb_result* h_results, fec_cb_re
   for (; err == cudaSuccess && t < n; ++t) {
     deliver(t);
   }
+  sb.flush(e);
   if (err != cudaSuccess) {
     // The device faulted: whatever was not handed over yet failed; the freed-slot marks this call consumed are put back.
     cudaGetLastError();

@@ -1785,7 +1785,8 @@ static inline int fec_packed_launch(cudaStream_t             st,
                                     int                      any_bg1,
                                     uint32_t                 sm_count,
                                     uint32_t*                work,
-                                    bool                     leftovers)
+                                    bool                     leftovers,
+                                    uint32_t                 grid_div = 1)
 {
   uint32_t threads = ((max_Z / 2 + 31) / 32) * 32;
   threads          = threads < 32 ? 32 : (threads > FEC_PACKED_MAX_THREADS ? FEC_PACKED_MAX_THREADS : threads);
@@ -1796,7 +1797,8 @@ static inline int fec_packed_launch(cudaStream_t             st,
     // FEC_B200_ONE_CTA_PER_CB=1 (measurements only): one CTA per codeblock, as before the kernel became persistent
     static const bool one_per_cb = getenv("FEC_B200_ONE_CTA_PER_CB") != nullptr;
     const uint32_t    resident   = sm_count * fec_packed_ctas_per_sm(threads, smem);
-    const uint32_t    grid       = (n < resident || one_per_cb) ? n : resident;
+    const uint32_t    cap        = std::max(1u, resident / std::max(1u, grid_div));
+    const uint32_t    grid       = one_per_cb ? n : std::min(n, cap);
     static const bool fixed_stride = getenv("FEC_B200_FIXED_STRIDE") != nullptr; // measurements only
     fec_cb_packed_kernel<<<grid, threads, smem, st>>>(descs, n, llr, out, res, harq, tab, ptab, fixed_stride ? nullptr : work);
     if (cudaGetLastError() != cudaSuccess) {
