@@ -367,7 +367,9 @@ __device__ __forceinline__ void fec_packed_row(uint32_t st,    // !TM: shared-wi
     uint32_t w0, w1, w2 = 0;
     if (TM) {
       FEC_CHECK((taddr & 0xffffu) + NW <= 512u && ((taddr >> 16) & 0x1fu) == 0, "row: tensor-memory address", taddr);
-      tmem_wait_st(); // this thread's store of the previous tensor-memory row
+      // this thread's store of the previous tensor-memory row (one wait per iteration in front of the row loop would be enough
+      // for correctness -- every row has columns of its own -- and was measured: 1.5 % slower)
+      tmem_wait_st();
       if (NW == 3) {
         tmem_ld3(taddr, w0, w1, w2);
       } else {
