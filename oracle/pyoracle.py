@@ -545,3 +545,44 @@ class RefTb:
         soft = np.zeros((nof_cbs, cb_len), np.int8)
         n = self.lib.ref_tb_peek(self.h, C.c_uint(buffer_id), C.c_uint(nof_cbs), C.c_uint(cb_len), _p(flags), _p(soft))
         return None if n < 0 else (flags.astype(bool), soft)
+
+
+# ---- UL-SCH demultiplexer (last pointer: ulsch_demultiplex_impl) --------------------------------------
+ULSCH_CFG_FIELDS = ("qm", "nof_layers", "nof_prb", "start_symbol", "nof_symbols", "nof_harq_ack_rvd", "dmrs_type", "dmrs_mask",
+                    "nof_cdm_groups_without_data", "nof_harq_ack_bits", "nof_enc_harq_ack_bits", "nof_csi_part1_bits",
+                    "nof_enc_csi_part1_bits", "nof_csi_part2_bits", "nof_enc_csi_part2_bits", "csi2_after_csi1")
+
+
+def ulsch_cfg_array(cfg):
+    return np.array([int(cfg.get(k, 0)) for k in ULSCH_CFG_FIELDS], np.uint32)
+
+
+def ulsch_codeword_len(cfg):
+    """Soft bits of the allocation: every RE of every OFDM symbol that is not a DM-RS RE, times Qm x layers."""
+    per_prb_dmrs = 12 - cfg["nof_cdm_groups_without_data"] * (6 if cfg["dmrs_type"] == 1 else 4)
+    n = 0
+    for l in range(cfg["start_symbol"], cfg["start_symbol"] + cfg["nof_symbols"]):
+        n += (per_prb_dmrs if (cfg["dmrs_mask"] >> l) & 1 else 12) * cfg["nof_prb"]
+    return n * cfg["qm"] * cfg["nof_layers"]
+
+
+def _ulsch_call(fn, cfg, codeword, scrambling, extra=()):
+    codeword = np.ascontiguousarray(codeword, np.int8)
+    scrambling = np.ascontiguousarray(scrambling, np.uint8)
+    cap = codeword.size
+    outs = [np.zeros(cap, np.int8) for _ in range(4)]
+    counts = np.zeros(8, np.uint32)
+    c = ulsch_cfg_array(cfg)
+    rc = fn(_p(c), _p(codeword), C.c_uint32(codeword.size), _p(scrambling), *extra, *[_p(o) for o in outs], C.c_uint32(cap),
+            _p(counts))
+    return rc, [o[:int(k)] for o, k in zip(outs, counts[:4])], counts[4:].astype(bool)
+
+
+def oracle_ulsch_demux(oracle, cfg, codeword, scrambling):
+    """oracle/fec_ulsch.c. Returns (rc, [sch, harq_ack, csi1, csi2], ended flags)."""
+    return _ulsch_call(oracle.lib.orc_ulsch_demux, cfg, codeword, scrambling)
+
+
+def ref_ulsch_demux(ref, cfg, codeword, scrambling, block=4096):
+    """The reference's ulsch_demultiplex_impl (oracle/_ref), fed `block` soft bits per on_new_block call."""
+    return _ulsch_call(ref.lib.ref_ulsch_demux, cfg, codeword, scrambling, extra=(C.c_uint32(block),))
