@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define FEC_B200_ABI_VERSION 8
+#define FEC_B200_ABI_VERSION 9
 
 typedef enum {
   FEC_OK             = 0,
@@ -448,6 +448,57 @@ int fec_tb_run_host_symbols(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, c
                             const fec_demod_desc* h_demod, uint32_t n_demod, const float* h_symbols,
                             const float* h_noise_vars, size_t nof_symbols, uint32_t flavour, uint8_t* h_out, size_t out_bytes,
                             fec_tb_result* h_results, fec_cb_result* h_cb_results);
+
+/* ---- UL-SCH demultiplexing on the device (last pointer) ------------------------------------------------
+ * Replaces ulsch_demultiplex (include/srsran/phy/upper/channel_processors/pusch/ulsch_demultiplex.h:44-101, implementation
+ * lib/phy/upper/channel_processors/pusch/ulsch_demultiplex_impl.cpp): the descrambled soft bits of a PUSCH codeword that
+ * carries UCI are sorted into the SCH data stream (what the decoder's on_new_softbits receives) and the HARQ-ACK / CSI Part 1
+ * / CSI Part 2 streams (what the UCI decoders receive), TS 38.212 6.2.7, bit for bit as the reference does it: allocation
+ * order and spacing, HARQ-ACK of one or two bits on reserved elements puncturing what lies underneath (those soft bits read
+ * as zeros), placeholder bits of one- and two-bit payloads with their scrambling undone. fec_ulsch_cfg mirrors
+ * ulsch_demultiplex::configuration plus the arguments of set_csi_part2. */
+typedef struct fec_ulsch_cfg {
+  uint8_t  qm;                          /* bits per modulation symbol: 1 (pi/2-BPSK), 2, 4, 6, 8                           */
+  uint8_t  nof_layers;                  /* 1..4                                                                             */
+  uint8_t  start_symbol_index;          /* first OFDM symbol of the allocation                                              */
+  uint8_t  nof_symbols;
+  uint8_t  dmrs_type;                   /* 1 or 2                                                                           */
+  uint8_t  nof_cdm_groups_without_data;
+  uint8_t  csi2_after_csi1;             /* 0: CSI Part 2 is known from the start (set_csi_part2 right after demultiplex, as  */
+                                        /* the reference's unit test does); 1: it becomes known when the last CSI Part 1   */
+                                        /* soft bit has been delivered (pusch_processor_impl.cpp:73-101), and is placed from */
+                                        /* that OFDM symbol on                                                              */
+  uint8_t  reserved0;
+  uint16_t nof_prb;
+  uint16_t dmrs_symbol_mask;            /* bit l = OFDM symbol l of the slot carries DM-RS                                  */
+  uint32_t nof_harq_ack_rvd;            /* G^HARQ-ACK_rvd                                                                   */
+  uint32_t nof_harq_ack_bits;           /* O_HARQ-ACK                                                                       */
+  uint32_t nof_enc_harq_ack_bits;       /* G^HARQ-ACK                                                                       */
+  uint32_t nof_csi_part1_bits;          /* O_CSI-1                                                                          */
+  uint32_t nof_enc_csi_part1_bits;      /* G^CSI-1                                                                          */
+  uint32_t nof_csi_part2_bits;          /* O_CSI-2                                                                          */
+  uint32_t nof_enc_csi_part2_bits;      /* G^CSI-2                                                                          */
+} fec_ulsch_cfg; /* 40 bytes */
+
+typedef struct fec_ulsch_sizes {
+  uint32_t nof_codeword_bits; /* soft bits of the allocation (input)                                                          */
+  uint32_t nof_sch_bits;      /* soft bits delivered to each stream (a punctured element counts for HARQ-ACK AND underneath)  */
+  uint32_t nof_harq_ack_bits;
+  uint32_t nof_csi_part1_bits;
+  uint32_t nof_csi_part2_bits;
+} fec_ulsch_sizes;
+
+/* Host only (no GPU): validates the configuration and tells how many soft bits each stream receives. */
+int fec_ulsch_demux_sizes(const fec_ulsch_cfg* cfg, fec_ulsch_sizes* out);
+/* Device-resident: codeword, packed scrambling sequence (MSB first like bit_buffer, nof_codeword_bits bits; may be NULL when
+ * no UCI field has a payload of one or two bits) and the four outputs (each with room for its stream) already in HBM;
+ * asynchronous on fec_engine_stream(). d_sch is what fec_tb_desc.llr_offset / fec_launch_device then reads. */
+int fec_ulsch_demux_launch_device(fec_engine* e, const fec_ulsch_cfg* cfg, const int8_t* d_codeword,
+                                  const uint8_t* d_scrambling_seq, int8_t* d_sch, int8_t* d_harq_ack, int8_t* d_csi_part1,
+                                  int8_t* d_csi_part2);
+/* Host buffers: H2D + kernel + D2H, synchronous (the mirror of feeding the reference's pusch_codeword_buffer). */
+int fec_ulsch_demux_run_host(fec_engine* e, const fec_ulsch_cfg* cfg, const int8_t* h_codeword, const uint8_t* h_scrambling_seq,
+                             int8_t* h_sch, int8_t* h_harq_ack, int8_t* h_csi_part1, int8_t* h_csi_part2);
 
 #ifdef __cplusplus
 }

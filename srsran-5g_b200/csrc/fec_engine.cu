@@ -19,6 +19,7 @@ static inline int launch_flags_of(uint32_t base_graph, uint32_t Z)
 #include "fec_tb.cuh"
 #include "fec_encode.cuh"
 #include "fec_demod.cuh"
+#include "fec_ulsch.cuh"
 #include "ldpc_tables.h"
 #include <algorithm>
 #include <atomic>
@@ -247,6 +248,17 @@ struct fec_engine {
   std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
   // host-call contexts: ctxs[0] also serves the encoder / demodulator host paths (their staging is engine-wide)
   std::vector<host_ctx*>  ctxs;
+  // UL-SCH demultiplexing plans (fec_ulsch.cuh), by configuration: flags and segments in HBM
+  struct ulsch_entry {
+    fec_ulsch_cfg  cfg;
+    fec_ulsch_plan plan;
+    fec_ulsch_seg* d_segs  = nullptr;
+    uint8_t*       d_flags = nullptr;
+    uint64_t       stamp   = 0;
+  };
+  std::mutex               ulsch_mtx;
+  std::vector<ulsch_entry> ulsch_cache;
+  uint64_t                 ulsch_clock = 0;
   std::mutex              ctx_mtx;
   std::condition_variable ctx_cv;
   std::vector<queue_t>* queues = nullptr;
@@ -964,6 +976,10 @@ void fec_engine_destroy(fec_engine* e)
   cudaFree(e->d_tab);
   cudaFree(e->d_ptab);
   cudaFree(e->d_work);
+  for (auto& en : e->ulsch_cache) {
+    cudaFree(en.d_segs);
+    cudaFree(en.d_flags);
+  }
   if (e->stream) {
     cudaStreamDestroy(e->stream);
   }
@@ -2827,6 +2843,171 @@ int fec_tb_assemble_device_noalloc(fec_engine* e, const fec_tb_desc* tbs, uint32
 }
 
 } // extern "C"
+
+
+// ---- UL-SCH demultiplexing (fec_ulsch.cuh) --------------------------------------------------------------------------------
+int fec_ulsch_demux_sizes(const fec_ulsch_cfg* cfg, fec_ulsch_sizes* out)
+{
+  if (!cfg || !out) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  fec_ulsch_plan P;
+  if (!fec_ulsch_plan_build(*cfg, P)) {
+    return fail(FEC_ERR_BAD_ARG, "invalid UL-SCH multiplexing configuration");
+  }
+  out->nof_codeword_bits  = (uint32_t)P.flags.size() * P.bits_per_re;
+  out->nof_sch_bits       = P.nof_re[0] * P.bits_per_re;
+  out->nof_harq_ack_bits  = P.nof_re[1] * P.bits_per_re;
+  out->nof_csi_part1_bits = P.nof_re[2] * P.bits_per_re;
+  out->nof_csi_part2_bits = P.nof_re[3] * P.bits_per_re;
+  return FEC_OK;
+}
+
+namespace {
+// The plan of a configuration, resident in HBM. Called and used under e->ulsch_mtx (an eviction frees device memory, which
+// waits for the kernels that read it).
+int ulsch_plan_get(fec_engine* e, const fec_ulsch_cfg& cfg, fec_engine::ulsch_entry** out)
+{
+  for (auto& en : e->ulsch_cache) {
+    if (memcmp(&en.cfg, &cfg, sizeof(cfg)) == 0) {
+      en.stamp = ++e->ulsch_clock;
+      *out     = &en;
+      return FEC_OK;
+    }
+  }
+  fec_engine::ulsch_entry en;
+  en.cfg = cfg;
+  if (!fec_ulsch_plan_build(cfg, en.plan)) {
+    return fail(FEC_ERR_BAD_ARG, "invalid UL-SCH multiplexing configuration");
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  if (e->ulsch_cache.size() >= 16) { // drop the least recently used
+    size_t lru = 0;
+    for (size_t i = 1; i < e->ulsch_cache.size(); ++i) {
+      lru = (e->ulsch_cache[i].stamp < e->ulsch_cache[lru].stamp) ? i : lru;
+    }
+    cudaFree(e->ulsch_cache[lru].d_segs);
+    cudaFree(e->ulsch_cache[lru].d_flags);
+    e->ulsch_cache.erase(e->ulsch_cache.begin() + lru);
+  }
+  const size_t fb = en.plan.flags.size(), sb = en.plan.segs.size() * sizeof(fec_ulsch_seg);
+  CU_TRY(cudaMalloc((void**)&en.d_flags, fb ? fb : 1));
+  CU_TRY(cudaMalloc((void**)&en.d_segs, sb ? sb : 1));
+  CU_TRY(cudaMemcpy(en.d_flags, en.plan.flags.data(), fb, cudaMemcpyHostToDevice));
+  CU_TRY(cudaMemcpy(en.d_segs, en.plan.segs.data(), sb, cudaMemcpyHostToDevice));
+  en.stamp = ++e->ulsch_clock;
+  e->ulsch_cache.push_back(std::move(en));
+  *out = &e->ulsch_cache.back();
+  return FEC_OK;
+}
+
+int ulsch_launch(fec_engine* e, cudaStream_t st, const fec_ulsch_cfg& cfg, const int8_t* d_cw, const uint8_t* d_seq,
+                 int8_t* d_sch, int8_t* d_harq, int8_t* d_csi1, int8_t* d_csi2, fec_ulsch_sizes* sizes)
+{
+  std::lock_guard<std::mutex> lk(e->ulsch_mtx);
+  fec_engine::ulsch_entry*    en = nullptr;
+  int                         rc = ulsch_plan_get(e, cfg, &en);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  const fec_ulsch_plan& P = en->plan;
+  fec_ulsch_launch      L;
+  L.bits_per_re = P.bits_per_re;
+  L.qm          = cfg.qm;
+  L.mode[0]     = 0;
+  L.mode[1]     = (cfg.nof_harq_ack_bits <= 2) ? cfg.nof_harq_ack_bits : 0;
+  L.mode[2]     = (cfg.nof_csi_part1_bits <= 2) ? cfg.nof_csi_part1_bits : 0;
+  L.mode[3]     = (cfg.nof_csi_part2_bits <= 2) ? cfg.nof_csi_part2_bits : 0;
+  L.harq_punctures = (cfg.nof_harq_ack_bits == 1 || cfg.nof_harq_ack_bits == 2) ? 1u : 0u;
+  const bool needs_seq = cfg.qm > 1 && ((P.nof_re[1] && L.mode[1]) || (P.nof_re[2] && L.mode[2]) || (P.nof_re[3] && L.mode[3]));
+  if (needs_seq && !d_seq) {
+    return fail(FEC_ERR_BAD_ARG, "a UCI field of one or two bits needs the scrambling sequence of the codeword");
+  }
+  if (!d_cw || (P.nof_re[0] && !d_sch) || (P.nof_re[1] && !d_harq) || (P.nof_re[2] && !d_csi1) || (P.nof_re[3] && !d_csi2)) {
+    return fail(FEC_ERR_BAD_ARG, "null buffer for a stream that receives soft bits");
+  }
+  if (sizes) {
+    sizes->nof_codeword_bits  = (uint32_t)P.flags.size() * P.bits_per_re;
+    sizes->nof_sch_bits       = P.nof_re[0] * P.bits_per_re;
+    sizes->nof_harq_ack_bits  = P.nof_re[1] * P.bits_per_re;
+    sizes->nof_csi_part1_bits = P.nof_re[2] * P.bits_per_re;
+    sizes->nof_csi_part2_bits = P.nof_re[3] * P.bits_per_re;
+  }
+  if (P.segs.empty()) {
+    return FEC_OK;
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  fec_ulsch_demux_kernel<<<(unsigned)P.segs.size(), FEC_ULSCH_SEG, 0, st>>>(en->d_segs, en->d_flags, L, d_cw, d_seq, d_sch, d_harq,
+                                                                           d_csi1, d_csi2);
+  CU_TRY(cudaGetLastError());
+  e->launches.fetch_add(1);
+  return FEC_OK;
+}
+} // namespace
+
+int fec_ulsch_demux_launch_device(fec_engine* e, const fec_ulsch_cfg* cfg, const int8_t* d_codeword,
+                                  const uint8_t* d_scrambling_seq, int8_t* d_sch, int8_t* d_harq_ack, int8_t* d_csi_part1,
+                                  int8_t* d_csi_part2)
+{
+  if (!e || !cfg) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  return ulsch_launch(e, e->stream, *cfg, d_codeword, d_scrambling_seq, d_sch, d_harq_ack, d_csi_part1, d_csi_part2, nullptr);
+}
+
+int fec_ulsch_demux_run_host(fec_engine* e, const fec_ulsch_cfg* cfg, const int8_t* h_codeword, const uint8_t* h_scrambling_seq,
+                             int8_t* h_sch, int8_t* h_harq_ack, int8_t* h_csi_part1, int8_t* h_csi_part2)
+{
+  if (!e || !cfg || !h_codeword) {
+    return fail(FEC_ERR_BAD_ARG, "null argument");
+  }
+  fec_ulsch_sizes z;
+  int             rc = fec_ulsch_demux_sizes(cfg, &z);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  CU_TRY(cudaSetDevice(e->cfg.device));
+  // one device allocation for everything (this is the convenience path; the production path keeps all of it in HBM)
+  const size_t a16 = 15;
+  const size_t o_cw = 0, o_seq = (o_cw + z.nof_codeword_bits + a16) & ~a16, o_sch = (o_seq + (z.nof_codeword_bits + 7) / 8 + a16) & ~a16,
+               o_h = (o_sch + z.nof_sch_bits + a16) & ~a16, o_c1 = (o_h + z.nof_harq_ack_bits + a16) & ~a16,
+               o_c2 = (o_c1 + z.nof_csi_part1_bits + a16) & ~a16, total = o_c2 + z.nof_csi_part2_bits + 16;
+  uint8_t* d = nullptr;
+  CU_TRY(cudaMalloc((void**)&d, total));
+  cudaStream_t st = e->stream;
+  cudaError_t  err = cudaMemcpyAsync(d + o_cw, h_codeword, z.nof_codeword_bits, cudaMemcpyHostToDevice, st);
+  if (err == cudaSuccess && h_scrambling_seq) {
+    err = cudaMemcpyAsync(d + o_seq, h_scrambling_seq, (z.nof_codeword_bits + 7) / 8, cudaMemcpyHostToDevice, st);
+  }
+  if (err == cudaSuccess) {
+    rc = ulsch_launch(e, st, *cfg, (const int8_t*)(d + o_cw), h_scrambling_seq ? d + o_seq : nullptr, (int8_t*)(d + o_sch),
+                      (int8_t*)(d + o_h), (int8_t*)(d + o_c1), (int8_t*)(d + o_c2), nullptr);
+  }
+  const struct {
+    int8_t*  h;
+    size_t   off;
+    uint32_t n;
+  } outs[4] = {{h_sch, o_sch, z.nof_sch_bits}, {h_harq_ack, o_h, z.nof_harq_ack_bits}, {h_csi_part1, o_c1, z.nof_csi_part1_bits},
+               {h_csi_part2, o_c2, z.nof_csi_part2_bits}};
+  for (int k = 0; k < 4 && err == cudaSuccess && rc == FEC_OK; ++k) {
+    if (outs[k].n) {
+      if (!outs[k].h) {
+        rc = fail(FEC_ERR_BAD_ARG, "null buffer for a stream that receives soft bits");
+        break;
+      }
+      err = cudaMemcpyAsync(outs[k].h, d + outs[k].off, outs[k].n, cudaMemcpyDeviceToHost, st);
+    }
+  }
+  const cudaError_t serr = cudaStreamSynchronize(st);
+  cudaFree(d);
+  if (rc != FEC_OK) {
+    return rc;
+  }
+  if (err != cudaSuccess || serr != cudaSuccess) {
+    return fail(FEC_ERR_CUDA, "UL-SCH demultiplexing failed on the device: %s", cudaGetErrorString(err != cudaSuccess ? err : serr));
+  }
+  return FEC_OK;
+}
 
 #ifdef FEC_PROFILE
 // Profiling build only (profiles/scripts/phase_clocks.py): the phase clocks accumulated by fec_cb_packed_kernel.

@@ -26,7 +26,7 @@ MAX_TB_CBS = 162
 TB_SLOTS_CONTIGUOUS = 0xFFFFFFFF
 HARQ_SLOT_BYTES = 25344
 MAX_CB_OUT_BYTES = 1056
-ABI_VERSION = 8
+ABI_VERSION = 9
 LAUNCH_EVEN_Z = 2  # fec_launch_device: any_bg1 flag bit
 NOALLOC_MAX_TBS, NOALLOC_MAX_CBS = 64, 2048
 
@@ -89,6 +89,39 @@ class EngineCfg(C.Structure):
 
 
 STATS_ITER_BINS = 16
+
+
+class UlschCfg(C.Structure):
+    """fec_ulsch_cfg: mirror of ulsch_demultiplex::configuration + the arguments of set_csi_part2."""
+    _fields_ = [("qm", C.c_uint8), ("nof_layers", C.c_uint8), ("start_symbol_index", C.c_uint8), ("nof_symbols", C.c_uint8),
+                ("dmrs_type", C.c_uint8), ("nof_cdm_groups_without_data", C.c_uint8), ("csi2_after_csi1", C.c_uint8),
+                ("reserved0", C.c_uint8), ("nof_prb", C.c_uint16), ("dmrs_symbol_mask", C.c_uint16),
+                ("nof_harq_ack_rvd", C.c_uint32), ("nof_harq_ack_bits", C.c_uint32), ("nof_enc_harq_ack_bits", C.c_uint32),
+                ("nof_csi_part1_bits", C.c_uint32), ("nof_enc_csi_part1_bits", C.c_uint32), ("nof_csi_part2_bits", C.c_uint32),
+                ("nof_enc_csi_part2_bits", C.c_uint32)]
+
+
+class UlschSizes(C.Structure):
+    _fields_ = [("nof_codeword_bits", C.c_uint32), ("nof_sch_bits", C.c_uint32), ("nof_harq_ack_bits", C.c_uint32),
+                ("nof_csi_part1_bits", C.c_uint32), ("nof_csi_part2_bits", C.c_uint32)]
+
+
+def ulsch_cfg(**kw):
+    """Builds a UlschCfg from the field names of ulsch_demultiplex::configuration (start_symbol / dmrs_mask accepted as short
+    forms, as tests/ulsch_cases.py writes them)."""
+    alias = {"start_symbol": "start_symbol_index", "dmrs_mask": "dmrs_symbol_mask"}
+    c = UlschCfg()
+    for k, v in kw.items():
+        setattr(c, alias.get(k, k), int(v))
+    return c
+
+
+def ulsch_demux_sizes(cfg):
+    """fec_ulsch_demux_sizes (host only): soft bits per stream as a dict."""
+    lib = load_library()
+    z = UlschSizes()
+    _check(lib, lib.fec_ulsch_demux_sizes(C.byref(cfg), C.byref(z)))
+    return {name: int(getattr(z, name)) for name, _ in UlschSizes._fields_}
 
 
 class EngineStats(C.Structure):
@@ -175,6 +208,9 @@ def load_library():
     lib.fec_tb_reset_slots.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
     lib.fec_engine_get_stats.argtypes = [C.c_void_p, C.POINTER(EngineStats)]
     lib.fec_engine_debug_fail_launches.argtypes = [C.c_void_p, C.c_uint32]
+    lib.fec_ulsch_demux_sizes.argtypes = [C.POINTER(UlschCfg), C.POINTER(UlschSizes)]
+    lib.fec_ulsch_demux_launch_device.argtypes = [C.c_void_p, C.POINTER(UlschCfg)] + [C.c_void_p] * 6
+    lib.fec_ulsch_demux_run_host.argtypes = [C.c_void_p, C.POINTER(UlschCfg)] + [C.c_void_p] * 6
     lib.fec_tb_enqueue.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
                                    C.c_size_t, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
     lib.fec_tb_poll.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
@@ -450,6 +486,28 @@ class FecEngine:
                                                      noise_vars.ctypes.data, noise_vars.size, llr.ctypes.data, llr.nbytes,
                                                      flavour))
         return llr
+
+    def ulsch_demux_run_host(self, cfg, codeword, scrambling_bits=None):
+        """fec_ulsch_demux_run_host: the soft bits of a codeword with UCI -> (sch, harq_ack, csi_part1, csi_part2) int8 arrays.
+        scrambling_bits: the unpacked scrambling sequence of the codeword (0/1 per soft bit), packed MSB first here as the
+        reference's bit_buffer holds it; needed only when a UCI field has a payload of one or two bits."""
+        z = ulsch_demux_sizes(cfg)
+        cw = np.ascontiguousarray(codeword, np.int8)
+        if cw.size != z["nof_codeword_bits"]:
+            raise FecError("codeword of %d soft bits, the allocation holds %d" % (cw.size, z["nof_codeword_bits"]))
+        seq = None if scrambling_bits is None else np.packbits(np.ascontiguousarray(scrambling_bits, np.uint8))
+        outs = [np.zeros(max(z[k], 1), np.int8) for k in ("nof_sch_bits", "nof_harq_ack_bits", "nof_csi_part1_bits",
+                                                            "nof_csi_part2_bits")]
+        _check(self.lib, self.lib.fec_ulsch_demux_run_host(self.h, C.byref(cfg), cw.ctypes.data,
+                                                           None if seq is None else seq.ctypes.data,
+                                                           *[o.ctypes.data for o in outs]))
+        return [o[:z[k]] for o, k in zip(outs, ("nof_sch_bits", "nof_harq_ack_bits", "nof_csi_part1_bits", "nof_csi_part2_bits"))]
+
+    def ulsch_demux_launch_device(self, cfg, d_codeword, d_scrambling_seq, d_sch, d_harq_ack, d_csi_part1, d_csi_part2):
+        """Asynchronous on self.stream; device addresses (ints, 0 / None for streams that receive nothing)."""
+        _check(self.lib, self.lib.fec_ulsch_demux_launch_device(self.h, C.byref(cfg), d_codeword, d_scrambling_seq or None,
+                                                                d_sch or None, d_harq_ack or None, d_csi_part1 or None,
+                                                                d_csi_part2 or None))
 
     def tb_run_host_symbols(self, tbs, demod, symbols, noise_vars, out, slots=None, cb_results=False,
                             flavour=DEMOD_AVX512):

@@ -35,6 +35,7 @@ def test_struct_layouts_match_header(fec):
     assert fec.RESULT_DTYPE.itemsize == 8
     assert C.sizeof(fec.EngineCfg) == 48
     assert C.sizeof(fec.EngineStats) == 8 * (14 + fec.STATS_ITER_BINS)
+    assert C.sizeof(fec.UlschCfg) == 40 and C.sizeof(fec.UlschSizes) == 20
 
 
 def test_desc_prepare_fills_k0_like_the_reference(fec):
