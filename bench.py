@@ -613,6 +613,54 @@ def bench_pusch_demod(fec, eng, torch, dev, stream, args):
     return out
 
 
+def bench_ulsch_demux(fec, eng, torch, dev, stream):
+    """UL-SCH demultiplexing (fec_ulsch_demux_launch_device) on the config-3 allocation (273 PRB x 4 layers 256QAM, 13 data
+    symbols + 1 DM-RS symbol: 1.36 M soft bits) carrying a 2-bit HARQ-ACK on reserved elements, CSI Part 1 and CSI Part 2:
+    46 codewords back to back, device-resident. HBM-bound byte moving: reads the codeword once, writes every soft bit once."""
+    cfg = fec.ulsch_cfg(qm=8, nof_layers=4, nof_prb=273, start_symbol=0, nof_symbols=14, dmrs_type=1, dmrs_mask=0b100,
+                        nof_cdm_groups_without_data=2, nof_harq_ack_rvd=64 * 32, nof_harq_ack_bits=2, nof_enc_harq_ack_bits=48 * 32,
+                        nof_csi_part1_bits=7, nof_enc_csi_part1_bits=300 * 32, nof_csi_part2_bits=20,
+                        nof_enc_csi_part2_bits=800 * 32)
+    z = fec.ulsch_demux_sizes(cfg)
+    n, reps = z["nof_codeword_bits"], 46
+    rng = np.random.default_rng(3)
+    d_cw = torch.from_numpy(rng.integers(-100, 101, (reps, n)).astype(np.int8)).to(dev)
+    d_seq = torch.from_numpy(np.packbits(rng.integers(0, 2, n).astype(np.uint8))).to(dev)
+    d_sch = torch.zeros((reps, z["nof_sch_bits"] + 64), dtype=torch.int8, device=dev)
+    d_uci = [torch.zeros(max(z[k], 1), dtype=torch.int8, device=dev) for k in ("nof_harq_ack_bits", "nof_csi_part1_bits",
+                                                                             "nof_csi_part2_bits")]
+    torch.cuda.synchronize()
+
+    def step():
+        for r in range(reps):
+            eng.ulsch_demux_launch_device(cfg, d_cw[r].data_ptr(), d_seq.data_ptr(), d_sch[r].data_ptr(),
+                                          *[u.data_ptr() for u in d_uci])
+
+    step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(5):
+            step()
+        e1.record(stream)
+    stream.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    moved = reps * (n + sum(z[k] for k in ("nof_sch_bits", "nof_harq_ack_bits", "nof_csi_part1_bits", "nof_csi_part2_bits")))
+    return {"workload": "273 PRB x 4 layers 256QAM, 2-bit HARQ-ACK on reserved elements + CSI Part 1 + CSI Part 2, %d soft bits per "
+                        "codeword, %d codewords (one launch each) per step" % (n, reps),
+            "value": reps * n / (ms * 1e-3) / 1e9, "unit": "G soft bits/s", "ms_per_step": ms, "us_per_codeword": ms * 1e3 / reps,
+            "sizes": z,
+            "roofline": {"bound": "hbm", "achieved": moved / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": moved / (ms * 1e-3) / 1e9 / peak,
+                         "note": "one launch per codeword of 84 CTAs: launch-bound at this size, not bandwidth-bound"}}
+
+
 def ncu_capture_numbers():
     """DRAM traffic per codeblock and issue statistics of the committed ncu --set full capture of the decode kernel
     (profiles/r02_ncu_packed_full_metrics.csv: raw page of the .ncu-rep, filtered), read at run time so that the line can be
@@ -968,6 +1016,11 @@ def run_ours(args):
     dmd = None
     if not args.no_demod and world == 1:
         dmd = bench_pusch_demod(fec, eng, torch, dev, stream, args)
+    if dmd is not None:
+        try:
+            dmd["ulsch_demux"] = bench_ulsch_demux(fec, eng, torch, dev, stream)
+        except Exception as ex:  # a side leg must not take the line down
+            dmd["ulsch_demux"] = {"error": str(ex)}
     cfg4 = None
     if not args.no_config4 and world == 1:
         cfg4 = bench_config4(fec, eng, torch, dev, stream, args, rank)

@@ -280,19 +280,61 @@ fec_ulsch_demux_kernel(const fec_ulsch_seg* __restrict__ segs,
   const uint32_t B   = L.bits_per_re;
   const uint32_t pos = (S.first_re + t) * B; // position of the element's first soft bit in the codeword
   int8_t*        out[4] = {o_sch, o_harq, o_csi1, o_csi2};
-  int8_t         x[32];
+  // Fast path: an element whose soft bits are whole 32-bit words and that is copied as it is (no placeholder rules for the
+  // streams it belongs to). The stream bases come from cudaMalloc-aligned buffers in the engine's own calls; a caller's
+  // unaligned pointer takes the byte path.
+  const bool punct = L.harq_punctures && (f & FEC_ULSCH_F_HARQ);
+  bool       plain = (B % 4u == 0) && ((reinterpret_cast<uintptr_t>(codeword) & 3u) == 0);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if ((f >> k) & 1u) {
+      plain = plain && ((reinterpret_cast<uintptr_t>(out[k]) & 3u) == 0) && (k == 0 || L.mode[k] == 0 || L.qm == 1);
+    }
+  }
+  if (plain) {
+    const uint32_t  W   = B / 4u;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(codeword + pos);
+    uint32_t        xw[8];
+#pragma unroll
+    for (uint32_t w = 0; w < 8; ++w) {
+      xw[w] = (w < W) ? src[w] : 0u;
+    }
+#pragma unroll
+    for (int k = 1; k < 4; ++k) { // UCI streams first, then SCH: the order of demux_current_ofdm_symbol
+      if ((f >> k) & 1u) {
+        uint32_t*  o      = reinterpret_cast<uint32_t*>(out[k] + (size_t)rank[k] * B);
+        const bool zeroed = (k != 1) && punct;
+#pragma unroll
+        for (uint32_t w = 0; w < 8; ++w) {
+          if (w < W) {
+            o[w] = zeroed ? 0u : xw[w];
+          }
+        }
+      }
+    }
+    if (f & FEC_ULSCH_F_SCH) {
+      uint32_t* o = reinterpret_cast<uint32_t*>(o_sch + (size_t)rank[0] * B);
+#pragma unroll
+      for (uint32_t w = 0; w < 8; ++w) {
+        if (w < W) {
+          o[w] = punct ? 0u : xw[w];
+        }
+      }
+    }
+    return;
+  }
+  int8_t x[32];
   for (uint32_t b = 0; b < B; ++b) {
     x[b] = codeword[pos + b];
   }
-  // UCI streams first (HARQ-ACK, CSI Part 1, CSI Part 2), then SCH: the order of demux_current_ofdm_symbol
 #pragma unroll
   for (int k = 1; k < 4; ++k) {
     if (!((f >> k) & 1u)) {
       continue;
     }
-    int8_t*        o       = out[k] + (size_t)rank[k] * B;
-    const bool     zeroed  = (k != 1) && L.harq_punctures && (f & FEC_ULSCH_F_HARQ);
-    const uint32_t mode    = L.mode[k];
+    int8_t*        o      = out[k] + (size_t)rank[k] * B;
+    const bool     zeroed = (k != 1) && punct;
+    const uint32_t mode   = L.mode[k];
     for (uint32_t b = 0; b < B; ++b) {
       int v = zeroed ? 0 : (int)x[b];
       if (mode != 0 && L.qm > 1 && !zeroed) {
@@ -309,10 +351,9 @@ fec_ulsch_demux_kernel(const fec_ulsch_seg* __restrict__ segs,
     }
   }
   if (f & FEC_ULSCH_F_SCH) {
-    int8_t*    o      = o_sch + (size_t)rank[0] * B;
-    const bool zeroed = L.harq_punctures && (f & FEC_ULSCH_F_HARQ);
+    int8_t* o = o_sch + (size_t)rank[0] * B;
     for (uint32_t b = 0; b < B; ++b) {
-      o[b] = zeroed ? (int8_t)0 : x[b];
+      o[b] = punct ? (int8_t)0 : x[b];
     }
   }
 }
