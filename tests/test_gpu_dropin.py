@@ -72,3 +72,19 @@ def test_demodulation_mapper_over_the_cuda_engine():
     assert r.returncode == 0, r.stdout + r.stderr
     print(r.stdout)
     assert "OK cases=120" in r.stdout, r.stdout
+
+
+ULSCH_BIN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "dropin_ulsch_demultiplex")
+
+
+def test_ulsch_demultiplex_cuda_is_a_drop_in():
+    """The reference's ulsch_demultiplex_impl and srsran::b200::cuda_ulsch_demultiplex behind the same interfaces on 150 random
+    configurations, CSI Part 2 announced at the start or from inside the CSI Part 1 buffer's on_end_softbits: every stream
+    and every end-of-stream notification identical."""
+    if not os.path.exists(ULSCH_BIN):
+        pytest.skip("tests/cpp/_build/dropin_ulsch_demultiplex not built (needs the reference headers)")
+    r = subprocess.run([ULSCH_BIN, "150"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    print(r.stdout)
+    assert "OK cases=150" in r.stdout, r.stdout
+    assert int(r.stdout.split("csi2_after_csi1=")[1]) >= 10, r.stdout
