@@ -520,29 +520,47 @@ __device__ __forceinline__ void fec_packed_iteration(uint32_t prog, // shared-wi
   const uint32_t tq = min(tid, H - 1);
   const uint32_t h4 = 4 * H;
   const uint32_t dab = tm_a - tm_b;
-  for (uint32_t l = 0; l < nlayers; ++l) {
-    // row program record: x = address of the row's edge records, y = where the state is (shared memory: shared-window address
-    // of thread 0's first word; tensor memory: column inside the region), z = instantiation, w = 1 for region A
-    const uint4    P  = lds_u128(prog + 16 * l);
-    const uint32_t ta = imad(P.w, dab, tm_b + P.y);
-    const uint32_t sa = imad(tq, 4u, P.y);
+  // Row program record: x = address of the row's edge records, y = where the state is (shared memory: shared-window address
+  // of thread 0's first word; tensor memory: column inside the region), z = instantiation, w = 1 for region A.
+  // Consecutive rows that run the same body (BG1: 4 x degree 19, 6 x degree 6, 9 x degree 5, ...) stay inside it: the next
+  // record is fetched in the body's own loop and the jump table is only consulted when the instantiation changes
+  // (+0.8 % forced, +1.7 % with early stop over one dispatch per row).
+#define FEC_ROW_CASE(code, D, TM)                                                                                              \
+  case code:                                                                                                                     \
+    do {                                                                                                                         \
+      fec_packed_row<D, TM>(imad(tq, 4u, P.y), h4, imad(P.w, dab, tm_b + P.y), P.x, tq, smul, sadd);                              \
+      if (++l >= nlayers) {                                                                                                      \
+        return;                                                                                                                  \
+      }                                                                                                                          \
+      P = lds_u128(prog + 16 * l);                                                                                               \
+    } while (P.z == code);                                                                                                       \
+    break;
+  uint32_t l = 0;
+  if (nlayers == 0) {
+    return;
+  }
+  uint4 P = lds_u128(prog);
+  for (;;) {
     __builtin_assume(P.z <= FEC_ROW_S19);
     switch (P.z) {
-      case FEC_ROW_T3: fec_packed_row<3, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_T4: fec_packed_row<4, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_T5: fec_packed_row<5, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_T6: fec_packed_row<6, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_T7: fec_packed_row<7, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_T8: fec_packed_row<8, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_T9: fec_packed_row<9, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_T10: fec_packed_row<10, true>(0u, 0u, ta, P.x, tq, smul, sadd); break;
-      case FEC_ROW_S3: fec_packed_row<3, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
-      case FEC_ROW_S8: fec_packed_row<8, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
-      case FEC_ROW_S9: fec_packed_row<9, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
-      case FEC_ROW_S10: fec_packed_row<10, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
-      default: fec_packed_row<19, false>(sa, h4, 0u, P.x, tq, smul, sadd); break;
+      FEC_ROW_CASE(FEC_ROW_T3, 3, true)
+      FEC_ROW_CASE(FEC_ROW_T4, 4, true)
+      FEC_ROW_CASE(FEC_ROW_T5, 5, true)
+      FEC_ROW_CASE(FEC_ROW_T6, 6, true)
+      FEC_ROW_CASE(FEC_ROW_T7, 7, true)
+      FEC_ROW_CASE(FEC_ROW_T8, 8, true)
+      FEC_ROW_CASE(FEC_ROW_T9, 9, true)
+      FEC_ROW_CASE(FEC_ROW_T10, 10, true)
+      FEC_ROW_CASE(FEC_ROW_S3, 3, false)
+      FEC_ROW_CASE(FEC_ROW_S8, 8, false)
+      FEC_ROW_CASE(FEC_ROW_S9, 9, false)
+      FEC_ROW_CASE(FEC_ROW_S10, 10, false)
+      FEC_ROW_CASE(FEC_ROW_S19, 19, false)
+      default:
+        return;
     }
   }
+#undef FEC_ROW_CASE
 }
 
 // Index, in 16-bit units, of variable j (0 <= j < Z) of column col in the pair-word soft layout.
