@@ -15,11 +15,12 @@ import cases
 pytestmark = pytest.mark.gpu
 
 
-def _run(fec, eng, items):
-    """One fec_run_host call over `items` (dict(p, llr, slot)); new data everywhere. Returns (res, out bytes list)."""
+def _run(fec, eng, items, align=16):
+    """One fec_run_host call over `items` (dict(p, llr, slot)); new data everywhere. Returns (res, out bytes list). The soft
+    bits of each codeblock start at a multiple of `align` bytes (1: back to back, any alignment)."""
     n = len(items)
     d = fec.make_descs(n)
-    offs = np.cumsum([0] + [((it["llr"].size + 15) // 16) * 16 for it in items])
+    offs = np.cumsum([0] + [((it["llr"].size + align - 1) // align) * align for it in items])
     llr = np.zeros(int(offs[-1]) + 16, np.int8)
     nbytes = [(cases.dims(it["p"]["bg"], it["p"]["Z"])[0] + 7) // 8 for it in items]
     out_off = np.cumsum([0] + nbytes)
@@ -33,8 +34,8 @@ def _run(fec, eng, items):
     return res, [out[out_off[i]:out_off[i + 1]] for i in range(n)]
 
 
-def _check(fec, eng, oracle, items, tag):
-    res, outs = _run(fec, eng, items)
+def _check(fec, eng, oracle, items, tag, align=16):
+    res, outs = _run(fec, eng, items, align)
     n_pass = n_fail = 0
     its = []
     for i, it in enumerate(items):
@@ -161,3 +162,49 @@ def test_scaling_factor_changes_the_result(fec, oracle, orc):
         b = oracle.decode(bg, Z, llr, 0, orc.CRC24B, 10, scaling=0.8)
         differ += (a[0] != b[0]) or not (a[1] == b[1]).all()
     assert differ > 0
+
+
+def test_dematcher_paths_first_transmissions(fec, engine, oracle, orc):
+    """The round-2 dematcher paths, 640 random first transmissions from the start of the buffer (rv 0) at the lifting sizes that
+    take them (Z a multiple of 8): the direct path with and without fillers that are a multiple of four, E below / at / above
+    the systematic part, limited buffers (Nref), BPSK (no transposed staging), and repetition (E > Ncb - fillers: the
+    word-wise wrap path), inputs aligned to 16 bytes and packed back to back (any alignment), in four launches and against the
+    oracle: bytes, iterations, CRC flags, soft buffers."""
+    rng = np.random.default_rng(808)
+    zs = [8, 16, 24, 32, 40, 48, 56, 64, 80, 96, 128, 192, 256, 384]
+    items = []
+    for i in range(640):
+        bg = int(rng.integers(1, 3))
+        Z = int(zs[i % len(zs)]) if i % 5 else 384
+        K, N = cases.dims(bg, Z)
+        Kb = 22 if bg == 1 else 10
+        poly = int(rng.choice([0, 1, 2]))
+        max_fill = min((Kb - 2) * Z - 1, 2 * Z, K - cases.ORC_CRC_LEN[poly] - 1)
+        fill = int(rng.integers(0, max_fill + 1)) if i % 3 else 0
+        qm = int(rng.choice([1, 2, 4, 6, 8]))
+        Nref = 0 if rng.random() < 0.6 else int(rng.integers(K + 2 * Z + 1, N + 10))
+        Ncb = min(Nref, N) if Nref else N
+        kind = i % 4
+        if kind == 0:    # high rate: ends inside or just behind the systematic part
+            E = int(rng.integers(K - fill - 3 * Z, K - fill + 4 * Z))
+        elif kind == 1:  # ordinary
+            E = int(rng.integers(K - fill + 2 * Z, Ncb - fill))
+        elif kind == 2:  # around the end of the buffer
+            E = int(rng.integers(Ncb - fill - 40, Ncb - fill + 40))
+        else:            # repetition: one to three passes
+            E = int(rng.integers(Ncb - fill + 1, 3 * (Ncb - fill)))
+        E = max(qm, E // qm * qm)
+        if E > 50000:
+            E = 50000 // qm * qm
+        p = dict(bg=bg, Z=Z, E=E, rv=0, qm=qm, Nref=Nref, fill=fill, poly=poly, max_iter=int(rng.choice([2, 6])),
+                 early=bool(i % 2))
+        rate = (K - fill) / E
+        snr = 10 * np.log10(max(2 ** (2 * min(rate, 1.2)) - 1, 1e-3)) + float(rng.uniform(0.0, 7.0))
+        llr, _ = oracle.make_case(bg, Z, E, 0, qm, Nref, fill, poly, snr, seed=700000 + i)
+        items.append(dict(p=p, llr=llr, slot=i))
+    n_pass = n_fail = 0
+    for c0 in range(0, len(items), 160):
+        a, b, _ = _check(fec, engine, oracle, items[c0:c0 + 160], ("dematch", c0), align=16 if c0 < 320 else 1)
+        n_pass += a
+        n_fail += b
+    assert n_pass >= 200 and n_fail >= 60, (n_pass, n_fail)
