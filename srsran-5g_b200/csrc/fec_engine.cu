@@ -881,9 +881,16 @@ int fec_engine_create(const fec_engine_cfg* cfg, fec_engine** out)
   {
     fec_packed_tables* hp = new (std::nothrow) fec_packed_tables();
     e->packed_ok          = fec_packed_build_tables(*hp, *h, FEC_ALL_Z);
-    uint32_t rowinfo[2][48];
-    e->packed_ok = e->packed_ok && fec_packed_build_rowinfo(rowinfo, *h, *hp);
-    CU_TRY(cudaMemcpyToSymbol(fec_c_rowinfo, rowinfo, sizeof(rowinfo))); // constant memory of this device: the row schedule
+    // The row schedule lives in constant memory, i.e. it is shared by every engine of this process on this device. It is a
+    // function of the base graphs alone, so every engine writes the same words -- but only a schedule that was actually built
+    // may be written: an engine whose scaling factor the packed kernel cannot represent (packed_ok false above) used to skip
+    // the builder and then upload the uninitialised array, which broke the packed launches of the engines created before it.
+    uint32_t   rowinfo[2][48] = {};
+    const bool rows_ok        = fec_packed_build_rowinfo(rowinfo, *h, *hp);
+    e->packed_ok              = e->packed_ok && rows_ok;
+    if (rows_ok) {
+      CU_TRY(cudaMemcpyToSymbol(fec_c_rowinfo, rowinfo, sizeof(rowinfo)));
+    }
     CU_TRY(cudaMalloc((void**)&e->d_ptab, sizeof(fec_packed_tables)));
     CU_TRY(cudaMalloc((void**)&e->d_work, FEC_WORK_SLOTS * 2 * sizeof(uint32_t)));
     CU_TRY(cudaMemset(e->d_work, 0, FEC_WORK_SLOTS * 2 * sizeof(uint32_t)));

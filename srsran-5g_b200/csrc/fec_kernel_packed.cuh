@@ -703,7 +703,7 @@ __device__ __forceinline__ bool fec_hard_bits_packed(const uint16_t* soft16, uin
 // CRC remainder == 0 test of the first T bits of bitsw (crc_calculator_generic_impl.cpp:111-133 computes the same
 // remainder bytewise). Byte i of the message contributes byte_i(x) * x^(8 (nb-1-i)) mod g; x8[j] = x^(8 j) mod g comes from
 // the engine's table in HBM (4 KB per polynomial, L1 / L2 resident; shared memory has no room for it beside the 16-bit
-// soft bits). Up to six independent 8-step multiply chains per thread, one barrier.
+// soft bits). Up to six bytes per thread, eight multiply-and-add steps each, one barrier.
 // (Round 1 kept this out of line because an inlined build decoded wrongly. That no longer reproduces: the suspect, a byte
 // load in inline asm without a "memory" clobber next to plain C++ shared-memory stores, is gone, every asm access here
 // clobbers memory, and the inlined build passes the whole parity suite. Inlined, the kernel is 2 % faster.)
@@ -721,12 +721,14 @@ __device__ __forceinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_
       a[k]             = v ? __ldg(x8 + (nb - 1 - i)) : 0u;
       w[k]             = v ? (bitsw[i >> 2] >> (24 - 8 * (i & 3))) : 0u;
     }
+    // bit s of the byte contributes x^s * a = a << s: one AND, one multiply by the isolated bit (a << s or 0; a < 2^24 and
+    // s <= 7, so no bit is lost) and one XOR per step. The products are NOT reduced mod g here: reduction is linear, so the
+    // seven bits above the remainder are folded back once, after the sums of all threads have been added up.
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
-        acc ^= ((w[k] >> s) & 1u) ? a[k] : 0u;
-        a[k] = fec_crc_shift1(a[k], poly, top);
+        acc ^= (w[k] & (1u << s)) * a[k];
       }
     }
   }
@@ -741,6 +743,10 @@ __device__ __forceinline__ bool fec_crc_ok_packed(const uint32_t* bitsw, uint32_
   uint32_t rem = 0;
   for (uint32_t i = 0; i < (blockDim.x >> 5); ++i) {
     rem ^= red[i];
+  }
+#pragma unroll
+  for (int b = 6; b >= 0; --b) { // degree < crc_len + 7 -> degree < crc_len
+    rem = (rem & (top << b)) ? (rem ^ (poly << b)) : rem;
   }
   if (r != 0) {
     // rem = (the nb full bytes) mod g; continue bitwise over the remaining bits.
@@ -1492,6 +1498,9 @@ __device__ __forceinline__ void fec_packed_cb(const fec_cb_desc& D,
       tmem_wait_st();
     }
   }
+  // (Fetching these three where they are used instead, so that nothing of the CRC lives through the row bodies, shrinks the
+  // stack frame from 56 to 40 bytes and was measured at -2.4 % for the headline, +1.4 % for the config-3 shape: ptxas
+  // allocates and schedules the row bodies differently with every change around them -- see DESIGN.md 3.3.)
   const uint32_t* x8       = tab->crc_x8[D.crc_type];
   const uint32_t  crc_poly = tab->crc_poly[D.crc_type], crc_top = 1u << tab->crc_len[D.crc_type];
   __syncthreads();
