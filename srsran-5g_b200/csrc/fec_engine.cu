@@ -1039,6 +1039,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   }
   static const bool trace = getenv("FEC_B200_TRACE") != nullptr; // host timestamps of the call's phases on stderr
   static std::vector<cudaEvent_t> trace_ev;                      // and, per chunk, when its kernel started and ended
+  static std::vector<cudaEvent_t> trace_cp;                      // and when its input copy was complete
   const auto        t_in  = std::chrono::steady_clock::now();
   uint32_t max_Z = 0;
   int      any1  = 0;
@@ -1074,7 +1075,9 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   // chunk overlaps the kernels of the previous one and the D2H copy of the one before (PCIe is full duplex).
   const uint32_t wave  = FEC_PACKED_CTAS_PER_SM * (uint32_t)e->sm_count;
   uint32_t       chunk = (n >= 2 * wave) ? wave : n; // measured on B200: 1 wave beats 2, 3, 4 and 6 (e2e 11.4 vs 10.8 Gbit/s at 3)
-  // (also measured: 1/2, 3/4, 5/4, 3/2 and 2 waves per chunk, and a finer-cut first wave: all 1-3 % slower end to end)
+  // (also measured: 1/2, 3/4, 5/4, 3/2 and 2 waves per chunk, and a finer-cut first wave: all 1-3 % slower end to end; the last
+  // wave cut 1/2, 1/4, 1/4 so that less work is left when the last input byte arrives: no change, 15.70 vs 15.71 Gbit/s -- the
+  // SMs still hold a chunk and a half of backlog at that moment, FEC_B200_TRACE shows it)
   // The first wave is cut finer (1/4, 1/4, 1/2 of a wave): the first kernel starts after a quarter of the first wave's copy
   // instead of all of it; from then on the copy engine stays ahead of the SMs.
   // FEC_B200_CHUNK_WAVES (measurements): waves per chunk after the first wave
@@ -1159,6 +1162,15 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
       CU_TRY(cudaMemcpyAsync(c.d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, in));
     }
+    if (trace && nchunks < 32) {
+      if (trace_cp.empty()) {
+        trace_cp.resize(32);
+        for (cudaEvent_t& ev : trace_cp) {
+          cudaEventCreate(&ev);
+        }
+      }
+      cudaEventRecord(trace_cp[nchunks], in); // this chunk's input has arrived
+    }
     if (in != st) {
       if (c.chunk_in.size() <= nchunks) {
         cudaEvent_t ev = nullptr;
@@ -1234,6 +1246,13 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
         cudaEventElapsedTime(&a, trace_ev[64], trace_ev[2 * c]);
         cudaEventElapsedTime(&b, trace_ev[64], trace_ev[2 * c + 1]);
         fprintf(stderr, " [%.0f, %.0f]", a * 1e3f, b * 1e3f);
+      }
+      fprintf(stderr, "\n");
+      fprintf(stderr, "fec_b200 trace: chunk inputs complete at:");
+      for (uint32_t c = 0; c < nchunks && c < 32 && !trace_cp.empty(); ++c) {
+        float a = 0;
+        cudaEventElapsedTime(&a, trace_ev[64], trace_cp[c]);
+        fprintf(stderr, " %.0f", a * 1e3f);
       }
       fprintf(stderr, "\n");
     }
