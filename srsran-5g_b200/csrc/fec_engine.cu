@@ -1071,7 +1071,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   host_ctx& c      = *lease.c;
   const auto t_prep = std::chrono::steady_clock::now();
   CU_TRY(cudaSetDevice(e->cfg.device));
-  // Large batches are cut into chunks of one kernel wave (2 CTAs per SM) that travel on three streams, so that the H2D copy of one
+  // Large batches are cut into chunks of one kernel wave (the resident CTAs of the packed kernel: 3 per SM) that travel on three streams, so that the H2D copy of one
   // chunk overlaps the kernels of the previous one and the D2H copy of the one before (PCIe is full duplex).
   const uint32_t wave  = FEC_PACKED_CTAS_PER_SM * (uint32_t)e->sm_count;
   uint32_t       chunk = (n >= 2 * wave) ? wave : n; // measured on B200: 1 wave beats 2, 3, 4 and 6 (e2e 11.4 vs 10.8 Gbit/s at 3)
