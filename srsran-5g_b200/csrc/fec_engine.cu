@@ -136,10 +136,16 @@ void build_tables(fec_dev_tables& t, float sf)
 //   FREE -> FILLING (enqueue) -> PENDING (handed to the batcher) -> INFLIGHT (copies and kernel issued) -> DONE (event seen).
 // The owner of the queue touches a batch under queue_t::mtx; the batcher (whichever thread holds fec_engine::disp_mtx) only
 // moves PENDING batches to INFLIGHT, publishing with a release store of `state`.
+struct dispatch_res;
 struct batch_slot {
   enum state_t { FREE, FILLING, PENDING, INFLIGHT, DONE };
   std::atomic<int> state{FREE};
   std::atomic<bool> failed{false}; // the dispatch that carried this batch failed: every operation reports a failed codeblock
+  // The results of a dispatch come back in one piece (dispatch_res::h_res); whoever needs this batch's part first -- its
+  // consumer, or the batcher when it is about to reuse the set -- copies it into h_res: 0 not yet, 1 being copied, 2 done.
+  std::atomic<int> harvest{2};
+  dispatch_res* disp   = nullptr; // the dispatch that carries this batch (valid while INFLIGHT and harvest != 2)
+  uint32_t      res_at = 0;       // first result of this batch in its array
   uint32_t      n        = 0;
   uint32_t      llr_used = 0;
   uint32_t      out_used = 0;
@@ -154,7 +160,6 @@ struct batch_slot {
   fec_cb_result* h_res   = nullptr; // pinned
   int8_t*       d_llr    = nullptr;
   uint8_t*      d_out    = nullptr;
-  cudaEvent_t   done     = nullptr;
   std::chrono::steady_clock::time_point t_pending;
 };
 
@@ -173,10 +178,13 @@ struct dispatch_res {
   fec_cb_desc*   h_descs = nullptr; // pinned
   fec_cb_desc*   d_descs = nullptr;
   fec_cb_result* d_res   = nullptr;
+  fec_cb_result* h_res   = nullptr; // pinned: the results of the launch, copied back in one piece
   cudaEvent_t    done    = nullptr; // the launch and every copy of the dispatch have finished: the set can be reused
   bool           used    = false;
+  std::vector<batch_slot*> batches; // what the last dispatch with this set carried
 };
-constexpr int DISPATCH_RING = 8;
+constexpr int DISPATCH_RING = 16;
+constexpr int DISPATCH_STREAMS = 8;
 
 // One host-call context: the stream set, device staging and pinned bounce buffers one fec_run_host / transport-block call
 // works in. An engine owns several, so that calls from different threads run concurrently (each on its own streams) instead
@@ -270,7 +278,7 @@ struct fec_engine {
   std::mutex               disp_mtx;
   dispatch_res             disp[DISPATCH_RING];
   uint32_t                 disp_next = 0;
-  cudaStream_t             disp_stream[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t             disp_stream[DISPATCH_STREAMS] = {}; // dispatches rotate over them: that many launches in flight
   uint32_t                 disp_cap = 0; // codeblocks one dispatch can carry
   // transport-block layer (allocated on first use)
   std::mutex            tb_alloc_mtx;
@@ -597,8 +605,22 @@ int slot_alloc(fec_engine* e, batch_slot& s)
   s.tags = new (std::nothrow) uint64_t[nc];
   CU_TRY(cudaMalloc((void**)&s.d_llr, nl));
   CU_TRY(cudaMalloc((void**)&s.d_out, (size_t)nc * FEC_MAX_CB_OUT_BYTES));
-  CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
   return FEC_OK;
+}
+
+// The batch's part of its dispatch's results, copied into the batch's own array exactly once (see batch_slot::harvest).
+// Only called when the dispatch is known to have finished.
+void harvest_batch(batch_slot& s)
+{
+  int expected = 0;
+  if (s.harvest.compare_exchange_strong(expected, 1, std::memory_order_acq_rel)) {
+    memcpy(s.h_res, s.disp->h_res + s.res_at, s.n * sizeof(fec_cb_result));
+    s.harvest.store(2, std::memory_order_release);
+    return;
+  }
+  while (s.harvest.load(std::memory_order_acquire) != 2) {
+    std::this_thread::yield();
+  }
 }
 
 void slot_free(batch_slot* s)
@@ -613,9 +635,6 @@ void slot_free(batch_slot* s)
   delete[] s->tags;
   cudaFree(s->d_llr);
   cudaFree(s->d_out);
-  if (s->done) {
-    cudaEventDestroy(s->done);
-  }
   delete s;
 }
 
@@ -637,6 +656,7 @@ int disp_resources(fec_engine* e)
     CU_TRY(cudaHostAlloc((void**)&r.h_descs, (size_t)cap * sizeof(fec_cb_desc), cudaHostAllocDefault));
     CU_TRY(cudaMalloc((void**)&r.d_descs, (size_t)cap * sizeof(fec_cb_desc)));
     CU_TRY(cudaMalloc((void**)&r.d_res, (size_t)cap * sizeof(fec_cb_result)));
+    CU_TRY(cudaHostAlloc((void**)&r.h_res, (size_t)cap * sizeof(fec_cb_result), cudaHostAllocDefault));
     CU_TRY(cudaEventCreateWithFlags(&r.done, cudaEventDisableTiming));
   }
   for (cudaStream_t& st : e->disp_stream) {
@@ -651,20 +671,45 @@ void dispatch_batches(fec_engine* e, batch_slot** b, size_t nb)
 {
   cudaSetDevice(e->cfg.device);
   dispatch_res& r = e->disp[e->disp_next % DISPATCH_RING];
-  cudaStream_t  st = e->disp_stream[e->disp_next % 3];
+  cudaStream_t  st = e->disp_stream[e->disp_next % DISPATCH_STREAMS];
   ++e->disp_next;
   bool ok = true;
   if (r.used) {
-    ok = cudaEventSynchronize(r.done) == cudaSuccess; // eight dispatches ago: normally long done
+    ok = cudaEventSynchronize(r.done) == cudaSuccess; // sixteen dispatches ago: normally long done
+    // Batches of that dispatch whose consumer has not looked yet still read their results from r.h_res: hand them over
+    // before the array is written again.
+    for (batch_slot* old : r.batches) {
+      if (old->disp == &r && old->harvest.load(std::memory_order_acquire) != 2) {
+        harvest_batch(*old);
+      }
+    }
   }
+  r.batches.assign(b, b + nb);
   uint32_t n = 0, max_Z = 0;
   int      any1 = 0;
+  // Zero copy: the staging buffers of a batch are pinned host memory, which the device addresses directly. The kernel then
+  // reads the soft bits over PCIe itself (each is read exactly once, with coalesced 16-byte loads) and writes the decoded
+  // bytes straight into the batch's host buffer: two copies per batch less for this thread to issue -- the dispatcher is
+  // serial, and with 16 consumer threads its CUDA calls (about 4 per batch, 3-4 us each) were what bounded the queue path.
+  // Not for operations the packed kernel reads byte by byte (inputs longer than its staging area) or leaves to the generic
+  // kernel. FEC_B200_QUEUE_ZEROCOPY=0 (measurements) keeps the copies.
+  static const bool zc_on = !(getenv("FEC_B200_QUEUE_ZEROCOPY") && atoi(getenv("FEC_B200_QUEUE_ZEROCOPY")) == 0);
+  bool              zc    = zc_on && e->packed_ok && e->cfg.kernel_variant != 1;
+  for (size_t k = 0; k < nb && zc; ++k) {
+    const batch_slot& s = *b[k];
+    zc                  = (s.any_bg1 & FEC_LF_SMALL_Z) == 0;
+    for (uint32_t i = 0; i < s.n && zc; ++i) {
+      const fec_cb_desc& d = s.h_descs[i];
+      zc = d.E <= ((d.base_graph == 1) ? 68u : 52u) * d.lifting_size * 2u;
+    }
+  }
   for (size_t k = 0; k < nb; ++k) {
     batch_slot& s = *b[k];
     for (uint32_t i = 0; i < s.n; ++i) {
       fec_cb_desc d = s.h_descs[i];
-      const uint64_t out = (uint64_t)(uintptr_t)s.d_out + d.out_offset;
-      d.llr_offset += (uint64_t)(uintptr_t)s.d_llr; // absolute device addresses: the launch passes null base pointers
+      const uint64_t out = (uint64_t)(uintptr_t)(zc ? s.h_out : s.d_out) + d.out_offset;
+      // absolute addresses: the launch passes null base pointers
+      d.llr_offset += (uint64_t)(uintptr_t)(zc ? s.h_llr : s.d_llr);
       d.out_offset = (uint32_t)out;
       d.reserved1  = (uint32_t)(out >> 32);
       r.h_descs[n + i] = d;
@@ -674,27 +719,38 @@ void dispatch_batches(fec_engine* e, batch_slot** b, size_t nb)
     any1 |= s.any_bg1;
   }
   ok = ok && cudaMemcpyAsync(r.d_descs, r.h_descs, (size_t)n * sizeof(fec_cb_desc), cudaMemcpyHostToDevice, st) == cudaSuccess;
-  for (size_t k = 0; k < nb && ok; ++k) {
+  for (size_t k = 0; k < nb && ok && !zc; ++k) {
     ok = cudaMemcpyAsync(b[k]->d_llr, b[k]->h_llr, b[k]->llr_used, cudaMemcpyHostToDevice, st) == cudaSuccess;
   }
   ok = ok && launch(e, st, r.d_descs, n, nullptr, nullptr, r.d_res, max_Z, any1) == FEC_OK;
   uint32_t at = 0;
   for (size_t k = 0; k < nb; ++k) {
     batch_slot& s = *b[k];
-    if (ok) {
-      ok = cudaMemcpyAsync(s.h_out, s.d_out, s.out_used, cudaMemcpyDeviceToHost, st) == cudaSuccess &&
-           cudaMemcpyAsync(s.h_res, r.d_res + at, s.n * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st) == cudaSuccess;
+    if (ok && !zc) {
+      ok = cudaMemcpyAsync(s.h_out, s.d_out, s.out_used, cudaMemcpyDeviceToHost, st) == cudaSuccess;
     }
+    s.disp   = &r;
+    s.res_at = at;
     at += s.n;
-    if (!ok) {
-      cudaGetLastError();
-      s.failed.store(true);
-    }
-    cudaEventRecord(s.done, st);
-    s.state.store(batch_slot::INFLIGHT, std::memory_order_release);
   }
+  // One copy for the results of every batch and one event for the whole dispatch (a copy and an event per batch were
+  // two more driver calls per batch on the batcher's serial path).
+  ok = ok && cudaMemcpyAsync(r.h_res, r.d_res, (size_t)n * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st) == cudaSuccess;
+  if (!ok) {
+    cudaGetLastError();
+  }
+  // The event is recorded BEFORE the batches are published: a consumer that sees INFLIGHT must never find the completed
+  // record of this set's previous dispatch.
   cudaEventRecord(r.done, st);
   r.used = true;
+  for (size_t k = 0; k < nb; ++k) {
+    batch_slot& s = *b[k];
+    if (!ok) {
+      s.failed.store(true);
+    }
+    s.harvest.store(0, std::memory_order_release);
+    s.state.store(batch_slot::INFLIGHT, std::memory_order_release);
+  }
   if (!ok) {
     e->st_faults.fetch_add(1, std::memory_order_relaxed);
   }
@@ -955,6 +1011,7 @@ void fec_engine_destroy(fec_engine* e)
     cudaFreeHost(r.h_descs);
     cudaFree(r.d_descs);
     cudaFree(r.d_res);
+    cudaFreeHost(r.h_res);
     if (r.done) {
       cudaEventDestroy(r.done);
     }
@@ -1383,8 +1440,11 @@ int fec_queue_free(fec_engine* e, uint32_t queue_id)
       dispatch_try(e);
       std::this_thread::yield();
     }
-    if (s->state.load(std::memory_order_acquire) == batch_slot::INFLIGHT) {
-      cudaEventSynchronize(s->done);
+    if (s->state.load(std::memory_order_acquire) == batch_slot::INFLIGHT && s->harvest.load(std::memory_order_acquire) != 2) {
+      cudaEventSynchronize(s->disp->done); // (a later record of the same event only waits longer)
+      if (!s->failed.load()) {
+        harvest_batch(*s);
+      }
     }
     s->state.store(batch_slot::FREE);
     s->n = s->llr_used = s->out_used = s->polled = 0;
@@ -1573,9 +1633,17 @@ int fec_queue_poll(fec_engine* e, uint32_t queue_id, uint64_t* tags, fec_cb_resu
       break; // not dispatched yet
     }
     if (s.state.load(std::memory_order_acquire) == batch_slot::INFLIGHT) {
-      cudaError_t st = cudaEventQuery(s.done);
-      if (st == cudaErrorNotReady) {
-        break;
+      cudaError_t st = cudaSuccess;
+      if (s.harvest.load(std::memory_order_acquire) != 2) {
+        // (If the batcher reuses the set meanwhile it hands the results over first and only then records the event again:
+        // "not ready" from the newer record just means one more look, at which harvest reads 2.)
+        st = cudaEventQuery(s.disp->done);
+        if (st == cudaErrorNotReady) {
+          break;
+        }
+        if (st == cudaSuccess && !s.failed.load()) {
+          harvest_batch(s);
+        }
       }
       if (st != cudaSuccess || s.failed.load()) {
         // A device fault must surface as failed codeblocks, never as a hang (the consumer's poll loop has no timeout).
