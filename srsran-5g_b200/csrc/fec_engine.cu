@@ -251,6 +251,7 @@ struct fec_engine {
   uint32_t*             d_work       = nullptr; // FEC_WORK_SLOTS x {next, done} counters of the persistent kernel
   std::atomic<uint32_t> work_slot{0};
   bool                  packed_ok    = false;
+  std::atomic<int>      ctx_busy{0}; // host-call contexts in use (a call that is alone on the engine may read its input in place)
   int8_t*               d_harq       = nullptr;
   std::atomic<uint64_t> launches{0};
   std::atomic<uint8_t>* fresh = nullptr; // per HARQ slot: freed, reads as zeros until the next operation rewrites it
@@ -536,6 +537,7 @@ host_ctx* ctx_acquire(fec_engine* e, int index, bool block)
     if (index >= 0) {
       if (!e->ctxs[index]->busy) {
         e->ctxs[index]->busy = true;
+        e->ctx_busy.fetch_add(1, std::memory_order_relaxed);
         return e->ctxs[index];
       }
     } else {
@@ -543,6 +545,7 @@ host_ctx* ctx_acquire(fec_engine* e, int index, bool block)
       for (size_t i = e->ctxs.size(); i-- > 0;) {
         if (!e->ctxs[i]->busy) {
           e->ctxs[i]->busy = true;
+          e->ctx_busy.fetch_add(1, std::memory_order_relaxed);
           return e->ctxs[i];
         }
       }
@@ -559,6 +562,7 @@ void ctx_release(fec_engine* e, host_ctx* c)
   {
     std::lock_guard<std::mutex> lk(e->ctx_mtx);
     c->busy = false;
+    e->ctx_busy.fetch_sub(1, std::memory_order_relaxed);
   }
   e->ctx_cv.notify_all();
 }
@@ -638,6 +642,30 @@ void slot_free(batch_slot* s)
   delete s;
 }
 
+// Device-side address of host memory the device can address directly (cudaHostAlloc / fec_host_alloc / cudaHostRegister),
+// nullptr for pageable memory. Small calls let the kernel read its soft bits -- and write its bytes -- there instead of
+// copying first: the transfer then overlaps the decoding codeblock by codeblock inside one launch (one config-3 transport
+// block: 61 us instead of 78 us of device time). FEC_B200_HOST_ZEROCOPY=0 (measurements) keeps the copies.
+const void* pinned_device_ptr(const void* h)
+{
+  static const bool on = !(getenv("FEC_B200_HOST_ZEROCOPY") && atoi(getenv("FEC_B200_HOST_ZEROCOPY")) == 0);
+  if (!on || h == nullptr) {
+    return nullptr;
+  }
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, h) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return (a.type == cudaMemoryTypeHost) ? a.devicePointer : nullptr;
+}
+
+// True when the packed kernel reads the input of this operation exactly once, through its staging area.
+inline bool reads_input_once(const fec_cb_desc& d)
+{
+  return fec_packed_covers(d.lifting_size) && d.E <= ((d.base_graph == 1) ? 68u : 52u) * d.lifting_size * 2u;
+}
+
 // ---- cross-queue batcher ---------------------------------------------------------------------------------------------------
 // Queues hand their full (or flushed) batches over; whichever thread gets disp_mtx dispatches EVERYTHING that is pending, of
 // every queue, as one launch: one combined descriptor array (buffer positions as absolute device addresses: the kernel is given
@@ -699,8 +727,7 @@ void dispatch_batches(fec_engine* e, batch_slot** b, size_t nb)
     const batch_slot& s = *b[k];
     zc                  = (s.any_bg1 & FEC_LF_SMALL_Z) == 0;
     for (uint32_t i = 0; i < s.n && zc; ++i) {
-      const fec_cb_desc& d = s.h_descs[i];
-      zc = d.E <= ((d.base_graph == 1) ? 68u : 52u) * d.lifting_size * 2u;
+      zc = reads_input_once(s.h_descs[i]);
     }
   }
   for (size_t k = 0; k < nb; ++k) {
@@ -1100,6 +1127,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
   const auto        t_in  = std::chrono::steady_clock::now();
   uint32_t max_Z = 0;
   int      any1  = 0;
+  bool     once  = e->packed_ok && e->cfg.kernel_variant != 1; // every input is read once (zero copy is possible)
   for (uint32_t i = 0; i < n; ++i) {
     // A descriptor with the parameters of its predecessor (the usual case: the codeblocks of one transport block) inherits
     // its checked and derived fields instead of going through fec_desc_prepare again.
@@ -1123,6 +1151,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     }
     max_Z = d.lifting_size > max_Z ? d.lifting_size : max_Z;
     any1 |= launch_flags_of(d.base_graph, d.lifting_size);
+    once = once && reads_input_once(d);
   }
   ctx_lease lease(e, -1);
   host_ctx& c      = *lease.c;
@@ -1214,8 +1243,18 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
       c1 |= launch_flags_of(d.base_graph, d.lifting_size);
       keep |= (d.flags & FEC_FLAG_EARLY_STOP) != 0;
     }
-    CU_TRY(cudaMemcpyAsync(c.d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, in));
-    if (out_bytes && o1 > o0 && keep) {
+    // A call that is not chunked (less than two kernel waves) reads pinned inputs and writes pinned outputs in place.
+    // Only when no other host call is in flight: measured with several calls at once, kernels that wait for PCIe reads hold
+    // the SMs' codeblock slots and the copy engine's pipeline is the faster one (4 asynchronous callers: 32 -> 11 Gbit/s).
+    const bool    alone  = e->ctx_busy.load(std::memory_order_relaxed) <= 1;
+    const int8_t* zc_llr = (chunk == n && once && alone) ? static_cast<const int8_t*>(pinned_device_ptr(h_llr)) : nullptr;
+    uint8_t*      zc_out = (chunk == n && once && alone && out_bytes)
+                               ? static_cast<uint8_t*>(const_cast<void*>(pinned_device_ptr(h_out)))
+                               : nullptr;
+    if (!zc_llr) {
+      CU_TRY(cudaMemcpyAsync(c.d_llr + l0, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, in));
+    }
+    if (!zc_out && out_bytes && o1 > o0 && keep) {
       // Early-stop operations that bail out leave their output untouched: start from the caller's bytes.
       CU_TRY(cudaMemcpyAsync(c.d_out + o0, h_out + o0, o1 - o0, cudaMemcpyHostToDevice, in));
     }
@@ -1251,14 +1290,15 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     }
     // FEC_B200_CHUNK_GRID_DIV (measurements): chunk kernels on fewer CTAs so that consecutive chunks interleave on the SMs
     static const uint32_t chunk_grid_div = getenv("FEC_B200_CHUNK_GRID_DIV") ? (uint32_t)atoi(getenv("FEC_B200_CHUNK_GRID_DIV")) : 1u;
-    int r = launch(e, st, c.d_descs + c0, cn, c.d_llr, c.d_out, c.d_res + c0, cz, c1, (chunk != n) ? chunk_grid_div : 1u);
+    int r = launch(e, st, c.d_descs + c0, cn, zc_llr ? zc_llr : c.d_llr, zc_out ? zc_out : c.d_out, c.d_res + c0, cz, c1,
+                   (chunk != n) ? chunk_grid_div : 1u);
     if (r != FEC_OK) {
       return r;
     }
     if (trace && nchunks < 32) {
       cudaEventRecord(trace_ev[2 * nchunks + 1], st);
     }
-    if (out_bytes && o1 > o0) {
+    if (!zc_out && out_bytes && o1 > o0) {
       CU_TRY(cudaMemcpyAsync(h_out + o0, c.d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, st));
     }
     CU_TRY(cudaMemcpyAsync(c.h_res_pin + c0, c.d_res + c0, cn * sizeof(fec_cb_result), cudaMemcpyDeviceToHost, st));
@@ -1860,6 +1900,7 @@ int tb_submit(fec_engine* e, host_ctx& hx, const fec_tb_desc* tbs, uint32_t n, c
   uint32_t n_map = 0, max_Z = 0;
   int      any1  = 0;
   bool     aligned = true; // every payload is whole bytes: the one-CTA-per-codeblock gather applies
+  bool     once    = e->packed_ok && e->cfg.kernel_variant != 1; // every input is read exactly once (zero copy is possible)
   for (uint32_t t = 0; t < n; ++t) {
     const fec_tb_desc& tb = tbs[t];
     fec_tb_geometry&   g  = hx.tb_geo[t];
@@ -1993,6 +2034,7 @@ int tb_submit(fec_engine* e, host_ctx& hx, const fec_tb_desc* tbs, uint32_t n, c
         return rc;
       }
       ref.result_index = already_ok ? -1 : (int32_t)m;
+      once             = once && reads_input_once(d);
       l0               = d.llr_offset < l0 ? (size_t)d.llr_offset : l0;
       l1               = d.llr_offset + d.E > l1 ? (size_t)(d.llr_offset + d.E) : l1;
       cw_off += d.E;
@@ -2071,15 +2113,23 @@ int tb_submit(fec_engine* e, host_ctx& hx, const fec_tb_desc* tbs, uint32_t n, c
       CU_TRY(cudaEventRecord(hx.chunk_out[c], ps));
     }
   } else {
+    const int8_t* zc_llr = nullptr;
     if (dm) {
       rc = demod_stage(e, st, *dm, l0, l1, hx.d_llr);
       if (rc != FEC_OK) {
         return rc;
       }
     } else {
-      CU_TRY(cudaMemcpyAsync(hx.d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+      // pinned input: the kernel reads it in place (the transfer overlaps the decoding inside the one launch)
+      // (only for a call that is alone on the engine, see fec_run_host)
+      zc_llr = (once && e->ctx_busy.load(std::memory_order_relaxed) <= 1)
+                   ? static_cast<const int8_t*>(pinned_device_ptr(h_llr + l0))
+                   : nullptr;
+      if (!zc_llr) {
+        CU_TRY(cudaMemcpyAsync(hx.d_llr, h_llr + l0, l1 - l0, cudaMemcpyHostToDevice, st));
+      }
     }
-    rc = launch(e, st, d_descs, n_map, hx.d_llr, e->d_msg, d_cbres, max_Z, any1);
+    rc = launch(e, st, d_descs, n_map, zc_llr ? zc_llr : hx.d_llr, e->d_msg, d_cbres, max_Z, any1);
     if (rc != FEC_OK) {
       return rc;
     }
