@@ -660,10 +660,12 @@ const void* pinned_device_ptr(const void* h)
   return (a.type == cudaMemoryTypeHost) ? a.devicePointer : nullptr;
 }
 
-// True when the packed kernel reads the input of this operation exactly once, through its staging area.
+// True when the packed kernel reads the input of this operation exactly once, with the 16-byte loads of the dematcher's
+// staging loop (the decoder-only mode reads its input byte by byte: fine from HBM, wasteful over PCIe).
 inline bool reads_input_once(const fec_cb_desc& d)
 {
-  return fec_packed_covers(d.lifting_size) && d.E <= ((d.base_graph == 1) ? 68u : 52u) * d.lifting_size * 2u;
+  return d.mode != FEC_MODE_DECODE && fec_packed_covers(d.lifting_size) &&
+         d.E <= ((d.base_graph == 1) ? 68u : 52u) * d.lifting_size * 2u;
 }
 
 // ---- cross-queue batcher ---------------------------------------------------------------------------------------------------
@@ -1248,6 +1250,7 @@ int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* 
     // the SMs' codeblock slots and the copy engine's pipeline is the faster one (4 asynchronous callers: 32 -> 11 Gbit/s).
     const bool    alone  = e->ctx_busy.load(std::memory_order_relaxed) <= 1;
     const int8_t* zc_llr = (chunk == n && once && alone) ? static_cast<const int8_t*>(pinned_device_ptr(h_llr)) : nullptr;
+    // (chunked calls with their outputs written in place as well: measured, no change -- 15.65 vs 15.65 Gbit/s)
     uint8_t*      zc_out = (chunk == n && once && alone && out_bytes)
                                ? static_cast<uint8_t*>(const_cast<void*>(pinned_device_ptr(h_out)))
                                : nullptr;
