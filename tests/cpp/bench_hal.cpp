@@ -80,7 +80,7 @@ struct result_t {
 } // namespace
 
 // One mode at one thread count. Returns false if a decoder failed.
-static bool run_mode(const std::string& mode, unsigned T, double seconds, double esn0_db, unsigned max_wait_us)
+static bool run_mode(const std::string& mode, unsigned T, double seconds, double esn0_db, unsigned max_wait_us, unsigned batch_cbs)
 {
   const unsigned inst_per_thread = (mode == "tb_async") ? 2 : 1;
   const unsigned n_inst          = T * inst_per_thread;
@@ -90,7 +90,7 @@ static bool run_mode(const std::string& mode, unsigned T, double seconds, double
   ecfg.max_batch_cbs   = 162;
   ecfg.max_batch_llrs  = G + 4096;
   ecfg.nof_queues      = T;
-  ecfg.queue_batch_cbs = 38; // a quarter of the block: the GPU starts while the consumer is still enqueuing
+  ecfg.queue_batch_cbs = batch_cbs; // default 38, a quarter of the block: the GPU starts while the consumer is still enqueuing
   ecfg.queue_batches   = 6;
   ecfg.max_wait_us     = max_wait_us;
   ecfg.host_contexts   = std::min(16u, std::max(2u, n_inst));
@@ -230,12 +230,13 @@ static bool run_mode(const std::string& mode, unsigned T, double seconds, double
 
 int main(int argc, char** argv)
 {
-  // usage: bench_hal [seconds per point] [comma-separated thread counts] [modes] [Es/N0 dB] [max_wait_us]
+  // usage: bench_hal [seconds per point] [comma-separated thread counts] [modes] [Es/N0 dB] [max_wait_us] [queue_batch_cbs]
   const double      seconds = (argc > 1) ? std::atof(argv[1]) : 2.0;
   const std::string tlist   = (argc > 2) ? argv[2] : "1,4,16,32";
   const std::string mlist   = (argc > 3) ? argv[3] : "hal,tb,tb_async";
   const double      esn0    = (argc > 4) ? std::atof(argv[4]) : 10.0;
   const unsigned    wait_us = (argc > 5) ? std::atoi(argv[5]) : 0;
+  const unsigned    batch   = (argc > 6) ? std::atoi(argv[6]) : 38;
   auto split = [](const std::string& s) {
     std::vector<std::string> out;
     size_t                   a = 0;
@@ -252,7 +253,7 @@ int main(int argc, char** argv)
   bool ok = true;
   for (const std::string& m : split(mlist)) {
     for (const std::string& t : split(tlist)) {
-      ok = run_mode(m, (unsigned)std::atoi(t.c_str()), seconds, esn0, wait_us) && ok;
+      ok = run_mode(m, (unsigned)std::atoi(t.c_str()), seconds, esn0, wait_us, batch) && ok;
     }
   }
   return ok ? 0 : 1;
