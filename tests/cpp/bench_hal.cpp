@@ -84,6 +84,7 @@ static bool run_mode(const std::string& mode, unsigned T, double seconds, double
 {
   const unsigned inst_per_thread = (mode == "tb_async") ? 2 : 1;
   const unsigned n_inst          = T * inst_per_thread;
+  static const unsigned hctx_cap = getenv("BENCH_HAL_CONTEXTS") ? (unsigned)std::atoi(getenv("BENCH_HAL_CONTEXTS")) : 16u;
   fec_engine_cfg ecfg;
   fec_engine_default_cfg(&ecfg);
   ecfg.harq_slots      = n_inst * 2 * 162 + 162;
@@ -93,7 +94,7 @@ static bool run_mode(const std::string& mode, unsigned T, double seconds, double
   ecfg.queue_batch_cbs = batch_cbs; // default 38, a quarter of the block: the GPU starts while the consumer is still enqueuing
   ecfg.queue_batches   = 6;
   ecfg.max_wait_us     = max_wait_us;
-  ecfg.host_contexts   = std::min(16u, std::max(2u, n_inst));
+  ecfg.host_contexts   = std::min(hctx_cap, std::max(2u, n_inst + 2));
   auto engine          = std::make_shared<b200::fec_engine_handle>(ecfg);
   b200::cuda_pusch_dec_factory factory_shared(engine);
 
