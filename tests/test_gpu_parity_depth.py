@@ -208,3 +208,59 @@ def test_dematcher_paths_first_transmissions(fec, engine, oracle, orc):
         n_pass += a
         n_fail += b
     assert n_pass >= 200 and n_fail >= 60, (n_pass, n_fail)
+
+
+def test_pinned_buffers_are_read_in_place_and_give_the_same_answer(fec, oracle, orc):
+    """fec_run_host / fec_tb_run_host on pinned host buffers (small call, alone on the engine: the kernel reads the soft bits
+    and writes the bytes in the caller's memory, no copies) against the same calls on pageable numpy buffers (copied): same
+    results, same bytes (blocks that never pass included), same soft buffers."""
+    import ctypes as C
+    import torch
+    eng = fec.FecEngine(device=0, harq_slots=512, max_batch_cbs=512)
+    try:
+        rng = np.random.default_rng(4242)
+        items = []
+        for i in range(96):
+            bg = int(rng.integers(1, 3))
+            Z = int(rng.choice([32, 96, 208, 384, 384]))
+            K, N = cases.dims(bg, Z)
+            qm = int(rng.choice([2, 4, 6, 8]))
+            E = int(rng.integers(K, N)) // qm * qm
+            p = dict(bg=bg, Z=Z, E=E, rv=0, qm=qm, Nref=0, fill=0, poly=orc.CRC24B, max_iter=6, early=True)
+            snr = 10 * np.log10(2 ** (2 * K / E) - 1) + float(rng.uniform(-3.0, 3.0))
+            llr, _ = oracle.make_case(bg, Z, E, 0, qm, 0, 0, orc.CRC24B, snr, seed=99000 + i)
+            items.append(dict(p=p, llr=llr))
+        n = len(items)
+        d = fec.make_descs(n)
+        offs = np.cumsum([0] + [it["llr"].size for it in items])  # back to back: any alignment
+        nbytes = [(cases.dims(it["p"]["bg"], it["p"]["Z"])[0] + 7) // 8 for it in items]
+        out_off = np.cumsum([0] + nbytes)
+        llr = np.zeros(int(offs[-1]) + 16, np.int8)
+        for i, it in enumerate(items):
+            cases.fill_chain_desc(fec, d, i, it["p"], True, i, int(offs[i]), int(out_off[i]))
+            llr[offs[i]:offs[i] + it["llr"].size] = it["llr"]
+        # pageable buffers: the copy path
+        for i in range(n):
+            eng.harq_free(i)
+        out_a = np.full(int(out_off[-1]), 0x5A, np.uint8)
+        res_a = eng.run_host(d.copy(), llr, out_a)
+        soft_a = [eng.harq_read(i, cases.dims(items[i]["p"]["bg"], items[i]["p"]["Z"])[1]).copy() for i in range(n)]
+        # pinned buffers: read and written in place
+        for i in range(n):
+            eng.harq_free(i)
+        t_llr = torch.from_numpy(llr.copy()).pin_memory()
+        t_out = torch.full((int(out_off[-1]),), 0x5A, dtype=torch.uint8).pin_memory()
+        res_b = np.zeros(n, fec.RESULT_DTYPE)
+        db = d.copy()
+        rc = eng.lib.fec_run_host(eng.h, db.ctypes.data, n, C.c_void_p(t_llr.data_ptr()), t_llr.numel(),
+                                  C.c_void_p(t_out.data_ptr()), t_out.numel(), res_b.ctypes.data, None)
+        assert rc == 0
+        assert (res_a["status"] == res_b["status"]).all() and (res_a["nof_ldpc_iterations"] == res_b["nof_ldpc_iterations"]).all()
+        assert (t_out.numpy() == out_a).all()
+        for i in range(n):
+            N = cases.dims(items[i]["p"]["bg"], items[i]["p"]["Z"])[1]
+            assert (eng.harq_read(i, N) == soft_a[i]).all(), i
+        ok = (res_a["status"] & fec.RES_CRC_PASS) != 0
+        assert 10 <= ok.sum() <= n - 5, ok.sum()
+    finally:
+        eng.close()
