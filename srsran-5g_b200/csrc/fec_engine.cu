@@ -1691,12 +1691,20 @@ int fec_queue_poll(fec_engine* e, uint32_t queue_id, uint64_t* tags, fec_cb_resu
       if (st != cudaSuccess || s.failed.load()) {
         // A device fault must surface as failed codeblocks, never as a hang (the consumer's poll loop has no timeout).
         cudaGetLastError();
+        // (the batcher must not hand this batch "results" of the failed dispatch later: take the hand-over ourselves)
+        int expected = 0;
+        if (!s.harvest.compare_exchange_strong(expected, 1, std::memory_order_acq_rel)) {
+          while (s.harvest.load(std::memory_order_acquire) != 2) {
+            std::this_thread::yield();
+          }
+        }
         for (uint32_t i = 0; i < s.n; ++i) {
           s.h_res[i].status              = FEC_RES_DONE;
           s.h_res[i].nof_ldpc_iterations = s.h_descs[i].max_iter;
           s.h_res[i].nof_layers          = 0;
           s.h_res[i].reserved            = 0;
         }
+        s.harvest.store(2, std::memory_order_release);
       }
       s.state.store(batch_slot::DONE);
     }
