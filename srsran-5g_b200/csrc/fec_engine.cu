@@ -133,7 +133,7 @@ void build_tables(fec_dev_tables& t, float sf)
 }
 
 // One batch of a queue: pinned host staging, its own slice of device memory, and the state machine
-//   FREE -> FILLING (enqueue) -> PENDING (handed to the batcher) -> INFLIGHT (copies and kernel issued) -> DONE (event seen).
+//   FREE -> FILLING (enqueue) -> PENDING (handed to the batcher) -> INFLIGHT (kernel issued) -> DONE (the dispatch's event seen).
 // The owner of the queue touches a batch under queue_t::mtx; the batcher (whichever thread holds fec_engine::disp_mtx) only
 // moves PENDING batches to INFLIGHT, publishing with a release store of `state`.
 struct dispatch_res;
@@ -671,8 +671,9 @@ inline bool reads_input_once(const fec_cb_desc& d)
 // ---- cross-queue batcher ---------------------------------------------------------------------------------------------------
 // Queues hand their full (or flushed) batches over; whichever thread gets disp_mtx dispatches EVERYTHING that is pending, of
 // every queue, as one launch: one combined descriptor array (buffer positions as absolute device addresses: the kernel is given
-// null base pointers), one kernel over all the codeblocks, the copies of each batch in front of and behind it, one event per
-// batch. A thread that finds the lock taken leaves its batch to the holder and returns at once; progress is guaranteed
+// null base pointers), one kernel over all the codeblocks -- which reads the batches' pinned staging buffers and writes their
+// output buffers in place where it can, and is framed by the batches' copies where it cannot --, one copy for all the results
+// and one event. A thread that finds the lock taken leaves its batch to the holder and returns at once; progress is guaranteed
 // because every poll tries again. With max_wait_us > 0 a dispatch that holds less than one kernel wave waits that long
 // (since its oldest batch was handed over) for other queues to join: fewer, fuller launches under load, bounded added latency.
 int disp_resources(fec_engine* e)
