@@ -183,8 +183,10 @@ int fec_launch_device(fec_engine* e, const fec_cb_desc* d_descs, uint32_t n, con
 
 /* ---- host-buffer batch: H2D + kernels + D2H, synchronous (bench.py "e2e", unit-test surface) ----------------------- */
 /* h_descs need not be prepared. llr_bytes / out_bytes are the sizes of the two host buffers. h_soft_out, if not NULL,
- * receives the n soft buffers (n * FEC_HARQ_SLOT_BYTES) after the operation. Pinned buffers (fec_host_alloc) make the
- * copies asynchronous DMA. */
+ * receives the n soft buffers (n * FEC_HARQ_SLOT_BYTES) after the operation. Pinned buffers (fec_host_alloc, or memory the
+ * caller registered with cudaHostRegister) make the copies asynchronous DMA, and a small call (less than two kernel waves)
+ * that is alone on the engine is not copied at all: the kernel reads h_llr and writes h_out in place. Either way the
+ * buffers belong to the engine until the call returns. */
 int fec_run_host(fec_engine* e, fec_cb_desc* h_descs, uint32_t n, const int8_t* h_llr, size_t llr_bytes, uint8_t* h_out,
                  size_t out_bytes, fec_cb_result* h_results, int8_t* h_soft_out);
 
