@@ -292,8 +292,7 @@ int fec_tb_run_host(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uin
  * and slots are copied. Completion, either way:
  *   callback == NULL: the caller collects with fec_tb_poll (1 = done and results written, 0 = still running, < 0 = error;
  *                     non-blocking) or fec_tb_wait (blocking); both take the ticket exactly once;
- *   callback != NULL: one of the engine's completion threads (three; calls are taken in submission order, callbacks of
- *                     different calls may run at the same time) waits for the GPU, hands the blocks over and calls
+ *   callback != NULL: an engine thread waits for the GPU, hands the blocks over and calls
  *                     callback(user, ticket, status, results, n) -- status FEC_OK or the error; on a device fault the
  *                     results say "nothing delivered" for the blocks that were lost. */
 typedef void (*fec_tb_callback)(void* user, uint64_t ticket, int status, const fec_tb_result* results, uint32_t n);

@@ -305,7 +305,7 @@ struct fec_engine {
   std::atomic<uint64_t> st_iter_hist[FEC_STATS_ITER_BINS];
   std::atomic<uint32_t> debug_fail_launches{0}; // fec_engine_debug_fail_launches: the next n codeblock launches fail
   // asynchronous transport-block interface: completion thread for calls that carry a callback
-  std::vector<std::thread> tb_threads; // completion threads of the asynchronous transport-block calls (FEC_TB_COMPLETION_THREADS)
+  std::thread             tb_thread;
   std::mutex              tb_mtx;
   std::condition_variable tb_cv;
   std::vector<host_ctx*>  tb_fifo; // contexts in flight that carry a callback, in submission order
@@ -1020,15 +1020,13 @@ void fec_engine_destroy(fec_engine* e)
     return;
   }
   cudaSetDevice(e->cfg.device);
-  if (!e->tb_threads.empty()) {
+  if (e->tb_thread.joinable()) {
     {
       std::lock_guard<std::mutex> lk(e->tb_mtx);
       e->tb_stop = true;
     }
     e->tb_cv.notify_all();
-    for (std::thread& t : e->tb_threads) {
-      t.join(); // finishes what is in flight first
-    }
+    e->tb_thread.join(); // finishes what is in flight first
   }
   cudaDeviceSynchronize();
   if (e->queues) {
@@ -2383,15 +2381,8 @@ int fec_tb_enqueue(fec_engine* e, const fec_tb_desc* tbs, uint32_t n, const uint
   *ticket       = P.ticket;
   if (callback != nullptr) {
     std::lock_guard<std::mutex> lk(e->tb_mtx);
-    if (e->tb_threads.empty()) {
-      // Several threads take the in-flight calls off the list: one thread hands a block over in 30-60 us (results, the copy
-      // of the block's bytes, the callback), which capped this interface at about 30 Gbit/s of config-3 blocks and made the
-      // latency of everything behind a slow hand-over grow. Calls are still taken in submission order; their callbacks may
-      // now run concurrently (they belong to different calls).
-      static const int nthreads = getenv("FEC_B200_TB_COMPLETION_THREADS") ? atoi(getenv("FEC_B200_TB_COMPLETION_THREADS")) : 3;
-      for (int k = 0; k < (nthreads < 1 ? 1 : nthreads); ++k) {
-        e->tb_threads.emplace_back(tb_completion_loop, e);
-      }
+    if (!e->tb_thread.joinable()) {
+      e->tb_thread = std::thread(tb_completion_loop, e);
     }
     e->tb_fifo.push_back(c);
     e->tb_cv.notify_one();
